@@ -1,0 +1,804 @@
+// beifong_b200 — C ABI (include/beifong_b200/abi.h): host scene object, flattening, upload, the
+// wavefront driver loop.  There is no CPU fallback behind this file: bf_scene_commit fails with
+// BF_ERR_CUDA when no device is usable and every compute entry point requires a committed scene.
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <chrono>
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "bf_wave.h"
+
+using namespace bf;
+
+namespace bf {
+
+M4 m4_inverse(const M4 &a) {
+    double inv[16], m[16];
+    for (int i = 0; i < 4; ++i) for (int j = 0; j < 4; ++j) m[i * 4 + j] = a.m[i][j];
+    inv[0] = m[5]*m[10]*m[15]-m[5]*m[11]*m[14]-m[9]*m[6]*m[15]+m[9]*m[7]*m[14]+m[13]*m[6]*m[11]-m[13]*m[7]*m[10];
+    inv[4] = -m[4]*m[10]*m[15]+m[4]*m[11]*m[14]+m[8]*m[6]*m[15]-m[8]*m[7]*m[14]-m[12]*m[6]*m[11]+m[12]*m[7]*m[10];
+    inv[8] = m[4]*m[9]*m[15]-m[4]*m[11]*m[13]-m[8]*m[5]*m[15]+m[8]*m[7]*m[13]+m[12]*m[5]*m[11]-m[12]*m[7]*m[9];
+    inv[12] = -m[4]*m[9]*m[14]+m[4]*m[10]*m[13]+m[8]*m[5]*m[14]-m[8]*m[6]*m[13]-m[12]*m[5]*m[10]+m[12]*m[6]*m[9];
+    inv[1] = -m[1]*m[10]*m[15]+m[1]*m[11]*m[14]+m[9]*m[2]*m[15]-m[9]*m[3]*m[14]-m[13]*m[2]*m[11]+m[13]*m[3]*m[10];
+    inv[5] = m[0]*m[10]*m[15]-m[0]*m[11]*m[14]-m[8]*m[2]*m[15]+m[8]*m[3]*m[14]+m[12]*m[2]*m[11]-m[12]*m[3]*m[10];
+    inv[9] = -m[0]*m[9]*m[15]+m[0]*m[11]*m[13]+m[8]*m[1]*m[15]-m[8]*m[3]*m[13]-m[12]*m[1]*m[11]+m[12]*m[3]*m[9];
+    inv[13] = m[0]*m[9]*m[14]-m[0]*m[10]*m[13]-m[8]*m[1]*m[14]+m[8]*m[2]*m[13]+m[12]*m[1]*m[10]-m[12]*m[2]*m[9];
+    inv[2] = m[1]*m[6]*m[15]-m[1]*m[7]*m[14]-m[5]*m[2]*m[15]+m[5]*m[3]*m[14]+m[13]*m[2]*m[7]-m[13]*m[3]*m[6];
+    inv[6] = -m[0]*m[6]*m[15]+m[0]*m[7]*m[14]+m[4]*m[2]*m[15]-m[4]*m[3]*m[14]-m[12]*m[2]*m[7]+m[12]*m[3]*m[6];
+    inv[10] = m[0]*m[5]*m[15]-m[0]*m[7]*m[13]-m[4]*m[1]*m[15]+m[4]*m[3]*m[13]+m[12]*m[1]*m[7]-m[12]*m[3]*m[5];
+    inv[14] = -m[0]*m[5]*m[14]+m[0]*m[6]*m[13]+m[4]*m[1]*m[14]-m[4]*m[2]*m[13]-m[12]*m[1]*m[6]+m[12]*m[2]*m[5];
+    inv[3] = -m[1]*m[6]*m[11]+m[1]*m[7]*m[10]+m[5]*m[2]*m[11]-m[5]*m[3]*m[10]-m[9]*m[2]*m[7]+m[9]*m[3]*m[6];
+    inv[7] = m[0]*m[6]*m[11]-m[0]*m[7]*m[10]-m[4]*m[2]*m[11]+m[4]*m[3]*m[10]+m[8]*m[2]*m[7]-m[8]*m[3]*m[6];
+    inv[11] = -m[0]*m[5]*m[11]+m[0]*m[7]*m[9]+m[4]*m[1]*m[11]-m[4]*m[3]*m[9]-m[8]*m[1]*m[7]+m[8]*m[3]*m[5];
+    inv[15] = m[0]*m[5]*m[10]-m[0]*m[6]*m[9]-m[4]*m[1]*m[10]+m[4]*m[2]*m[9]+m[8]*m[1]*m[6]-m[8]*m[2]*m[5];
+    double det = m[0]*inv[0]+m[1]*inv[4]+m[2]*inv[8]+m[3]*inv[12];
+    M4 r; double id = 1.0 / det;
+    for (int i = 0; i < 4; ++i) for (int j = 0; j < 4; ++j) r.m[i][j] = (float) (inv[i * 4 + j] * id);
+    return r;
+}
+
+// Rectangle::Rectangle / update (src/shapes/rectangle.cpp:75-95)
+DevRect make_rect(const float *to_world16, uint32_t shape) {
+    DevRect r;
+    memset(&r, 0, sizeof(r));
+    memcpy(r.to_world.m, to_world16, 64);
+    r.to_object = m4_inverse(r.to_world);
+    V3 dp_du = xf_vector(r.to_world, V3(2.f, 0.f, 0.f)), dp_dv = xf_vector(r.to_world, V3(0.f, 2.f, 0.f));
+    V3 normal = normalize(xf_normal(r.to_object, V3(0.f, 0.f, 1.f)));
+    r.fs = dp_du; r.ft = dp_dv; r.fn = normal;
+    r.area = norm(cross(r.fs, r.ft));
+    r.inv_area = rcp(r.area);
+    r.wid_x = norm(r.fs); r.wid_y = norm(r.ft);
+    r.ns = normalize(r.fs); r.nt = normalize(r.ft); r.nn = normalize(r.fn);
+    r.shape = shape;
+    return r;
+}
+
+}  // namespace bf
+
+struct HostShape { uint32_t type, index, bsdf; int32_t tx; };
+struct HostTx { int32_t shape; bf_endpoint_desc d; };
+
+template <typename T> struct DevBuf {
+    T *p = nullptr; size_t n = 0;
+    cudaError_t alloc(size_t count) {
+        if (count <= n && p) return cudaSuccess;
+        if (p) cudaFree(p);
+        p = nullptr; n = 0;
+        cudaError_t e = cudaMalloc((void **) &p, std::max<size_t>(count, 1) * sizeof(T));
+        if (e == cudaSuccess) n = count;
+        return e;
+    }
+    void release() { if (p) cudaFree(p); p = nullptr; n = 0; }
+};
+
+struct bf_scene {
+    bf_constants C;
+    std::vector<HostSpectrum> spectra;
+    std::vector<bf_bsdf_desc> bsdfs;
+    std::vector<HostMesh> meshes;
+    std::vector<DevRect> rects;
+    std::vector<HostShape> shapes;
+    std::vector<HostTx> txs;
+    int32_t rx_shape = -1; bf_endpoint_desc rx; bool has_rx = false;
+    bf_adc_desc adc; bool has_adc = false;
+    bf_integrator_desc integ; bool has_integ = false;
+    std::vector<uint8_t> blob;        // recorded construction calls (flat_scene.h)
+    std::string err;
+
+    // device side
+    bool committed = false, tables_dirty = false;
+    int device = 0, sm_count = 148;
+    cudaStream_t stream = nullptr;
+    DevScene dev;
+    DevBuf<uint4> d_nodes; DevBuf<float4> d_tris, d_tri_nrm;
+    DevBuf<DevRect> d_rects; DevBuf<DevShape> d_shapes; DevBuf<bf_bsdf_desc> d_bsdfs;
+    DevBuf<DevSpectrum> d_spectra; DevBuf<float> d_spec_pool; DevBuf<DevEndpoint> d_txs, d_rx;
+    DevBuf<float> d_profile; size_t profile_floats = 0;
+    // image of the geometry tables in pinned host memory (re-upload without a rebuild)
+    void *h_geom = nullptr; size_t h_geom_bytes = 0, h_nodes_bytes = 0, h_tris_bytes = 0, h_nrm_bytes = 0;
+    // wave
+    Wave wave; uint32_t wave_capacity = 0; std::vector<void *> wave_allocs;
+    DevBuf<uint32_t> d_counters; DevBuf<unsigned long long> d_totals;
+    uint32_t *h_counts = nullptr;     // pinned read-back of queue counts
+    // stats / timing
+    bf_stats stats;
+    cudaEvent_t ev_begin = nullptr, ev_end = nullptr;
+    std::vector<cudaEvent_t> ev_trace; size_t ev_trace_used = 0;
+    bool time_trace = false;
+};
+
+static thread_local std::string g_create_error;
+
+static int fail(bf_scene *s, int code, const std::string &msg) {
+    if (s) s->err = msg; else g_create_error = msg;
+    return code;
+}
+#define BF_CUDA(call)                                                                                   \
+    do {                                                                                                \
+        cudaError_t e__ = (call);                                                                       \
+        if (e__ != cudaSuccess)                                                                         \
+            return fail(s, BF_ERR_CUDA, std::string(#call) + ": " + cudaGetErrorString(e__));           \
+    } while (0)
+
+static void record(bf_scene *s, uint32_t tag, const void *a, size_t na, const void *b = nullptr, size_t nb = 0,
+                   const void *c = nullptr, size_t nc = 0, const void *d = nullptr, size_t nd = 0) {
+    bf_flat_record r; r.tag = tag; r.reserved = 0; r.payload_bytes = na + nb + nc + nd;
+    size_t off = s->blob.size();
+    size_t padded = (r.payload_bytes + 7) & ~(size_t) 7;
+    s->blob.resize(off + sizeof(r) + padded, 0);
+    memcpy(s->blob.data() + off, &r, sizeof(r));
+    uint8_t *p = s->blob.data() + off + sizeof(r);
+    if (na) memcpy(p, a, na); p += na;
+    if (nb) memcpy(p, b, nb); p += nb;
+    if (nc) memcpy(p, c, nc); p += nc;
+    if (nd) memcpy(p, d, nd);
+}
+
+static uint32_t n_channels(const bf_scene *s) {
+    if (s->integ.gen == BF_GEN_PHASE) return 3 + s->integ.phase_bins;
+    if (s->integ.gen == BF_GEN_RANGE) return 5 + s->integ.range_bins;
+    return 5 + 50 * 3;
+}
+static void film_size(const bf_scene *s, uint32_t &w, uint32_t &h) {
+    if (s->integ.gen == BF_GEN_PHASE) { w = s->adc.window_t_bins; h = s->adc.window_f_bins; }
+    else { w = s->rx.film_width ? s->rx.film_width : 1; h = s->rx.film_height ? s->rx.film_height : 1; }
+}
+
+static DevEndpoint make_endpoint(const bf_endpoint_desc &d, int32_t shape) {
+    DevEndpoint e;
+    memset(&e, 0, sizeof(e));
+    e.kind = d.kind; e.texture = d.texture; e.receive_type = d.receive_type; e.shape = shape;
+    e.signal = d.signal;
+    e.adc_sampling_start = d.adc_sampling_start; e.adc_sampling_time = d.adc_sampling_time;
+    e.near_clip = d.near_clip; e.far_clip = d.far_clip;
+    e.shutter_open = d.shutter_open; e.shutter_open_time = d.shutter_open_time;
+    e.film_width = d.film_width; e.film_height = d.film_height;
+    memcpy(e.to_world.m, d.to_world, 64);
+    bool identity_ok = false;
+    for (int i = 0; i < 16; ++i) if (d.to_world[i] != 0.f) identity_ok = true;
+    if (!identity_ok) { for (int i = 0; i < 4; ++i) e.to_world.m[i][i] = 1.f; }
+    e.to_object = m4_inverse(e.to_world);
+    memcpy(e.sample_to_camera.m, d.sample_to_camera, 64);
+    // spot.cpp:85-93
+    float cutoff = d.cutoff_angle_deg * (BF_PI / 180.f), beam = d.beam_width_deg * (BF_PI / 180.f);
+    e.cutoff = cutoff;
+    e.inv_transition = 1.0f / (cutoff - beam);
+    e.cos_cutoff = cosf(cutoff);
+    e.cos_beam = cosf(beam);
+    return e;
+}
+
+extern "C" {
+
+uint32_t bf_abi_version(void) { return BF_ABI_VERSION; }
+
+int bf_scene_create(const bf_constants *consts, bf_scene **out) {
+    if (!consts || !out) return fail(nullptr, BF_ERR_INVALID, "bf_scene_create: null argument");
+    if (consts->spectrum_width != 1 && consts->spectrum_width != 4)
+        return fail(nullptr, BF_ERR_UNSUPPORTED, "bf_scene_create: spectrum_width must be 1 (mono) or 4 (spectral)");
+    if (!(consts->c > 0.f)) return fail(nullptr, BF_ERR_INVALID, "bf_scene_create: propagation speed must be positive");
+    bf_scene *s = new bf_scene();
+    s->C = *consts;
+    memset(&s->rx, 0, sizeof(s->rx)); memset(&s->adc, 0, sizeof(s->adc)); memset(&s->integ, 0, sizeof(s->integ));
+    memset(&s->stats, 0, sizeof(s->stats)); memset(&s->wave, 0, sizeof(s->wave)); memset(&s->dev, 0, sizeof(s->dev));
+    *out = s;
+    return BF_OK;
+}
+
+static void free_wave(bf_scene *s) {
+    for (void *p : s->wave_allocs) cudaFree(p);
+    s->wave_allocs.clear();
+    memset(&s->wave, 0, sizeof(s->wave));
+    s->wave_capacity = 0;
+}
+
+void bf_scene_destroy(bf_scene *s) {
+    if (!s) return;
+    if (s->committed) {
+        cudaSetDevice(s->device);
+        if (s->stream) cudaStreamSynchronize(s->stream);
+        free_wave(s);
+        s->d_nodes.release(); s->d_tris.release(); s->d_tri_nrm.release(); s->d_rects.release(); s->d_shapes.release();
+        s->d_bsdfs.release(); s->d_spectra.release(); s->d_spec_pool.release(); s->d_txs.release(); s->d_rx.release();
+        s->d_profile.release(); s->d_counters.release(); s->d_totals.release();
+        if (s->h_geom) cudaFreeHost(s->h_geom);
+        if (s->h_counts) cudaFreeHost(s->h_counts);
+        if (s->ev_begin) cudaEventDestroy(s->ev_begin);
+        if (s->ev_end) cudaEventDestroy(s->ev_end);
+        for (cudaEvent_t e : s->ev_trace) cudaEventDestroy(e);
+        if (s->stream) cudaStreamDestroy(s->stream);
+    }
+    delete s;
+}
+
+const char *bf_last_error(const bf_scene *s) { return s ? s->err.c_str() : g_create_error.c_str(); }
+
+int bf_scene_add_spectrum(bf_scene *s, uint32_t kind, uint32_t n, const float *lambda_nm, const float *values, uint32_t *spectrum_id) {
+    if (!s || !values || n == 0) return fail(s, BF_ERR_INVALID, "bf_scene_add_spectrum: null / empty");
+    if (kind > BF_SPEC_ZERO_OUTSIDE_VISIBLE) return fail(s, BF_ERR_UNSUPPORTED, "bf_scene_add_spectrum: unknown kind");
+    if ((kind == BF_SPEC_REGULAR || kind == BF_SPEC_IRREGULAR) && (n < 2 || !lambda_nm))
+        return fail(s, BF_ERR_INVALID, "bf_scene_add_spectrum: tabulated spectra need >= 2 nodes with wavelengths");
+    HostSpectrum t; t.kind = kind;
+    t.value.assign(values, values + n);
+    if (lambda_nm) t.lambda.assign(lambda_nm, lambda_nm + n); else t.lambda.assign(n, 0.f);
+    if (kind == BF_SPEC_IRREGULAR)
+        for (uint32_t i = 1; i < n; ++i)
+            if (!(t.lambda[i] > t.lambda[i - 1])) return fail(s, BF_ERR_INVALID, "bf_scene_add_spectrum: wavelengths must increase");
+    uint32_t hdr[2] = {kind, n};
+    record(s, BF_TAG_SPECTRUM, hdr, 8, t.lambda.data(), 4 * (size_t) n, t.value.data(), 4 * (size_t) n);
+    if (spectrum_id) *spectrum_id = (uint32_t) s->spectra.size();
+    s->spectra.push_back(std::move(t));
+    s->tables_dirty = true;
+    return BF_OK;
+}
+
+int bf_scene_add_bsdf(bf_scene *s, const bf_bsdf_desc *desc, uint32_t *bsdf_id) {
+    if (!s || !desc) return fail(s, BF_ERR_INVALID, "bf_scene_add_bsdf: null");
+    if (desc->kind > BF_BSDF_NULL_BLACK) return fail(s, BF_ERR_UNSUPPORTED, "bf_scene_add_bsdf: BSDF plugin outside the radar path (supported: diffuse, roughconductor, conductor, twosided)");
+    auto spec_ok = [&](uint32_t id) { return id < s->spectra.size(); };
+    if (desc->kind == BF_BSDF_DIFFUSE && !spec_ok(desc->reflectance)) return fail(s, BF_ERR_INVALID, "bf_scene_add_bsdf: reflectance spectrum id out of range");
+    if ((desc->kind == BF_BSDF_ROUGHCONDUCTOR || desc->kind == BF_BSDF_CONDUCTOR) && (!spec_ok(desc->eta) || !spec_ok(desc->k)))
+        return fail(s, BF_ERR_INVALID, "bf_scene_add_bsdf: eta / k spectrum id out of range");
+    if (desc->specular_reflectance != BF_NONE && !spec_ok(desc->specular_reflectance)) return fail(s, BF_ERR_INVALID, "bf_scene_add_bsdf: specular_reflectance id out of range");
+    if (desc->back_bsdf != BF_NONE && desc->back_bsdf >= s->bsdfs.size()) return fail(s, BF_ERR_INVALID, "bf_scene_add_bsdf: back_bsdf id out of range");
+    record(s, BF_TAG_BSDF, desc, sizeof(*desc));
+    if (bsdf_id) *bsdf_id = (uint32_t) s->bsdfs.size();
+    s->bsdfs.push_back(*desc);
+    s->tables_dirty = true;
+    return BF_OK;
+}
+
+int bf_scene_add_mesh(bf_scene *s, const float *positions, uint32_t n_vertices, const uint32_t *faces, uint32_t n_faces,
+                      const float *normals, uint32_t bsdf_id, uint32_t *shape_id) {
+    if (!s || !positions || !faces) return fail(s, BF_ERR_INVALID, "bf_scene_add_mesh: null");
+    if (bsdf_id >= s->bsdfs.size()) return fail(s, BF_ERR_INVALID, "bf_scene_add_mesh: bsdf id out of range");
+    if (s->committed) return fail(s, BF_ERR_STATE, "bf_scene_add_mesh: scene already committed");
+    for (size_t i = 0; i < 3 * (size_t) n_faces; ++i)
+        if (faces[i] >= n_vertices) return fail(s, BF_ERR_INVALID, "bf_scene_add_mesh: face index out of range");
+    HostMesh m; m.nv = n_vertices; m.nf = n_faces;
+    m.pos.assign(positions, positions + 3 * (size_t) n_vertices);
+    m.idx.assign(faces, faces + 3 * (size_t) n_faces);
+    if (normals) m.nrm.assign(normals, normals + 3 * (size_t) n_vertices);
+    uint32_t hdr[4] = {n_vertices, n_faces, bsdf_id, normals ? 1u : 0u};
+    record(s, BF_TAG_MESH, hdr, 16, m.pos.data(), 4 * m.pos.size(), m.idx.data(), 4 * m.idx.size(), normals ? m.nrm.data() : nullptr, normals ? 4 * m.nrm.size() : 0);
+    HostShape sh; sh.type = 0; sh.index = (uint32_t) s->meshes.size(); sh.bsdf = bsdf_id; sh.tx = -1;
+    if (shape_id) *shape_id = (uint32_t) s->shapes.size();
+    s->meshes.push_back(std::move(m));
+    s->shapes.push_back(sh);
+    return BF_OK;
+}
+
+int bf_scene_add_rect(bf_scene *s, const float to_world[16], uint32_t bsdf_id, uint32_t *shape_id) {
+    if (!s || !to_world) return fail(s, BF_ERR_INVALID, "bf_scene_add_rect: null");
+    if (bsdf_id >= s->bsdfs.size()) return fail(s, BF_ERR_INVALID, "bf_scene_add_rect: bsdf id out of range");
+    if (s->committed) return fail(s, BF_ERR_STATE, "bf_scene_add_rect: scene already committed (use bf_scene_update_rect)");
+    if (s->rects.size() >= BF_MAX_RECTS) return fail(s, BF_ERR_UNSUPPORTED, "bf_scene_add_rect: more than 64 analytic rectangles");
+    uint32_t tail[2] = {bsdf_id, 0};
+    record(s, BF_TAG_RECT, to_world, 64, tail, 8);
+    HostShape sh; sh.type = 1; sh.index = (uint32_t) s->rects.size(); sh.bsdf = bsdf_id; sh.tx = -1;
+    uint32_t id = (uint32_t) s->shapes.size();
+    s->rects.push_back(make_rect(to_world, id));
+    s->shapes.push_back(sh);
+    if (shape_id) *shape_id = id;
+    return BF_OK;
+}
+
+static int check_endpoint(bf_scene *s, uint32_t shape_id, const bf_endpoint_desc *d, bool is_tx) {
+    if (!d) return fail(s, BF_ERR_INVALID, "endpoint: null descriptor");
+    bool free_standing = is_tx ? d->kind == BF_TX_SPOT : d->kind == BF_RX_PERSPECTIVE;
+    if (is_tx && d->kind == BF_TX_PHASED) return fail(s, BF_ERR_UNSUPPORTED, "phasedtransmitter is not on the accelerated path yet");
+    if (!is_tx && d->kind == BF_RX_PHASED) return fail(s, BF_ERR_UNSUPPORTED, "phasedreceiver is not on the accelerated path yet");
+    if (is_tx && d->kind > BF_TX_AREALIGHT) return fail(s, BF_ERR_UNSUPPORTED, "unknown transmitter kind");
+    if (!is_tx && d->kind > BF_RX_PERSPECTIVE) return fail(s, BF_ERR_UNSUPPORTED, "unknown receiver kind");
+    if (!free_standing) {
+        if (shape_id >= s->shapes.size()) return fail(s, BF_ERR_INVALID, "endpoint: shape id out of range");
+        if (s->shapes[shape_id].type != 1) return fail(s, BF_ERR_UNSUPPORTED, "endpoint: only rectangle apertures are supported (every radar scene of the reference uses rectangles)");
+    }
+    if (is_tx && d->texture >= s->spectra.size()) return fail(s, BF_ERR_INVALID, "endpoint: texture spectrum id out of range");
+    return BF_OK;
+}
+
+int bf_scene_add_transmitter(bf_scene *s, uint32_t shape_id, const bf_endpoint_desc *desc, uint32_t *transmitter_id) {
+    if (!s) return BF_ERR_INVALID;
+    int rc = check_endpoint(s, shape_id, desc, true);
+    if (rc) return rc;
+    HostTx t; t.shape = desc->kind == BF_TX_SPOT ? -1 : (int32_t) shape_id; t.d = *desc;
+    uint32_t hdr[2] = {t.shape < 0 ? BF_NONE : shape_id, 0};
+    record(s, BF_TAG_TX, hdr, 8, desc, sizeof(*desc));
+    if (t.shape >= 0) s->shapes[shape_id].tx = (int32_t) s->txs.size();
+    if (transmitter_id) *transmitter_id = (uint32_t) s->txs.size();
+    s->txs.push_back(t);
+    s->tables_dirty = true;
+    return BF_OK;
+}
+
+int bf_scene_set_receiver(bf_scene *s, uint32_t shape_id, const bf_endpoint_desc *desc) {
+    if (!s) return BF_ERR_INVALID;
+    int rc = check_endpoint(s, shape_id, desc, false);
+    if (rc) return rc;
+    s->rx = *desc; s->has_rx = true;
+    s->rx_shape = desc->kind == BF_RX_PERSPECTIVE ? -1 : (int32_t) shape_id;
+    uint32_t hdr[2] = {s->rx_shape < 0 ? BF_NONE : shape_id, 0};
+    record(s, BF_TAG_RX, hdr, 8, desc, sizeof(*desc));
+    s->tables_dirty = true;
+    return BF_OK;
+}
+
+int bf_scene_set_adc(bf_scene *s, const bf_adc_desc *desc) {
+    if (!s || !desc) return fail(s, BF_ERR_INVALID, "bf_scene_set_adc: null");
+    if (desc->t_bins == 0 || desc->f_bins == 0 || desc->window_t_bins == 0 || desc->window_f_bins == 0)
+        return fail(s, BF_ERR_INVALID, "bf_scene_set_adc: zero-sized ADC");
+    if (!(desc->t_bandwidth > 0.f) || !(desc->f_bandwidth > 0.f)) return fail(s, BF_ERR_INVALID, "bf_scene_set_adc: bandwidths must be positive");
+    // Receivers warn when the reconstruction filter is wider than one bin (phasedreceiver.cpp:59-62);
+    // the accelerated path implements the single-bin branch of SignalBlock::put (signalblock.cpp:162-169).
+    if (desc->filter_radius > 0.5f + BF_RAY_EPS) return fail(s, BF_ERR_UNSUPPORTED, "bf_scene_set_adc: reconstruction filters wider than box/0.5 are not on the accelerated path");
+    if (s->committed) return fail(s, BF_ERR_STATE, "bf_scene_set_adc: scene already committed");
+    s->adc = *desc; s->has_adc = true;
+    record(s, BF_TAG_ADC, desc, sizeof(*desc));
+    return BF_OK;
+}
+
+int bf_scene_set_integrator(bf_scene *s, const bf_integrator_desc *desc) {
+    if (!s || !desc) return fail(s, BF_ERR_INVALID, "bf_scene_set_integrator: null");
+    if (desc->gen < BF_GEN_TIME || desc->gen > BF_GEN_PHASE) return fail(s, BF_ERR_UNSUPPORTED, "bf_scene_set_integrator: gen must be 1 (time), 2 (range) or 3 (phase)");
+    if (desc->rng_mode != 0) return fail(s, BF_ERR_UNSUPPORTED, "bf_scene_set_integrator: only per-sample PCG32 streams (rng_mode 0) run on the GPU");
+    if (desc->max_depth == 0 || desc->max_depth < -1) return fail(s, BF_ERR_INVALID, "bf_scene_set_integrator: max_depth must be -1 or > 0 (integrator.cpp:1713-1720)");
+    if (desc->gen == BF_GEN_RANGE && !(desc->dr > 0.f)) return fail(s, BF_ERR_INVALID, "bf_scene_set_integrator: range integrator needs dr > 0");
+    if (s->committed) return fail(s, BF_ERR_STATE, "bf_scene_set_integrator: scene already committed");
+    s->integ = *desc; s->has_integ = true;
+    record(s, BF_TAG_INTEGRATOR, desc, sizeof(*desc));
+    return BF_OK;
+}
+
+int bf_profile_size(const bf_scene *s, uint32_t *width, uint32_t *height, uint32_t *channels) {
+    if (!s || !s->has_integ || !s->has_rx) return BF_ERR_STATE;
+    if (s->integ.gen == BF_GEN_PHASE && !s->has_adc) return BF_ERR_STATE;
+    uint32_t w, h; film_size(s, w, h);
+    if (width) *width = w;
+    if (height) *height = h;
+    if (channels) *channels = n_channels(s);
+    return BF_OK;
+}
+int bf_profile_channels(const bf_scene *s, uint32_t *channels) { return bf_profile_size(s, nullptr, nullptr, channels); }
+
+int bf_scene_export(const bf_scene *s, void *dst, size_t capacity, size_t *required) {
+    if (!s) return BF_ERR_INVALID;
+    size_t total = sizeof(bf_flat_header) + s->blob.size();
+    if (required) *required = total;
+    if (!dst) return BF_OK;
+    if (capacity < total) return BF_ERR_INVALID;
+    bf_flat_header h; h.magic = BF_FLAT_MAGIC; h.abi_version = BF_ABI_VERSION; h.total_bytes = total; h.consts = s->C;
+    memcpy(dst, &h, sizeof(h));
+    if (!s->blob.empty()) memcpy((uint8_t *) dst + sizeof(h), s->blob.data(), s->blob.size());
+    return BF_OK;
+}
+
+// ---- upload ---------------------------------------------------------------------------------------------
+static int upload_tables(bf_scene *s) {
+    // spectra
+    std::vector<DevSpectrum> ds; std::vector<float> pool;
+    for (const HostSpectrum &t : s->spectra) {
+        DevSpectrum d; d.kind = t.kind; d.n = (uint32_t) t.value.size(); d.offset = (uint32_t) pool.size(); d.inv_interval = 0.f;
+        if (t.kind == BF_SPEC_REGULAR && d.n >= 2) {
+            double interval = ((double) t.lambda.back() - (double) t.lambda.front()) / (double) (d.n - 1);
+            d.inv_interval = (float) (1.0 / interval);
+        }
+        pool.insert(pool.end(), t.lambda.begin(), t.lambda.end());
+        pool.insert(pool.end(), t.value.begin(), t.value.end());
+        ds.push_back(d);
+    }
+    std::vector<DevShape> sh(s->shapes.size());
+    for (size_t i = 0; i < sh.size(); ++i) {
+        memset(&sh[i], 0, sizeof(DevShape));
+        sh[i].type = s->shapes[i].type; sh[i].index = s->shapes[i].index; sh[i].bsdf = s->shapes[i].bsdf; sh[i].tx = s->shapes[i].tx;
+        sh[i].has_normals = s->shapes[i].type == 0 && !s->meshes[s->shapes[i].index].nrm.empty();
+    }
+    std::vector<DevEndpoint> txs;
+    for (const HostTx &t : s->txs) txs.push_back(make_endpoint(t.d, t.shape));
+    DevEndpoint rx = make_endpoint(s->rx, s->rx_shape);
+
+    BF_CUDA(s->d_spectra.alloc(ds.size())); BF_CUDA(s->d_spec_pool.alloc(pool.size()));
+    BF_CUDA(s->d_shapes.alloc(sh.size())); BF_CUDA(s->d_bsdfs.alloc(s->bsdfs.size()));
+    BF_CUDA(s->d_rects.alloc(s->rects.size())); BF_CUDA(s->d_txs.alloc(txs.size())); BF_CUDA(s->d_rx.alloc(1));
+    BF_CUDA(cudaStreamSynchronize(s->stream));
+    if (!ds.empty()) BF_CUDA(cudaMemcpy(s->d_spectra.p, ds.data(), ds.size() * sizeof(DevSpectrum), cudaMemcpyHostToDevice));
+    if (!pool.empty()) BF_CUDA(cudaMemcpy(s->d_spec_pool.p, pool.data(), pool.size() * 4, cudaMemcpyHostToDevice));
+    if (!sh.empty()) BF_CUDA(cudaMemcpy(s->d_shapes.p, sh.data(), sh.size() * sizeof(DevShape), cudaMemcpyHostToDevice));
+    if (!s->bsdfs.empty()) BF_CUDA(cudaMemcpy(s->d_bsdfs.p, s->bsdfs.data(), s->bsdfs.size() * sizeof(bf_bsdf_desc), cudaMemcpyHostToDevice));
+    if (!s->rects.empty()) BF_CUDA(cudaMemcpy(s->d_rects.p, s->rects.data(), s->rects.size() * sizeof(DevRect), cudaMemcpyHostToDevice));
+    if (!txs.empty()) BF_CUDA(cudaMemcpy(s->d_txs.p, txs.data(), txs.size() * sizeof(DevEndpoint), cudaMemcpyHostToDevice));
+    BF_CUDA(cudaMemcpy(s->d_rx.p, &rx, sizeof(rx), cudaMemcpyHostToDevice));
+
+    DevScene &d = s->dev;
+    d.C = s->C; d.S = s->C.spectrum_width;
+    d.n_rects = (uint32_t) s->rects.size(); d.n_shapes = (uint32_t) sh.size(); d.n_txs = (uint32_t) txs.size();
+    d.rects = s->d_rects.p; d.shapes = s->d_shapes.p; d.bsdfs = s->d_bsdfs.p; d.spectra = s->d_spectra.p;
+    d.spec_pool = s->d_spec_pool.p; d.txs = s->d_txs.p; d.rx = s->d_rx.p;
+    d.adc = s->adc; d.integ = s->integ;
+    film_size(s, d.film_w, d.film_h); d.channels = n_channels(s);
+    d.rx_needs_aperture = s->rx.kind != BF_RX_PERSPECTIVE;   // Sensor::needs_aperture_sample
+    d.phase_denom = (double) ((s->C.lambda_max_nm - s->C.lambda_min_nm) / 2) * 1e-9;
+    s->tables_dirty = false;
+    return BF_OK;
+}
+
+// Copy the pinned image of the geometry tables (nodes, triangles, normals) to the device.
+static int upload_geometry(bf_scene *s) {
+    const uint8_t *h = (const uint8_t *) s->h_geom;
+    if (s->h_nodes_bytes) BF_CUDA(cudaMemcpyAsync(s->d_nodes.p, h, s->h_nodes_bytes, cudaMemcpyHostToDevice, s->stream));
+    if (s->h_tris_bytes) BF_CUDA(cudaMemcpyAsync(s->d_tris.p, h + s->h_nodes_bytes, s->h_tris_bytes, cudaMemcpyHostToDevice, s->stream));
+    if (s->h_nrm_bytes) BF_CUDA(cudaMemcpyAsync(s->d_tri_nrm.p, h + s->h_nodes_bytes + s->h_tris_bytes, s->h_nrm_bytes, cudaMemcpyHostToDevice, s->stream));
+    return BF_OK;
+}
+
+int bf_scene_commit(bf_scene *s, int device) {
+    if (!s) return BF_ERR_INVALID;
+    if (!s->has_rx) return fail(s, BF_ERR_STATE, "bf_scene_commit: no receiver / sensor set");
+    if (!s->has_integ) return fail(s, BF_ERR_STATE, "bf_scene_commit: no integrator set");
+    if (s->integ.gen == BF_GEN_PHASE && !s->has_adc) return fail(s, BF_ERR_STATE, "bf_scene_commit: phase integrator needs an ADC");
+    if (s->committed) return fail(s, BF_ERR_STATE, "bf_scene_commit: already committed");
+    int n_dev = 0;
+    cudaError_t e = cudaGetDeviceCount(&n_dev);
+    if (e != cudaSuccess || n_dev == 0)
+        return fail(s, BF_ERR_CUDA, std::string("bf_scene_commit: no CUDA device (") + cudaGetErrorString(e) + "); there is no CPU fallback");
+    if (device < 0 || device >= n_dev) return fail(s, BF_ERR_INVALID, "bf_scene_commit: device index out of range");
+    BF_CUDA(cudaSetDevice(device));
+    s->device = device;
+    cudaDeviceProp prop;
+    BF_CUDA(cudaGetDeviceProperties(&prop, device));
+    s->sm_count = prop.multiProcessorCount;
+    BF_CUDA(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
+    BF_CUDA(cudaEventCreate(&s->ev_begin)); BF_CUDA(cudaEventCreate(&s->ev_end));
+
+    // ---- BVH over all mesh triangles, shape order ----
+    auto t0 = std::chrono::steady_clock::now();
+    std::vector<BvhTriIn> tris;
+    float scene_abs = 0.f;
+    for (size_t si = 0; si < s->shapes.size(); ++si) {
+        if (s->shapes[si].type != 0) continue;
+        const HostMesh &m = s->meshes[s->shapes[si].index];
+        for (uint32_t f = 0; f < m.nf; ++f) {
+            BvhTriIn t; t.shape = (uint32_t) si; t.prim = f;
+            for (int k = 0; k < 3; ++k) {
+                uint32_t vi = m.idx[3 * (size_t) f + k];
+                float *dst = k == 0 ? t.p0 : (k == 1 ? t.p1 : t.p2);
+                for (int a = 0; a < 3; ++a) { dst[a] = m.pos[3 * (size_t) vi + a]; scene_abs = std::max(scene_abs, std::fabs(dst[a])); }
+            }
+            tris.push_back(t);
+        }
+    }
+    for (const DevRect &r : s->rects)
+        for (int a = 0; a < 3; ++a)
+            scene_abs = std::max(scene_abs, std::fabs(r.to_world.m[a][3]) + std::fabs(r.to_world.m[a][0]) + std::fabs(r.to_world.m[a][1]));
+    WideBvh bvh;
+    build_wide_bvh(tris, 4e-6f * std::max(scene_abs, 1e-3f), bvh);
+    if (bvh.stats.depth > BF_TRACE_STACK_DEPTH)
+        return fail(s, BF_ERR_UNSUPPORTED, "bf_scene_commit: BVH deeper than the traversal stack");
+    bool any_normals = false;
+    for (const HostMesh &m : s->meshes) any_normals |= !m.nrm.empty();
+    s->h_nodes_bytes = bvh.nodes.size() * 4; s->h_tris_bytes = bvh.tris.size() * 4;
+    s->h_nrm_bytes = any_normals ? bvh.tris.size() * 4 : 0;
+    s->h_geom_bytes = s->h_nodes_bytes + s->h_tris_bytes + s->h_nrm_bytes;
+    BF_CUDA(cudaMallocHost(&s->h_geom, std::max<size_t>(s->h_geom_bytes, 16)));
+    uint8_t *hg = (uint8_t *) s->h_geom;
+    if (s->h_nodes_bytes) memcpy(hg, bvh.nodes.data(), s->h_nodes_bytes);
+    if (s->h_tris_bytes) memcpy(hg + s->h_nodes_bytes, bvh.tris.data(), s->h_tris_bytes);
+    if (any_normals) {
+        float *nr = (float *) (hg + s->h_nodes_bytes + s->h_tris_bytes);
+        for (size_t slot = 0; slot < bvh.tri_src.size(); ++slot) {
+            const BvhTriIn &t = tris[bvh.tri_src[slot]];
+            const HostMesh &m = s->meshes[s->shapes[t.shape].index];
+            for (int k = 0; k < 3; ++k) {
+                float *dst = nr + 12 * slot + 4 * k;
+                if (m.nrm.empty()) { dst[0] = dst[1] = dst[2] = 0.f; }
+                else { uint32_t vi = m.idx[3 * (size_t) t.prim + k]; dst[0] = m.nrm[3 * (size_t) vi]; dst[1] = m.nrm[3 * (size_t) vi + 1]; dst[2] = m.nrm[3 * (size_t) vi + 2]; }
+                dst[3] = 0.f;
+            }
+        }
+    }
+    s->stats.build_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+    s->stats.bvh_nodes = bvh.stats.n_nodes; s->stats.bvh_tris = bvh.stats.n_tris; s->stats.bvh_depth = bvh.stats.depth;
+    s->stats.n_rects = (uint32_t) s->rects.size();
+
+    auto t1 = std::chrono::steady_clock::now();
+    BF_CUDA(s->d_nodes.alloc(bvh.nodes.size() / 4)); BF_CUDA(s->d_tris.alloc(bvh.tris.size() / 4));
+    if (any_normals) BF_CUDA(s->d_tri_nrm.alloc(bvh.tris.size() / 4));
+    int rc = upload_geometry(s);
+    if (rc) return rc;
+    rc = upload_tables(s);
+    if (rc) return rc;
+    s->dev.nodes = s->d_nodes.p; s->dev.tris = s->d_tris.p; s->dev.tri_nrm = any_normals ? s->d_tri_nrm.p : nullptr;
+    s->dev.n_nodes = bvh.stats.n_nodes; s->dev.n_tris = bvh.stats.n_tris;
+
+    s->profile_floats = (size_t) s->dev.film_w * s->dev.film_h * s->dev.channels;
+    BF_CUDA(s->d_profile.alloc(s->profile_floats));
+    BF_CUDA(cudaMemsetAsync(s->d_profile.p, 0, s->profile_floats * 4, s->stream));
+    BF_CUDA(s->d_counters.alloc(BF_CTR_STRIDE * (BF_MAX_BOUNCES + 2)));
+    BF_CUDA(s->d_totals.alloc(2));
+    BF_CUDA(cudaMemsetAsync(s->d_totals.p, 0, 16, s->stream));
+    BF_CUDA(cudaMallocHost((void **) &s->h_counts, 64));
+    BF_CUDA(cudaStreamSynchronize(s->stream));
+    s->stats.upload_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t1).count();
+    s->committed = true;
+    return BF_OK;
+}
+
+int bf_scene_reupload(bf_scene *s) {
+    if (!s || !s->committed) return fail(s, BF_ERR_STATE, "bf_scene_reupload: scene not committed");
+    BF_CUDA(cudaSetDevice(s->device));
+    int rc = upload_geometry(s);
+    if (rc) return rc;
+    return upload_tables(s);
+}
+
+int bf_scene_device_bytes(const bf_scene *s, size_t *geometry_bytes) {
+    if (!s || !s->committed) return BF_ERR_STATE;
+    if (geometry_bytes) *geometry_bytes = s->h_geom_bytes;
+    return BF_OK;
+}
+
+int bf_scene_update_rect(bf_scene *s, uint32_t shape_id, const float to_world[16]) {
+    if (!s || !to_world) return BF_ERR_INVALID;
+    if (shape_id >= s->shapes.size() || s->shapes[shape_id].type != 1) return fail(s, BF_ERR_INVALID, "bf_scene_update_rect: not a rectangle");
+    s->rects[s->shapes[shape_id].index] = make_rect(to_world, shape_id);
+    s->tables_dirty = true;
+    return BF_OK;
+}
+
+// ---- wave allocation ------------------------------------------------------------------------------------
+static uint32_t wave_lanes_default() {
+    const char *e = getenv("BF_WAVE_LANES");
+    if (e) { long v = atol(e); if (v >= 1024) return (uint32_t) v; }
+    return 1u << 21;
+}
+
+static int ensure_wave(bf_scene *s, uint32_t lanes, bool records) {
+    if (s->wave_capacity >= lanes && (!records || s->wave.records)) return BF_OK;
+    BF_CUDA(cudaStreamSynchronize(s->stream));
+    free_wave(s);
+    auto A = [&](void **p, size_t bytes) -> cudaError_t {
+        cudaError_t e = cudaMalloc(p, bytes);
+        if (e == cudaSuccess) s->wave_allocs.push_back(*p);
+        return e;
+    };
+    Wave &w = s->wave;
+    size_t n = lanes;
+    BF_CUDA(A((void **) &w.ray_o, n * 16)); BF_CUDA(A((void **) &w.ray_d, n * 16)); BF_CUDA(A((void **) &w.sh_d, n * 16));
+    BF_CUDA(A((void **) &w.hit, n * 16)); BF_CUDA(A((void **) &w.occl, n * 4)); BF_CUDA(A((void **) &w.rng, n * 16));
+    BF_CUDA(A((void **) &w.x1, n * 16)); BF_CUDA(A((void **) &w.x2, n * 16));
+    int n_spec = s->C.spectrum_width == 1 ? 1 : 5;
+    for (int k = 0; k < n_spec; ++k) BF_CUDA(A((void **) &w.spec[k], n * 16));
+    BF_CUDA(A((void **) &w.flags, n * 4));
+    BF_CUDA(A((void **) &w.queue[0], n * 4)); BF_CUDA(A((void **) &w.queue[1], n * 4)); BF_CUDA(A((void **) &w.queue_s, n * 4));
+    if (records) BF_CUDA(A((void **) &w.records, n * sizeof(bf_sample_record)));
+    w.capacity = lanes;
+    w.counters = s->d_counters.p;
+    w.totals = s->d_totals.p;
+    s->wave_capacity = lanes;
+    return BF_OK;
+}
+
+static cudaEvent_t next_trace_event(bf_scene *s) {
+    if (s->ev_trace_used == s->ev_trace.size()) {
+        cudaEvent_t e; cudaEventCreate(&e); s->ev_trace.push_back(e);
+    }
+    return s->ev_trace[s->ev_trace_used++];
+}
+
+// One wave: lanes [0, n) <-> sample indices [first, first + n)
+static int run_wave(bf_scene *s, uint64_t seed, uint64_t first, uint32_t n, float *profile) {
+    const DevScene &sc = s->dev;
+    const Wave &w = s->wave;
+    LaunchCfg cfg; cfg.stream = s->stream; cfg.sm_count = s->sm_count;
+    uint32_t *ctr = s->d_counters.p;
+    const bool unbounded = sc.integ.max_depth < 0 || sc.integ.max_depth > 64;
+    const uint32_t max_depth = sc.integ.max_depth < 0 ? BF_MAX_BOUNCES : std::min<uint32_t>((uint32_t) sc.integ.max_depth, BF_MAX_BOUNCES);
+    const uint32_t ctr_blocks = unbounded ? BF_MAX_BOUNCES + 2 : max_depth + 2;
+    BF_CUDA(cudaMemsetAsync(ctr, 0, (size_t) BF_CTR_STRIDE * ctr_blocks * 4, s->stream));
+    uint64_t launches = 0;
+    launches += launch_raygen(sc, w, seed, first, n, cfg);
+    auto timed = [&](auto &&fn) {
+        if (s->time_trace) { cudaEventRecord(next_trace_event(s), s->stream); }
+        launches += fn();
+        if (s->time_trace) { cudaEventRecord(next_trace_event(s), s->stream); }
+    };
+    timed([&] { return launch_trace_closest(sc, w, nullptr, nullptr, n, ctr + 2, cfg); });
+    for (uint32_t depth = 1; depth <= max_depth; ++depth) {
+        uint32_t *blk = ctr + (size_t) BF_CTR_STRIDE * depth, *prev = ctr + (size_t) BF_CTR_STRIDE * (depth - 1);
+        launches += launch_shade(sc, w, depth, depth == 1 ? nullptr : w.queue[(depth - 1) & 1], prev + 0, n, w.queue[depth & 1], blk, cfg);
+        if (depth >= max_depth) break;
+        timed([&] { return launch_trace_shadow(sc, w, w.queue_s, blk + 1, blk + 3, cfg); });
+        timed([&] { return launch_trace_closest(sc, w, w.queue[depth & 1], blk + 0, 0, blk + 2, cfg); });
+        if (unbounded && depth >= 8) {
+            BF_CUDA(cudaMemcpyAsync(s->h_counts, blk, 8, cudaMemcpyDeviceToHost, s->stream));
+            BF_CUDA(cudaStreamSynchronize(s->stream));
+            if (s->h_counts[0] == 0) break;
+        }
+    }
+    launches += launch_finalize(sc, w, n, profile, cfg);
+    s->stats.kernel_launches += launches;
+    BF_CUDA(cudaGetLastError());
+    return BF_OK;
+}
+
+int bf_receive(bf_scene *s, uint64_t seed, uint64_t first_sample, uint64_t n_samples, int accumulate) {
+    if (!s) return BF_ERR_INVALID;
+    if (!s->committed) return fail(s, BF_ERR_STATE, "bf_receive: scene not committed");
+    BF_CUDA(cudaSetDevice(s->device));
+    if (s->tables_dirty) { int rc = upload_tables(s); if (rc) return rc; }
+    uint32_t chunk = (uint32_t) std::min<uint64_t>(std::max<uint64_t>(n_samples, 1024), wave_lanes_default());
+    int rc = ensure_wave(s, chunk, false);
+    if (rc) return rc;
+    // resolve the previous call's trace timings before the events are re-used
+    s->ev_trace_used = 0;
+    BF_CUDA(cudaEventRecord(s->ev_begin, s->stream));
+    if (!accumulate) BF_CUDA(cudaMemsetAsync(s->d_profile.p, 0, s->profile_floats * 4, s->stream));
+    bf_sample_record *saved = s->wave.records;
+    s->wave.records = nullptr;
+    for (uint64_t done = 0; done < n_samples; done += s->wave_capacity) {
+        uint32_t n = (uint32_t) std::min<uint64_t>(s->wave_capacity, n_samples - done);
+        rc = run_wave(s, seed, first_sample + done, n, s->d_profile.p);
+        if (rc) { s->wave.records = saved; return rc; }
+    }
+    s->wave.records = saved;
+    BF_CUDA(cudaEventRecord(s->ev_end, s->stream));
+    s->stats.samples += n_samples;
+    return BF_OK;
+}
+
+int bf_synchronize(bf_scene *s) {
+    if (!s || !s->committed) return BF_ERR_STATE;
+    BF_CUDA(cudaSetDevice(s->device));
+    BF_CUDA(cudaStreamSynchronize(s->stream));
+    return BF_OK;
+}
+
+int bf_profile_read(bf_scene *s, float *dst, size_t n_floats) {
+    if (!s || !dst) return BF_ERR_INVALID;
+    if (!s->committed) return fail(s, BF_ERR_STATE, "bf_profile_read: scene not committed");
+    if (n_floats < s->profile_floats) return fail(s, BF_ERR_INVALID, "bf_profile_read: destination too small");
+    BF_CUDA(cudaSetDevice(s->device));
+    BF_CUDA(cudaMemcpyAsync(dst, s->d_profile.p, s->profile_floats * 4, cudaMemcpyDeviceToHost, s->stream));
+    BF_CUDA(cudaStreamSynchronize(s->stream));
+    return BF_OK;
+}
+
+int bf_profile_device_ptr(bf_scene *s, void **dptr, size_t *n_floats, void **cuda_stream) {
+    if (!s || !s->committed) return BF_ERR_STATE;
+    if (dptr) *dptr = s->d_profile.p;
+    if (n_floats) *n_floats = s->profile_floats;
+    if (cuda_stream) *cuda_stream = (void *) s->stream;
+    return BF_OK;
+}
+
+static int trace_rays_common(bf_scene *s, const float *origins, const float *directions, const float *mint, const float *maxt,
+                             uint64_t n_rays, uint32_t *shape, uint32_t *prim, float *t, float *u, float *v, uint8_t *occl) {
+    if (!s || !origins || !directions) return BF_ERR_INVALID;
+    if (!s->committed) return fail(s, BF_ERR_STATE, "trace: scene not committed");
+    if (n_rays == 0) return BF_OK;
+    if (n_rays > (1ull << 28)) return fail(s, BF_ERR_INVALID, "trace: too many rays in one call");
+    BF_CUDA(cudaSetDevice(s->device));
+    if (s->tables_dirty) { int rc = upload_tables(s); if (rc) return rc; }
+    size_t n = (size_t) n_rays;
+    std::vector<float4> ho(n), hd(n);
+    for (size_t i = 0; i < n; ++i) {
+        ho[i] = make_float4(origins[3 * i], origins[3 * i + 1], origins[3 * i + 2], mint ? mint[i] : BF_RAY_EPS);
+        hd[i] = make_float4(directions[3 * i], directions[3 * i + 1], directions[3 * i + 2], maxt ? maxt[i] : INFINITY);
+    }
+    DevBuf<float4> d_o, d_d, d_hit; DevBuf<uint32_t> d_a, d_b, d_cursor;
+    auto cleanup = [&]() { d_o.release(); d_d.release(); d_hit.release(); d_a.release(); d_b.release(); d_cursor.release(); };
+    cudaError_t e = cudaSuccess;
+    if ((e = d_o.alloc(n)) || (e = d_d.alloc(n)) || (e = d_hit.alloc(n)) || (e = d_a.alloc(n)) || (e = d_b.alloc(n)) || (e = d_cursor.alloc(1))) {
+        cleanup();
+        return fail(s, BF_ERR_CUDA, std::string("trace: ") + cudaGetErrorString(e));
+    }
+    LaunchCfg cfg; cfg.stream = s->stream; cfg.sm_count = s->sm_count;
+    cudaMemcpyAsync(d_o.p, ho.data(), n * 16, cudaMemcpyHostToDevice, s->stream);
+    cudaMemcpyAsync(d_d.p, hd.data(), n * 16, cudaMemcpyHostToDevice, s->stream);
+    cudaMemsetAsync(d_cursor.p, 0, 4, s->stream);
+    if (!occl) {
+        s->stats.kernel_launches += launch_trace_rays(s->dev, d_o.p, d_d.p, (uint32_t) n, d_hit.p, nullptr, d_cursor.p, cfg);
+        s->stats.kernel_launches += launch_resolve_hits(s->dev, d_hit.p, (uint32_t) n, d_a.p, d_b.p, cfg);
+        std::vector<float4> hh(n);
+        cudaMemcpyAsync(hh.data(), d_hit.p, n * 16, cudaMemcpyDeviceToHost, s->stream);
+        if (shape) cudaMemcpyAsync(shape, d_a.p, n * 4, cudaMemcpyDeviceToHost, s->stream);
+        if (prim) cudaMemcpyAsync(prim, d_b.p, n * 4, cudaMemcpyDeviceToHost, s->stream);
+        e = cudaStreamSynchronize(s->stream);
+        for (size_t i = 0; i < n && e == cudaSuccess; ++i) {
+            if (t) t[i] = hh[i].x;
+            if (u) u[i] = hh[i].y;
+            if (v) v[i] = hh[i].z;
+        }
+    } else {
+        s->stats.kernel_launches += launch_trace_rays(s->dev, d_o.p, d_d.p, (uint32_t) n, nullptr, d_a.p, d_cursor.p, cfg);
+        std::vector<uint32_t> hh(n);
+        cudaMemcpyAsync(hh.data(), d_a.p, n * 4, cudaMemcpyDeviceToHost, s->stream);
+        e = cudaStreamSynchronize(s->stream);
+        for (size_t i = 0; i < n && e == cudaSuccess; ++i) occl[i] = (uint8_t) hh[i];
+    }
+    if (e == cudaSuccess) e = cudaGetLastError();
+    cleanup();
+    if (e != cudaSuccess) return fail(s, BF_ERR_CUDA, std::string("trace: ") + cudaGetErrorString(e));
+    return BF_OK;
+}
+
+int bf_trace_first_hits(bf_scene *s, const float *origins, const float *directions, const float *mint, const float *maxt,
+                        uint64_t n_rays, uint32_t *shape, uint32_t *prim, float *t, float *u, float *v) {
+    return trace_rays_common(s, origins, directions, mint, maxt, n_rays, shape, prim, t, u, v, nullptr);
+}
+int bf_trace_occluded(bf_scene *s, const float *origins, const float *directions, const float *mint, const float *maxt,
+                      uint64_t n_rays, uint8_t *hit) {
+    if (!hit) return BF_ERR_INVALID;
+    return trace_rays_common(s, origins, directions, mint, maxt, n_rays, nullptr, nullptr, nullptr, nullptr, nullptr, hit);
+}
+
+int bf_debug_sample_records(bf_scene *s, uint64_t seed, uint64_t first_sample, uint64_t n_samples, bf_sample_record *records) {
+    if (!s || !records) return BF_ERR_INVALID;
+    if (!s->committed) return fail(s, BF_ERR_STATE, "bf_debug_sample_records: scene not committed");
+    if (n_samples == 0) return BF_OK;
+    if (n_samples > (1u << 24)) return fail(s, BF_ERR_INVALID, "bf_debug_sample_records: at most 2^24 samples per call");
+    BF_CUDA(cudaSetDevice(s->device));
+    if (s->tables_dirty) { int rc = upload_tables(s); if (rc) return rc; }
+    int rc = ensure_wave(s, (uint32_t) std::max<uint64_t>(n_samples, 1024), true);
+    if (rc) return rc;
+    DevBuf<float> scratch;
+    BF_CUDA(scratch.alloc(s->profile_floats));
+    BF_CUDA(cudaMemsetAsync(scratch.p, 0, s->profile_floats * 4, s->stream));
+    s->ev_trace_used = 0;
+    rc = run_wave(s, seed, first_sample, (uint32_t) n_samples, scratch.p);
+    if (rc == BF_OK) {
+        cudaError_t e = cudaMemcpyAsync(records, s->wave.records, n_samples * sizeof(bf_sample_record), cudaMemcpyDeviceToHost, s->stream);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(s->stream);
+        if (e != cudaSuccess) rc = fail(s, BF_ERR_CUDA, cudaGetErrorString(e));
+    }
+    cudaStreamSynchronize(s->stream);
+    scratch.release();
+    return rc;
+}
+
+int bf_get_stats(const bf_scene *s_, bf_stats *stats) {
+    bf_scene *s = const_cast<bf_scene *>(s_);
+    if (!s || !stats) return BF_ERR_INVALID;
+    if (s->committed) {
+        BF_CUDA(cudaSetDevice(s->device));
+        unsigned long long t[2] = {0, 0};
+        BF_CUDA(cudaStreamSynchronize(s->stream));
+        BF_CUDA(cudaMemcpy(t, s->d_totals.p, 16, cudaMemcpyDeviceToHost));
+        s->stats.closest_queries = t[0]; s->stats.shadow_queries = t[1];
+    }
+    *stats = s->stats;
+    return BF_OK;
+}
+
+int bf_set_trace_timing(bf_scene *s, int enabled) {
+    if (!s) return BF_ERR_INVALID;
+    s->time_trace = enabled != 0;
+    return BF_OK;
+}
+
+int bf_last_receive_ms(bf_scene *s, float *total_ms, float *traverse_ms) {
+    if (!s || !s->committed) return BF_ERR_STATE;
+    BF_CUDA(cudaSetDevice(s->device));
+    BF_CUDA(cudaEventSynchronize(s->ev_end));
+    float ms = 0.f;
+    BF_CUDA(cudaEventElapsedTime(&ms, s->ev_begin, s->ev_end));
+    if (total_ms) *total_ms = ms;
+    if (traverse_ms) {
+        float acc = 0.f;
+        for (size_t i = 0; i + 1 < s->ev_trace_used; i += 2) {
+            float m = 0.f;
+            if (cudaEventElapsedTime(&m, s->ev_trace[i], s->ev_trace[i + 1]) == cudaSuccess) acc += m;
+        }
+        *traverse_ms = s->time_trace ? acc : -1.f;
+    }
+    return BF_OK;
+}
+
+}  // extern "C"

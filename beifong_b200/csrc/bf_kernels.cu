@@ -1,0 +1,695 @@
+// beifong_b200 — sm_100a wavefront kernels of the radar path:
+//   k_raygen    receiver ray generation       (integrator.cpp:1538-1569 / :255-279, receivers/*.cpp)
+//   k_trace     8-wide compressed-BVH traversal + Möller-Trumbore + analytic rectangles
+//               (Scene::ray_intersect_preliminary / ray_test, scene.cpp:129-178; mesh.h:194-226;
+//                rectangle.cpp:229-263)
+//   k_shade     surface interaction, emission, russian roulette, transmitter sampling (NEE) + MIS,
+//               BSDF sampling, next-ray spawn, queue compaction
+//               (pathtimefrequency.cpp:103-460, pathlength.cpp:114-325, pathtime.cpp:114-286)
+//   k_finalize  phase/range/time binning + range-bin scatter
+//               (phase.cpp:85-138, range.cpp:141-161, time.cpp:118-153, integrator.cpp:1588-1665,
+//                signalblock.cpp:162-169)
+// Compiled with -fmad=false: see bf_math.h for the arithmetic contract.
+#include "bf_wave.h"
+#include "bf_device.cuh"
+
+namespace bf {
+
+// =========================================================================================================
+// helpers
+// =========================================================================================================
+__device__ __forceinline__ uint32_t lane_id() { return threadIdx.x & 31u; }
+
+// warp-aggregated queue push: one atomic per warp, lane ids written in lane order
+__device__ __forceinline__ void queue_push(bool pred, uint32_t value, uint32_t *queue, uint32_t *counter, unsigned long long *total) {
+    uint32_t mask = __ballot_sync(0xffffffffu, pred);
+    if (mask == 0) return;
+    uint32_t leader = __ffs(mask) - 1, base = 0;
+    if (lane_id() == leader) {
+        base = atomicAdd(counter, (uint32_t) __popc(mask));
+        if (total) atomicAdd(total, (unsigned long long) __popc(mask));
+    }
+    base = __shfl_sync(0xffffffffu, base, leader);
+    if (pred) queue[base + __popc(mask & ((1u << lane_id()) - 1u))] = value;
+}
+
+template <int S> struct SpecIO;
+template <> struct SpecIO<1> {
+    static __device__ __forceinline__ void load(const Wave &w, uint32_t l, Spec<1> &thr, Spec<1> &res, Spec<1> &pend, Spec<1> &wl) {
+        float4 a = w.spec[0][l]; thr.v[0] = a.x; res.v[0] = a.y; pend.v[0] = a.z; wl.v[0] = a.w;
+    }
+    static __device__ __forceinline__ void store(const Wave &w, uint32_t l, const Spec<1> &thr, const Spec<1> &res, const Spec<1> &pend, const Spec<1> &wl) {
+        w.spec[0][l] = make_float4(thr.v[0], res.v[0], pend.v[0], wl.v[0]);
+    }
+    static __device__ __forceinline__ Spec<1> load_weight(const Wave &w, uint32_t l, float4 x2) { Spec<1> r; r.v[0] = x2.w; return r; }
+    static __device__ __forceinline__ void store_weight(const Wave &, uint32_t, const Spec<1> &wg, float4 &x2) { x2.w = wg.v[0]; }
+};
+template <> struct SpecIO<4> {
+    static __device__ __forceinline__ Spec<4> ld(const float4 *p, uint32_t l) { float4 a = p[l]; Spec<4> r; r.v[0] = a.x; r.v[1] = a.y; r.v[2] = a.z; r.v[3] = a.w; return r; }
+    static __device__ __forceinline__ void st(float4 *p, uint32_t l, const Spec<4> &s) { p[l] = make_float4(s.v[0], s.v[1], s.v[2], s.v[3]); }
+    static __device__ __forceinline__ void load(const Wave &w, uint32_t l, Spec<4> &thr, Spec<4> &res, Spec<4> &pend, Spec<4> &wl) {
+        thr = ld(w.spec[0], l); res = ld(w.spec[1], l); pend = ld(w.spec[2], l); wl = ld(w.spec[3], l);
+    }
+    static __device__ __forceinline__ void store(const Wave &w, uint32_t l, const Spec<4> &thr, const Spec<4> &res, const Spec<4> &pend, const Spec<4> &wl) {
+        st(w.spec[0], l, thr); st(w.spec[1], l, res); st(w.spec[2], l, pend); st(w.spec[3], l, wl);
+    }
+    static __device__ __forceinline__ Spec<4> load_weight(const Wave &w, uint32_t l, float4) { return ld(w.spec[4], l); }
+    static __device__ __forceinline__ void store_weight(const Wave &w, uint32_t l, const Spec<4> &wg, float4 &) { st(w.spec[4], l, wg); }
+};
+
+// =========================================================================================================
+// raygen
+// =========================================================================================================
+template <int S>
+__global__ void __launch_bounds__(256) k_raygen(const __grid_constant__ DevScene sc, const __grid_constant__ Wave w, uint64_t seed, uint64_t first_sample, uint32_t n) {
+    uint32_t l = blockIdx.x * blockDim.x + threadIdx.x;
+    if (l >= n) return;
+    uint64_t idx = first_sample + l;
+    PCG32 rng;
+    rng.seed(sample_tea_64_wide(seed, idx), sample_tea_64_wide(idx, seed));   // sampler.cpp:89-92
+
+    const DevEndpoint &rx = *sc.rx;
+    V2 position_sample; position_sample.x = rng.next_float32(); position_sample.y = rng.next_float32();
+    V2 aperture_sample(.5f, .5f);
+    if (sc.rx_needs_aperture) { aperture_sample.x = rng.next_float32(); aperture_sample.y = rng.next_float32(); }
+    float time;
+    float4 x2 = make_float4(0.f, 0.f, 0.f, 0.f);
+    RayGen ray; Spec<S> wl, weight;
+    if (sc.integ.gen == BF_GEN_PHASE) {
+        // integrator.cpp:1544-1569
+        time = rx.adc_sampling_start;
+        if (rx.adc_sampling_time > 0.f) time += rng.next_float32() * rx.adc_sampling_time; else time = 0.f;
+        float wavelength_sample = rng.next_float32();
+        rx_sample_ray<S>(sc, time, wavelength_sample, position_sample, aperture_sample, ray, wl, weight);
+        x2.x = time;
+        x2.y = freq_from_wl(sc.C.c, wl.v[0]);   // f_rx of mix_resample (integrator.cpp:1603)
+    } else {
+        // integrator.cpp:263-279 (1x1 film, pos = 0)
+        time = rx.shutter_open;
+        if (rx.shutter_open_time > 0.f) time += rng.next_float32() * rx.shutter_open_time;
+        float wavelength_sample = rng.next_float32();
+        V2 adjusted((position_sample.x - 0.f) / (float) sc.film_w, (position_sample.y - 0.f) / (float) sc.film_h);
+        rx_sample_ray<S>(sc, time, wavelength_sample, adjusted, aperture_sample, ray, wl, weight);
+        x2.x = position_sample.x; x2.y = position_sample.y;
+    }
+    SpecIO<S>::store_weight(w, l, weight, x2);
+    w.ray_o[l] = make_float4(ray.o.x, ray.o.y, ray.o.z, ray.mint);
+    w.ray_d[l] = make_float4(ray.d.x, ray.d.y, ray.d.z, ray.maxt);
+    w.rng[l] = make_ulonglong2(rng.state, rng.inc);
+    w.x1[l] = make_float4(time, 0.f, 0.f, 0.f);
+    w.x2[l] = x2;
+    SpecIO<S>::store(w, l, Spec<S>(1.f), Spec<S>(0.f), Spec<S>(0.f), wl);
+    w.flags[l] = LANE_ACTIVE;
+    if (w.records) {
+        bf_sample_record r;
+        r.first_shape = BF_NONE; r.first_prim = BF_NONE; r.first_t = bf_inf(); r.valid = 0; r.tf_t = 0.f; r.tf_f = 0.f;
+        r.value = 0.f; r.phase = 0.f; r.n_closest = 1; r.n_shadow = 0; r.wavelength0 = wl.v[0]; r.depth = 0;
+        w.records[l] = r;
+    }
+}
+
+// =========================================================================================================
+// traversal
+// =========================================================================================================
+#define TRACE_THREADS 128
+#define TRACE_SM_STACK BF_TRACE_SM_STACK
+#define TRACE_LOCAL_STACK BF_TRACE_LOCAL_STACK
+
+__device__ __forceinline__ uint32_t sign_extend_s8x4(uint32_t x) {
+    uint32_t r;
+    asm("prmt.b32 %0, %1, 0x0, 0x0000BA98;" : "=r"(r) : "r"(x));
+    return r;
+}
+__device__ __forceinline__ uint32_t byte_of(uint32_t x, int i) { return (x >> (8 * i)) & 0xffu; }
+
+struct HitAcc {
+    float t; float u, v; uint32_t slot; uint32_t shape, prim;
+};
+
+// Möller-Trumbore exactly as Mesh::ray_intersect_triangle (mesh.h:194-226): no backface culling,
+// no determinant epsilon, u in [0,1], v >= 0, u+v <= 1, t in [mint, maxt].
+__device__ __forceinline__ bool tri_test(const float4 *__restrict__ tris, uint32_t slot, V3 o, V3 d, float mint, float maxt,
+                                         float &t_out, float &u_out, float &v_out, uint32_t &shape, uint32_t &prim) {
+    float4 a = __ldg(&tris[3 * (size_t) slot]), b = __ldg(&tris[3 * (size_t) slot + 1]), c = __ldg(&tris[3 * (size_t) slot + 2]);
+    V3 p0(a.x, a.y, a.z), p1(b.x, b.y, b.z), p2(c.x, c.y, c.z);
+    V3 e1 = p1 - p0, e2 = p2 - p0;
+    V3 pvec = cross(d, e2);
+    float inv_det = rcp(dot(e1, pvec));
+    V3 tvec = o - p0;
+    float u = dot(tvec, pvec) * inv_det;
+    bool active = u >= 0.f && u <= 1.f;
+    V3 qvec = cross(tvec, e1);
+    float v = dot(d, qvec) * inv_det;
+    active &= v >= 0.f && u + v <= 1.f;
+    float t = dot(e2, qvec) * inv_det;
+    active &= t >= mint && t <= maxt;
+    t_out = t; u_out = u; v_out = v;
+    shape = __float_as_uint(a.w); prim = __float_as_uint(b.w);
+    return active;
+}
+
+// Closest hit: lowest t, ties broken by the lowest (shape, prim) — the order a brute-force loop over
+// the scene's shapes visits them in (ray_intersect_naive, scene_native.inl:43-61).
+template <bool ANY_HIT>
+__device__ __forceinline__ void trace_one(const DevScene &sc, const float *s_rect, uint2 *s_stack, V3 o, V3 d, float mint, float maxt, HitAcc &best, bool &occluded) {
+    best.t = maxt; best.u = 0.f; best.v = 0.f; best.slot = BF_NONE; best.shape = BF_NONE; best.prim = BF_NONE;
+    occluded = false;
+
+    // analytic rectangles (rectangle.cpp:229-263)
+    for (uint32_t r = 0; r < sc.n_rects; ++r) {
+        const float *m = s_rect + 12 * r;
+        float ox = fmadd(m[2], o.z, fmadd(m[1], o.y, fmadd(m[0], o.x, m[3])));
+        float oy = fmadd(m[6], o.z, fmadd(m[5], o.y, fmadd(m[4], o.x, m[7])));
+        float oz = fmadd(m[10], o.z, fmadd(m[9], o.y, fmadd(m[8], o.x, m[11])));
+        float dx = fmadd(m[2], d.z, fmadd(m[1], d.y, m[0] * d.x));
+        float dy = fmadd(m[6], d.z, fmadd(m[5], d.y, m[4] * d.x));
+        float dz = fmadd(m[10], d.z, fmadd(m[9], d.y, m[8] * d.x));
+        float t = -oz * rcp(dz);
+        float lx = fmadd(dx, t, ox), ly = fmadd(dy, t, oy);
+        bool hit = t >= mint && t <= maxt && fabsf(lx) <= 1.f && fabsf(ly) <= 1.f;
+        if (!hit) continue;
+        if (ANY_HIT) { occluded = true; return; }
+        uint32_t shape = __float_as_uint(s_rect[12 * BF_MAX_RECTS + r]);
+        if (t < best.t || (t == best.t && shape < best.shape)) {
+            best.t = t; best.u = lx; best.v = ly; best.slot = 0x80000000u | r; best.shape = shape; best.prim = 0;
+        }
+    }
+    if (sc.n_nodes == 0) return;
+
+    // ---- 8-wide compressed BVH ---------------------------------------------------------------------------
+    const float tiny = 1e-30f;
+    float idx_ = __fdividef(1.f, fabsf(d.x) > tiny ? d.x : copysignf(tiny, d.x));
+    float idy_ = __fdividef(1.f, fabsf(d.y) > tiny ? d.y : copysignf(tiny, d.y));
+    float idz_ = __fdividef(1.f, fabsf(d.z) > tiny ? d.z : copysignf(tiny, d.z));
+    const uint32_t octinv = (d.x < 0.f ? 0u : 4u) | (d.y < 0.f ? 0u : 2u) | (d.z < 0.f ? 0u : 1u);
+    const uint32_t octinv4 = octinv * 0x01010101u;
+    // conservative ray interval for the slab tests
+    const float tmin_ray = mint * (1.f - 4e-7f);
+
+    uint2 l_stack[TRACE_LOCAL_STACK];
+    int sp = 0;
+    uint2 ngroup = make_uint2(0u, 0x80000000u);
+    const uint32_t tid = threadIdx.x;
+
+    while (true) {
+        uint2 tgroup = make_uint2(0u, 0u);
+        {
+            const uint32_t hits_imask = ngroup.y;
+            const uint32_t child_bit_index = 31u - __clz(hits_imask);
+            const uint32_t child_node_base = ngroup.x;
+            ngroup.y &= ~(1u << child_bit_index);
+            if (ngroup.y > 0x00ffffffu) {
+                if (sp < TRACE_SM_STACK) s_stack[sp * TRACE_THREADS + tid] = ngroup;
+                else l_stack[sp - TRACE_SM_STACK] = ngroup;
+                ++sp;
+            }
+            const uint32_t slot_index = (child_bit_index - 24u) ^ octinv;
+            const uint32_t relative_index = __popc(hits_imask & ~(0xffffffffu << slot_index));
+            const uint32_t node_index = child_node_base + relative_index;
+
+            const uint4 *np = sc.nodes + 5 * (size_t) node_index;
+            const uint4 n0 = __ldg(np), n1 = __ldg(np + 1), n2 = __ldg(np + 2), n3 = __ldg(np + 3), n4 = __ldg(np + 4);
+
+            const float px = __uint_as_float(n0.x), py = __uint_as_float(n0.y), pz = __uint_as_float(n0.z);
+            const uint32_t ex = n0.w & 0xffu, ey = (n0.w >> 8) & 0xffu, ez = (n0.w >> 16) & 0xffu, imask = n0.w >> 24;
+            ngroup.x = n1.x;
+            tgroup.x = n1.y;
+            uint32_t hitmask = 0;
+
+            const float ax = __uint_as_float(ex << 23) * idx_, ay = __uint_as_float(ey << 23) * idy_, az = __uint_as_float(ez << 23) * idz_;
+            const float bx = (px - o.x) * idx_, by = (py - o.y) * idy_, bz = (pz - o.z) * idz_;
+            const float tmax_ray = best.t * (1.f + 4e-7f);
+
+#pragma unroll
+            for (int half = 0; half < 2; ++half) {
+                const uint32_t meta4 = half ? n1.w : n1.z;
+                const uint32_t is_inner4 = (meta4 & (meta4 << 1)) & 0x10101010u;
+                const uint32_t inner_mask4 = sign_extend_s8x4(is_inner4 << 3);
+                const uint32_t bit_index4 = (meta4 ^ (octinv4 & inner_mask4)) & 0x1f1f1f1fu;
+                const uint32_t child_bits4 = (meta4 >> 5) & 0x07070707u;
+                const uint32_t qlx = half ? n2.y : n2.x, qly = half ? n2.w : n2.z, qlz = half ? n3.y : n3.x;
+                const uint32_t qhx = half ? n3.w : n3.z, qhy = half ? n4.y : n4.x, qhz = half ? n4.w : n4.z;
+                const uint32_t x_min = d.x < 0.f ? qhx : qlx, x_max = d.x < 0.f ? qlx : qhx;
+                const uint32_t y_min = d.y < 0.f ? qhy : qly, y_max = d.y < 0.f ? qly : qhy;
+                const uint32_t z_min = d.z < 0.f ? qhz : qlz, z_max = d.z < 0.f ? qlz : qhz;
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    float tminx = fmaf((float) byte_of(x_min, j), ax, bx), tmaxx = fmaf((float) byte_of(x_max, j), ax, bx);
+                    float tminy = fmaf((float) byte_of(y_min, j), ay, by), tmaxy = fmaf((float) byte_of(y_max, j), ay, by);
+                    float tminz = fmaf((float) byte_of(z_min, j), az, bz), tmaxz = fmaf((float) byte_of(z_max, j), az, bz);
+                    float cmin = fmaxf(fmaxf(tminx, tminy), fmaxf(tminz, tmin_ray));
+                    float cmax = fminf(fminf(tmaxx, tmaxy), fminf(tmaxz, tmax_ray));
+                    if (cmin <= cmax * (1.f + 4e-7f))
+                        hitmask |= byte_of(child_bits4, j) << byte_of(bit_index4, j);
+                }
+            }
+            ngroup.y = (hitmask & 0xff000000u) | imask;
+            tgroup.y = hitmask & 0x00ffffffu;
+        }
+
+        while (tgroup.y != 0) {
+            const uint32_t i = 31u - __clz(tgroup.y);
+            tgroup.y &= ~(1u << i);
+            const uint32_t slot = tgroup.x + i;
+            float t, u, v; uint32_t shape, prim;
+            if (tri_test(sc.tris, slot, o, d, mint, maxt, t, u, v, shape, prim)) {
+                if (ANY_HIT) { occluded = true; return; }
+                if (t < best.t || (t == best.t && (shape < best.shape || (shape == best.shape && prim < best.prim)))) {
+                    best.t = t; best.u = u; best.v = v; best.slot = slot; best.shape = shape; best.prim = prim;
+                }
+            }
+        }
+
+        if (ngroup.y <= 0x00ffffffu) {
+            if (sp == 0) break;
+            --sp;
+            ngroup = sp < TRACE_SM_STACK ? s_stack[sp * TRACE_THREADS + tid] : l_stack[sp - TRACE_SM_STACK];
+        }
+    }
+}
+
+__device__ __forceinline__ void stage_rects(const DevScene &sc, float *s_rect) {
+    for (uint32_t i = threadIdx.x; i < sc.n_rects * 12u; i += blockDim.x) {
+        uint32_t r = i / 12u, k = i % 12u;
+        s_rect[i] = sc.rects[r].to_object.m[k / 4u][k % 4u];
+    }
+    for (uint32_t r = threadIdx.x; r < sc.n_rects; r += blockDim.x)
+        s_rect[12 * BF_MAX_RECTS + r] = __uint_as_float(sc.rects[r].shape);
+    __syncthreads();
+}
+
+// One persistent grid; each warp claims 32 rays at a time from a global cursor.
+template <bool ANY_HIT>
+__global__ void __launch_bounds__(TRACE_THREADS) k_trace(const __grid_constant__ DevScene sc, const float4 *__restrict__ ray_o,
+                                                         const float4 *__restrict__ ray_d, const uint32_t *__restrict__ queue,
+                                                         const uint32_t *__restrict__ count, uint32_t n_direct,
+                                                         float4 *__restrict__ hit_out, uint32_t *__restrict__ occl_out,
+                                                         uint32_t *work_cursor, unsigned long long *total) {
+    __shared__ float s_rect[13 * BF_MAX_RECTS];
+    __shared__ uint2 s_stack[TRACE_SM_STACK * TRACE_THREADS];
+    stage_rects(sc, s_rect);
+    const uint32_t n = queue ? *count : n_direct;
+    if (total && blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(total, (unsigned long long) n);
+    while (true) {
+        uint32_t base = 0;
+        if (lane_id() == 0) base = atomicAdd(work_cursor, 32u);
+        base = __shfl_sync(0xffffffffu, base, 0);
+        if (base >= n) break;
+        uint32_t i = base + lane_id();
+        if (i < n) {
+            uint32_t l = queue ? queue[i] : i;
+            float4 ro = ray_o[l], rd = ray_d[l];
+            HitAcc best; bool occluded;
+            trace_one<ANY_HIT>(sc, s_rect, s_stack, V3(ro.x, ro.y, ro.z), V3(rd.x, rd.y, rd.z), ro.w, rd.w, best, occluded);
+            if (ANY_HIT) occl_out[l] = occluded ? 1u : 0u;
+            else hit_out[l] = make_float4(best.slot == BF_NONE ? bf_inf() : best.t, best.u, best.v, __uint_as_float(best.slot));
+        }
+    }
+}
+
+__global__ void k_resolve_hits(const __grid_constant__ DevScene sc, const float4 *__restrict__ hit, uint32_t n, uint32_t *shape, uint32_t *prim) {
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    float4 h = hit[i];
+    uint32_t slot = __float_as_uint(h.w);
+    if (h.x == bf_inf() || slot == BF_NONE) { shape[i] = BF_NONE; prim[i] = BF_NONE; return; }
+    if (slot & 0x80000000u) { shape[i] = sc.rects[slot & 0x7fffffffu].shape; prim[i] = 0; return; }
+    shape[i] = __float_as_uint(__ldg(&sc.tris[3 * (size_t) slot]).w);
+    prim[i] = __float_as_uint(__ldg(&sc.tris[3 * (size_t) slot + 1]).w);
+}
+
+// =========================================================================================================
+// shade
+// =========================================================================================================
+// Ray::update_state (ray.h:89-93): time += t / MTS_C; phase += 2 pi t / ((MAX-MIN)/2*1e-9) (double)
+__device__ __forceinline__ void update_state(const DevScene &sc, float &time, float &phase, float t) {
+    time += t / sc.C.c;
+    phase = (float) ((double) phase + (double) (BF_TWO_PI * t) / sc.phase_denom);
+}
+
+template <int S>
+__global__ void __launch_bounds__(128) k_shade(const __grid_constant__ DevScene sc, const __grid_constant__ Wave w, uint32_t depth,
+                                               const uint32_t *__restrict__ queue, const uint32_t *__restrict__ count, uint32_t n_direct,
+                                               uint32_t *__restrict__ next_queue, uint32_t *ctr) {
+    const uint32_t n = queue ? *count : n_direct;
+    const uint32_t gen = sc.integ.gen;
+    const uint32_t stride = gridDim.x * blockDim.x;
+    const uint32_t n_round = (n + 31u) & ~31u;   // keep warps converged for the ballot in queue_push
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n_round; i += stride) {
+        bool push_next = false, push_shadow = false;
+        uint32_t l = 0;
+        if (i < n) {
+            l = queue ? queue[i] : i;
+            uint32_t flags = w.flags[l];
+            const float4 ro = w.ray_o[l], rd = w.ray_d[l];
+            const float4 hit = w.hit[l];
+            float4 x1 = w.x1[l];
+            Spec<S> thr, res, pend, wl;
+            SpecIO<S>::load(w, l, thr, res, pend, wl);
+            if (flags & LANE_PENDING) {
+                if (!w.occl[l]) {
+#pragma unroll
+                    for (int k = 0; k < S; ++k) res.v[k] += pend.v[k];
+                }
+                flags &= ~LANE_PENDING;
+            }
+            const V3 o(ro.x, ro.y, ro.z), d(rd.x, rd.y, rd.z);
+            SI si = compute_si(sc, o, d, hit);
+            float time = x1.x, phase = x1.y, bs_pdf = x1.z, scalar = x1.w;
+            float emission_weight = 1.f;
+            int transmitter = si.is_valid() ? sc.shapes[si.shape].tx : -1;
+
+            if (depth == 1) {
+                if (si.is_valid()) flags |= LANE_VALID;
+                if (gen == BF_GEN_PHASE) { if (si.is_valid()) update_state(sc, time, phase, -si.t); }
+                else if (gen == BF_GEN_RANGE) scalar += si.is_valid() ? si.t : 0.f;
+                else scalar = si.is_valid() ? si.t / 3.0e8f : 0.f;
+                if (w.records) {
+                    bf_sample_record *r = w.records + l;
+                    r->first_shape = si.is_valid() ? si.shape : BF_NONE;
+                    r->first_prim = si.is_valid() ? si.prim : BF_NONE;
+                    r->first_t = si.t;
+                }
+            } else {
+                // tail of the previous loop iteration (pathtimefrequency.cpp:368-399)
+                if (gen == BF_GEN_PHASE) { phase = 0.f; update_state(sc, time, phase, -si.t); }
+                if (transmitter >= 0) {
+                    DirectionSample ds;   // DirectionSample3f(si_bsdf, si), records.h:168-174
+                    ds.p = si.p; ds.n = si.sh.n; ds.time = time; ds.delta = false; ds.pdf = 0.f;
+                    ds.d = si.p - o; ds.dist = norm(ds.d); ds.d = ds.d / ds.dist; ds.object = transmitter;
+                    float tx_pdf = 0.f;
+                    if (!(flags & LANE_BS_DELTA)) {
+                        tx_pdf = tx_pdf_direction(sc, sc.txs[transmitter], wl.v[0], ds);
+                        if (sc.n_txs > 1) tx_pdf *= (1.f / (float) sc.n_txs);
+                    }
+                    emission_weight = mis_weight(bs_pdf, tx_pdf);
+                }
+                if (gen == BF_GEN_RANGE) scalar += si.is_valid() ? si.t : 0.f;
+                else if (gen == BF_GEN_TIME) scalar += si.is_valid() ? si.t / 3.0e8f : 0.f;
+            }
+
+            // ---- loop body (pathtimefrequency.cpp:154-364) ----
+            bool active = true;
+            if (transmitter >= 0) {
+                Spec<S> e = tx_eval<S>(sc, sc.txs[transmitter], si, time, wl);
+#pragma unroll
+                for (int k = 0; k < S; ++k) res.v[k] += emission_weight * thr.v[k] * e.v[k];
+                if (gen == BF_GEN_RANGE) scalar += si.is_valid() ? si.t : 0.f;      // pathlength.cpp:161
+            }
+            active &= si.is_valid();
+            PCG32 rng; { ulonglong2 r = w.rng[l]; rng.state = r.x; rng.inc = r.y; }
+            if ((int) depth > sc.integ.rr_depth) {
+                float q = fminf(hmax_spec<S>(thr) * 1.f, .95f);
+                active &= rng.next_float32() < q;
+                float iq = rcp(q);
+#pragma unroll
+                for (int k = 0; k < S; ++k) thr.v[k] *= iq;
+            }
+            bool go_on = !(depth >= (uint32_t) sc.integ.max_depth || !active);
+            V3 new_d(0.f, 0.f, 0.f);
+            if (go_on) {
+                const uint32_t bsdf = sc.shapes[si.shape].bsdf;
+                bool active_e = bsdf_is_smooth(sc.bsdfs[bsdf]);
+                if (active_e) {
+                    // Scene::sample_transmitter_direction (scene.cpp:249-299)
+                    V2 sample; sample.x = rng.next_float32(); sample.y = rng.next_float32();
+                    DirectionSample ds; Spec<S> tspec;
+                    ds.pdf = 0.f; ds.delta = false; ds.dist = 0.f;
+                    if (sc.n_txs == 1) {
+                        tspec = tx_sample_direction<S>(sc, sc.txs[0], si.p, time, wl, sample, ds);
+                    } else if (sc.n_txs > 1) {
+                        float nt = (float) sc.n_txs, transmitter_pdf = 1.f / nt;
+                        uint32_t index = min((uint32_t) (sample.x * nt), sc.n_txs - 1u);
+                        sample.x = (sample.x - index * transmitter_pdf) * nt;
+                        tspec = tx_sample_direction<S>(sc, sc.txs[index], si.p, time, wl, sample, ds);
+                        ds.pdf *= transmitter_pdf;
+                        float inv = rcp(transmitter_pdf);
+#pragma unroll
+                        for (int k = 0; k < S; ++k) tspec.v[k] *= inv;
+                    }
+                    active_e &= ds.pdf != 0.f;
+                    if (active_e) {
+                        V3 wo = si.to_local(ds.d);
+                        Spec<S> bsdf_val = bsdf_eval<S>(sc, bsdf, wl, si.wi, wo);
+                        float bpdf = bsdf_pdf(sc, bsdf, si.wi, wo);
+                        float mis = ds.delta ? 1.f : mis_weight(ds.pdf, bpdf);
+                        bool nonzero = false;
+#pragma unroll
+                        for (int k = 0; k < S; ++k) { pend.v[k] = mis * thr.v[k] * bsdf_val.v[k] * tspec.v[k]; nonzero |= pend.v[k] != 0.f; }
+                        if (w.records) w.records[l].n_shadow++;
+                        if (nonzero) {   // a zero contribution needs no visibility test
+                            flags |= LANE_PENDING;
+                            push_shadow = true;
+                            w.sh_d[l] = make_float4(ds.d.x, ds.d.y, ds.d.z, ds.dist * (1.f - BF_SHADOW_EPS));
+                        }
+                    }
+                    if (gen == BF_GEN_RANGE) scalar += si.is_valid() ? si.t : 0.f;  // pathlength.cpp:209
+                }
+                // BSDF sampling (pathtimefrequency.cpp:346-364)
+                float s1 = rng.next_float32(); (void) s1;
+                V2 s2; s2.x = rng.next_float32(); s2.y = rng.next_float32();
+                BSDFSample bs;
+                Spec<S> bsdf_val = bsdf_sample<S>(sc, bsdf, wl, si.wi, s2, bs);
+                bool any_nz = false;
+#pragma unroll
+                for (int k = 0; k < S; ++k) { thr.v[k] = thr.v[k] * bsdf_val.v[k]; any_nz |= thr.v[k] != 0.f; }
+                active &= any_nz;
+                if (active) {
+                    new_d = si.to_world(bs.wo);
+                    bs_pdf = bs.pdf;
+                    flags = bs.delta ? (flags | LANE_BS_DELTA) : (flags & ~LANE_BS_DELTA);
+                    push_next = true;
+                }
+                go_on = active;
+            }
+            if (push_next || push_shadow) {
+                // Interaction::spawn_ray (interaction.h:61-64); the shadow ray shares origin and mint
+                float mint = (1.f + hmax_abs(si.p)) * BF_RAY_EPS;
+                w.ray_o[l] = make_float4(si.p.x, si.p.y, si.p.z, mint);
+                if (push_next) w.ray_d[l] = make_float4(new_d.x, new_d.y, new_d.z, bf_inf());
+            }
+            if (!go_on) flags &= ~LANE_ACTIVE;
+            w.flags[l] = flags;
+            w.x1[l] = make_float4(time, phase, bs_pdf, scalar);
+            SpecIO<S>::store(w, l, thr, res, pend, wl);
+            w.rng[l] = make_ulonglong2(rng.state, rng.inc);
+            if (w.records) {
+                bf_sample_record *r = w.records + l;
+                r->depth = depth;
+                if (push_next) r->n_closest++;
+            }
+        }
+        queue_push(push_shadow, l, w.queue_s, ctr + 1, nullptr);
+        queue_push(push_next, l, next_queue, ctr + 0, nullptr);
+    }
+}
+
+// =========================================================================================================
+// finalize: wrappers' binning + SignalBlock::put / ImageBlock::put (single-bin box filter)
+// =========================================================================================================
+#define FIN_THREADS 256
+#define FIN_SMEM_FLOATS 8192
+
+// Sum `val` over the lanes of `peers` (lanes sharing one destination) into the group's leader.
+__device__ __forceinline__ float group_sum(uint32_t peers, float val) {
+    float acc = 0.f;
+    const uint32_t leader = __ffs(peers) - 1;
+#pragma unroll 4
+    for (int i = 0; i < 32; ++i) {
+        float v = __shfl_sync(0xffffffffu, val, i);
+        if ((peers >> i) & 1u) acc += v;
+    }
+    return lane_id() == leader ? acc : 0.f;
+}
+
+template <int S>
+__global__ void __launch_bounds__(FIN_THREADS) k_finalize(const __grid_constant__ DevScene sc, const __grid_constant__ Wave w, uint32_t n,
+                                                         float *__restrict__ profile) {
+    __shared__ float s_hist[FIN_SMEM_FLOATS];
+    const uint32_t C = sc.channels, W = sc.film_w, H = sc.film_h;
+    const uint32_t total_floats = C * W * H;
+    const bool use_smem = total_floats <= FIN_SMEM_FLOATS;
+    if (use_smem) {
+        for (uint32_t i = threadIdx.x; i < total_floats; i += blockDim.x) s_hist[i] = 0.f;
+        __syncthreads();
+    }
+    float *dst = use_smem ? s_hist : profile;
+    const uint32_t gen = sc.integ.gen;
+    const uint32_t stride = gridDim.x * blockDim.x;
+    const uint32_t n_round = (n + 31u) & ~31u;
+    for (uint32_t l = blockIdx.x * blockDim.x + threadIdx.x; l < n_round; l += stride) {
+        int pixel = -1;          // destination pixel or -1
+        float fixed[5] = {0.f, 0.f, 0.f, 0.f, 0.f};
+        uint32_t n_fixed = gen == BF_GEN_PHASE ? 3u : 5u;
+        int var_ch = -1;         // the single non-zero wrapper channel of this sample
+        float var_val = 0.f;
+        uint32_t var_rep = 1;    // gen 1 writes the value to 3 consecutive channels
+        if (l < n) {
+            uint32_t flags = w.flags[l];
+            float4 x1 = w.x1[l], x2 = w.x2[l];
+            Spec<S> thr, res, pend, wl;
+            SpecIO<S>::load(w, l, thr, res, pend, wl);
+            if ((flags & LANE_PENDING) && !w.occl[l]) {
+#pragma unroll
+                for (int k = 0; k < S; ++k) res.v[k] += pend.v[k];
+            }
+            Spec<S> weight = SpecIO<S>::load_weight(w, l, x2);
+            const bool valid = flags & LANE_VALID;
+            float posx, posy;
+            int off_x = 0, off_y = 0;
+            if (gen == BF_GEN_PHASE) {
+                const DevEndpoint &rx = *sc.rx;
+                // integrator.cpp:1588-1639
+                float tfx = 0.f, tfy = 0.f;
+                bool ran = true;
+                float wl0 = wl.v[0];
+                float phase = valid ? x1.y : 0.f;
+                if (rx.receive_type == BF_RECV_MIX_RESAMPLE) {
+                    tfx = x2.x - rx.adc_sampling_start;
+                    tfy = (float) fabs(freq_from_wl_d(sc.C.c, wl0) - (double) x2.y);
+                } else if (rx.receive_type == BF_RECV_RAW || rx.receive_type == BF_RECV_RAW_RESAMPLE) {
+                    tfx = x2.x - rx.adc_sampling_start;
+                    tfy = freq_from_wl(sc.C.c, wl0);
+                } else {
+                    ran = false;
+                }
+                if (!ran) {
+#pragma unroll
+                    for (int k = 0; k < S; ++k) res.v[k] = 0.f;
+                    phase = 0.f;
+                }
+                // phase.cpp:117-124
+                float hs = hsum_spec<S>(res);
+                float ph = fmodf(phase, BF_TWO_PI);
+                ph += ph < 0.f ? BF_TWO_PI : 0.f;
+                if (ran && sc.integ.phase_bins > 0) {
+                    float bin_width = BF_TWO_PI / (float) sc.integ.phase_bins;
+                    float pv = (valid && ran) ? hs : 0.f;
+                    for (uint32_t k = 0; k < sc.integ.phase_bins; ++k) {
+                        float centre = (float) ((double) bin_width * ((double) k + 0.5));
+                        if (rect((ph - centre) / bin_width) > 0.f && pv != 0.f) { var_ch = 3 + (int) k; var_val = pv; }
+                    }
+                }
+                tfx *= (float) sc.adc.t_bins / sc.adc.t_bandwidth;
+                tfy *= (float) sc.adc.f_bins / sc.adc.f_bandwidth;
+                Spec<S> wres;
+#pragma unroll
+                for (int k = 0; k < S; ++k) wres.v[k] = fabsf(weight.v[k]) * res.v[k];
+                fixed[0] = (valid && ran) ? hsum_spec<S>(wres) : 0.f;
+                fixed[1] = (valid && ran) ? 1.f : 0.f;
+                fixed[2] = 1.f;
+                posx = tfx; posy = tfy;
+                off_x = (int) sc.adc.window_offset_t; off_y = (int) sc.adc.window_offset_f;
+                if (w.records) {
+                    bf_sample_record *r = w.records + l;
+                    r->valid = (valid && ran) ? 1u : 0u; r->tf_t = tfx; r->tf_f = tfy; r->value = fixed[0];
+                    r->phase = phase; r->wavelength0 = wl0;
+                }
+            } else {
+                // range.cpp:141-161 / time.cpp:118-153: bins from the UNWEIGHTED spectrum, first channel
+                float scalar = x1.w, r0 = res.v[0];
+                if (gen == BF_GEN_RANGE) {
+                    for (uint32_t i = 0; i < sc.integ.range_bins; ++i) {
+                        float lo = (float) i * sc.integ.dr, hi = (float) i * sc.integ.dr + sc.integ.dr;
+                        if (scalar >= lo && scalar < hi && r0 != 0.f) { var_ch = 5 + (int) i; var_val = r0; }
+                    }
+                } else {
+                    const float dt = 0.5e-9f;
+                    for (int i = 0; i < 50; ++i) {
+                        float lo = (float) i * dt, hi = (float) i * dt + dt;
+                        if (scalar >= lo && scalar < hi && r0 != 0.f) { var_ch = 5 + 3 * i; var_val = r0; var_rep = 3; }
+                    }
+                }
+                Spec<S> wres;
+#pragma unroll
+                for (int k = 0; k < S; ++k) wres.v[k] = weight.v[k] * res.v[k];
+                // mono: xyz = value broadcast; spectral: the CIE matching functions vanish at radar wavelengths
+                float x = S == 1 ? wres.v[0] : 0.f;
+                fixed[0] = x; fixed[1] = x; fixed[2] = x; fixed[3] = valid ? 1.f : 0.f; fixed[4] = 1.f;
+                posx = x2.x; posy = x2.y;
+                if (w.records) {
+                    bf_sample_record *r = w.records + l;
+                    r->valid = valid ? 1u : 0u; r->tf_t = posx; r->tf_f = posy; r->value = r0; r->phase = scalar; r->wavelength0 = wl.v[0];
+                }
+            }
+            // SignalBlock::put, box filter of radius 0.5 (signalblock.cpp:162-169)
+            float px = posx - ((float) off_x - 0.f + .5f), py = posy - ((float) off_y - 0.f + .5f);
+            float cx = ceilf(px - .5f), cy = ceilf(py - .5f);
+            if (cx >= 0.f && cy >= 0.f && cx < (float) W && cy < (float) H) pixel = (int) ((uint32_t) cy * W + (uint32_t) cx);
+        }
+        // warp aggregation: lanes that hit the same pixel are summed in registers, one atomic per group
+        uint32_t peers = __match_any_sync(0xffffffffu, pixel);
+        const bool leader = lane_id() == (uint32_t) (__ffs(peers) - 1);
+        for (uint32_t c = 0; c < n_fixed; ++c) {
+            float s = group_sum(peers, fixed[c]);
+            if (leader && pixel >= 0 && s != 0.f) atomicAdd(dst + (size_t) C * pixel + c, s);
+        }
+        int key = (pixel >= 0 && var_ch >= 0) ? pixel * (int) C + var_ch : -1;
+        if (__any_sync(0xffffffffu, key >= 0)) {
+            uint32_t vp = __match_any_sync(0xffffffffu, key);
+            float s = group_sum(vp, var_val);
+            if (lane_id() == (uint32_t) (__ffs(vp) - 1) && key >= 0)
+                for (uint32_t r = 0; r < var_rep; ++r) atomicAdd(dst + key + r, s);
+        }
+    }
+    if (use_smem) {
+        __syncthreads();
+        for (uint32_t i = threadIdx.x; i < total_floats; i += blockDim.x) {
+            float v = s_hist[i];
+            if (v != 0.f) atomicAdd(profile + i, v);
+        }
+    }
+}
+
+// =========================================================================================================
+// launchers
+// =========================================================================================================
+static int trace_grid(const LaunchCfg &cfg) { return cfg.sm_count * 8; }
+
+int launch_raygen(const DevScene &sc, const Wave &w, uint64_t seed, uint64_t first_sample, uint32_t n, const LaunchCfg &cfg) {
+    if (n == 0) return 0;
+    dim3 grid((n + 255) / 256), block(256);
+    if (sc.S == 1) k_raygen<1><<<grid, block, 0, cfg.stream>>>(sc, w, seed, first_sample, n);
+    else k_raygen<4><<<grid, block, 0, cfg.stream>>>(sc, w, seed, first_sample, n);
+    return 1;
+}
+int launch_trace_closest(const DevScene &sc, const Wave &w, const uint32_t *queue, const uint32_t *count, uint32_t n_direct,
+                         uint32_t *work_cursor, const LaunchCfg &cfg) {
+    k_trace<false><<<trace_grid(cfg), TRACE_THREADS, 0, cfg.stream>>>(sc, w.ray_o, w.ray_d, queue, count, n_direct, w.hit, nullptr, work_cursor, w.totals + 0);
+    return 1;
+}
+int launch_trace_shadow(const DevScene &sc, const Wave &w, const uint32_t *queue, const uint32_t *count, uint32_t *work_cursor,
+                        const LaunchCfg &cfg) {
+    k_trace<true><<<trace_grid(cfg), TRACE_THREADS, 0, cfg.stream>>>(sc, w.ray_o, w.sh_d, queue, count, 0, nullptr, w.occl, work_cursor, w.totals + 1);
+    return 1;
+}
+int launch_shade(const DevScene &sc, const Wave &w, uint32_t depth, const uint32_t *queue, const uint32_t *count, uint32_t n_direct,
+                 uint32_t *next_queue, uint32_t *ctr_block, const LaunchCfg &cfg) {
+    int grid = cfg.sm_count * 8;
+    if (!queue) grid = (int) min((uint32_t) grid, (n_direct + 127u) / 128u);
+    if (grid < 1) grid = 1;
+    if (sc.S == 1) k_shade<1><<<grid, 128, 0, cfg.stream>>>(sc, w, depth, queue, count, n_direct, next_queue, ctr_block);
+    else k_shade<4><<<grid, 128, 0, cfg.stream>>>(sc, w, depth, queue, count, n_direct, next_queue, ctr_block);
+    return 1;
+}
+int launch_finalize(const DevScene &sc, const Wave &w, uint32_t n, float *profile, const LaunchCfg &cfg) {
+    if (n == 0) return 0;
+    int grid = (int) min((uint32_t) (cfg.sm_count * 4), (n + FIN_THREADS - 1) / FIN_THREADS);
+    if (sc.S == 1) k_finalize<1><<<grid, FIN_THREADS, 0, cfg.stream>>>(sc, w, n, profile);
+    else k_finalize<4><<<grid, FIN_THREADS, 0, cfg.stream>>>(sc, w, n, profile);
+    return 1;
+}
+int launch_trace_rays(const DevScene &sc, const float4 *ray_o, const float4 *ray_d, uint32_t n, float4 *hit, uint32_t *occl,
+                      uint32_t *work_cursor, const LaunchCfg &cfg) {
+    if (n == 0) return 0;
+    if (hit) k_trace<false><<<trace_grid(cfg), TRACE_THREADS, 0, cfg.stream>>>(sc, ray_o, ray_d, nullptr, nullptr, n, hit, nullptr, work_cursor, nullptr);
+    else k_trace<true><<<trace_grid(cfg), TRACE_THREADS, 0, cfg.stream>>>(sc, ray_o, ray_d, nullptr, nullptr, n, nullptr, occl, work_cursor, nullptr);
+    return 1;
+}
+int launch_resolve_hits(const DevScene &sc, const float4 *hit, uint32_t n, uint32_t *shape, uint32_t *prim, const LaunchCfg &cfg) {
+    if (n == 0) return 0;
+    k_resolve_hits<<<(n + 255) / 256, 256, 0, cfg.stream>>>(sc, hit, n, shape, prim);
+    return 1;
+}
+
+}  // namespace bf

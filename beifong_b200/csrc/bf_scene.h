@@ -1,0 +1,89 @@
+// beifong_b200 — flattened scene: the POD tables the kernels read and the host object behind the
+// C ABI handle.  Mirrors what Scene::Scene (src/librender/scene.cpp:22-120) and
+// Shape::Shape (src/librender/shape.cpp:38-99) gather from the plugin tree.
+#pragma once
+#include <stdint.h>
+#include <string>
+#include <vector>
+#include <vector_types.h>
+
+#include "../../include/beifong_b200/abi.h"
+#include "../../include/beifong_b200/flat_scene.h"
+#include "bf_math.h"
+#include "bf_bvh.h"
+
+namespace bf {
+
+#define BF_MAX_RECTS 64u
+
+// Rectangle (src/shapes/rectangle.cpp:83-95): everything derived from to_world at load time.
+struct DevRect {
+    M4 to_world, to_object;
+    V3 fs, ft, fn;          // m_frame: dp_du, dp_dv (not normalised), normal
+    V3 ns, nt, nn;          // normalize(frame.s/t/n), used by sample_wigner (rectangle.cpp:152-158)
+    float area, inv_area;   // |s x t|
+    float wid_x, wid_y;     // |s|, |t|
+    uint32_t shape;         // scene shape id
+    uint32_t pad;
+};
+struct DevShape {
+    uint32_t type;          // 0 mesh, 1 rectangle
+    uint32_t index;         // mesh index / rectangle index
+    uint32_t bsdf;
+    int32_t tx;             // transmitter / emitter id attached to the shape, -1 none
+    uint32_t has_normals;   // vertex normals present (Mesh::has_vertex_normals)
+    uint32_t pad[3];
+};
+// Spectrum texture (src/spectra/uniform.cpp, regular.cpp, irregular.cpp)
+struct DevSpectrum {
+    uint32_t kind, n, offset;   // offset into the float pool: lambda[n] then value[n]
+    float inv_interval;         // regular: 1 / ((hi - lo) / (n - 1))
+};
+struct DevEndpoint {
+    uint32_t kind, texture, receive_type;
+    int32_t shape;              // parent shape id, -1 if free standing
+    bf_signal_desc signal;
+    float adc_sampling_start, adc_sampling_time;
+    float cutoff, inv_transition, cos_cutoff, cos_beam;   // spot.cpp:85-93
+    float near_clip, far_clip, shutter_open, shutter_open_time;
+    uint32_t film_width, film_height;
+    M4 to_world, to_object, sample_to_camera;
+};
+
+// Passed to every kernel by value (constant bank): pointers to the tables + small constants.
+struct DevScene {
+    bf_constants C;
+    uint32_t S;
+    uint32_t n_rects, n_shapes, n_txs, n_nodes, n_tris;
+    const uint4 *nodes;        // 5 per node
+    const float4 *tris;        // 3 per triangle (leaf order)
+    const float4 *tri_nrm;     // 3 per triangle (vertex normals, leaf order) or null
+    const DevRect *rects;
+    const DevShape *shapes;
+    const bf_bsdf_desc *bsdfs;
+    const DevSpectrum *spectra;
+    const float *spec_pool;
+    const DevEndpoint *txs;
+    const DevEndpoint *rx;
+    bf_adc_desc adc;
+    bf_integrator_desc integ;
+    uint32_t film_w, film_h, channels;
+    uint32_t rx_needs_aperture;
+    double phase_denom;        // (lambda_max - lambda_min) / 2 * 1e-9 evaluated like ray.h:92
+};
+
+struct HostMesh {
+    std::vector<float> pos;
+    std::vector<uint32_t> idx;
+    std::vector<float> nrm;
+    uint32_t nv = 0, nf = 0;
+};
+struct HostSpectrum {
+    uint32_t kind = 0;
+    std::vector<float> lambda, value;
+};
+
+DevRect make_rect(const float *to_world16, uint32_t shape);
+M4 m4_inverse(const M4 &a);
+
+}  // namespace bf

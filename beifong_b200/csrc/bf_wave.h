@@ -1,0 +1,65 @@
+// beifong_b200 — wavefront state (SoA in HBM) and the kernel launchers.
+//
+// One lane = one radar path sample (one iteration of SamplingIntegrator::receive_sample,
+// src/librender/integrator.cpp:1538-1667, or render_sample, :255-310).  A wave of lanes is carried
+// through   raygen -> trace(closest) -> [ shade -> trace(shadow) + trace(closest) ]* -> bin scatter
+// with lane ids compacted into queues between stages.  All arrays are indexed by lane id, 16-byte
+// records so that every access is one 128-bit load/store.
+#pragma once
+#include <cuda_runtime.h>
+#include "bf_scene.h"
+
+namespace bf {
+
+enum : uint32_t { LANE_ACTIVE = 1u, LANE_VALID = 2u, LANE_BS_DELTA = 4u, LANE_PENDING = 8u };
+
+#define BF_MAX_BOUNCES 1024u
+#define BF_TRACE_SM_STACK 8        // traversal stack entries kept in shared memory per thread
+#define BF_TRACE_LOCAL_STACK 56    // deeper entries spill to local memory
+#define BF_TRACE_STACK_DEPTH (BF_TRACE_SM_STACK + BF_TRACE_LOCAL_STACK)
+#define BF_CTR_STRIDE 8u     // per-depth counter block: [0] next-closest count, [1] shadow count,
+                             // [2] closest work cursor, [3] shadow work cursor, [4] shade cursor
+
+struct Wave {
+    uint32_t capacity;
+    float4 *ray_o;       // o.xyz, mint         (shared by the continuation and the shadow ray)
+    float4 *ray_d;       // d.xyz, maxt         continuation ray
+    float4 *sh_d;        // d.xyz, maxt         shadow ray
+    float4 *hit;         // t, u, v, slot       closest-hit result (slot: leaf-order triangle index,
+                         //                     0x80000000|rect index for rectangles)
+    uint32_t *occl;      // any-hit result
+    ulonglong2 *rng;     // PCG32 state, inc
+    float4 *x1;          // time, phase, bs.pdf, scalar (gen 2 path length / gen 1 path time)
+    float4 *x2;          // gen 3: sample time, f_rx ; gen 1/2: film position ; .w = ray weight (S = 1)
+    float4 *spec[5];     // S = 1: [0] = (throughput, result, pending, wavelength)
+                         // S = 4: throughput, result, pending, wavelengths, ray weight
+    uint32_t *flags;
+    uint32_t *queue[2];  // ping-pong lane-id queues for continuation rays
+    uint32_t *queue_s;   // lane-id queue for shadow rays
+    uint32_t *counters;  // BF_CTR_STRIDE * (BF_MAX_BOUNCES + 2)
+    unsigned long long *totals;  // [0] closest queries traced, [1] shadow queries traced
+    bf_sample_record *records;   // optional per-lane debug records
+};
+
+struct LaunchCfg {
+    cudaStream_t stream;
+    int sm_count;
+};
+
+// Kernel launchers (bf_kernels.cu).  Return the number of kernels launched.
+int launch_raygen(const DevScene &sc, const Wave &w, uint64_t seed, uint64_t first_sample, uint32_t n, const LaunchCfg &cfg);
+// queue == nullptr: lanes [0, n_direct); else lane ids from queue[0 .. *count)
+int launch_trace_closest(const DevScene &sc, const Wave &w, const uint32_t *queue, const uint32_t *count, uint32_t n_direct,
+                         uint32_t *work_cursor, const LaunchCfg &cfg);
+int launch_trace_shadow(const DevScene &sc, const Wave &w, const uint32_t *queue, const uint32_t *count, uint32_t *work_cursor,
+                        const LaunchCfg &cfg);
+int launch_shade(const DevScene &sc, const Wave &w, uint32_t depth, const uint32_t *queue, const uint32_t *count, uint32_t n_direct,
+                 uint32_t *next_queue, uint32_t *ctr_block, const LaunchCfg &cfg);
+int launch_finalize(const DevScene &sc, const Wave &w, uint32_t n, float *profile, const LaunchCfg &cfg);
+// Stand-alone ray queries (Scene::ray_intersect_preliminary / ray_test for caller-provided rays)
+int launch_trace_rays(const DevScene &sc, const float4 *ray_o, const float4 *ray_d, uint32_t n, float4 *hit, uint32_t *occl,
+                      uint32_t *work_cursor, const LaunchCfg &cfg);
+// resolve (slot -> shape, prim) for hits produced by launch_trace_rays
+int launch_resolve_hits(const DevScene &sc, const float4 *hit, uint32_t n, uint32_t *shape, uint32_t *prim, const LaunchCfg &cfg);
+
+}  // namespace bf

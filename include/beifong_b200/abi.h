@@ -225,6 +225,11 @@ int bf_scene_set_integrator(bf_scene *s, const bf_integrator_desc *desc);
  * compressed 8-wide nodes, upload.  Re-commit after bf_scene_update_* is allowed. */
 int bf_scene_commit(bf_scene *s, int device);
 int bf_scene_update_rect(bf_scene *s, uint32_t shape_id, const float to_world[16]);
+/* Copy the flattened geometry (BVH nodes, triangles, normals) again from the library's pinned host
+ * image to the device without rebuilding: the host->device leg of Scene::accel_init_gpu
+ * (scene_optix.inl:236-300) on its own, used to time the path end to end from host buffers. */
+int bf_scene_reupload(bf_scene *s);
+int bf_scene_device_bytes(const bf_scene *s, size_t *geometry_bytes);
 
 /* Number of fp32 channels per bin: gen 3: ["Y","A","W"] + phase_bins
  * (integrator.cpp:359-370, phase.cpp:140-145); gen 1/2: ["X","Y","Z","A","W"] + bins. */
@@ -260,6 +265,9 @@ int bf_get_stats(const bf_scene *s, bf_stats *stats);
 /* Time (ms, CUDA events on the scene's stream) of the most recent bf_receive: whole call
  * and the traverse kernels alone. */
 int bf_last_receive_ms(bf_scene *s, float *total_ms, float *traverse_ms);
+/* Record CUDA events around every traversal launch so that bf_last_receive_ms can report
+ * traverse_ms (-1 when disabled, the default). */
+int bf_set_trace_timing(bf_scene *s, int enabled);
 
 /* Flat export of everything added so far (test infrastructure feeds it to the CPU oracle;
  * also a cheap checkpoint: profile + (seed, next index) + this blob is a resumable state). */
