@@ -1,0 +1,115 @@
+"""The benchmark / parity configurations of BASELINE.json as concrete scenes.
+
+Each builder returns an un-committed FlatScene.  Meshes named by BASELINE.json that are missing from
+the reference tree (.MISSING_LARGE_BLOBS: Car-body.ply, Motorbike, Bus) are replaced by procedural
+stand-ins of the same triangle-count class (beifong_b200.meshes); this is stated in every result.
+"""
+import numpy as np
+
+from . import _native as N
+from .meshes import Transform as T
+from . import meshes
+from .scene import FlatScene, RADAR_94GHZ
+
+C0 = 299792458.0
+
+
+def rect_to_world(scale_xy, origin, target, up=(0, 0, 1)):
+    """<scale x y/> followed by <lookat/>: later XML transforms multiply from the left (xml.cpp:918)."""
+    return (T.look_at(origin, target, up) * T.scale([scale_xy[0], scale_xy[1], 1.0])).matrix32()
+
+
+def c1_trans_rad(spectrum_width=1, max_depth=-1, rr_depth=5):
+    """python_scripts/trans_rad.xml verbatim: fluxmeter on a 0.05 x 0.05 rectangle at the origin facing -y,
+    spot emitter (cutoff 25, beam 20), 1 x 1 target at y = -4, 20 x 20 ground at z = -0.5, all
+    twosided(diffuse 1.0); gen-1 integrator time(pathtime): 50 bins of 0.5 ns."""
+    s = FlatScene(spectrum_width=spectrum_width)          # reference defaults (spectrum.h:15-40)
+    default_bsdf = s.add_diffuse(0.5, two_sided=False)     # Shape's default BSDF (shape.cpp:52-60)
+    material = s.add_diffuse(1.0, two_sided=True)
+    rx = s.add_rect(rect_to_world((0.05, 0.05), (0, 0, 0), (0, -1, 0)), default_bsdf)
+    s.add_rect(rect_to_world((1, 1), (0, -4, 0), (0, 0, 0)), material)
+    s.add_rect(rect_to_world((20, 20), (0, 0, -0.5), (0, 0, 0.5), up=(0, 1, 0)), material)
+    intensity = s.add_uniform(1.0)
+    spot = FlatScene.endpoint(N.BF_TX_SPOT, texture=intensity, cutoff_angle_deg=25.0, beam_width_deg=20.0,
+                              to_world=T.look_at((0, 0, 0), (0, -1, 0), (0, 0, 1)).matrix32())
+    s.add_transmitter(None, spot)
+    s.set_receiver(rx, FlatScene.endpoint(N.BF_RX_FLUXMETER))
+    s.set_integrator(N.BF_GEN_TIME, max_depth=max_depth, rr_depth=rr_depth)
+    return s
+
+
+def fmcw_signal(resample_freq, gain=1.0):
+    # Receive.ipynb cell 5: 94 GHz centre, 6 GHz sweep, 200 us chirp
+    return FlatScene.signal(N.BF_SIG_LINFMCW, sig_is_delta=True, resample_freq=resample_freq, amplitude=1.0,
+                            repfreq=1.0 / 200e-6, t_ext=200e-6, f_centre=94e9, f_ext=6e9, gain=gain)
+
+
+def radar_scene(mesh_pos, mesh_faces, spectrum_width=1, max_depth=4, range_bins=1024, bin_m=0.03, smooth_normals=True,
+                extra_meshes=()):
+    """Common 94 GHz FMCW layout of python_scripts/Render.py / Receive.ipynb: Tx and Rx are 5 mm x 5 mm
+    rectangles at (0, 0, 0.3) facing +x, ground 20 x 20 diffuse 0.5, corner reflector 0.1 x 0.05 diffuse 1,
+    target mesh twosided(roughconductor alpha 0.1).  Receiver `wignerreceiver` (mix_resample) + transmitter
+    `wignertransmitter` (resample_freq): beat frequency = sweep rate x delay, binned on the frequency axis."""
+    s = FlatScene(spectrum_width=spectrum_width, **RADAR_94GHZ)
+    default_bsdf = s.add_diffuse(0.5, two_sided=False)
+    ground = s.add_diffuse(0.5, two_sided=True)
+    refl = s.add_diffuse(1.0, two_sided=True)
+    # twosided(roughconductor): Beckmann alpha 0.1; a perfect conductor at radar wavelengths (the
+    # reference's default Cu table evaluates to eta = k = 0 outside the visible range => F = 1)
+    eta, k = s.add_uniform(0.0), s.add_uniform(1.0)
+    car = s.add_bsdf(N.BF_BSDF_ROUGHCONDUCTOR, two_sided=True, eta=eta, k=k, alpha_u=0.1, alpha_v=0.1)
+    ant = (T.translate([0.0, 0.0, 0.3]) * T.rotate([0, 1, 0], 90.0) * T.scale([0.0025, 0.0025, 1.0]))
+    rx = s.add_rect(ant.matrix32(), default_bsdf)
+    tx = s.add_rect((T.translate([0.0, 0.01, 0.0]) * ant).matrix32(), default_bsdf)
+    s.add_rect((T.translate([0, 0, 0]) * T.scale([20.0, 20.0, 1.0])).matrix32(), ground)
+    s.add_rect((T.translate([6.0, -2.0, 0.5]) * T.rotate([0, 1, 0], -90.0) * T.scale([0.05, 0.025, 1.0])).matrix32(), refl)
+    nrm = meshes.vertex_normals(mesh_pos, mesh_faces) if smooth_normals else None
+    s.add_mesh(mesh_pos, mesh_faces, car, normals=nrm)
+    for (p, f) in extra_meshes:
+        s.add_mesh(p, f, car, normals=meshes.vertex_normals(p, f) if smooth_normals else None)
+    tex = s.add_uniform(1.0)
+    s.add_transmitter(tx, FlatScene.endpoint(N.BF_TX_WIGNER, texture=tex, signal=fmcw_signal(True)))
+    sweep_rate = 6e9 / 200e-6
+    f_bandwidth = range_bins * bin_m * 2.0 / C0 * sweep_rate
+    s.set_receiver(rx, FlatScene.endpoint(N.BF_RX_WIGNER, texture=tex, signal=fmcw_signal(False), receive_type=N.BF_RECV_MIX_RESAMPLE,
+                                          adc_sampling_start=20e-6, adc_sampling_time=160e-6))
+    s.set_adc(t_bins=1, f_bins=range_bins, t_bandwidth=200e-6, f_bandwidth=f_bandwidth)
+    s.set_integrator(N.BF_GEN_PHASE, max_depth=max_depth, rr_depth=5, phase_bins=1)
+    return s
+
+
+def car_pose():
+    # Render.py:305-316: rotate x 90, rotate z -20, translate (10, 3, 1); the stand-in is already z-up
+    return T.translate([10.0, 3.0, 1.0]) * T.rotate([0, 0, 1], -20.0)
+
+
+def c2_car_body(spectrum_width=1, max_depth=4, n_u=264, n_v=133):
+    """BASELINE config 2: car-body mesh (procedural stand-in, 69 696 triangles), 1 Tx / 1 Rx, 3 bounces."""
+    p, f = meshes.car_body(n_u, n_v)
+    p = meshes.transform_points(car_pose().matrix32(), p)
+    return radar_scene(p, f, spectrum_width=spectrum_width, max_depth=max_depth)
+
+
+def small_radar(spectrum_width=1, max_depth=4, n_u=24, n_v=13, smooth_normals=True):
+    """The C2 layout with a few hundred triangles: sized for the brute-force oracle."""
+    p, f = meshes.car_body(n_u, n_v)
+    p = meshes.transform_points(car_pose().matrix32(), p)
+    return radar_scene(p, f, spectrum_width=spectrum_width, max_depth=max_depth, smooth_normals=smooth_normals)
+
+
+def c3_multi_object(spectrum_width=1, max_depth=4, copies=14, n_u=264, n_v=133, f_bins=1024, t_bins=1024):
+    """BASELINE config 3 stand-in: `copies` car bodies on a 7 x 2 grid (~1 M triangles), 1024 x 1024 ADC."""
+    base_p, base_f = meshes.car_body(n_u, n_v)
+    extra = []
+    first = None
+    for i in range(copies):
+        gx, gy = i % 7, i // 7
+        scale = 1.0 if i % 2 == 0 else 2.2
+        m = (T.translate([8.0 + 3.0 * gx * 2.0, -6.0 + 12.0 * gy, 1.0 * scale]) * T.rotate([0, 0, 1], 17.0 * i) * T.scale(scale)).matrix32()
+        p = meshes.transform_points(m, base_p)
+        if first is None:
+            first = (p, base_f)
+        else:
+            extra.append((p, base_f))
+    s = radar_scene(first[0], first[1], spectrum_width=spectrum_width, max_depth=max_depth, extra_meshes=extra)
+    return s

@@ -1,0 +1,109 @@
+"""GPU parity: the CUDA path through the C ABI against the CPU oracle on the same seeded inputs."""
+import numpy as np
+import pytest
+
+from beifong_b200 import configs, meshes
+from beifong_b200 import _native as N
+from oracle_lib import OracleScene
+
+pytestmark = pytest.mark.gpu
+
+
+def rel_l2(a, b):
+    a, b = np.asarray(a, np.float64), np.asarray(b, np.float64)
+    return np.linalg.norm(a - b) / max(np.linalg.norm(b), 1e-300)
+
+
+def random_rays(n, seed, center, radius):
+    rng = np.random.default_rng(seed)
+    o = rng.normal(size=(n, 3))
+    o = center + radius * o / np.linalg.norm(o, axis=1, keepdims=True)
+    tgt = center + rng.uniform(-0.4, 0.4, size=(n, 3)) * radius
+    d = tgt - o
+    d /= np.linalg.norm(d, axis=1, keepdims=True)
+    return o.astype(np.float32), d.astype(np.float32)
+
+
+@pytest.fixture(scope="module")
+def small(native):
+    s = configs.small_radar(spectrum_width=1).commit()
+    orc = OracleScene(s.export(), accel=OracleScene.BRUTE)
+    yield s, orc
+    s.close()
+
+
+def test_first_hits_small_vs_bruteforce(small):
+    s, orc = small
+    o, d = random_rays(20000, 1, np.array([10.0, 3.0, 1.0]), 6.0)
+    g = s.trace_first_hits(o, d)
+    c = orc.trace_first_hits(o, d, accel=0)
+    assert np.array_equal(g[0], c[0]) and np.array_equal(g[1], c[1])
+    hit = c[0] != N.BF_NONE
+    assert hit.sum() > 2000
+    for k in (2, 3, 4):     # t, u, v bit-exact
+        assert np.array_equal(g[k][hit].view(np.uint32), c[k][hit].view(np.uint32))
+    assert np.all(np.isinf(g[2][~hit]))
+
+
+def test_occlusion_small_vs_bruteforce(small):
+    s, orc = small
+    o, d = random_rays(20000, 2, np.array([10.0, 3.0, 1.0]), 6.0)
+    maxt = np.random.default_rng(3).uniform(1.0, 12.0, size=len(o)).astype(np.float32)
+    g = s.trace_occluded(o, d, maxt=maxt)
+    c = orc.trace_occluded(o, d, maxt=maxt, accel=0)
+    assert np.array_equal(g, c)
+    assert 0 < g.sum() < len(g)
+
+
+@pytest.mark.parametrize("width", [1, 4])
+def test_sample_records_small(native, width):
+    s = configs.small_radar(spectrum_width=width).commit()
+    orc = OracleScene(s.export(), accel=OracleScene.BRUTE)
+    n = 20000
+    g = s.sample_records(n, seed=7)
+    c = orc.sample_records(n, seed=7)
+    same_first = (g["first_shape"] == c["first_shape"]) & (g["first_prim"] == c["first_prim"])
+    assert same_first.mean() >= 0.9999
+    assert np.array_equal(g["first_t"][same_first].view(np.uint32), c["first_t"][same_first].view(np.uint32))
+    agree = same_first & (g["depth"] == c["depth"]) & (g["n_closest"] == c["n_closest"]) & (g["n_shadow"] == c["n_shadow"])
+    assert agree.mean() >= 0.999
+    assert (c["valid"] == 1).mean() > 0.3
+    both = agree & (c["value"] != 0)
+    assert both.sum() > 100
+    assert np.allclose(g["value"][both], c["value"][both], rtol=2e-4, atol=0)
+    assert np.allclose(g["tf_f"][both], c["tf_f"][both], rtol=1e-5, atol=1.5)
+    s.close()
+
+
+@pytest.mark.parametrize("width", [1, 4])
+def test_profile_small(native, width):
+    s = configs.small_radar(spectrum_width=width).commit()
+    orc = OracleScene(s.export(), accel=OracleScene.BVH)
+    n = 1 << 18
+    s.receive(n, seed=11)
+    g = s.profile()
+    c = orc.receive(n, seed=11, threads=8)
+    assert g.shape == c.shape
+    # weight and alpha channels are exact counts
+    assert g[..., 2].sum() == pytest.approx(c[..., 2].sum(), abs=0.5)
+    assert abs(g[..., 1].sum() - c[..., 1].sum()) <= 1e-4 * n
+    # range-profile relative L2 error (north_star: <= 1e-3 at equal spp)
+    assert rel_l2(g[..., 0], c[..., 0]) <= 1e-3
+    assert rel_l2(g[..., 3], c[..., 3]) <= 1e-3
+    assert c[..., 0].sum() > 0
+    s.close()
+
+
+def test_c1_trans_rad(native):
+    s = configs.c1_trans_rad(spectrum_width=1).commit()
+    orc = OracleScene(s.export(), accel=OracleScene.BRUTE)
+    n = 100000
+    s.receive(n, seed=0)
+    g = s.profile()
+    c = orc.receive(n, seed=0, threads=8)
+    assert g.shape == c.shape == (1, 1, 155)
+    assert g[0, 0, 4] == n
+    assert c[0, 0, 5:].sum() > 0
+    assert rel_l2(g[0, 0, 5:], c[0, 0, 5:]) <= 1e-3
+    assert rel_l2(g[0, 0, :3], c[0, 0, :3]) <= 1e-3
+    s.close()
