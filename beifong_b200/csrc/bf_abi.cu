@@ -110,7 +110,7 @@ struct bf_scene {
     // stats / timing
     bf_stats stats;
     cudaEvent_t ev_begin = nullptr, ev_end = nullptr;
-    std::vector<cudaEvent_t> ev_trace; size_t ev_trace_used = 0;
+    std::vector<cudaEvent_t> ev_trace; size_t ev_trace_used = 0; std::vector<uint8_t> ev_kind;
     bool time_trace = false;
 };
 
@@ -585,10 +585,11 @@ static int ensure_wave(bf_scene *s, uint32_t lanes, bool records) {
     return BF_OK;
 }
 
-static cudaEvent_t next_trace_event(bf_scene *s) {
+static cudaEvent_t next_trace_event(bf_scene *s, int kind) {
     if (s->ev_trace_used == s->ev_trace.size()) {
-        cudaEvent_t e; cudaEventCreate(&e); s->ev_trace.push_back(e);
+        cudaEvent_t e; cudaEventCreate(&e); s->ev_trace.push_back(e); s->ev_kind.push_back(0);
     }
+    s->ev_kind[s->ev_trace_used] = (uint8_t) kind;
     return s->ev_trace[s->ev_trace_used++];
 }
 
@@ -603,26 +604,26 @@ static int run_wave(bf_scene *s, uint64_t seed, uint64_t first, uint32_t n, floa
     const uint32_t ctr_blocks = unbounded ? BF_MAX_BOUNCES + 2 : max_depth + 2;
     BF_CUDA(cudaMemsetAsync(ctr, 0, (size_t) BF_CTR_STRIDE * ctr_blocks * 4, s->stream));
     uint64_t launches = 0;
-    launches += launch_raygen(sc, w, seed, first, n, cfg);
-    auto timed = [&](auto &&fn) {
-        if (s->time_trace) { cudaEventRecord(next_trace_event(s), s->stream); }
+    auto timed = [&](int kind, auto &&fn) {
+        if (s->time_trace) { cudaEventRecord(next_trace_event(s, kind), s->stream); }
         launches += fn();
-        if (s->time_trace) { cudaEventRecord(next_trace_event(s), s->stream); }
+        if (s->time_trace) { cudaEventRecord(next_trace_event(s, kind), s->stream); }
     };
-    timed([&] { return launch_trace_closest(sc, w, nullptr, nullptr, n, ctr + 2, cfg); });
+    timed(BF_K_RAYGEN, [&] { return launch_raygen(sc, w, seed, first, n, cfg); });
+    timed(BF_K_TRACE_CLOSEST, [&] { return launch_trace_closest(sc, w, nullptr, nullptr, n, ctr + 2, cfg); });
     for (uint32_t depth = 1; depth <= max_depth; ++depth) {
         uint32_t *blk = ctr + (size_t) BF_CTR_STRIDE * depth, *prev = ctr + (size_t) BF_CTR_STRIDE * (depth - 1);
-        launches += launch_shade(sc, w, depth, depth == 1 ? nullptr : w.queue[(depth - 1) & 1], prev + 0, n, w.queue[depth & 1], blk, cfg);
+        timed(BF_K_SHADE, [&] { return launch_shade(sc, w, depth, depth == 1 ? nullptr : w.queue[(depth - 1) & 1], prev + 0, n, w.queue[depth & 1], blk, cfg); });
         if (depth >= max_depth) break;
-        timed([&] { return launch_trace_shadow(sc, w, w.queue_s, blk + 1, blk + 3, cfg); });
-        timed([&] { return launch_trace_closest(sc, w, w.queue[depth & 1], blk + 0, 0, blk + 2, cfg); });
+        timed(BF_K_TRACE_SHADOW, [&] { return launch_trace_shadow(sc, w, w.queue_s, blk + 1, blk + 3, cfg); });
+        timed(BF_K_TRACE_CLOSEST, [&] { return launch_trace_closest(sc, w, w.queue[depth & 1], blk + 0, 0, blk + 2, cfg); });
         if (unbounded && depth >= 8) {
             BF_CUDA(cudaMemcpyAsync(s->h_counts, blk, 8, cudaMemcpyDeviceToHost, s->stream));
             BF_CUDA(cudaStreamSynchronize(s->stream));
             if (s->h_counts[0] == 0) break;
         }
     }
-    launches += launch_finalize(sc, w, n, profile, cfg);
+    timed(BF_K_FINALIZE, [&] { return launch_finalize(sc, w, n, profile, cfg); });
     s->stats.kernel_launches += launches;
     BF_CUDA(cudaGetLastError());
     return BF_OK;
@@ -794,9 +795,24 @@ int bf_last_receive_ms(bf_scene *s, float *total_ms, float *traverse_ms) {
         float acc = 0.f;
         for (size_t i = 0; i + 1 < s->ev_trace_used; i += 2) {
             float m = 0.f;
+            if (s->ev_kind[i] != BF_K_TRACE_CLOSEST && s->ev_kind[i] != BF_K_TRACE_SHADOW) continue;
             if (cudaEventElapsedTime(&m, s->ev_trace[i], s->ev_trace[i + 1]) == cudaSuccess) acc += m;
         }
         *traverse_ms = s->time_trace ? acc : -1.f;
+    }
+    return BF_OK;
+}
+
+int bf_last_kernel_ms(bf_scene *s, float *ms, uint32_t *launches) {
+    if (!s || !s->committed || !ms || !launches) return BF_ERR_STATE;
+    if (!s->time_trace) return fail(s, BF_ERR_STATE, "bf_last_kernel_ms: enable bf_set_trace_timing first");
+    BF_CUDA(cudaSetDevice(s->device));
+    BF_CUDA(cudaEventSynchronize(s->ev_end));
+    for (int k = 0; k < BF_K_COUNT; ++k) { ms[k] = 0.f; launches[k] = 0; }
+    for (size_t i = 0; i + 1 < s->ev_trace_used; i += 2) {
+        float m = 0.f;
+        BF_CUDA(cudaEventElapsedTime(&m, s->ev_trace[i], s->ev_trace[i + 1]));
+        ms[s->ev_kind[i]] += m; launches[s->ev_kind[i]]++;
     }
     return BF_OK;
 }

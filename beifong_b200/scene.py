@@ -243,6 +243,13 @@ class FlatScene:
     def set_trace_timing(self, enabled):
         self._ck(N.lib().bf_set_trace_timing(self._h, int(enabled)), "bf_set_trace_timing")
 
+    KERNELS = ("raygen", "trace_closest", "trace_shadow", "shade", "finalize")
+
+    def last_kernel_ms(self):
+        ms, n = (C.c_float * 5)(), (C.c_uint32 * 5)()
+        self._ck(N.lib().bf_last_kernel_ms(self._h, ms, n), "bf_last_kernel_ms")
+        return {k: (ms[i], n[i]) for i, k in enumerate(self.KERNELS)}
+
     def last_receive_ms(self):
         a, b = C.c_float(), C.c_float()
         self._ck(N.lib().bf_last_receive_ms(self._h, C.byref(a), C.byref(b)), "bf_last_receive_ms")

@@ -268,6 +268,10 @@ int bf_last_receive_ms(bf_scene *s, float *total_ms, float *traverse_ms);
 /* Record CUDA events around every traversal launch so that bf_last_receive_ms can report
  * traverse_ms (-1 when disabled, the default). */
 int bf_set_trace_timing(bf_scene *s, int enabled);
+/* Per-kernel device time (ms) and launch count of the most recent bf_receive, indexed by BF_K_*;
+ * needs bf_set_trace_timing(s, 1).  Used for the roofline of the dominant kernel. */
+enum { BF_K_RAYGEN = 0, BF_K_TRACE_CLOSEST = 1, BF_K_TRACE_SHADOW = 2, BF_K_SHADE = 3, BF_K_FINALIZE = 4, BF_K_COUNT = 5 };
+int bf_last_kernel_ms(bf_scene *s, float *ms, uint32_t *launches);
 
 /* Flat export of everything added so far (test infrastructure feeds it to the CPU oracle;
  * also a cheap checkpoint: profile + (seed, next index) + this blob is a resumable state). */
