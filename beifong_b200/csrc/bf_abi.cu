@@ -576,7 +576,7 @@ static int ensure_wave(bf_scene *s, uint32_t lanes, bool records) {
     int n_spec = s->C.spectrum_width == 1 ? 1 : 5;
     for (int k = 0; k < n_spec; ++k) BF_CUDA(A((void **) &w.spec[k], n * 16));
     BF_CUDA(A((void **) &w.flags, n * 4));
-    BF_CUDA(A((void **) &w.queue[0], n * 4)); BF_CUDA(A((void **) &w.queue[1], n * 4)); BF_CUDA(A((void **) &w.queue_s, n * 4));
+    BF_CUDA(A((void **) &w.queue[0], n * 4)); BF_CUDA(A((void **) &w.queue_h, n * 4)); BF_CUDA(A((void **) &w.queue_s, n * 4));
     if (records) BF_CUDA(A((void **) &w.records, n * sizeof(bf_sample_record)));
     w.capacity = lanes;
     w.counters = s->d_counters.p;
@@ -610,13 +610,13 @@ static int run_wave(bf_scene *s, uint64_t seed, uint64_t first, uint32_t n, floa
         if (s->time_trace) { cudaEventRecord(next_trace_event(s, kind), s->stream); }
     };
     timed(BF_K_RAYGEN, [&] { return launch_raygen(sc, w, seed, first, n, cfg); });
-    timed(BF_K_TRACE_CLOSEST, [&] { return launch_trace_closest(sc, w, nullptr, nullptr, n, ctr + 2, cfg); });
+    timed(BF_K_TRACE_CLOSEST, [&] { return launch_trace_closest(sc, w, nullptr, nullptr, n, 1, ctr + 4, ctr + 2, cfg); });
     for (uint32_t depth = 1; depth <= max_depth; ++depth) {
         uint32_t *blk = ctr + (size_t) BF_CTR_STRIDE * depth, *prev = ctr + (size_t) BF_CTR_STRIDE * (depth - 1);
-        timed(BF_K_SHADE, [&] { return launch_shade(sc, w, depth, depth == 1 ? nullptr : w.queue[(depth - 1) & 1], prev + 0, n, w.queue[depth & 1], blk, cfg); });
+        timed(BF_K_SHADE, [&] { return launch_shade(sc, w, depth, w.queue_h, prev + 4, n, w.queue[0], blk, cfg); });
         if (depth >= max_depth) break;
         timed(BF_K_TRACE_SHADOW, [&] { return launch_trace_shadow(sc, w, w.queue_s, blk + 1, blk + 3, cfg); });
-        timed(BF_K_TRACE_CLOSEST, [&] { return launch_trace_closest(sc, w, w.queue[depth & 1], blk + 0, 0, blk + 2, cfg); });
+        timed(BF_K_TRACE_CLOSEST, [&] { return launch_trace_closest(sc, w, w.queue[0], blk + 0, 0, depth + 1, blk + 4, blk + 2, cfg); });
         if (unbounded && depth >= 8) {
             BF_CUDA(cudaMemcpyAsync(s->h_counts, blk, 8, cudaMemcpyDeviceToHost, s->stream));
             BF_CUDA(cudaStreamSynchronize(s->stream));

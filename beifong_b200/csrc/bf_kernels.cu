@@ -12,6 +12,7 @@
 // Compiled with -fmad=false: see bf_math.h for the arithmetic contract.
 #include "bf_wave.h"
 #include "bf_device.cuh"
+#include "bf_trace.cuh"
 
 namespace bf {
 
@@ -105,205 +106,6 @@ __global__ void __launch_bounds__(256) k_raygen(const __grid_constant__ DevScene
         r.first_shape = BF_NONE; r.first_prim = BF_NONE; r.first_t = bf_inf(); r.valid = 0; r.tf_t = 0.f; r.tf_f = 0.f;
         r.value = 0.f; r.phase = 0.f; r.n_closest = 1; r.n_shadow = 0; r.wavelength0 = wl.v[0]; r.depth = 0;
         w.records[l] = r;
-    }
-}
-
-// =========================================================================================================
-// traversal
-// =========================================================================================================
-#define TRACE_THREADS 128
-#define TRACE_SM_STACK BF_TRACE_SM_STACK
-#define TRACE_LOCAL_STACK BF_TRACE_LOCAL_STACK
-
-__device__ __forceinline__ uint32_t sign_extend_s8x4(uint32_t x) {
-    uint32_t r;
-    asm("prmt.b32 %0, %1, 0x0, 0x0000BA98;" : "=r"(r) : "r"(x));
-    return r;
-}
-__device__ __forceinline__ uint32_t byte_of(uint32_t x, int i) { return (x >> (8 * i)) & 0xffu; }
-
-struct HitAcc {
-    float t; float u, v; uint32_t slot; uint32_t shape, prim;
-};
-
-// Möller-Trumbore exactly as Mesh::ray_intersect_triangle (mesh.h:194-226): no backface culling,
-// no determinant epsilon, u in [0,1], v >= 0, u+v <= 1, t in [mint, maxt].
-__device__ __forceinline__ bool tri_test(const float4 *__restrict__ tris, uint32_t slot, V3 o, V3 d, float mint, float maxt,
-                                         float &t_out, float &u_out, float &v_out, uint32_t &shape, uint32_t &prim) {
-    float4 a = __ldg(&tris[3 * (size_t) slot]), b = __ldg(&tris[3 * (size_t) slot + 1]), c = __ldg(&tris[3 * (size_t) slot + 2]);
-    V3 p0(a.x, a.y, a.z), p1(b.x, b.y, b.z), p2(c.x, c.y, c.z);
-    V3 e1 = p1 - p0, e2 = p2 - p0;
-    V3 pvec = cross(d, e2);
-    float inv_det = rcp(dot(e1, pvec));
-    V3 tvec = o - p0;
-    float u = dot(tvec, pvec) * inv_det;
-    bool active = u >= 0.f && u <= 1.f;
-    V3 qvec = cross(tvec, e1);
-    float v = dot(d, qvec) * inv_det;
-    active &= v >= 0.f && u + v <= 1.f;
-    float t = dot(e2, qvec) * inv_det;
-    active &= t >= mint && t <= maxt;
-    t_out = t; u_out = u; v_out = v;
-    shape = __float_as_uint(a.w); prim = __float_as_uint(b.w);
-    return active;
-}
-
-// Closest hit: lowest t, ties broken by the lowest (shape, prim) — the order a brute-force loop over
-// the scene's shapes visits them in (ray_intersect_naive, scene_native.inl:43-61).
-template <bool ANY_HIT>
-__device__ __forceinline__ void trace_one(const DevScene &sc, const float *s_rect, uint2 *s_stack, V3 o, V3 d, float mint, float maxt, HitAcc &best, bool &occluded) {
-    best.t = maxt; best.u = 0.f; best.v = 0.f; best.slot = BF_NONE; best.shape = BF_NONE; best.prim = BF_NONE;
-    occluded = false;
-
-    // analytic rectangles (rectangle.cpp:229-263)
-    for (uint32_t r = 0; r < sc.n_rects; ++r) {
-        const float *m = s_rect + 12 * r;
-        float ox = fmadd(m[2], o.z, fmadd(m[1], o.y, fmadd(m[0], o.x, m[3])));
-        float oy = fmadd(m[6], o.z, fmadd(m[5], o.y, fmadd(m[4], o.x, m[7])));
-        float oz = fmadd(m[10], o.z, fmadd(m[9], o.y, fmadd(m[8], o.x, m[11])));
-        float dx = fmadd(m[2], d.z, fmadd(m[1], d.y, m[0] * d.x));
-        float dy = fmadd(m[6], d.z, fmadd(m[5], d.y, m[4] * d.x));
-        float dz = fmadd(m[10], d.z, fmadd(m[9], d.y, m[8] * d.x));
-        float t = -oz * rcp(dz);
-        float lx = fmadd(dx, t, ox), ly = fmadd(dy, t, oy);
-        bool hit = t >= mint && t <= maxt && fabsf(lx) <= 1.f && fabsf(ly) <= 1.f;
-        if (!hit) continue;
-        if (ANY_HIT) { occluded = true; return; }
-        uint32_t shape = __float_as_uint(s_rect[12 * BF_MAX_RECTS + r]);
-        if (t < best.t || (t == best.t && shape < best.shape)) {
-            best.t = t; best.u = lx; best.v = ly; best.slot = 0x80000000u | r; best.shape = shape; best.prim = 0;
-        }
-    }
-    if (sc.n_nodes == 0) return;
-
-    // ---- 8-wide compressed BVH ---------------------------------------------------------------------------
-    const float tiny = 1e-30f;
-    float idx_ = __fdividef(1.f, fabsf(d.x) > tiny ? d.x : copysignf(tiny, d.x));
-    float idy_ = __fdividef(1.f, fabsf(d.y) > tiny ? d.y : copysignf(tiny, d.y));
-    float idz_ = __fdividef(1.f, fabsf(d.z) > tiny ? d.z : copysignf(tiny, d.z));
-    const uint32_t octinv = (d.x < 0.f ? 0u : 4u) | (d.y < 0.f ? 0u : 2u) | (d.z < 0.f ? 0u : 1u);
-    const uint32_t octinv4 = octinv * 0x01010101u;
-    // conservative ray interval for the slab tests
-    const float tmin_ray = mint * (1.f - 4e-7f);
-
-    uint2 l_stack[TRACE_LOCAL_STACK];
-    int sp = 0;
-    uint2 ngroup = make_uint2(0u, 0x80000000u);
-    const uint32_t tid = threadIdx.x;
-
-    while (true) {
-        uint2 tgroup = make_uint2(0u, 0u);
-        {
-            const uint32_t hits_imask = ngroup.y;
-            const uint32_t child_bit_index = 31u - __clz(hits_imask);
-            const uint32_t child_node_base = ngroup.x;
-            ngroup.y &= ~(1u << child_bit_index);
-            if (ngroup.y > 0x00ffffffu) {
-                if (sp < TRACE_SM_STACK) s_stack[sp * TRACE_THREADS + tid] = ngroup;
-                else l_stack[sp - TRACE_SM_STACK] = ngroup;
-                ++sp;
-            }
-            const uint32_t slot_index = (child_bit_index - 24u) ^ octinv;
-            const uint32_t relative_index = __popc(hits_imask & ~(0xffffffffu << slot_index));
-            const uint32_t node_index = child_node_base + relative_index;
-
-            const uint4 *np = sc.nodes + 5 * (size_t) node_index;
-            const uint4 n0 = __ldg(np), n1 = __ldg(np + 1), n2 = __ldg(np + 2), n3 = __ldg(np + 3), n4 = __ldg(np + 4);
-
-            const float px = __uint_as_float(n0.x), py = __uint_as_float(n0.y), pz = __uint_as_float(n0.z);
-            const uint32_t ex = n0.w & 0xffu, ey = (n0.w >> 8) & 0xffu, ez = (n0.w >> 16) & 0xffu, imask = n0.w >> 24;
-            ngroup.x = n1.x;
-            tgroup.x = n1.y;
-            uint32_t hitmask = 0;
-
-            const float ax = __uint_as_float(ex << 23) * idx_, ay = __uint_as_float(ey << 23) * idy_, az = __uint_as_float(ez << 23) * idz_;
-            const float bx = (px - o.x) * idx_, by = (py - o.y) * idy_, bz = (pz - o.z) * idz_;
-            const float tmax_ray = best.t * (1.f + 4e-7f);
-
-#pragma unroll
-            for (int half = 0; half < 2; ++half) {
-                const uint32_t meta4 = half ? n1.w : n1.z;
-                const uint32_t is_inner4 = (meta4 & (meta4 << 1)) & 0x10101010u;
-                const uint32_t inner_mask4 = sign_extend_s8x4(is_inner4 << 3);
-                const uint32_t bit_index4 = (meta4 ^ (octinv4 & inner_mask4)) & 0x1f1f1f1fu;
-                const uint32_t child_bits4 = (meta4 >> 5) & 0x07070707u;
-                const uint32_t qlx = half ? n2.y : n2.x, qly = half ? n2.w : n2.z, qlz = half ? n3.y : n3.x;
-                const uint32_t qhx = half ? n3.w : n3.z, qhy = half ? n4.y : n4.x, qhz = half ? n4.w : n4.z;
-                const uint32_t x_min = d.x < 0.f ? qhx : qlx, x_max = d.x < 0.f ? qlx : qhx;
-                const uint32_t y_min = d.y < 0.f ? qhy : qly, y_max = d.y < 0.f ? qly : qhy;
-                const uint32_t z_min = d.z < 0.f ? qhz : qlz, z_max = d.z < 0.f ? qlz : qhz;
-#pragma unroll
-                for (int j = 0; j < 4; ++j) {
-                    float tminx = fmaf((float) byte_of(x_min, j), ax, bx), tmaxx = fmaf((float) byte_of(x_max, j), ax, bx);
-                    float tminy = fmaf((float) byte_of(y_min, j), ay, by), tmaxy = fmaf((float) byte_of(y_max, j), ay, by);
-                    float tminz = fmaf((float) byte_of(z_min, j), az, bz), tmaxz = fmaf((float) byte_of(z_max, j), az, bz);
-                    float cmin = fmaxf(fmaxf(tminx, tminy), fmaxf(tminz, tmin_ray));
-                    float cmax = fminf(fminf(tmaxx, tmaxy), fminf(tmaxz, tmax_ray));
-                    if (cmin <= cmax * (1.f + 4e-7f))
-                        hitmask |= byte_of(child_bits4, j) << byte_of(bit_index4, j);
-                }
-            }
-            ngroup.y = (hitmask & 0xff000000u) | imask;
-            tgroup.y = hitmask & 0x00ffffffu;
-        }
-
-        while (tgroup.y != 0) {
-            const uint32_t i = 31u - __clz(tgroup.y);
-            tgroup.y &= ~(1u << i);
-            const uint32_t slot = tgroup.x + i;
-            float t, u, v; uint32_t shape, prim;
-            if (tri_test(sc.tris, slot, o, d, mint, maxt, t, u, v, shape, prim)) {
-                if (ANY_HIT) { occluded = true; return; }
-                if (t < best.t || (t == best.t && (shape < best.shape || (shape == best.shape && prim < best.prim)))) {
-                    best.t = t; best.u = u; best.v = v; best.slot = slot; best.shape = shape; best.prim = prim;
-                }
-            }
-        }
-
-        if (ngroup.y <= 0x00ffffffu) {
-            if (sp == 0) break;
-            --sp;
-            ngroup = sp < TRACE_SM_STACK ? s_stack[sp * TRACE_THREADS + tid] : l_stack[sp - TRACE_SM_STACK];
-        }
-    }
-}
-
-__device__ __forceinline__ void stage_rects(const DevScene &sc, float *s_rect) {
-    for (uint32_t i = threadIdx.x; i < sc.n_rects * 12u; i += blockDim.x) {
-        uint32_t r = i / 12u, k = i % 12u;
-        s_rect[i] = sc.rects[r].to_object.m[k / 4u][k % 4u];
-    }
-    for (uint32_t r = threadIdx.x; r < sc.n_rects; r += blockDim.x)
-        s_rect[12 * BF_MAX_RECTS + r] = __uint_as_float(sc.rects[r].shape);
-    __syncthreads();
-}
-
-// One persistent grid; each warp claims 32 rays at a time from a global cursor.
-template <bool ANY_HIT>
-__global__ void __launch_bounds__(TRACE_THREADS) k_trace(const __grid_constant__ DevScene sc, const float4 *__restrict__ ray_o,
-                                                         const float4 *__restrict__ ray_d, const uint32_t *__restrict__ queue,
-                                                         const uint32_t *__restrict__ count, uint32_t n_direct,
-                                                         float4 *__restrict__ hit_out, uint32_t *__restrict__ occl_out,
-                                                         uint32_t *work_cursor, unsigned long long *total) {
-    __shared__ float s_rect[13 * BF_MAX_RECTS];
-    __shared__ uint2 s_stack[TRACE_SM_STACK * TRACE_THREADS];
-    stage_rects(sc, s_rect);
-    const uint32_t n = queue ? *count : n_direct;
-    if (total && blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(total, (unsigned long long) n);
-    while (true) {
-        uint32_t base = 0;
-        if (lane_id() == 0) base = atomicAdd(work_cursor, 32u);
-        base = __shfl_sync(0xffffffffu, base, 0);
-        if (base >= n) break;
-        uint32_t i = base + lane_id();
-        if (i < n) {
-            uint32_t l = queue ? queue[i] : i;
-            float4 ro = ray_o[l], rd = ray_d[l];
-            HitAcc best; bool occluded;
-            trace_one<ANY_HIT>(sc, s_rect, s_stack, V3(ro.x, ro.y, ro.z), V3(rd.x, rd.y, rd.z), ro.w, rd.w, best, occluded);
-            if (ANY_HIT) occl_out[l] = occluded ? 1u : 0u;
-            else hit_out[l] = make_float4(best.slot == BF_NONE ? bf_inf() : best.t, best.u, best.v, __uint_as_float(best.slot));
-        }
     }
 }
 
@@ -653,20 +455,33 @@ int launch_raygen(const DevScene &sc, const Wave &w, uint64_t seed, uint64_t fir
     else k_raygen<4><<<grid, block, 0, cfg.stream>>>(sc, w, seed, first_sample, n);
     return 1;
 }
+static TraceIO trace_io(const Wave &w, const float4 *dirs, const uint32_t *queue, const uint32_t *count, uint32_t n_direct,
+                        uint32_t *work_cursor) {
+    TraceIO io;
+    memset(&io, 0, sizeof(io));
+    io.ray_o = w.ray_o; io.ray_d = dirs; io.queue = queue; io.count = count; io.n_direct = n_direct; io.work_cursor = work_cursor;
+    return io;
+}
 int launch_trace_closest(const DevScene &sc, const Wave &w, const uint32_t *queue, const uint32_t *count, uint32_t n_direct,
-                         uint32_t *work_cursor, const LaunchCfg &cfg) {
-    k_trace<false><<<trace_grid(cfg), TRACE_THREADS, 0, cfg.stream>>>(sc, w.ray_o, w.ray_d, queue, count, n_direct, w.hit, nullptr, work_cursor, w.totals + 0);
+                         uint32_t depth, uint32_t *hit_count, uint32_t *work_cursor, const LaunchCfg &cfg) {
+    TraceIO io = trace_io(w, w.ray_d, queue, count, n_direct, work_cursor);
+    io.hit = w.hit; io.hit_queue = w.queue_h; io.hit_count = hit_count; io.x1 = w.x1; io.records = w.records; io.depth = depth;
+    io.total = w.totals + 0;
+    k_trace<false><<<trace_grid(cfg), TRACE_THREADS, 0, cfg.stream>>>(sc, io);
     return 1;
 }
 int launch_trace_shadow(const DevScene &sc, const Wave &w, const uint32_t *queue, const uint32_t *count, uint32_t *work_cursor,
                         const LaunchCfg &cfg) {
-    k_trace<true><<<trace_grid(cfg), TRACE_THREADS, 0, cfg.stream>>>(sc, w.ray_o, w.sh_d, queue, count, 0, nullptr, w.occl, work_cursor, w.totals + 1);
+    TraceIO io = trace_io(w, w.sh_d, queue, count, 0, work_cursor);
+    io.occl = w.occl; io.total = w.totals + 1;
+    k_trace<true><<<trace_grid(cfg), TRACE_THREADS, 0, cfg.stream>>>(sc, io);
     return 1;
 }
 int launch_shade(const DevScene &sc, const Wave &w, uint32_t depth, const uint32_t *queue, const uint32_t *count, uint32_t n_direct,
                  uint32_t *next_queue, uint32_t *ctr_block, const LaunchCfg &cfg) {
     int grid = cfg.sm_count * 8;
     if (!queue) grid = (int) min((uint32_t) grid, (n_direct + 127u) / 128u);
+    else if (n_direct) grid = (int) min((uint32_t) grid, (n_direct + 127u) / 128u);   // n_direct = upper bound of *count
     if (grid < 1) grid = 1;
     if (sc.S == 1) k_shade<1><<<grid, 128, 0, cfg.stream>>>(sc, w, depth, queue, count, n_direct, next_queue, ctr_block);
     else k_shade<4><<<grid, 128, 0, cfg.stream>>>(sc, w, depth, queue, count, n_direct, next_queue, ctr_block);
@@ -682,8 +497,11 @@ int launch_finalize(const DevScene &sc, const Wave &w, uint32_t n, float *profil
 int launch_trace_rays(const DevScene &sc, const float4 *ray_o, const float4 *ray_d, uint32_t n, float4 *hit, uint32_t *occl,
                       uint32_t *work_cursor, const LaunchCfg &cfg) {
     if (n == 0) return 0;
-    if (hit) k_trace<false><<<trace_grid(cfg), TRACE_THREADS, 0, cfg.stream>>>(sc, ray_o, ray_d, nullptr, nullptr, n, hit, nullptr, work_cursor, nullptr);
-    else k_trace<true><<<trace_grid(cfg), TRACE_THREADS, 0, cfg.stream>>>(sc, ray_o, ray_d, nullptr, nullptr, n, nullptr, occl, work_cursor, nullptr);
+    TraceIO io;
+    memset(&io, 0, sizeof(io));
+    io.ray_o = ray_o; io.ray_d = ray_d; io.n_direct = n; io.work_cursor = work_cursor; io.hit = hit; io.occl = occl;
+    if (hit) k_trace<false><<<trace_grid(cfg), TRACE_THREADS, 0, cfg.stream>>>(sc, io);
+    else k_trace<true><<<trace_grid(cfg), TRACE_THREADS, 0, cfg.stream>>>(sc, io);
     return 1;
 }
 int launch_resolve_hits(const DevScene &sc, const float4 *hit, uint32_t n, uint32_t *shape, uint32_t *prim, const LaunchCfg &cfg) {

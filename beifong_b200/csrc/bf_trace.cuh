@@ -1,0 +1,302 @@
+// beifong_b200 — ray queries: 8-wide compressed-BVH traversal + Möller-Trumbore + analytic rectangles.
+// Replaces Scene::ray_intersect_preliminary / Scene::ray_test (src/librender/scene.cpp:129-178) and the
+// accelerators behind them (kdtree.h:2078-2171,2361-2390; scene_embree.inl:147-312; scene_optix.inl).
+//
+// Execution model: one persistent grid; every warp keeps its 32 lanes busy by claiming new rays from a
+// global cursor whenever fewer than TRACE_REFILL lanes are still traversing (lanes of a warp finish at
+// very different times: half of the receiver rays leave the scene after the root test).  A lane's
+// traversal state lives in registers, its stack in shared memory (first BF_TRACE_SM_STACK entries) and
+// local memory (the rest).  Results are committed at the refill points, where the warp is converged,
+// so queue pushes are one atomic per warp.
+#pragma once
+#include "bf_wave.h"
+#include "bf_device.cuh"
+
+namespace bf {
+
+#define TRACE_THREADS 128
+#define TRACE_SM_STACK BF_TRACE_SM_STACK
+#define TRACE_LOCAL_STACK BF_TRACE_LOCAL_STACK
+#define TRACE_REFILL 20
+
+__device__ __forceinline__ uint32_t sign_extend_s8x4(uint32_t x) {
+    uint32_t r;
+    asm("prmt.b32 %0, %1, 0x0, 0x0000BA98;" : "=r"(r) : "r"(x));
+    return r;
+}
+__device__ __forceinline__ uint32_t byte_of(uint32_t x, int i) { return (x >> (8 * i)) & 0xffu; }
+// byte j of x as the float 32768 + byte: the byte lands in mantissa bits 8..15 of 0x47000000 (one PRMT
+// instead of a quarter-rate I2F); the 32768 is folded into the additive term of the slab FMA.
+__device__ __forceinline__ float magic_byte(uint32_t x, int j) {
+    return __uint_as_float(__byte_perm(x, 0x47000000u, 0x7504u | ((uint32_t) j << 4)));
+}
+
+struct HitAcc {
+    float t; float u, v; uint32_t slot; uint32_t shape, prim;
+};
+
+// Möller-Trumbore exactly as Mesh::ray_intersect_triangle (mesh.h:194-226): no backface culling,
+// no determinant epsilon, u in [0,1], v >= 0, u+v <= 1, t in [mint, maxt].
+__device__ __forceinline__ bool tri_test(const float4 *__restrict__ tris, uint32_t slot, V3 o, V3 d, float mint, float maxt,
+                                         float &t_out, float &u_out, float &v_out, uint32_t &shape, uint32_t &prim) {
+    float4 a = __ldg(&tris[3 * (size_t) slot]), b = __ldg(&tris[3 * (size_t) slot + 1]), c = __ldg(&tris[3 * (size_t) slot + 2]);
+    V3 p0(a.x, a.y, a.z), p1(b.x, b.y, b.z), p2(c.x, c.y, c.z);
+    V3 e1 = p1 - p0, e2 = p2 - p0;
+    V3 pvec = cross(d, e2);
+    float inv_det = rcp(dot(e1, pvec));
+    V3 tvec = o - p0;
+    float u = dot(tvec, pvec) * inv_det;
+    bool active = u >= 0.f && u <= 1.f;
+    V3 qvec = cross(tvec, e1);
+    float v = dot(d, qvec) * inv_det;
+    active &= v >= 0.f && u + v <= 1.f;
+    float t = dot(e2, qvec) * inv_det;
+    active &= t >= mint && t <= maxt;
+    t_out = t; u_out = u; v_out = v;
+    shape = __float_as_uint(a.w); prim = __float_as_uint(b.w);
+    return active;
+}
+
+// Per-lane traversal state
+struct TraceLane {
+    V3 o, d;
+    float mint, maxt;
+    float idx, idy, idz;
+    uint32_t octinv;
+    HitAcc best;
+    uint2 ngroup;
+    int sp;
+    bool occluded;
+};
+
+// Ray setup + analytic rectangles (rectangle.cpp:229-263).  Returns false when the query is already
+// decided (any-hit occluded by a rectangle, or no BVH).
+template <bool ANY_HIT>
+__device__ __forceinline__ bool trace_begin(const DevScene &sc, const float *s_rect, TraceLane &L) {
+    L.best.t = L.maxt; L.best.u = 0.f; L.best.v = 0.f; L.best.slot = BF_NONE; L.best.shape = BF_NONE; L.best.prim = BF_NONE;
+    L.occluded = false;
+    const V3 o = L.o, d = L.d;
+    for (uint32_t r = 0; r < sc.n_rects; ++r) {
+        const float *m = s_rect + 12 * r;
+        float ox = fmadd(m[2], o.z, fmadd(m[1], o.y, fmadd(m[0], o.x, m[3])));
+        float oy = fmadd(m[6], o.z, fmadd(m[5], o.y, fmadd(m[4], o.x, m[7])));
+        float oz = fmadd(m[10], o.z, fmadd(m[9], o.y, fmadd(m[8], o.x, m[11])));
+        float dx = fmadd(m[2], d.z, fmadd(m[1], d.y, m[0] * d.x));
+        float dy = fmadd(m[6], d.z, fmadd(m[5], d.y, m[4] * d.x));
+        float dz = fmadd(m[10], d.z, fmadd(m[9], d.y, m[8] * d.x));
+        float t = -oz * rcp(dz);
+        float lx = fmadd(dx, t, ox), ly = fmadd(dy, t, oy);
+        bool hit = t >= L.mint && t <= L.maxt && fabsf(lx) <= 1.f && fabsf(ly) <= 1.f;
+        if (!hit) continue;
+        if (ANY_HIT) { L.occluded = true; return false; }
+        uint32_t shape = __float_as_uint(s_rect[12 * BF_MAX_RECTS + r]);
+        if (t < L.best.t || (t == L.best.t && shape < L.best.shape)) {
+            L.best.t = t; L.best.u = lx; L.best.v = ly; L.best.slot = 0x80000000u | r; L.best.shape = shape; L.best.prim = 0;
+        }
+    }
+    if (sc.n_nodes == 0) return false;
+    const float tiny = 1e-30f;
+    L.idx = __fdividef(1.f, fabsf(d.x) > tiny ? d.x : copysignf(tiny, d.x));
+    L.idy = __fdividef(1.f, fabsf(d.y) > tiny ? d.y : copysignf(tiny, d.y));
+    L.idz = __fdividef(1.f, fabsf(d.z) > tiny ? d.z : copysignf(tiny, d.z));
+    L.octinv = (d.x < 0.f ? 0u : 4u) | (d.y < 0.f ? 0u : 2u) | (d.z < 0.f ? 0u : 1u);
+    L.ngroup = make_uint2(0u, 0x80000000u);
+    L.sp = 0;
+    return true;
+}
+
+// One traversal step: pop one child of the current node group, test its 8 quantised child boxes, test
+// the triangles of the leaves hit.  Returns false when the traversal is finished.
+// Closest hit: lowest t, ties broken by the lowest (shape, prim) — the order a brute-force loop over the
+// scene's shapes visits them in (ray_intersect_naive, scene_native.inl:43-61).
+template <bool ANY_HIT>
+__device__ __forceinline__ bool trace_step(const DevScene &sc, uint2 *s_stack, uint2 *l_stack, TraceLane &L) {
+    const uint32_t tid = threadIdx.x;
+    uint2 tgroup = make_uint2(0u, 0u);
+    {
+        const uint32_t hits_imask = L.ngroup.y;
+        const uint32_t child_bit_index = 31u - __clz(hits_imask);
+        const uint32_t child_node_base = L.ngroup.x;
+        L.ngroup.y &= ~(1u << child_bit_index);
+        if (L.ngroup.y > 0x00ffffffu) {
+            if (L.sp < TRACE_SM_STACK) s_stack[L.sp * TRACE_THREADS + tid] = L.ngroup;
+            else l_stack[L.sp - TRACE_SM_STACK] = L.ngroup;
+            ++L.sp;
+        }
+        const uint32_t slot_index = (child_bit_index - 24u) ^ L.octinv;
+        const uint32_t relative_index = __popc(hits_imask & ~(0xffffffffu << slot_index));
+        const uint32_t node_index = child_node_base + relative_index;
+
+        const uint4 *np = sc.nodes + 5 * (size_t) node_index;
+        const uint4 n0 = __ldg(np), n1 = __ldg(np + 1), n2 = __ldg(np + 2), n3 = __ldg(np + 3), n4 = __ldg(np + 4);
+
+        const float px = __uint_as_float(n0.x), py = __uint_as_float(n0.y), pz = __uint_as_float(n0.z);
+        const uint32_t ex = n0.w & 0xffu, ey = (n0.w >> 8) & 0xffu, ez = (n0.w >> 16) & 0xffu, imask = n0.w >> 24;
+        L.ngroup.x = n1.x;
+        tgroup.x = n1.y;
+        uint32_t hitmask = 0;
+
+        // t = (32768 + q) * a + (b - 32768 a); the folded constant costs at most |a| / 512 of accuracy, the
+        // +-|a| / 128 slack below keeps the test conservative (a = one quantisation step in t)
+        const float ax = __uint_as_float(ex << 23) * L.idx, ay = __uint_as_float(ey << 23) * L.idy, az = __uint_as_float(ez << 23) * L.idz;
+        const float bx = fmaf(-32768.f, ax, (px - L.o.x) * L.idx), by = fmaf(-32768.f, ay, (py - L.o.y) * L.idy),
+                    bz = fmaf(-32768.f, az, (pz - L.o.z) * L.idz);
+        const float sx = fabsf(ax) * 0.0078125f, sy = fabsf(ay) * 0.0078125f, sz = fabsf(az) * 0.0078125f;
+        const float bxl = bx - sx, bxh = bx + sx, byl = by - sy, byh = by + sy, bzl = bz - sz, bzh = bz + sz;
+        const float tmin_ray = L.mint * (1.f - 4e-7f);
+        const float tmax_ray = L.best.t * (1.f + 4e-7f);
+        const uint32_t octinv4 = L.octinv * 0x01010101u;
+        const bool nx = L.d.x < 0.f, ny = L.d.y < 0.f, nz = L.d.z < 0.f;
+
+#pragma unroll
+        for (int half = 0; half < 2; ++half) {
+            const uint32_t meta4 = half ? n1.w : n1.z;
+            const uint32_t is_inner4 = (meta4 & (meta4 << 1)) & 0x10101010u;
+            const uint32_t inner_mask4 = sign_extend_s8x4(is_inner4 << 3);
+            const uint32_t bit_index4 = (meta4 ^ (octinv4 & inner_mask4)) & 0x1f1f1f1fu;
+            const uint32_t child_bits4 = (meta4 >> 5) & 0x07070707u;
+            const uint32_t qlx = half ? n2.y : n2.x, qly = half ? n2.w : n2.z, qlz = half ? n3.y : n3.x;
+            const uint32_t qhx = half ? n3.w : n3.z, qhy = half ? n4.y : n4.x, qhz = half ? n4.w : n4.z;
+            const uint32_t x_min = nx ? qhx : qlx, x_max = nx ? qlx : qhx;
+            const uint32_t y_min = ny ? qhy : qly, y_max = ny ? qly : qhy;
+            const uint32_t z_min = nz ? qhz : qlz, z_max = nz ? qlz : qhz;
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                float tminx = fmaf(magic_byte(x_min, j), ax, bxl), tmaxx = fmaf(magic_byte(x_max, j), ax, bxh);
+                float tminy = fmaf(magic_byte(y_min, j), ay, byl), tmaxy = fmaf(magic_byte(y_max, j), ay, byh);
+                float tminz = fmaf(magic_byte(z_min, j), az, bzl), tmaxz = fmaf(magic_byte(z_max, j), az, bzh);
+                float cmin = fmaxf(fmaxf(tminx, tminy), fmaxf(tminz, tmin_ray));
+                float cmax = fminf(fminf(tmaxx, tmaxy), fminf(tmaxz, tmax_ray));
+                if (cmin <= cmax)
+                    hitmask |= byte_of(child_bits4, j) << byte_of(bit_index4, j);
+            }
+        }
+        L.ngroup.y = (hitmask & 0xff000000u) | imask;
+        tgroup.y = hitmask & 0x00ffffffu;
+    }
+
+    while (tgroup.y != 0) {
+        const uint32_t i = 31u - __clz(tgroup.y);
+        tgroup.y &= ~(1u << i);
+        const uint32_t slot = tgroup.x + i;
+        float t, u, v; uint32_t shape, prim;
+        if (tri_test(sc.tris, slot, L.o, L.d, L.mint, L.maxt, t, u, v, shape, prim)) {
+            if (ANY_HIT) { L.occluded = true; return false; }
+            if (t < L.best.t || (t == L.best.t && (shape < L.best.shape || (shape == L.best.shape && prim < L.best.prim)))) {
+                L.best.t = t; L.best.u = u; L.best.v = v; L.best.slot = slot; L.best.shape = shape; L.best.prim = prim;
+            }
+        }
+    }
+
+    if (L.ngroup.y <= 0x00ffffffu) {
+        if (L.sp == 0) return false;
+        --L.sp;
+        L.ngroup = L.sp < TRACE_SM_STACK ? s_stack[L.sp * TRACE_THREADS + tid] : l_stack[L.sp - TRACE_SM_STACK];
+    }
+    return true;
+}
+
+__device__ __forceinline__ void stage_rects(const DevScene &sc, float *s_rect) {
+    for (uint32_t i = threadIdx.x; i < sc.n_rects * 12u; i += blockDim.x) {
+        uint32_t r = i / 12u, k = i % 12u;
+        s_rect[i] = sc.rects[r].to_object.m[k / 4u][k % 4u];
+    }
+    for (uint32_t r = threadIdx.x; r < sc.n_rects; r += blockDim.x)
+        s_rect[12 * BF_MAX_RECTS + r] = __uint_as_float(sc.rects[r].shape);
+    __syncthreads();
+}
+
+// What a trace launch reads and writes.
+struct TraceIO {
+    const float4 *ray_o, *ray_d;     // (o, mint), (d, maxt) indexed by lane id
+    const uint32_t *queue;           // lane ids, or null for lanes [0, n_direct)
+    const uint32_t *count;           // device-side queue length
+    uint32_t n_direct;
+    float4 *hit;                     // closest: (t, u, v, slot)
+    uint32_t *occl;                  // any-hit: 0 / 1
+    uint32_t *hit_queue, *hit_count; // closest: lanes whose ray hit something (the shade kernel's input), may be null
+    float4 *x1;                      // closest, gen 3, depth > 1: a missed continuation ray leaves time = phase = -inf
+    bf_sample_record *records;
+    uint32_t depth;                  // the shade iteration this trace feeds
+    uint32_t *work_cursor;
+    unsigned long long *total;
+};
+
+template <bool ANY_HIT>
+__global__ void __launch_bounds__(TRACE_THREADS) k_trace(const __grid_constant__ DevScene sc, const __grid_constant__ TraceIO io) {
+    __shared__ float s_rect[13 * BF_MAX_RECTS];
+    __shared__ uint2 s_stack[TRACE_SM_STACK * TRACE_THREADS];
+    uint2 l_stack[TRACE_LOCAL_STACK];
+    stage_rects(sc, s_rect);
+    const uint32_t n = io.queue ? *io.count : io.n_direct;
+    if (io.total && blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(io.total, (unsigned long long) n);
+    const uint32_t lane = threadIdx.x & 31u, lt_mask = (1u << lane) - 1u;
+
+    enum { EMPTY = 0, BUSY = 1, FINISHED = 2, EXHAUSTED = 3 };
+    int state = EMPTY;
+    uint32_t l = 0;
+    TraceLane L;
+    while (true) {
+        // ---- commit finished lanes (warp converged here) ----
+        bool push = false;
+        if (state == FINISHED) {
+            if (ANY_HIT) {
+                io.occl[l] = L.occluded ? 1u : 0u;
+            } else {
+                const bool hit = L.best.slot != BF_NONE;
+                io.hit[l] = make_float4(hit ? L.best.t : bf_inf(), L.best.u, L.best.v, __uint_as_float(L.best.slot));
+                push = hit && io.hit_queue;
+                if (!hit && io.hit_queue) {
+                    // the miss branch of the integrator loop (pathtimefrequency.cpp:368-371 with t = inf, then
+                    // `active &= si.is_valid()` ends the path): nothing else of the shade step is observable
+                    if (io.depth > 1 && sc.integ.gen == BF_GEN_PHASE) {
+                        float4 x = io.x1[l]; x.x = -bf_inf(); x.y = -bf_inf(); io.x1[l] = x;
+                    }
+                    if (io.records) io.records[l].depth = io.depth;
+                }
+            }
+            state = EMPTY;
+        }
+        if (!ANY_HIT && io.hit_queue) {
+            uint32_t m = __ballot_sync(0xffffffffu, push);
+            if (m) {
+                uint32_t leader = __ffs(m) - 1, base = 0;
+                if (lane == leader) base = atomicAdd(io.hit_count, (uint32_t) __popc(m));
+                base = __shfl_sync(0xffffffffu, base, leader);
+                if (push) io.hit_queue[base + __popc(m & lt_mask)] = l;
+            }
+        }
+        // ---- refill empty lanes ----
+        uint32_t want = __ballot_sync(0xffffffffu, state == EMPTY);
+        if (want) {
+            uint32_t leader = __ffs(want) - 1, base = 0;
+            if (lane == leader) base = atomicAdd(io.work_cursor, (uint32_t) __popc(want));
+            base = __shfl_sync(0xffffffffu, base, leader);
+            if (state == EMPTY) {
+                uint32_t i = base + __popc(want & lt_mask);
+                if (i < n) {
+                    l = io.queue ? io.queue[i] : i;
+                    float4 ro = io.ray_o[l], rd = io.ray_d[l];
+                    L.o = V3(ro.x, ro.y, ro.z); L.d = V3(rd.x, rd.y, rd.z); L.mint = ro.w; L.maxt = rd.w;
+                    state = trace_begin<ANY_HIT>(sc, s_rect, L) ? BUSY : FINISHED;
+                } else {
+                    state = EXHAUSTED;
+                }
+            }
+        }
+        uint32_t busy = __ballot_sync(0xffffffffu, state == BUSY);
+        uint32_t fin = __ballot_sync(0xffffffffu, state == FINISHED);
+        if (busy == 0 && fin == 0) break;
+        if (busy == 0) continue;
+        const bool drained = __any_sync(0xffffffffu, state == EXHAUSTED);
+        const int min_busy = drained ? 1 : TRACE_REFILL;
+        // ---- traverse until too few lanes are left ----
+        do {
+            if (state == BUSY) {
+                if (!trace_step<ANY_HIT>(sc, s_stack, l_stack, L)) state = FINISHED;
+            }
+        } while (__popc(__ballot_sync(0xffffffffu, state == BUSY)) >= min_busy);
+    }
+}
+
+}  // namespace bf

@@ -18,7 +18,7 @@ enum : uint32_t { LANE_ACTIVE = 1u, LANE_VALID = 2u, LANE_BS_DELTA = 4u, LANE_PE
 #define BF_TRACE_LOCAL_STACK 56    // deeper entries spill to local memory
 #define BF_TRACE_STACK_DEPTH (BF_TRACE_SM_STACK + BF_TRACE_LOCAL_STACK)
 #define BF_CTR_STRIDE 8u     // per-depth counter block: [0] next-closest count, [1] shadow count,
-                             // [2] closest work cursor, [3] shadow work cursor, [4] shade cursor
+                             // [2] closest work cursor, [3] shadow work cursor, [4] hit count of that closest trace
 
 struct Wave {
     uint32_t capacity;
@@ -34,7 +34,8 @@ struct Wave {
     float4 *spec[5];     // S = 1: [0] = (throughput, result, pending, wavelength)
                          // S = 4: throughput, result, pending, wavelengths, ray weight
     uint32_t *flags;
-    uint32_t *queue[2];  // ping-pong lane-id queues for continuation rays
+    uint32_t *queue[2];  // [0] lane-id queue of continuation rays (shade -> trace), [1] unused
+    uint32_t *queue_h;   // lane-id queue of lanes whose continuation ray hit something (trace -> shade)
     uint32_t *queue_s;   // lane-id queue for shadow rays
     uint32_t *counters;  // BF_CTR_STRIDE * (BF_MAX_BOUNCES + 2)
     unsigned long long *totals;  // [0] closest queries traced, [1] shadow queries traced
@@ -49,8 +50,9 @@ struct LaunchCfg {
 // Kernel launchers (bf_kernels.cu).  Return the number of kernels launched.
 int launch_raygen(const DevScene &sc, const Wave &w, uint64_t seed, uint64_t first_sample, uint32_t n, const LaunchCfg &cfg);
 // queue == nullptr: lanes [0, n_direct); else lane ids from queue[0 .. *count)
+// depth = the shade iteration this trace feeds; lanes that hit are appended to w.queue_h / *hit_count
 int launch_trace_closest(const DevScene &sc, const Wave &w, const uint32_t *queue, const uint32_t *count, uint32_t n_direct,
-                         uint32_t *work_cursor, const LaunchCfg &cfg);
+                         uint32_t depth, uint32_t *hit_count, uint32_t *work_cursor, const LaunchCfg &cfg);
 int launch_trace_shadow(const DevScene &sc, const Wave &w, const uint32_t *queue, const uint32_t *count, uint32_t *work_cursor,
                         const LaunchCfg &cfg);
 int launch_shade(const DevScene &sc, const Wave &w, uint32_t depth, const uint32_t *queue, const uint32_t *count, uint32_t n_direct,
