@@ -104,11 +104,13 @@ PROTOTYPES = {
     "bf_synchronize": (C.c_int, [vp]),
     "bf_trace_first_hits": (C.c_int, [vp, P(f32), P(f32), P(f32), P(f32), u64, P(u32), P(u32), P(f32), P(f32), P(f32)]),
     "bf_trace_occluded": (C.c_int, [vp, P(f32), P(f32), P(f32), P(f32), u64, P(C.c_uint8)]),
+    "bf_debug_trace_steps": (C.c_int, [vp, P(f32), P(f32), P(f32), P(f32), u64, P(u32), P(f32)]),
     "bf_debug_sample_records": (C.c_int, [vp, u64, u64, u64, P(bf_sample_record)]),
     "bf_get_stats": (C.c_int, [vp, P(bf_stats)]),
     "bf_last_receive_ms": (C.c_int, [vp, P(f32), P(f32)]),
     "bf_set_trace_timing": (C.c_int, [vp, C.c_int]),
     "bf_last_kernel_ms": (C.c_int, [vp, P(f32), P(u32)]),
+    "bf_last_launch_list": (C.c_int, [vp, P(f32), P(u32), u32, P(u32)]),
     "bf_scene_export": (C.c_int, [vp, vp, C.c_size_t, P(C.c_size_t)]),
 }
 

@@ -78,6 +78,12 @@ template <typename T> struct DevBuf {
     void release() { if (p) cudaFree(p); p = nullptr; n = 0; }
 };
 
+struct WaveSlot {
+    Wave wave; uint32_t capacity = 0; std::vector<void *> allocs;
+    cudaStream_t stream = nullptr; bool own_stream = false; cudaEvent_t done = nullptr;
+    uint32_t *h_counts = nullptr;     // pinned read-back of queue counts
+};
+
 struct bf_scene {
     bf_constants C;
     std::vector<HostSpectrum> spectra;
@@ -104,9 +110,9 @@ struct bf_scene {
     // image of the geometry tables in pinned host memory (re-upload without a rebuild)
     void *h_geom = nullptr; size_t h_geom_bytes = 0, h_nodes_bytes = 0, h_tris_bytes = 0, h_nrm_bytes = 0;
     // wave
-    Wave wave; uint32_t wave_capacity = 0; std::vector<void *> wave_allocs;
-    DevBuf<uint32_t> d_counters; DevBuf<unsigned long long> d_totals;
-    uint32_t *h_counts = nullptr;     // pinned read-back of queue counts
+    std::vector<WaveSlot> slots;      // slot 0 runs on `stream`
+    DevBuf<unsigned long long> d_totals;
+    cudaEvent_t ev_fork = nullptr;
     // stats / timing
     bf_stats stats;
     cudaEvent_t ev_begin = nullptr, ev_end = nullptr;
@@ -187,17 +193,12 @@ int bf_scene_create(const bf_constants *consts, bf_scene **out) {
     bf_scene *s = new bf_scene();
     s->C = *consts;
     memset(&s->rx, 0, sizeof(s->rx)); memset(&s->adc, 0, sizeof(s->adc)); memset(&s->integ, 0, sizeof(s->integ));
-    memset(&s->stats, 0, sizeof(s->stats)); memset(&s->wave, 0, sizeof(s->wave)); memset(&s->dev, 0, sizeof(s->dev));
+    memset(&s->stats, 0, sizeof(s->stats)); memset(&s->dev, 0, sizeof(s->dev));
     *out = s;
     return BF_OK;
 }
 
-static void free_wave(bf_scene *s) {
-    for (void *p : s->wave_allocs) cudaFree(p);
-    s->wave_allocs.clear();
-    memset(&s->wave, 0, sizeof(s->wave));
-    s->wave_capacity = 0;
-}
+static void free_wave(bf_scene *s);
 
 void bf_scene_destroy(bf_scene *s) {
     if (!s) return;
@@ -207,9 +208,9 @@ void bf_scene_destroy(bf_scene *s) {
         free_wave(s);
         s->d_nodes.release(); s->d_tris.release(); s->d_tri_nrm.release(); s->d_rects.release(); s->d_shapes.release();
         s->d_bsdfs.release(); s->d_spectra.release(); s->d_spec_pool.release(); s->d_txs.release(); s->d_rx.release();
-        s->d_profile.release(); s->d_counters.release(); s->d_totals.release();
+        s->d_profile.release(); s->d_totals.release();
         if (s->h_geom) cudaFreeHost(s->h_geom);
-        if (s->h_counts) cudaFreeHost(s->h_counts);
+        if (s->ev_fork) cudaEventDestroy(s->ev_fork);
         if (s->ev_begin) cudaEventDestroy(s->ev_begin);
         if (s->ev_end) cudaEventDestroy(s->ev_end);
         for (cudaEvent_t e : s->ev_trace) cudaEventDestroy(e);
@@ -520,10 +521,9 @@ int bf_scene_commit(bf_scene *s, int device) {
     s->profile_floats = (size_t) s->dev.film_w * s->dev.film_h * s->dev.channels;
     BF_CUDA(s->d_profile.alloc(s->profile_floats));
     BF_CUDA(cudaMemsetAsync(s->d_profile.p, 0, s->profile_floats * 4, s->stream));
-    BF_CUDA(s->d_counters.alloc(BF_CTR_STRIDE * (BF_MAX_BOUNCES + 2)));
     BF_CUDA(s->d_totals.alloc(2));
     BF_CUDA(cudaMemsetAsync(s->d_totals.p, 0, 16, s->stream));
-    BF_CUDA(cudaMallocHost((void **) &s->h_counts, 64));
+    BF_CUDA(cudaEventCreateWithFlags(&s->ev_fork, cudaEventDisableTiming));
     BF_CUDA(cudaStreamSynchronize(s->stream));
     s->stats.upload_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t1).count();
     s->committed = true;
@@ -552,23 +552,59 @@ int bf_scene_update_rect(bf_scene *s, uint32_t shape_id, const float to_world[16
     return BF_OK;
 }
 
-// ---- wave allocation ------------------------------------------------------------------------------------
-static uint32_t wave_lanes_default() {
-    const char *e = getenv("BF_WAVE_LANES");
-    if (e) { long v = atol(e); if (v >= 1024) return (uint32_t) v; }
-    return 1u << 21;
+// ---- wave slots --------------------------------------------------------------------------------------------
+// A call to bf_receive is cut into waves of BF_WAVE_LANES lanes; BF_WAVE_STREAMS waves are in flight at a
+// time, each on its own stream with its own state buffers.  Every traversal launch ends with a latency-bound
+// tail (a handful of rays with ~100 sequential node visits); with several waves in flight the tail of one
+// wave's launch overlaps the bulk of another's.
+static uint32_t env_u32(const char *name, uint32_t dflt, uint32_t lo, uint32_t hi) {
+    const char *e = getenv(name);
+    if (!e) return dflt;
+    long v = atol(e);
+    if (v < (long) lo) v = lo;
+    if (v > (long) hi) v = hi;
+    return (uint32_t) v;
+}
+static uint32_t wave_lanes_default() { return env_u32("BF_WAVE_LANES", 1u << 20, 1024, 1u << 24); }
+static uint32_t wave_streams_default() { return env_u32("BF_WAVE_STREAMS", 8, 1, 16); }
+
+static void free_slot(WaveSlot &sl, bool keep_stream) {
+    for (void *p : sl.allocs) cudaFree(p);
+    sl.allocs.clear();
+    memset(&sl.wave, 0, sizeof(sl.wave));
+    sl.capacity = 0;
+    if (!keep_stream) {
+        if (sl.stream && sl.own_stream) cudaStreamDestroy(sl.stream);
+        if (sl.done) cudaEventDestroy(sl.done);
+        if (sl.h_counts) cudaFreeHost(sl.h_counts);
+        sl.stream = nullptr; sl.done = nullptr; sl.h_counts = nullptr;
+    }
+}
+static void free_wave(bf_scene *s) {
+    for (WaveSlot &sl : s->slots) free_slot(sl, false);
+    s->slots.clear();
 }
 
-static int ensure_wave(bf_scene *s, uint32_t lanes, bool records) {
-    if (s->wave_capacity >= lanes && (!records || s->wave.records)) return BF_OK;
-    BF_CUDA(cudaStreamSynchronize(s->stream));
-    free_wave(s);
+static int ensure_slot(bf_scene *s, size_t index, uint32_t lanes, bool records) {
+    while (s->slots.size() <= index) {
+        WaveSlot sl;
+        memset(&sl.wave, 0, sizeof(sl.wave));
+        if (s->slots.empty()) { sl.stream = s->stream; sl.own_stream = false; }
+        else { BF_CUDA(cudaStreamCreateWithFlags(&sl.stream, cudaStreamNonBlocking)); sl.own_stream = true; }
+        BF_CUDA(cudaEventCreateWithFlags(&sl.done, cudaEventDisableTiming));
+        BF_CUDA(cudaMallocHost((void **) &sl.h_counts, 64));
+        s->slots.push_back(sl);
+    }
+    WaveSlot &sl = s->slots[index];
+    if (sl.capacity >= lanes && (!records || sl.wave.records)) return BF_OK;
+    BF_CUDA(cudaStreamSynchronize(sl.stream));
+    free_slot(sl, true);
     auto A = [&](void **p, size_t bytes) -> cudaError_t {
         cudaError_t e = cudaMalloc(p, bytes);
-        if (e == cudaSuccess) s->wave_allocs.push_back(*p);
+        if (e == cudaSuccess) sl.allocs.push_back(*p);
         return e;
     };
-    Wave &w = s->wave;
+    Wave &w = sl.wave;
     size_t n = lanes;
     BF_CUDA(A((void **) &w.ray_o, n * 16)); BF_CUDA(A((void **) &w.ray_d, n * 16)); BF_CUDA(A((void **) &w.sh_d, n * 16));
     BF_CUDA(A((void **) &w.hit, n * 16)); BF_CUDA(A((void **) &w.occl, n * 4)); BF_CUDA(A((void **) &w.rng, n * 16));
@@ -577,11 +613,11 @@ static int ensure_wave(bf_scene *s, uint32_t lanes, bool records) {
     for (int k = 0; k < n_spec; ++k) BF_CUDA(A((void **) &w.spec[k], n * 16));
     BF_CUDA(A((void **) &w.flags, n * 4));
     BF_CUDA(A((void **) &w.queue[0], n * 4)); BF_CUDA(A((void **) &w.queue_h, n * 4)); BF_CUDA(A((void **) &w.queue_s, n * 4));
+    BF_CUDA(A((void **) &w.counters, (size_t) BF_CTR_STRIDE * (BF_MAX_BOUNCES + 2) * 4));
     if (records) BF_CUDA(A((void **) &w.records, n * sizeof(bf_sample_record)));
     w.capacity = lanes;
-    w.counters = s->d_counters.p;
     w.totals = s->d_totals.p;
-    s->wave_capacity = lanes;
+    sl.capacity = lanes;
     return BF_OK;
 }
 
@@ -593,21 +629,23 @@ static cudaEvent_t next_trace_event(bf_scene *s, int kind) {
     return s->ev_trace[s->ev_trace_used++];
 }
 
-// One wave: lanes [0, n) <-> sample indices [first, first + n)
-static int run_wave(bf_scene *s, uint64_t seed, uint64_t first, uint32_t n, float *profile) {
+// One wave on one slot: lanes [0, n) <-> sample indices [first, first + n)
+static int run_wave(bf_scene *s, WaveSlot &sl, uint64_t seed, uint64_t first, uint32_t n, float *profile, bool with_records) {
     const DevScene &sc = s->dev;
-    const Wave &w = s->wave;
-    LaunchCfg cfg; cfg.stream = s->stream; cfg.sm_count = s->sm_count;
-    uint32_t *ctr = s->d_counters.p;
+    Wave w = sl.wave;
+    if (!with_records) w.records = nullptr;
+    LaunchCfg cfg; cfg.stream = sl.stream; cfg.sm_count = s->sm_count;
+    uint32_t *ctr = w.counters;
     const bool unbounded = sc.integ.max_depth < 0 || sc.integ.max_depth > 64;
     const uint32_t max_depth = sc.integ.max_depth < 0 ? BF_MAX_BOUNCES : std::min<uint32_t>((uint32_t) sc.integ.max_depth, BF_MAX_BOUNCES);
     const uint32_t ctr_blocks = unbounded ? BF_MAX_BOUNCES + 2 : max_depth + 2;
-    BF_CUDA(cudaMemsetAsync(ctr, 0, (size_t) BF_CTR_STRIDE * ctr_blocks * 4, s->stream));
+    BF_CUDA(cudaMemsetAsync(ctr, 0, (size_t) BF_CTR_STRIDE * ctr_blocks * 4, sl.stream));
     uint64_t launches = 0;
+    const bool timing = s->time_trace;
     auto timed = [&](int kind, auto &&fn) {
-        if (s->time_trace) { cudaEventRecord(next_trace_event(s, kind), s->stream); }
+        if (timing) { cudaEventRecord(next_trace_event(s, kind), sl.stream); }
         launches += fn();
-        if (s->time_trace) { cudaEventRecord(next_trace_event(s, kind), s->stream); }
+        if (timing) { cudaEventRecord(next_trace_event(s, kind), sl.stream); }
     };
     timed(BF_K_RAYGEN, [&] { return launch_raygen(sc, w, seed, first, n, cfg); });
     timed(BF_K_TRACE_CLOSEST, [&] { return launch_trace_closest(sc, w, nullptr, nullptr, n, 1, ctr + 4, ctr + 2, cfg); });
@@ -618,9 +656,9 @@ static int run_wave(bf_scene *s, uint64_t seed, uint64_t first, uint32_t n, floa
         timed(BF_K_TRACE_SHADOW, [&] { return launch_trace_shadow(sc, w, w.queue_s, blk + 1, blk + 3, cfg); });
         timed(BF_K_TRACE_CLOSEST, [&] { return launch_trace_closest(sc, w, w.queue[0], blk + 0, 0, depth + 1, blk + 4, blk + 2, cfg); });
         if (unbounded && depth >= 8) {
-            BF_CUDA(cudaMemcpyAsync(s->h_counts, blk, 8, cudaMemcpyDeviceToHost, s->stream));
-            BF_CUDA(cudaStreamSynchronize(s->stream));
-            if (s->h_counts[0] == 0) break;
+            BF_CUDA(cudaMemcpyAsync(sl.h_counts, blk, 8, cudaMemcpyDeviceToHost, sl.stream));
+            BF_CUDA(cudaStreamSynchronize(sl.stream));
+            if (sl.h_counts[0] == 0) break;
         }
     }
     timed(BF_K_FINALIZE, [&] { return launch_finalize(sc, w, n, profile, cfg); });
@@ -634,21 +672,28 @@ int bf_receive(bf_scene *s, uint64_t seed, uint64_t first_sample, uint64_t n_sam
     if (!s->committed) return fail(s, BF_ERR_STATE, "bf_receive: scene not committed");
     BF_CUDA(cudaSetDevice(s->device));
     if (s->tables_dirty) { int rc = upload_tables(s); if (rc) return rc; }
-    uint32_t chunk = (uint32_t) std::min<uint64_t>(std::max<uint64_t>(n_samples, 1024), wave_lanes_default());
-    int rc = ensure_wave(s, chunk, false);
-    if (rc) return rc;
-    // resolve the previous call's trace timings before the events are re-used
+    const uint32_t lanes = (uint32_t) std::min<uint64_t>(std::max<uint64_t>(n_samples, 1024), wave_lanes_default());
+    const uint64_t n_waves = (n_samples + lanes - 1) / lanes;
+    // per-kernel timing needs the launches serialised on one stream
+    const size_t n_slots = s->time_trace ? 1 : (size_t) std::min<uint64_t>(wave_streams_default(), std::max<uint64_t>(n_waves, 1));
+    for (size_t k = 0; k < n_slots; ++k) { int rc = ensure_slot(s, k, lanes, false); if (rc) return rc; }
     s->ev_trace_used = 0;
     BF_CUDA(cudaEventRecord(s->ev_begin, s->stream));
     if (!accumulate) BF_CUDA(cudaMemsetAsync(s->d_profile.p, 0, s->profile_floats * 4, s->stream));
-    bf_sample_record *saved = s->wave.records;
-    s->wave.records = nullptr;
-    for (uint64_t done = 0; done < n_samples; done += s->wave_capacity) {
-        uint32_t n = (uint32_t) std::min<uint64_t>(s->wave_capacity, n_samples - done);
-        rc = run_wave(s, seed, first_sample + done, n, s->d_profile.p);
-        if (rc) { s->wave.records = saved; return rc; }
+    if (n_slots > 1) {
+        BF_CUDA(cudaEventRecord(s->ev_fork, s->stream));
+        for (size_t k = 1; k < n_slots; ++k) BF_CUDA(cudaStreamWaitEvent(s->slots[k].stream, s->ev_fork, 0));
     }
-    s->wave.records = saved;
+    uint64_t wave_index = 0;
+    for (uint64_t done = 0; done < n_samples; done += lanes, ++wave_index) {
+        uint32_t n = (uint32_t) std::min<uint64_t>(lanes, n_samples - done);
+        int rc = run_wave(s, s->slots[wave_index % n_slots], seed, first_sample + done, n, s->d_profile.p, false);
+        if (rc) return rc;
+    }
+    for (size_t k = 1; k < n_slots; ++k) {
+        BF_CUDA(cudaEventRecord(s->slots[k].done, s->slots[k].stream));
+        BF_CUDA(cudaStreamWaitEvent(s->stream, s->slots[k].done, 0));
+    }
     BF_CUDA(cudaEventRecord(s->ev_end, s->stream));
     s->stats.samples += n_samples;
     return BF_OK;
@@ -680,7 +725,7 @@ int bf_profile_device_ptr(bf_scene *s, void **dptr, size_t *n_floats, void **cud
 }
 
 static int trace_rays_common(bf_scene *s, const float *origins, const float *directions, const float *mint, const float *maxt,
-                             uint64_t n_rays, uint32_t *shape, uint32_t *prim, float *t, float *u, float *v, uint8_t *occl) {
+                             uint64_t n_rays, uint32_t *shape, uint32_t *prim, float *t, float *u, float *v, uint8_t *occl, uint32_t *steps = nullptr) {
     if (!s || !origins || !directions) return BF_ERR_INVALID;
     if (!s->committed) return fail(s, BF_ERR_STATE, "trace: scene not committed");
     if (n_rays == 0) return BF_OK;
@@ -705,7 +750,8 @@ static int trace_rays_common(bf_scene *s, const float *origins, const float *dir
     cudaMemcpyAsync(d_d.p, hd.data(), n * 16, cudaMemcpyHostToDevice, s->stream);
     cudaMemsetAsync(d_cursor.p, 0, 4, s->stream);
     if (!occl) {
-        s->stats.kernel_launches += launch_trace_rays(s->dev, d_o.p, d_d.p, (uint32_t) n, d_hit.p, nullptr, d_cursor.p, cfg);
+        s->stats.kernel_launches += launch_trace_rays(s->dev, d_o.p, d_d.p, (uint32_t) n, d_hit.p, steps ? d_b.p : nullptr, d_cursor.p, cfg);
+        if (steps) cudaMemcpyAsync(steps, d_b.p, n * 4, cudaMemcpyDeviceToHost, s->stream);
         s->stats.kernel_launches += launch_resolve_hits(s->dev, d_hit.p, (uint32_t) n, d_a.p, d_b.p, cfg);
         std::vector<float4> hh(n);
         cudaMemcpyAsync(hh.data(), d_hit.p, n * 16, cudaMemcpyDeviceToHost, s->stream);
@@ -734,6 +780,11 @@ int bf_trace_first_hits(bf_scene *s, const float *origins, const float *directio
                         uint64_t n_rays, uint32_t *shape, uint32_t *prim, float *t, float *u, float *v) {
     return trace_rays_common(s, origins, directions, mint, maxt, n_rays, shape, prim, t, u, v, nullptr);
 }
+int bf_debug_trace_steps(bf_scene *s, const float *origins, const float *directions, const float *mint, const float *maxt,
+                         uint64_t n_rays, uint32_t *steps, float *t) {
+    if (!steps) return BF_ERR_INVALID;
+    return trace_rays_common(s, origins, directions, mint, maxt, n_rays, nullptr, nullptr, t, nullptr, nullptr, nullptr, steps);
+}
 int bf_trace_occluded(bf_scene *s, const float *origins, const float *directions, const float *mint, const float *maxt,
                       uint64_t n_rays, uint8_t *hit) {
     if (!hit) return BF_ERR_INVALID;
@@ -747,15 +798,15 @@ int bf_debug_sample_records(bf_scene *s, uint64_t seed, uint64_t first_sample, u
     if (n_samples > (1u << 24)) return fail(s, BF_ERR_INVALID, "bf_debug_sample_records: at most 2^24 samples per call");
     BF_CUDA(cudaSetDevice(s->device));
     if (s->tables_dirty) { int rc = upload_tables(s); if (rc) return rc; }
-    int rc = ensure_wave(s, (uint32_t) std::max<uint64_t>(n_samples, 1024), true);
+    int rc = ensure_slot(s, 0, (uint32_t) std::max<uint64_t>(n_samples, 1024), true);
     if (rc) return rc;
     DevBuf<float> scratch;
     BF_CUDA(scratch.alloc(s->profile_floats));
     BF_CUDA(cudaMemsetAsync(scratch.p, 0, s->profile_floats * 4, s->stream));
     s->ev_trace_used = 0;
-    rc = run_wave(s, seed, first_sample, (uint32_t) n_samples, scratch.p);
+    rc = run_wave(s, s->slots[0], seed, first_sample, (uint32_t) n_samples, scratch.p, true);
     if (rc == BF_OK) {
-        cudaError_t e = cudaMemcpyAsync(records, s->wave.records, n_samples * sizeof(bf_sample_record), cudaMemcpyDeviceToHost, s->stream);
+        cudaError_t e = cudaMemcpyAsync(records, s->slots[0].wave.records, n_samples * sizeof(bf_sample_record), cudaMemcpyDeviceToHost, s->stream);
         if (e == cudaSuccess) e = cudaStreamSynchronize(s->stream);
         if (e != cudaSuccess) rc = fail(s, BF_ERR_CUDA, cudaGetErrorString(e));
     }
@@ -800,6 +851,20 @@ int bf_last_receive_ms(bf_scene *s, float *total_ms, float *traverse_ms) {
         }
         *traverse_ms = s->time_trace ? acc : -1.f;
     }
+    return BF_OK;
+}
+
+int bf_last_launch_list(bf_scene *s, float *ms, uint32_t *kind, uint32_t capacity, uint32_t *n_out) {
+    if (!s || !s->committed || !ms || !kind || !n_out) return BF_ERR_STATE;
+    if (!s->time_trace) return fail(s, BF_ERR_STATE, "bf_last_launch_list: enable bf_set_trace_timing first");
+    BF_CUDA(cudaSetDevice(s->device));
+    BF_CUDA(cudaEventSynchronize(s->ev_end));
+    uint32_t n = 0;
+    for (size_t i = 0; i + 1 < s->ev_trace_used && n < capacity; i += 2, ++n) {
+        BF_CUDA(cudaEventElapsedTime(&ms[n], s->ev_trace[i], s->ev_trace[i + 1]));
+        kind[n] = s->ev_kind[i];
+    }
+    *n_out = n;
     return BF_OK;
 }
 

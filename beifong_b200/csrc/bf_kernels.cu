@@ -499,7 +499,8 @@ int launch_trace_rays(const DevScene &sc, const float4 *ray_o, const float4 *ray
     if (n == 0) return 0;
     TraceIO io;
     memset(&io, 0, sizeof(io));
-    io.ray_o = ray_o; io.ray_d = ray_d; io.n_direct = n; io.work_cursor = work_cursor; io.hit = hit; io.occl = occl;
+    io.ray_o = ray_o; io.ray_d = ray_d; io.n_direct = n; io.work_cursor = work_cursor; io.hit = hit; io.occl = hit ? nullptr : occl;
+    io.steps = hit ? occl : nullptr;   // closest queries: `occl`, when given, receives the per-ray step count
     if (hit) k_trace<false><<<trace_grid(cfg), TRACE_THREADS, 0, cfg.stream>>>(sc, io);
     else k_trace<true><<<trace_grid(cfg), TRACE_THREADS, 0, cfg.stream>>>(sc, io);
     return 1;

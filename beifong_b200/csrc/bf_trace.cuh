@@ -218,6 +218,7 @@ struct TraceIO {
     float4 *x1;                      // closest, gen 3, depth > 1: a missed continuation ray leaves time = phase = -inf
     bf_sample_record *records;
     uint32_t depth;                  // the shade iteration this trace feeds
+    uint32_t *steps;                 // optional debug output: traversal steps per ray
     uint32_t *work_cursor;
     unsigned long long *total;
 };
@@ -234,12 +235,13 @@ __global__ void __launch_bounds__(TRACE_THREADS) k_trace(const __grid_constant__
 
     enum { EMPTY = 0, BUSY = 1, FINISHED = 2, EXHAUSTED = 3 };
     int state = EMPTY;
-    uint32_t l = 0;
+    uint32_t l = 0, n_steps = 0;
     TraceLane L;
     while (true) {
         // ---- commit finished lanes (warp converged here) ----
         bool push = false;
         if (state == FINISHED) {
+            if (io.steps) io.steps[l] = n_steps;
             if (ANY_HIT) {
                 io.occl[l] = L.occluded ? 1u : 0u;
             } else {
@@ -278,6 +280,7 @@ __global__ void __launch_bounds__(TRACE_THREADS) k_trace(const __grid_constant__
                     l = io.queue ? io.queue[i] : i;
                     float4 ro = io.ray_o[l], rd = io.ray_d[l];
                     L.o = V3(ro.x, ro.y, ro.z); L.d = V3(rd.x, rd.y, rd.z); L.mint = ro.w; L.maxt = rd.w;
+                    n_steps = 0;
                     state = trace_begin<ANY_HIT>(sc, s_rect, L) ? BUSY : FINISHED;
                 } else {
                     state = EXHAUSTED;
@@ -293,6 +296,7 @@ __global__ void __launch_bounds__(TRACE_THREADS) k_trace(const __grid_constant__
         // ---- traverse until too few lanes are left ----
         do {
             if (state == BUSY) {
+                ++n_steps;
                 if (!trace_step<ANY_HIT>(sc, s_stack, l_stack, L)) state = FINISHED;
             }
         } while (__popc(__ballot_sync(0xffffffffu, state == BUSY)) >= min_busy);

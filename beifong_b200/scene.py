@@ -230,6 +230,12 @@ class FlatScene:
                  "bf_trace_occluded")
         return hit
 
+    def trace_steps(self, origins, directions):
+        o, d = _f32(origins).reshape(-1, 3), _f32(directions).reshape(-1, 3)
+        steps, t = np.empty(len(o), np.uint32), np.empty(len(o), np.float32)
+        self._ck(N.lib().bf_debug_trace_steps(self._h, _fp(o), _fp(d), None, None, len(o), _up(steps), _fp(t)), "bf_debug_trace_steps")
+        return steps, t
+
     def sample_records(self, n_samples, seed=0, first_sample=0):
         recs = (N.bf_sample_record * n_samples)()
         self._ck(N.lib().bf_debug_sample_records(self._h, seed, first_sample, n_samples, recs), "bf_debug_sample_records")
@@ -249,6 +255,11 @@ class FlatScene:
         ms, n = (C.c_float * 5)(), (C.c_uint32 * 5)()
         self._ck(N.lib().bf_last_kernel_ms(self._h, ms, n), "bf_last_kernel_ms")
         return {k: (ms[i], n[i]) for i, k in enumerate(self.KERNELS)}
+
+    def last_launch_list(self, capacity=4096):
+        ms, kind, n = (C.c_float * capacity)(), (C.c_uint32 * capacity)(), C.c_uint32()
+        self._ck(N.lib().bf_last_launch_list(self._h, ms, kind, capacity, C.byref(n)), "bf_last_launch_list")
+        return [(self.KERNELS[kind[i]], ms[i]) for i in range(n.value)]
 
     def last_receive_ms(self):
         a, b = C.c_float(), C.c_float()

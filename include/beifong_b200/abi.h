@@ -259,6 +259,9 @@ int bf_trace_first_hits(bf_scene *s, const float *origins, const float *directio
 /* Scene::ray_test (scene.cpp:170-178) */
 int bf_trace_occluded(bf_scene *s, const float *origins, const float *directions,
                       const float *mint, const float *maxt, uint64_t n_rays, uint8_t *hit);
+/* Tuning hook: BVH traversal steps (wide nodes visited) per closest-hit query. */
+int bf_debug_trace_steps(bf_scene *s, const float *origins, const float *directions, const float *mint, const float *maxt,
+                         uint64_t n_rays, uint32_t *steps, float *t);
 int bf_debug_sample_records(bf_scene *s, uint64_t seed, uint64_t first_sample,
                             uint64_t n_samples, bf_sample_record *records);
 int bf_get_stats(const bf_scene *s, bf_stats *stats);
@@ -272,6 +275,8 @@ int bf_set_trace_timing(bf_scene *s, int enabled);
  * needs bf_set_trace_timing(s, 1).  Used for the roofline of the dominant kernel. */
 enum { BF_K_RAYGEN = 0, BF_K_TRACE_CLOSEST = 1, BF_K_TRACE_SHADOW = 2, BF_K_SHADE = 3, BF_K_FINALIZE = 4, BF_K_COUNT = 5 };
 int bf_last_kernel_ms(bf_scene *s, float *ms, uint32_t *launches);
+/* The same, launch by launch in issue order (kind[i] = BF_K_*). */
+int bf_last_launch_list(bf_scene *s, float *ms, uint32_t *kind, uint32_t capacity, uint32_t *n_out);
 
 /* Flat export of everything added so far (test infrastructure feeds it to the CPU oracle;
  * also a cheap checkpoint: profile + (seed, next index) + this blob is a resumable state). */
