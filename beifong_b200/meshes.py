@@ -291,20 +291,19 @@ def car_body(n_u=264, n_v=133, length=4.5, width=1.8, height=1.4):
 
 
 def stairs(n_steps):
-    """create_stairs of src/librender/tests/mesh_generation.py: n_steps unit-width steps along y, step i at
-    height z = 1 - i / n_steps (known answer: t = 2 - floor(y n)/n for rays from z = 2 going down)."""
+    """The stairs fixture of src/librender/tests/mesh_generation.py:30-60 (same vertex and face numbering):
+    n_steps treads of unit width along y, tread i at height z = i / n_steps, joined by vertical risers.
+    Known answer (test_kdtrees.py:25-57): rays from z = 2 going down hit at t = 2 - floor(y n) / n."""
     h = 1.0 / n_steps
-    pos, faces = [], []
+    pos = np.zeros((4 * n_steps, 3), np.float32)
+    faces = []
     for i in range(n_steps):
-        y0, y1, z = i * h, (i + 1) * h, 1.0 - i * h
-        b = len(pos)
-        pos += [[0, y0, z], [1, y0, z], [1, y1, z], [0, y1, z]]
-        faces += [[b, b + 1, b + 2], [b, b + 2, b + 3]]
-        if i + 1 < n_steps:
-            b = len(pos)
-            pos += [[0, y1, z], [1, y1, z], [1, y1, z - h], [0, y1, z - h]]
-            faces += [[b, b + 1, b + 2], [b, b + 2, b + 3]]
-    return np.array(pos, np.float32), np.array(faces, np.uint32)
+        k, y0, y1, z = 4 * i, i * h, (i + 1) * h, i * h
+        pos[k:k + 4] = [[0, y0, z], [1, y0, z], [0, y1, z], [1, y1, z]]
+        faces += [[k, k + 1, k + 2], [k + 1, k + 3, k + 2]]
+        if i < n_steps - 1:
+            faces += [[k + 2, k + 3, k + 5], [k + 5, k + 4, k + 2]]
+    return pos, np.array(faces, np.uint32)
 
 
 def box_city(n_side=100, tess=10, extent=1000.0, seed=42):

@@ -1,0 +1,121 @@
+"""CPU tests of the drop-in boundary: the C-ABI library loads, exports every symbol include/beifong_b200/abi.h
+declares, and the host side mirrors the reference's error behaviour (Throw -> RuntimeError,
+NotImplementedError for plugins outside the path).  No compute call is made (no GPU here)."""
+import ctypes as C
+import os
+import re
+import subprocess
+
+import numpy as np
+import pytest
+
+from beifong_b200 import _native as N
+from beifong_b200 import configs, meshes
+from beifong_b200.scene import FlatScene, BeifongError
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+HEADER = os.path.join(ROOT, "include", "beifong_b200", "abi.h")
+
+
+def declared_symbols():
+    text = open(HEADER).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(bf_[a-z0-9_]+)\s*\(", text)))
+
+
+def test_library_exports_every_declared_symbol(native):
+    syms = declared_symbols()
+    assert len(syms) >= 30
+    for name in syms:
+        assert hasattr(native, name), f"{name} declared in abi.h but not exported"
+    assert set(syms) == set(N.PROTOTYPES), set(syms) ^ set(N.PROTOTYPES)
+    out = subprocess.run(["nm", "-D", "--defined-only", N.LIB_PATH], capture_output=True, text=True).stdout
+    exported = set(re.findall(r" T (bf_[a-z0-9_]+)", out))
+    assert set(syms) <= exported
+    assert native.bf_abi_version() == 1
+
+
+def test_struct_layouts_match_header(native):
+    # sizes the C side and the ctypes mirror must agree on (checked through the flat export round trip below too)
+    assert C.sizeof(N.bf_constants) == 32 and C.sizeof(N.bf_bsdf_desc) == 48 and C.sizeof(N.bf_signal_desc) == 40
+    assert C.sizeof(N.bf_adc_desc) == 40 and C.sizeof(N.bf_integrator_desc) == 32 and C.sizeof(N.bf_sample_record) == 48
+
+
+def test_product_is_sm100a_only_and_has_no_oracle_dependency():
+    out = subprocess.run(["cuobjdump", "--list-elf", N.LIB_PATH], capture_output=True, text=True).stdout
+    archs = set(re.findall(r"sm_(\d+a?)", out))
+    assert archs == {"100a"}, archs
+    ldd = subprocess.run(["ldd", N.LIB_PATH], capture_output=True, text=True).stdout
+    assert "oracle" not in ldd and "embree" not in ldd
+    for dirpath, _, files in os.walk(os.path.join(ROOT, "beifong_b200")):
+        for fn in files:
+            if fn.endswith((".py", ".cu", ".cuh", ".h", ".cpp")):
+                src = open(os.path.join(dirpath, fn), errors="replace").read()
+                assert "liboracle" not in src and "oracle_lib" not in src, fn
+
+
+def test_commit_fails_loudly_without_gpu(native):
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    s = configs.small_radar()
+    with pytest.raises(BeifongError, match="no CUDA device|CUDA"):
+        s.commit(0)
+    with pytest.raises(BeifongError, match="not committed"):
+        s.receive(16)
+
+
+def test_error_behaviour_mirrors_reference():
+    s = FlatScene(spectrum_width=1)
+    with pytest.raises(NotImplementedError):
+        FlatScene(spectrum_width=3)                          # only *_mono / *_spectral exist (mitsuba.conf)
+    with pytest.raises(BeifongError):
+        s.add_bsdf(N.BF_BSDF_DIFFUSE, reflectance=7)         # dangling reference (xml.cpp: unresolved <ref>)
+    with pytest.raises(NotImplementedError):
+        s.add_bsdf(17)                                       # plugin outside the radar path
+    b = s.add_diffuse(0.5)
+    with pytest.raises(BeifongError):
+        s.add_mesh(np.zeros((3, 3), np.float32), np.array([[0, 1, 3]], np.uint32), b)   # face index out of range
+    with pytest.raises(BeifongError):
+        s.set_integrator(N.BF_GEN_PHASE, max_depth=0)        # integrator.cpp:1713-1720
+    with pytest.raises(NotImplementedError):
+        s.set_adc(filter_radius=2.0)                         # wide reconstruction filters: not on the accelerated path
+    with pytest.raises(BeifongError):
+        s.commit(0)                                          # no receiver / integrator yet
+
+
+def test_flat_export_round_trip_and_profile_size():
+    s = configs.small_radar(spectrum_width=4)
+    blob = s.export()
+    magic, version = np.frombuffer(blob[:8], np.uint32)
+    assert magic == 0x31464642 and version == 1
+    assert int(np.frombuffer(blob[8:16], np.uint64)[0]) == blob.size
+    assert s.profile_shape() == (1024, 1, 4)                 # [f][t][Y, A, W, phase bin 0]
+    assert configs.c1_trans_rad().profile_shape() == (1, 1, 155)
+    from oracle_lib import OracleScene                       # the oracle parses the same blob: shapes agree
+    assert OracleScene(blob).profile_shape() == (1024, 1, 4)
+
+
+def test_ply_obj_loaders_on_generated_files(tmp_path):
+    p, f = meshes.stairs(3)
+    # ascii PLY with an extra vertex property and a quad face; binary little-endian PLY; OBJ with v/vt indices
+    ascii_ply = tmp_path / "a.ply"
+    with open(ascii_ply, "w") as fh:
+        fh.write("ply\nformat ascii 1.0\nelement vertex 4\nproperty float x\nproperty float y\nproperty float z\n"
+                 "property float confidence\nelement face 1\nproperty list uchar int vertex_indices\nend_header\n")
+        fh.write("0 0 0 1\n1 0 0 1\n1 1 0 1\n0 1 0 1\n4 0 1 2 3\n")
+    pp, ff, nn = meshes.load_ply(str(ascii_ply))
+    assert pp.shape == (4, 3) and ff.tolist() == [[0, 1, 2], [0, 2, 3]] and nn is None
+    bin_ply = tmp_path / "b.ply"
+    with open(bin_ply, "wb") as fh:
+        fh.write(b"ply\nformat binary_little_endian 1.0\nelement vertex %d\nproperty float x\nproperty float y\nproperty float z\n"
+                 b"element face %d\nproperty list uchar int vertex_indices\nend_header\n" % (len(p), len(f)))
+        fh.write(p.astype("<f4").tobytes())
+        for tri in f:
+            fh.write(b"\x03" + tri.astype("<i4").tobytes())
+    pp, ff, _ = meshes.load_ply(str(bin_ply))
+    assert np.array_equal(pp, p) and np.array_equal(ff, f)
+    obj = tmp_path / "c.obj"
+    obj.write_text("v -1 -1 0\nv 1 -1 0\nv -1 1 0\nv 1 1 0\nvt 1 1\nvt 0 0\nf 2/1 3/2 1/2\nf 2/1 4/2 3/2\n")
+    pp, ff, _ = meshes.load_obj(str(obj))
+    assert ff.tolist() == [[1, 2, 0], [1, 3, 2]]
