@@ -28,7 +28,7 @@ def c1_trans_rad(spectrum_width=1, max_depth=-1, rr_depth=5):
     material = s.add_diffuse(1.0, two_sided=True)
     rx = s.add_rect(rect_to_world((0.05, 0.05), (0, 0, 0), (0, -1, 0)), default_bsdf)
     s.add_rect(rect_to_world((1, 1), (0, -4, 0), (0, 0, 0)), material)
-    s.add_rect(rect_to_world((20, 20), (0, 0, -0.5), (0, 0, 0.5), up=(0, 1, 0)), material)
+    s.add_rect(rect_to_world((20, 20), (0, 0, -0.5), (0, 0, 0.5), up=(1, 0, 0)), material)   # no <up>: xml.cpp:911-913
     intensity = s.add_uniform(1.0)
     spot = FlatScene.endpoint(N.BF_TX_SPOT, texture=intensity, cutoff_angle_deg=25.0, beam_width_deg=20.0,
                               to_world=T.look_at((0, 0, 0), (0, -1, 0), (0, 0, 1)).matrix32())
