@@ -400,6 +400,7 @@ static int upload_tables(bf_scene *s) {
         memset(&sh[i], 0, sizeof(DevShape));
         sh[i].type = s->shapes[i].type; sh[i].index = s->shapes[i].index; sh[i].bsdf = s->shapes[i].bsdf; sh[i].tx = s->shapes[i].tx;
         sh[i].has_normals = s->shapes[i].type == 0 && !s->meshes[s->shapes[i].index].nrm.empty();
+        sh[i].mat_class = s->bsdfs[s->shapes[i].bsdf].kind == BF_BSDF_DIFFUSE ? 0u : 1u;
     }
     std::vector<DevEndpoint> txs;
     for (const HostTx &t : s->txs) txs.push_back(make_endpoint(t.d, t.shape));
@@ -565,7 +566,7 @@ static uint32_t env_u32(const char *name, uint32_t dflt, uint32_t lo, uint32_t h
     if (v > (long) hi) v = hi;
     return (uint32_t) v;
 }
-static uint32_t wave_lanes_default() { return env_u32("BF_WAVE_LANES", 1u << 20, 1024, 1u << 24); }
+static uint32_t wave_lanes_default() { return env_u32("BF_WAVE_LANES", 1u << 23, 1024, 1u << 24); }
 static uint32_t wave_streams_default() { return env_u32("BF_WAVE_STREAMS", 8, 1, 16); }
 
 static void free_slot(WaveSlot &sl, bool keep_stream) {
@@ -612,7 +613,7 @@ static int ensure_slot(bf_scene *s, size_t index, uint32_t lanes, bool records) 
     int n_spec = s->C.spectrum_width == 1 ? 1 : 5;
     for (int k = 0; k < n_spec; ++k) BF_CUDA(A((void **) &w.spec[k], n * 16));
     BF_CUDA(A((void **) &w.flags, n * 4));
-    BF_CUDA(A((void **) &w.queue[0], n * 4)); BF_CUDA(A((void **) &w.queue_h, n * 4)); BF_CUDA(A((void **) &w.queue_s, n * 4));
+    BF_CUDA(A((void **) &w.queue[0], n * 4)); BF_CUDA(A((void **) &w.queue_h, n * 4)); BF_CUDA(A((void **) &w.queue_h2, n * 4)); BF_CUDA(A((void **) &w.queue_s, n * 4));
     BF_CUDA(A((void **) &w.counters, (size_t) BF_CTR_STRIDE * (BF_MAX_BOUNCES + 2) * 4));
     if (records) BF_CUDA(A((void **) &w.records, n * sizeof(bf_sample_record)));
     w.capacity = lanes;
@@ -651,7 +652,7 @@ static int run_wave(bf_scene *s, WaveSlot &sl, uint64_t seed, uint64_t first, ui
     timed(BF_K_TRACE_CLOSEST, [&] { return launch_trace_closest(sc, w, nullptr, nullptr, n, 1, ctr + 4, ctr + 2, cfg); });
     for (uint32_t depth = 1; depth <= max_depth; ++depth) {
         uint32_t *blk = ctr + (size_t) BF_CTR_STRIDE * depth, *prev = ctr + (size_t) BF_CTR_STRIDE * (depth - 1);
-        timed(BF_K_SHADE, [&] { return launch_shade(sc, w, depth, w.queue_h, prev + 4, n, w.queue[0], blk, cfg); });
+        timed(BF_K_SHADE, [&] { return launch_shade(sc, w, depth, prev + 4, n, w.queue[0], blk, cfg); });
         if (depth >= max_depth) break;
         timed(BF_K_TRACE_SHADOW, [&] { return launch_trace_shadow(sc, w, w.queue_s, blk + 1, blk + 3, cfg); });
         timed(BF_K_TRACE_CLOSEST, [&] { return launch_trace_closest(sc, w, w.queue[0], blk + 0, 0, depth + 1, blk + 4, blk + 2, cfg); });

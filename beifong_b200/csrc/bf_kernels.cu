@@ -131,17 +131,20 @@ __device__ __forceinline__ void update_state(const DevScene &sc, float &time, fl
 
 template <int S>
 __global__ void __launch_bounds__(128) k_shade(const __grid_constant__ DevScene sc, const __grid_constant__ Wave w, uint32_t depth,
-                                               const uint32_t *__restrict__ queue, const uint32_t *__restrict__ count, uint32_t n_direct,
-                                               uint32_t *__restrict__ next_queue, uint32_t *ctr) {
-    const uint32_t n = queue ? *count : n_direct;
+                                               const uint32_t *__restrict__ hit_counts, uint32_t *__restrict__ next_queue, uint32_t *ctr) {
+    // two input queues, one per material class; the second starts on a warp boundary of the virtual index space
+    const uint32_t n_a = hit_counts[0], n_b = hit_counts[1];
+    const uint32_t n_a_round = (n_a + 31u) & ~31u;
     const uint32_t gen = sc.integ.gen;
     const uint32_t stride = gridDim.x * blockDim.x;
-    const uint32_t n_round = (n + 31u) & ~31u;   // keep warps converged for the ballot in queue_push
+    const uint32_t n_round = n_a_round + ((n_b + 31u) & ~31u);   // keep warps converged for the ballot in queue_push
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n_round; i += stride) {
         bool push_next = false, push_shadow = false;
         uint32_t l = 0;
-        if (i < n) {
-            l = queue ? queue[i] : i;
+        const bool second = i >= n_a_round;
+        const uint32_t j = second ? i - n_a_round : i;
+        if (j < (second ? n_b : n_a)) {
+            l = second ? w.queue_h2[j] : w.queue_h[j];
             uint32_t flags = w.flags[l];
             const float4 ro = w.ray_o[l], rd = w.ray_d[l];
             const float4 hit = w.hit[l];
@@ -292,16 +295,25 @@ __global__ void __launch_bounds__(128) k_shade(const __grid_constant__ DevScene 
 #define FIN_THREADS 256
 #define FIN_SMEM_FLOATS 8192
 
-// Sum `val` over the lanes of `peers` (lanes sharing one destination) into the group's leader.
-__device__ __forceinline__ float group_sum(uint32_t peers, float val) {
+// Warp-aggregated float scatter: lanes with key >= 0 and val != 0 add val to dst[key .. key + rep).  Lanes that
+// share a key are summed in registers first (one pass over the set bits of the participation ballot), and the
+// lowest lane of each key issues the atomics.
+__device__ __forceinline__ void agg_add(float *dst, int key, float val, uint32_t rep) {
+    const bool mine = key >= 0 && val != 0.f;
+    uint32_t todo = __ballot_sync(0xffffffffu, mine);
+    if (todo == 0) return;
     float acc = 0.f;
-    const uint32_t leader = __ffs(peers) - 1;
-#pragma unroll 4
-    for (int i = 0; i < 32; ++i) {
-        float v = __shfl_sync(0xffffffffu, val, i);
-        if ((peers >> i) & 1u) acc += v;
+    bool first = true;
+    const uint32_t lane = lane_id();
+    while (todo) {
+        const int i = __ffs(todo) - 1;
+        todo &= todo - 1;
+        const int k = __shfl_sync(0xffffffffu, key, i);
+        const float v = __shfl_sync(0xffffffffu, val, i);
+        if (k == key) { acc += v; if ((uint32_t) i < lane) first = false; }
     }
-    return lane_id() == leader ? acc : 0.f;
+    if (mine && first)
+        for (uint32_t r = 0; r < rep; ++r) atomicAdd(dst + key + r, acc);
 }
 
 template <int S>
@@ -321,7 +333,8 @@ __global__ void __launch_bounds__(FIN_THREADS) k_finalize(const __grid_constant_
     const uint32_t n_round = (n + 31u) & ~31u;
     for (uint32_t l = blockIdx.x * blockDim.x + threadIdx.x; l < n_round; l += stride) {
         int pixel = -1;          // destination pixel or -1
-        float fixed[5] = {0.f, 0.f, 0.f, 0.f, 0.f};
+        float val_a = 0.f;       // weighted value: channel Y (gen 3) or X = Y = Z (gen 1/2)
+        bool cnt_valid = false;  // alpha channel
         uint32_t n_fixed = gen == BF_GEN_PHASE ? 3u : 5u;
         int var_ch = -1;         // the single non-zero wrapper channel of this sample
         float var_val = 0.f;
@@ -377,14 +390,13 @@ __global__ void __launch_bounds__(FIN_THREADS) k_finalize(const __grid_constant_
                 Spec<S> wres;
 #pragma unroll
                 for (int k = 0; k < S; ++k) wres.v[k] = fabsf(weight.v[k]) * res.v[k];
-                fixed[0] = (valid && ran) ? hsum_spec<S>(wres) : 0.f;
-                fixed[1] = (valid && ran) ? 1.f : 0.f;
-                fixed[2] = 1.f;
+                val_a = (valid && ran) ? hsum_spec<S>(wres) : 0.f;
+                cnt_valid = valid && ran;
                 posx = tfx; posy = tfy;
                 off_x = (int) sc.adc.window_offset_t; off_y = (int) sc.adc.window_offset_f;
                 if (w.records) {
                     bf_sample_record *r = w.records + l;
-                    r->valid = (valid && ran) ? 1u : 0u; r->tf_t = tfx; r->tf_f = tfy; r->value = fixed[0];
+                    r->valid = (valid && ran) ? 1u : 0u; r->tf_t = tfx; r->tf_f = tfy; r->value = val_a;
                     r->phase = phase; r->wavelength0 = wl0;
                 }
             } else {
@@ -407,7 +419,7 @@ __global__ void __launch_bounds__(FIN_THREADS) k_finalize(const __grid_constant_
                 for (int k = 0; k < S; ++k) wres.v[k] = weight.v[k] * res.v[k];
                 // mono: xyz = value broadcast; spectral: the CIE matching functions vanish at radar wavelengths
                 float x = S == 1 ? wres.v[0] : 0.f;
-                fixed[0] = x; fixed[1] = x; fixed[2] = x; fixed[3] = valid ? 1.f : 0.f; fixed[4] = 1.f;
+                val_a = x; cnt_valid = valid;
                 posx = x2.x; posy = x2.y;
                 if (w.records) {
                     bf_sample_record *r = w.records + l;
@@ -419,20 +431,18 @@ __global__ void __launch_bounds__(FIN_THREADS) k_finalize(const __grid_constant_
             float cx = ceilf(px - .5f), cy = ceilf(py - .5f);
             if (cx >= 0.f && cy >= 0.f && cx < (float) W && cy < (float) H) pixel = (int) ((uint32_t) cy * W + (uint32_t) cx);
         }
-        // warp aggregation: lanes that hit the same pixel are summed in registers, one atomic per group
-        uint32_t peers = __match_any_sync(0xffffffffu, pixel);
-        const bool leader = lane_id() == (uint32_t) (__ffs(peers) - 1);
-        for (uint32_t c = 0; c < n_fixed; ++c) {
-            float s = group_sum(peers, fixed[c]);
-            if (leader && pixel >= 0 && s != 0.f) atomicAdd(dst + (size_t) C * pixel + c, s);
+        // Count channels (alpha, weight) are integers: one MATCH.ANY groups the lanes by pixel and the group leader
+        // adds the population counts.  Value channels go through agg_add.
+        const uint32_t peers = __match_any_sync(0xffffffffu, pixel);
+        const uint32_t valid_mask = __ballot_sync(0xffffffffu, cnt_valid);
+        if (pixel >= 0 && lane_id() == (uint32_t) (__ffs(peers) - 1)) {
+            float *px = dst + (size_t) C * pixel;
+            atomicAdd(px + n_fixed - 1, (float) __popc(peers));
+            const uint32_t nv = __popc(peers & valid_mask);
+            if (nv) atomicAdd(px + n_fixed - 2, (float) nv);
         }
-        int key = (pixel >= 0 && var_ch >= 0) ? pixel * (int) C + var_ch : -1;
-        if (__any_sync(0xffffffffu, key >= 0)) {
-            uint32_t vp = __match_any_sync(0xffffffffu, key);
-            float s = group_sum(vp, var_val);
-            if (lane_id() == (uint32_t) (__ffs(vp) - 1) && key >= 0)
-                for (uint32_t r = 0; r < var_rep; ++r) atomicAdd(dst + key + r, s);
-        }
+        agg_add(dst, pixel >= 0 ? pixel * (int) C : -1, val_a, n_fixed - 2);   // gen 3: Y; gen 1/2: X = Y = Z
+        agg_add(dst, (pixel >= 0 && var_ch >= 0) ? pixel * (int) C + var_ch : -1, var_val, var_rep);
     }
     if (use_smem) {
         __syncthreads();
@@ -465,7 +475,7 @@ static TraceIO trace_io(const Wave &w, const float4 *dirs, const uint32_t *queue
 int launch_trace_closest(const DevScene &sc, const Wave &w, const uint32_t *queue, const uint32_t *count, uint32_t n_direct,
                          uint32_t depth, uint32_t *hit_count, uint32_t *work_cursor, const LaunchCfg &cfg) {
     TraceIO io = trace_io(w, w.ray_d, queue, count, n_direct, work_cursor);
-    io.hit = w.hit; io.hit_queue = w.queue_h; io.hit_count = hit_count; io.x1 = w.x1; io.records = w.records; io.depth = depth;
+    io.hit = w.hit; io.hit_queue[0] = w.queue_h; io.hit_queue[1] = w.queue_h2; io.hit_count[0] = hit_count; io.hit_count[1] = hit_count + 1; io.x1 = w.x1; io.records = w.records; io.depth = depth;
     io.total = w.totals + 0;
     k_trace<false><<<trace_grid(cfg), TRACE_THREADS, 0, cfg.stream>>>(sc, io);
     return 1;
@@ -477,14 +487,12 @@ int launch_trace_shadow(const DevScene &sc, const Wave &w, const uint32_t *queue
     k_trace<true><<<trace_grid(cfg), TRACE_THREADS, 0, cfg.stream>>>(sc, io);
     return 1;
 }
-int launch_shade(const DevScene &sc, const Wave &w, uint32_t depth, const uint32_t *queue, const uint32_t *count, uint32_t n_direct,
+int launch_shade(const DevScene &sc, const Wave &w, uint32_t depth, const uint32_t *hit_counts, uint32_t n_bound,
                  uint32_t *next_queue, uint32_t *ctr_block, const LaunchCfg &cfg) {
-    int grid = cfg.sm_count * 8;
-    if (!queue) grid = (int) min((uint32_t) grid, (n_direct + 127u) / 128u);
-    else if (n_direct) grid = (int) min((uint32_t) grid, (n_direct + 127u) / 128u);   // n_direct = upper bound of *count
+    int grid = (int) min((uint32_t) (cfg.sm_count * 8), (n_bound + 64u + 127u) / 128u);   // n_bound = upper bound of the queue lengths
     if (grid < 1) grid = 1;
-    if (sc.S == 1) k_shade<1><<<grid, 128, 0, cfg.stream>>>(sc, w, depth, queue, count, n_direct, next_queue, ctr_block);
-    else k_shade<4><<<grid, 128, 0, cfg.stream>>>(sc, w, depth, queue, count, n_direct, next_queue, ctr_block);
+    if (sc.S == 1) k_shade<1><<<grid, 128, 0, cfg.stream>>>(sc, w, depth, hit_counts, next_queue, ctr_block);
+    else k_shade<4><<<grid, 128, 0, cfg.stream>>>(sc, w, depth, hit_counts, next_queue, ctr_block);
     return 1;
 }
 int launch_finalize(const DevScene &sc, const Wave &w, uint32_t n, float *profile, const LaunchCfg &cfg) {

@@ -32,7 +32,8 @@ struct DevShape {
     uint32_t bsdf;
     int32_t tx;             // transmitter / emitter id attached to the shape, -1 none
     uint32_t has_normals;   // vertex normals present (Mesh::has_vertex_normals)
-    uint32_t pad[3];
+    uint32_t mat_class;     // 0: diffuse BSDF, 1: anything else (shade-queue split, bf_trace.cuh)
+    uint32_t pad[2];
 };
 // Spectrum texture (src/spectra/uniform.cpp, regular.cpp, irregular.cpp)
 struct DevSpectrum {

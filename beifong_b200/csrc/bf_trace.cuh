@@ -31,6 +31,18 @@ __device__ __forceinline__ float magic_byte(uint32_t x, int j) {
     return __uint_as_float(__byte_perm(x, 0x47000000u, 0x7504u | ((uint32_t) j << 4)));
 }
 
+// Ray state is read once per query: keep it out of L1 so that the cache holds BVH nodes and triangles.
+__device__ __forceinline__ float4 ld_stream(const float4 *p) {
+    float4 v;
+    asm volatile("ld.global.L1::no_allocate.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p));
+    return v;
+}
+__device__ __forceinline__ uint32_t ld_stream(const uint32_t *p) {
+    uint32_t v;
+    asm volatile("ld.global.L1::no_allocate.u32 %0, [%1];" : "=r"(v) : "l"(p));
+    return v;
+}
+
 struct HitAcc {
     float t; float u, v; uint32_t slot; uint32_t shape, prim;
 };
@@ -214,7 +226,9 @@ struct TraceIO {
     uint32_t n_direct;
     float4 *hit;                     // closest: (t, u, v, slot)
     uint32_t *occl;                  // any-hit: 0 / 1
-    uint32_t *hit_queue, *hit_count; // closest: lanes whose ray hit something (the shade kernel's input), may be null
+    // closest: lanes whose ray hit something, split by the material class of the surface hit (the shade kernel's
+    // input: class 0 = diffuse, class 1 = everything else), so that a shading warp runs one BSDF.  May be null.
+    uint32_t *hit_queue[2], *hit_count[2];
     float4 *x1;                      // closest, gen 3, depth > 1: a missed continuation ray leaves time = phase = -inf
     bf_sample_record *records;
     uint32_t depth;                  // the shade iteration this trace feeds
@@ -223,8 +237,12 @@ struct TraceIO {
     unsigned long long *total;
 };
 
+// Work distribution: a warp claims chunks of consecutive rays from the global cursor and always has the NEXT chunk's
+// claim in flight (the atomic is issued when the previous chunk is opened and its result is first read when that
+// chunk runs dry), so the ~1 us round trip of a returning global atomic is off the critical path.  The same is
+// done for hit-queue pushes: the slot reservation is issued at one commit point and consumed at the next.
 template <bool ANY_HIT>
-__global__ void __launch_bounds__(TRACE_THREADS) k_trace(const __grid_constant__ DevScene sc, const __grid_constant__ TraceIO io) {
+__global__ void __launch_bounds__(TRACE_THREADS, 8) k_trace(const __grid_constant__ DevScene sc, const __grid_constant__ TraceIO io) {
     __shared__ float s_rect[13 * BF_MAX_RECTS];
     __shared__ uint2 s_stack[TRACE_SM_STACK * TRACE_THREADS];
     uint2 l_stack[TRACE_LOCAL_STACK];
@@ -232,14 +250,46 @@ __global__ void __launch_bounds__(TRACE_THREADS) k_trace(const __grid_constant__
     const uint32_t n = io.queue ? *io.count : io.n_direct;
     if (io.total && blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(io.total, (unsigned long long) n);
     const uint32_t lane = threadIdx.x & 31u, lt_mask = (1u << lane) - 1u;
+    const bool push_hits = !ANY_HIT && io.hit_queue[0] != nullptr;
+
+    // Every warp starts on a static batch of 32 rays (no atomic, a small launch is spread over the whole grid); the
+    // rest of the queue is handed out dynamically in chunks sized for >= ~8 claims per warp.
+    const uint32_t n_warps = gridDim.x * (TRACE_THREADS / 32);
+    const uint32_t static_total = n_warps * 32u;
+    const bool dynamic = n > static_total;
+    uint32_t chunk = 32;
+    while (dynamic && chunk < 256 && chunk * 16 * n_warps <= n - static_total) chunk *= 2;
+    uint32_t c_next = (blockIdx.x * (TRACE_THREADS / 32) + (threadIdx.x >> 5)) * 32u, c_end = c_next + 32u;   // warp-uniform
+    uint32_t claim = 0xffffffffu;                   // lane 0: start of the chunk claimed ahead
+    if (dynamic && lane == 0) claim = static_total + atomicAdd(io.work_cursor, chunk);
+    bool out_of_work = c_next >= n;
+
+    // deferred hit-queue push
+    uint32_t pend_base = 0, pend_meta = 0;          // meta: bit 31 valid, bit 30 class, bits 0..4 rank, bits 8..12 leader lane
 
     enum { EMPTY = 0, BUSY = 1, FINISHED = 2, EXHAUSTED = 3 };
     int state = EMPTY;
-    uint32_t l = 0, n_steps = 0;
+    uint32_t l = 0, n_steps = 0, pend_l = 0;
     TraceLane L;
     while (true) {
+        // ---- complete the push reserved at the previous commit point ----
+        if (push_hits) {
+            uint32_t any = __ballot_sync(0xffffffffu, pend_meta >> 31);
+            if (any) {
+#pragma unroll
+                for (int c = 0; c < 2; ++c) {
+                    uint32_t m = __ballot_sync(0xffffffffu, (pend_meta >> 31) && ((pend_meta >> 30) & 1u) == (uint32_t) c);
+                    if (m) {
+                        uint32_t base = __shfl_sync(0xffffffffu, pend_base, __ffs(m) - 1);
+                        if ((m >> lane) & 1u) io.hit_queue[c][base + __popc(m & lt_mask)] = pend_l;
+                    }
+                }
+                pend_meta = 0;
+            }
+        }
         // ---- commit finished lanes (warp converged here) ----
         bool push = false;
+        uint32_t cls = 0;
         if (state == FINISHED) {
             if (io.steps) io.steps[l] = n_steps;
             if (ANY_HIT) {
@@ -247,8 +297,9 @@ __global__ void __launch_bounds__(TRACE_THREADS) k_trace(const __grid_constant__
             } else {
                 const bool hit = L.best.slot != BF_NONE;
                 io.hit[l] = make_float4(hit ? L.best.t : bf_inf(), L.best.u, L.best.v, __uint_as_float(L.best.slot));
-                push = hit && io.hit_queue;
-                if (!hit && io.hit_queue) {
+                push = hit && push_hits;
+                if (push) cls = sc.shapes[L.best.shape].mat_class;
+                if (!hit && push_hits) {
                     // the miss branch of the integrator loop (pathtimefrequency.cpp:368-371 with t = inf, then
                     // `active &= si.is_valid()` ends the path): nothing else of the shade step is observable
                     if (io.depth > 1 && sc.integ.gen == BF_GEN_PHASE) {
@@ -259,39 +310,55 @@ __global__ void __launch_bounds__(TRACE_THREADS) k_trace(const __grid_constant__
             }
             state = EMPTY;
         }
-        if (!ANY_HIT && io.hit_queue) {
-            uint32_t m = __ballot_sync(0xffffffffu, push);
-            if (m) {
-                uint32_t leader = __ffs(m) - 1, base = 0;
-                if (lane == leader) base = atomicAdd(io.hit_count, (uint32_t) __popc(m));
-                base = __shfl_sync(0xffffffffu, base, leader);
-                if (push) io.hit_queue[base + __popc(m & lt_mask)] = l;
+        if (push_hits) {
+#pragma unroll
+            for (int c = 0; c < 2; ++c) {
+                uint32_t m = __ballot_sync(0xffffffffu, push && cls == (uint32_t) c);
+                if (m) {
+                    if (lane == (uint32_t) (__ffs(m) - 1)) pend_base = atomicAdd(io.hit_count[c], (uint32_t) __popc(m));   // consumed next round
+                    if ((m >> lane) & 1u) { pend_meta = 0x80000000u | ((uint32_t) c << 30); pend_l = l; }
+                }
             }
         }
-        // ---- refill empty lanes ----
+        // ---- refill empty lanes from the open chunk, running over into the chunk claimed ahead ----
         uint32_t want = __ballot_sync(0xffffffffu, state == EMPTY);
         if (want) {
-            uint32_t leader = __ffs(want) - 1, base = 0;
-            if (lane == leader) base = atomicAdd(io.work_cursor, (uint32_t) __popc(want));
-            base = __shfl_sync(0xffffffffu, base, leader);
+            const uint32_t cnt = __popc(want), rank = __popc(want & lt_mask);
+            const uint32_t avail = out_of_work ? 0u : c_end - c_next;
+            uint32_t i = rank < avail ? c_next + rank : 0xffffffffu;
+            if (!out_of_work && cnt > avail) {      // warp-uniform: open the next chunk (chunk >= 32 >= cnt - avail)
+                const uint32_t nxt = __shfl_sync(0xffffffffu, claim, 0);
+                if (nxt < n) {
+                    if (lane == 0) claim = static_total + atomicAdd(io.work_cursor, chunk);
+                    if (rank >= avail) i = nxt + (rank - avail);
+                    c_next = nxt + (cnt - avail); c_end = nxt + chunk;
+                } else {
+                    out_of_work = true;             // the cursor is past the end: so is every later claim
+                }
+            } else if (!out_of_work) {
+                c_next += cnt;
+            }
+            if (!out_of_work && c_next >= n) out_of_work = true;
             if (state == EMPTY) {
-                uint32_t i = base + __popc(want & lt_mask);
                 if (i < n) {
-                    l = io.queue ? io.queue[i] : i;
-                    float4 ro = io.ray_o[l], rd = io.ray_d[l];
+                    l = io.queue ? ld_stream(io.queue + i) : i;
+                    float4 ro = ld_stream(io.ray_o + l), rd = ld_stream(io.ray_d + l);
                     L.o = V3(ro.x, ro.y, ro.z); L.d = V3(rd.x, rd.y, rd.z); L.mint = ro.w; L.maxt = rd.w;
                     n_steps = 0;
                     state = trace_begin<ANY_HIT>(sc, s_rect, L) ? BUSY : FINISHED;
                 } else {
-                    state = EXHAUSTED;
+                    state = EXHAUSTED;              // only reached once the cursor is past the end
                 }
             }
         }
         uint32_t busy = __ballot_sync(0xffffffffu, state == BUSY);
         uint32_t fin = __ballot_sync(0xffffffffu, state == FINISHED);
-        if (busy == 0 && fin == 0) break;
+        if (busy == 0 && fin == 0) {
+            if (__ballot_sync(0xffffffffu, pend_meta >> 31) == 0) break;
+            continue;                                // one more round to flush the deferred push
+        }
         if (busy == 0) continue;
-        const bool drained = __any_sync(0xffffffffu, state == EXHAUSTED);
+        const bool drained = out_of_work;
         const int min_busy = drained ? 1 : TRACE_REFILL;
         // ---- traverse until too few lanes are left ----
         do {

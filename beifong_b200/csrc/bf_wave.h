@@ -18,7 +18,7 @@ enum : uint32_t { LANE_ACTIVE = 1u, LANE_VALID = 2u, LANE_BS_DELTA = 4u, LANE_PE
 #define BF_TRACE_LOCAL_STACK 56    // deeper entries spill to local memory
 #define BF_TRACE_STACK_DEPTH (BF_TRACE_SM_STACK + BF_TRACE_LOCAL_STACK)
 #define BF_CTR_STRIDE 8u     // per-depth counter block: [0] next-closest count, [1] shadow count,
-                             // [2] closest work cursor, [3] shadow work cursor, [4] hit count of that closest trace
+                             // [2] closest work cursor, [3] shadow work cursor, [4], [5] hit counts of that closest trace per material class
 
 struct Wave {
     uint32_t capacity;
@@ -35,7 +35,8 @@ struct Wave {
                          // S = 4: throughput, result, pending, wavelengths, ray weight
     uint32_t *flags;
     uint32_t *queue[2];  // [0] lane-id queue of continuation rays (shade -> trace), [1] unused
-    uint32_t *queue_h;   // lane-id queue of lanes whose continuation ray hit something (trace -> shade)
+    uint32_t *queue_h;   // lane-id queue of lanes whose continuation ray hit a diffuse surface (trace -> shade)
+    uint32_t *queue_h2;  // ... any other material: a shading warp runs one BSDF class
     uint32_t *queue_s;   // lane-id queue for shadow rays
     uint32_t *counters;  // BF_CTR_STRIDE * (BF_MAX_BOUNCES + 2)
     unsigned long long *totals;  // [0] closest queries traced, [1] shadow queries traced
@@ -55,7 +56,8 @@ int launch_trace_closest(const DevScene &sc, const Wave &w, const uint32_t *queu
                          uint32_t depth, uint32_t *hit_count, uint32_t *work_cursor, const LaunchCfg &cfg);
 int launch_trace_shadow(const DevScene &sc, const Wave &w, const uint32_t *queue, const uint32_t *count, uint32_t *work_cursor,
                         const LaunchCfg &cfg);
-int launch_shade(const DevScene &sc, const Wave &w, uint32_t depth, const uint32_t *queue, const uint32_t *count, uint32_t n_direct,
+// shades the lanes of w.queue_h[0 .. hit_counts[0]) and w.queue_h2[0 .. hit_counts[1]); n_bound >= their sum
+int launch_shade(const DevScene &sc, const Wave &w, uint32_t depth, const uint32_t *hit_counts, uint32_t n_bound,
                  uint32_t *next_queue, uint32_t *ctr_block, const LaunchCfg &cfg);
 int launch_finalize(const DevScene &sc, const Wave &w, uint32_t n, float *profile, const LaunchCfg &cfg);
 // Stand-alone ray queries (Scene::ray_intersect_preliminary / ray_test for caller-provided rays)

@@ -39,46 +39,45 @@ def algorithmic_bytes(n_tris, channels):
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons sampled during the timed region."""
-    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
-         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+    """SM clock / throttle reasons sampled through NVML every 10 ms while the timed region runs."""
 
     def __init__(self, index):
-        self.proc, self.lines = None, []
+        self.samples, self.reasons, self.stop_flag, self.thread, self.err = [], set(), False, None, None
         try:
-            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-i", str(index), "-lms", "100"],
-                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
-            self.thread = threading.Thread(target=self._read, daemon=True)
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_sm = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+            self.thread = threading.Thread(target=self._run, daemon=True)
             self.thread.start()
-        except OSError:
-            self.proc = None
+        except Exception as e:   # noqa: BLE001
+            self.err = f"nvml unavailable: {e}"
 
-    def _read(self):
-        for line in self.proc.stdout:
-            self.lines.append(line.strip())
+    def _run(self):
+        nv = self.nv
+        names = {"hw_slowdown": nv.nvmlClocksThrottleReasonHwSlowdown, "hw_thermal_slowdown": nv.nvmlClocksThrottleReasonHwThermalSlowdown,
+                 "sw_thermal_slowdown": nv.nvmlClocksThrottleReasonSwThermalSlowdown, "sw_power_cap": nv.nvmlClocksThrottleReasonSwPowerCap}
+        while not self.stop_flag:
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for k, bit in names.items():
+                    if r & bit:
+                        self.reasons.add(k)
+            except Exception as e:   # noqa: BLE001
+                self.err = str(e)
+                return
+            time.sleep(0.01)
 
     def stop(self):
-        if not self.proc:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        self.proc.terminate()
-        try:
-            self.proc.wait(timeout=2)
-        except Exception:
-            self.proc.kill()
-        sm, mx, reasons = [], [], set()
-        for ln in self.lines:
-            f = [x.strip() for x in ln.split(",")]
-            if len(f) < 7:
-                continue
-            try:
-                sm.append(float(f[0])); mx.append(float(f[1]))
-            except ValueError:
-                continue
-            for name, val in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[3:7]):
-                if val.lower().startswith("active"):
-                    reasons.add(name)
-        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": sorted(reasons),
-                "samples": len(sm)}
+        self.stop_flag = True
+        if self.thread:
+            self.thread.join(timeout=1)
+        if not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [self.err or "no samples"], "samples": 0}
+        return {"sm_mhz": float(np.median(self.samples)), "sm_max_mhz": float(self.max_sm), "reasons": sorted(self.reasons),
+                "samples": len(self.samples)}
 
 
 def cpu_reference_run(scene_blob, n_samples, steps, warmup, threads):
@@ -109,9 +108,9 @@ class DevArray:
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--samples", type=int, default=1 << 23, help="radar path samples per step per GPU")
+    ap.add_argument("--samples", type=int, default=1 << 27, help="radar path samples per step per GPU")
     ap.add_argument("--impl", default="native", choices=["native", "reference"])
     ap.add_argument("--cpu-samples", type=int, default=0, help="samples per step of the CPU arm (0 = calibrate to ~10 s)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -136,7 +135,7 @@ def main():
         n = args.cpu_samples
         if n <= 0:
             rate, _, _, _, _ = cpu_reference_run(blob, 1 << 16, 1, 0, threads)
-            n = int(max(1 << 16, min(1 << 24, rate * 8.0 / max(steps, 1))))
+            n = int(max(1 << 16, min(1 << 31, rate * 20.0 / max(steps + min(warmup, 1) / 8.0, 1))))
         value, dt, kind, what, qps = cpu_reference_run(blob, n, steps, min(warmup, 1), threads)
         out = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": steps, "warmup": warmup,
                "ms_per_step": dt / steps * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
@@ -249,7 +248,7 @@ def main():
         if world == 1 and not args.no_cpu_baseline:
             blob = scene.export()
             rate, _, _, _, _ = cpu_reference_run(blob, 1 << 16, 1, 0, threads)
-            cn = args.cpu_samples or int(max(1 << 16, min(1 << 24, rate * 10.0)))
+            cn = args.cpu_samples or int(max(1 << 16, min(1 << 31, rate * 12.0)))
             v, dt, kind, what, _ = cpu_reference_run(blob, cn, 1, 0, threads)
             cpu = {"value": v, "unit": UNIT, "cores": threads, "kind": kind, "sample": f"1 x {cn} samples of the same workload ({dt:.1f} s); {what}"}
         out = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": steps, "warmup": warmup, "ms_per_step": ms / steps,
