@@ -45,7 +45,7 @@ def fmcw_signal(resample_freq, gain=1.0):
 
 
 def radar_scene(mesh_pos, mesh_faces, spectrum_width=1, max_depth=4, range_bins=1024, bin_m=0.03, smooth_normals=True,
-                extra_meshes=()):
+                extra_meshes=(), phased=None):
     """Common 94 GHz FMCW layout of python_scripts/Render.py / Receive.ipynb: Tx and Rx are 5 mm x 5 mm
     rectangles at (0, 0, 0.3) facing +x, ground 20 x 20 diffuse 0.5, corner reflector 0.1 x 0.05 diffuse 1,
     target mesh twosided(roughconductor alpha 0.1).  Receiver `wignerreceiver` (mix_resample) + transmitter
@@ -68,11 +68,22 @@ def radar_scene(mesh_pos, mesh_faces, spectrum_width=1, max_depth=4, range_bins=
     for (p, f) in extra_meshes:
         s.add_mesh(p, f, car, normals=meshes.vertex_normals(p, f) if smooth_normals else None)
     tex = s.add_uniform(1.0)
-    s.add_transmitter(tx, FlatScene.endpoint(N.BF_TX_WIGNER, texture=tex, signal=fmcw_signal(True)))
+    tx_kind, rx_kind, tx_arr, rx_arr = N.BF_TX_WIGNER, N.BF_RX_WIGNER, None, None
+    if phased:
+        # `phased` = dict(n_elems, steer): phasedtransmitter / phasedreceiver on the same apertures, the aperture split into
+        # n_elems elements along its local y axis (elem_spacing = pitch, elem_axis = y), array_loc = the aperture's pose
+        n = int(phased.get("n_elems", 4))
+        pitch = 0.005 / n
+        def arr(pose):
+            return FlatScene.array(n, phased.get("steer", (0.0, 0.0, 0.0)), pose.matrix32(), (0.005, pitch, 1.0), (pitch, pitch, pitch), (0, 1, 0))
+        pose = T.translate([0.0, 0.0, 0.3]) * T.rotate([0, 1, 0], 90.0)
+        tx_kind, rx_kind = N.BF_TX_PHASED, N.BF_RX_PHASED
+        tx_arr, rx_arr = arr(T.translate([0.0, 0.01, 0.0]) * pose), arr(pose)
+    s.add_transmitter(tx, FlatScene.endpoint(tx_kind, texture=tex, signal=fmcw_signal(True), array=tx_arr))
     sweep_rate = 6e9 / 200e-6
     f_bandwidth = range_bins * bin_m * 2.0 / C0 * sweep_rate
-    s.set_receiver(rx, FlatScene.endpoint(N.BF_RX_WIGNER, texture=tex, signal=fmcw_signal(False), receive_type=N.BF_RECV_MIX_RESAMPLE,
-                                          adc_sampling_start=20e-6, adc_sampling_time=160e-6))
+    s.set_receiver(rx, FlatScene.endpoint(rx_kind, texture=tex, signal=fmcw_signal(False), receive_type=N.BF_RECV_MIX_RESAMPLE,
+                                          adc_sampling_start=20e-6, adc_sampling_time=160e-6, array=rx_arr))
     s.set_adc(t_bins=1, f_bins=range_bins, t_bandwidth=200e-6, f_bandwidth=f_bandwidth)
     s.set_integrator(N.BF_GEN_PHASE, max_depth=max_depth, rr_depth=5, phase_bins=1)
     return s
@@ -90,11 +101,11 @@ def c2_car_body(spectrum_width=1, max_depth=4, n_u=264, n_v=133):
     return radar_scene(p, f, spectrum_width=spectrum_width, max_depth=max_depth)
 
 
-def small_radar(spectrum_width=1, max_depth=4, n_u=24, n_v=13, smooth_normals=True):
+def small_radar(spectrum_width=1, max_depth=4, n_u=24, n_v=13, smooth_normals=True, phased=None):
     """The C2 layout with a few hundred triangles: sized for the brute-force oracle."""
     p, f = meshes.car_body(n_u, n_v)
     p = meshes.transform_points(car_pose().matrix32(), p)
-    return radar_scene(p, f, spectrum_width=spectrum_width, max_depth=max_depth, smooth_normals=smooth_normals)
+    return radar_scene(p, f, spectrum_width=spectrum_width, max_depth=max_depth, smooth_normals=smooth_normals, phased=phased)
 
 
 def c3_multi_object(spectrum_width=1, max_depth=4, copies=14, n_u=264, n_v=133, f_bins=1024, t_bins=1024):

@@ -60,6 +60,53 @@ DevRect make_rect(const float *to_world16, uint32_t shape) {
     return r;
 }
 
+static M4 m4_mul(const M4 &a, const M4 &b) {
+    M4 r;
+    for (int i = 0; i < 4; ++i) for (int j = 0; j < 4; ++j) {
+        double acc = 0;
+        for (int k = 0; k < 4; ++k) acc += (double) a.m[i][k] * b.m[k][j];
+        r.m[i][j] = (float) acc;
+    }
+    return r;
+}
+// Phased-array virtual elements, appended to `out` (phasedtransmitter.cpp:104-167).  to_world = array_loc *
+// translate(r_v) * scale(w.x/2, w.y/2, w.z); Transform::inverse() of the product is the product of the explicit
+// inverses (transform.h:53-61,161-171).  Load-time matrices are evaluated in double and rounded once.
+void make_velems(const bf_array_desc &a, const bf_constants &C, std::vector<DevVElem> &out) {
+    const int n = (int) a.n_elems;
+    std::vector<V3> locs;
+    for (int i = 0; i < n; ++i) {
+        double k = (n % 2 == 0) ? ((double) ((float) i - ((float) n / 2.f)) + 0.5) : (double) ((float) i - ((float) n - 1.f) / 2.f);
+        locs.push_back(V3((float) (0.0 - (double) (a.elem_spacing[0] * a.elem_axis[0]) * k),
+                          (float) (0.0 - (double) (a.elem_spacing[1] * a.elem_axis[1]) * k),
+                          (float) (0.0 - (double) (a.elem_spacing[2] * a.elem_axis[2]) * k)));
+    }
+    const V3 steer(sinf(a.steering_vector[0]), sinf(a.steering_vector[1]), sinf(a.steering_vector[2]));
+    M4 A; memcpy(A.m, a.array_loc, 64);
+    const M4 Ainv = m4_inverse(A);
+    const float k_psi = (float) (1.0 / ((double) (C.lambda_max_nm - C.lambda_min_nm) * 1e-9 / 2));
+    for (int i = 0; i < n; ++i) for (int j = 0; j < n; ++j) {
+        DevVElem e;
+        memset(&e, 0, sizeof(e));
+        const V3 r_v = (locs[i] + locs[j]) / 2.f;
+        e.r_dash = locs[i] - locs[j];
+        const float sx = a.elem_dims[0] / 2, sy = a.elem_dims[1] / 2, sz = a.elem_dims[2];
+        M4 TS, TSinv;
+        memset(&TS, 0, sizeof(TS)); memset(&TSinv, 0, sizeof(TSinv));
+        TS.m[0][0] = sx; TS.m[1][1] = sy; TS.m[2][2] = sz; TS.m[3][3] = 1.f; TS.m[0][3] = r_v.x; TS.m[1][3] = r_v.y; TS.m[2][3] = r_v.z;
+        TSinv.m[0][0] = rcp(sx); TSinv.m[1][1] = rcp(sy); TSinv.m[2][2] = rcp(sz); TSinv.m[3][3] = 1.f;
+        TSinv.m[0][3] = -r_v.x * rcp(sx); TSinv.m[1][3] = -r_v.y * rcp(sy); TSinv.m[2][3] = -r_v.z * rcp(sz);
+        const M4 to_world = m4_mul(A, TS);
+        e.to_object = m4_mul(TSinv, Ainv);
+        const V3 dp_du = xf_vector(to_world, V3(2.f, 0.f, 0.f)), dp_dv = xf_vector(to_world, V3(0.f, 2.f, 0.f));
+        const V3 normal = normalize(xf_normal(e.to_object, V3(0.f, 0.f, 1.f)));
+        e.ns = normalize(dp_du); e.nt = normalize(dp_dv); e.nn = normalize(normal);
+        const float arg = k_psi * dot(V3(0.f, 0.f, 0.f) - e.r_dash, steer);
+        e.psi_re = cosf(arg); e.psi_im = sinf(arg);
+        out.push_back(e);
+    }
+}
+
 }  // namespace bf
 
 struct HostShape { uint32_t type, index, bsdf; int32_t tx; };
@@ -105,7 +152,7 @@ struct bf_scene {
     DevScene dev;
     DevBuf<uint4> d_nodes; DevBuf<float4> d_tris, d_tri_nrm;
     DevBuf<DevRect> d_rects; DevBuf<DevShape> d_shapes; DevBuf<bf_bsdf_desc> d_bsdfs;
-    DevBuf<DevSpectrum> d_spectra; DevBuf<float> d_spec_pool; DevBuf<DevEndpoint> d_txs, d_rx;
+    DevBuf<DevSpectrum> d_spectra; DevBuf<float> d_spec_pool; DevBuf<DevEndpoint> d_txs, d_rx; DevBuf<DevVElem> d_velems;
     DevBuf<float> d_profile; size_t profile_floats = 0;
     // image of the geometry tables in pinned host memory (re-upload without a rebuild)
     void *h_geom = nullptr; size_t h_geom_bytes = 0, h_nodes_bytes = 0, h_tris_bytes = 0, h_nrm_bytes = 0;
@@ -207,7 +254,7 @@ void bf_scene_destroy(bf_scene *s) {
         if (s->stream) cudaStreamSynchronize(s->stream);
         free_wave(s);
         s->d_nodes.release(); s->d_tris.release(); s->d_tri_nrm.release(); s->d_rects.release(); s->d_shapes.release();
-        s->d_bsdfs.release(); s->d_spectra.release(); s->d_spec_pool.release(); s->d_txs.release(); s->d_rx.release();
+        s->d_bsdfs.release(); s->d_spectra.release(); s->d_spec_pool.release(); s->d_txs.release(); s->d_rx.release(); s->d_velems.release();
         s->d_profile.release(); s->d_totals.release();
         if (s->h_geom) cudaFreeHost(s->h_geom);
         if (s->ev_fork) cudaEventDestroy(s->ev_fork);
@@ -294,8 +341,11 @@ int bf_scene_add_rect(bf_scene *s, const float to_world[16], uint32_t bsdf_id, u
 static int check_endpoint(bf_scene *s, uint32_t shape_id, const bf_endpoint_desc *d, bool is_tx) {
     if (!d) return fail(s, BF_ERR_INVALID, "endpoint: null descriptor");
     bool free_standing = is_tx ? d->kind == BF_TX_SPOT : d->kind == BF_RX_PERSPECTIVE;
-    if (is_tx && d->kind == BF_TX_PHASED) return fail(s, BF_ERR_UNSUPPORTED, "phasedtransmitter is not on the accelerated path yet");
-    if (!is_tx && d->kind == BF_RX_PHASED) return fail(s, BF_ERR_UNSUPPORTED, "phasedreceiver is not on the accelerated path yet");
+    if ((is_tx && d->kind == BF_TX_PHASED) || (!is_tx && d->kind == BF_RX_PHASED)) {
+        if (d->array.n_elems < 1 || d->array.n_elems > BF_MAX_ARRAY_ELEMS) return fail(s, BF_ERR_INVALID, "phased endpoint: n_elems must be in [1, 16]");
+        if (d->array.elem_dims[0] == 0.f || d->array.elem_dims[1] == 0.f || d->array.elem_dims[2] == 0.f)
+            return fail(s, BF_ERR_INVALID, "phased endpoint: elem_dims has a zero component (scale() of the virtual element is singular)");
+    }
     if (is_tx && d->kind > BF_TX_AREALIGHT) return fail(s, BF_ERR_UNSUPPORTED, "unknown transmitter kind");
     if (!is_tx && d->kind > BF_RX_PERSPECTIVE) return fail(s, BF_ERR_UNSUPPORTED, "unknown receiver kind");
     if (!free_standing) {
@@ -403,13 +453,25 @@ static int upload_tables(bf_scene *s) {
         sh[i].mat_class = s->bsdfs[s->shapes[i].bsdf].kind == BF_BSDF_DIFFUSE ? 0u : 1u;
     }
     std::vector<DevEndpoint> txs;
-    for (const HostTx &t : s->txs) txs.push_back(make_endpoint(t.d, t.shape));
-    DevEndpoint rx = make_endpoint(s->rx, s->rx_shape);
+    std::vector<DevVElem> velems;
+    auto with_array = [&](DevEndpoint e, const bf_endpoint_desc &d, bool phased) {
+        if (phased) {
+            e.velem_offset = (uint32_t) velems.size();
+            make_velems(d.array, s->C, velems);
+            e.n_velems = (uint32_t) velems.size() - e.velem_offset;
+            e.wid_x = d.array.elem_dims[0]; e.wid_y = d.array.elem_dims[1];
+        }
+        return e;
+    };
+    for (const HostTx &t : s->txs) txs.push_back(with_array(make_endpoint(t.d, t.shape), t.d, t.d.kind == BF_TX_PHASED));
+    DevEndpoint rx = with_array(make_endpoint(s->rx, s->rx_shape), s->rx, s->has_rx && s->rx.kind == BF_RX_PHASED);
 
     BF_CUDA(s->d_spectra.alloc(ds.size())); BF_CUDA(s->d_spec_pool.alloc(pool.size()));
     BF_CUDA(s->d_shapes.alloc(sh.size())); BF_CUDA(s->d_bsdfs.alloc(s->bsdfs.size()));
     BF_CUDA(s->d_rects.alloc(s->rects.size())); BF_CUDA(s->d_txs.alloc(txs.size())); BF_CUDA(s->d_rx.alloc(1));
+    BF_CUDA(s->d_velems.alloc(velems.size()));
     BF_CUDA(cudaStreamSynchronize(s->stream));
+    if (!velems.empty()) BF_CUDA(cudaMemcpy(s->d_velems.p, velems.data(), velems.size() * sizeof(DevVElem), cudaMemcpyHostToDevice));
     if (!ds.empty()) BF_CUDA(cudaMemcpy(s->d_spectra.p, ds.data(), ds.size() * sizeof(DevSpectrum), cudaMemcpyHostToDevice));
     if (!pool.empty()) BF_CUDA(cudaMemcpy(s->d_spec_pool.p, pool.data(), pool.size() * 4, cudaMemcpyHostToDevice));
     if (!sh.empty()) BF_CUDA(cudaMemcpy(s->d_shapes.p, sh.data(), sh.size() * sizeof(DevShape), cudaMemcpyHostToDevice));
@@ -422,7 +484,7 @@ static int upload_tables(bf_scene *s) {
     d.C = s->C; d.S = s->C.spectrum_width;
     d.n_rects = (uint32_t) s->rects.size(); d.n_shapes = (uint32_t) sh.size(); d.n_txs = (uint32_t) txs.size();
     d.rects = s->d_rects.p; d.shapes = s->d_shapes.p; d.bsdfs = s->d_bsdfs.p; d.spectra = s->d_spectra.p;
-    d.spec_pool = s->d_spec_pool.p; d.txs = s->d_txs.p; d.rx = s->d_rx.p;
+    d.spec_pool = s->d_spec_pool.p; d.txs = s->d_txs.p; d.rx = s->d_rx.p; d.velems = s->d_velems.p;
     d.adc = s->adc; d.integ = s->integ;
     film_size(s, d.film_w, d.film_h); d.channels = n_channels(s);
     d.rx_needs_aperture = s->rx.kind != BF_RX_PERSPECTIVE;   // Sensor::needs_aperture_sample

@@ -112,6 +112,32 @@ BF_NI float rect_sample_wigner(const DevRect &r, V3 ds_p, V3 ds_d, float wavelen
                  sinc(BF_TWO_PI * nu_y * r.wid_y * tri(r_hat.y));
     return gain;
 }
+// Phased arrays: sample_wigner (phasedtransmitter.cpp:275-290 == phasedreceiver.cpp:289-304) with W_rect_2D (:261-273):
+// the real part of sum_i W_rect(r_hat_i, nu_hat_i) exp(2 pi i nu_hat_i . r'_i) psi'_i over the n^2 virtual elements
+// whose footprint contains the point.  Complex arithmetic spelled out as std::complex<float> evaluates it.
+BF_NI float phased_sample_wigner(const DevScene &sc, const DevEndpoint &ep, V3 ds_p, V3 ds_d, float wavelength0) {
+    float w_re = 0.f;
+    const double inv_wl = 1.0 / ((double) wavelength0 * 1e-9);
+    const DevVElem *ve = sc.velems + ep.velem_offset;
+    for (uint32_t i = 0; i < ep.n_velems; ++i) {
+        const DevVElem &e = ve[i];
+        V3 r_hat = xf_point(e.to_object, ds_p) / 2.f;
+        if (!(jabs(r_hat.x) <= 0.5f && jabs(r_hat.y) <= 0.5f)) continue;
+        V3 tv(fmadd(e.ns.z, ds_d.z, fmadd(e.ns.y, ds_d.y, e.ns.x * ds_d.x)),
+              fmadd(e.nt.z, ds_d.z, fmadd(e.nt.y, ds_d.y, e.nt.x * ds_d.x)),
+              fmadd(e.nn.z, ds_d.z, fmadd(e.nn.y, ds_d.y, e.nn.x * ds_d.x)));
+        V3 nu_hat((float) ((double) tv.x * inv_wl), (float) ((double) tv.y * inv_wl), (float) ((double) tv.z * inv_wl));
+        float g = 4 * ep.wid_x * ep.wid_y * tri(r_hat.x) * tri(r_hat.y) *
+                  sinc(BF_TWO_PI * nu_hat.x * ep.wid_x * tri(r_hat.x)) *
+                  sinc(BF_TWO_PI * nu_hat.y * ep.wid_y * tri(r_hat.y));
+        float th = BF_TWO_PI * dot(nu_hat, e.r_dash);
+        float sn, cs;
+        sincosf(th, &sn, &cs);
+        float a_re = g * cs, a_im = g * sn;
+        w_re += a_re * e.psi_re - a_im * e.psi_im;
+    }
+    return w_re;
+}
 // Shape::sample_direction / pdf_direction, src/librender/shape.cpp:323-354
 BF_D DirectionSample shape_sample_direction(const DevRect &r, V3 it_p, float it_time, V2 sample) {
     PositionSample ps = rect_sample_position(r, it_time, sample);
@@ -499,6 +525,25 @@ template <int S> BF_NI Spec<S> tx_eval(const DevScene &sc, const DevEndpoint &tx
         for (int k = 0; k < S; ++k) r.v[k] = signal_power * tx.signal.gain * (geom.v[k] * w) * BF_TWO_PI;
         return r;
     }
+    else if (tx.kind == BF_TX_PHASED) {                          // phasedtransmitter.cpp:296-381
+        float signal_power;
+        if (tx.signal.resample_freq) {
+            float f = sample_delta_frequency(tx.signal, si_time);
+            signal_power = 1.f;
+            float w = sc.C.c * rcp(f) * 1e9f;
+#pragma unroll
+            for (int k = 0; k < S; ++k) wl.v[k] = w;
+        } else {
+            signal_power = eval_signal(tx.signal, si_time, freq_from_wl(sc.C.c, wl.v[0]));
+        }
+        Spec<S> geom = spectrum_eval<S>(sc, tx.texture, wl);
+        float inv_area = rcp(sc.rects[sc.shapes[tx.shape].index].area);
+        float w = phased_sample_wigner(sc, tx, si.p, V3(0.f, 0.f, 0.f), wl.v[0]);
+        if (!(si.wi.z > 0.f)) return r;
+#pragma unroll
+        for (int k = 0; k < S; ++k) r.v[k] = signal_power * tx.signal.gain * (geom.v[k] * inv_area * w);
+        return r;
+    }
     return r;  // spot: eval = 0 (spot.cpp:166)
 }
 template <int S> BF_NI Spec<S> tx_sample_direction(const DevScene &sc, const DevEndpoint &tx, V3 it_p, float it_time, Spec<S> &wl, V2 sample, DirectionSample &ds) {
@@ -546,6 +591,16 @@ template <int S> BF_NI Spec<S> tx_sample_direction(const DevScene &sc, const Dev
     } else {
         signal_power = eval_signal(tx.signal, ds.time, freq_from_wl(sc.C.c, wl.v[0]));
     }
+    if (tx.kind == BF_TX_PHASED) {                                 // phasedtransmitter.cpp:596-654
+        float w = phased_sample_wigner(sc, tx, ds.p, ds.d * -1.f, wl.v[0]);
+#pragma unroll
+        for (int k = 0; k < S; ++k) geom.v[k] *= w;
+        ds.pdf *= w;
+        ds.pdf = sqrtf(ds.pdf * ds.pdf);
+#pragma unroll
+        for (int k = 0; k < S; ++k) out.v[k] = active ? signal_power * tx.signal.gain * geom.v[k] * 1.f : 0.f;
+        return out;
+    }
     float w = rect_sample_wigner(rc, ds.p, ds.d * -1.f, wl.v[0]);
 #pragma unroll
     for (int k = 0; k < S; ++k) geom.v[k] *= w;
@@ -563,6 +618,10 @@ BF_NI float tx_pdf_direction(const DevScene &sc, const DevEndpoint &tx, float wl
     float value = shape_pdf_direction(rc, ds);
     if (tx.kind == BF_TX_WIGNER)                                   // wignertransmitter.cpp:540-577
         value *= rect_sample_wigner(rc, ds.p, ds.d * -1.f, wl0);
+    else if (tx.kind == BF_TX_PHASED) {                            // phasedtransmitter.cpp:660-702
+        value *= phased_sample_wigner(sc, tx, ds.p, ds.d * -1.f, wl0);
+        value = sqrtf(value * value);
+    }
     return active ? value : 0.f;
 }
 
@@ -619,8 +678,15 @@ template <int S> BF_D void rx_sample_ray(const DevScene &sc, float time, float s
     PositionSample ps = rect_sample_position(r, time, sample2);
     Frame fr(ps.n);
     V3 dloc = square_to_cosine_hemisphere(sample3);
-    float w = rect_sample_wigner(r, ps.p, dloc, wl.v[0]);
-    float geom_gain = w * ps.pdf;
+    float geom_gain;
+    if (d.kind == BF_RX_PHASED) {                                  // phasedreceiver.cpp:313-375 (:353)
+        float w = phased_sample_wigner(sc, d, ps.p, dloc, wl.v[0]);
+        float dn = dot(dloc, ps.n);                                // local direction against the world normal, as written
+        geom_gain = w * ps.pdf * (1 - dn * dn * dn * dn);
+    } else {
+        float w = rect_sample_wigner(r, ps.p, dloc, wl.v[0]);
+        geom_gain = w * ps.pdf;
+    }
     float extents0 = r.area * BF_PI;
     ray.o = ps.p; ray.d = fr.to_world(dloc);
 #pragma unroll

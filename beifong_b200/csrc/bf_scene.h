@@ -40,9 +40,19 @@ struct DevSpectrum {
     uint32_t kind, n, offset;   // offset into the float pool: lambda[n] then value[n]
     float inv_interval;         // regular: 1 / ((hi - lo) / (n - 1))
 };
+// Virtual element (i, j) of a phased array (phasedtransmitter.cpp:119-167 == phasedreceiver.cpp:115-173):
+// world -> element-local transform, the normalised element frame, r' = loc_i - loc_j and the steering phasor psi'.
+struct DevVElem {
+    M4 to_object;
+    V3 ns, nt, nn;
+    V3 r_dash;
+    float psi_re, psi_im;
+};
 struct DevEndpoint {
     uint32_t kind, texture, receive_type;
     int32_t shape;              // parent shape id, -1 if free standing
+    uint32_t velem_offset, n_velems;   // phased: slice of DevScene::velems (n_elems^2 entries)
+    float wid_x, wid_y;         // phased: elem_dims.x / .y
     bf_signal_desc signal;
     float adc_sampling_start, adc_sampling_time;
     float cutoff, inv_transition, cos_cutoff, cos_beam;   // spot.cpp:85-93
@@ -66,6 +76,7 @@ struct DevScene {
     const float *spec_pool;
     const DevEndpoint *txs;
     const DevEndpoint *rx;
+    const DevVElem *velems;
     bf_adc_desc adc;
     bf_integrator_desc integ;
     uint32_t film_w, film_h, channels;
@@ -85,6 +96,7 @@ struct HostSpectrum {
 };
 
 DevRect make_rect(const float *to_world16, uint32_t shape);
+void make_velems(const bf_array_desc &a, const bf_constants &C, std::vector<DevVElem> &out);
 M4 m4_inverse(const M4 &a);
 
 }  // namespace bf

@@ -112,10 +112,12 @@ class FlatScene:
     @staticmethod
     def endpoint(kind, texture=0, signal=None, receive_type=N.BF_RECV_RAW, adc_sampling_start=0.0, adc_sampling_time=0.0,
                  to_world=None, cutoff_angle_deg=20.0, beam_width_deg=None, near_clip=1e-2, far_clip=1e4, sample_to_camera=None,
-                 shutter_open=0.0, shutter_open_time=0.0, film_width=1, film_height=1):
+                 shutter_open=0.0, shutter_open_time=0.0, film_width=1, film_height=1, array=None):
         d = N.bf_endpoint_desc()
         d.kind = kind
         d.texture = texture
+        if array is not None:
+            d.array = array
         if signal is not None:
             d.signal = signal
         d.receive_type = receive_type
@@ -131,6 +133,20 @@ class FlatScene:
         d.shutter_open, d.shutter_open_time = shutter_open, shutter_open_time
         d.film_width, d.film_height = film_width, film_height
         return d
+
+    @staticmethod
+    def array(n_elems=1, steering_vector=(0, 0, 0), array_loc=None, elem_dims=(0, 0, 0), elem_spacing=(0, 0, 0), elem_axis=(0, 0, 0)):
+        """Phased-array block of phasedtransmitter / phasedreceiver (phasedtransmitter.cpp:104-117): same names, same
+        defaults (zero vectors, identity array_loc)."""
+        a = N.bf_array_desc()
+        a.n_elems = int(n_elems)
+        a.steering_vector = (C.c_float * 3)(*[float(x) for x in steering_vector])
+        loc = np.eye(4, dtype=np.float32) if array_loc is None else _f32(array_loc).reshape(4, 4)
+        a.array_loc = (C.c_float * 16)(*loc.reshape(16))
+        a.elem_dims = (C.c_float * 3)(*[float(x) for x in elem_dims])
+        a.elem_spacing = (C.c_float * 3)(*[float(x) for x in elem_spacing])
+        a.elem_axis = (C.c_float * 3)(*[float(x) for x in elem_axis])
+        return a
 
     @staticmethod
     def signal(signaltype=N.BF_SIG_LINFMCW, sig_is_delta=True, resample_freq=False, amplitude=1.0, repfreq=1.0, t_ext=1.0,

@@ -194,6 +194,22 @@ class _Loader:
         return FlatScene.signal(N.BF_SIG_OTHER, g("sig_is_delta", True), g("resample_freq", False), g("amplitude", 1.0), g("prf", 1.0),
                                 t_ext, g("freq_centre", 1.0), 1.0 / t_ext, g("phase", 0.0), g("gain", 1.0))
 
+    def rx_signal(self, p, receive_type):
+        """Receivers read their signal block by receive_type (wignerreceiver.cpp:61-110 == phasedreceiver.cpp:67-113):
+        raw / raw_resample only have freq_centre, freq_ext and gain; m_sig_is_delta is left uninitialised there and is
+        defined here as false (a raw receiver samples the band, so `extents` carries the bandwidth)."""
+        if receive_type in ("raw", "raw_resample"):
+            g = p.get
+            return FlatScene.signal(N.BF_SIG_UNSET, False, False, 1.0, 1.0, 1.0, g("freq_centre", 1.0), g("freq_ext", 1.0), 0.0, g("gain", 1.0))
+        return self.signal(p)
+
+    def array(self, el, p):
+        """Phased-array parameters (phasedtransmitter.cpp:104-117)."""
+        loc = next((c for c in el if c.tag == "transform" and c.get("name") == "array_loc"), None)
+        z = [0.0, 0.0, 0.0]
+        return FlatScene.array(int(p.get("n_elems", 1)), p.get("steering_vector", z), (_transform(loc) if loc is not None else T()).matrix32(),
+                               p.get("elem_dims", z), p.get("elem_spacing", z), p.get("elem_axis", z))
+
     def antenna_texture(self, el, name, within_emitter=True):
         tex = self.spectrum(el, name, None, within_emitter)
         if tex is None:                                     # Texture::D65(1.f): d65 in spectral mode, uniform 1 otherwise
@@ -218,6 +234,12 @@ class _Loader:
         elif kind == "wignertransmitter":
             name = "antenna_texture" if any(c.get("name") == "antenna_texture" for c in el) else "radiance"
             d = FlatScene.endpoint(N.BF_TX_WIGNER, texture=self.antenna_texture(el, name), signal=self.signal(p))
+        elif kind == "phasedtransmitter":
+            if any(c.tag == "transform" and c.get("name") == "to_world" for c in el):   # phasedtransmitter.cpp:54-57
+                raise BeifongError("Found a 'to_world' transformation -- this is not allowed. The area light inherits this "
+                                   "transformation from its parent shape.")
+            d = FlatScene.endpoint(N.BF_TX_PHASED, texture=self.antenna_texture(el, "antenna_texture"), signal=self.signal(p),
+                                   array=self.array(el, p))
         else:
             raise NotImplementedError(f"xml: emitter / transmitter plugin \"{kind}\" is not on the accelerated path")
         return self.s.add_transmitter(shape_id, d)
@@ -252,16 +274,18 @@ class _Loader:
                                        sample_to_camera=meshes.perspective_sample_to_camera(fov, near, far, w, h), **common)
                 shape_id = None
             self.film = ("film", w, h)
-        elif kind in ("omnidirectional", "wignerreceiver"):
+        elif kind in ("omnidirectional", "wignerreceiver", "phasedreceiver"):
             start = p.get("adc_sampling_start", 0.0)
             if p.get("adc_sampling_end", 0.0) - start < 0:
                 raise BeifongError("ADC sampling time must be less than or equal to the adc sampling end time!")
-            rk = N.BF_RX_OMNIDIRECTIONAL if kind == "omnidirectional" else N.BF_RX_WIGNER
+            rk = {"omnidirectional": N.BF_RX_OMNIDIRECTIONAL, "wignerreceiver": N.BF_RX_WIGNER, "phasedreceiver": N.BF_RX_PHASED}[kind]
             if p.get("receive_type", "raw") not in RECEIVE_TYPES:
                 raise BeifongError(f"xml: unknown receive_type \"{p.get('receive_type')}\"")
-            d = FlatScene.endpoint(rk, texture=self.antenna_texture(el, "antenna_texture", False), signal=self.signal(p),
+            d = FlatScene.endpoint(rk, texture=self.antenna_texture(el, "antenna_texture", False),
+                                   signal=self.rx_signal(p, p.get("receive_type", "raw")),
                                    receive_type=RECEIVE_TYPES[p.get("receive_type", "raw")], adc_sampling_start=start,
-                                   adc_sampling_time=p.get("adc_sampling_end", 0.0) - start)
+                                   adc_sampling_time=p.get("adc_sampling_end", 0.0) - start,
+                                   array=self.array(el, p) if kind == "phasedreceiver" else None)
             t_bins, f_bins = int(fp.get("t_bins", 1024)), int(fp.get("f_bins", 1024))   # adc.cpp:18-21
             self.s.set_adc(t_bins=t_bins, f_bins=f_bins, t_bandwidth=fp.get("t_bandwidth", 3.81e-6), f_bandwidth=fp.get("f_bandwidth", 250e6),
                            window_t_bins=int(fp.get("window_t_bins", t_bins)), window_f_bins=int(fp.get("window_f_bins", f_bins)),

@@ -72,7 +72,10 @@ struct SpectrumTex { uint32_t kind = 0; std::vector<float> lambda, value; float 
 struct MeshData { std::vector<float> pos; std::vector<uint32_t> idx; std::vector<float> nrm; uint32_t nv = 0, nf = 0; };
 struct RectData { M4 to_world, to_object; Frame frame; float inv_area = 0, area = 0; };
 struct ShapeRec { int type = 0; /*0 mesh 1 rect*/ int index = 0; uint32_t bsdf = 0; int tx = -1; bool is_rx = false; };
-struct TxRec { int shape = -1; bf_endpoint_desc d; M4 to_world, to_object; float inv_transition = 0, cos_cutoff = 0, cos_beam = 0, cutoff = 0; };
+// Virtual element (i, j) of a phased array: phasedtransmitter.cpp:119-167 == phasedreceiver.cpp:115-173
+struct VElem { M4 to_object; V3 ns, nt, nn; V3 r_dash; float psi_re = 1.f, psi_im = 0.f; };
+struct TxRec { int shape = -1; bf_endpoint_desc d; M4 to_world, to_object; float inv_transition = 0, cos_cutoff = 0, cos_beam = 0, cutoff = 0;
+               std::vector<VElem> velems; };
 
 // ---- minimal BVH over triangles (test-side accelerator; equality with brute force is tested) ---
 struct BvhNode { float lo[3], hi[3]; uint32_t left, count; /* count>0: leaf, left = first */ };
@@ -113,6 +116,7 @@ struct Scene {
     std::vector<TxRec> txs;
     int rx_shape = -1; bf_endpoint_desc rx; bool has_rx = false;
     M4 rx_to_world;
+    std::vector<VElem> rx_velems;
     bf_adc_desc adc; bf_integrator_desc integ;
     // accel
     int accel = 0;  // 0 brute force, 1 own BVH, 2 embree
@@ -252,6 +256,72 @@ static float rect_sample_wigner(const RectData &r, V3 ds_p, V3 ds_d, float wavel
                  sinc(TwoPi * nu_hat.x * wid_x * tri(r_hat.x)) *
                  sinc(TwoPi * nu_hat.y * wid_y * tri(r_hat.y));
     return gain;
+}
+
+// ---- phased arrays: phasedtransmitter.cpp:104-167, 261-290 == phasedreceiver.cpp:115-173, 275-304 ----
+// Load-time geometry of the n x n virtual elements (double arithmetic rounded to fp32 once, as for every
+// load-time matrix of this oracle).  Transform::inverse() of a product is the product of the explicit
+// inverses (transform.h:53-61,161-171): to_object = S(1/w) T(-r_v) array_loc^-1.
+static std::vector<VElem> make_velems(const bf_array_desc &a, const bf_constants &C) {
+    std::vector<VElem> out;
+    int n = (int) a.n_elems;
+    if (n <= 0) return out;
+    std::vector<V3> locs;
+    for (int i = 0; i < n; ++i) {
+        // array_centre - elem_spacing*elem_axis*(i - n/2.f + 0.5)   (even)   |   (i - (n - 1.f)/2.f)   (odd)
+        double k = (n % 2 == 0) ? ((double) ((float) i - ((float) n / 2.f)) + 0.5) : (double) ((float) i - ((float) n - 1.f) / 2.f);
+        V3 l;
+        l.x = (float) (0.0 - (double) (a.elem_spacing[0] * a.elem_axis[0]) * k);
+        l.y = (float) (0.0 - (double) (a.elem_spacing[1] * a.elem_axis[1]) * k);
+        l.z = (float) (0.0 - (double) (a.elem_spacing[2] * a.elem_axis[2]) * k);
+        locs.push_back(l);
+    }
+    V3 steer(std::sin(a.steering_vector[0]), std::sin(a.steering_vector[1]), std::sin(a.steering_vector[2]));
+    M4 A = M4::from_rows16(a.array_loc), Ainv = inverse(A);
+    float k_psi = (float) (1.0 / ((double) (C.lambda_max_nm - C.lambda_min_nm) * 1e-9 / 2));
+    for (int i = 0; i < n; ++i) for (int j = 0; j < n; ++j) {
+        VElem e;
+        V3 r_v = (locs[i] + locs[j]) / 2.f;
+        e.r_dash = locs[i] - locs[j];
+        float sx = a.elem_dims[0] / 2, sy = a.elem_dims[1] / 2, sz = a.elem_dims[2];
+        M4 TS = M4::identity(), TSinv = M4::identity();
+        TS.m[0][0] = sx; TS.m[1][1] = sy; TS.m[2][2] = sz; TS.m[0][3] = r_v.x; TS.m[1][3] = r_v.y; TS.m[2][3] = r_v.z;
+        TSinv.m[0][0] = rcp(sx); TSinv.m[1][1] = rcp(sy); TSinv.m[2][2] = rcp(sz);
+        TSinv.m[0][3] = -r_v.x * rcp(sx); TSinv.m[1][3] = -r_v.y * rcp(sy); TSinv.m[2][3] = -r_v.z * rcp(sz);
+        M4 to_world = mul(A, TS);
+        e.to_object = mul(TSinv, Ainv);
+        V3 dp_du = xf_vector(to_world, V3(2, 0, 0)), dp_dv = xf_vector(to_world, V3(0, 2, 0));
+        V3 normal = normalize(xf_normal(e.to_object, V3(0, 0, 1)));
+        e.ns = normalize(dp_du); e.nt = normalize(dp_dv); e.nn = normalize(normal);
+        // exp(i * k_psi * dot(array_centre - r_dash, sin(steering)))
+        float arg = k_psi * dot(V3(0, 0, 0) - e.r_dash, steer);
+        e.psi_re = std::cos(arg); e.psi_im = std::sin(arg);
+        out.push_back(e);
+    }
+    return out;
+}
+// sample_wigner (phasedtransmitter.cpp:275-290): real part of the phasor sum over the virtual elements
+static float phased_sample_wigner(const std::vector<VElem> &ve, const float wid[3], V3 ds_p, V3 ds_d, float wavelength0) {
+    float w_re = 0.f, w_im = 0.f;
+    double inv_wl = 1.0 / ((double) wavelength0 * 1e-9);
+    for (const VElem &e : ve) {
+        V3 r_hat = xf_point(e.to_object, ds_p) / 2.f;
+        if (!(jabs(r_hat.x) <= 0.5f && jabs(r_hat.y) <= 0.5f)) continue;
+        V3 tv(fmadd(e.ns.z, ds_d.z, fmadd(e.ns.y, ds_d.y, e.ns.x * ds_d.x)),
+              fmadd(e.nt.z, ds_d.z, fmadd(e.nt.y, ds_d.y, e.nt.x * ds_d.x)),
+              fmadd(e.nn.z, ds_d.z, fmadd(e.nn.y, ds_d.y, e.nn.x * ds_d.x)));
+        V3 nu_hat((float) ((double) tv.x * inv_wl), (float) ((double) tv.y * inv_wl), (float) ((double) tv.z * inv_wl));
+        // W_rect_2D (:261-273)
+        float g = 4 * wid[0] * wid[1] * tri(r_hat.x) * tri(r_hat.y) *
+                  sinc(TwoPi * nu_hat.x * wid[0] * tri(r_hat.x)) *
+                  sinc(TwoPi * nu_hat.y * wid[1] * tri(r_hat.y));
+        float th = TwoPi * dot(nu_hat, e.r_dash);
+        float a_re = g * std::cos(th), a_im = g * std::sin(th);
+        w_re += a_re * e.psi_re - a_im * e.psi_im;
+        w_im += a_re * e.psi_im + a_im * e.psi_re;
+    }
+    (void) w_im;
+    return w_re;
 }
 
 // ---- Shape base: src/librender/shape.cpp:323-354 ------------------------------------------------
@@ -838,6 +908,25 @@ static Spec tx_eval(const Scene &sc, const TxRec &tx, SI &si) {
         for (int k = 0; k < sc.S; ++k) r.v[k] = signal_power * d.signal.gain * (geom.v[k] * w) * TwoPi;
         return r;
     }
+    else if (d.kind == BF_TX_PHASED) {                           // phasedtransmitter.cpp:296-381
+        float signal_power;
+        if (d.signal.resample_freq) {
+            float f = sample_delta_frequency(d.signal, si.time);
+            signal_power = 1.f;
+            for (int k = 0; k < sc.S; ++k) si.wl.v[k] = sc.C.c * rcp(f) * 1e9f;
+            si.phase = 0.f;
+        } else {
+            signal_power = eval_signal(d.signal, si.time, freq_from_wl(sc.C.c, si.wl.v[0]));
+            si.phase = 0.f;
+        }
+        Spec geom = spectrum_eval(sc, d.texture, si.wl);
+        float inv_area = rcp(sc.rects[sc.shapes[tx.shape].index].area);
+        // ds.d uninitialised in the reference as for the wigner transmitter: defined as the zero vector
+        float w = phased_sample_wigner(tx.velems, d.array.elem_dims, si.p, V3(0, 0, 0), si.wl.v[0]);
+        if (!(si.wi.z > 0.f)) return r;
+        for (int k = 0; k < sc.S; ++k) r.v[k] = signal_power * d.signal.gain * (geom.v[k] * inv_area * w);
+        return r;
+    }
     return r;  // spot: eval = 0 (spot.cpp:166)
 }
 struct TxDirResult { DirectionSample ds; Spec spec; };
@@ -886,6 +975,14 @@ static TxDirResult tx_sample_direction(const Scene &sc, const TxRec &tx, SI &it,
         signal_power = eval_signal(d.signal, ds.time, freq_from_wl(sc.C.c, it.wl.v[0]));
         it.phase = 0.f;
     }
+    if (d.kind == BF_TX_PHASED) {                                  // phasedtransmitter.cpp:596-654
+        float w = phased_sample_wigner(tx.velems, d.array.elem_dims, ds.p, ds.d * -1.f, it.wl.v[0]);
+        for (int k = 0; k < sc.S; ++k) geom.v[k] *= w;
+        ds.pdf *= w;
+        ds.pdf = std::sqrt(ds.pdf * ds.pdf);
+        for (int k = 0; k < sc.S; ++k) out.spec.v[k] = active ? signal_power * d.signal.gain * geom.v[k] * 1.f : 0.f;
+        return out;
+    }
     float w = rect_sample_wigner(sc.rects[sc.shapes[tx.shape].index], ds.p, ds.d * -1.f, it.wl.v[0]);
     for (int k = 0; k < sc.S; ++k) geom.v[k] *= w;
     ds.pdf *= w;
@@ -902,6 +999,9 @@ static float tx_pdf_direction(const Scene &sc, const TxRec &tx, const SI &it, co
     if (d.kind == BF_TX_WIGNER) {                                  // wignertransmitter.cpp:540-577
         float w = rect_sample_wigner(sc.rects[sc.shapes[tx.shape].index], ds.p, ds.d * -1.f, it.wl.v[0]);
         value *= w;
+    } else if (d.kind == BF_TX_PHASED) {                           // phasedtransmitter.cpp:660-702
+        value *= phased_sample_wigner(tx.velems, d.array.elem_dims, ds.p, ds.d * -1.f, it.wl.v[0]);
+        value = std::sqrt(value * value);
     }
     return active ? value : 0.f;
 }
@@ -997,8 +1097,15 @@ static void rx_sample_ray(const Scene &sc, float time, float sample1, V2 sample2
     PositionSample ps = rect_sample_position(r, time, sample2);
     Frame fr(ps.n);
     V3 dloc = square_to_cosine_hemisphere(sample3);
-    float w = rect_sample_wigner(r, ps.p, dloc, wavelength.v[0]);
-    float geom_gain = w * ps.pdf;
+    float geom_gain;
+    if (d.kind == BF_RX_PHASED) {                                  // phasedreceiver.cpp:313-375 (:353)
+        float w = phased_sample_wigner(sc.rx_velems, d.array.elem_dims, ps.p, dloc, wavelength.v[0]);
+        float dn = dot(dloc, ps.n);                                // local direction against the world normal, as written
+        geom_gain = w * ps.pdf * (1 - dn * dn * dn * dn);
+    } else {
+        float w = rect_sample_wigner(r, ps.p, dloc, wavelength.v[0]);
+        geom_gain = w * ps.pdf;
+    }
     float extents0 = r.area * Pi;
     ray = Ray(); ray.o = ps.p; ray.d = fr.to_world(dloc); ray.time = time; ray.phase = 0.f; ray.wl = wavelength;
     for (int k = 0; k < sc.S; ++k) {
@@ -1347,6 +1454,7 @@ orc_scene *orc_scene_import(const void *blob, size_t bytes) {
                     t.cutoff = cutoff; t.inv_transition = 1.0f / (cutoff - beam);
                     t.cos_cutoff = std::cos(cutoff); t.cos_beam = std::cos(beam);
                 }
+                if (t.d.kind == BF_TX_PHASED) t.velems = make_velems(t.d.array, sc.C);
                 if (t.shape >= 0) sc.shapes[t.shape].tx = (int) sc.txs.size();
                 sc.txs.push_back(t); break;
             }
@@ -1354,6 +1462,7 @@ orc_scene *orc_scene_import(const void *blob, size_t bytes) {
                 uint32_t sh = *(const uint32_t *) pl; sc.rx_shape = sh == BF_NONE ? -1 : (int) sh;
                 sc.rx = *(const bf_endpoint_desc *) (pl + 8); sc.has_rx = true;
                 sc.rx_to_world = M4::from_rows16(sc.rx.to_world);
+                if (sc.rx.kind == BF_RX_PHASED) sc.rx_velems = make_velems(sc.rx.array, sc.C);
                 if (sc.rx_shape >= 0) sc.shapes[sc.rx_shape].is_rx = true;
                 break;
             }
@@ -1468,6 +1577,12 @@ void orc_bsdf_sample(orc_scene *s, uint32_t id, const float *wi, float u1, float
 }
 float orc_rect_sample_wigner(orc_scene *s, uint32_t shape, const float *p, const float *d, float wavelength_nm) {
     return rect_sample_wigner(s->sc.rects[s->sc.shapes[shape].index], V3(p[0], p[1], p[2]), V3(d[0], d[1], d[2]), wavelength_nm);
+}
+// which: -1 = the receiver's array, >= 0 = transmitter index
+float orc_phased_sample_wigner(orc_scene *s, int which, const float *p, const float *d, float wavelength_nm) {
+    const std::vector<VElem> &ve = which < 0 ? s->sc.rx_velems : s->sc.txs[which].velems;
+    const float *wid = which < 0 ? s->sc.rx.array.elem_dims : s->sc.txs[which].d.array.elem_dims;
+    return phased_sample_wigner(ve, wid, V3(p[0], p[1], p[2]), V3(d[0], d[1], d[2]), wavelength_nm);
 }
 float orc_rect_area(orc_scene *s, uint32_t shape) { return s->sc.rects[s->sc.shapes[shape].index].area; }
 float orc_eval_signal(const bf_signal_desc *sg, float time, float f0) { return eval_signal(*sg, time, f0); }

@@ -68,6 +68,8 @@ def lib():
         L.orc_bsdf_pdf.restype = f32
         L.orc_bsdf_pdf.argtypes = [C.c_void_p, u32, P(f32), P(f32), P(f32)]
         L.orc_bsdf_sample.argtypes = [C.c_void_p, u32, P(f32), f32, f32, f32, P(f32), P(f32), P(f32), P(f32)]
+        L.orc_phased_sample_wigner.restype = f32
+        L.orc_phased_sample_wigner.argtypes = [C.c_void_p, C.c_int, P(f32), P(f32), f32]
         L.orc_rect_sample_wigner.restype = f32
         L.orc_rect_sample_wigner.argtypes = [C.c_void_p, u32, P(f32), P(f32), f32]
         L.orc_rect_area.restype = f32

@@ -118,3 +118,30 @@ def test_gen3_radar_scene_from_xml():
     k = int(6.0 / (6e6 / 256 / (6e9 / 200e-6) * 299792458.0 / 2))       # wall at 6 m -> beat-frequency bin 51
     assert prof[:k - 1, 0, 0].sum() == 0 and prof[k - 1:k + 6, 0, 0].sum() > 0.5 * prof[..., 0].sum()
     assert prof[..., 3].sum() > 0 and prof[..., 4].sum() > 0           # both phase bins populated
+
+
+ARRAY_XML = """<integer name="n_elems" value="4"/><vector name="steering_vector" x="0" y="0.05" z="0"/>
+      <vector name="elem_dims" x="0.005" y="0.00125" z="1"/><vector name="elem_spacing" x="0.00125" y="0.00125" z="0.00125"/>
+      <vector name="elem_axis" x="0" y="1" z="0"/>
+      <transform name="array_loc"><rotate y="1" angle="90"/><translate x="0" y="%s" z="0.3"/></transform>"""
+
+
+def test_phased_endpoints_from_xml():
+    """phasedtransmitter / phasedreceiver keep the reference's parameter names (phasedtransmitter.cpp:104-117)."""
+    from beifong_b200.scene import RADAR_94GHZ
+    from beifong_b200 import _native as N
+    text = (RADAR_XML.replace('<receiver type="wignerreceiver">', '<receiver type="phasedreceiver">' + ARRAY_XML % "0")
+            .replace('<transmitter type="wignertransmitter">', '<transmitter type="phasedtransmitter">' + ARRAY_XML % "0.01"))
+    L = xmlscene.load_string(text, consts=RADAR_94GHZ)
+    orc = OracleScene(L.scene.export(), accel=OracleScene.BRUTE)
+    prof = orc.receive(50000, seed=3, threads=4)
+    assert np.all(np.isfinite(prof)) and np.abs(prof[..., 0]).sum() > 0
+    # the same array built programmatically gives the same flat scene
+    ref = xmlscene.load_string(RADAR_XML, consts=RADAR_94GHZ)
+    assert len(L.scene.export()) == len(ref.scene.export())
+    with pytest.raises(BeifongError):     # to_world is not allowed on the transmitter itself (phasedtransmitter.cpp:54-57)
+        xmlscene.load_string(text.replace('<transmitter type="phasedtransmitter">',
+                                          '<transmitter type="phasedtransmitter"><transform name="to_world"><translate x="1"/></transform>'),
+                             consts=RADAR_94GHZ)
+    with pytest.raises(BeifongError):     # n_elems outside [1, 16]
+        xmlscene.load_string(text.replace('<integer name="n_elems" value="4"/>', '<integer name="n_elems" value="40"/>'), consts=RADAR_94GHZ)
