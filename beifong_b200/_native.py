@@ -8,7 +8,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libbeifong_b200.so")
+LIB_PATH = os.environ.get("BF_NATIVE_LIB") or os.path.join(_HERE, "libbeifong_b200.so")   # BF_NATIVE_LIB: an alternative build of the same library (tuning experiments)
 
 BF_NONE = 0xFFFFFFFF
 BF_OK, BF_ERR_INVALID, BF_ERR_UNSUPPORTED, BF_ERR_CUDA, BF_ERR_STATE, BF_ERR_IO = 0, -1, -2, -3, -4, -5

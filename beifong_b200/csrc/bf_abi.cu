@@ -57,6 +57,15 @@ DevRect make_rect(const float *to_world16, uint32_t shape) {
     r.wid_x = norm(r.fs); r.wid_y = norm(r.ft);
     r.ns = normalize(r.fs); r.nt = normalize(r.ft); r.nn = normalize(r.fn);
     r.shape = shape;
+    // padded world-space box of the four corners: margin 1e-4 of the largest coordinate / extent involved, far above the
+    // rounding of the object-space test it guards (a few 1e-7 relative)
+    float lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY}, mag = 1e-3f;
+    for (int c = 0; c < 4; ++c) {
+        V3 p = xf_point_affine(r.to_world, V3((c & 1) ? 1.f : -1.f, (c & 2) ? 1.f : -1.f, 0.f));
+        const float v[3] = {p.x, p.y, p.z};
+        for (int k = 0; k < 3; ++k) { lo[k] = std::min(lo[k], v[k]); hi[k] = std::max(hi[k], v[k]); mag = std::max(mag, std::fabs(v[k])); }
+    }
+    for (int k = 0; k < 3; ++k) { r.box_lo[k] = lo[k] - 1e-4f * mag; r.box_hi[k] = hi[k] + 1e-4f * mag; }
     return r;
 }
 
@@ -446,11 +455,18 @@ static int upload_tables(bf_scene *s) {
         ds.push_back(d);
     }
     std::vector<DevShape> sh(s->shapes.size());
+    int32_t cls1_kind = -2;   // -2: no class-1 shape seen yet
     for (size_t i = 0; i < sh.size(); ++i) {
         memset(&sh[i], 0, sizeof(DevShape));
         sh[i].type = s->shapes[i].type; sh[i].index = s->shapes[i].index; sh[i].bsdf = s->shapes[i].bsdf; sh[i].tx = s->shapes[i].tx;
         sh[i].has_normals = s->shapes[i].type == 0 && !s->meshes[s->shapes[i].index].nrm.empty();
-        sh[i].mat_class = s->bsdfs[s->shapes[i].bsdf].kind == BF_BSDF_DIFFUSE ? 0u : 1u;
+        const bf_bsdf_desc &bd = s->bsdfs[s->shapes[i].bsdf];
+        const uint32_t back_kind = (bd.two_sided && bd.back_bsdf != BF_NONE) ? s->bsdfs[bd.back_bsdf].kind : bd.kind;
+        sh[i].mat_class = (bd.kind == BF_BSDF_DIFFUSE && back_kind == BF_BSDF_DIFFUSE) ? 0u : 1u;
+        if (sh[i].mat_class == 1u) {
+            const int32_t k = (bd.kind == back_kind) ? (int32_t) bd.kind : -1;
+            cls1_kind = cls1_kind == -2 ? k : (cls1_kind == k ? k : -1);
+        }
     }
     std::vector<DevEndpoint> txs;
     std::vector<DevVElem> velems;
@@ -488,6 +504,9 @@ static int upload_tables(bf_scene *s) {
     d.adc = s->adc; d.integ = s->integ;
     film_size(s, d.film_w, d.film_h); d.channels = n_channels(s);
     d.rx_needs_aperture = s->rx.kind != BF_RX_PERSPECTIVE;   // Sensor::needs_aperture_sample
+    d.hint_cls1_bsdf = cls1_kind < 0 ? -1 : cls1_kind;
+    d.hint_tx_kind = txs.empty() ? -1 : (int32_t) txs[0].kind;
+    for (const DevEndpoint &e : txs) if ((int32_t) e.kind != d.hint_tx_kind) d.hint_tx_kind = -1;
     d.phase_denom = (double) ((s->C.lambda_max_nm - s->C.lambda_min_nm) / 2) * 1e-9;
     s->tables_dirty = false;
     return BF_OK;

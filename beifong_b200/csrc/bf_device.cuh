@@ -162,7 +162,7 @@ BF_D float shape_pdf_direction(const DevRect &r, const DirectionSample &ds) {
 // Mesh::compute_surface_interaction (src/librender/mesh.cpp:452-548), Rectangle::
 // compute_surface_interaction (rectangle.cpp:265-298), initialize_sh_frame + wi
 // (interaction.h:159-162, 613-644).
-BF_NI SI compute_si(const DevScene &sc, V3 ray_o, V3 ray_d, float4 hit) {
+BF_D SI compute_si_impl(const DevScene &sc, V3 ray_o, V3 ray_d, float4 hit) {
     SI si;
     si.t = hit.x;
     if (hit.x == bf_inf()) {
@@ -201,6 +201,8 @@ BF_NI SI compute_si(const DevScene &sc, V3 ray_o, V3 ray_d, float4 hit) {
     si.wi = si.to_local(-ray_d);
     return si;
 }
+
+BF_NI SI compute_si(const DevScene &sc, V3 ray_o, V3 ray_d, float4 hit) { return compute_si_impl(sc, ray_o, ray_d, hit); }
 
 // ---- microfacet distribution: include/mitsuba/render/microfacet.h -------------------------------------
 struct Microfacet {
@@ -325,16 +327,18 @@ struct BSDFSample { V3 wo; float pdf, eta; bool delta; };
 
 BF_D bool bsdf_is_smooth(const bf_bsdf_desc &b) { return b.kind == BF_BSDF_DIFFUSE || b.kind == BF_BSDF_ROUGHCONDUCTOR; }
 
-template <int S> BF_NI Spec<S> onesided_eval(const DevScene &sc, const bf_bsdf_desc &b, const Spec<S> &wl, V3 wi, V3 wo) {
+// BK >= 0: the BSDF kind is known at compile time (material-class shade kernels); -1: read from the descriptor.
+template <int S, int BK> BF_D Spec<S> onesided_eval_impl(const DevScene &sc, const bf_bsdf_desc &b, const Spec<S> &wl, V3 wi, V3 wo) {
     Spec<S> r;
+    const uint32_t kind = BK >= 0 ? (uint32_t) BK : b.kind;
     float cos_theta_i = wi.z, cos_theta_o = wo.z;
-    if (b.kind == BF_BSDF_DIFFUSE) {
+    if (kind == BF_BSDF_DIFFUSE) {
         if (!(cos_theta_i > 0.f && cos_theta_o > 0.f)) return r;
         Spec<S> refl = spectrum_eval<S>(sc, b.reflectance, wl);
 #pragma unroll
         for (int k = 0; k < S; ++k) r.v[k] = refl.v[k] * BF_INV_PI * cos_theta_o;
         return r;
-    } else if (b.kind == BF_BSDF_ROUGHCONDUCTOR) {
+    } else if (kind == BF_BSDF_ROUGHCONDUCTOR) {
         bool active = cos_theta_i > 0.f && cos_theta_o > 0.f;
         if (!active) return r;
         V3 H = normalize(wo + wi);
@@ -358,12 +362,13 @@ template <int S> BF_NI Spec<S> onesided_eval(const DevScene &sc, const bf_bsdf_d
     }
     return r;
 }
-BF_NI float onesided_pdf(const bf_bsdf_desc &b, V3 wi, V3 wo) {
+template <int BK> BF_D float onesided_pdf_impl(const bf_bsdf_desc &b, V3 wi, V3 wo) {
+    const uint32_t kind = BK >= 0 ? (uint32_t) BK : b.kind;
     float cos_theta_i = wi.z, cos_theta_o = wo.z;
-    if (b.kind == BF_BSDF_DIFFUSE) {
+    if (kind == BF_BSDF_DIFFUSE) {
         float pdf = square_to_cosine_hemisphere_pdf(wo);
         return (cos_theta_i > 0.f && cos_theta_o > 0.f) ? pdf : 0.f;
-    } else if (b.kind == BF_BSDF_ROUGHCONDUCTOR) {
+    } else if (kind == BF_BSDF_ROUGHCONDUCTOR) {
         V3 m = normalize(wo + wi);
         bool active = cos_theta_i > 0.f && cos_theta_o > 0.f && dot(wi, m) > 0.f && dot(wo, m) > 0.f;
         if (!active) return 0.f;
@@ -375,18 +380,19 @@ BF_NI float onesided_pdf(const bf_bsdf_desc &b, V3 wi, V3 wo) {
     }
     return 0.f;
 }
-template <int S> BF_NI Spec<S> onesided_sample(const DevScene &sc, const bf_bsdf_desc &b, const Spec<S> &wl, V3 wi, V2 sample2, BSDFSample &bs) {
+template <int S, int BK> BF_D Spec<S> onesided_sample_impl(const DevScene &sc, const bf_bsdf_desc &b, const Spec<S> &wl, V3 wi, V2 sample2, BSDFSample &bs) {
     Spec<S> r;
+    const uint32_t kind = BK >= 0 ? (uint32_t) BK : b.kind;
     bs.wo = V3(0.f, 0.f, 0.f); bs.pdf = 0.f; bs.eta = 0.f; bs.delta = false;
     float cos_theta_i = wi.z;
-    if (b.kind == BF_BSDF_DIFFUSE) {
+    if (kind == BF_BSDF_DIFFUSE) {
         if (!(cos_theta_i > 0.f)) return r;
         bs.wo = square_to_cosine_hemisphere(sample2);
         bs.pdf = square_to_cosine_hemisphere_pdf(bs.wo);
         bs.eta = 1.f;
         if (bs.pdf > 0.f) r = spectrum_eval<S>(sc, b.reflectance, wl);
         return r;
-    } else if (b.kind == BF_BSDF_ROUGHCONDUCTOR) {
+    } else if (kind == BF_BSDF_ROUGHCONDUCTOR) {
         if (!(cos_theta_i > 0.f)) return r;
         Microfacet distr((int) b.distribution, b.alpha_u, b.alpha_v, b.sample_visible != 0);
         V3 m; distr.sample(wi, sample2, m, bs.pdf);
@@ -409,7 +415,7 @@ template <int S> BF_NI Spec<S> onesided_sample(const DevScene &sc, const bf_bsdf
             r.v[k] = active ? F * w : 0.f;
         }
         return r;
-    } else if (b.kind == BF_BSDF_CONDUCTOR) {
+    } else if (kind == BF_BSDF_CONDUCTOR) {
         if (!(cos_theta_i > 0.f)) return r;
         bs.wo = V3(-wi.x, -wi.y, wi.z); bs.eta = 1.f; bs.pdf = 1.f; bs.delta = true;
         Spec<S> eta = spectrum_eval<S>(sc, b.eta, wl), kk = spectrum_eval<S>(sc, b.k, wl);
@@ -424,6 +430,10 @@ template <int S> BF_NI Spec<S> onesided_sample(const DevScene &sc, const bf_bsdf
     }
     return r;
 }
+// out-of-line generic versions (one copy each keeps the generic shade kernel's code small)
+template <int S> BF_NI Spec<S> onesided_eval(const DevScene &sc, const bf_bsdf_desc &b, const Spec<S> &wl, V3 wi, V3 wo) { return onesided_eval_impl<S, -1>(sc, b, wl, wi, wo); }
+BF_NI float onesided_pdf(const bf_bsdf_desc &b, V3 wi, V3 wo) { return onesided_pdf_impl<-1>(b, wi, wo); }
+template <int S> BF_NI Spec<S> onesided_sample(const DevScene &sc, const bf_bsdf_desc &b, const Spec<S> &wl, V3 wi, V2 sample2, BSDFSample &bs) { return onesided_sample_impl<S, -1>(sc, b, wl, wi, sample2, bs); }
 // twosided.cpp:94-181: strict inequalities, cos_theta == 0 gives a zero result
 // Front / back selection of twosided: the branch taken decides (descriptor, wi, wo); one call site each.
 BF_D const bf_bsdf_desc *twosided_select(const DevScene &sc, const bf_bsdf_desc &b, V3 &wi, bool &flipped, bool &dead) {
@@ -438,25 +448,29 @@ BF_D const bf_bsdf_desc *twosided_select(const DevScene &sc, const bf_bsdf_desc 
     dead = true;   // cos_theta == 0 (or NaN): zero result
     return &b;
 }
-template <int S> BF_D Spec<S> bsdf_eval(const DevScene &sc, uint32_t id, const Spec<S> &wl, V3 wi, V3 wo) {
+template <int S, int BK = -1> BF_D Spec<S> bsdf_eval(const DevScene &sc, uint32_t id, const Spec<S> &wl, V3 wi, V3 wo) {
     bool flipped, dead;
     const bf_bsdf_desc *b = twosided_select(sc, sc.bsdfs[id], wi, flipped, dead);
     if (dead) return Spec<S>();
     if (flipped) wo = V3(wo.x, wo.y, wo.z * -1.f);
-    return onesided_eval<S>(sc, *b, wl, wi, wo);
+    if constexpr (BK >= 0) return onesided_eval_impl<S, BK>(sc, *b, wl, wi, wo);
+    else return onesided_eval<S>(sc, *b, wl, wi, wo);
 }
-BF_D float bsdf_pdf(const DevScene &sc, uint32_t id, V3 wi, V3 wo) {
+template <int BK = -1> BF_D float bsdf_pdf(const DevScene &sc, uint32_t id, V3 wi, V3 wo) {
     bool flipped, dead;
     const bf_bsdf_desc *b = twosided_select(sc, sc.bsdfs[id], wi, flipped, dead);
     if (dead) return 0.f;
     if (flipped) wo = V3(wo.x, wo.y, wo.z * -1.f);
-    return onesided_pdf(*b, wi, wo);
+    if constexpr (BK >= 0) return onesided_pdf_impl<BK>(*b, wi, wo);
+    else return onesided_pdf(*b, wi, wo);
 }
-template <int S> BF_D Spec<S> bsdf_sample(const DevScene &sc, uint32_t id, const Spec<S> &wl, V3 wi, V2 s2, BSDFSample &bs) {
+template <int S, int BK = -1> BF_D Spec<S> bsdf_sample(const DevScene &sc, uint32_t id, const Spec<S> &wl, V3 wi, V2 s2, BSDFSample &bs) {
     bool flipped, dead;
     const bf_bsdf_desc *b = twosided_select(sc, sc.bsdfs[id], wi, flipped, dead);
     if (dead) { bs.wo = V3(0.f, 0.f, 0.f); bs.pdf = 0.f; bs.eta = 0.f; bs.delta = false; return Spec<S>(); }
-    Spec<S> r = onesided_sample<S>(sc, *b, wl, wi, s2, bs);
+    Spec<S> r;
+    if constexpr (BK >= 0) r = onesided_sample_impl<S, BK>(sc, *b, wl, wi, s2, bs);
+    else r = onesided_sample<S>(sc, *b, wl, wi, s2, bs);
     if (flipped) bs.wo.z *= -1.f;
     return r;
 }
@@ -494,19 +508,20 @@ template <int S> BF_D Spec<S> sample_shifted(float sample) {                    
 // ---- transmitters / emitters ------------------------------------------------------------------------------
 // `wl` is the path's current wavelength state: the reference mutates si.wavelengths through a
 // const_cast (wignertransmitter.cpp:220-221,439-440) and the last write decides the frequency bin.
-template <int S> BF_NI Spec<S> tx_eval(const DevScene &sc, const DevEndpoint &tx, const SI &si, float si_time, Spec<S> &wl) {
+template <int S, int TXK> BF_D Spec<S> tx_eval_impl(const DevScene &sc, const DevEndpoint &tx, const SI &si, float si_time, Spec<S> &wl) {
     Spec<S> r;
-    if (tx.kind == BF_TX_AREA) {                                   // areatransmitter.cpp:65-74
+    const uint32_t kind = TXK >= 0 ? (uint32_t) TXK : tx.kind;
+    if (kind == BF_TX_AREA) {                                   // areatransmitter.cpp:65-74
         if (!(si.wi.z > 0.f)) return r;
         Spec<S> rad = spectrum_eval<S>(sc, tx.texture, wl);
         float area = sc.rects[sc.shapes[tx.shape].index].area;
 #pragma unroll
         for (int k = 0; k < S; ++k) r.v[k] = rad.v[k] * area;
         return r;
-    } else if (tx.kind == BF_TX_AREALIGHT) {                       // src/emitters/area.cpp:63-72
+    } else if (kind == BF_TX_AREALIGHT) {                       // src/emitters/area.cpp:63-72
         if (!(si.wi.z > 0.f)) return r;
         return spectrum_eval<S>(sc, tx.texture, wl);
-    } else if (tx.kind == BF_TX_WIGNER) {                          // wignertransmitter.cpp:193-271
+    } else if (kind == BF_TX_WIGNER) {                          // wignertransmitter.cpp:193-271
         float signal_power;
         if (tx.signal.resample_freq) {
             float f = sample_delta_frequency(tx.signal, si_time);
@@ -525,7 +540,7 @@ template <int S> BF_NI Spec<S> tx_eval(const DevScene &sc, const DevEndpoint &tx
         for (int k = 0; k < S; ++k) r.v[k] = signal_power * tx.signal.gain * (geom.v[k] * w) * BF_TWO_PI;
         return r;
     }
-    else if (tx.kind == BF_TX_PHASED) {                          // phasedtransmitter.cpp:296-381
+    else if (kind == BF_TX_PHASED) {                          // phasedtransmitter.cpp:296-381
         float signal_power;
         if (tx.signal.resample_freq) {
             float f = sample_delta_frequency(tx.signal, si_time);
@@ -546,9 +561,10 @@ template <int S> BF_NI Spec<S> tx_eval(const DevScene &sc, const DevEndpoint &tx
     }
     return r;  // spot: eval = 0 (spot.cpp:166)
 }
-template <int S> BF_NI Spec<S> tx_sample_direction(const DevScene &sc, const DevEndpoint &tx, V3 it_p, float it_time, Spec<S> &wl, V2 sample, DirectionSample &ds) {
+template <int S, int TXK> BF_D Spec<S> tx_sample_direction_impl(const DevScene &sc, const DevEndpoint &tx, V3 it_p, float it_time, Spec<S> &wl, V2 sample, DirectionSample &ds) {
     Spec<S> out;
-    if (tx.kind == BF_TX_SPOT) {                                   // spot.cpp:97-115, 141-164
+    const uint32_t kind = TXK >= 0 ? (uint32_t) TXK : tx.kind;
+    if (kind == BF_TX_SPOT) {                                   // spot.cpp:97-115, 141-164
         ds.p = V3(tx.to_world.m[0][3], tx.to_world.m[1][3], tx.to_world.m[2][3]);
         ds.n = V3(0.f, 0.f, 0.f); ds.pdf = 1.f; ds.time = it_time; ds.delta = true; ds.object = 0;
         ds.d = ds.p - it_p; ds.dist = norm(ds.d);
@@ -569,7 +585,7 @@ template <int S> BF_NI Spec<S> tx_sample_direction(const DevScene &sc, const Dev
     const DevRect &rc = sc.rects[sc.shapes[tx.shape].index];
     ds = shape_sample_direction(rc, it_p, it_time, sample);
     bool active = dot(ds.d, ds.n) < 0.f && ds.pdf != 0.f;
-    if (tx.kind == BF_TX_AREA || tx.kind == BF_TX_AREALIGHT) {     // areatransmitter.cpp:131-182, area.cpp
+    if (kind == BF_TX_AREA || kind == BF_TX_AREALIGHT) {     // areatransmitter.cpp:131-182, area.cpp
         Spec<S> rad = spectrum_eval<S>(sc, tx.texture, wl);
 #pragma unroll
         for (int k = 0; k < S; ++k) out.v[k] = active ? rad.v[k] / ds.pdf : 0.f;
@@ -591,7 +607,7 @@ template <int S> BF_NI Spec<S> tx_sample_direction(const DevScene &sc, const Dev
     } else {
         signal_power = eval_signal(tx.signal, ds.time, freq_from_wl(sc.C.c, wl.v[0]));
     }
-    if (tx.kind == BF_TX_PHASED) {                                 // phasedtransmitter.cpp:596-654
+    if (kind == BF_TX_PHASED) {                                 // phasedtransmitter.cpp:596-654
         float w = phased_sample_wigner(sc, tx, ds.p, ds.d * -1.f, wl.v[0]);
 #pragma unroll
         for (int k = 0; k < S; ++k) geom.v[k] *= w;
@@ -610,19 +626,34 @@ template <int S> BF_NI Spec<S> tx_sample_direction(const DevScene &sc, const Dev
     for (int k = 0; k < S; ++k) out.v[k] = active ? signal_power * tx.signal.gain * geom.v[k] * extents : 0.f;
     return out;
 }
-BF_NI float tx_pdf_direction(const DevScene &sc, const DevEndpoint &tx, float wl0, const DirectionSample &ds) {
-    if (tx.kind == BF_TX_SPOT) return 0.f;
+template <int TXK> BF_D float tx_pdf_direction_impl(const DevScene &sc, const DevEndpoint &tx, float wl0, const DirectionSample &ds) {
+    const uint32_t kind = TXK >= 0 ? (uint32_t) TXK : tx.kind;
+    if (kind == BF_TX_SPOT) return 0.f;
     const DevRect &rc = sc.rects[sc.shapes[tx.shape].index];
     float dp = dot(ds.d, ds.n);
     bool active = dp < 0.f;
     float value = shape_pdf_direction(rc, ds);
-    if (tx.kind == BF_TX_WIGNER)                                   // wignertransmitter.cpp:540-577
+    if (kind == BF_TX_WIGNER)                                   // wignertransmitter.cpp:540-577
         value *= rect_sample_wigner(rc, ds.p, ds.d * -1.f, wl0);
-    else if (tx.kind == BF_TX_PHASED) {                            // phasedtransmitter.cpp:660-702
+    else if (kind == BF_TX_PHASED) {                            // phasedtransmitter.cpp:660-702
         value *= phased_sample_wigner(sc, tx, ds.p, ds.d * -1.f, wl0);
         value = sqrtf(value * value);
     }
     return active ? value : 0.f;
+}
+
+// out-of-line generic versions, and the dispatch on the compile-time hint
+template <int S> BF_NI Spec<S> tx_eval_generic(const DevScene &sc, const DevEndpoint &tx, const SI &si, float si_time, Spec<S> &wl) { return tx_eval_impl<S, -1>(sc, tx, si, si_time, wl); }
+template <int S> BF_NI Spec<S> tx_sample_direction_generic(const DevScene &sc, const DevEndpoint &tx, V3 it_p, float it_time, Spec<S> &wl, V2 sample, DirectionSample &ds) { return tx_sample_direction_impl<S, -1>(sc, tx, it_p, it_time, wl, sample, ds); }
+BF_NI float tx_pdf_direction_generic(const DevScene &sc, const DevEndpoint &tx, float wl0, const DirectionSample &ds) { return tx_pdf_direction_impl<-1>(sc, tx, wl0, ds); }
+template <int S, int TXK = -1> BF_D Spec<S> tx_eval(const DevScene &sc, const DevEndpoint &tx, const SI &si, float si_time, Spec<S> &wl) {
+    if constexpr (TXK >= 0) return tx_eval_impl<S, TXK>(sc, tx, si, si_time, wl); else return tx_eval_generic<S>(sc, tx, si, si_time, wl);
+}
+template <int S, int TXK = -1> BF_D Spec<S> tx_sample_direction(const DevScene &sc, const DevEndpoint &tx, V3 it_p, float it_time, Spec<S> &wl, V2 sample, DirectionSample &ds) {
+    if constexpr (TXK >= 0) return tx_sample_direction_impl<S, TXK>(sc, tx, it_p, it_time, wl, sample, ds); else return tx_sample_direction_generic<S>(sc, tx, it_p, it_time, wl, sample, ds);
+}
+template <int TXK = -1> BF_D float tx_pdf_direction(const DevScene &sc, const DevEndpoint &tx, float wl0, const DirectionSample &ds) {
+    if constexpr (TXK >= 0) return tx_pdf_direction_impl<TXK>(sc, tx, wl0, ds); else return tx_pdf_direction_generic(sc, tx, wl0, ds);
 }
 
 // ---- receivers / sensors -------------------------------------------------------------------------------------

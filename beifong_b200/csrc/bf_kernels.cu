@@ -34,6 +34,37 @@ __device__ __forceinline__ void queue_push(bool pred, uint32_t value, uint32_t *
     if (pred) queue[base + __popc(mask & ((1u << lane_id()) - 1u))] = value;
 }
 
+__device__ __forceinline__ void prefetch_l2(const void *p) { asm volatile("prefetch.global.L2 [%0];" :: "l"(p)); }
+
+// Deferred pair of warp-aggregated queue pushes: reserve() issues the two slot reservations (one atomic per queue per
+// warp) and complete(), called one loop iteration later, reads their results and writes the lane ids, so the ~1 us
+// round trip of a returning global atomic overlaps the next lane's shading.
+struct DeferredPush2 {
+    uint32_t base_a = 0, base_b = 0;   // atomic results, valid in the leader lanes
+    uint32_t meta = 0;                 // bit 0 / 1: this lane pushes to a / b; bits 8..12 / 16..20: rank; bits 24..31 unused
+    uint32_t value = 0;
+    __device__ __forceinline__ void reserve(bool pred_a, uint32_t *counter_a, bool pred_b, uint32_t *counter_b, uint32_t v) {
+        const uint32_t mask_a = __ballot_sync(0xffffffffu, pred_a), mask_b = __ballot_sync(0xffffffffu, pred_b);
+        const uint32_t lane = lane_id(), lt = (1u << lane) - 1u;
+        if (mask_a && lane == (uint32_t) (__ffs(mask_a) - 1)) base_a = atomicAdd(counter_a, (uint32_t) __popc(mask_a));
+        if (mask_b && lane == (uint32_t) (__ffs(mask_b) - 1)) base_b = atomicAdd(counter_b, (uint32_t) __popc(mask_b));
+        meta = (pred_a ? 1u : 0u) | (pred_b ? 2u : 0u) | ((uint32_t) __popc(mask_a & lt) << 8) | ((uint32_t) __popc(mask_b & lt) << 16);
+        value = v;
+    }
+    __device__ __forceinline__ void complete(uint32_t *queue_a, uint32_t *queue_b) {
+        const uint32_t mask_a = __ballot_sync(0xffffffffu, meta & 1u), mask_b = __ballot_sync(0xffffffffu, meta & 2u);
+        if (mask_a) {
+            const uint32_t base = __shfl_sync(0xffffffffu, base_a, __ffs(mask_a) - 1);
+            if (meta & 1u) queue_a[base + ((meta >> 8) & 31u)] = value;
+        }
+        if (mask_b) {
+            const uint32_t base = __shfl_sync(0xffffffffu, base_b, __ffs(mask_b) - 1);
+            if (meta & 2u) queue_b[base + ((meta >> 16) & 31u)] = value;
+        }
+        meta = 0;
+    }
+};
+
 template <int S> struct SpecIO;
 template <> struct SpecIO<1> {
     static __device__ __forceinline__ void load(const Wave &w, uint32_t l, Spec<1> &thr, Spec<1> &res, Spec<1> &pend, Spec<1> &wl) {
@@ -129,26 +160,50 @@ __device__ __forceinline__ void update_state(const DevScene &sc, float &time, fl
     phase = (float) ((double) phase + (double) (BF_TWO_PI * t) / sc.phase_denom);
 }
 
-template <int S>
-__global__ void __launch_bounds__(128) k_shade(const __grid_constant__ DevScene sc, const __grid_constant__ Wave w, uint32_t depth,
+#ifndef BF_SHADE_MIN_BLOCKS
+#define BF_SHADE_MIN_BLOCKS 5
+#endif
+// GEN / TXK / BK >= 0: the integrator generation, the transmitter kind and the BSDF kind are compile-time constants (the
+// device functions are then inlined with their other branches folded away, which keeps the executed code inside the 32 KB
+// instruction cache and the intermediate structs in registers); -1: read from the scene (out-of-line generic functions).
+// QSEL: 0 / 1 = shade the lanes of one material-class queue, 2 = both.
+template <int S, int GEN, int TXK, int BK, int QSEL>
+__global__ void __launch_bounds__(128, BF_SHADE_MIN_BLOCKS) k_shade(const __grid_constant__ DevScene sc, const __grid_constant__ Wave w, uint32_t depth,
                                                const uint32_t *__restrict__ hit_counts, uint32_t *__restrict__ next_queue, uint32_t *ctr) {
     // two input queues, one per material class; the second starts on a warp boundary of the virtual index space
-    const uint32_t n_a = hit_counts[0], n_b = hit_counts[1];
+    const uint32_t n_a = QSEL == 1 ? 0u : hit_counts[0], n_b = QSEL == 0 ? 0u : hit_counts[1];
     const uint32_t n_a_round = (n_a + 31u) & ~31u;
-    const uint32_t gen = sc.integ.gen;
+    const uint32_t gen = GEN >= 0 ? (uint32_t) GEN : sc.integ.gen;
     const uint32_t stride = gridDim.x * blockDim.x;
     const uint32_t n_round = n_a_round + ((n_b + 31u) & ~31u);   // keep warps converged for the ballot in queue_push
-    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n_round; i += stride) {
-        bool push_next = false, push_shadow = false;
-        uint32_t l = 0;
+    // lane id of virtual index i, or BF_NONE in the padding between / after the two queues
+    auto lane_of = [&](uint32_t i) -> uint32_t {
         const bool second = i >= n_a_round;
         const uint32_t j = second ? i - n_a_round : i;
-        if (j < (second ? n_b : n_a)) {
-            l = second ? w.queue_h2[j] : w.queue_h[j];
+        if (i >= n_round || j >= (second ? n_b : n_a)) return BF_NONE;
+        return second ? w.queue_h2[j] : w.queue_h[j];
+    };
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    uint32_t l_cur = lane_of(i), l_next = lane_of(i + stride);
+    DeferredPush2 dpush;
+    for (; i < n_round; i += stride) {
+        bool push_next = false, push_shadow = false;
+        const uint32_t l = l_cur;
+        // queue entries are read two iterations ahead; the records of the next lane are pulled into L2 while this one
+        // is shaded (queue entry -> records -> triangle is a chain of dependent DRAM round trips otherwise)
+        const uint32_t l_after = lane_of(i + 2u * stride);
+        if (l_next != BF_NONE) {
+            prefetch_l2(w.flags + l_next); prefetch_l2(w.ray_o + l_next); prefetch_l2(w.ray_d + l_next); prefetch_l2(w.hit + l_next);
+            prefetch_l2(w.x1 + l_next); prefetch_l2(w.rng + l_next);
+#pragma unroll
+            for (int k = 0; k < (S == 1 ? 1 : 4); ++k) prefetch_l2(w.spec[k] + l_next);
+        }
+        if (l != BF_NONE) {
             uint32_t flags = w.flags[l];
             const float4 ro = w.ray_o[l], rd = w.ray_d[l];
             const float4 hit = w.hit[l];
             float4 x1 = w.x1[l];
+            PCG32 rng; { ulonglong2 r = w.rng[l]; rng.state = r.x; rng.inc = r.y; }
             Spec<S> thr, res, pend, wl;
             SpecIO<S>::load(w, l, thr, res, pend, wl);
             if (flags & LANE_PENDING) {
@@ -159,7 +214,7 @@ __global__ void __launch_bounds__(128) k_shade(const __grid_constant__ DevScene 
                 flags &= ~LANE_PENDING;
             }
             const V3 o(ro.x, ro.y, ro.z), d(rd.x, rd.y, rd.z);
-            SI si = compute_si(sc, o, d, hit);
+            SI si = (GEN >= 0) ? compute_si_impl(sc, o, d, hit) : compute_si(sc, o, d, hit);
             float time = x1.x, phase = x1.y, bs_pdf = x1.z, scalar = x1.w;
             float emission_weight = 1.f;
             int transmitter = si.is_valid() ? sc.shapes[si.shape].tx : -1;
@@ -184,7 +239,7 @@ __global__ void __launch_bounds__(128) k_shade(const __grid_constant__ DevScene 
                     ds.d = si.p - o; ds.dist = norm(ds.d); ds.d = ds.d / ds.dist; ds.object = transmitter;
                     float tx_pdf = 0.f;
                     if (!(flags & LANE_BS_DELTA)) {
-                        tx_pdf = tx_pdf_direction(sc, sc.txs[transmitter], wl.v[0], ds);
+                        tx_pdf = tx_pdf_direction<TXK>(sc, sc.txs[transmitter], wl.v[0], ds);
                         if (sc.n_txs > 1) tx_pdf *= (1.f / (float) sc.n_txs);
                     }
                     emission_weight = mis_weight(bs_pdf, tx_pdf);
@@ -196,13 +251,12 @@ __global__ void __launch_bounds__(128) k_shade(const __grid_constant__ DevScene 
             // ---- loop body (pathtimefrequency.cpp:154-364) ----
             bool active = true;
             if (transmitter >= 0) {
-                Spec<S> e = tx_eval<S>(sc, sc.txs[transmitter], si, time, wl);
+                Spec<S> e = tx_eval<S, TXK>(sc, sc.txs[transmitter], si, time, wl);
 #pragma unroll
                 for (int k = 0; k < S; ++k) res.v[k] += emission_weight * thr.v[k] * e.v[k];
                 if (gen == BF_GEN_RANGE) scalar += si.is_valid() ? si.t : 0.f;      // pathlength.cpp:161
             }
             active &= si.is_valid();
-            PCG32 rng; { ulonglong2 r = w.rng[l]; rng.state = r.x; rng.inc = r.y; }
             if ((int) depth > sc.integ.rr_depth) {
                 float q = fminf(hmax_spec<S>(thr) * 1.f, .95f);
                 active &= rng.next_float32() < q;
@@ -214,19 +268,19 @@ __global__ void __launch_bounds__(128) k_shade(const __grid_constant__ DevScene 
             V3 new_d(0.f, 0.f, 0.f);
             if (go_on) {
                 const uint32_t bsdf = sc.shapes[si.shape].bsdf;
-                bool active_e = bsdf_is_smooth(sc.bsdfs[bsdf]);
+                bool active_e = (BK == BF_BSDF_DIFFUSE || BK == BF_BSDF_ROUGHCONDUCTOR) ? true : bsdf_is_smooth(sc.bsdfs[bsdf]);
                 if (active_e) {
                     // Scene::sample_transmitter_direction (scene.cpp:249-299)
                     V2 sample; sample.x = rng.next_float32(); sample.y = rng.next_float32();
                     DirectionSample ds; Spec<S> tspec;
                     ds.pdf = 0.f; ds.delta = false; ds.dist = 0.f;
                     if (sc.n_txs == 1) {
-                        tspec = tx_sample_direction<S>(sc, sc.txs[0], si.p, time, wl, sample, ds);
+                        tspec = tx_sample_direction<S, TXK>(sc, sc.txs[0], si.p, time, wl, sample, ds);
                     } else if (sc.n_txs > 1) {
                         float nt = (float) sc.n_txs, transmitter_pdf = 1.f / nt;
                         uint32_t index = min((uint32_t) (sample.x * nt), sc.n_txs - 1u);
                         sample.x = (sample.x - index * transmitter_pdf) * nt;
-                        tspec = tx_sample_direction<S>(sc, sc.txs[index], si.p, time, wl, sample, ds);
+                        tspec = tx_sample_direction<S, TXK>(sc, sc.txs[index], si.p, time, wl, sample, ds);
                         ds.pdf *= transmitter_pdf;
                         float inv = rcp(transmitter_pdf);
 #pragma unroll
@@ -235,8 +289,8 @@ __global__ void __launch_bounds__(128) k_shade(const __grid_constant__ DevScene 
                     active_e &= ds.pdf != 0.f;
                     if (active_e) {
                         V3 wo = si.to_local(ds.d);
-                        Spec<S> bsdf_val = bsdf_eval<S>(sc, bsdf, wl, si.wi, wo);
-                        float bpdf = bsdf_pdf(sc, bsdf, si.wi, wo);
+                        Spec<S> bsdf_val = bsdf_eval<S, BK>(sc, bsdf, wl, si.wi, wo);
+                        float bpdf = bsdf_pdf<BK>(sc, bsdf, si.wi, wo);
                         float mis = ds.delta ? 1.f : mis_weight(ds.pdf, bpdf);
                         bool nonzero = false;
 #pragma unroll
@@ -254,7 +308,7 @@ __global__ void __launch_bounds__(128) k_shade(const __grid_constant__ DevScene 
                 float s1 = rng.next_float32(); (void) s1;
                 V2 s2; s2.x = rng.next_float32(); s2.y = rng.next_float32();
                 BSDFSample bs;
-                Spec<S> bsdf_val = bsdf_sample<S>(sc, bsdf, wl, si.wi, s2, bs);
+                Spec<S> bsdf_val = bsdf_sample<S, BK>(sc, bsdf, wl, si.wi, s2, bs);
                 bool any_nz = false;
 #pragma unroll
                 for (int k = 0; k < S; ++k) { thr.v[k] = thr.v[k] * bsdf_val.v[k]; any_nz |= thr.v[k] != 0.f; }
@@ -284,9 +338,11 @@ __global__ void __launch_bounds__(128) k_shade(const __grid_constant__ DevScene 
                 if (push_next) r->n_closest++;
             }
         }
-        queue_push(push_shadow, l, w.queue_s, ctr + 1, nullptr);
-        queue_push(push_next, l, next_queue, ctr + 0, nullptr);
+        dpush.complete(w.queue_s, next_queue);       // the previous iteration's pushes
+        dpush.reserve(push_shadow, ctr + 1, push_next, ctr + 0, l);
+        l_cur = l_next; l_next = l_after;
     }
+    dpush.complete(w.queue_s, next_queue);
 }
 
 // =========================================================================================================
@@ -295,9 +351,22 @@ __global__ void __launch_bounds__(128) k_shade(const __grid_constant__ DevScene 
 #define FIN_THREADS 256
 #define FIN_SMEM_FLOATS 8192
 
+// fmodf(x, 2 pi) with fmodf's exact result, through one double division instead of the library's subtract-and-shift
+// loop (|x / 2 pi| reaches 1e5 for the carrier phase): q = trunc(|x| / y) is off by at most one, q * y is exact in
+// double (27 + 24 bits), and the corrected remainder is a float-representable number, so no step rounds.
+__device__ __forceinline__ float fmod_two_pi(float x) {
+    const float ax = fabsf(x);
+    if (!(ax < 1e8f)) return fmodf(x, BF_TWO_PI);      // inf / nan / huge: library path
+    const double y = (double) BF_TWO_PI;
+    const double q = trunc((double) ax / y);
+    double r = fma(-q, y, (double) ax);
+    if (r < 0.0) r += y; else if (r >= y) r -= y;
+    return copysignf((float) r, x);
+}
+
 // Warp-aggregated float scatter: lanes with key >= 0 and val != 0 add val to dst[key .. key + rep).  Lanes that
 // share a key are summed in registers first (one pass over the set bits of the participation ballot), and the
-// lowest lane of each key issues the atomics.
+// lowest lane of each key issues the atomics.  Used when the lanes of a warp land in the same pixel (1x1 films).
 __device__ __forceinline__ void agg_add(float *dst, int key, float val, uint32_t rep) {
     const bool mine = key >= 0 && val != 0.f;
     uint32_t todo = __ballot_sync(0xffffffffu, mine);
@@ -316,138 +385,186 @@ __device__ __forceinline__ void agg_add(float *dst, int key, float val, uint32_t
         for (uint32_t r = 0; r < rep; ++r) atomicAdd(dst + key + r, acc);
 }
 
+// What one sample adds to the profile (the tail of receive_sample / render_sample).
+struct Splat {
+    int pixel;          // destination pixel or -1
+    float val_a;        // weighted value: channel Y (gen 3) or X = Y = Z (gen 1/2)
+    bool cnt_valid;     // alpha channel
+    int var_ch;         // the single non-zero wrapper channel of this sample, or -1
+    float var_val;
+    uint32_t var_rep;   // gen 1 writes the value to 3 consecutive channels
+};
+
 template <int S>
+__device__ __forceinline__ Splat finalize_lane(const DevScene &sc, const Wave &w, uint32_t l) {
+    Splat sp; sp.pixel = -1; sp.val_a = 0.f; sp.cnt_valid = false; sp.var_ch = -1; sp.var_val = 0.f; sp.var_rep = 1;
+    const uint32_t gen = sc.integ.gen, W = sc.film_w, H = sc.film_h;
+    uint32_t flags = w.flags[l];
+    float4 x1 = w.x1[l], x2 = w.x2[l];
+    Spec<S> thr, res, pend, wl;
+    SpecIO<S>::load(w, l, thr, res, pend, wl);
+    if ((flags & LANE_PENDING) && !w.occl[l]) {
+#pragma unroll
+        for (int k = 0; k < S; ++k) res.v[k] += pend.v[k];
+    }
+    Spec<S> weight = SpecIO<S>::load_weight(w, l, x2);
+    const bool valid = flags & LANE_VALID;
+    float posx, posy;
+    int off_x = 0, off_y = 0;
+    if (gen == BF_GEN_PHASE) {
+        const DevEndpoint &rx = *sc.rx;
+        // integrator.cpp:1588-1639
+        float tfx = 0.f, tfy = 0.f;
+        bool ran = true;
+        float wl0 = wl.v[0];
+        float phase = valid ? x1.y : 0.f;
+        if (rx.receive_type == BF_RECV_MIX_RESAMPLE) {
+            tfx = x2.x - rx.adc_sampling_start;
+            tfy = (float) fabs(freq_from_wl_d(sc.C.c, wl0) - (double) x2.y);
+        } else if (rx.receive_type == BF_RECV_RAW || rx.receive_type == BF_RECV_RAW_RESAMPLE) {
+            tfx = x2.x - rx.adc_sampling_start;
+            tfy = freq_from_wl(sc.C.c, wl0);
+        } else {
+            ran = false;
+        }
+        if (!ran) {
+#pragma unroll
+            for (int k = 0; k < S; ++k) res.v[k] = 0.f;
+            phase = 0.f;
+        }
+        // phase.cpp:117-124; a zero value writes nothing, so the phase is only reduced where one is written
+        float hs = hsum_spec<S>(res);
+        float pv = (valid && ran) ? hs : 0.f;
+        if (ran && sc.integ.phase_bins > 0 && pv != 0.f) {
+            float ph = fmod_two_pi(phase);
+            ph += ph < 0.f ? BF_TWO_PI : 0.f;
+            float bin_width = BF_TWO_PI / (float) sc.integ.phase_bins;
+            for (uint32_t k = 0; k < sc.integ.phase_bins; ++k) {
+                float centre = (float) ((double) bin_width * ((double) k + 0.5));
+                if (rect((ph - centre) / bin_width) > 0.f) { sp.var_ch = 3 + (int) k; sp.var_val = pv; }
+            }
+        }
+        tfx *= (float) sc.adc.t_bins / sc.adc.t_bandwidth;
+        tfy *= (float) sc.adc.f_bins / sc.adc.f_bandwidth;
+        Spec<S> wres;
+#pragma unroll
+        for (int k = 0; k < S; ++k) wres.v[k] = fabsf(weight.v[k]) * res.v[k];
+        sp.val_a = (valid && ran) ? hsum_spec<S>(wres) : 0.f;
+        sp.cnt_valid = valid && ran;
+        posx = tfx; posy = tfy;
+        off_x = (int) sc.adc.window_offset_t; off_y = (int) sc.adc.window_offset_f;
+        if (w.records) {
+            bf_sample_record *r = w.records + l;
+            r->valid = (valid && ran) ? 1u : 0u; r->tf_t = tfx; r->tf_f = tfy; r->value = sp.val_a;
+            r->phase = phase; r->wavelength0 = wl0;
+        }
+    } else {
+        // range.cpp:141-161 / time.cpp:118-153: bins from the UNWEIGHTED spectrum, first channel
+        float scalar = x1.w, r0 = res.v[0];
+        if (gen == BF_GEN_RANGE) {
+            for (uint32_t i = 0; i < sc.integ.range_bins; ++i) {
+                float lo = (float) i * sc.integ.dr, hi = (float) i * sc.integ.dr + sc.integ.dr;
+                if (scalar >= lo && scalar < hi && r0 != 0.f) { sp.var_ch = 5 + (int) i; sp.var_val = r0; }
+            }
+        } else {
+            const float dt = 0.5e-9f;
+            for (int i = 0; i < 50; ++i) {
+                float lo = (float) i * dt, hi = (float) i * dt + dt;
+                if (scalar >= lo && scalar < hi && r0 != 0.f) { sp.var_ch = 5 + 3 * i; sp.var_val = r0; sp.var_rep = 3; }
+            }
+        }
+        Spec<S> wres;
+#pragma unroll
+        for (int k = 0; k < S; ++k) wres.v[k] = weight.v[k] * res.v[k];
+        // mono: xyz = value broadcast; spectral: the CIE matching functions vanish at radar wavelengths
+        float x = S == 1 ? wres.v[0] : 0.f;
+        sp.val_a = x; sp.cnt_valid = valid;
+        posx = x2.x; posy = x2.y;
+        if (w.records) {
+            bf_sample_record *r = w.records + l;
+            r->valid = valid ? 1u : 0u; r->tf_t = posx; r->tf_f = posy; r->value = r0; r->phase = scalar; r->wavelength0 = wl.v[0];
+        }
+    }
+    // SignalBlock::put, box filter of radius 0.5 (signalblock.cpp:162-169)
+    float px = posx - ((float) off_x - 0.f + .5f), py = posy - ((float) off_y - 0.f + .5f);
+    float cx = ceilf(px - .5f), cy = ceilf(py - .5f);
+    if (cx >= 0.f && cy >= 0.f && cx < (float) W && cy < (float) H) sp.pixel = (int) ((uint32_t) cy * W + (uint32_t) cx);
+    return sp;
+}
+
+// SMEM: the whole profile fits a per-CTA shared-memory histogram (range profiles): value channels are fp32 (CAS-loop
+// shared atomics), the two count channels (alpha, weight) are accumulated as integers with native shared atomics and
+// converted at the flush, which is one global atomic per non-zero entry.  Otherwise samples go to HBM directly, as one
+// 128-bit reduction per sample when a pixel is four channels wide.
+template <int S, bool SMEM>
 __global__ void __launch_bounds__(FIN_THREADS) k_finalize(const __grid_constant__ DevScene sc, const __grid_constant__ Wave w, uint32_t n,
                                                          float *__restrict__ profile) {
-    __shared__ float s_hist[FIN_SMEM_FLOATS];
-    const uint32_t C = sc.channels, W = sc.film_w, H = sc.film_h;
-    const uint32_t total_floats = C * W * H;
-    const bool use_smem = total_floats <= FIN_SMEM_FLOATS;
-    if (use_smem) {
+    __shared__ float s_hist[SMEM ? FIN_SMEM_FLOATS : 1];
+    const uint32_t C = sc.channels;
+    const uint32_t total_floats = C * sc.film_w * sc.film_h;
+    if (SMEM) {
         for (uint32_t i = threadIdx.x; i < total_floats; i += blockDim.x) s_hist[i] = 0.f;
         __syncthreads();
     }
-    float *dst = use_smem ? s_hist : profile;
-    const uint32_t gen = sc.integ.gen;
+    const uint32_t n_fixed = sc.integ.gen == BF_GEN_PHASE ? 3u : 5u;
     const uint32_t stride = gridDim.x * blockDim.x;
     const uint32_t n_round = (n + 31u) & ~31u;
     for (uint32_t l = blockIdx.x * blockDim.x + threadIdx.x; l < n_round; l += stride) {
-        int pixel = -1;          // destination pixel or -1
-        float val_a = 0.f;       // weighted value: channel Y (gen 3) or X = Y = Z (gen 1/2)
-        bool cnt_valid = false;  // alpha channel
-        uint32_t n_fixed = gen == BF_GEN_PHASE ? 3u : 5u;
-        int var_ch = -1;         // the single non-zero wrapper channel of this sample
-        float var_val = 0.f;
-        uint32_t var_rep = 1;    // gen 1 writes the value to 3 consecutive channels
-        if (l < n) {
-            uint32_t flags = w.flags[l];
-            float4 x1 = w.x1[l], x2 = w.x2[l];
-            Spec<S> thr, res, pend, wl;
-            SpecIO<S>::load(w, l, thr, res, pend, wl);
-            if ((flags & LANE_PENDING) && !w.occl[l]) {
-#pragma unroll
-                for (int k = 0; k < S; ++k) res.v[k] += pend.v[k];
-            }
-            Spec<S> weight = SpecIO<S>::load_weight(w, l, x2);
-            const bool valid = flags & LANE_VALID;
-            float posx, posy;
-            int off_x = 0, off_y = 0;
-            if (gen == BF_GEN_PHASE) {
-                const DevEndpoint &rx = *sc.rx;
-                // integrator.cpp:1588-1639
-                float tfx = 0.f, tfy = 0.f;
-                bool ran = true;
-                float wl0 = wl.v[0];
-                float phase = valid ? x1.y : 0.f;
-                if (rx.receive_type == BF_RECV_MIX_RESAMPLE) {
-                    tfx = x2.x - rx.adc_sampling_start;
-                    tfy = (float) fabs(freq_from_wl_d(sc.C.c, wl0) - (double) x2.y);
-                } else if (rx.receive_type == BF_RECV_RAW || rx.receive_type == BF_RECV_RAW_RESAMPLE) {
-                    tfx = x2.x - rx.adc_sampling_start;
-                    tfy = freq_from_wl(sc.C.c, wl0);
+        Splat sp; sp.pixel = -1; sp.val_a = 0.f; sp.cnt_valid = false; sp.var_ch = -1; sp.var_val = 0.f; sp.var_rep = 1;
+        if (l < n) sp = finalize_lane<S>(sc, w, l);
+        const int pixel = sp.pixel;
+        // do all the lanes of the warp that land in the film land in one pixel?  (1x1 films: every warp)
+        const uint32_t in_film = __ballot_sync(0xffffffffu, pixel >= 0);
+        if (in_film == 0) continue;
+        const int pixel0 = __shfl_sync(0xffffffffu, pixel, __ffs(in_film) - 1);
+        const bool one_pixel = __all_sync(0xffffffffu, pixel < 0 || pixel == pixel0) && (in_film & (in_film - 1));
+        if (one_pixel) {
+            float *dst = SMEM ? s_hist : profile;
+            const uint32_t nv = __popc(__ballot_sync(0xffffffffu, pixel >= 0 && sp.cnt_valid));
+            if (lane_id() == (uint32_t) (__ffs(in_film) - 1)) {
+                float *px = dst + (size_t) C * pixel;
+                if (SMEM) {
+                    atomicAdd(reinterpret_cast<uint32_t *>(px + n_fixed - 1), (uint32_t) __popc(in_film));
+                    if (nv) atomicAdd(reinterpret_cast<uint32_t *>(px + n_fixed - 2), nv);
                 } else {
-                    ran = false;
+                    atomicAdd(px + n_fixed - 1, (float) __popc(in_film));
+                    if (nv) atomicAdd(px + n_fixed - 2, (float) nv);
                 }
-                if (!ran) {
-#pragma unroll
-                    for (int k = 0; k < S; ++k) res.v[k] = 0.f;
-                    phase = 0.f;
-                }
-                // phase.cpp:117-124
-                float hs = hsum_spec<S>(res);
-                float ph = fmodf(phase, BF_TWO_PI);
-                ph += ph < 0.f ? BF_TWO_PI : 0.f;
-                if (ran && sc.integ.phase_bins > 0) {
-                    float bin_width = BF_TWO_PI / (float) sc.integ.phase_bins;
-                    float pv = (valid && ran) ? hs : 0.f;
-                    for (uint32_t k = 0; k < sc.integ.phase_bins; ++k) {
-                        float centre = (float) ((double) bin_width * ((double) k + 0.5));
-                        if (rect((ph - centre) / bin_width) > 0.f && pv != 0.f) { var_ch = 3 + (int) k; var_val = pv; }
-                    }
-                }
-                tfx *= (float) sc.adc.t_bins / sc.adc.t_bandwidth;
-                tfy *= (float) sc.adc.f_bins / sc.adc.f_bandwidth;
-                Spec<S> wres;
-#pragma unroll
-                for (int k = 0; k < S; ++k) wres.v[k] = fabsf(weight.v[k]) * res.v[k];
-                val_a = (valid && ran) ? hsum_spec<S>(wres) : 0.f;
-                cnt_valid = valid && ran;
-                posx = tfx; posy = tfy;
-                off_x = (int) sc.adc.window_offset_t; off_y = (int) sc.adc.window_offset_f;
-                if (w.records) {
-                    bf_sample_record *r = w.records + l;
-                    r->valid = (valid && ran) ? 1u : 0u; r->tf_t = tfx; r->tf_f = tfy; r->value = val_a;
-                    r->phase = phase; r->wavelength0 = wl0;
-                }
+            }
+            agg_add(dst, pixel >= 0 ? pixel * (int) C : -1, sp.val_a, n_fixed - 2);   // gen 3: Y; gen 1/2: X = Y = Z
+            agg_add(dst, (pixel >= 0 && sp.var_ch >= 0) ? pixel * (int) C + sp.var_ch : -1, sp.var_val, sp.var_rep);
+            continue;
+        }
+        if (pixel < 0) continue;
+        if (SMEM) {
+            float *px = s_hist + (size_t) C * pixel;
+            atomicAdd(reinterpret_cast<uint32_t *>(px + n_fixed - 1), 1u);
+            if (sp.cnt_valid) atomicAdd(reinterpret_cast<uint32_t *>(px + n_fixed - 2), 1u);
+            if (sp.val_a != 0.f)
+                for (uint32_t r = 0; r < n_fixed - 2; ++r) atomicAdd(px + r, sp.val_a);
+            if (sp.var_ch >= 0 && sp.var_val != 0.f)
+                for (uint32_t r = 0; r < sp.var_rep; ++r) atomicAdd(px + sp.var_ch + r, sp.var_val);
+        } else {
+            float *px = profile + (size_t) C * pixel;
+            if (C == 4 && n_fixed == 3) {
+                // gen 3, one phase bin: (Y, A, W, P0) is one aligned 16-byte record
+                atomicAdd(reinterpret_cast<float4 *>(px), make_float4(sp.val_a, sp.cnt_valid ? 1.f : 0.f, 1.f, sp.var_ch >= 0 ? sp.var_val : 0.f));
             } else {
-                // range.cpp:141-161 / time.cpp:118-153: bins from the UNWEIGHTED spectrum, first channel
-                float scalar = x1.w, r0 = res.v[0];
-                if (gen == BF_GEN_RANGE) {
-                    for (uint32_t i = 0; i < sc.integ.range_bins; ++i) {
-                        float lo = (float) i * sc.integ.dr, hi = (float) i * sc.integ.dr + sc.integ.dr;
-                        if (scalar >= lo && scalar < hi && r0 != 0.f) { var_ch = 5 + (int) i; var_val = r0; }
-                    }
-                } else {
-                    const float dt = 0.5e-9f;
-                    for (int i = 0; i < 50; ++i) {
-                        float lo = (float) i * dt, hi = (float) i * dt + dt;
-                        if (scalar >= lo && scalar < hi && r0 != 0.f) { var_ch = 5 + 3 * i; var_val = r0; var_rep = 3; }
-                    }
-                }
-                Spec<S> wres;
-#pragma unroll
-                for (int k = 0; k < S; ++k) wres.v[k] = weight.v[k] * res.v[k];
-                // mono: xyz = value broadcast; spectral: the CIE matching functions vanish at radar wavelengths
-                float x = S == 1 ? wres.v[0] : 0.f;
-                val_a = x; cnt_valid = valid;
-                posx = x2.x; posy = x2.y;
-                if (w.records) {
-                    bf_sample_record *r = w.records + l;
-                    r->valid = valid ? 1u : 0u; r->tf_t = posx; r->tf_f = posy; r->value = r0; r->phase = scalar; r->wavelength0 = wl.v[0];
-                }
+                atomicAdd(px + n_fixed - 1, 1.f);
+                if (sp.cnt_valid) atomicAdd(px + n_fixed - 2, 1.f);
+                if (sp.val_a != 0.f)
+                    for (uint32_t r = 0; r < n_fixed - 2; ++r) atomicAdd(px + r, sp.val_a);
+                if (sp.var_ch >= 0 && sp.var_val != 0.f)
+                    for (uint32_t r = 0; r < sp.var_rep; ++r) atomicAdd(px + sp.var_ch + r, sp.var_val);
             }
-            // SignalBlock::put, box filter of radius 0.5 (signalblock.cpp:162-169)
-            float px = posx - ((float) off_x - 0.f + .5f), py = posy - ((float) off_y - 0.f + .5f);
-            float cx = ceilf(px - .5f), cy = ceilf(py - .5f);
-            if (cx >= 0.f && cy >= 0.f && cx < (float) W && cy < (float) H) pixel = (int) ((uint32_t) cy * W + (uint32_t) cx);
         }
-        // Count channels (alpha, weight) are integers: one MATCH.ANY groups the lanes by pixel and the group leader
-        // adds the population counts.  Value channels go through agg_add.
-        const uint32_t peers = __match_any_sync(0xffffffffu, pixel);
-        const uint32_t valid_mask = __ballot_sync(0xffffffffu, cnt_valid);
-        if (pixel >= 0 && lane_id() == (uint32_t) (__ffs(peers) - 1)) {
-            float *px = dst + (size_t) C * pixel;
-            atomicAdd(px + n_fixed - 1, (float) __popc(peers));
-            const uint32_t nv = __popc(peers & valid_mask);
-            if (nv) atomicAdd(px + n_fixed - 2, (float) nv);
-        }
-        agg_add(dst, pixel >= 0 ? pixel * (int) C : -1, val_a, n_fixed - 2);   // gen 3: Y; gen 1/2: X = Y = Z
-        agg_add(dst, (pixel >= 0 && var_ch >= 0) ? pixel * (int) C + var_ch : -1, var_val, var_rep);
     }
-    if (use_smem) {
+    if (SMEM) {
         __syncthreads();
         for (uint32_t i = threadIdx.x; i < total_floats; i += blockDim.x) {
-            float v = s_hist[i];
+            const uint32_t ch = i % C;
+            const bool is_count = ch == n_fixed - 1 || ch == n_fixed - 2;
+            const float v = is_count ? (float) __float_as_uint(s_hist[i]) : s_hist[i];
             if (v != 0.f) atomicAdd(profile + i, v);
         }
     }
@@ -487,19 +604,34 @@ int launch_trace_shadow(const DevScene &sc, const Wave &w, const uint32_t *queue
     k_trace<true><<<trace_grid(cfg), TRACE_THREADS, 0, cfg.stream>>>(sc, io);
     return 1;
 }
+template <int S>
+static int launch_shade_s(const DevScene &sc, const Wave &w, uint32_t depth, const uint32_t *hit_counts, int grid, uint32_t *next_queue,
+                          uint32_t *ctr_block, const LaunchCfg &cfg) {
+    // Specialised kernels for the radar configuration (gen-3 integrator, wigner transmitters): one launch per material class.
+    if (sc.integ.gen == BF_GEN_PHASE && sc.hint_tx_kind == BF_TX_WIGNER) {
+        k_shade<S, BF_GEN_PHASE, BF_TX_WIGNER, BF_BSDF_DIFFUSE, 0><<<grid, 128, 0, cfg.stream>>>(sc, w, depth, hit_counts, next_queue, ctr_block);
+        if (sc.hint_cls1_bsdf == BF_BSDF_ROUGHCONDUCTOR)
+            k_shade<S, BF_GEN_PHASE, BF_TX_WIGNER, BF_BSDF_ROUGHCONDUCTOR, 1><<<grid, 128, 0, cfg.stream>>>(sc, w, depth, hit_counts, next_queue, ctr_block);
+        else
+            k_shade<S, BF_GEN_PHASE, BF_TX_WIGNER, -1, 1><<<grid, 128, 0, cfg.stream>>>(sc, w, depth, hit_counts, next_queue, ctr_block);
+        return 2;
+    }
+    k_shade<S, -1, -1, -1, 2><<<grid, 128, 0, cfg.stream>>>(sc, w, depth, hit_counts, next_queue, ctr_block);
+    return 1;
+}
 int launch_shade(const DevScene &sc, const Wave &w, uint32_t depth, const uint32_t *hit_counts, uint32_t n_bound,
                  uint32_t *next_queue, uint32_t *ctr_block, const LaunchCfg &cfg) {
     int grid = (int) min((uint32_t) (cfg.sm_count * 8), (n_bound + 64u + 127u) / 128u);   // n_bound = upper bound of the queue lengths
     if (grid < 1) grid = 1;
-    if (sc.S == 1) k_shade<1><<<grid, 128, 0, cfg.stream>>>(sc, w, depth, hit_counts, next_queue, ctr_block);
-    else k_shade<4><<<grid, 128, 0, cfg.stream>>>(sc, w, depth, hit_counts, next_queue, ctr_block);
-    return 1;
+    return sc.S == 1 ? launch_shade_s<1>(sc, w, depth, hit_counts, grid, next_queue, ctr_block, cfg)
+                     : launch_shade_s<4>(sc, w, depth, hit_counts, grid, next_queue, ctr_block, cfg);
 }
 int launch_finalize(const DevScene &sc, const Wave &w, uint32_t n, float *profile, const LaunchCfg &cfg) {
     if (n == 0) return 0;
     int grid = (int) min((uint32_t) (cfg.sm_count * 4), (n + FIN_THREADS - 1) / FIN_THREADS);
-    if (sc.S == 1) k_finalize<1><<<grid, FIN_THREADS, 0, cfg.stream>>>(sc, w, n, profile);
-    else k_finalize<4><<<grid, FIN_THREADS, 0, cfg.stream>>>(sc, w, n, profile);
+    const bool smem = sc.channels * sc.film_w * sc.film_h <= FIN_SMEM_FLOATS;
+    if (sc.S == 1) { if (smem) k_finalize<1, true><<<grid, FIN_THREADS, 0, cfg.stream>>>(sc, w, n, profile); else k_finalize<1, false><<<grid, FIN_THREADS, 0, cfg.stream>>>(sc, w, n, profile); }
+    else { if (smem) k_finalize<4, true><<<grid, FIN_THREADS, 0, cfg.stream>>>(sc, w, n, profile); else k_finalize<4, false><<<grid, FIN_THREADS, 0, cfg.stream>>>(sc, w, n, profile); }
     return 1;
 }
 int launch_trace_rays(const DevScene &sc, const float4 *ray_o, const float4 *ray_d, uint32_t n, float4 *hit, uint32_t *occl,

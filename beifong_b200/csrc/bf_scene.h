@@ -25,6 +25,7 @@ struct DevRect {
     float wid_x, wid_y;     // |s|, |t|
     uint32_t shape;         // scene shape id
     uint32_t pad;
+    float box_lo[3], box_hi[3];   // world-space bounding box, padded: the traversal kernel's conservative pre-test
 };
 struct DevShape {
     uint32_t type;          // 0 mesh, 1 rectangle
@@ -81,6 +82,9 @@ struct DevScene {
     bf_integrator_desc integ;
     uint32_t film_w, film_h, channels;
     uint32_t rx_needs_aperture;
+    // what the whole scene has in common, for the specialised shade kernels: the kind shared by every transmitter and by
+    // every BSDF (front and back) of material class 1, or -1
+    int32_t hint_tx_kind, hint_cls1_bsdf;
     double phase_denom;        // (lambda_max - lambda_min) / 2 * 1e-9 evaluated like ray.h:92
 };
 

@@ -83,19 +83,40 @@ struct TraceLane {
 
 // Ray setup + analytic rectangles (rectangle.cpp:229-263).  Returns false when the query is already
 // decided (any-hit occluded by a rectangle, or no BVH).
+#define RECT_SM_FLOATS 19   // per rectangle in shared memory: 12 to_object, 1 shape id, 6 padded world box
+
 template <bool ANY_HIT>
 __device__ __forceinline__ bool trace_begin(const DevScene &sc, const float *s_rect, TraceLane &L) {
     L.best.t = L.maxt; L.best.u = 0.f; L.best.v = 0.f; L.best.slot = BF_NONE; L.best.shape = BF_NONE; L.best.prim = BF_NONE;
     L.occluded = false;
     const V3 o = L.o, d = L.d;
+    const float tiny = 1e-30f;
+    L.idx = __fdividef(1.f, fabsf(d.x) > tiny ? d.x : copysignf(tiny, d.x));
+    L.idy = __fdividef(1.f, fabsf(d.y) > tiny ? d.y : copysignf(tiny, d.y));
+    L.idz = __fdividef(1.f, fabsf(d.z) > tiny ? d.z : copysignf(tiny, d.z));
+    const bool quick = L.mint > 0.f;
+    const float t_lo = L.mint * 0.999f, t_hi = L.maxt * 1.001f;
     for (uint32_t r = 0; r < sc.n_rects; ++r) {
         const float *m = s_rect + 12 * r;
+        float oz = fmadd(m[10], o.z, fmadd(m[9], o.y, fmadd(m[8], o.x, m[11])));
+        float dz = fmadd(m[10], d.z, fmadd(m[9], d.y, m[8] * d.x));
+        // Conservative rejections, so that a warp skips the exact test of a rectangle none of its rays can reach:
+        // (1) t = -oz / dz is negative, or smaller than mint in magnitude (rays leaving the rectangle they start on);
+        // (2) the ray misses the rectangle's padded world-space box.
+        if (quick && (oz * dz > 0.f || fabsf(oz) < 0.999f * L.mint * fabsf(dz))) continue;
+        {
+            const float *bx = s_rect + 13 * BF_MAX_RECTS + 6 * r;
+            float x0 = (bx[0] - o.x) * L.idx, x1 = (bx[3] - o.x) * L.idx;
+            float y0 = (bx[1] - o.y) * L.idy, y1 = (bx[4] - o.y) * L.idy;
+            float z0 = (bx[2] - o.z) * L.idz, z1 = (bx[5] - o.z) * L.idz;
+            float t_in = fmaxf(fmaxf(fminf(x0, x1), fminf(y0, y1)), fmaxf(fminf(z0, z1), t_lo));
+            float t_out = fminf(fminf(fmaxf(x0, x1), fmaxf(y0, y1)), fminf(fmaxf(z0, z1), t_hi));
+            if (t_in > t_out * 1.001f) continue;
+        }
         float ox = fmadd(m[2], o.z, fmadd(m[1], o.y, fmadd(m[0], o.x, m[3])));
         float oy = fmadd(m[6], o.z, fmadd(m[5], o.y, fmadd(m[4], o.x, m[7])));
-        float oz = fmadd(m[10], o.z, fmadd(m[9], o.y, fmadd(m[8], o.x, m[11])));
         float dx = fmadd(m[2], d.z, fmadd(m[1], d.y, m[0] * d.x));
         float dy = fmadd(m[6], d.z, fmadd(m[5], d.y, m[4] * d.x));
-        float dz = fmadd(m[10], d.z, fmadd(m[9], d.y, m[8] * d.x));
         float t = -oz * rcp(dz);
         float lx = fmadd(dx, t, ox), ly = fmadd(dy, t, oy);
         bool hit = t >= L.mint && t <= L.maxt && fabsf(lx) <= 1.f && fabsf(ly) <= 1.f;
@@ -107,10 +128,6 @@ __device__ __forceinline__ bool trace_begin(const DevScene &sc, const float *s_r
         }
     }
     if (sc.n_nodes == 0) return false;
-    const float tiny = 1e-30f;
-    L.idx = __fdividef(1.f, fabsf(d.x) > tiny ? d.x : copysignf(tiny, d.x));
-    L.idy = __fdividef(1.f, fabsf(d.y) > tiny ? d.y : copysignf(tiny, d.y));
-    L.idz = __fdividef(1.f, fabsf(d.z) > tiny ? d.z : copysignf(tiny, d.z));
     L.octinv = (d.x < 0.f ? 0u : 4u) | (d.y < 0.f ? 0u : 2u) | (d.z < 0.f ? 0u : 1u);
     L.ngroup = make_uint2(0u, 0x80000000u);
     L.sp = 0;
@@ -215,6 +232,10 @@ __device__ __forceinline__ void stage_rects(const DevScene &sc, float *s_rect) {
     }
     for (uint32_t r = threadIdx.x; r < sc.n_rects; r += blockDim.x)
         s_rect[12 * BF_MAX_RECTS + r] = __uint_as_float(sc.rects[r].shape);
+    for (uint32_t i = threadIdx.x; i < sc.n_rects * 6u; i += blockDim.x) {
+        uint32_t r = i / 6u, k = i % 6u;
+        s_rect[13 * BF_MAX_RECTS + i] = k < 3u ? sc.rects[r].box_lo[k] : sc.rects[r].box_hi[k - 3u];
+    }
     __syncthreads();
 }
 
@@ -243,7 +264,7 @@ struct TraceIO {
 // done for hit-queue pushes: the slot reservation is issued at one commit point and consumed at the next.
 template <bool ANY_HIT>
 __global__ void __launch_bounds__(TRACE_THREADS, 8) k_trace(const __grid_constant__ DevScene sc, const __grid_constant__ TraceIO io) {
-    __shared__ float s_rect[13 * BF_MAX_RECTS];
+    __shared__ float s_rect[RECT_SM_FLOATS * BF_MAX_RECTS];
     __shared__ uint2 s_stack[TRACE_SM_STACK * TRACE_THREADS];
     uint2 l_stack[TRACE_LOCAL_STACK];
     stage_rects(sc, s_rect);
