@@ -12,6 +12,15 @@
 
 namespace bf {
 
+// atomicAdd with a returned value, issued by ONE elected lane: written as PTX so that the compiler does not wrap it in its
+// own warp aggregation (elect + SHFL broadcast of the result right behind the atomic, which makes the issuing warp wait
+// out the ~1 us round trip on the spot; the callers consume the result one loop iteration later instead).
+__device__ __forceinline__ uint32_t atomic_add_async(uint32_t *p, uint32_t v) {
+    uint32_t old;
+    asm volatile("atom.global.add.u32 %0, [%1], %2;" : "=r"(old) : "l"(p), "r"(v) : "memory");
+    return old;
+}
+
 template <int S> struct Spec {
     float v[S];
     BF_D Spec() {

@@ -46,8 +46,8 @@ struct DeferredPush2 {
     __device__ __forceinline__ void reserve(bool pred_a, uint32_t *counter_a, bool pred_b, uint32_t *counter_b, uint32_t v) {
         const uint32_t mask_a = __ballot_sync(0xffffffffu, pred_a), mask_b = __ballot_sync(0xffffffffu, pred_b);
         const uint32_t lane = lane_id(), lt = (1u << lane) - 1u;
-        if (mask_a && lane == (uint32_t) (__ffs(mask_a) - 1)) base_a = atomicAdd(counter_a, (uint32_t) __popc(mask_a));
-        if (mask_b && lane == (uint32_t) (__ffs(mask_b) - 1)) base_b = atomicAdd(counter_b, (uint32_t) __popc(mask_b));
+        if (mask_a && lane == (uint32_t) (__ffs(mask_a) - 1)) base_a = atomic_add_async(counter_a, (uint32_t) __popc(mask_a));
+        if (mask_b && lane == (uint32_t) (__ffs(mask_b) - 1)) base_b = atomic_add_async(counter_b, (uint32_t) __popc(mask_b));
         meta = (pred_a ? 1u : 0u) | (pred_b ? 2u : 0u) | ((uint32_t) __popc(mask_a & lt) << 8) | ((uint32_t) __popc(mask_b & lt) << 16);
         value = v;
     }

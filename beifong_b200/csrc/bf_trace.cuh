@@ -282,7 +282,7 @@ __global__ void __launch_bounds__(TRACE_THREADS, 8) k_trace(const __grid_constan
     while (dynamic && chunk < 256 && chunk * 16 * n_warps <= n - static_total) chunk *= 2;
     uint32_t c_next = (blockIdx.x * (TRACE_THREADS / 32) + (threadIdx.x >> 5)) * 32u, c_end = c_next + 32u;   // warp-uniform
     uint32_t claim = 0xffffffffu;                   // lane 0: start of the chunk claimed ahead
-    if (dynamic && lane == 0) claim = static_total + atomicAdd(io.work_cursor, chunk);
+    if (dynamic && lane == 0) claim = static_total + atomic_add_async(io.work_cursor, chunk);
     bool out_of_work = c_next >= n;
 
     // deferred hit-queue push
@@ -336,7 +336,7 @@ __global__ void __launch_bounds__(TRACE_THREADS, 8) k_trace(const __grid_constan
             for (int c = 0; c < 2; ++c) {
                 uint32_t m = __ballot_sync(0xffffffffu, push && cls == (uint32_t) c);
                 if (m) {
-                    if (lane == (uint32_t) (__ffs(m) - 1)) pend_base = atomicAdd(io.hit_count[c], (uint32_t) __popc(m));   // consumed next round
+                    if (lane == (uint32_t) (__ffs(m) - 1)) pend_base = atomic_add_async(io.hit_count[c], (uint32_t) __popc(m));   // consumed next round
                     if ((m >> lane) & 1u) { pend_meta = 0x80000000u | ((uint32_t) c << 30); pend_l = l; }
                 }
             }
@@ -350,7 +350,7 @@ __global__ void __launch_bounds__(TRACE_THREADS, 8) k_trace(const __grid_constan
             if (!out_of_work && cnt > avail) {      // warp-uniform: open the next chunk (chunk >= 32 >= cnt - avail)
                 const uint32_t nxt = __shfl_sync(0xffffffffu, claim, 0);
                 if (nxt < n) {
-                    if (lane == 0) claim = static_total + atomicAdd(io.work_cursor, chunk);
+                    if (lane == 0) claim = static_total + atomic_add_async(io.work_cursor, chunk);
                     if (rank >= avail) i = nxt + (rank - avail);
                     c_next = nxt + (cnt - avail); c_end = nxt + chunk;
                 } else {
