@@ -696,7 +696,7 @@ static int ensure_slot(bf_scene *s, size_t index, uint32_t lanes, bool records) 
     BF_CUDA(A((void **) &w.flags, n * 4));
     BF_CUDA(A((void **) &w.queue[0], n * 4)); BF_CUDA(A((void **) &w.queue_h, n * 4)); BF_CUDA(A((void **) &w.queue_h2, n * 4)); BF_CUDA(A((void **) &w.queue_s, n * 4));
     BF_CUDA(A((void **) &w.counters, (size_t) BF_CTR_STRIDE * (BF_MAX_BOUNCES + 2) * 4));
-    if (records) BF_CUDA(A((void **) &w.records, n * sizeof(bf_sample_record)));
+    if (records) { BF_CUDA(A((void **) &w.records, n * sizeof(bf_sample_record))); BF_CUDA(A((void **) &w.sample_of, n * 4)); }
     w.capacity = lanes;
     w.totals = s->d_totals.p;
     sl.capacity = lanes;
@@ -715,7 +715,10 @@ static cudaEvent_t next_trace_event(bf_scene *s, int kind) {
 static int run_wave(bf_scene *s, WaveSlot &sl, uint64_t seed, uint64_t first, uint32_t n, float *profile, bool with_records) {
     const DevScene &sc = s->dev;
     Wave w = sl.wave;
-    if (!with_records) w.records = nullptr;
+    if (!with_records) { w.records = nullptr; w.sample_of = nullptr; }
+    // BF_FUSED_PRIMARY=0 selects the unfused raygen + trace pair (lanes = samples), kept for A/B measurements
+    static const bool fused = env_u32("BF_FUSED_PRIMARY", 1, 0, 1) != 0;
+    if (!fused) w.sample_of = nullptr;
     LaunchCfg cfg; cfg.stream = sl.stream; cfg.sm_count = s->sm_count;
     uint32_t *ctr = w.counters;
     const bool unbounded = sc.integ.max_depth < 0 || sc.integ.max_depth > 64;
@@ -729,8 +732,14 @@ static int run_wave(bf_scene *s, WaveSlot &sl, uint64_t seed, uint64_t first, ui
         launches += fn();
         if (timing) { cudaEventRecord(next_trace_event(s, kind), sl.stream); }
     };
-    timed(BF_K_RAYGEN, [&] { return launch_raygen(sc, w, seed, first, n, cfg); });
-    timed(BF_K_TRACE_CLOSEST, [&] { return launch_trace_closest(sc, w, nullptr, nullptr, n, 1, ctr + 4, ctr + 2, cfg); });
+    if (fused) {
+        w.n_lanes = ctr + 6;
+        timed(BF_K_TRACE_CLOSEST, [&] { return launch_primary(sc, w, seed, first, n, ctr + 4, ctr + 2, profile, cfg); });
+    } else {
+        w.n_lanes = nullptr;
+        timed(BF_K_RAYGEN, [&] { return launch_raygen(sc, w, seed, first, n, cfg); });
+        timed(BF_K_TRACE_CLOSEST, [&] { return launch_trace_closest(sc, w, nullptr, nullptr, n, 1, ctr + 4, ctr + 2, cfg); });
+    }
     for (uint32_t depth = 1; depth <= max_depth; ++depth) {
         uint32_t *blk = ctr + (size_t) BF_CTR_STRIDE * depth, *prev = ctr + (size_t) BF_CTR_STRIDE * (depth - 1);
         timed(BF_K_SHADE, [&] { return launch_shade(sc, w, depth, prev + 4, n, w.queue[0], blk, cfg); });

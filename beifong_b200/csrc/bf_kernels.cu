@@ -65,6 +65,8 @@ struct DeferredPush2 {
     }
 };
 
+__device__ __forceinline__ bf_sample_record *rec_of(const Wave &w, uint32_t l) { return w.records + (w.sample_of ? w.sample_of[l] : l); }
+
 template <int S> struct SpecIO;
 template <> struct SpecIO<1> {
     static __device__ __forceinline__ void load(const Wave &w, uint32_t l, Spec<1> &thr, Spec<1> &res, Spec<1> &pend, Spec<1> &wl) {
@@ -92,51 +94,251 @@ template <> struct SpecIO<4> {
 // =========================================================================================================
 // raygen
 // =========================================================================================================
-template <int S>
-__global__ void __launch_bounds__(256) k_raygen(const __grid_constant__ DevScene sc, const __grid_constant__ Wave w, uint64_t seed, uint64_t first_sample, uint32_t n) {
-    uint32_t l = blockIdx.x * blockDim.x + threadIdx.x;
-    if (l >= n) return;
-    uint64_t idx = first_sample + l;
-    PCG32 rng;
-    rng.seed(sample_tea_64_wide(seed, idx), sample_tea_64_wide(idx, seed));   // sampler.cpp:89-92
+// One out-of-line copy of the TEA mixer (called twice per sample): halves its share of the primary kernel's code footprint.
+__device__ __noinline__ uint64_t tea64_shared(uint64_t v0, uint64_t v1) { return sample_tea_64_wide(v0, v1); }
 
+// What raygen produces for one sample: the receiver ray and the per-sample state of the path.
+template <int S> struct PrimaryState {
+    RayGen ray;
+    PCG32 rng;
+    Spec<S> wl, weight;
+    float time;          // ray time
+    float4 x2;           // gen 3: (sample time, f_rx, 0, weight[S == 1]); gen 1/2: (film position, 0, weight)
+};
+
+// Head of receive_sample (integrator.cpp:1544-1569) / render_sample (:263-279) for sample `idx`.
+template <int S>
+__device__ __forceinline__ void raygen_sample(const DevScene &sc, uint64_t seed, uint64_t idx, PrimaryState<S> &ps) {
+    PCG32 rng;
+    rng.seed(tea64_shared(seed, idx), tea64_shared(idx, seed));   // sampler.cpp:89-92
     const DevEndpoint &rx = *sc.rx;
     V2 position_sample; position_sample.x = rng.next_float32(); position_sample.y = rng.next_float32();
     V2 aperture_sample(.5f, .5f);
     if (sc.rx_needs_aperture) { aperture_sample.x = rng.next_float32(); aperture_sample.y = rng.next_float32(); }
     float time;
     float4 x2 = make_float4(0.f, 0.f, 0.f, 0.f);
-    RayGen ray; Spec<S> wl, weight;
     if (sc.integ.gen == BF_GEN_PHASE) {
         // integrator.cpp:1544-1569
         time = rx.adc_sampling_start;
         if (rx.adc_sampling_time > 0.f) time += rng.next_float32() * rx.adc_sampling_time; else time = 0.f;
         float wavelength_sample = rng.next_float32();
-        rx_sample_ray<S>(sc, time, wavelength_sample, position_sample, aperture_sample, ray, wl, weight);
+        rx_sample_ray<S>(sc, time, wavelength_sample, position_sample, aperture_sample, ps.ray, ps.wl, ps.weight);
         x2.x = time;
-        x2.y = freq_from_wl(sc.C.c, wl.v[0]);   // f_rx of mix_resample (integrator.cpp:1603)
+        x2.y = freq_from_wl(sc.C.c, ps.wl.v[0]);   // f_rx of mix_resample (integrator.cpp:1603)
     } else {
         // integrator.cpp:263-279 (1x1 film, pos = 0)
         time = rx.shutter_open;
         if (rx.shutter_open_time > 0.f) time += rng.next_float32() * rx.shutter_open_time;
         float wavelength_sample = rng.next_float32();
         V2 adjusted((position_sample.x - 0.f) / (float) sc.film_w, (position_sample.y - 0.f) / (float) sc.film_h);
-        rx_sample_ray<S>(sc, time, wavelength_sample, adjusted, aperture_sample, ray, wl, weight);
+        rx_sample_ray<S>(sc, time, wavelength_sample, adjusted, aperture_sample, ps.ray, ps.wl, ps.weight);
         x2.x = position_sample.x; x2.y = position_sample.y;
     }
-    SpecIO<S>::store_weight(w, l, weight, x2);
-    w.ray_o[l] = make_float4(ray.o.x, ray.o.y, ray.o.z, ray.mint);
-    w.ray_d[l] = make_float4(ray.d.x, ray.d.y, ray.d.z, ray.maxt);
-    w.rng[l] = make_ulonglong2(rng.state, rng.inc);
-    w.x1[l] = make_float4(time, 0.f, 0.f, 0.f);
+    if (S == 1) x2.w = ps.weight.v[0];
+    ps.rng = rng; ps.time = time; ps.x2 = x2;
+}
+
+// Writes the state of a freshly generated sample into lane l.
+template <int S>
+__device__ __forceinline__ void store_primary(const Wave &w, uint32_t l, const PrimaryState<S> &ps) {
+    float4 x2 = ps.x2;
+    SpecIO<S>::store_weight(w, l, ps.weight, x2);
+    w.ray_o[l] = make_float4(ps.ray.o.x, ps.ray.o.y, ps.ray.o.z, ps.ray.mint);
+    w.ray_d[l] = make_float4(ps.ray.d.x, ps.ray.d.y, ps.ray.d.z, ps.ray.maxt);
+    w.rng[l] = make_ulonglong2(ps.rng.state, ps.rng.inc);
+    w.x1[l] = make_float4(ps.time, 0.f, 0.f, 0.f);
     w.x2[l] = x2;
-    SpecIO<S>::store(w, l, Spec<S>(1.f), Spec<S>(0.f), Spec<S>(0.f), wl);
+    SpecIO<S>::store(w, l, Spec<S>(1.f), Spec<S>(0.f), Spec<S>(0.f), ps.wl);
     w.flags[l] = LANE_ACTIVE;
-    if (w.records) {
-        bf_sample_record r;
-        r.first_shape = BF_NONE; r.first_prim = BF_NONE; r.first_t = bf_inf(); r.valid = 0; r.tf_t = 0.f; r.tf_f = 0.f;
-        r.value = 0.f; r.phase = 0.f; r.n_closest = 1; r.n_shadow = 0; r.wavelength0 = wl.v[0]; r.depth = 0;
-        w.records[l] = r;
+}
+__device__ __forceinline__ void init_record(bf_sample_record *rp, float wavelength0) {
+    bf_sample_record r;
+    r.first_shape = BF_NONE; r.first_prim = BF_NONE; r.first_t = bf_inf(); r.valid = 0; r.tf_t = 0.f; r.tf_f = 0.f;
+    r.value = 0.f; r.phase = 0.f; r.n_closest = 1; r.n_shadow = 0; r.wavelength0 = wavelength0; r.depth = 0;
+    *rp = r;
+}
+
+template <int S>
+__global__ void __launch_bounds__(256) k_raygen(const __grid_constant__ DevScene sc, const __grid_constant__ Wave w, uint64_t seed, uint64_t first_sample, uint32_t n) {
+    uint32_t l = blockIdx.x * blockDim.x + threadIdx.x;
+    if (l >= n) return;
+    PrimaryState<S> ps;
+    raygen_sample<S>(sc, seed, first_sample + l, ps);
+    store_primary<S>(w, l, ps);
+    if (w.records) init_record(w.records + l, ps.wl.v[0]);
+}
+
+// Where a sample lands on the film.  gen 3: (time, frequency) -> fractional ADC bin (integrator.cpp:1588-1639), `ran` is
+// false for receive types the reference leaves unhandled; gen 1/2: the film position sample.
+__device__ __forceinline__ void sample_position(const DevScene &sc, float4 x2, float wl0, float &posx, float &posy, bool &ran, int &off_x, int &off_y) {
+    ran = true; off_x = 0; off_y = 0;
+    if (sc.integ.gen == BF_GEN_PHASE) {
+        const DevEndpoint &rx = *sc.rx;
+        float tfx = 0.f, tfy = 0.f;
+        if (rx.receive_type == BF_RECV_MIX_RESAMPLE) {
+            tfx = x2.x - rx.adc_sampling_start;
+            tfy = (float) fabs(freq_from_wl_d(sc.C.c, wl0) - (double) x2.y);
+        } else if (rx.receive_type == BF_RECV_RAW || rx.receive_type == BF_RECV_RAW_RESAMPLE) {
+            tfx = x2.x - rx.adc_sampling_start;
+            tfy = freq_from_wl(sc.C.c, wl0);
+        } else {
+            ran = false;
+        }
+        tfx *= (float) sc.adc.t_bins / sc.adc.t_bandwidth;
+        tfy *= (float) sc.adc.f_bins / sc.adc.f_bandwidth;
+        posx = tfx; posy = tfy;
+        off_x = (int) sc.adc.window_offset_t; off_y = (int) sc.adc.window_offset_f;
+    } else {
+        posx = x2.x; posy = x2.y;
+    }
+}
+// SignalBlock::put, box filter of radius 0.5 (signalblock.cpp:162-169): destination pixel or -1
+__device__ __forceinline__ int pixel_of(const DevScene &sc, float posx, float posy, int off_x, int off_y) {
+    float px = posx - ((float) off_x - 0.f + .5f), py = posy - ((float) off_y - 0.f + .5f);
+    float cx = ceilf(px - .5f), cy = ceilf(py - .5f);
+    if (cx >= 0.f && cy >= 0.f && cx < (float) sc.film_w && cy < (float) sc.film_h) return (int) ((uint32_t) cy * sc.film_w + (uint32_t) cx);
+    return -1;
+}
+
+// =========================================================================================================
+// primary: raygen + first closest-hit query + compaction, fused
+// =========================================================================================================
+// One persistent kernel generates the receiver rays and traverses them (the loop of k_trace<false>, bf_trace.cuh).  A ray
+// that leaves the scene ends its sample on the spot: all it contributes is a count in the weight channel of its bin
+// (SignalBlock::put of a zero value), so nothing of it is ever written to HBM.  A ray that hits gets the next free lane:
+// the wave state holds the surviving samples only, densely packed, and every later kernel reads and writes it coalesced.
+#define PRIM_MISS_PIXELS 2048
+
+struct PrimaryIO {
+    uint64_t seed, first_sample;
+    uint32_t n;
+    uint32_t *work_cursor;
+    uint32_t *hit_count;         // [2]: lengths of the two material-class queues
+    uint32_t *n_lanes;           // number of lanes handed out
+    unsigned long long *total;   // closest queries traced
+    float *profile;
+};
+
+#ifndef BF_PRIMARY_MIN_BLOCKS
+#define BF_PRIMARY_MIN_BLOCKS 8
+#endif
+template <int S>
+__global__ void __launch_bounds__(TRACE_THREADS, BF_PRIMARY_MIN_BLOCKS) k_primary(const __grid_constant__ DevScene sc, const __grid_constant__ Wave w, const __grid_constant__ PrimaryIO io) {
+    __shared__ float s_rect[RECT_SM_FLOATS * BF_MAX_RECTS];
+    __shared__ uint2 s_stack[TRACE_SM_STACK * TRACE_THREADS];
+    __shared__ uint32_t s_miss[PRIM_MISS_PIXELS];
+    uint2 l_stack[TRACE_LOCAL_STACK];
+    const uint32_t n_pixels = sc.film_w * sc.film_h, C = sc.channels;
+    const bool miss_smem = n_pixels <= PRIM_MISS_PIXELS;
+    const uint32_t w_channel = (sc.integ.gen == BF_GEN_PHASE ? 3u : 5u) - 1u;
+    if (miss_smem) for (uint32_t i = threadIdx.x; i < n_pixels; i += blockDim.x) s_miss[i] = 0u;
+    stage_rects(sc, s_rect);
+    const uint32_t n = io.n;
+    if (io.total && blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(io.total, (unsigned long long) n);
+    const uint32_t lane = threadIdx.x & 31u, lt_mask = (1u << lane) - 1u;
+
+    // work distribution as in k_trace: a static first batch, then chunks claimed one ahead
+    const uint32_t n_warps = gridDim.x * (TRACE_THREADS / 32);
+    const uint32_t static_total = n_warps * 32u;
+    const bool dynamic = n > static_total;
+    uint32_t chunk = 32;
+    while (dynamic && chunk < 256 && chunk * 16 * n_warps <= n - static_total) chunk *= 2;
+    uint32_t c_next = (blockIdx.x * (TRACE_THREADS / 32) + (threadIdx.x >> 5)) * 32u, c_end = c_next + 32u;   // warp-uniform
+    uint32_t claim = 0xffffffffu;
+    if (dynamic && lane == 0) claim = static_total + atomic_add_async(io.work_cursor, chunk);
+    bool out_of_work = c_next >= n;
+
+    enum { EMPTY = 0, BUSY = 1, FINISHED = 2, EXHAUSTED = 3 };
+    int state = EMPTY;
+    uint32_t smp = 0;            // sample offset in the wave
+    TraceLane L;
+    PrimaryState<S> ps;
+    while (true) {
+        // ---- commit finished samples (warp converged here) ----
+        const bool fin = state == FINISHED;
+        const bool hit = fin && L.best.slot != BF_NONE;
+        if (fin && !hit) {
+            float posx, posy; bool ran; int off_x, off_y;
+            sample_position(sc, ps.x2, ps.wl.v[0], posx, posy, ran, off_x, off_y);
+            const int pixel = pixel_of(sc, posx, posy, off_x, off_y);
+            if (pixel >= 0) {
+                if (miss_smem) atomicAdd(&s_miss[pixel], 1u);
+                else atomicAdd(io.profile + (size_t) C * pixel + w_channel, 1.f);
+            }
+            if (w.records) {
+                bf_sample_record *r = w.records + smp;
+                init_record(r, ps.wl.v[0]);
+                r->depth = 1; r->tf_t = posx; r->tf_f = posy;
+            }
+        }
+        const uint32_t hits = __ballot_sync(0xffffffffu, hit);
+        if (hits) {
+            const uint32_t cls = hit ? sc.shapes[L.best.shape].mat_class : 0u;
+            const uint32_t m0 = __ballot_sync(0xffffffffu, hit && cls == 0u), m1 = hits & ~m0;
+            // three reservations in flight together (lane slots + the two class queues), one wait
+            uint32_t base = 0;
+            if (lane == 0) base = atomic_add_async(io.n_lanes, (uint32_t) __popc(hits));
+            else if (lane == 1 && m0) base = atomic_add_async(io.hit_count + 0, (uint32_t) __popc(m0));
+            else if (lane == 2 && m1) base = atomic_add_async(io.hit_count + 1, (uint32_t) __popc(m1));
+            const uint32_t base_l = __shfl_sync(0xffffffffu, base, 0), base_0 = __shfl_sync(0xffffffffu, base, 1), base_1 = __shfl_sync(0xffffffffu, base, 2);
+            if (hit) {
+                const uint32_t dl = base_l + __popc(hits & lt_mask);
+                store_primary<S>(w, dl, ps);
+                w.hit[dl] = make_float4(L.best.t, L.best.u, L.best.v, __uint_as_float(L.best.slot));
+                if (w.sample_of) w.sample_of[dl] = smp;
+                if (cls == 0u) w.queue_h[base_0 + __popc(m0 & lt_mask)] = dl;
+                else w.queue_h2[base_1 + __popc(m1 & lt_mask)] = dl;
+                if (w.records) init_record(w.records + smp, ps.wl.v[0]);
+            }
+        }
+        if (fin) state = EMPTY;
+        // ---- refill empty lanes from the open chunk, running over into the chunk claimed ahead ----
+        uint32_t want = __ballot_sync(0xffffffffu, state == EMPTY);
+        if (want) {
+            const uint32_t cnt = __popc(want), rank = __popc(want & lt_mask);
+            const uint32_t avail = out_of_work ? 0u : c_end - c_next;
+            uint32_t i = rank < avail ? c_next + rank : 0xffffffffu;
+            if (!out_of_work && cnt > avail) {
+                const uint32_t nxt = __shfl_sync(0xffffffffu, claim, 0);
+                if (nxt < n) {
+                    if (lane == 0) claim = static_total + atomic_add_async(io.work_cursor, chunk);
+                    if (rank >= avail) i = nxt + (rank - avail);
+                    c_next = nxt + (cnt - avail); c_end = nxt + chunk;
+                } else {
+                    out_of_work = true;
+                }
+            } else if (!out_of_work) {
+                c_next += cnt;
+            }
+            if (!out_of_work && c_next >= n) out_of_work = true;
+            if (state == EMPTY) {
+                if (i < n) {
+                    smp = i;
+                    raygen_sample<S>(sc, io.seed, io.first_sample + i, ps);
+                    L.o = ps.ray.o; L.d = ps.ray.d; L.mint = ps.ray.mint; L.maxt = ps.ray.maxt;
+                    state = trace_begin<false>(sc, s_rect, L) ? BUSY : FINISHED;
+                } else {
+                    state = EXHAUSTED;
+                }
+            }
+        }
+        const uint32_t busy = __ballot_sync(0xffffffffu, state == BUSY);
+        const uint32_t finm = __ballot_sync(0xffffffffu, state == FINISHED);
+        if (busy == 0 && finm == 0) break;
+        if (busy == 0) continue;
+        const int min_busy = out_of_work ? 1 : TRACE_REFILL;
+        do {
+            if (state == BUSY) {
+                if (!trace_step<false>(sc, s_stack, l_stack, L)) state = FINISHED;
+            }
+        } while (__popc(__ballot_sync(0xffffffffu, state == BUSY)) >= min_busy);
+    }
+    if (miss_smem) {
+        __syncthreads();
+        for (uint32_t i = threadIdx.x; i < n_pixels; i += blockDim.x) {
+            const uint32_t v = s_miss[i];
+            if (v) atomicAdd(io.profile + (size_t) C * i + w_channel, (float) v);
+        }
     }
 }
 
@@ -225,7 +427,7 @@ __global__ void __launch_bounds__(128, BF_SHADE_MIN_BLOCKS) k_shade(const __grid
                 else if (gen == BF_GEN_RANGE) scalar += si.is_valid() ? si.t : 0.f;
                 else scalar = si.is_valid() ? si.t / 3.0e8f : 0.f;
                 if (w.records) {
-                    bf_sample_record *r = w.records + l;
+                    bf_sample_record *r = rec_of(w, l);
                     r->first_shape = si.is_valid() ? si.shape : BF_NONE;
                     r->first_prim = si.is_valid() ? si.prim : BF_NONE;
                     r->first_t = si.t;
@@ -295,7 +497,7 @@ __global__ void __launch_bounds__(128, BF_SHADE_MIN_BLOCKS) k_shade(const __grid
                         bool nonzero = false;
 #pragma unroll
                         for (int k = 0; k < S; ++k) { pend.v[k] = mis * thr.v[k] * bsdf_val.v[k] * tspec.v[k]; nonzero |= pend.v[k] != 0.f; }
-                        if (w.records) w.records[l].n_shadow++;
+                        if (w.records) rec_of(w, l)->n_shadow++;
                         if (nonzero) {   // a zero contribution needs no visibility test
                             flags |= LANE_PENDING;
                             push_shadow = true;
@@ -333,7 +535,7 @@ __global__ void __launch_bounds__(128, BF_SHADE_MIN_BLOCKS) k_shade(const __grid
             SpecIO<S>::store(w, l, thr, res, pend, wl);
             w.rng[l] = make_ulonglong2(rng.state, rng.inc);
             if (w.records) {
-                bf_sample_record *r = w.records + l;
+                bf_sample_record *r = rec_of(w, l);
                 r->depth = depth;
                 if (push_next) r->n_closest++;
             }
@@ -398,7 +600,7 @@ struct Splat {
 template <int S>
 __device__ __forceinline__ Splat finalize_lane(const DevScene &sc, const Wave &w, uint32_t l) {
     Splat sp; sp.pixel = -1; sp.val_a = 0.f; sp.cnt_valid = false; sp.var_ch = -1; sp.var_val = 0.f; sp.var_rep = 1;
-    const uint32_t gen = sc.integ.gen, W = sc.film_w, H = sc.film_h;
+    const uint32_t gen = sc.integ.gen;
     uint32_t flags = w.flags[l];
     float4 x1 = w.x1[l], x2 = w.x2[l];
     Spec<S> thr, res, pend, wl;
@@ -411,22 +613,11 @@ __device__ __forceinline__ Splat finalize_lane(const DevScene &sc, const Wave &w
     const bool valid = flags & LANE_VALID;
     float posx, posy;
     int off_x = 0, off_y = 0;
+    bool ran;
+    sample_position(sc, x2, wl.v[0], posx, posy, ran, off_x, off_y);
     if (gen == BF_GEN_PHASE) {
-        const DevEndpoint &rx = *sc.rx;
-        // integrator.cpp:1588-1639
-        float tfx = 0.f, tfy = 0.f;
-        bool ran = true;
         float wl0 = wl.v[0];
         float phase = valid ? x1.y : 0.f;
-        if (rx.receive_type == BF_RECV_MIX_RESAMPLE) {
-            tfx = x2.x - rx.adc_sampling_start;
-            tfy = (float) fabs(freq_from_wl_d(sc.C.c, wl0) - (double) x2.y);
-        } else if (rx.receive_type == BF_RECV_RAW || rx.receive_type == BF_RECV_RAW_RESAMPLE) {
-            tfx = x2.x - rx.adc_sampling_start;
-            tfy = freq_from_wl(sc.C.c, wl0);
-        } else {
-            ran = false;
-        }
         if (!ran) {
 #pragma unroll
             for (int k = 0; k < S; ++k) res.v[k] = 0.f;
@@ -444,18 +635,14 @@ __device__ __forceinline__ Splat finalize_lane(const DevScene &sc, const Wave &w
                 if (rect((ph - centre) / bin_width) > 0.f) { sp.var_ch = 3 + (int) k; sp.var_val = pv; }
             }
         }
-        tfx *= (float) sc.adc.t_bins / sc.adc.t_bandwidth;
-        tfy *= (float) sc.adc.f_bins / sc.adc.f_bandwidth;
         Spec<S> wres;
 #pragma unroll
         for (int k = 0; k < S; ++k) wres.v[k] = fabsf(weight.v[k]) * res.v[k];
         sp.val_a = (valid && ran) ? hsum_spec<S>(wres) : 0.f;
         sp.cnt_valid = valid && ran;
-        posx = tfx; posy = tfy;
-        off_x = (int) sc.adc.window_offset_t; off_y = (int) sc.adc.window_offset_f;
         if (w.records) {
-            bf_sample_record *r = w.records + l;
-            r->valid = (valid && ran) ? 1u : 0u; r->tf_t = tfx; r->tf_f = tfy; r->value = sp.val_a;
+            bf_sample_record *r = rec_of(w, l);
+            r->valid = (valid && ran) ? 1u : 0u; r->tf_t = posx; r->tf_f = posy; r->value = sp.val_a;
             r->phase = phase; r->wavelength0 = wl0;
         }
     } else {
@@ -479,16 +666,12 @@ __device__ __forceinline__ Splat finalize_lane(const DevScene &sc, const Wave &w
         // mono: xyz = value broadcast; spectral: the CIE matching functions vanish at radar wavelengths
         float x = S == 1 ? wres.v[0] : 0.f;
         sp.val_a = x; sp.cnt_valid = valid;
-        posx = x2.x; posy = x2.y;
         if (w.records) {
-            bf_sample_record *r = w.records + l;
+            bf_sample_record *r = rec_of(w, l);
             r->valid = valid ? 1u : 0u; r->tf_t = posx; r->tf_f = posy; r->value = r0; r->phase = scalar; r->wavelength0 = wl.v[0];
         }
     }
-    // SignalBlock::put, box filter of radius 0.5 (signalblock.cpp:162-169)
-    float px = posx - ((float) off_x - 0.f + .5f), py = posy - ((float) off_y - 0.f + .5f);
-    float cx = ceilf(px - .5f), cy = ceilf(py - .5f);
-    if (cx >= 0.f && cy >= 0.f && cx < (float) W && cy < (float) H) sp.pixel = (int) ((uint32_t) cy * W + (uint32_t) cx);
+    sp.pixel = pixel_of(sc, posx, posy, off_x, off_y);
     return sp;
 }
 
@@ -500,6 +683,7 @@ template <int S, bool SMEM>
 __global__ void __launch_bounds__(FIN_THREADS) k_finalize(const __grid_constant__ DevScene sc, const __grid_constant__ Wave w, uint32_t n,
                                                          float *__restrict__ profile) {
     __shared__ float s_hist[SMEM ? FIN_SMEM_FLOATS : 1];
+    if (w.n_lanes) n = min(n, *w.n_lanes);      // compacted wave: the lanes handed out by k_primary
     const uint32_t C = sc.channels;
     const uint32_t total_floats = C * sc.film_w * sc.film_h;
     if (SMEM) {
@@ -592,7 +776,7 @@ static TraceIO trace_io(const Wave &w, const float4 *dirs, const uint32_t *queue
 int launch_trace_closest(const DevScene &sc, const Wave &w, const uint32_t *queue, const uint32_t *count, uint32_t n_direct,
                          uint32_t depth, uint32_t *hit_count, uint32_t *work_cursor, const LaunchCfg &cfg) {
     TraceIO io = trace_io(w, w.ray_d, queue, count, n_direct, work_cursor);
-    io.hit = w.hit; io.hit_queue[0] = w.queue_h; io.hit_queue[1] = w.queue_h2; io.hit_count[0] = hit_count; io.hit_count[1] = hit_count + 1; io.x1 = w.x1; io.records = w.records; io.depth = depth;
+    io.hit = w.hit; io.hit_queue[0] = w.queue_h; io.hit_queue[1] = w.queue_h2; io.hit_count[0] = hit_count; io.hit_count[1] = hit_count + 1; io.x1 = w.x1; io.records = w.records; io.sample_of = w.sample_of; io.depth = depth;
     io.total = w.totals + 0;
     k_trace<false><<<trace_grid(cfg), TRACE_THREADS, 0, cfg.stream>>>(sc, io);
     return 1;
@@ -632,6 +816,16 @@ int launch_finalize(const DevScene &sc, const Wave &w, uint32_t n, float *profil
     const bool smem = sc.channels * sc.film_w * sc.film_h <= FIN_SMEM_FLOATS;
     if (sc.S == 1) { if (smem) k_finalize<1, true><<<grid, FIN_THREADS, 0, cfg.stream>>>(sc, w, n, profile); else k_finalize<1, false><<<grid, FIN_THREADS, 0, cfg.stream>>>(sc, w, n, profile); }
     else { if (smem) k_finalize<4, true><<<grid, FIN_THREADS, 0, cfg.stream>>>(sc, w, n, profile); else k_finalize<4, false><<<grid, FIN_THREADS, 0, cfg.stream>>>(sc, w, n, profile); }
+    return 1;
+}
+int launch_primary(const DevScene &sc, const Wave &w, uint64_t seed, uint64_t first_sample, uint32_t n, uint32_t *hit_count,
+                   uint32_t *work_cursor, float *profile, const LaunchCfg &cfg) {
+    if (n == 0) return 0;
+    PrimaryIO io;
+    io.seed = seed; io.first_sample = first_sample; io.n = n; io.work_cursor = work_cursor; io.hit_count = hit_count; io.n_lanes = w.n_lanes;
+    io.total = w.totals + 0; io.profile = profile;
+    if (sc.S == 1) k_primary<1><<<cfg.sm_count * BF_PRIMARY_MIN_BLOCKS, TRACE_THREADS, 0, cfg.stream>>>(sc, w, io);
+    else k_primary<4><<<cfg.sm_count * BF_PRIMARY_MIN_BLOCKS, TRACE_THREADS, 0, cfg.stream>>>(sc, w, io);
     return 1;
 }
 int launch_trace_rays(const DevScene &sc, const float4 *ray_o, const float4 *ray_d, uint32_t n, float4 *hit, uint32_t *occl,

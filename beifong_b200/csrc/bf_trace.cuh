@@ -252,6 +252,7 @@ struct TraceIO {
     uint32_t *hit_queue[2], *hit_count[2];
     float4 *x1;                      // closest, gen 3, depth > 1: a missed continuation ray leaves time = phase = -inf
     bf_sample_record *records;
+    const uint32_t *sample_of;       // lane -> record index (null: identity)
     uint32_t depth;                  // the shade iteration this trace feeds
     uint32_t *steps;                 // optional debug output: traversal steps per ray
     uint32_t *work_cursor;
@@ -326,7 +327,7 @@ __global__ void __launch_bounds__(TRACE_THREADS, 8) k_trace(const __grid_constan
                     if (io.depth > 1 && sc.integ.gen == BF_GEN_PHASE) {
                         float4 x = io.x1[l]; x.x = -bf_inf(); x.y = -bf_inf(); io.x1[l] = x;
                     }
-                    if (io.records) io.records[l].depth = io.depth;
+                    if (io.records) io.records[io.sample_of ? io.sample_of[l] : l].depth = io.depth;
                 }
             }
             state = EMPTY;

@@ -40,7 +40,9 @@ struct Wave {
     uint32_t *queue_s;   // lane-id queue for shadow rays
     uint32_t *counters;  // BF_CTR_STRIDE * (BF_MAX_BOUNCES + 2)
     unsigned long long *totals;  // [0] closest queries traced, [1] shadow queries traced
-    bf_sample_record *records;   // optional per-lane debug records
+    bf_sample_record *records;   // optional debug records, indexed by sample (= lane unless sample_of is set)
+    uint32_t *sample_of;         // fused primary kernel: lane -> sample offset in the wave (lanes are compacted hits)
+    uint32_t *n_lanes;           // fused primary kernel: device-side count of compacted lanes
 };
 
 struct LaunchCfg {
@@ -49,6 +51,9 @@ struct LaunchCfg {
 };
 
 // Kernel launchers (bf_kernels.cu).  Return the number of kernels launched.
+// raygen + first closest-hit query + compaction of the hits into lanes [0, *w.n_lanes); misses are binned on the spot
+int launch_primary(const DevScene &sc, const Wave &w, uint64_t seed, uint64_t first_sample, uint32_t n, uint32_t *hit_count,
+                   uint32_t *work_cursor, float *profile, const LaunchCfg &cfg);
 int launch_raygen(const DevScene &sc, const Wave &w, uint64_t seed, uint64_t first_sample, uint32_t n, const LaunchCfg &cfg);
 // queue == nullptr: lanes [0, n_direct); else lane ids from queue[0 .. *count)
 // depth = the shade iteration this trace feeds; lanes that hit are appended to w.queue_h / *hit_count
