@@ -647,7 +647,7 @@ static uint32_t env_u32(const char *name, uint32_t dflt, uint32_t lo, uint32_t h
     if (v > (long) hi) v = hi;
     return (uint32_t) v;
 }
-static uint32_t wave_lanes_default() { return env_u32("BF_WAVE_LANES", 1u << 23, 1024, 1u << 24); }
+static uint32_t wave_lanes_default() { return env_u32("BF_WAVE_LANES", 1u << 23, 1024, 1u << 26); }
 static uint32_t wave_streams_default() { return env_u32("BF_WAVE_STREAMS", 8, 1, 16); }
 
 static void free_slot(WaveSlot &sl, bool keep_stream) {
@@ -763,7 +763,14 @@ int bf_receive(bf_scene *s, uint64_t seed, uint64_t first_sample, uint64_t n_sam
     if (!s->committed) return fail(s, BF_ERR_STATE, "bf_receive: scene not committed");
     BF_CUDA(cudaSetDevice(s->device));
     if (s->tables_dirty) { int rc = upload_tables(s); if (rc) return rc; }
-    const uint32_t lanes = (uint32_t) std::min<uint64_t>(std::max<uint64_t>(n_samples, 1024), wave_lanes_default());
+    // Wave size: BF_WAVE_LANES when set; otherwise the request is cut into as many waves as there are slots, between 2^22 and
+    // 2^25 samples each (larger waves amortise the traversal tails: profiles/r01d_tune_wave.txt)
+    uint64_t want_lanes = wave_lanes_default();
+    if (!getenv("BF_WAVE_LANES")) {
+        const uint64_t per_slot = (n_samples + wave_streams_default() - 1) / wave_streams_default();
+        want_lanes = std::min<uint64_t>(std::max<uint64_t>((per_slot + 1023) / 1024 * 1024, 1u << 22), 1u << 25);
+    }
+    const uint32_t lanes = (uint32_t) std::min<uint64_t>(std::max<uint64_t>(n_samples, 1024), want_lanes);
     const uint64_t n_waves = (n_samples + lanes - 1) / lanes;
     // per-kernel timing needs the launches serialised on one stream
     const size_t n_slots = s->time_trace ? 1 : (size_t) std::min<uint64_t>(wave_streams_default(), std::max<uint64_t>(n_waves, 1));
