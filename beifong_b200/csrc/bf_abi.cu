@@ -717,7 +717,7 @@ static int run_wave(bf_scene *s, WaveSlot &sl, uint64_t seed, uint64_t first, ui
     Wave w = sl.wave;
     if (!with_records) { w.records = nullptr; w.sample_of = nullptr; }
     // BF_FUSED_PRIMARY=0 selects the unfused raygen + trace pair (lanes = samples), kept for A/B measurements
-    static const bool fused = env_u32("BF_FUSED_PRIMARY", 1, 0, 1) != 0;
+    const bool fused = env_u32("BF_FUSED_PRIMARY", 1, 0, 1) != 0;
     if (!fused) w.sample_of = nullptr;
     LaunchCfg cfg; cfg.stream = sl.stream; cfg.sm_count = s->sm_count;
     uint32_t *ctr = w.counters;
@@ -734,7 +734,7 @@ static int run_wave(bf_scene *s, WaveSlot &sl, uint64_t seed, uint64_t first, ui
     };
     if (fused) {
         w.n_lanes = ctr + 6;
-        timed(BF_K_TRACE_CLOSEST, [&] { return launch_primary(sc, w, seed, first, n, ctr + 4, ctr + 2, profile, cfg); });
+        timed(BF_K_PRIMARY, [&] { return launch_primary(sc, w, seed, first, n, ctr + 4, ctr + 2, profile, cfg); });
     } else {
         w.n_lanes = nullptr;
         timed(BF_K_RAYGEN, [&] { return launch_raygen(sc, w, seed, first, n, cfg); });
@@ -944,7 +944,7 @@ int bf_last_receive_ms(bf_scene *s, float *total_ms, float *traverse_ms) {
         float acc = 0.f;
         for (size_t i = 0; i + 1 < s->ev_trace_used; i += 2) {
             float m = 0.f;
-            if (s->ev_kind[i] != BF_K_TRACE_CLOSEST && s->ev_kind[i] != BF_K_TRACE_SHADOW) continue;
+            if (s->ev_kind[i] != BF_K_TRACE_CLOSEST && s->ev_kind[i] != BF_K_TRACE_SHADOW && s->ev_kind[i] != BF_K_PRIMARY) continue;
             if (cudaEventElapsedTime(&m, s->ev_trace[i], s->ev_trace[i + 1]) == cudaSuccess) acc += m;
         }
         *traverse_ms = s->time_trace ? acc : -1.f;

@@ -265,10 +265,10 @@ class FlatScene:
     def set_trace_timing(self, enabled):
         self._ck(N.lib().bf_set_trace_timing(self._h, int(enabled)), "bf_set_trace_timing")
 
-    KERNELS = ("raygen", "trace_closest", "trace_shadow", "shade", "finalize")
+    KERNELS = ("raygen", "trace_closest", "trace_shadow", "shade", "finalize", "primary")
 
     def last_kernel_ms(self):
-        ms, n = (C.c_float * 5)(), (C.c_uint32 * 5)()
+        ms, n = (C.c_float * len(self.KERNELS))(), (C.c_uint32 * len(self.KERNELS))()
         self._ck(N.lib().bf_last_kernel_ms(self._h, ms, n), "bf_last_kernel_ms")
         return {k: (ms[i], n[i]) for i, k in enumerate(self.KERNELS)}
 

@@ -233,13 +233,28 @@ def main():
             pass
         peak = float(peaks.get("hbm_gbs", 6650.0))
         peak_src = "measured (MEASURED_PEAKS.json hbm_gbs)" if "hbm_gbs" in peaks else "fallback 6650 GB/s"
+        # Dominant kernel: k_primary (receiver ray generation + first closest-hit query + compaction, fused); it issues one
+        # closest-hit query per sample.  Later closest-hit launches (k_trace<closest>) are reported beside it.
+        pr_ms, pr_launch = km.get("primary", (0.0, 0))
         cl_ms, cl_launch = km["trace_closest"]
-        achieved = q_closest * b_closest / (cl_ms * 1e-3) / 1e9
+        if pr_launch:
+            dom_name, dom_ms, dom_launch, dom_queries = "k_primary (raygen + closest-hit query + compaction)", pr_ms, pr_launch, reps * n
+        else:
+            dom_name, dom_ms, dom_launch, dom_queries = "k_trace<closest>", cl_ms, cl_launch, q_closest
+        achieved = dom_queries * b_closest / (dom_ms * 1e-3) / 1e9
         total_ms = sum(v[0] for v in km.values())
-        roofline = {"bound": "hbm", "kernel": "k_trace<closest>", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                    "traffic": None, "peak_source": peak_src,
-                    "algorithmic_bytes_per_query": b_closest, "queries_per_launch": q_closest / max(cl_launch, 1),
-                    "avg_launch_ms": cl_ms / max(cl_launch, 1), "kernel_share_of_step": cl_ms / max(total_ms, 1e-9),
+        traffic = None
+        try:   # DRAM bytes per launch of the same kernel from the committed ncu --set full capture, scaled to this launch size
+            tr = json.load(open(os.path.join(ROOT, "profiles", "roofline_traffic.json")))
+            traffic = tr["dram_bytes_per_query"] * dom_queries / max(dom_launch, 1)
+        except Exception:
+            pass
+        roofline = {"bound": "hbm", "kernel": dom_name, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                    "traffic": traffic, "peak_source": peak_src,
+                    "algorithmic_bytes_per_query": b_closest, "queries_per_launch": dom_queries / max(dom_launch, 1),
+                    "avg_launch_ms": dom_ms / max(dom_launch, 1), "kernel_share_of_step": dom_ms / max(total_ms, 1e-9),
+                    "later_closest_launches": {"queries": q_closest - (reps * n if pr_launch else 0), "ms": cl_ms, "launches": cl_launch,
+                                               "achieved": (q_closest - (reps * n if pr_launch else 0)) * b_closest / max(cl_ms * 1e-3, 1e-12) / 1e9 if pr_launch else None},
                     "kernel_ms_per_step": {k: v[0] / reps for k, v in km.items()},
                     "queries_per_sample": {"closest": q_closest / (reps * n), "shadow": q_shadow / (reps * n)},
                     "algorithmic_bytes_per_sample": (q_closest * b_closest + q_shadow * b_shadow) / (reps * n) + b_bins,

@@ -273,7 +273,8 @@ int bf_last_receive_ms(bf_scene *s, float *total_ms, float *traverse_ms);
 int bf_set_trace_timing(bf_scene *s, int enabled);
 /* Per-kernel device time (ms) and launch count of the most recent bf_receive, indexed by BF_K_*;
  * needs bf_set_trace_timing(s, 1).  Used for the roofline of the dominant kernel. */
-enum { BF_K_RAYGEN = 0, BF_K_TRACE_CLOSEST = 1, BF_K_TRACE_SHADOW = 2, BF_K_SHADE = 3, BF_K_FINALIZE = 4, BF_K_COUNT = 5 };
+enum { BF_K_RAYGEN = 0, BF_K_TRACE_CLOSEST = 1, BF_K_TRACE_SHADOW = 2, BF_K_SHADE = 3, BF_K_FINALIZE = 4,
+       BF_K_PRIMARY = 5 /* fused raygen + first closest-hit query + compaction */, BF_K_COUNT = 6 };
 int bf_last_kernel_ms(bf_scene *s, float *ms, uint32_t *launches);
 /* The same, launch by launch in issue order (kind[i] = BF_K_*). */
 int bf_last_launch_list(bf_scene *s, float *ms, uint32_t *kind, uint32_t capacity, uint32_t *n_out);
