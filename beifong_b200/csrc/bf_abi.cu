@@ -505,6 +505,7 @@ static int upload_tables(bf_scene *s) {
     film_size(s, d.film_w, d.film_h); d.channels = n_channels(s);
     d.rx_needs_aperture = s->rx.kind != BF_RX_PERSPECTIVE;   // Sensor::needs_aperture_sample
     d.hint_cls1_bsdf = cls1_kind < 0 ? -1 : cls1_kind;
+    d.hint_rx_kind = (int32_t) s->rx.kind;
     d.hint_tx_kind = txs.empty() ? -1 : (int32_t) txs[0].kind;
     for (const DevEndpoint &e : txs) if ((int32_t) e.kind != d.hint_tx_kind) d.hint_tx_kind = -1;
     d.phase_denom = (double) ((s->C.lambda_max_nm - s->C.lambda_min_nm) / 2) * 1e-9;

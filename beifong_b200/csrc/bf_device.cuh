@@ -678,10 +678,12 @@ template <int S> BF_D void sample_wavelength(const DevScene &sc, float sample, S
     }
 }
 // omnidirectional.cpp:71-107, fluxmeter.cpp:63-84, wignerreceiver.cpp:150-269, perspective.cpp:166-196
-template <int S> BF_D void rx_sample_ray(const DevScene &sc, float time, float sample1, V2 sample2, V2 sample3, RayGen &ray, Spec<S> &wl, Spec<S> &weight) {
+// RXK >= 0: the receiver kind is a compile-time constant (specialised primary kernels); -1: read from the scene.
+template <int S, int RXK = -1> BF_D void rx_sample_ray(const DevScene &sc, float time, float sample1, V2 sample2, V2 sample3, RayGen &ray, Spec<S> &wl, Spec<S> &weight) {
     const DevEndpoint &d = *sc.rx;
+    const uint32_t kind = RXK >= 0 ? (uint32_t) RXK : d.kind;
     ray.mint = BF_RAY_EPS; ray.maxt = bf_inf(); ray.time = time;
-    if (d.kind == BF_RX_PERSPECTIVE) {
+    if (kind == BF_RX_PERSPECTIVE) {
         sample_wavelength<S>(sc, sample1, wl, weight);
         V3 near_p = xf_point(d.sample_to_camera, V3(sample2.x, sample2.y, 0.f));
         V3 dd = normalize(near_p);
@@ -692,12 +694,12 @@ template <int S> BF_D void rx_sample_ray(const DevScene &sc, float time, float s
         return;
     }
     const DevRect &r = sc.rects[sc.shapes[d.shape].index];
-    if (d.kind == BF_RX_OMNIDIRECTIONAL || d.kind == BF_RX_FLUXMETER) {
+    if (kind == BF_RX_OMNIDIRECTIONAL || kind == BF_RX_FLUXMETER) {
         PositionSample ps = rect_sample_position(r, time, sample2);
         V3 local = square_to_cosine_hemisphere(sample3);
         Spec<S> ww; sample_wavelength<S>(sc, sample1, wl, ww);
         ray.o = ps.p; ray.d = Frame(ps.n).to_world(local);
-        float k = d.kind == BF_RX_OMNIDIRECTIONAL ? r.area : BF_PI;
+        float k = kind == BF_RX_OMNIDIRECTIONAL ? r.area : BF_PI;
 #pragma unroll
         for (int i = 0; i < S; ++i) weight.v[i] = ww.v[i] * k;
         return;
@@ -719,7 +721,7 @@ template <int S> BF_D void rx_sample_ray(const DevScene &sc, float time, float s
     Frame fr(ps.n);
     V3 dloc = square_to_cosine_hemisphere(sample3);
     float geom_gain;
-    if (d.kind == BF_RX_PHASED) {                                  // phasedreceiver.cpp:313-375 (:353)
+    if (kind == BF_RX_PHASED) {                                  // phasedreceiver.cpp:313-375 (:353)
         float w = phased_sample_wigner(sc, d, ps.p, dloc, wl.v[0]);
         float dn = dot(dloc, ps.n);                                // local direction against the world normal, as written
         geom_gain = w * ps.pdf * (1 - dn * dn * dn * dn);

@@ -107,7 +107,7 @@ template <int S> struct PrimaryState {
 };
 
 // Head of receive_sample (integrator.cpp:1544-1569) / render_sample (:263-279) for sample `idx`.
-template <int S>
+template <int S, int GEN = -1, int RXK = -1>
 __device__ __forceinline__ void raygen_sample(const DevScene &sc, uint64_t seed, uint64_t idx, PrimaryState<S> &ps) {
     PCG32 rng;
     rng.seed(tea64_shared(seed, idx), tea64_shared(idx, seed));   // sampler.cpp:89-92
@@ -117,12 +117,12 @@ __device__ __forceinline__ void raygen_sample(const DevScene &sc, uint64_t seed,
     if (sc.rx_needs_aperture) { aperture_sample.x = rng.next_float32(); aperture_sample.y = rng.next_float32(); }
     float time;
     float4 x2 = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (sc.integ.gen == BF_GEN_PHASE) {
+    if ((GEN >= 0 ? (uint32_t) GEN : sc.integ.gen) == BF_GEN_PHASE) {
         // integrator.cpp:1544-1569
         time = rx.adc_sampling_start;
         if (rx.adc_sampling_time > 0.f) time += rng.next_float32() * rx.adc_sampling_time; else time = 0.f;
         float wavelength_sample = rng.next_float32();
-        rx_sample_ray<S>(sc, time, wavelength_sample, position_sample, aperture_sample, ps.ray, ps.wl, ps.weight);
+        rx_sample_ray<S, RXK>(sc, time, wavelength_sample, position_sample, aperture_sample, ps.ray, ps.wl, ps.weight);
         x2.x = time;
         x2.y = freq_from_wl(sc.C.c, ps.wl.v[0]);   // f_rx of mix_resample (integrator.cpp:1603)
     } else {
@@ -131,7 +131,7 @@ __device__ __forceinline__ void raygen_sample(const DevScene &sc, uint64_t seed,
         if (rx.shutter_open_time > 0.f) time += rng.next_float32() * rx.shutter_open_time;
         float wavelength_sample = rng.next_float32();
         V2 adjusted((position_sample.x - 0.f) / (float) sc.film_w, (position_sample.y - 0.f) / (float) sc.film_h);
-        rx_sample_ray<S>(sc, time, wavelength_sample, adjusted, aperture_sample, ps.ray, ps.wl, ps.weight);
+        rx_sample_ray<S, RXK>(sc, time, wavelength_sample, adjusted, aperture_sample, ps.ray, ps.wl, ps.weight);
         x2.x = position_sample.x; x2.y = position_sample.y;
     }
     if (S == 1) x2.w = ps.weight.v[0];
@@ -222,7 +222,7 @@ struct PrimaryIO {
 #ifndef BF_PRIMARY_MIN_BLOCKS
 #define BF_PRIMARY_MIN_BLOCKS 8
 #endif
-template <int S>
+template <int S, int GEN, int RXK>
 __global__ void __launch_bounds__(TRACE_THREADS, BF_PRIMARY_MIN_BLOCKS) k_primary(const __grid_constant__ DevScene sc, const __grid_constant__ Wave w, const __grid_constant__ PrimaryIO io) {
     __shared__ float s_rect[RECT_SM_FLOATS * BF_MAX_RECTS];
     __shared__ uint2 s_stack[TRACE_SM_STACK * TRACE_THREADS];
@@ -314,7 +314,7 @@ __global__ void __launch_bounds__(TRACE_THREADS, BF_PRIMARY_MIN_BLOCKS) k_primar
             if (state == EMPTY) {
                 if (i < n) {
                     smp = i;
-                    raygen_sample<S>(sc, io.seed, io.first_sample + i, ps);
+                    raygen_sample<S, GEN, RXK>(sc, io.seed, io.first_sample + i, ps);
                     L.o = ps.ray.o; L.d = ps.ray.d; L.mint = ps.ray.mint; L.maxt = ps.ray.maxt;
                     state = trace_begin<false>(sc, s_rect, L) ? BUSY : FINISHED;
                 } else {
@@ -824,8 +824,15 @@ int launch_primary(const DevScene &sc, const Wave &w, uint64_t seed, uint64_t fi
     PrimaryIO io;
     io.seed = seed; io.first_sample = first_sample; io.n = n; io.work_cursor = work_cursor; io.hit_count = hit_count; io.n_lanes = w.n_lanes;
     io.total = w.totals + 0; io.profile = profile;
-    if (sc.S == 1) k_primary<1><<<cfg.sm_count * BF_PRIMARY_MIN_BLOCKS, TRACE_THREADS, 0, cfg.stream>>>(sc, w, io);
-    else k_primary<4><<<cfg.sm_count * BF_PRIMARY_MIN_BLOCKS, TRACE_THREADS, 0, cfg.stream>>>(sc, w, io);
+    const int grid = cfg.sm_count * BF_PRIMARY_MIN_BLOCKS;
+    const bool radar = sc.integ.gen == BF_GEN_PHASE && sc.hint_rx_kind == BF_RX_WIGNER;   // specialised: gen-3 integrator, wigner receiver
+    if (sc.S == 1) {
+        if (radar) k_primary<1, BF_GEN_PHASE, BF_RX_WIGNER><<<grid, TRACE_THREADS, 0, cfg.stream>>>(sc, w, io);
+        else k_primary<1, -1, -1><<<grid, TRACE_THREADS, 0, cfg.stream>>>(sc, w, io);
+    } else {
+        if (radar) k_primary<4, BF_GEN_PHASE, BF_RX_WIGNER><<<grid, TRACE_THREADS, 0, cfg.stream>>>(sc, w, io);
+        else k_primary<4, -1, -1><<<grid, TRACE_THREADS, 0, cfg.stream>>>(sc, w, io);
+    }
     return 1;
 }
 int launch_trace_rays(const DevScene &sc, const float4 *ray_o, const float4 *ray_d, uint32_t n, float4 *hit, uint32_t *occl,
