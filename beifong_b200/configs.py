@@ -124,3 +124,36 @@ def c3_multi_object(spectrum_width=1, max_depth=4, copies=14, n_u=264, n_v=133, 
             extra.append((p, base_f))
     s = radar_scene(first[0], first[1], spectrum_width=spectrum_width, max_depth=max_depth, extra_meshes=extra)
     return s
+
+
+def c4_pose(frame, n_frames=256):
+    """Tx/Rx pose of frame `frame` of the animated sequence: boresight (0, -1, 0) rotated about z by frame * 360 / n_frames
+    degrees (python_scripts/animated_trans_rad.py:305-311 steps by 5 degrees; 256 positions is Receive.ipynb's da = 1 / 2**8)."""
+    rot = T.rotate([0, 0, 1], frame * 360.0 / n_frames).matrix32().astype(np.float64)
+    boresight = rot[:3, :3] @ np.array([0.0, -1.0, 0.0])
+    up = rot[:3, :3] @ np.array([0.0, 0.0, 1.0])
+    return T.look_at((0, 0, 0), tuple(boresight), tuple(up))
+
+
+def c4_receiver(pose, dr=0.2, bins=50):
+    near, far = dr, bins * dr + dr
+    return FlatScene.endpoint(N.BF_RX_PERSPECTIVE, film_width=1, film_height=1, near_clip=near, far_clip=far, to_world=pose.matrix32(),
+                              sample_to_camera=meshes.perspective_sample_to_camera(45.0, near, far, 1, 1))
+
+
+def c4_animated(frame=0, n_frames=256, spectrum_width=1, dr=0.2, bins=50, max_depth=-1):
+    """BASELINE config 4, one frame of python_scripts/animated_trans_rad.py: 1 x 1 target at y = +4 and 20 x 20 ground at
+    z = -0.5 (twosided diffuse 1), area emitter on a 0.5 x 0.5 rectangle at the origin (radiance 100), perspective sensor
+    fov 45, near / far = dr / (bins + 1) dr, 1 x 1 box-filtered film; gen-2 integrator range(pathlength), dr 0.2, 50 bins.
+    Returns (scene, tx_shape_id): later frames call scene.update_rect(tx_shape_id, ...) and scene.set_receiver(None, ...)."""
+    s = FlatScene(spectrum_width=spectrum_width)
+    default_bsdf = s.add_diffuse(0.5, two_sided=False)
+    material = s.add_diffuse(1.0, two_sided=True)
+    pose = c4_pose(frame, n_frames)
+    tx = s.add_rect((pose * T.scale([0.5, 0.5, 1.0])).matrix32(), default_bsdf)
+    s.add_rect(rect_to_world((1, 1), (0, 4, 0), (0, 0, 0)), material)
+    s.add_rect(rect_to_world((20, 20), (0, 0, -0.5), (0, 0, 0.5), up=(0, 1, 0)), material)
+    s.add_transmitter(tx, FlatScene.endpoint(N.BF_TX_AREALIGHT, texture=s.add_uniform(100.0)))
+    s.set_receiver(None, c4_receiver(pose, dr, bins))
+    s.set_integrator(N.BF_GEN_RANGE, max_depth=max_depth, rr_depth=5, range_bins=bins, dr=dr)
+    return s, tx

@@ -489,3 +489,17 @@ def test_c1_trans_rad_energy_in_expected_bins():
     bins = prof[0, 0, 5:].reshape(50, 3)
     assert np.array_equal(bins[:, 0], bins[:, 1]) and np.array_equal(bins[:, 0], bins[:, 2])
     assert bins[:6].sum() == 0 and bins[6:].sum() > 0
+
+
+def test_c4_animated_frame_range_bins():
+    """animated_trans_rad.py (gen 2, range(pathlength), dr 0.2 x 50 bins): the ground 0.5 m below the sensor is the nearest
+    surface; with the reference's path-length bookkeeping (si.t is added at pathlength.cpp:146, :161 and :209 for a lit
+    surface point) nothing can land below bin 13, and every sample is counted in the 1 x 1 film."""
+    s, _ = configs.c4_animated(frame=37)
+    prof = OracleScene(s.export(), accel=OracleScene.BRUTE).receive(50000, seed=0, threads=4)
+    assert prof.shape == (1, 1, 55) and prof[0, 0, 4] == 50000
+    bins = prof[0, 0, 5:]
+    assert bins[:13].sum() == 0 and bins[13:].sum() > 0
+    # the pose helper turns the boresight about z
+    p0, p64 = configs.c4_pose(0).matrix32(), configs.c4_pose(64).matrix32()
+    assert np.allclose(p0[:3, 2], [0, -1, 0], atol=1e-6) and np.allclose(p64[:3, 2], [1, 0, 0], atol=1e-6)
