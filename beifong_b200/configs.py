@@ -45,7 +45,7 @@ def fmcw_signal(resample_freq, gain=1.0):
 
 
 def radar_scene(mesh_pos, mesh_faces, spectrum_width=1, max_depth=4, range_bins=1024, bin_m=0.03, smooth_normals=True,
-                extra_meshes=(), phased=None):
+                extra_meshes=(), phased=None, ground_half=20.0, reflector=True, return_ids=False):
     """Common 94 GHz FMCW layout of python_scripts/Render.py / Receive.ipynb: Tx and Rx are 5 mm x 5 mm
     rectangles at (0, 0, 0.3) facing +x, ground 20 x 20 diffuse 0.5, corner reflector 0.1 x 0.05 diffuse 1,
     target mesh twosided(roughconductor alpha 0.1).  Receiver `wignerreceiver` (mix_resample) + transmitter
@@ -61,8 +61,9 @@ def radar_scene(mesh_pos, mesh_faces, spectrum_width=1, max_depth=4, range_bins=
     ant = (T.translate([0.0, 0.0, 0.3]) * T.rotate([0, 1, 0], 90.0) * T.scale([0.0025, 0.0025, 1.0]))
     rx = s.add_rect(ant.matrix32(), default_bsdf)
     tx = s.add_rect((T.translate([0.0, 0.01, 0.0]) * ant).matrix32(), default_bsdf)
-    s.add_rect((T.translate([0, 0, 0]) * T.scale([20.0, 20.0, 1.0])).matrix32(), ground)
-    s.add_rect((T.translate([6.0, -2.0, 0.5]) * T.rotate([0, 1, 0], -90.0) * T.scale([0.05, 0.025, 1.0])).matrix32(), refl)
+    s.add_rect((T.translate([0, 0, 0]) * T.scale([ground_half, ground_half, 1.0])).matrix32(), ground)
+    if reflector:
+        s.add_rect((T.translate([6.0, -2.0, 0.5]) * T.rotate([0, 1, 0], -90.0) * T.scale([0.05, 0.025, 1.0])).matrix32(), refl)
     nrm = meshes.vertex_normals(mesh_pos, mesh_faces) if smooth_normals else None
     s.add_mesh(mesh_pos, mesh_faces, car, normals=nrm)
     for (p, f) in extra_meshes:
@@ -86,7 +87,7 @@ def radar_scene(mesh_pos, mesh_faces, spectrum_width=1, max_depth=4, range_bins=
                                           adc_sampling_start=20e-6, adc_sampling_time=160e-6, array=rx_arr))
     s.set_adc(t_bins=1, f_bins=range_bins, t_bandwidth=200e-6, f_bandwidth=f_bandwidth)
     s.set_integrator(N.BF_GEN_PHASE, max_depth=max_depth, rr_depth=5, phase_bins=1)
-    return s
+    return (s, rx, tx) if return_ids else s
 
 
 def car_pose():
@@ -157,3 +158,24 @@ def c4_animated(frame=0, n_frames=256, spectrum_width=1, dr=0.2, bins=50, max_de
     s.set_receiver(None, c4_receiver(pose, dr, bins))
     s.set_integrator(N.BF_GEN_RANGE, max_depth=max_depth, rr_depth=5, range_bins=bins, dr=dr)
     return s, tx
+
+
+C5_ELEMENTS = 64
+C5_PITCH = 0.5 * C0 / 94e9          # lambda / 2 at the 94 GHz carrier of the stand-in signal (BASELINE names 76.5 GHz)
+
+
+def c5_element_pose(k, n_elements=C5_ELEMENTS):
+    """to_world of receive element k: 5 mm x 5 mm apertures on a line along y, pitch lambda / 2, at z = 0.3 facing +x."""
+    y = (k - 0.5 * (n_elements - 1)) * C5_PITCH
+    return (T.translate([0.0, y, 0.3]) * T.rotate([0, 1, 0], 90.0) * T.scale([0.0025, 0.0025, 1.0])).matrix32()
+
+
+def c5_urban(n_side=100, spectrum_width=1, max_depth=4, face_grid=10):
+    """BASELINE config 5 stand-in: procedural city of n_side x n_side tessellated boxes (default 1.0e7 triangles, facades
+    twosided(roughconductor)) on a 1 km ground plane, one wignertransmitter, receive elements on a line: element k is
+    received with `scene.update_rect(rx, c5_element_pose(k)); scene.receive(n, seed=k)` into its own 1024-bin profile.
+    Returns (scene, rx_shape_id)."""
+    p, f = meshes.city_blocks(n_side=n_side, face_grid=face_grid)
+    s, rx, _ = radar_scene(p, f, spectrum_width=spectrum_width, max_depth=max_depth, smooth_normals=False,
+                           ground_half=0.5 * n_side * 10.0, reflector=False, range_bins=1024, bin_m=0.25, return_ids=True)
+    return s, rx

@@ -146,6 +146,7 @@ struct bf_scene {
     std::vector<bf_bsdf_desc> bsdfs;
     std::vector<HostMesh> meshes;
     std::vector<DevRect> rects;
+    std::vector<size_t> rect_blob_off;   // offset of each rectangle's record in the export blob (bf_scene_update_rect rewrites it)
     std::vector<HostShape> shapes;
     std::vector<HostTx> txs;
     int32_t rx_shape = -1; bf_endpoint_desc rx; bool has_rx = false;
@@ -338,6 +339,7 @@ int bf_scene_add_rect(bf_scene *s, const float to_world[16], uint32_t bsdf_id, u
     if (s->committed) return fail(s, BF_ERR_STATE, "bf_scene_add_rect: scene already committed (use bf_scene_update_rect)");
     if (s->rects.size() >= BF_MAX_RECTS) return fail(s, BF_ERR_UNSUPPORTED, "bf_scene_add_rect: more than 64 analytic rectangles");
     uint32_t tail[2] = {bsdf_id, 0};
+    s->rect_blob_off.push_back(s->blob.size());
     record(s, BF_TAG_RECT, to_world, 64, tail, 8);
     HostShape sh; sh.type = 1; sh.index = (uint32_t) s->rects.size(); sh.bsdf = bsdf_id; sh.tx = -1;
     uint32_t id = (uint32_t) s->shapes.size();
@@ -631,6 +633,7 @@ int bf_scene_update_rect(bf_scene *s, uint32_t shape_id, const float to_world[16
     if (!s || !to_world) return BF_ERR_INVALID;
     if (shape_id >= s->shapes.size() || s->shapes[shape_id].type != 1) return fail(s, BF_ERR_INVALID, "bf_scene_update_rect: not a rectangle");
     s->rects[s->shapes[shape_id].index] = make_rect(to_world, shape_id);
+    memcpy(s->blob.data() + s->rect_blob_off[s->shapes[shape_id].index] + sizeof(bf_flat_record), to_world, 64);   // keep the export current
     s->tables_dirty = true;
     return BF_OK;
 }

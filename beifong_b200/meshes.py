@@ -333,3 +333,50 @@ def box_city(n_side=100, tess=10, extent=1000.0, seed=42):
                 face_all.append(gf + base)
                 base += len(q)
     return np.concatenate(pos_all).astype(np.float32), np.concatenate(face_all).astype(np.uint32)
+
+
+def _pcg32_floats(n, seed=42, seq=54):
+    """n uniform floats in [0, 1) from one PCG32 stream (the generator of the procedural city)."""
+    mask = (1 << 64) - 1
+    mult, inc = 0x5851f42d4c957f2d, ((seq << 1) | 1) & mask
+    state = 0
+    state = (state * mult + inc) & mask
+    state = (state + seed) & mask
+    state = (state * mult + inc) & mask
+    out = np.empty(n, dtype=np.float32)
+    for i in range(n):
+        old = state
+        state = (old * mult + inc) & mask
+        xs = (((old >> 18) ^ old) >> 27) & 0xffffffff
+        rot = old >> 59
+        u = ((xs >> rot) | (xs << ((-rot) & 31))) & 0xffffffff
+        out[i] = np.uint32((u >> 9) | 0x3f800000).view(np.float32) - np.float32(1.0)
+    return out
+
+
+def city_blocks(n_side=100, pitch=10.0, footprint=6.0, h_min=5.0, h_max=60.0, face_grid=10, seed=42):
+    """Procedural urban scene (BASELINE config 5 stand-in): n_side x n_side axis-aligned boxes on a square lattice of
+    `pitch` metres centred on the origin (streets run along the multiples of `pitch`, so the origin is a crossing), footprint
+    `footprint` x `footprint`, heights ~ U(h_min, h_max) from PCG32(seed); the 5 exposed faces of a box are tessellated into
+    face_grid x face_grid x 2 triangles each (default 1000 triangles per block: 100 x 100 blocks = 1.0e7 triangles)."""
+    heights = h_min + (h_max - h_min) * _pcg32_floats(n_side * n_side, seed)
+    g = face_grid
+    a, b = np.meshgrid(np.linspace(0.0, 1.0, g + 1), np.linspace(0.0, 1.0, g + 1), indexing="xy")
+    a, b = a.reshape(-1), b.reshape(-1)
+    quad = grid_faces(g + 1, g + 1, False)                    # (2 g^2, 3) over a (g+1) x (g+1) vertex grid
+    nv_face = (g + 1) * (g + 1)
+    # unit box [0,1]^3 faces as (origin, du, dv): four walls + roof, outward orientation
+    faces = [((0, 0, 0), (1, 0, 0), (0, 0, 1)), ((1, 0, 0), (0, 1, 0), (0, 0, 1)), ((1, 1, 0), (-1, 0, 0), (0, 0, 1)),
+             ((0, 1, 0), (0, -1, 0), (0, 0, 1)), ((0, 0, 1), (1, 0, 0), (0, 1, 0))]
+    unit = np.concatenate([np.asarray(o, np.float64)[None] + a[:, None] * np.asarray(du, np.float64)[None] + b[:, None] * np.asarray(dv, np.float64)[None]
+                           for o, du, dv in faces])            # (5 nv_face, 3)
+    unit_faces = np.concatenate([quad + k * nv_face for k in range(5)])
+    n_blocks = n_side * n_side
+    ii, jj = np.meshgrid(np.arange(n_side), np.arange(n_side), indexing="ij")
+    cx = (ii.reshape(-1) + 0.5 - n_side / 2.0) * pitch
+    cy = (jj.reshape(-1) + 0.5 - n_side / 2.0) * pitch
+    scale = np.stack([np.full(n_blocks, footprint), np.full(n_blocks, footprint), heights.astype(np.float64)], -1)
+    origin = np.stack([cx - footprint / 2.0, cy - footprint / 2.0, np.zeros(n_blocks)], -1)
+    pos = (unit[None] * scale[:, None] + origin[:, None]).reshape(-1, 3).astype(np.float32)
+    idx = (unit_faces[None].astype(np.int64) + (np.arange(n_blocks) * unit.shape[0])[:, None, None]).reshape(-1, 3).astype(np.uint32)
+    return pos, idx
