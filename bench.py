@@ -146,6 +146,11 @@ def main():
         print(json.dumps(out))
         return 0
 
+    # Everything below may print to stdout from native code (NCCL prints its version line there): keep fd 1 for the one JSON
+    # line and send the rest to stderr.
+    sys.stdout.flush()
+    json_fd = os.dup(1)
+    os.dup2(2, 1)
     import torch
     import torch.distributed as dist
     if world > 1:
@@ -274,7 +279,8 @@ def main():
                "clocks": clk, "gpu_launches": int(launches),
                "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(geom_bytes), "d2h_bytes_per_step": int(nfloats * 4)},
                "roofline": roofline, "cpu_baseline": cpu}
-        print(json.dumps(out))
+        sys.stdout.flush()
+        os.write(json_fd, (json.dumps(out) + "\n").encode())
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
