@@ -306,35 +306,6 @@ def stairs(n_steps):
     return pos, np.array(faces, np.uint32)
 
 
-def box_city(n_side=100, tess=10, extent=1000.0, seed=42):
-    """Procedural urban block grid (BASELINE config 5): n_side^2 axis-aligned boxes of 6 m x 6 m footprint and
-    U(5,60) m height, 5 exposed faces each tessellated into 2*tess^2 triangles."""
-    rng = np.random.Generator(np.random.PCG64(seed))
-    heights = rng.uniform(5.0, 60.0, size=(n_side, n_side))
-    pitch = extent / n_side
-    s = np.linspace(0.0, 1.0, tess + 1)
-    a, b = np.meshgrid(s, s, indexing="xy")
-    a, b = a.ravel(), b.ravel()
-    gf = grid_faces(tess + 1, tess + 1, False)
-    pos_all, face_all, base = [], [], 0
-    for i in range(n_side):
-        for j in range(n_side):
-            cx, cy, hgt = (i + 0.5) * pitch - extent / 2, (j + 0.5) * pitch - extent / 2, heights[i, j]
-            x0, x1, y0, y1 = cx - 3.0, cx + 3.0, cy - 3.0, cy + 3.0
-            quads = [
-                np.stack([x0 + (x1 - x0) * a, y0 + (y1 - y0) * b, np.full_like(a, hgt)], 1),        # roof
-                np.stack([x0 + (x1 - x0) * a, np.full_like(a, y0), hgt * b], 1),
-                np.stack([x1 - (x1 - x0) * a, np.full_like(a, y1), hgt * b], 1),
-                np.stack([np.full_like(a, x0), y1 - (y1 - y0) * a, hgt * b], 1),
-                np.stack([np.full_like(a, x1), y0 + (y1 - y0) * a, hgt * b], 1),
-            ]
-            for q in quads:
-                pos_all.append(q)
-                face_all.append(gf + base)
-                base += len(q)
-    return np.concatenate(pos_all).astype(np.float32), np.concatenate(face_all).astype(np.uint32)
-
-
 def _pcg32_floats(n, seed=42, seq=54):
     """n uniform floats in [0, 1) from one PCG32 stream (the generator of the procedural city)."""
     mask = (1 << 64) - 1
