@@ -757,7 +757,7 @@ __global__ void __launch_bounds__(FIN_THREADS) k_finalize(const __grid_constant_
 // =========================================================================================================
 // launchers
 // =========================================================================================================
-static int trace_grid(const LaunchCfg &cfg) { return cfg.sm_count * 8; }
+static int trace_grid(const LaunchCfg &cfg) { return cfg.sm_count * TRACE_MIN_BLOCKS; }
 
 int launch_raygen(const DevScene &sc, const Wave &w, uint64_t seed, uint64_t first_sample, uint32_t n, const LaunchCfg &cfg) {
     if (n == 0) return 0;

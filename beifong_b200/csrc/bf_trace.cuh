@@ -17,7 +17,12 @@ namespace bf {
 #define TRACE_THREADS 128
 #define TRACE_SM_STACK BF_TRACE_SM_STACK
 #define TRACE_LOCAL_STACK BF_TRACE_LOCAL_STACK
+#ifndef TRACE_REFILL
 #define TRACE_REFILL 20
+#endif
+#ifndef TRACE_MIN_BLOCKS
+#define TRACE_MIN_BLOCKS 8
+#endif
 
 __device__ __forceinline__ uint32_t sign_extend_s8x4(uint32_t x) {
     uint32_t r;
@@ -264,7 +269,7 @@ struct TraceIO {
 // chunk runs dry), so the ~1 us round trip of a returning global atomic is off the critical path.  The same is
 // done for hit-queue pushes: the slot reservation is issued at one commit point and consumed at the next.
 template <bool ANY_HIT>
-__global__ void __launch_bounds__(TRACE_THREADS, 8) k_trace(const __grid_constant__ DevScene sc, const __grid_constant__ TraceIO io) {
+__global__ void __launch_bounds__(TRACE_THREADS, TRACE_MIN_BLOCKS) k_trace(const __grid_constant__ DevScene sc, const __grid_constant__ TraceIO io) {
     __shared__ float s_rect[RECT_SM_FLOATS * BF_MAX_RECTS];
     __shared__ uint2 s_stack[TRACE_SM_STACK * TRACE_THREADS];
     uint2 l_stack[TRACE_LOCAL_STACK];
