@@ -45,7 +45,7 @@ def fmcw_signal(resample_freq, gain=1.0):
 
 
 def radar_scene(mesh_pos, mesh_faces, spectrum_width=1, max_depth=4, range_bins=1024, bin_m=0.03, smooth_normals=True,
-                extra_meshes=(), phased=None, ground_half=20.0, reflector=True, return_ids=False):
+                extra_meshes=(), phased=None, ground_half=20.0, reflector=True, return_ids=False, omni_area=False):
     """Common 94 GHz FMCW layout of python_scripts/Render.py / Receive.ipynb: Tx and Rx are 5 mm x 5 mm
     rectangles at (0, 0, 0.3) facing +x, ground 20 x 20 diffuse 0.5, corner reflector 0.1 x 0.05 diffuse 1,
     target mesh twosided(roughconductor alpha 0.1).  Receiver `wignerreceiver` (mix_resample) + transmitter
@@ -80,6 +80,8 @@ def radar_scene(mesh_pos, mesh_faces, spectrum_width=1, max_depth=4, range_bins=
         pose = T.translate([0.0, 0.0, 0.3]) * T.rotate([0, 1, 0], 90.0)
         tx_kind, rx_kind = N.BF_TX_PHASED, N.BF_RX_PHASED
         tx_arr, rx_arr = arr(T.translate([0.0, 0.01, 0.0]) * pose), arr(pose)
+    if omni_area:   # `areatransmitter` + `omnidirectional` receiver (Receive.ipynb cells 13, 15 use the omnidirectional receiver)
+        tx_kind, rx_kind = N.BF_TX_AREA, N.BF_RX_OMNIDIRECTIONAL
     s.add_transmitter(tx, FlatScene.endpoint(tx_kind, texture=tex, signal=fmcw_signal(True), array=tx_arr))
     sweep_rate = 6e9 / 200e-6
     f_bandwidth = range_bins * bin_m * 2.0 / C0 * sweep_rate
@@ -102,11 +104,11 @@ def c2_car_body(spectrum_width=1, max_depth=4, n_u=264, n_v=133):
     return radar_scene(p, f, spectrum_width=spectrum_width, max_depth=max_depth)
 
 
-def small_radar(spectrum_width=1, max_depth=4, n_u=24, n_v=13, smooth_normals=True, phased=None):
+def small_radar(spectrum_width=1, max_depth=4, n_u=24, n_v=13, smooth_normals=True, phased=None, omni_area=False):
     """The C2 layout with a few hundred triangles: sized for the brute-force oracle."""
     p, f = meshes.car_body(n_u, n_v)
     p = meshes.transform_points(car_pose().matrix32(), p)
-    return radar_scene(p, f, spectrum_width=spectrum_width, max_depth=max_depth, smooth_normals=smooth_normals, phased=phased)
+    return radar_scene(p, f, spectrum_width=spectrum_width, max_depth=max_depth, smooth_normals=smooth_normals, phased=phased, omni_area=omni_area)
 
 
 def c3_multi_object(spectrum_width=1, max_depth=4, copies=14, n_u=264, n_v=133, f_bins=1024, t_bins=1024):

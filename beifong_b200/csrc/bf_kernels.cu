@@ -791,15 +791,15 @@ int launch_trace_shadow(const DevScene &sc, const Wave &w, const uint32_t *queue
 template <int S>
 static int launch_shade_s(const DevScene &sc, const Wave &w, uint32_t depth, const uint32_t *hit_counts, int grid, uint32_t *next_queue,
                           uint32_t *ctr_block, const LaunchCfg &cfg) {
-    // Specialised kernels for the radar configuration (gen-3 integrator, wigner transmitters): one launch per material class.
-    if (sc.integ.gen == BF_GEN_PHASE && sc.hint_tx_kind == BF_TX_WIGNER) {
-        k_shade<S, BF_GEN_PHASE, BF_TX_WIGNER, BF_BSDF_DIFFUSE, 0><<<grid, 128, 0, cfg.stream>>>(sc, w, depth, hit_counts, next_queue, ctr_block);
-        if (sc.hint_cls1_bsdf == BF_BSDF_ROUGHCONDUCTOR)
-            k_shade<S, BF_GEN_PHASE, BF_TX_WIGNER, BF_BSDF_ROUGHCONDUCTOR, 1><<<grid, 128, 0, cfg.stream>>>(sc, w, depth, hit_counts, next_queue, ctr_block);
-        else
-            k_shade<S, BF_GEN_PHASE, BF_TX_WIGNER, -1, 1><<<grid, 128, 0, cfg.stream>>>(sc, w, depth, hit_counts, next_queue, ctr_block);
-        return 2;
-    }
+    // Specialised kernels for the radar configurations (gen-3 integrator, wigner or area transmitters): one launch per material class.
+#define BF_SHADE(T_, B_, Q_) k_shade<S, BF_GEN_PHASE, T_, B_, Q_><<<grid, 128, 0, cfg.stream>>>(sc, w, depth, hit_counts, next_queue, ctr_block)
+#define BF_SHADE_T(T_) do { \
+        BF_SHADE(T_, BF_BSDF_DIFFUSE, 0); \
+        if (sc.hint_cls1_bsdf == BF_BSDF_ROUGHCONDUCTOR) BF_SHADE(T_, BF_BSDF_ROUGHCONDUCTOR, 1); else BF_SHADE(T_, -1, 1); } while (0)
+    if (sc.integ.gen == BF_GEN_PHASE && sc.hint_tx_kind == BF_TX_WIGNER) { BF_SHADE_T(BF_TX_WIGNER); return 2; }
+    if (sc.integ.gen == BF_GEN_PHASE && sc.hint_tx_kind == BF_TX_AREA) { BF_SHADE_T(BF_TX_AREA); return 2; }
+#undef BF_SHADE_T
+#undef BF_SHADE
     k_shade<S, -1, -1, -1, 2><<<grid, 128, 0, cfg.stream>>>(sc, w, depth, hit_counts, next_queue, ctr_block);
     return 1;
 }
@@ -825,14 +825,15 @@ int launch_primary(const DevScene &sc, const Wave &w, uint64_t seed, uint64_t fi
     io.seed = seed; io.first_sample = first_sample; io.n = n; io.work_cursor = work_cursor; io.hit_count = hit_count; io.n_lanes = w.n_lanes;
     io.total = w.totals + 0; io.profile = profile;
     const int grid = cfg.sm_count * BF_PRIMARY_MIN_BLOCKS;
-    const bool radar = sc.integ.gen == BF_GEN_PHASE && sc.hint_rx_kind == BF_RX_WIGNER;   // specialised: gen-3 integrator, wigner receiver
-    if (sc.S == 1) {
-        if (radar) k_primary<1, BF_GEN_PHASE, BF_RX_WIGNER><<<grid, TRACE_THREADS, 0, cfg.stream>>>(sc, w, io);
-        else k_primary<1, -1, -1><<<grid, TRACE_THREADS, 0, cfg.stream>>>(sc, w, io);
-    } else {
-        if (radar) k_primary<4, BF_GEN_PHASE, BF_RX_WIGNER><<<grid, TRACE_THREADS, 0, cfg.stream>>>(sc, w, io);
-        else k_primary<4, -1, -1><<<grid, TRACE_THREADS, 0, cfg.stream>>>(sc, w, io);
-    }
+    // specialised instantiations: gen-3 integrator with a wigner or an omnidirectional receiver; generic otherwise
+#define BF_PRIMARY(S_, G_, R_) k_primary<S_, G_, R_><<<grid, TRACE_THREADS, 0, cfg.stream>>>(sc, w, io)
+#define BF_PRIMARY_S(S_) do { \
+        if (sc.integ.gen == BF_GEN_PHASE && sc.hint_rx_kind == BF_RX_WIGNER) BF_PRIMARY(S_, BF_GEN_PHASE, BF_RX_WIGNER); \
+        else if (sc.integ.gen == BF_GEN_PHASE && sc.hint_rx_kind == BF_RX_OMNIDIRECTIONAL) BF_PRIMARY(S_, BF_GEN_PHASE, BF_RX_OMNIDIRECTIONAL); \
+        else BF_PRIMARY(S_, -1, -1); } while (0)
+    if (sc.S == 1) BF_PRIMARY_S(1); else BF_PRIMARY_S(4);
+#undef BF_PRIMARY_S
+#undef BF_PRIMARY
     return 1;
 }
 int launch_trace_rays(const DevScene &sc, const float4 *ray_o, const float4 *ray_d, uint32_t n, float4 *hit, uint32_t *occl,

@@ -252,3 +252,28 @@ def test_c5_urban_small_receive_elements(native):
         rel = np.abs(rg["value"][both] - rc["value"][both]) / np.abs(rc["value"][both])
         assert np.percentile(rel, 99) <= 1e-4
     s.close()
+
+
+@pytest.mark.parametrize("width", [1, 4])
+def test_omnidirectional_receiver_area_transmitter(native, width):
+    """`omnidirectional` receiver + `areatransmitter` (the specialised k_primary / k_shade instantiations for them): per-sample
+    records against the oracle.  The omnidirectional receiver draws optical wavelengths (spectrum.h:310-371), so nothing lands
+    inside the radar ADC window; the records carry the path values."""
+    s = configs.small_radar(spectrum_width=width, omni_area=True).commit()
+    orc = OracleScene(s.export(), accel=OracleScene.BVH)
+    n = 20000
+    g, c = s.sample_records(n, seed=4), orc.sample_records(n, seed=4)
+    same_first = (g["first_shape"] == c["first_shape"]) & (g["first_prim"] == c["first_prim"])
+    assert same_first.mean() >= 0.9999
+    agree = same_first & (g["depth"] == c["depth"]) & (g["n_closest"] == c["n_closest"]) & (g["n_shadow"] == c["n_shadow"])
+    assert agree.mean() >= 0.999
+    fin = agree & np.isfinite(c["value"]) & (c["value"] != 0)
+    if fin.sum() > 100:
+        rel = np.abs(g["value"][fin] - c["value"][fin]) / np.abs(c["value"][fin])
+        assert np.percentile(rel, 99) <= 1e-4
+    if width == 1:   # width 4 evaluates the radar spectra at optical wavelengths: the handful of non-zero values are 0 * inf artefacts
+        assert np.array_equal(np.isnan(g["value"]), np.isnan(c["value"]))
+    s.receive(1 << 16, seed=4)
+    gp, cp = s.profile(), orc.receive(1 << 16, seed=4, threads=8)
+    assert gp[..., 2].sum() == cp[..., 2].sum()
+    s.close()
