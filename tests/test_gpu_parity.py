@@ -277,3 +277,39 @@ def test_omnidirectional_receiver_area_transmitter(native, width):
     gp, cp = s.profile(), orc.receive(1 << 16, seed=4, threads=8)
     assert gp[..., 2].sum() == cp[..., 2].sum()
     s.close()
+
+
+def test_c2_full_size_properties(native, monkeypatch):
+    """The bench configuration at full mesh size (69 696 triangles): properties that hold at any sample count -- the index
+    range is additive (two accumulated halves == the whole), the fused and the unfused primary path agree, the wave size does
+    not matter -- plus first hits and range profile against the oracle's BVH on what it finishes in seconds."""
+    s = configs.c2_car_body(1).commit()
+    n = 1 << 22
+    s.receive(2 * n, seed=3)
+    whole = s.profile()
+    s.receive(n, seed=3, first_sample=0)
+    s.receive(n, seed=3, first_sample=n, accumulate=True)
+    halves = s.profile()
+    assert np.array_equal(whole[..., 1:3], halves[..., 1:3])
+    assert whole[..., 2].sum() > 0.99 * 2 * n
+    assert rel_l2(halves[..., 0], whole[..., 0]) <= 1e-5
+    monkeypatch.setenv("BF_WAVE_LANES", str(1 << 20))
+    s.receive(2 * n, seed=3)
+    small_waves = s.profile()
+    monkeypatch.delenv("BF_WAVE_LANES")
+    assert np.array_equal(whole[..., 1:3], small_waves[..., 1:3]) and rel_l2(small_waves[..., 0], whole[..., 0]) <= 1e-5
+    monkeypatch.setenv("BF_FUSED_PRIMARY", "0")
+    s.receive(2 * n, seed=3)
+    unfused = s.profile()
+    monkeypatch.setenv("BF_FUSED_PRIMARY", "1")
+    assert np.array_equal(whole[..., 1:3], unfused[..., 1:3]) and rel_l2(unfused[..., 0], whole[..., 0]) <= 1e-5
+    orc = OracleScene(s.export(), accel=OracleScene.BVH)
+    m = 1 << 17
+    g, c = s.sample_records(m, seed=3), orc.sample_records(m, seed=3)
+    same_first = (g["first_shape"] == c["first_shape"]) & (g["first_prim"] == c["first_prim"])
+    assert same_first.mean() >= 0.9999
+    s.receive(1 << 20, seed=5)
+    gp, cp = s.profile(), orc.receive(1 << 20, seed=5, threads=8)
+    assert gp[..., 2].sum() == cp[..., 2].sum()
+    assert rel_l2(gp[..., 0], cp[..., 0]) <= 1e-3
+    s.close()
