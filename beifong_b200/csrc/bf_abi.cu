@@ -563,6 +563,16 @@ int bf_scene_commit(bf_scene *s, int device) {
     for (const DevRect &r : s->rects)
         for (int a = 0; a < 3; ++a)
             scene_abs = std::max(scene_abs, std::fabs(r.to_world.m[a][3]) + std::fabs(r.to_world.m[a][0]) + std::fabs(r.to_world.m[a][1]));
+    {   // bounds of the meshes, padded like the rectangles' boxes (1e-4 of the largest coordinate)
+        float lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY}, mag = 1e-3f;
+        for (const BvhTriIn &t : tris)
+            for (int a = 0; a < 3; ++a) {
+                lo[a] = std::min(lo[a], std::min(t.p0[a], std::min(t.p1[a], t.p2[a])));
+                hi[a] = std::max(hi[a], std::max(t.p0[a], std::max(t.p1[a], t.p2[a])));
+            }
+        for (int a = 0; a < 3; ++a) if (!tris.empty()) mag = std::max(mag, std::max(std::fabs(lo[a]), std::fabs(hi[a])));
+        for (int a = 0; a < 3; ++a) { s->dev.mesh_lo[a] = lo[a] - 1e-4f * mag; s->dev.mesh_hi[a] = hi[a] + 1e-4f * mag; }
+    }
     WideBvh bvh;
     build_wide_bvh(tris, 4e-6f * std::max(scene_abs, 1e-3f), bvh);
     if (bvh.stats.depth > BF_TRACE_STACK_DEPTH)

@@ -85,6 +85,7 @@ struct DevScene {
     // what the whole scene has in common, for the specialised shade kernels: the kind shared by every transmitter and by
     // every BSDF (front and back) of material class 1, or -1
     int32_t hint_tx_kind, hint_cls1_bsdf, hint_rx_kind;
+    float mesh_lo[3], mesh_hi[3];   // padded world-space bounds of all mesh triangles: rays that miss them skip the traversal
     double phase_denom;        // (lambda_max - lambda_min) / 2 * 1e-9 evaluated like ray.h:92
 };
 

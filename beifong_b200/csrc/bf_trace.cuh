@@ -90,7 +90,7 @@ struct TraceLane {
 // decided (any-hit occluded by a rectangle, or no BVH).
 #define RECT_SM_FLOATS 19   // per rectangle in shared memory: 12 to_object, 1 shape id, 6 padded world box
 
-template <bool ANY_HIT>
+template <bool ANY_HIT, bool CULL = true>
 __device__ __forceinline__ bool trace_begin(const DevScene &sc, const float *s_rect, TraceLane &L) {
     L.best.t = L.maxt; L.best.u = 0.f; L.best.v = 0.f; L.best.slot = BF_NONE; L.best.shape = BF_NONE; L.best.prim = BF_NONE;
     L.occluded = false;
@@ -133,6 +133,15 @@ __device__ __forceinline__ bool trace_begin(const DevScene &sc, const float *s_r
         }
     }
     if (sc.n_nodes == 0) return false;
+    if (CULL) {   // Rays that miss the padded bounds of the meshes within [mint, closest hit so far] skip the traversal altogether
+        // (C2: the car fills a few percent of the receiver's hemisphere; most shadow rays never come near it).
+        float x0 = (sc.mesh_lo[0] - o.x) * L.idx, x1 = (sc.mesh_hi[0] - o.x) * L.idx;
+        float y0 = (sc.mesh_lo[1] - o.y) * L.idy, y1 = (sc.mesh_hi[1] - o.y) * L.idy;
+        float z0 = (sc.mesh_lo[2] - o.z) * L.idz, z1 = (sc.mesh_hi[2] - o.z) * L.idz;
+        float t_in = fmaxf(fmaxf(fminf(x0, x1), fminf(y0, y1)), fmaxf(fminf(z0, z1), t_lo));
+        float t_out = fminf(fminf(fmaxf(x0, x1), fmaxf(y0, y1)), fminf(fmaxf(z0, z1), L.best.t * 1.001f));
+        if (t_in > t_out * 1.001f) return false;
+    }
     L.octinv = (d.x < 0.f ? 0u : 4u) | (d.y < 0.f ? 0u : 2u) | (d.z < 0.f ? 0u : 1u);
     L.ngroup = make_uint2(0u, 0x80000000u);
     L.sp = 0;
@@ -387,6 +396,9 @@ __global__ void __launch_bounds__(TRACE_THREADS, TRACE_MIN_BLOCKS) k_trace(const
         if (busy == 0) continue;
         const bool drained = out_of_work;
         const int min_busy = drained ? 1 : TRACE_REFILL;
+        // Most rays are decided in trace_begin (rectangles, mesh bounds): while rays remain, keep refilling until enough
+        // lanes actually traverse, so that a node step is never run for a handful of lanes
+        if (!drained && fin != 0 && __popc(busy) < min_busy) continue;
         // ---- traverse until too few lanes are left ----
         do {
             if (state == BUSY) {
