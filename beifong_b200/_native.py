@@ -100,6 +100,7 @@ PROTOTYPES = {
     "bf_profile_size": (C.c_int, [vp, P(u32), P(u32), P(u32)]),
     "bf_receive": (C.c_int, [vp, u64, u64, u64, C.c_int]),
     "bf_profile_read": (C.c_int, [vp, P(f32), C.c_size_t]),
+    "bf_profile_develop": (C.c_int, [vp, u32, vp, C.c_size_t]),
     "bf_profile_device_ptr": (C.c_int, [vp, P(vp), P(C.c_size_t), P(vp)]),
     "bf_synchronize": (C.c_int, [vp]),
     "bf_trace_first_hits": (C.c_int, [vp, P(f32), P(f32), P(f32), P(f32), u64, P(u32), P(u32), P(f32), P(f32), P(f32)]),

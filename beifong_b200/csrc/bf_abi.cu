@@ -164,6 +164,7 @@ struct bf_scene {
     DevBuf<DevRect> d_rects; DevBuf<DevShape> d_shapes; DevBuf<bf_bsdf_desc> d_bsdfs;
     DevBuf<DevSpectrum> d_spectra; DevBuf<float> d_spec_pool; DevBuf<DevEndpoint> d_txs, d_rx; DevBuf<DevVElem> d_velems;
     DevBuf<float> d_profile; size_t profile_floats = 0;
+    DevBuf<uint32_t> d_developed;    // bf_profile_develop output (fp32 or fp16 components)
     // image of the geometry tables in pinned host memory (re-upload without a rebuild)
     void *h_geom = nullptr; size_t h_geom_bytes = 0, h_nodes_bytes = 0, h_tris_bytes = 0, h_nrm_bytes = 0;
     // wave
@@ -265,7 +266,7 @@ void bf_scene_destroy(bf_scene *s) {
         free_wave(s);
         s->d_nodes.release(); s->d_tris.release(); s->d_tri_nrm.release(); s->d_rects.release(); s->d_shapes.release();
         s->d_bsdfs.release(); s->d_spectra.release(); s->d_spec_pool.release(); s->d_txs.release(); s->d_rx.release(); s->d_velems.release();
-        s->d_profile.release(); s->d_totals.release();
+        s->d_profile.release(); s->d_developed.release(); s->d_totals.release();
         if (s->h_geom) cudaFreeHost(s->h_geom);
         if (s->ev_fork) cudaEventDestroy(s->ev_fork);
         if (s->ev_begin) cudaEventDestroy(s->ev_begin);
@@ -824,6 +825,26 @@ int bf_profile_read(bf_scene *s, float *dst, size_t n_floats) {
     if (n_floats < s->profile_floats) return fail(s, BF_ERR_INVALID, "bf_profile_read: destination too small");
     BF_CUDA(cudaSetDevice(s->device));
     BF_CUDA(cudaMemcpyAsync(dst, s->d_profile.p, s->profile_floats * 4, cudaMemcpyDeviceToHost, s->stream));
+    BF_CUDA(cudaStreamSynchronize(s->stream));
+    return BF_OK;
+}
+
+int bf_profile_develop(bf_scene *s, uint32_t component_format, void *dst, size_t dst_bytes) {
+    if (!s || !dst) return BF_ERR_INVALID;
+    if (!s->committed) return fail(s, BF_ERR_STATE, "bf_profile_develop: scene not committed");
+    if (component_format != BF_COMPONENT_FLOAT32 && component_format != BF_COMPONENT_FLOAT16)
+        return fail(s, BF_ERR_UNSUPPORTED, "bf_profile_develop: component_format must be float32 or float16");
+    const uint32_t C = s->dev.channels;
+    if (C <= 3) return fail(s, BF_ERR_UNSUPPORTED, "bf_profile_develop: a storage without AOV channels has no developed form in the reference");
+    const size_t n_bins = (size_t) s->dev.film_w * s->dev.film_h, esz = component_format == BF_COMPONENT_FLOAT16 ? 2 : 4;
+    const size_t bytes = n_bins * (C - 1) * esz;
+    if (dst_bytes < bytes) return fail(s, BF_ERR_INVALID, "bf_profile_develop: destination too small");
+    BF_CUDA(cudaSetDevice(s->device));
+    BF_CUDA(s->d_developed.alloc((bytes + 3) / 4));
+    LaunchCfg cfg{s->stream, s->sm_count};
+    launch_develop(s->d_profile.p, s->d_developed.p, (uint32_t) n_bins, C, esz == 2, cfg);
+    BF_CUDA(cudaGetLastError());
+    BF_CUDA(cudaMemcpyAsync(dst, s->d_developed.p, bytes, cudaMemcpyDeviceToHost, s->stream));
     BF_CUDA(cudaStreamSynchronize(s->stream));
     return BF_OK;
 }

@@ -10,6 +10,7 @@
 //               (phase.cpp:85-138, range.cpp:141-161, time.cpp:118-153, integrator.cpp:1588-1665,
 //                signalblock.cpp:162-169)
 // Compiled with -fmad=false: see bf_math.h for the arithmetic contract.
+#include <cuda_fp16.h>
 #include "bf_wave.h"
 #include "bf_device.cuh"
 #include "bf_trace.cuh"
@@ -219,6 +220,9 @@ struct PrimaryIO {
     float *profile;
 };
 
+#ifndef BF_PRIMARY_CULL
+#define BF_PRIMARY_CULL false
+#endif
 #ifndef BF_PRIMARY_MIN_BLOCKS
 #define BF_PRIMARY_MIN_BLOCKS 8
 #endif
@@ -316,7 +320,7 @@ __global__ void __launch_bounds__(TRACE_THREADS, BF_PRIMARY_MIN_BLOCKS) k_primar
                     smp = i;
                     raygen_sample<S, GEN, RXK>(sc, io.seed, io.first_sample + i, ps);
                     L.o = ps.ray.o; L.d = ps.ray.d; L.mint = ps.ray.mint; L.maxt = ps.ray.maxt;
-                    state = trace_begin<false, false>(sc, s_rect, L) ? BUSY : FINISHED;   // no bounds cull: a step for 2 lanes costs what one for 28 does
+                    state = trace_begin<false, BF_PRIMARY_CULL>(sc, s_rect, L) ? BUSY : FINISHED;
                 } else {
                     state = EXHAUSTED;
                 }
@@ -327,6 +331,7 @@ __global__ void __launch_bounds__(TRACE_THREADS, BF_PRIMARY_MIN_BLOCKS) k_primar
         if (busy == 0 && finm == 0) break;
         if (busy == 0) continue;
         const int min_busy = out_of_work ? 1 : TRACE_REFILL;
+        if (BF_PRIMARY_CULL && !out_of_work && finm != 0 && __popc(busy) < min_busy) continue;
         do {
             if (state == BUSY) {
                 if (!trace_step<false>(sc, s_stack, l_stack, L)) state = FINISHED;
@@ -850,6 +855,37 @@ int launch_trace_rays(const DevScene &sc, const float4 *ray_o, const float4 *ray
 int launch_resolve_hits(const DevScene &sc, const float4 *hit, uint32_t n, uint32_t *shape, uint32_t *prim, const LaunchCfg &cfg) {
     if (n == 0) return 0;
     k_resolve_hits<<<(n + 255) / 256, 256, 0, cfg.stream>>>(sc, hit, n, shape, prim);
+    return 1;
+}
+
+// =========================================================================================================
+// develop: HDRADC::bitmap(raw = false) (hdradc.cpp:219-275) -- the step after the path
+// =========================================================================================================
+// The reference flags channel 2 of the storage as the Struct weight field and converts to a target without it:
+// every remaining channel becomes value * (1.f / weight) (struct.cpp:1761-1766, 1810-1811), stored in the ADC's
+// component format.  An empty bin (weight 0) therefore develops to 0 * inf = NaN, as it does in the reference.
+// One thread per output element; consecutive threads read consecutive floats of the raw profile (one skipped per
+// bin), the weight comes from the same lines.  HBM-bound: 4 C bytes read and 4 (C - 1) or 2 (C - 1) written per bin.
+template <typename OUT>
+__global__ void __launch_bounds__(256) k_develop(const float *__restrict__ raw, OUT *__restrict__ out, uint32_t n_bins, uint32_t C) {
+    const uint32_t Co = C - 1u;
+    const uint64_t total = (uint64_t) n_bins * Co, stride = (uint64_t) gridDim.x * blockDim.x;
+    for (uint64_t j = (uint64_t) blockIdx.x * blockDim.x + threadIdx.x; j < total; j += stride) {
+        const uint32_t bin = (uint32_t) (j / Co), c = (uint32_t) (j - (uint64_t) bin * Co);
+        const float *px = raw + (size_t) bin * C;
+        const float inv_weight = 1.f / px[2];
+        const float v = px[c < 2u ? c : c + 1u] * inv_weight;
+        if constexpr (sizeof(OUT) == 2) out[j] = __float2half_rn(v);
+        else out[j] = v;
+    }
+}
+
+int launch_develop(const float *raw, void *out, uint32_t n_bins, uint32_t channels, bool half_out, const LaunchCfg &cfg) {
+    if (n_bins == 0 || channels < 2) return 0;
+    const uint64_t total = (uint64_t) n_bins * (channels - 1u);
+    const int grid = (int) std::min<uint64_t>((total + 255) / 256, (uint64_t) cfg.sm_count * 8);
+    if (half_out) k_develop<__half><<<grid, 256, 0, cfg.stream>>>(raw, (__half *) out, n_bins, channels);
+    else k_develop<float><<<grid, 256, 0, cfg.stream>>>(raw, (float *) out, n_bins, channels);
     return 1;
 }
 

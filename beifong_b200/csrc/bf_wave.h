@@ -65,6 +65,7 @@ int launch_trace_shadow(const DevScene &sc, const Wave &w, const uint32_t *queue
 int launch_shade(const DevScene &sc, const Wave &w, uint32_t depth, const uint32_t *hit_counts, uint32_t n_bound,
                  uint32_t *next_queue, uint32_t *ctr_block, const LaunchCfg &cfg);
 int launch_finalize(const DevScene &sc, const Wave &w, uint32_t n, float *profile, const LaunchCfg &cfg);
+int launch_develop(const float *raw, void *out, uint32_t n_bins, uint32_t channels, bool half_out, const LaunchCfg &cfg);
 // Stand-alone ray queries (Scene::ray_intersect_preliminary / ray_test for caller-provided rays)
 int launch_trace_rays(const DevScene &sc, const float4 *ray_o, const float4 *ray_d, uint32_t n, float4 *hit, uint32_t *occl,
                       uint32_t *work_cursor, const LaunchCfg &cfg);

@@ -217,6 +217,20 @@ class FlatScene:
         self._ck(N.lib().bf_profile_read(self._h, _fp(out), out.size), "bf_profile_read")
         return out
 
+    def bitmap(self, raw=False, component_format="float16"):
+        """HDRADC::bitmap (hdradc.cpp:219-275): raw=True is the un-normalised fp32 storage; raw=False divides every
+        channel by the weight channel on the device and drops it ([f][t][channels - 1], float16 by default as in
+        the reference's `component_format`)."""
+        if raw:
+            return self.profile()
+        fmt = {"float32": (0, np.float32), "float16": (1, np.float16)}.get(component_format)
+        if fmt is None:
+            raise BeifongError(f'The "component_format" parameter must either be equal to "float16" or "float32" here. Found {component_format} instead.')
+        h, w, c = self.profile_shape()
+        out = np.empty((h, w, max(c - 1, 0)), dtype=fmt[1])
+        self._ck(N.lib().bf_profile_develop(self._h, fmt[0], out.ctypes.data_as(C.c_void_p), out.nbytes), "bf_profile_develop")
+        return out
+
     def profile_device(self):
         """(device pointer, n_floats, cuda stream handle) of the accumulated profile."""
         p, n, st = C.c_void_p(), C.c_size_t(), C.c_void_p()

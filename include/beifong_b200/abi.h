@@ -246,6 +246,15 @@ int bf_receive(bf_scene *s, uint64_t seed, uint64_t first_sample, uint64_t n_sam
 /* HDRADC::bitmap(raw=true) (hdradc.cpp:219-233): [f][t][channel] fp32, un-normalised.
  * Synchronises the scene's stream. */
 int bf_profile_read(bf_scene *s, float *dst, size_t n_floats);
+/* HDRADC::bitmap(raw=false) (hdradc.cpp:219-275), the step after the path: channel 2 of the storage is the
+ * Struct weight field; every other channel is multiplied by 1.f / weight (struct.cpp:1761-1766, 1810-1811) and
+ * stored as [f][t][channels - 1] in the ADC's component format (hdradc.cpp:134-144; the reference's default is
+ * float16).  Bins that received no sample develop to NaN (0 * inf), as in the reference.  Runs on the device,
+ * then copies to `dst` (dst_bytes >= bins * (channels - 1) * sizeof(component)); synchronises the scene's
+ * stream.  `uint32` components and 3-channel storages (no AOV channels: the reference's converter looks up a
+ * "Y" field the unnamed source does not have) return BF_ERR_UNSUPPORTED. */
+enum { BF_COMPONENT_FLOAT32 = 0, BF_COMPONENT_FLOAT16 = 1 };
+int bf_profile_develop(bf_scene *s, uint32_t component_format, void *dst, size_t dst_bytes);
 /* Device pointer of the accumulated profile + the stream it is produced on (for a caller
  * that reduces it with NCCL, §8e). */
 int bf_profile_device_ptr(bf_scene *s, void **dptr, size_t *n_floats, void **cuda_stream);

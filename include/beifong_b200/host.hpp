@@ -67,9 +67,23 @@ public:
     void prepare(const std::vector<std::string> &channels) { m_channels = channels; }
     const std::vector<std::string> &channels() const { return m_channels; }
     // ADC::bitmap(raw = true): the un-normalised fp32 buffer [f][t][channel] (hdradc.cpp:219-233)
-    const std::vector<float> &bitmap(bool raw = true) const {
-        if (!raw) throw NotImplementedError("ADC::bitmap(raw=false): develop() is outside the accelerated path");
-        return m_storage;
+    // ADC::bitmap(raw = false): every channel times 1.f / weight, weight channel dropped (hdradc.cpp:235-275), developed on
+    // the device from the profile of the last receive(); fp32 components here, bitmap_f16() for the reference's default.
+    const std::vector<float> &bitmap(bool raw = true) {
+        if (raw) return m_storage;
+        if (!m_source) throw Error("ADC::bitmap(raw=false): nothing received yet");
+        const size_t n = (size_t) m_w * m_h * (m_channels.size() - 1);
+        m_developed.resize(n);
+        if (int rc = bf_profile_develop(m_source, BF_COMPONENT_FLOAT32, m_developed.data(), n * sizeof(float)))
+            throw_rc(rc, "bf_profile_develop");
+        return m_developed;
+    }
+    std::vector<uint16_t> bitmap_f16() {
+        if (!m_source) throw Error("ADC::bitmap(raw=false): nothing received yet");
+        std::vector<uint16_t> out((size_t) m_w * m_h * (m_channels.size() - 1));
+        if (int rc = bf_profile_develop(m_source, BF_COMPONENT_FLOAT16, out.data(), out.size() * sizeof(uint16_t)))
+            throw_rc(rc, "bf_profile_develop");
+        return out;
     }
     uint32_t width() const { return m_w; }
     uint32_t height() const { return m_h; }
@@ -78,8 +92,15 @@ private:
     friend class Integrator;
     bf_adc_desc m_desc;
     std::vector<std::string> m_channels;
-    std::vector<float> m_storage;
+    std::vector<float> m_storage, m_developed;
     uint32_t m_w = 0, m_h = 0;
+    bf_scene *m_source = nullptr;      // scene of the last receive() (must outlive the ADC's developed reads)
+    void throw_rc(int rc, const char *what) const {
+        const char *msg = bf_last_error(m_source);
+        std::string text = std::string(what) + ": " + (msg && *msg ? msg : "error");
+        if (rc == BF_ERR_UNSUPPORTED) throw NotImplementedError(text);
+        throw Error(text);
+    }
 };
 
 // Signal block shared by the wigner / phased endpoints (wignertransmitter.cpp:59-102): same property names.
@@ -259,7 +280,7 @@ public:
         }
         uint32_t w = 0, h = 0, c = 0;
         scene.check(bf_profile_size(scene.handle(), &w, &h, &c), "bf_profile_size");
-        adc->m_w = w; adc->m_h = h;
+        adc->m_w = w; adc->m_h = h; adc->m_source = scene.handle();
         adc->m_storage.resize((size_t) w * h * c);
         scene.check(bf_profile_read(scene.handle(), adc->m_storage.data(), adc->m_storage.size()), "bf_profile_read");   // adc->put(block)
         m_samples_done = done;

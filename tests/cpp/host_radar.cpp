@@ -8,6 +8,7 @@
 #include <chrono>
 #include <cmath>
 #include <cstdio>
+#include <cstring>
 #include <dlfcn.h>
 #include <thread>
 
@@ -57,7 +58,7 @@ int main(int argc, char **argv) {
     EXPECT((throws<Error>([] { ADC a; Receiver r("wignerreceiver", 0, a, Signal(), "sideways"); }, "receive_type")));
     EXPECT((throws<Error>([] { Integrator i(4, 0); }, "rr_depth")));
     EXPECT((throws<Error>([] { Integrator i(-3); }, "max_depth")));
-    EXPECT((throws<NotImplementedError>([] { ADC a; a.bitmap(false); })));
+    EXPECT((throws<Error>([] { ADC a; a.bitmap(false); }, "nothing received")));
     {
         Scene s(constants(C0, C0 / 97e9f * 1e9f, C0 / 91e9f * 1e9f));
         EXPECT((throws<Error>([&] { const float m[16] = {1,0,0,0, 0,1,0,0, 0,0,1,0, 0,0,0,1}; s.add_rectangle(m, 99); }, "bsdf id out of range")));
@@ -119,6 +120,23 @@ int main(int argc, char **argv) {
     std::printf("receive: %llu samples, weight channel %.0f vs %.0f, range-profile rel L2 vs oracle %.3e\n", (unsigned long long) n, wg, wc, rel);
     EXPECT(wg == wc);
     EXPECT(den > 0 && rel <= 1e-3);
+
+    // bitmap(raw = false): channels Y, A, phase.bin0 = raw * (1.f / W)
+    {
+        const std::vector<float> &d = rx.adc()->bitmap(false);
+        EXPECT(d.size() == 1024 * 3);
+        bool same = true;
+        for (size_t b = 0; b < 1024; ++b) {
+            const float inv = 1.f / g[4 * b + 2];
+            const float want[3] = {g[4 * b] * inv, g[4 * b + 1] * inv, g[4 * b + 3] * inv};
+            for (int k = 0; k < 3; ++k) {
+                const float got = d[3 * b + k];
+                if (std::isnan(want[k]) ? !std::isnan(got) : std::memcmp(&want[k], &got, 4) != 0) same = false;
+            }
+        }
+        EXPECT(same);
+        EXPECT(rx.adc()->bitmap_f16().size() == 1024 * 3);
+    }
 
     // cancel() from another thread stops receive() between slices; it reports "cancelled" like the reference
     std::thread killer([&] { std::this_thread::sleep_for(std::chrono::milliseconds(30)); integ.cancel(); });

@@ -313,3 +313,39 @@ def test_c2_full_size_properties(native, monkeypatch):
     assert gp[..., 2].sum() == cp[..., 2].sum()
     assert rel_l2(gp[..., 0], cp[..., 0]) <= 1e-3
     s.close()
+
+
+@pytest.mark.parametrize("component_format", ["float32", "float16"])
+def test_develop_bitmap(native, component_format):
+    """HDRADC::bitmap(raw=False) (hdradc.cpp:219-275): weight-normalised channels, bit-exact against the restatement,
+    on a 1-D range profile and on a 2-D range-time frame with empty bins (0 * inf = NaN, as in the reference)."""
+    from oracle.develop import develop
+    frame = configs.small_radar(spectrum_width=1)
+    frame.set_adc(t_bins=64, f_bins=256, t_bandwidth=200e-6, f_bandwidth=256 * 0.12 * 2.0 / configs.C0 * (6e9 / 200e-6))
+    for s in (configs.small_radar(spectrum_width=1).commit(), frame.commit()):
+        s.receive(1 << 17, seed=3)
+        raw = s.bitmap(raw=True)
+        assert raw.shape[-1] > 3 and raw[..., 2].sum() > 0
+        dev = s.bitmap(raw=False, component_format=component_format)
+        ref = develop(raw, component_format)
+        assert dev.shape == ref.shape == raw.shape[:-1] + (raw.shape[-1] - 1,) and dev.dtype == ref.dtype
+        uint = np.uint32 if component_format == "float32" else np.uint16
+        nan = np.isnan(ref)
+        assert np.array_equal(np.isnan(dev), nan)       # empty bins; the NaN payload is the processor's (x86 vs sm_100)
+        assert np.array_equal(dev.view(uint)[~nan], ref.view(uint)[~nan])
+        filled = raw[..., 2] > 0
+        assert np.isfinite(dev[filled].astype(np.float32)).all()
+        # a developed bin is the mean over the samples that landed in it: developing is idempotent under accumulation of
+        # the same samples twice (values and weights both double)
+        s.receive(1 << 17, seed=3, accumulate=True)
+        dev2 = s.bitmap(raw=False, component_format="float32")
+        ref1 = develop(raw, "float32")
+        assert rel_l2(dev2[filled].astype(np.float64), ref1[filled].astype(np.float64)) <= 1e-4     # fp32 atomics: summation order
+        s.close()
+
+
+def test_develop_errors(native):
+    s = configs.small_radar(spectrum_width=1).commit()
+    with pytest.raises(Exception, match="component_format"):
+        s.bitmap(raw=False, component_format="uint32")
+    s.close()

@@ -503,3 +503,22 @@ def test_c4_animated_frame_range_bins():
     # the pose helper turns the boresight about z
     p0, p64 = configs.c4_pose(0).matrix32(), configs.c4_pose(64).matrix32()
     assert np.allclose(p0[:3, 2], [0, -1, 0], atol=1e-6) and np.allclose(p64[:3, 2], [1, 0, 0], atol=1e-6)
+
+
+def test_develop_restatement_known_answers():
+    """HDRADC::bitmap(raw=False): channel 2 is the weight (hdradc.cpp:256-259), value * (1.f / weight)
+    (struct.cpp:1766, 1811), float16 rounds to nearest even; an empty bin is 0 * inf = NaN."""
+    from oracle.develop import develop
+    raw = np.array([[[6.0, 3.0, 3.0, 1.5], [1.0, 1.0, 4096.0, 2049.0], [0.0, 0.0, 0.0, 0.0], [1e6, 1.0, 1.0, -2.0]]], np.float32)
+    f32 = develop(raw, "float32")
+    assert f32.shape == (1, 4, 3) and f32.dtype == np.float32
+    assert f32[0, 0].tolist() == [2.0, 1.0, 0.5]
+    inv = np.float32(1.0) / np.float32(4096.0)
+    assert f32[0, 1, 2] == np.float32(2049.0) * inv
+    assert np.isnan(f32[0, 2]).all()
+    f16 = develop(raw, "float16")
+    assert f16.dtype == np.float16 and f16[0, 0].tolist() == [2.0, 1.0, 0.5]
+    assert f16[0, 1, 2] == np.float16(0.5)            # 2049/4096 = 0.500244..: ties to even on the 10-bit mantissa
+    assert np.isinf(f16[0, 3, 0]) and f16[0, 3, 2] == np.float16(-2.0)   # 1e6 overflows float16
+    with pytest.raises(ValueError):
+        develop(raw, "uint32")
