@@ -164,6 +164,7 @@ struct bf_scene {
     DevBuf<DevRect> d_rects; DevBuf<DevShape> d_shapes; DevBuf<bf_bsdf_desc> d_bsdfs;
     DevBuf<DevSpectrum> d_spectra; DevBuf<float> d_spec_pool; DevBuf<DevEndpoint> d_txs, d_rx; DevBuf<DevVElem> d_velems;
     DevBuf<float> d_profile; size_t profile_floats = 0;
+    DevFilter filter; bool wide_filter = false;    // discretised reconstruction filter when wider than one bin
     DevBuf<uint32_t> d_developed;    // bf_profile_develop output (fp32 or fp16 components)
     // image of the geometry tables in pinned host memory (re-upload without a rebuild)
     void *h_geom = nullptr; size_t h_geom_bytes = 0, h_nodes_bytes = 0, h_tris_bytes = 0, h_nrm_bytes = 0;
@@ -203,6 +204,25 @@ static void record(bf_scene *s, uint32_t tag, const void *a, size_t na, const vo
     if (nb) memcpy(p, b, nb); p += nb;
     if (nc) memcpy(p, c, nc); p += nc;
     if (nd) memcpy(p, d, nd);
+}
+
+// ReconstructionFilter::init_discretization (rfilter.cpp:9-20) for the ADC's filter; GaussianFilter::eval (gaussian.cpp:47-49),
+// TentFilter::eval (tent.cpp:36-38).  Host arithmetic, fp32 as in the reference's scalar variants.
+static void build_filter(bf_scene *s) {
+    const bf_adc_desc &a = s->adc;
+    s->wide_filter = s->has_adc && s->integ.gen == BF_GEN_PHASE && a.filter_radius > 0.5f + BF_RAY_EPS;
+    if (!s->wide_filter) return;
+    DevFilter &f = s->filter;
+    const float radius = a.filter_radius;
+    const float stddev = radius / 4.f, alpha = -1.f / (2.f * stddev * stddev), bias = std::exp(alpha * (radius * radius));
+    for (int i = 0; i < 31; ++i) {
+        const float x = (radius * (float) i) / 31.f;
+        f.values[i] = a.filter_kind == 1 ? std::max(0.f, std::exp(alpha * (x * x)) - bias) : std::max(0.f, 1.f - std::fabs(x * (1.f / radius)));
+    }
+    f.values[31] = 0.f;
+    f.radius = radius; f.scale = 31.f / radius;
+    f.n = (uint32_t) (int) std::ceil((radius - 2.f * BF_RAY_EPS) * 2.f);
+    f.border = (uint32_t) (int) std::ceil(radius - .5f - 2.f * BF_RAY_EPS);
 }
 
 static uint32_t n_channels(const bf_scene *s) {
@@ -401,7 +421,13 @@ int bf_scene_set_adc(bf_scene *s, const bf_adc_desc *desc) {
     if (!(desc->t_bandwidth > 0.f) || !(desc->f_bandwidth > 0.f)) return fail(s, BF_ERR_INVALID, "bf_scene_set_adc: bandwidths must be positive");
     // Receivers warn when the reconstruction filter is wider than one bin (phasedreceiver.cpp:59-62);
     // the accelerated path implements the single-bin branch of SignalBlock::put (signalblock.cpp:162-169).
-    if (desc->filter_radius > 0.5f + BF_RAY_EPS) return fail(s, BF_ERR_UNSUPPORTED, "bf_scene_set_adc: reconstruction filters wider than box/0.5 are not on the accelerated path");
+    // Wider filters take the n x n splat (signalblock.cpp:113-161): gaussian (radius = 4 stddev, gaussian.cpp:37-45) and tent
+    // (radius 1, tent.cpp:30-34); the other rfilter plugins are not on the accelerated path.
+    if (desc->filter_radius > 0.5f + BF_RAY_EPS) {
+        if (desc->filter_kind == 1) { if (!(desc->filter_radius <= 8.f)) return fail(s, BF_ERR_INVALID, "bf_scene_set_adc: gaussian filter radius (4 stddev) must be <= 8 bins"); }
+        else if (desc->filter_kind == 2) { if (desc->filter_radius != 1.f) return fail(s, BF_ERR_INVALID, "bf_scene_set_adc: the tent filter has radius 1"); }
+        else return fail(s, BF_ERR_UNSUPPORTED, "bf_scene_set_adc: wide reconstruction filters other than gaussian / tent are not on the accelerated path");
+    }
     if (s->committed) return fail(s, BF_ERR_STATE, "bf_scene_set_adc: scene already committed");
     s->adc = *desc; s->has_adc = true;
     record(s, BF_TAG_ADC, desc, sizeof(*desc));
@@ -505,6 +531,7 @@ static int upload_tables(bf_scene *s) {
     d.rects = s->d_rects.p; d.shapes = s->d_shapes.p; d.bsdfs = s->d_bsdfs.p; d.spectra = s->d_spectra.p;
     d.spec_pool = s->d_spec_pool.p; d.txs = s->d_txs.p; d.rx = s->d_rx.p; d.velems = s->d_velems.p;
     d.adc = s->adc; d.integ = s->integ;
+    build_filter(s);
     film_size(s, d.film_w, d.film_h); d.channels = n_channels(s);
     d.rx_needs_aperture = s->rx.kind != BF_RX_PERSPECTIVE;   // Sensor::needs_aperture_sample
     d.hint_cls1_bsdf = cls1_kind < 0 ? -1 : cls1_kind;
@@ -732,7 +759,8 @@ static int run_wave(bf_scene *s, WaveSlot &sl, uint64_t seed, uint64_t first, ui
     Wave w = sl.wave;
     if (!with_records) { w.records = nullptr; w.sample_of = nullptr; }
     // BF_FUSED_PRIMARY=0 selects the unfused raygen + trace pair (lanes = samples), kept for A/B measurements
-    const bool fused = env_u32("BF_FUSED_PRIMARY", 1, 0, 1) != 0;
+    // wide reconstruction filters: every sample (misses too) is splatted by k_finalize_wide, so lanes = samples
+    const bool fused = env_u32("BF_FUSED_PRIMARY", 1, 0, 1) != 0 && !s->wide_filter;
     if (!fused) w.sample_of = nullptr;
     LaunchCfg cfg; cfg.stream = sl.stream; cfg.sm_count = s->sm_count;
     uint32_t *ctr = w.counters;
@@ -767,7 +795,7 @@ static int run_wave(bf_scene *s, WaveSlot &sl, uint64_t seed, uint64_t first, ui
             if (sl.h_counts[0] == 0) break;
         }
     }
-    timed(BF_K_FINALIZE, [&] { return launch_finalize(sc, w, n, profile, cfg); });
+    timed(BF_K_FINALIZE, [&] { return launch_finalize(sc, w, n, profile, s->wide_filter ? &s->filter : nullptr, cfg); });
     s->stats.kernel_launches += launches;
     BF_CUDA(cudaGetLastError());
     return BF_OK;

@@ -594,7 +594,9 @@ __device__ __forceinline__ void agg_add(float *dst, int key, float val, uint32_t
 
 // What one sample adds to the profile (the tail of receive_sample / render_sample).
 struct Splat {
-    int pixel;          // destination pixel or -1
+    int pixel;          // destination pixel or -1 (box filter)
+    float posx, posy;   // fractional sample position and the block offset (wide filters)
+    int off_x, off_y;
     float val_a;        // weighted value: channel Y (gen 3) or X = Y = Z (gen 1/2)
     bool cnt_valid;     // alpha channel
     int var_ch;         // the single non-zero wrapper channel of this sample, or -1
@@ -677,6 +679,7 @@ __device__ __forceinline__ Splat finalize_lane(const DevScene &sc, const Wave &w
         }
     }
     sp.pixel = pixel_of(sc, posx, posy, off_x, off_y);
+    sp.posx = posx; sp.posy = posy; sp.off_x = off_x; sp.off_y = off_y;
     return sp;
 }
 
@@ -759,6 +762,51 @@ __global__ void __launch_bounds__(FIN_THREADS) k_finalize(const __grid_constant_
     }
 }
 
+// SignalBlock::put, filters wider than one bin (signalblock.cpp:113-161): the sample is spread over an n x n footprint with
+// separable weights looked up in the discretised filter.  The reference splats into a block with a border of `border` bins
+// and crops it when the block is put into the ADC storage (signalblock.cpp:49-77): here the crop is the bounds test on the
+// destination bin.  Float-to-int conversions saturate (the reference's are undefined for non-finite positions).
+__device__ __forceinline__ float filter_weight(const DevFilter &f, float x) {
+    const int index = min((int) fabsf(x * f.scale), 31);          // rfilter.h:62-65
+    return f.values[max(index, 0)];
+}
+template <int S>
+__global__ void __launch_bounds__(FIN_THREADS) k_finalize_wide(const __grid_constant__ DevScene sc, const __grid_constant__ Wave w, uint32_t n,
+                                                              float *__restrict__ profile, const __grid_constant__ DevFilter f) {
+    if (w.n_lanes) n = min(n, *w.n_lanes);
+    const uint32_t C = sc.channels;
+    const uint32_t n_fixed = sc.integ.gen == BF_GEN_PHASE ? 3u : 5u;
+    const int border = (int) f.border, size_x = (int) sc.film_w + 2 * border, size_y = (int) sc.film_h + 2 * border;
+    const uint32_t stride = gridDim.x * blockDim.x;
+    for (uint32_t l = blockIdx.x * blockDim.x + threadIdx.x; l < n; l += stride) {
+        const Splat sp = finalize_lane<S>(sc, w, l);
+        const float px = sp.posx - ((float) (sp.off_x - border) + .5f), py = sp.posy - ((float) (sp.off_y - border) + .5f);
+        if (!(fabsf(px) < 1e9f && fabsf(py) < 1e9f)) continue;
+        const int lox = max((int) ceilf(px - f.radius), 0), loy = max((int) ceilf(py - f.radius), 0);
+        const uint32_t hix = (uint32_t) min((int) floorf(px + f.radius), size_x - 1), hiy = (uint32_t) min((int) floorf(py + f.radius), size_y - 1);
+        const float basex = (float) lox - px, basey = (float) loy - py;
+        for (uint32_t yr = 0; yr < f.n; ++yr) {
+            const uint32_t y = (uint32_t) loy + yr;
+            bool enabled = y <= hiy;
+            const float wy = filter_weight(f, basey + (float) yr);
+            for (uint32_t xr = 0; xr < f.n; ++xr) {
+                const uint32_t x = (uint32_t) lox + xr;
+                const float weight = wy * filter_weight(f, basex + (float) xr);
+                enabled &= x <= hix;
+                const int tx = (int) x - border, ty = (int) y - border;
+                if (!enabled || weight == 0.f || tx < 0 || ty < 0 || tx >= (int) sc.film_w || ty >= (int) sc.film_h) continue;
+                float *dst = profile + (size_t) C * ((size_t) ty * sc.film_w + (size_t) tx);
+                atomicAdd(dst + n_fixed - 1, weight);                                   // W: value 1
+                if (sp.cnt_valid) atomicAdd(dst + n_fixed - 2, weight);                 // A: value 1
+                if (sp.val_a != 0.f)
+                    for (uint32_t r = 0; r < n_fixed - 2; ++r) atomicAdd(dst + r, sp.val_a * weight);
+                if (sp.var_ch >= 0 && sp.var_val != 0.f)
+                    for (uint32_t r = 0; r < sp.var_rep; ++r) atomicAdd(dst + sp.var_ch + r, sp.var_val * weight);
+            }
+        }
+    }
+}
+
 // =========================================================================================================
 // launchers
 // =========================================================================================================
@@ -815,9 +863,14 @@ int launch_shade(const DevScene &sc, const Wave &w, uint32_t depth, const uint32
     return sc.S == 1 ? launch_shade_s<1>(sc, w, depth, hit_counts, grid, next_queue, ctr_block, cfg)
                      : launch_shade_s<4>(sc, w, depth, hit_counts, grid, next_queue, ctr_block, cfg);
 }
-int launch_finalize(const DevScene &sc, const Wave &w, uint32_t n, float *profile, const LaunchCfg &cfg) {
+int launch_finalize(const DevScene &sc, const Wave &w, uint32_t n, float *profile, const DevFilter *filter, const LaunchCfg &cfg) {
     if (n == 0) return 0;
     int grid = (int) min((uint32_t) (cfg.sm_count * 4), (n + FIN_THREADS - 1) / FIN_THREADS);
+    if (filter) {
+        if (sc.S == 1) k_finalize_wide<1><<<grid, FIN_THREADS, 0, cfg.stream>>>(sc, w, n, profile, *filter);
+        else k_finalize_wide<4><<<grid, FIN_THREADS, 0, cfg.stream>>>(sc, w, n, profile, *filter);
+        return 1;
+    }
     const bool smem = sc.channels * sc.film_w * sc.film_h <= FIN_SMEM_FLOATS;
     if (sc.S == 1) { if (smem) k_finalize<1, true><<<grid, FIN_THREADS, 0, cfg.stream>>>(sc, w, n, profile); else k_finalize<1, false><<<grid, FIN_THREADS, 0, cfg.stream>>>(sc, w, n, profile); }
     else { if (smem) k_finalize<4, true><<<grid, FIN_THREADS, 0, cfg.stream>>>(sc, w, n, profile); else k_finalize<4, false><<<grid, FIN_THREADS, 0, cfg.stream>>>(sc, w, n, profile); }

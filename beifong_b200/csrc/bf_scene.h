@@ -63,6 +63,15 @@ struct DevEndpoint {
 };
 
 // Passed to every kernel by value (constant bank): pointers to the tables + small constants.
+// Discretised reconstruction filter (ReconstructionFilter::init_discretization, src/libcore/rfilter.cpp:9-20): the
+// MTS_FILTER_RESOLUTION + 1 = 32 table values, built on the host.  Only read by the wide-filter finalize kernel.
+struct DevFilter {
+    float values[32];
+    float radius, scale;      // m_radius, m_scale_factor = 31 / radius
+    uint32_t n;               // footprint width: ceil((radius - 2 RayEpsilon) * 2) (signalblock.cpp:121)
+    uint32_t border;          // m_border_size = ceil(radius - 0.5 - 2 RayEpsilon)
+};
+
 struct DevScene {
     bf_constants C;
     uint32_t S;

@@ -64,7 +64,8 @@ int launch_trace_shadow(const DevScene &sc, const Wave &w, const uint32_t *queue
 // shades the lanes of w.queue_h[0 .. hit_counts[0]) and w.queue_h2[0 .. hit_counts[1]); n_bound >= their sum
 int launch_shade(const DevScene &sc, const Wave &w, uint32_t depth, const uint32_t *hit_counts, uint32_t n_bound,
                  uint32_t *next_queue, uint32_t *ctr_block, const LaunchCfg &cfg);
-int launch_finalize(const DevScene &sc, const Wave &w, uint32_t n, float *profile, const LaunchCfg &cfg);
+// filter == nullptr: box filter (one bin per sample); otherwise the separable n x n splat of SignalBlock::put
+int launch_finalize(const DevScene &sc, const Wave &w, uint32_t n, float *profile, const DevFilter *filter, const LaunchCfg &cfg);
 int launch_develop(const float *raw, void *out, uint32_t n_bins, uint32_t channels, bool half_out, const LaunchCfg &cfg);
 // Stand-alone ray queries (Scene::ray_intersect_preliminary / ray_test for caller-provided rays)
 int launch_trace_rays(const DevScene &sc, const float4 *ray_o, const float4 *ray_d, uint32_t n, float4 *hit, uint32_t *occl,

@@ -250,11 +250,18 @@ class _Loader:
         kind, p = el.get("type"), self.props(el)
         film = next((c for c in el if c.tag in ("film", "adc")), None)
         fp = self.props(film) if film is not None else {}
+        filt = dict(filter_radius=0.5, filter_kind=0)
         if film is not None:
             rf = next((c for c in film if c.tag == "rfilter"), None)
-            # Film / ADC default reconstruction filter is gaussian (adc.cpp:60-76); the path implements box only
-            if rf is None or rf.get("type") != "box":
-                raise NotImplementedError("xml: reconstruction filters other than box are not on the accelerated path")
+            # Film / ADC default reconstruction filter is gaussian (adc.cpp:60-76).  ADCs: box, gaussian (radius = 4 stddev,
+            # gaussian.cpp:37-45) and tent (radius 1, tent.cpp:30-34); films (gen 1/2): box only
+            rtype = rf.get("type") if rf is not None else "gaussian"
+            if rtype == "gaussian" and film.tag == "adc":
+                filt = dict(filter_radius=4.0 * float(self.props(rf).get("stddev", 0.5)) if rf is not None else 2.0, filter_kind=1)
+            elif rtype == "tent" and film.tag == "adc":
+                filt = dict(filter_radius=1.0, filter_kind=2)
+            elif rtype != "box":
+                raise NotImplementedError(f"xml: reconstruction filter \"{rtype}\" is not on the accelerated path here")
         sampler = next((c for c in el if c.tag == "sampler"), None)
         if sampler is not None:
             sp = self.props(sampler)
@@ -289,7 +296,7 @@ class _Loader:
             t_bins, f_bins = int(fp.get("t_bins", 1024)), int(fp.get("f_bins", 1024))   # adc.cpp:18-21
             self.s.set_adc(t_bins=t_bins, f_bins=f_bins, t_bandwidth=fp.get("t_bandwidth", 3.81e-6), f_bandwidth=fp.get("f_bandwidth", 250e6),
                            window_t_bins=int(fp.get("window_t_bins", t_bins)), window_f_bins=int(fp.get("window_f_bins", f_bins)),
-                           window_offset_t=int(fp.get("window_offset_t", 0)), window_offset_f=int(fp.get("window_offset_f", 0)))
+                           window_offset_t=int(fp.get("window_offset_t", 0)), window_offset_f=int(fp.get("window_offset_f", 0)), **filt)
             self.film = ("adc", t_bins, f_bins)
         else:
             raise NotImplementedError(f"xml: sensor / receiver plugin \"{kind}\" is not on the accelerated path")

@@ -57,7 +57,14 @@ public:
     void set_window(uint32_t t_bins, uint32_t f_bins, uint32_t offset_t, uint32_t offset_f) {
         m_desc.window_t_bins = t_bins; m_desc.window_f_bins = f_bins; m_desc.window_offset_t = offset_t; m_desc.window_offset_f = offset_f;
     }
-    // ADC::size() = (t_bins, f_bins); ADC::bandwidth() = (t_bandwidth, f_bandwidth)
+    // <rfilter>: "box" (default here; the reference's scripts all use it), "gaussian" (radius = 4 stddev, gaussian.cpp:37-45),
+    // "tent" (radius 1, tent.cpp:30-34); the wide ones take the n x n splat of SignalBlock::put (signalblock.cpp:113-161)
+    void set_reconstruction_filter(const std::string &type, float stddev = 0.5f) {
+        if (type == "box") { m_desc.filter_kind = 0; m_desc.filter_radius = 0.5f; }
+        else if (type == "gaussian") { m_desc.filter_kind = 1; m_desc.filter_radius = 4.f * stddev; }
+        else if (type == "tent") { m_desc.filter_kind = 2; m_desc.filter_radius = 1.f; }
+        else throw NotImplementedError("rfilter plugin \"" + type + "\"");
+    }
     uint32_t t_bins() const { return m_desc.t_bins; }
     uint32_t f_bins() const { return m_desc.f_bins; }
     float t_bandwidth() const { return m_desc.t_bandwidth; }

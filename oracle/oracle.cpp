@@ -1283,6 +1283,59 @@ static inline void block_put(float *data, uint32_t C, int off_x, int off_y, uint
     size_t offset = (size_t) C * ((size_t) ly * size_x + lx);
     for (uint32_t k = 0; k < C; ++k) data[offset + k] += value[k];
 }
+// Discretised reconstruction filter: ReconstructionFilter::init_discretization (src/libcore/rfilter.cpp:9-20) over
+// GaussianFilter::eval (src/rfilters/gaussian.cpp:37-49; radius = 4 stddev) or TentFilter::eval (src/rfilters/tent.cpp:30-38).
+struct Filter { float values[32]; float radius, scale; uint32_t n, border; bool wide; };
+static Filter make_filter(const bf_adc_desc &a) {
+    Filter f;
+    std::memset(&f, 0, sizeof(f));
+    f.radius = a.filter_radius;
+    f.wide = a.filter_radius > .5f + RayEpsilon;                      // signalblock.cpp:113
+    if (!f.wide) return f;
+    float m_stddev = a.filter_radius / 4.f;
+    float m_alpha = -1.f / (2.f * m_stddev * m_stddev);
+    float m_bias = std::exp(m_alpha * (f.radius * f.radius));
+    float m_inv_radius = 1.f / f.radius;
+    for (size_t i = 0; i < 31; ++i) {
+        float x = (f.radius * i) / 31;
+        f.values[i] = a.filter_kind == 1 ? std::max(0.f, std::exp(m_alpha * (x * x)) - m_bias) : std::max(0.f, 1.f - std::abs(x * m_inv_radius));
+    }
+    f.values[31] = 0;
+    f.scale = 31 / f.radius;
+    f.border = (uint32_t) (int) std::ceil(f.radius - .5f - 2.f * RayEpsilon);
+    f.n = (uint32_t) (int) std::ceil((f.radius - 2.f * RayEpsilon) * 2.f);     // signalblock.cpp:121
+    return f;
+}
+static inline float eval_discretized(const Filter &f, float x) {       // include/mitsuba/core/rfilter.h:62-65
+    int index = std::min((int) std::abs(x * f.scale), 31);
+    return f.values[std::max(index, 0)];
+}
+// SignalBlock::put, wide branch (signalblock.cpp:113-161), into a block with a border of f.border bins, followed by the crop
+// of SignalBlock::put(block) into the border-less ADC storage (signalblock.cpp:49-77, hdradc.cpp:166-176).
+static inline void block_put_wide(float *data, uint32_t C, int off_x, int off_y, uint32_t size_x, uint32_t size_y, const Filter &f, V2 pos_, const float *value) {
+    const int border = (int) f.border;
+    const int bsx = (int) size_x + 2 * border, bsy = (int) size_y + 2 * border;
+    float px = pos_.x - ((float) (off_x - border) + .5f), py = pos_.y - ((float) (off_y - border) + .5f);
+    if (!(std::abs(px) < 1e9f && std::abs(py) < 1e9f)) return;      // non-finite positions index out of bounds in the reference
+    int lox = std::max((int) std::ceil(px - f.radius), 0), loy = std::max((int) std::ceil(py - f.radius), 0);
+    uint32_t hix = (uint32_t) std::min((int) std::floor(px + f.radius), bsx - 1), hiy = (uint32_t) std::min((int) std::floor(py + f.radius), bsy - 1);
+    float basex = (float) lox - px, basey = (float) loy - py;
+    float wx[20], wy[20];
+    for (uint32_t i = 0; i < f.n; ++i) { wx[i] = eval_discretized(f, basex + (float) i); wy[i] = eval_discretized(f, basey + (float) i); }
+    for (uint32_t yr = 0; yr < f.n; ++yr) {
+        uint32_t y = (uint32_t) loy + yr;
+        bool enabled = y <= hiy;
+        for (uint32_t xr = 0; xr < f.n; ++xr) {
+            uint32_t x = (uint32_t) lox + xr;
+            float weight = wy[yr] * wx[xr];
+            enabled &= x <= hix;
+            int tx = (int) x - border, ty = (int) y - border;      // crop to the storage
+            if (!enabled || tx < 0 || ty < 0 || tx >= (int) size_x || ty >= (int) size_y) continue;
+            size_t offset = (size_t) C * ((size_t) ty * size_x + (size_t) tx);
+            for (uint32_t k = 0; k < C; ++k) data[offset + k] += value[k] * weight;
+        }
+    }
+}
 static void seed_sample(const Scene &sc, Sampler &s, uint64_t seed, uint64_t idx) {
     (void) sc;
     s.rng.seed(sample_tea_64_wide(seed, idx), sample_tea_64_wide(idx, seed));  // sampler.cpp:89-92
@@ -1332,7 +1385,11 @@ static void one_sample(const Scene &sc, Sampler &sampler, float *block, bf_sampl
         aovs[0] = res.valid ? hsum_spec(wres, sc.S) : 0.f;
         aovs[1] = res.valid ? 1.f : 0.f;
         aovs[2] = 1.f;
-        if (block) block_put(block, C, (int) sc.adc.window_offset_t, (int) sc.adc.window_offset_f, W, H, tf, aovs);
+        if (block) {
+            const Filter filt = make_filter(sc.adc);
+            if (filt.wide) block_put_wide(block, C, (int) sc.adc.window_offset_t, (int) sc.adc.window_offset_f, W, H, filt, tf, aovs);
+            else block_put(block, C, (int) sc.adc.window_offset_t, (int) sc.adc.window_offset_f, W, H, tf, aovs);
+        }
         if (rec) {
             rec->first_shape = res.first.shape >= 0 ? (uint32_t) res.first.shape : BF_NONE;
             rec->first_prim = res.first.shape >= 0 ? res.first.prim : BF_NONE; rec->first_t = res.first.t;
@@ -1594,6 +1651,15 @@ int orc_block_bin(uint32_t size_x, uint32_t size_y, int off_x, int off_y, float 
     block_put(data.data(), 1, off_x, off_y, size_x, size_y, V2(px, py), &one);
     for (size_t i = 0; i < data.size(); ++i) if (data[i] != 0.f) return (int) i;
     return -1;
+}
+
+// SignalBlock::put with a wide filter: one sample of value 1 at (px, py) into a size_x x size_y single-channel storage
+void orc_block_splat(uint32_t size_x, uint32_t size_y, int off_x, int off_y, uint32_t filter_kind, float filter_radius, float px, float py, float *out) {
+    bf_adc_desc a; std::memset(&a, 0, sizeof(a)); a.filter_kind = filter_kind; a.filter_radius = filter_radius;
+    const Filter f = make_filter(a);
+    float one = 1.f;
+    if (f.wide) block_put_wide(out, 1, off_x, off_y, size_x, size_y, f, V2(px, py), &one);
+    else block_put(out, 1, off_x, off_y, size_x, size_y, V2(px, py), &one);
 }
 
 }  // extern "C"

@@ -59,6 +59,8 @@ int main(int argc, char **argv) {
     EXPECT((throws<Error>([] { Integrator i(4, 0); }, "rr_depth")));
     EXPECT((throws<Error>([] { Integrator i(-3); }, "max_depth")));
     EXPECT((throws<Error>([] { ADC a; a.bitmap(false); }, "nothing received")));
+    EXPECT((throws<NotImplementedError>([] { ADC a; a.set_reconstruction_filter("lanczos"); }, "lanczos")));
+    { ADC a; a.set_reconstruction_filter("gaussian"); EXPECT(a.desc().filter_kind == 1 && a.desc().filter_radius == 2.f); }
     {
         Scene s(constants(C0, C0 / 97e9f * 1e9f, C0 / 91e9f * 1e9f));
         EXPECT((throws<Error>([&] { const float m[16] = {1,0,0,0, 0,1,0,0, 0,0,1,0, 0,0,0,1}; s.add_rectangle(m, 99); }, "bsdf id out of range")));

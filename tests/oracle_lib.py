@@ -35,6 +35,7 @@ def lib():
         L.orc_last_error.argtypes = [C.c_void_p]
         L.orc_scene_set_accel.argtypes = [C.c_void_p, C.c_int, C.c_char_p]
         L.orc_profile_size.argtypes = [C.c_void_p, P(u32), P(u32), P(u32)]
+        L.orc_block_splat.argtypes = [u32, u32, C.c_int, C.c_int, u32, f32, f32, f32, P(f32)]
         L.orc_receive.argtypes = [C.c_void_p, u64, u64, u64, P(f32), C.c_int, C.c_int, C.c_int, P(u64)]
         L.orc_sample_records.argtypes = [C.c_void_p, u64, u64, u64, C.c_void_p, C.c_int]
         L.orc_trace_first_hits.argtypes = [C.c_void_p, P(f32), P(f32), P(f32), P(f32), u64, P(u32), P(u32), P(f32), P(f32), P(f32), C.c_int]

@@ -349,3 +349,43 @@ def test_develop_errors(native):
     with pytest.raises(Exception, match="component_format"):
         s.bitmap(raw=False, component_format="uint32")
     s.close()
+
+
+@pytest.mark.parametrize("kind,radius", [(1, 2.0), (2, 1.0), (1, 1.0)])
+@pytest.mark.parametrize("frame", [False, True])
+def test_wide_reconstruction_filter(native, kind, radius, frame):
+    """SignalBlock::put, wide branch (signalblock.cpp:113-161): gaussian (radius = 4 stddev) and tent splats of every
+    sample (hits and misses) against the oracle, on the 1-D range profile and on a 2-D range-time frame."""
+    s = configs.small_radar(spectrum_width=1)
+    f_bins, t_bins, bin_m = (256, 64, 0.12) if frame else (1024, 1, 0.03)
+    s.set_adc(t_bins=t_bins, f_bins=f_bins, t_bandwidth=200e-6, f_bandwidth=f_bins * bin_m * 2.0 / configs.C0 * (6e9 / 200e-6),
+              filter_radius=radius, filter_kind=kind)
+    s.commit()
+    orc = OracleScene(s.export(), accel=OracleScene.BVH)
+    n = 1 << 17
+    s.receive(n, seed=5)
+    g = s.profile()
+    c = orc.receive(n, seed=5, threads=8)
+    assert g.shape == c.shape and c[..., 0].sum() > 0
+    for ch in range(g.shape[-1]):
+        assert rel_l2(g[..., ch], c[..., ch]) <= 1e-3, ch
+    # the splat spreads a sample over more than one bin: more bins are touched than with the box filter
+    box = configs.small_radar(spectrum_width=1)
+    box.set_adc(t_bins=t_bins, f_bins=f_bins, t_bandwidth=200e-6, f_bandwidth=f_bins * bin_m * 2.0 / configs.C0 * (6e9 / 200e-6))
+    box.commit()
+    box.receive(n, seed=5)
+    b = box.profile()
+    assert np.count_nonzero(g[..., 0]) > np.count_nonzero(b[..., 0])
+    # per-sample records are unaffected by the filter
+    r_w, r_b = s.sample_records(2000, seed=5), box.sample_records(2000, seed=5)
+    assert np.array_equal(r_w["value"], r_b["value"], equal_nan=True) and np.array_equal(r_w["tf_f"], r_b["tf_f"], equal_nan=True)
+    s.close(); box.close()
+
+
+def test_wide_filter_rejected_kinds(native):
+    s = configs.small_radar(spectrum_width=1)
+    with pytest.raises(Exception, match="gaussian / tent"):
+        s.set_adc(t_bins=1, f_bins=64, filter_radius=2.0, filter_kind=0)
+    with pytest.raises(Exception, match="radius 1"):
+        s.set_adc(t_bins=1, f_bins=64, filter_radius=1.5, filter_kind=2)
+    s.close()

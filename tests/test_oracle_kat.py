@@ -522,3 +522,35 @@ def test_develop_restatement_known_answers():
     assert np.isinf(f16[0, 3, 0]) and f16[0, 3, 2] == np.float16(-2.0)   # 1e6 overflows float16
     with pytest.raises(ValueError):
         develop(raw, "uint32")
+
+
+def _splat(size_x, size_y, kind, radius, px, py, off=(0, 0)):
+    out = np.zeros((size_y, size_x), np.float32)
+    lib().orc_block_splat(size_x, size_y, off[0], off[1], kind, radius, px, py, out.ctypes.data_as(C.POINTER(C.c_float)))
+    return out
+
+
+def test_wide_filter_splat_known_answers():
+    """SignalBlock::put, wide branch (signalblock.cpp:113-161) over the discretised filter (rfilter.cpp:9-20,
+    rfilter.h:62-65): analytic footprints of the tent (radius 1) and gaussian (stddev 0.5, radius 2) filters."""
+    # tent, sample on a bin centre: x = -1, 0 -> table[31] = 0 and table[0] = 1: everything in that bin
+    o = _splat(8, 8, 2, 1.0, 3.5, 4.5)
+    assert o[4, 3] == 1.0 and o.sum() == 1.0
+    # tent, a quarter bin to the right: x = -0.25, 0.75 -> table[int(.25 * 31)] = 1 - 7/31, table[23] = 1 - 23/31
+    o = _splat(8, 1, 2, 1.0, 3.75, 0.5)
+    a, b = np.float32(1) - np.float32(7) / np.float32(31), np.float32(1) - np.float32(23) / np.float32(31)
+    assert np.isclose(o[0, 3], a, rtol=1e-6) and np.isclose(o[0, 4], b, rtol=1e-6) and np.count_nonzero(o) == 2
+    # gaussian: footprint 4 x 4, separable and symmetric about a bin corner
+    o = _splat(16, 16, 1, 2.0, 8.0, 8.0)          # position 8.0 = the corner between bins 7 and 8
+    assert np.count_nonzero(o) == 16 and np.allclose(o, o[::-1, ::-1]) and np.allclose(o, o.T)
+    g = lambda x: max(0.0, math.exp(-2 * x * x) - math.exp(-8.0))
+    tab = lambda x: g(2.0 * int(abs(x) * 31 / 2.0) / 31)          # the discretised filter is a step function
+    assert np.isclose(o[8, 8], tab(0.5) ** 2, rtol=1e-5) and np.isclose(o[8, 9], tab(0.5) * tab(1.5), rtol=1e-5)
+    # the crop at the storage edge: a sample half a bin outside still reaches the first bins; one beyond the radius does not
+    o = _splat(16, 1, 1, 2.0, -0.5, 0.5)
+    assert o[0, 0] > 0 and o[0, 1] >= 0 and np.count_nonzero(o) <= 2
+    assert _splat(16, 1, 1, 2.0, -2.6, 0.5).sum() == 0 and _splat(16, 1, 1, 2.0, 18.6, 0.5).sum() == 0
+    # window offset: positions are relative to it
+    assert np.array_equal(_splat(8, 8, 2, 1.0, 13.5, 24.5, off=(10, 20)), _splat(8, 8, 2, 1.0, 3.5, 4.5))
+    # radius 0.5 keeps the single-bin branch
+    assert _splat(8, 8, 0, 0.5, 3.2, 4.9)[4, 3] == 1.0
