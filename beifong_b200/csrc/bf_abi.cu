@@ -215,9 +215,28 @@ static void build_filter(bf_scene *s) {
     DevFilter &f = s->filter;
     const float radius = a.filter_radius;
     const float stddev = radius / 4.f, alpha = -1.f / (2.f * stddev * stddev), bias = std::exp(alpha * (radius * radius));
+    // Mitchell-Netravali polynomial (mitchell.cpp:52-64; catmullrom.cpp:33-45 is the same with B = 0, C = 0.5)
+    auto cubic = [](float x, float B, float C) {
+        const float x2 = x * x, x3 = x2 * x;
+        const float r = (1.f / 6.f) * (x < 1.f ? (12.f - 9.f * B - 6.f * C) * x3 + (-18.f + 12.f * B + 6.f * C) * x2 + (6.f - 2.f * B)
+                                               : (-B - 6.f * C) * x3 + (6.f * B + 30.f * C) * x2 + (-12.f * B - 48.f * C) * x + (8.f * B + 24.f * C));
+        return x < 2.f ? r : 0.f;
+    };
     for (int i = 0; i < 31; ++i) {
         const float x = (radius * (float) i) / 31.f;
-        f.values[i] = a.filter_kind == 1 ? std::max(0.f, std::exp(alpha * (x * x)) - bias) : std::max(0.f, 1.f - std::fabs(x * (1.f / radius)));
+        float v = 0.f;
+        switch (a.filter_kind) {
+            case 1: v = std::max(0.f, std::exp(alpha * (x * x)) - bias); break;
+            case 2: v = std::max(0.f, 1.f - std::fabs(x * (1.f / radius))); break;
+            case 3: v = cubic(x, 1.f / 3.f, 1.f / 3.f); break;
+            case 4: v = cubic(x, 0.f, .5f); break;
+            case 5: {   // lanczos.cpp:47-55
+                const float x1 = 3.14159265358979323846f * x, x2 = x1 / radius;
+                v = x < 5.9604644775390625e-08f ? 1.f : (x > radius ? 0.f : (std::sin(x1) * std::sin(x2)) / (x1 * x2));
+                break;
+            }
+        }
+        f.values[i] = v;
     }
     f.values[31] = 0.f;
     f.radius = radius; f.scale = 31.f / radius;
@@ -421,12 +440,14 @@ int bf_scene_set_adc(bf_scene *s, const bf_adc_desc *desc) {
     if (!(desc->t_bandwidth > 0.f) || !(desc->f_bandwidth > 0.f)) return fail(s, BF_ERR_INVALID, "bf_scene_set_adc: bandwidths must be positive");
     // Receivers warn when the reconstruction filter is wider than one bin (phasedreceiver.cpp:59-62);
     // the accelerated path implements the single-bin branch of SignalBlock::put (signalblock.cpp:162-169).
-    // Wider filters take the n x n splat (signalblock.cpp:113-161): gaussian (radius = 4 stddev, gaussian.cpp:37-45) and tent
-    // (radius 1, tent.cpp:30-34); the other rfilter plugins are not on the accelerated path.
+    // Wider filters take the n x n splat (signalblock.cpp:113-161): gaussian (radius = 4 stddev, gaussian.cpp:37-45), tent
+    // (radius 1, tent.cpp:30-34), mitchell (B = C = 1/3) and catmullrom (radius 2), lanczos (radius = lobes).
     if (desc->filter_radius > 0.5f + BF_RAY_EPS) {
         if (desc->filter_kind == 1) { if (!(desc->filter_radius <= 8.f)) return fail(s, BF_ERR_INVALID, "bf_scene_set_adc: gaussian filter radius (4 stddev) must be <= 8 bins"); }
         else if (desc->filter_kind == 2) { if (desc->filter_radius != 1.f) return fail(s, BF_ERR_INVALID, "bf_scene_set_adc: the tent filter has radius 1"); }
-        else return fail(s, BF_ERR_UNSUPPORTED, "bf_scene_set_adc: wide reconstruction filters other than gaussian / tent are not on the accelerated path");
+        else if (desc->filter_kind == 3 || desc->filter_kind == 4) { if (desc->filter_radius != 2.f) return fail(s, BF_ERR_INVALID, "bf_scene_set_adc: the mitchell / catmullrom filters have radius 2"); }
+        else if (desc->filter_kind == 5) { if (!(desc->filter_radius >= 1.f && desc->filter_radius <= 8.f && desc->filter_radius == std::floor(desc->filter_radius))) return fail(s, BF_ERR_INVALID, "bf_scene_set_adc: lanczos radius = lobes, an integer in [1, 8]"); }
+        else return fail(s, BF_ERR_UNSUPPORTED, "bf_scene_set_adc: unknown wide reconstruction filter kind (1 gaussian, 2 tent, 3 mitchell, 4 catmullrom, 5 lanczos)");
     }
     if (s->committed) return fail(s, BF_ERR_STATE, "bf_scene_set_adc: scene already committed");
     s->adc = *desc; s->has_adc = true;

@@ -254,12 +254,18 @@ class _Loader:
         if film is not None:
             rf = next((c for c in film if c.tag == "rfilter"), None)
             # Film / ADC default reconstruction filter is gaussian (adc.cpp:60-76).  ADCs: box, gaussian (radius = 4 stddev,
-            # gaussian.cpp:37-45) and tent (radius 1, tent.cpp:30-34); films (gen 1/2): box only
+            # gaussian.cpp:37-45), tent (radius 1, tent.cpp:30-34), mitchell, catmullrom, lanczos; films (gen 1/2): box only
             rtype = rf.get("type") if rf is not None else "gaussian"
             if rtype == "gaussian" and film.tag == "adc":
                 filt = dict(filter_radius=4.0 * float(self.props(rf).get("stddev", 0.5)) if rf is not None else 2.0, filter_kind=1)
             elif rtype == "tent" and film.tag == "adc":
                 filt = dict(filter_radius=1.0, filter_kind=2)
+            elif rtype in ("mitchell", "catmullrom") and film.tag == "adc":
+                if rtype == "mitchell" and any(k in self.props(rf) for k in ("B", "C")):
+                    raise NotImplementedError("xml: mitchell filter with non-default B / C")
+                filt = dict(filter_radius=2.0, filter_kind=3 if rtype == "mitchell" else 4)
+            elif rtype == "lanczos" and film.tag == "adc":
+                filt = dict(filter_radius=float(int(self.props(rf).get("lobes", 3))), filter_kind=5)
             elif rtype != "box":
                 raise NotImplementedError(f"xml: reconstruction filter \"{rtype}\" is not on the accelerated path here")
         sampler = next((c for c in el if c.tag == "sampler"), None)

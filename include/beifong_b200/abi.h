@@ -147,7 +147,7 @@ typedef struct bf_adc_desc {
     uint32_t window_offset_t, window_offset_f;
     float t_bandwidth, f_bandwidth;       /* defaults 3.81e-6 s, 250e6 Hz */
     float filter_radius;                  /* box = 0.5; > 0.5+RayEpsilon selects the wide splat (signalblock.cpp:113-161) */
-    uint32_t filter_kind;                 /* 0 box, 1 gaussian (radius = 4 stddev), 2 tent (radius 1) */
+    uint32_t filter_kind;                 /* 0 box, 1 gaussian (radius = 4 stddev), 2 tent (radius 1), 3 mitchell (B = C = 1/3), 4 catmullrom (radius 2), 5 lanczos (radius = lobes) */
 } bf_adc_desc;
 
 /* Integrators.  gen 3: phase(pathtimefrequency) (src/integrators/phase.cpp:63-145,

@@ -59,10 +59,13 @@ public:
     }
     // <rfilter>: "box" (default here; the reference's scripts all use it), "gaussian" (radius = 4 stddev, gaussian.cpp:37-45),
     // "tent" (radius 1, tent.cpp:30-34); the wide ones take the n x n splat of SignalBlock::put (signalblock.cpp:113-161)
-    void set_reconstruction_filter(const std::string &type, float stddev = 0.5f) {
+    void set_reconstruction_filter(const std::string &type, float stddev = 0.5f, int lobes = 3) {
         if (type == "box") { m_desc.filter_kind = 0; m_desc.filter_radius = 0.5f; }
         else if (type == "gaussian") { m_desc.filter_kind = 1; m_desc.filter_radius = 4.f * stddev; }
         else if (type == "tent") { m_desc.filter_kind = 2; m_desc.filter_radius = 1.f; }
+        else if (type == "mitchell") { m_desc.filter_kind = 3; m_desc.filter_radius = 2.f; }       // B = C = 1/3
+        else if (type == "catmullrom") { m_desc.filter_kind = 4; m_desc.filter_radius = 2.f; }
+        else if (type == "lanczos") { m_desc.filter_kind = 5; m_desc.filter_radius = (float) lobes; }
         else throw NotImplementedError("rfilter plugin \"" + type + "\"");
     }
     uint32_t t_bins() const { return m_desc.t_bins; }

@@ -1297,8 +1297,23 @@ static Filter make_filter(const bf_adc_desc &a) {
     float m_bias = std::exp(m_alpha * (f.radius * f.radius));
     float m_inv_radius = 1.f / f.radius;
     for (size_t i = 0; i < 31; ++i) {
-        float x = (f.radius * i) / 31;
-        f.values[i] = a.filter_kind == 1 ? std::max(0.f, std::exp(m_alpha * (x * x)) - m_bias) : std::max(0.f, 1.f - std::abs(x * m_inv_radius));
+        float x = (f.radius * i) / 31, v = 0.f;
+        if (a.filter_kind == 1) v = std::max(0.f, std::exp(m_alpha * (x * x)) - m_bias);
+        else if (a.filter_kind == 2) v = std::max(0.f, 1.f - std::abs(x * m_inv_radius));
+        else if (a.filter_kind == 3 || a.filter_kind == 4) {
+            // MitchellNetravaliFilter::eval (src/rfilters/mitchell.cpp:52-64, B = C = 1/3); CatmullRomFilter::eval
+            // (src/rfilters/catmullrom.cpp:33-45, B = 0, C = 0.5)
+            float m_b = a.filter_kind == 3 ? 1.f / 3.f : 0.f, m_c = a.filter_kind == 3 ? 1.f / 3.f : .5f;
+            float x2 = x * x, x3 = x2 * x;
+            float result = (1.f / 6.f) * (x < 1 ? (12.f - 9.f * m_b - 6.f * m_c) * x3 + (-18.f + 12.f * m_b + 6.f * m_c) * x2 + (6.f - 2.f * m_b)
+                                                : (-m_b - 6.f * m_c) * x3 + (6.f * m_b + 30.f * m_c) * x2 + (-12.f * m_b - 48.f * m_c) * x + (8.f * m_b + 24.f * m_c));
+            v = x < 2.f ? result : 0.f;
+        } else if (a.filter_kind == 5) {
+            // LanczosSincFilter::eval (src/rfilters/lanczos.cpp:47-55), radius = lobes
+            float x1 = 3.14159265358979323846f * x, x2 = x1 / f.radius, result = (std::sin(x1) * std::sin(x2)) / (x1 * x2);
+            v = x < 5.9604644775390625e-08f ? 1.f : (x > f.radius ? 0.f : result);
+        }
+        f.values[i] = v;
     }
     f.values[31] = 0;
     f.scale = 31 / f.radius;

@@ -351,7 +351,7 @@ def test_develop_errors(native):
     s.close()
 
 
-@pytest.mark.parametrize("kind,radius", [(1, 2.0), (2, 1.0), (1, 1.0)])
+@pytest.mark.parametrize("kind,radius", [(1, 2.0), (2, 1.0), (1, 1.0), (3, 2.0), (4, 2.0), (5, 3.0)])
 @pytest.mark.parametrize("frame", [False, True])
 def test_wide_reconstruction_filter(native, kind, radius, frame):
     """SignalBlock::put, wide branch (signalblock.cpp:113-161): gaussian (radius = 4 stddev) and tent splats of every
@@ -384,8 +384,10 @@ def test_wide_reconstruction_filter(native, kind, radius, frame):
 
 def test_wide_filter_rejected_kinds(native):
     s = configs.small_radar(spectrum_width=1)
-    with pytest.raises(Exception, match="gaussian / tent"):
+    with pytest.raises(Exception, match="unknown wide reconstruction filter"):
         s.set_adc(t_bins=1, f_bins=64, filter_radius=2.0, filter_kind=0)
+    with pytest.raises(Exception, match="lobes"):
+        s.set_adc(t_bins=1, f_bins=64, filter_radius=2.5, filter_kind=5)
     with pytest.raises(Exception, match="radius 1"):
         s.set_adc(t_bins=1, f_bins=64, filter_radius=1.5, filter_kind=2)
     s.close()

@@ -554,3 +554,16 @@ def test_wide_filter_splat_known_answers():
     assert np.array_equal(_splat(8, 8, 2, 1.0, 13.5, 24.5, off=(10, 20)), _splat(8, 8, 2, 1.0, 3.5, 4.5))
     # radius 0.5 keeps the single-bin branch
     assert _splat(8, 8, 0, 0.5, 3.2, 4.9)[4, 3] == 1.0
+
+
+def test_cubic_and_lanczos_filter_tables():
+    """mitchell (B = C = 1/3), catmullrom and lanczos through the discretised table: value at the sample position, the
+    negative lobe, and the closed forms at x = 0 (mitchell 8/9, catmullrom 1, lanczos 1)."""
+    for kind, radius, centre in ((3, 2.0, (8.0 / 9.0) ** 2), (4, 2.0, 1.0), (5, 3.0, 1.0)):
+        o = _splat(16, 16, kind, radius, 8.5, 8.5)            # on the centre of bin (8, 8): x = 0 for that bin
+        assert np.isclose(o[8, 8], centre, rtol=1e-6)
+        assert (o.min() < 0) == (kind == 5)                   # at integer offsets only lanczos-3 has a negative lobe
+    o = _splat(32, 1, 4, 2.0, 8.0, 0.5)                       # catmullrom at x = 1.5: (1/6)(-3 x^3 + 15 x^2 - 24 x + 12) < 0
+    x = 2.0 * int(1.5 * 31 / 2.0) / 31
+    want = (1 / 6) * (-3 * x ** 3 + 15 * x ** 2 - 24 * x + 12)
+    assert want < 0 and np.isclose(o[0, 9], want, rtol=1e-4) and np.isclose(o[0, 6], want, rtol=1e-4)

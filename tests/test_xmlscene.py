@@ -152,9 +152,10 @@ def test_adc_reconstruction_filters_from_xml():
     (adc.cpp:60-76); the oracle then takes the wide branch of SignalBlock::put and spreads the wall's peak."""
     from beifong_b200.scene import RADAR_94GHZ
     box = OracleScene(xmlscene.load_string(RADAR_XML, consts=RADAR_94GHZ).scene.export(), accel=OracleScene.BRUTE).receive(20000, seed=3, threads=4)
-    for rf in ('<rfilter type="gaussian"><float name="stddev" value="0.5"/></rfilter>', '<rfilter type="tent"/>', ''):
+    for rf in ('<rfilter type="gaussian"><float name="stddev" value="0.5"/></rfilter>', '<rfilter type="tent"/>', '',
+               '<rfilter type="mitchell"/>', '<rfilter type="catmullrom"/>', '<rfilter type="lanczos"><integer name="lobes" value="2"/></rfilter>'):
         L = xmlscene.load_string(RADAR_XML.replace('<rfilter type="box"/>', rf), consts=RADAR_94GHZ)
         wide = OracleScene(L.scene.export(), accel=OracleScene.BRUTE).receive(20000, seed=3, threads=4)
         assert wide.shape == box.shape and np.count_nonzero(wide[..., 0]) > np.count_nonzero(box[..., 0])
     with pytest.raises(NotImplementedError):
-        xmlscene.load_string(RADAR_XML.replace('<rfilter type="box"/>', '<rfilter type="lanczos"/>'), consts=RADAR_94GHZ)
+        xmlscene.load_string(RADAR_XML.replace('<rfilter type="box"/>', '<rfilter type="mitchell"><float name="B" value="0.5"/></rfilter>'), consts=RADAR_94GHZ)
