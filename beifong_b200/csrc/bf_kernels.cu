@@ -810,7 +810,10 @@ __global__ void __launch_bounds__(FIN_THREADS) k_finalize_wide(const __grid_cons
 // =========================================================================================================
 // launchers
 // =========================================================================================================
-static int trace_grid(const LaunchCfg &cfg) { return cfg.sm_count * TRACE_MIN_BLOCKS; }
+#ifndef BF_TRACE_GRID_BLOCKS
+#define BF_TRACE_GRID_BLOCKS TRACE_MIN_BLOCKS
+#endif
+static int trace_grid(const LaunchCfg &cfg) { return cfg.sm_count * BF_TRACE_GRID_BLOCKS; }
 
 int launch_raygen(const DevScene &sc, const Wave &w, uint64_t seed, uint64_t first_sample, uint32_t n, const LaunchCfg &cfg) {
     if (n == 0) return 0;
