@@ -221,6 +221,89 @@ def load_obj(path, to_world=None):
     return p, np.array(faces, dtype=np.uint32).reshape(-1, 3), None
 
 
+def load_serialized(path, to_world=None, shape_index=0):
+    """Mitsuba `.serialized` triangle mesh (src/shapes/serialized.cpp:196-300): little-endian header (0x041C, version
+    3 or 4), one zlib stream per sub-shape (flags, [v4: name], vertex / face counts as u64, positions, optional normals /
+    texcoords / colours in single or double precision, u32 face indices), sub-shape offsets in a dictionary at the
+    end of the file (u64 offsets in v4, u32 in v3).  Returns (positions, faces, normals or None)."""
+    import struct
+    import zlib
+    with open(path, "rb") as f:
+        data = f.read()
+    if len(data) < 4:
+        raise RuntimeError(f"{path}: encountered an invalid file format!")
+    fmt, version = struct.unpack_from("<HH", data, 0)
+    if fmt != 0x041C:
+        raise RuntimeError(f"{path}: encountered an invalid file format!")
+    if version not in (3, 4):
+        raise RuntimeError(f"{path}: encountered an incompatible file version!")
+    start = 0
+    if shape_index != 0:
+        if shape_index < 0:
+            raise RuntimeError("shape index must be nonnegative!")
+        count = struct.unpack_from("<I", data, len(data) - 4)[0]
+        if shape_index >= count:
+            raise RuntimeError(f"Unable to unserialize mesh, shape index is out of range! (requested {shape_index} out of 0..{count - 1})")
+        if version == 4:
+            start = struct.unpack_from("<Q", data, len(data) - 8 * (count - shape_index) - 4)[0]
+        else:
+            start = struct.unpack_from("<I", data, len(data) - 4 * (count - shape_index + 1))[0]
+    body = zlib.decompressobj().decompress(data[start + 4:])
+    off = 0
+    flags = struct.unpack_from("<I", body, off)[0]
+    off += 4
+    if version == 4:
+        off = body.index(b"\0", off) + 1                     # utf-8 name, null-terminated
+    n_vertices, n_faces = struct.unpack_from("<QQ", body, off)
+    off += 16
+    ft = np.dtype("<f8") if flags & 0x2000 else np.dtype("<f4")
+
+    def take(n_comp):
+        nonlocal off
+        a = np.frombuffer(body, dtype=ft, count=n_vertices * n_comp, offset=off).reshape(n_vertices, n_comp)
+        off += a.nbytes
+        return a.astype(np.float32)
+    pos = take(3)
+    nrm = take(3) if flags & 0x0001 else None
+    if flags & 0x0002:
+        take(2)
+    if flags & 0x0008:
+        take(3)
+    faces = np.frombuffer(body, dtype="<u4", count=n_faces * 3, offset=off).reshape(n_faces, 3).astype(np.uint32)
+    if faces.size and int(faces.max()) >= n_vertices:
+        raise RuntimeError(f"{path}: face index out of range")
+    if to_world is not None:
+        m = np.asarray(to_world, dtype=np.float32)
+        pos = transform_points(m, pos)
+        if nrm is not None:
+            inv_t = np.linalg.inv(m.astype(np.float64)).T[:3, :3]
+            nrm = nrm.astype(np.float64) @ inv_t.T
+            nrm = (nrm / np.linalg.norm(nrm, axis=1, keepdims=True)).astype(np.float32)
+    return pos, faces, nrm
+
+
+def save_serialized(path, meshes_list, version=4, double_precision=False):
+    """Writer for the same format (tests, scene conversion): `meshes_list` = [(positions, faces, normals or None), ...]."""
+    import struct
+    import zlib
+    ft = "<f8" if double_precision else "<f4"
+    out, offsets = bytearray(), []
+    for pos, faces, nrm in meshes_list:
+        offsets.append(len(out))
+        flags = (0x2000 if double_precision else 0x1000) | (0x0001 if nrm is not None else 0)
+        body = struct.pack("<I", flags) + (b"mesh\0" if version == 4 else b"") + struct.pack("<QQ", len(pos), len(faces))
+        body += np.asarray(pos, dtype=ft).tobytes()
+        if nrm is not None:
+            body += np.asarray(nrm, dtype=ft).tobytes()
+        body += np.asarray(faces, dtype="<u4").tobytes()
+        out += struct.pack("<HH", 0x041C, version) + zlib.compress(body)
+    for o in offsets:
+        out += struct.pack("<Q" if version == 4 else "<I", o)
+    out += struct.pack("<I", len(offsets))
+    with open(path, "wb") as f:
+        f.write(bytes(out))
+
+
 def vertex_normals(pos, faces):
     """Angle-weighted vertex normals (Mesh::recompute_vertex_normals, src/librender/mesh.cpp:201-278)."""
     p = np.asarray(pos, dtype=np.float32).astype(np.float64)

@@ -6,7 +6,7 @@ Supported subset = what the radar path needs: <defaul
 range(pathlength), phase(pathtimefrequency)), <shape type=rectangle|ply|obj> with <transform name="to_world">
 (scale, translate, rotate, lookat, matrix; later entries multiply from the left, xml.cpp:918), nested or
 referenced <bsdf> (diffuse, twosided, roughconductor, conductor), <emitter|transmitter>, <sensor|receiver> with
-<film|adc> and <sampler>, <spectrum> / <float> reflectance values, <ref id>.  Anything else raises
+<film|adc> and <sampler>, <spectrum> / <float> reflectance values, <ref id>, <include filename>, <alias id as>, <shape type=serialized>.  Anything else raises
 NotImplementedError, as the reference's plugin loader does for an unknown plugin.
 """
 import os
@@ -325,7 +325,7 @@ class _Loader:
             if p.get("flip_normals", False):                # rectangle.cpp:76-81
                 m = m * T.scale([1.0, 1.0, -1.0])
             sid = self.s.add_rect(m.matrix32(), bsdf)
-        elif kind in ("ply", "obj"):
+        elif kind in ("ply", "obj", "serialized"):
             path = p.get("filename")
             if path is None:
                 raise BeifongError(f"xml: <shape type=\"{kind}\"> without a filename")
@@ -333,7 +333,13 @@ class _Loader:
                 path = os.path.join(self.base_dir, path)
             if not os.path.exists(path):
                 raise BeifongError(f"\"{path}\": file does not exist!")       # ply.cpp:120-122
-            pos, faces, nrm = (meshes.load_ply if kind == "ply" else meshes.load_obj)(path, to_world=m.matrix32())
+            if kind == "serialized":
+                try:
+                    pos, faces, nrm = meshes.load_serialized(path, to_world=m.matrix32(), shape_index=int(p.get("shape_index", 0)))
+                except RuntimeError as e:
+                    raise BeifongError(str(e))
+            else:
+                pos, faces, nrm = (meshes.load_ply if kind == "ply" else meshes.load_obj)(path, to_world=m.matrix32())
             if p.get("face_normals", False):
                 nrm = None
             elif nrm is None:
@@ -368,16 +374,53 @@ class _Loader:
             raise NotImplementedError(f"xml: integrator \"{kind}\"" + (f"({nested})" if nested else "") + " is not a radar integrator")
 
 
+XML_INCLUDE_MAX_RECURSION = 15          # include/mitsuba/core/xml.h:8
+
+
+def _expand_includes(node, base_dir, depth=0):
+    """<include filename="..."/> (xml.cpp:653-705): the children of an included <scene> (or the included root element
+    itself) take the place of the tag; nested up to MTS_XML_INCLUDE_MAX_RECURSION levels."""
+    out = []
+    for child in list(node):
+        if child.tag != "include":
+            _expand_includes(child, base_dir, depth)
+            out.append(child)
+            continue
+        if set(child.attrib) != {"filename"}:
+            raise BeifongError("xml: <include> takes exactly the attribute \"filename\"")
+        path = child.get("filename")
+        if not os.path.isabs(path):
+            path = os.path.join(base_dir, path)
+        if not os.path.exists(path):
+            raise BeifongError(f"included file \"{path}\" not found")
+        if depth + 1 > XML_INCLUDE_MAX_RECURSION:
+            raise BeifongError(f"Exceeded <include> recursion limit of {XML_INCLUDE_MAX_RECURSION}")
+        try:
+            inc = ET.parse(path).getroot()
+        except ET.ParseError as e:
+            raise BeifongError(f"error while loading \"{path}\": {e}")
+        _expand_includes(inc, os.path.dirname(path), depth + 1)
+        out.extend(list(inc) if inc.tag == "scene" else [inc])
+    node[:] = out
+
+
 def load_string(text, base_dir=".", spectrum_width=1, consts=None, **params):
     """Parse a scene; `params` override <default> values like the CLI's -Dname=value (mitsuba.cpp:176-177)."""
     root = ET.fromstring(text)
     if root.tag != "scene":
         raise BeifongError("xml: root element must be <scene>")
+    _expand_includes(root, base_dir)
     defaults = {el.get("name"): el.get("value") for el in root if el.tag == "default"}
     defaults.update({k: v for k, v in params.items()})
     _substitute(root, defaults)
     ld = _Loader(root, base_dir, spectrum_width, dict(ULTRASOUND_DEFAULTS) if consts is None else consts)
     integ = None
+    # <alias id as> (xml.cpp:594-613): a second id for a named object; BSDF aliases are resolved before the shapes that use them
+    for el in root:
+        if el.tag == "alias" and el.get("id") in ld.named_bsdf_nodes:
+            if el.get("as") in ld.named_bsdf_nodes:
+                raise BeifongError(f"\"alias\" has duplicate id \"{el.get('as')}\"")
+            ld.named_bsdf_nodes[el.get("as")] = ld.named_bsdf_nodes[el.get("id")]
     for el in root:
         if el.tag == "shape":
             ld.shape(el)
@@ -389,6 +432,16 @@ def load_string(text, base_dir=".", spectrum_width=1, consts=None, **params):
             integ = el
         elif el.tag in ("default", "bsdf"):
             pass
+        elif el.tag == "alias":                             # shapes: the alias follows the shape it names
+            src, dst = el.get("id"), el.get("as")
+            if src in ld.named_bsdf_nodes:
+                continue
+            if dst in ld.shape_ids:
+                raise BeifongError(f"\"alias\" has duplicate id \"{dst}\"")
+            if src in ld.shape_ids:
+                ld.shape_ids[dst] = ld.shape_ids[src]
+            else:
+                raise BeifongError(f"referenced id \"{src}\" not found")
         else:
             raise NotImplementedError(f"xml: top-level element <{el.tag}>")
     if integ is None:

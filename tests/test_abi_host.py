@@ -119,3 +119,47 @@ def test_ply_obj_loaders_on_generated_files(tmp_path):
     obj.write_text("v -1 -1 0\nv 1 -1 0\nv -1 1 0\nv 1 1 0\nvt 1 1\nvt 0 0\nf 2/1 3/2 1/2\nf 2/1 4/2 3/2\n")
     pp, ff, _ = meshes.load_obj(str(obj))
     assert ff.tolist() == [[1, 2, 0], [1, 3, 2]]
+
+
+@pytest.mark.parametrize("version,double_precision", [(4, False), (3, False), (4, True)])
+def test_serialized_loader_round_trip(tmp_path, version, double_precision):
+    """Mitsuba .serialized meshes (serialized.cpp:196-300): v3 / v4 headers, single / double precision, several
+    sub-shapes addressed by shape_index through the offset dictionary at the end of the file."""
+    p0, f0 = meshes.car_body(12, 7)
+    n0 = meshes.vertex_normals(p0, f0)
+    p1, f1 = meshes.stairs(5)
+    path = str(tmp_path / "two.serialized")
+    meshes.save_serialized(path, [(p0, f0, n0), (p1, f1, None)], version=version, double_precision=double_precision)
+    a = meshes.load_serialized(path)
+    assert np.array_equal(a[0], p0.astype(np.float32)) and np.array_equal(a[1], f0) and np.allclose(a[2], n0, atol=1e-7)
+    b = meshes.load_serialized(path, shape_index=1)
+    assert np.array_equal(b[0], p1.astype(np.float32)) and np.array_equal(b[1], f1) and b[2] is None
+    with pytest.raises(RuntimeError, match="out of range"):
+        meshes.load_serialized(path, shape_index=2)
+    m = (meshes.Transform.translate([1.0, 2.0, 3.0]) * meshes.Transform.scale(2.0)).matrix32()
+    c = meshes.load_serialized(path, to_world=m)
+    assert np.allclose(c[0], p0 * 2.0 + np.array([1.0, 2.0, 3.0], np.float32), atol=1e-5)
+    bad = tmp_path / "bad.serialized"
+    bad.write_bytes(b"\x00\x01\x04\x00garbage")
+    with pytest.raises(RuntimeError, match="invalid file format"):
+        meshes.load_serialized(str(bad))
+
+
+REF_SERIALIZED = "/root/reference/resources/data/tests/serialized"
+
+
+@pytest.mark.skipif(not os.path.isdir(REF_SERIALIZED), reason="reference tree not present")
+@pytest.mark.parametrize("features", ["normals", "uv", "normals_uv"])
+def test_serialized_reference_fixtures(features):
+    """The reference's own fixtures and expectations (src/librender/tests/test_mesh.py:130-172, test06)."""
+    pos, faces, nrm = meshes.load_serialized(os.path.join(REF_SERIALIZED, f"rectangle_{features}.serialized"))
+    assert np.allclose(pos[0], [-2.85, 0.0, -7.6], atol=1e-3)
+    assert np.allclose(pos[2], [2.85, 0.0, 0.599999], atol=1e-3)
+    assert np.allclose(pos[3], [2.85, 0.0, -7.6], atol=1e-3)
+    assert faces.shape[1] == 3 and faces.max() < len(pos)
+    if "normals" in features:
+        assert np.allclose(nrm[[0, 2, 3]], [0.0, 1.0, 0.0])
+    else:
+        assert nrm is None
+        assert np.allclose(meshes.vertex_normals(pos, faces)[[0, 2, 3]], [0.0, 1.0, 0.0], atol=1e-6) or \
+            np.allclose(meshes.vertex_normals(pos, faces)[[0, 2, 3]], [0.0, -1.0, 0.0], atol=1e-6)

@@ -159,3 +159,34 @@ def test_adc_reconstruction_filters_from_xml():
         assert wide.shape == box.shape and np.count_nonzero(wide[..., 0]) > np.count_nonzero(box[..., 0])
     with pytest.raises(NotImplementedError):
         xmlscene.load_string(RADAR_XML.replace('<rfilter type="box"/>', '<rfilter type="mitchell"><float name="B" value="0.5"/></rfilter>'), consts=RADAR_94GHZ)
+
+
+def test_include_alias_and_serialized_shapes(tmp_path):
+    """<include> (xml.cpp:653-705), <alias> (xml.cpp:594-613) and <shape type="serialized"> (serialized.cpp) build the same
+    scene as the inline form."""
+    from beifong_b200 import meshes
+    from beifong_b200.scene import RADAR_94GHZ
+    p, f = meshes.car_body(12, 7)
+    meshes.save_serialized(str(tmp_path / "body.serialized"), [(meshes.stairs(3)[0], meshes.stairs(3)[1], None), (p, f, None)])
+    (tmp_path / "materials.xml").write_text(
+        '<scene version="2.1.0"><bsdf type="twosided" id="metal"><bsdf type="roughconductor"><float name="alpha" value="0.3"/>'
+        '<string name="distribution" value="ggx"/></bsdf></bsdf><alias id="metal" as="hull"/></scene>')
+    (tmp_path / "target.xml").write_text(
+        '<shape type="serialized" id="car"><string name="filename" value="body.serialized"/><integer name="shape_index" value="1"/>'
+        '<transform name="to_world"><translate x="5" y="0" z="0"/></transform><ref id="hull"/></shape>')
+    text = RADAR_XML.replace("</scene>", '<include filename="materials.xml"/><include filename="target.xml"/><alias id="car" as="target"/></scene>')
+    L = xmlscene.load_string(text, base_dir=str(tmp_path), consts=RADAR_94GHZ)
+    assert L.shape_ids["target"] == L.shape_ids["car"]
+    inline = RADAR_XML.replace("</scene>", '<bsdf type="twosided" id="metal"><bsdf type="roughconductor"><float name="alpha" value="0.3"/>'
+                               '<string name="distribution" value="ggx"/></bsdf></bsdf>'
+                               '<shape type="serialized" id="car"><string name="filename" value="body.serialized"/><integer name="shape_index" value="1"/>'
+                               '<transform name="to_world"><translate x="5" y="0" z="0"/></transform><ref id="metal"/></shape></scene>')
+    L2 = xmlscene.load_string(inline, base_dir=str(tmp_path), consts=RADAR_94GHZ)
+    assert np.array_equal(L.scene.export(), L2.scene.export())
+    with pytest.raises(BeifongError, match="not found"):
+        xmlscene.load_string(RADAR_XML.replace("</scene>", '<include filename="nope.xml"/></scene>'), base_dir=str(tmp_path), consts=RADAR_94GHZ)
+    with pytest.raises(BeifongError, match="referenced id"):
+        xmlscene.load_string(RADAR_XML.replace("</scene>", '<alias id="ghost" as="x"/></scene>'), consts=RADAR_94GHZ)
+    (tmp_path / "loop.xml").write_text('<scene version="2.1.0"><include filename="loop.xml"/></scene>')
+    with pytest.raises(BeifongError, match="recursion limit"):
+        xmlscene.load_string(RADAR_XML.replace("</scene>", '<include filename="loop.xml"/></scene>'), base_dir=str(tmp_path), consts=RADAR_94GHZ)
