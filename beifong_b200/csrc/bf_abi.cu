@@ -164,6 +164,7 @@ struct bf_scene {
     DevBuf<DevRect> d_rects; DevBuf<DevShape> d_shapes; DevBuf<bf_bsdf_desc> d_bsdfs;
     DevBuf<DevSpectrum> d_spectra; DevBuf<float> d_spec_pool; DevBuf<DevEndpoint> d_txs, d_rx; DevBuf<DevVElem> d_velems;
     DevBuf<float> d_profile; size_t profile_floats = 0;
+    bool primary_defer = false;      // fused primary: traverse the rays that enter the mesh bounds in a separate dense launch
     DevFilter filter; bool wide_filter = false;    // discretised reconstruction filter when wider than one bin
     DevBuf<uint32_t> d_developed;    // bf_profile_develop output (fp32 or fp16 components)
     // image of the geometry tables in pinned host memory (re-upload without a rebuild)
@@ -242,6 +243,36 @@ static void build_filter(bf_scene *s) {
     f.radius = radius; f.scale = 31.f / radius;
     f.n = (uint32_t) (int) std::ceil((radius - 2.f * BF_RAY_EPS) * 2.f);
     f.border = (uint32_t) (int) std::ceil(radius - .5f - 2.f * BF_RAY_EPS);
+}
+
+// Which primary kernel: the share of receiver rays (cosine-weighted about the receiver rectangle's normal, from its centre)
+// that enter the padded bounds of the meshes, on a 64 x 64 stratified grid.  Below a quarter, traversal is left to a
+// separate dense launch (k_primary<DEFER>); results are the same either way.
+static void estimate_primary_defer(bf_scene *s) {
+    s->primary_defer = false;
+    if (!s->has_rx || s->rx_shape < 0 || (size_t) s->rx_shape >= s->shapes.size() || s->shapes[s->rx_shape].type != 1) return;
+    const DevRect &r = s->rects[s->shapes[s->rx_shape].index];
+    const float *lo = s->dev.mesh_lo, *hi = s->dev.mesh_hi;
+    if (!(lo[0] <= hi[0])) return;
+    const double o[3] = {r.to_world.m[0][3], r.to_world.m[1][3], r.to_world.m[2][3]};
+    const double fs[3] = {r.ns.x, r.ns.y, r.ns.z}, ft[3] = {r.nt.x, r.nt.y, r.nt.z}, fn[3] = {r.nn.x, r.nn.y, r.nn.z};
+    int inside = 0;
+    const int N = 64;
+    for (int iy = 0; iy < N; ++iy)
+        for (int ix = 0; ix < N; ++ix) {
+            // cosine-weighted direction: uniform disk (polar form is fine for an estimate) lifted to the hemisphere
+            const double u = (ix + 0.5) / N, v = (iy + 0.5) / N, rad = std::sqrt(u), phi = 6.283185307179586 * v;
+            const double x = rad * std::cos(phi), y = rad * std::sin(phi), z = std::sqrt(std::max(0.0, 1.0 - u));
+            double t0 = 0.0, t1 = 1e30;
+            for (int a = 0; a < 3; ++a) {
+                const double d = x * fs[a] + y * ft[a] + z * fn[a];
+                if (std::fabs(d) < 1e-12) { if (o[a] < lo[a] || o[a] > hi[a]) { t1 = -1.0; break; } continue; }
+                const double ta = (lo[a] - o[a]) / d, tb = (hi[a] - o[a]) / d;
+                t0 = std::max(t0, std::min(ta, tb)); t1 = std::min(t1, std::max(ta, tb));
+            }
+            inside += t0 <= t1;
+        }
+    s->primary_defer = inside * 4 < N * N;
 }
 
 static uint32_t n_channels(const bf_scene *s) {
@@ -553,6 +584,7 @@ static int upload_tables(bf_scene *s) {
     d.spec_pool = s->d_spec_pool.p; d.txs = s->d_txs.p; d.rx = s->d_rx.p; d.velems = s->d_velems.p;
     d.adc = s->adc; d.integ = s->integ;
     build_filter(s);
+    estimate_primary_defer(s);
     film_size(s, d.film_w, d.film_h); d.channels = n_channels(s);
     d.rx_needs_aperture = s->rx.kind != BF_RX_PERSPECTIVE;   // Sensor::needs_aperture_sample
     d.hint_cls1_bsdf = cls1_kind < 0 ? -1 : cls1_kind;
@@ -798,7 +830,10 @@ static int run_wave(bf_scene *s, WaveSlot &sl, uint64_t seed, uint64_t first, ui
     };
     if (fused) {
         w.n_lanes = ctr + 6;
-        timed(BF_K_PRIMARY, [&] { return launch_primary(sc, w, seed, first, n, ctr + 4, ctr + 2, profile, cfg); });
+        // few receiver rays reach the meshes (bf_scene_commit's estimate): k_primary leaves those to a dense k_trace launch
+        const bool defer = env_u32("BF_PRIMARY_DEFER", s->primary_defer ? 1 : 0, 0, 1) != 0 && sc.n_nodes != 0;
+        timed(BF_K_PRIMARY, [&] { return launch_primary(sc, w, seed, first, n, ctr + 4, ctr + 2, profile, defer ? w.queue[0] : nullptr, ctr + 0, cfg); });
+        if (defer) timed(BF_K_TRACE_CLOSEST, [&] { return launch_trace_closest(sc, w, w.queue[0], ctr + 0, 0, 1, ctr + 4, ctr + 3, cfg, false); });
     } else {
         w.n_lanes = nullptr;
         timed(BF_K_RAYGEN, [&] { return launch_raygen(sc, w, seed, first, n, cfg); });

@@ -218,6 +218,7 @@ struct PrimaryIO {
     uint32_t *n_lanes;           // number of lanes handed out
     unsigned long long *total;   // closest queries traced
     float *profile;
+    uint32_t *defer_queue, *defer_count;   // DEFER: lanes whose ray enters the mesh bounds, traversed by the k_trace launch that follows
 };
 
 #ifndef BF_PRIMARY_CULL
@@ -226,7 +227,12 @@ struct PrimaryIO {
 #ifndef BF_PRIMARY_MIN_BLOCKS
 #define BF_PRIMARY_MIN_BLOCKS 8
 #endif
-template <int S, int GEN, int RXK>
+// DEFER (scenes where few receiver rays reach the meshes): no traversal here at all.  A ray that misses the padded mesh
+// bounds within [mint, nearest rectangle hit] is decided by the rectangles alone and committed as before; a ray that enters
+// them gets its lane straight away and is queued for a k_trace<closest> launch over just those lanes (dense warps), which
+// records the hit and feeds the shade queues, or leaves the lane a miss for k_finalize to count.  Every warp then generates
+// 32 samples per round, and the traversal code is out of this kernel's instruction footprint.
+template <int S, int GEN, int RXK, bool DEFER>
 __global__ void __launch_bounds__(TRACE_THREADS, BF_PRIMARY_MIN_BLOCKS) k_primary(const __grid_constant__ DevScene sc, const __grid_constant__ Wave w, const __grid_constant__ PrimaryIO io) {
     __shared__ float s_rect[RECT_SM_FLOATS * BF_MAX_RECTS];
     __shared__ uint2 s_stack[TRACE_SM_STACK * TRACE_THREADS];
@@ -255,12 +261,13 @@ __global__ void __launch_bounds__(TRACE_THREADS, BF_PRIMARY_MIN_BLOCKS) k_primar
     enum { EMPTY = 0, BUSY = 1, FINISHED = 2, EXHAUSTED = 3 };
     int state = EMPTY;
     uint32_t smp = 0;            // sample offset in the wave
+    bool deferred = false;       // DEFER: the ray needs the BVH
     TraceLane L;
     PrimaryState<S> ps;
     while (true) {
         // ---- commit finished samples (warp converged here) ----
         const bool fin = state == FINISHED;
-        const bool hit = fin && L.best.slot != BF_NONE;
+        const bool hit = fin && (L.best.slot != BF_NONE || (DEFER && deferred));      // = gets a lane
         if (fin && !hit) {
             float posx, posy; bool ran; int off_x, off_y;
             sample_position(sc, ps.x2, ps.wl.v[0], posx, posy, ran, off_x, off_y);
@@ -277,21 +284,29 @@ __global__ void __launch_bounds__(TRACE_THREADS, BF_PRIMARY_MIN_BLOCKS) k_primar
         }
         const uint32_t hits = __ballot_sync(0xffffffffu, hit);
         if (hits) {
-            const uint32_t cls = hit ? sc.shapes[L.best.shape].mat_class : 0u;
-            const uint32_t m0 = __ballot_sync(0xffffffffu, hit && cls == 0u), m1 = hits & ~m0;
-            // three reservations in flight together (lane slots + the two class queues), one wait
+            const bool shade_now = hit && !(DEFER && deferred);
+            const uint32_t cls = shade_now ? sc.shapes[L.best.shape].mat_class : 0u;
+            const uint32_t m0 = __ballot_sync(0xffffffffu, shade_now && cls == 0u), m1 = __ballot_sync(0xffffffffu, shade_now && cls != 0u);
+            const uint32_t md = DEFER ? hits & ~(m0 | m1) : 0u;
+            // the reservations are in flight together (lane slots, the two class queues, the traversal queue), one wait
             uint32_t base = 0;
             if (lane == 0) base = atomic_add_async(io.n_lanes, (uint32_t) __popc(hits));
             else if (lane == 1 && m0) base = atomic_add_async(io.hit_count + 0, (uint32_t) __popc(m0));
             else if (lane == 2 && m1) base = atomic_add_async(io.hit_count + 1, (uint32_t) __popc(m1));
+            else if (DEFER && lane == 3 && md) base = atomic_add_async(io.defer_count, (uint32_t) __popc(md));
             const uint32_t base_l = __shfl_sync(0xffffffffu, base, 0), base_0 = __shfl_sync(0xffffffffu, base, 1), base_1 = __shfl_sync(0xffffffffu, base, 2);
+            const uint32_t base_d = DEFER ? __shfl_sync(0xffffffffu, base, 3) : 0u;
             if (hit) {
                 const uint32_t dl = base_l + __popc(hits & lt_mask);
                 store_primary<S>(w, dl, ps);
-                w.hit[dl] = make_float4(L.best.t, L.best.u, L.best.v, __uint_as_float(L.best.slot));
                 if (w.sample_of) w.sample_of[dl] = smp;
-                if (cls == 0u) w.queue_h[base_0 + __popc(m0 & lt_mask)] = dl;
-                else w.queue_h2[base_1 + __popc(m1 & lt_mask)] = dl;
+                if (!shade_now) {
+                    io.defer_queue[base_d + __popc(md & lt_mask)] = dl;
+                } else {
+                    w.hit[dl] = make_float4(L.best.t, L.best.u, L.best.v, __uint_as_float(L.best.slot));
+                    if (cls == 0u) w.queue_h[base_0 + __popc(m0 & lt_mask)] = dl;
+                    else w.queue_h2[base_1 + __popc(m1 & lt_mask)] = dl;
+                }
                 if (w.records) init_record(w.records + smp, ps.wl.v[0]);
             }
         }
@@ -320,7 +335,8 @@ __global__ void __launch_bounds__(TRACE_THREADS, BF_PRIMARY_MIN_BLOCKS) k_primar
                     smp = i;
                     raygen_sample<S, GEN, RXK>(sc, io.seed, io.first_sample + i, ps);
                     L.o = ps.ray.o; L.d = ps.ray.d; L.mint = ps.ray.mint; L.maxt = ps.ray.maxt;
-                    state = trace_begin<false, BF_PRIMARY_CULL>(sc, s_rect, L) ? BUSY : FINISHED;
+                    if (DEFER) { deferred = trace_begin<false, true>(sc, s_rect, L); state = FINISHED; }
+                    else state = trace_begin<false, BF_PRIMARY_CULL>(sc, s_rect, L) ? BUSY : FINISHED;
                 } else {
                     state = EXHAUSTED;
                 }
@@ -329,7 +345,7 @@ __global__ void __launch_bounds__(TRACE_THREADS, BF_PRIMARY_MIN_BLOCKS) k_primar
         const uint32_t busy = __ballot_sync(0xffffffffu, state == BUSY);
         const uint32_t finm = __ballot_sync(0xffffffffu, state == FINISHED);
         if (busy == 0 && finm == 0) break;
-        if (busy == 0) continue;
+        if (DEFER || busy == 0) continue;
         const int min_busy = out_of_work ? 1 : TRACE_REFILL;
         if (BF_PRIMARY_CULL && !out_of_work && finm != 0 && __popc(busy) < min_busy) continue;
         do {
@@ -830,10 +846,10 @@ static TraceIO trace_io(const Wave &w, const float4 *dirs, const uint32_t *queue
     return io;
 }
 int launch_trace_closest(const DevScene &sc, const Wave &w, const uint32_t *queue, const uint32_t *count, uint32_t n_direct,
-                         uint32_t depth, uint32_t *hit_count, uint32_t *work_cursor, const LaunchCfg &cfg) {
+                         uint32_t depth, uint32_t *hit_count, uint32_t *work_cursor, const LaunchCfg &cfg, bool count_queries) {
     TraceIO io = trace_io(w, w.ray_d, queue, count, n_direct, work_cursor);
     io.hit = w.hit; io.hit_queue[0] = w.queue_h; io.hit_queue[1] = w.queue_h2; io.hit_count[0] = hit_count; io.hit_count[1] = hit_count + 1; io.x1 = w.x1; io.records = w.records; io.sample_of = w.sample_of; io.depth = depth;
-    io.total = w.totals + 0;
+    io.total = count_queries ? w.totals + 0 : nullptr;     // the deferred half of the primary query is counted by k_primary
     k_trace<false><<<trace_grid(cfg), TRACE_THREADS, 0, cfg.stream>>>(sc, io);
     return 1;
 }
@@ -880,14 +896,16 @@ int launch_finalize(const DevScene &sc, const Wave &w, uint32_t n, float *profil
     return 1;
 }
 int launch_primary(const DevScene &sc, const Wave &w, uint64_t seed, uint64_t first_sample, uint32_t n, uint32_t *hit_count,
-                   uint32_t *work_cursor, float *profile, const LaunchCfg &cfg) {
+                   uint32_t *work_cursor, float *profile, uint32_t *defer_queue, uint32_t *defer_count, const LaunchCfg &cfg) {
     if (n == 0) return 0;
     PrimaryIO io;
     io.seed = seed; io.first_sample = first_sample; io.n = n; io.work_cursor = work_cursor; io.hit_count = hit_count; io.n_lanes = w.n_lanes;
-    io.total = w.totals + 0; io.profile = profile;
+    io.total = w.totals + 0; io.profile = profile; io.defer_queue = defer_queue; io.defer_count = defer_count;
+    const bool defer = defer_queue != nullptr;
     const int grid = cfg.sm_count * BF_PRIMARY_MIN_BLOCKS;
     // specialised instantiations: gen-3 integrator with a wigner or an omnidirectional receiver; generic otherwise
-#define BF_PRIMARY(S_, G_, R_) k_primary<S_, G_, R_><<<grid, TRACE_THREADS, 0, cfg.stream>>>(sc, w, io)
+#define BF_PRIMARY(S_, G_, R_) do { if (defer) k_primary<S_, G_, R_, true><<<grid, TRACE_THREADS, 0, cfg.stream>>>(sc, w, io); \
+                                     else k_primary<S_, G_, R_, false><<<grid, TRACE_THREADS, 0, cfg.stream>>>(sc, w, io); } while (0)
 #define BF_PRIMARY_S(S_) do { \
         if (sc.integ.gen == BF_GEN_PHASE && sc.hint_rx_kind == BF_RX_WIGNER) BF_PRIMARY(S_, BF_GEN_PHASE, BF_RX_WIGNER); \
         else if (sc.integ.gen == BF_GEN_PHASE && sc.hint_rx_kind == BF_RX_OMNIDIRECTIONAL) BF_PRIMARY(S_, BF_GEN_PHASE, BF_RX_OMNIDIRECTIONAL); \

@@ -52,13 +52,15 @@ struct LaunchCfg {
 
 // Kernel launchers (bf_kernels.cu).  Return the number of kernels launched.
 // raygen + first closest-hit query + compaction of the hits into lanes [0, *w.n_lanes); misses are binned on the spot
+// defer_queue != nullptr: rays that enter the mesh bounds are not traversed here but queued (lane ids) for a
+// launch_trace_closest(depth 1) over defer_queue / defer_count
 int launch_primary(const DevScene &sc, const Wave &w, uint64_t seed, uint64_t first_sample, uint32_t n, uint32_t *hit_count,
-                   uint32_t *work_cursor, float *profile, const LaunchCfg &cfg);
+                   uint32_t *work_cursor, float *profile, uint32_t *defer_queue, uint32_t *defer_count, const LaunchCfg &cfg);
 int launch_raygen(const DevScene &sc, const Wave &w, uint64_t seed, uint64_t first_sample, uint32_t n, const LaunchCfg &cfg);
 // queue == nullptr: lanes [0, n_direct); else lane ids from queue[0 .. *count)
 // depth = the shade iteration this trace feeds; lanes that hit are appended to w.queue_h / *hit_count
 int launch_trace_closest(const DevScene &sc, const Wave &w, const uint32_t *queue, const uint32_t *count, uint32_t n_direct,
-                         uint32_t depth, uint32_t *hit_count, uint32_t *work_cursor, const LaunchCfg &cfg);
+                         uint32_t depth, uint32_t *hit_count, uint32_t *work_cursor, const LaunchCfg &cfg, bool count_queries = true);
 int launch_trace_shadow(const DevScene &sc, const Wave &w, const uint32_t *queue, const uint32_t *count, uint32_t *work_cursor,
                         const LaunchCfg &cfg);
 // shades the lanes of w.queue_h[0 .. hit_counts[0]) and w.queue_h2[0 .. hit_counts[1]); n_bound >= their sum

@@ -156,6 +156,32 @@ def test_fused_primary_equals_unfused(native, monkeypatch):
     s.close()
 
 
+@pytest.mark.parametrize("width,frame", [(1, False), (4, False), (1, True)])
+def test_deferred_primary_equals_fused(native, monkeypatch, width, frame):
+    """k_primary<DEFER> (rays that enter the mesh bounds are traversed by a separate dense k_trace launch) against the fused
+    in-kernel traversal: bit-identical per-sample records, identical counts, same query statistics."""
+    s = configs.small_radar(spectrum_width=width)
+    if frame:
+        s.set_adc(t_bins=64, f_bins=256, t_bandwidth=200e-6, f_bandwidth=256 * 0.12 * 2.0 / configs.C0 * (6e9 / 200e-6))
+    s.commit()
+    n = 50000
+    out = {}
+    for mode in ("0", "1"):
+        monkeypatch.setenv("BF_PRIMARY_DEFER", mode)
+        before = s.stats()
+        rec = s.sample_records(n, seed=5)
+        s.receive(1 << 18, seed=6)
+        prof = s.profile()
+        after = s.stats()
+        out[mode] = (rec, prof, after["closest_queries"] - before["closest_queries"], after["shadow_queries"] - before["shadow_queries"])
+    a, b = out["0"], out["1"]
+    assert a[0].tobytes() == b[0].tobytes()
+    assert np.array_equal(a[1][..., 1:3], b[1][..., 1:3])
+    assert rel_l2(a[1][..., 0], b[1][..., 0]) <= 1e-5 and rel_l2(a[1][..., 3], b[1][..., 3]) <= 1e-5
+    assert a[2] == b[2] and a[3] == b[3]
+    s.close()
+
+
 def test_range_time_frame_global_scatter(native):
     """A 64 x 256 (time x beat-frequency) frame does not fit the shared-memory histograms: samples are scattered to HBM
     directly (one 128-bit reduction per sample in k_finalize, weight-channel adds for the misses in k_primary)."""
