@@ -839,12 +839,19 @@ static int run_wave(bf_scene *s, WaveSlot &sl, uint64_t seed, uint64_t first, ui
         timed(BF_K_RAYGEN, [&] { return launch_raygen(sc, w, seed, first, n, cfg); });
         timed(BF_K_TRACE_CLOSEST, [&] { return launch_trace_closest(sc, w, nullptr, nullptr, n, 1, ctr + 4, ctr + 2, cfg); });
     }
+    const bool trace_defer = env_u32("BF_TRACE_DEFER", s->primary_defer ? 1 : 0, 0, 1) != 0 && sc.n_nodes != 0;
     for (uint32_t depth = 1; depth <= max_depth; ++depth) {
         uint32_t *blk = ctr + (size_t) BF_CTR_STRIDE * depth, *prev = ctr + (size_t) BF_CTR_STRIDE * (depth - 1);
         timed(BF_K_SHADE, [&] { return launch_shade(sc, w, depth, prev + 4, n, w.queue[0], blk, cfg); });
         if (depth >= max_depth) break;
         timed(BF_K_TRACE_SHADOW, [&] { return launch_trace_shadow(sc, w, w.queue_s, blk + 1, blk + 3, cfg); });
-        timed(BF_K_TRACE_CLOSEST, [&] { return launch_trace_closest(sc, w, w.queue[0], blk + 0, 0, depth + 1, blk + 4, blk + 2, cfg); });
+        if (trace_defer) {
+            // the shadow launch above has consumed queue_s: it carries the deferred lanes to the dense follow-up launch
+            timed(BF_K_TRACE_CLOSEST, [&] { return launch_trace_closest(sc, w, w.queue[0], blk + 0, 0, depth + 1, blk + 4, blk + 2, cfg, true, w.queue_s, blk + 6); });
+            timed(BF_K_TRACE_CLOSEST, [&] { return launch_trace_closest(sc, w, w.queue_s, blk + 6, 0, depth + 1, blk + 4, blk + 7, cfg, false); });
+        } else {
+            timed(BF_K_TRACE_CLOSEST, [&] { return launch_trace_closest(sc, w, w.queue[0], blk + 0, 0, depth + 1, blk + 4, blk + 2, cfg); });
+        }
         if (unbounded && depth >= 8) {
             BF_CUDA(cudaMemcpyAsync(sl.h_counts, blk, 8, cudaMemcpyDeviceToHost, sl.stream));
             BF_CUDA(cudaStreamSynchronize(sl.stream));

@@ -846,11 +846,14 @@ static TraceIO trace_io(const Wave &w, const float4 *dirs, const uint32_t *queue
     return io;
 }
 int launch_trace_closest(const DevScene &sc, const Wave &w, const uint32_t *queue, const uint32_t *count, uint32_t n_direct,
-                         uint32_t depth, uint32_t *hit_count, uint32_t *work_cursor, const LaunchCfg &cfg, bool count_queries) {
+                         uint32_t depth, uint32_t *hit_count, uint32_t *work_cursor, const LaunchCfg &cfg, bool count_queries,
+                         uint32_t *defer_queue, uint32_t *defer_count) {
     TraceIO io = trace_io(w, w.ray_d, queue, count, n_direct, work_cursor);
     io.hit = w.hit; io.hit_queue[0] = w.queue_h; io.hit_queue[1] = w.queue_h2; io.hit_count[0] = hit_count; io.hit_count[1] = hit_count + 1; io.x1 = w.x1; io.records = w.records; io.sample_of = w.sample_of; io.depth = depth;
-    io.total = count_queries ? w.totals + 0 : nullptr;     // the deferred half of the primary query is counted by k_primary
-    k_trace<false><<<trace_grid(cfg), TRACE_THREADS, 0, cfg.stream>>>(sc, io);
+    io.total = count_queries ? w.totals + 0 : nullptr;     // the deferred half of a query is counted by the launch that deferred it
+    io.hit_queue[2] = defer_queue; io.hit_count[2] = defer_count;
+    if (defer_queue) k_trace<false, true><<<trace_grid(cfg), TRACE_THREADS, 0, cfg.stream>>>(sc, io);
+    else k_trace<false><<<trace_grid(cfg), TRACE_THREADS, 0, cfg.stream>>>(sc, io);
     return 1;
 }
 int launch_trace_shadow(const DevScene &sc, const Wave &w, const uint32_t *queue, const uint32_t *count, uint32_t *work_cursor,

@@ -263,7 +263,7 @@ struct TraceIO {
     uint32_t *occl;                  // any-hit: 0 / 1
     // closest: lanes whose ray hit something, split by the material class of the surface hit (the shade kernel's
     // input: class 0 = diffuse, class 1 = everything else), so that a shading warp runs one BSDF.  May be null.
-    uint32_t *hit_queue[2], *hit_count[2];
+    uint32_t *hit_queue[3], *hit_count[3];   // [2] (DEFER): lanes whose ray enters the mesh bounds, for the dense follow-up launch
     float4 *x1;                      // closest, gen 3, depth > 1: a missed continuation ray leaves time = phase = -inf
     bf_sample_record *records;
     const uint32_t *sample_of;       // lane -> record index (null: identity)
@@ -277,7 +277,10 @@ struct TraceIO {
 // claim in flight (the atomic is issued when the previous chunk is opened and its result is first read when that
 // chunk runs dry), so the ~1 us round trip of a returning global atomic is off the critical path.  The same is
 // done for hit-queue pushes: the slot reservation is issued at one commit point and consumed at the next.
-template <bool ANY_HIT>
+// DEFER (closest queries of scenes where few rays reach the meshes): this launch decides the rays that miss the mesh bounds
+// from the rectangles alone and queues the others (hit_queue[2]) for a second, plain launch that traverses them with dense
+// warps -- the split k_primary<DEFER> makes for the receiver rays.
+template <bool ANY_HIT, bool DEFER = false>
 __global__ void __launch_bounds__(TRACE_THREADS, TRACE_MIN_BLOCKS) k_trace(const __grid_constant__ DevScene sc, const __grid_constant__ TraceIO io) {
     __shared__ float s_rect[RECT_SM_FLOATS * BF_MAX_RECTS];
     __shared__ uint2 s_stack[TRACE_SM_STACK * TRACE_THREADS];
@@ -295,13 +298,18 @@ __global__ void __launch_bounds__(TRACE_THREADS, TRACE_MIN_BLOCKS) k_trace(const
     const bool dynamic = n > static_total;
     uint32_t chunk = 32;
     while (dynamic && chunk < 256 && chunk * 16 * n_warps <= n - static_total) chunk *= 2;
-    uint32_t c_next = (blockIdx.x * (TRACE_THREADS / 32) + (threadIdx.x >> 5)) * 32u, c_end = c_next + 32u;   // warp-uniform
+    // a launch smaller than one static batch per warp (the deferred-lane launches, deep bounces) is cut evenly over all
+    // the warps instead: such a launch is bound by its slowest rays, and fewer rays per warp means more of them run at once
+    const uint32_t quota = dynamic ? 32u : max((n + n_warps - 1u) / n_warps, 1u);
+    uint32_t c_next = (blockIdx.x * (TRACE_THREADS / 32) + (threadIdx.x >> 5)) * quota, c_end = c_next + quota;   // warp-uniform
     uint32_t claim = 0xffffffffu;                   // lane 0: start of the chunk claimed ahead
     if (dynamic && lane == 0) claim = static_total + atomic_add_async(io.work_cursor, chunk);
     bool out_of_work = c_next >= n;
 
     // deferred hit-queue push
-    uint32_t pend_base = 0, pend_meta = 0;          // meta: bit 31 valid, bit 30 class, bits 0..4 rank, bits 8..12 leader lane
+    uint32_t pend_base = 0, pend_meta = 0;          // meta: bit 31 valid, bits 29..30 queue (class 0 / 1, 2 = deferred)
+    constexpr int N_QUEUES = DEFER ? 3 : 2;
+    bool deferred = false;
 
     enum { EMPTY = 0, BUSY = 1, FINISHED = 2, EXHAUSTED = 3 };
     int state = EMPTY;
@@ -313,8 +321,8 @@ __global__ void __launch_bounds__(TRACE_THREADS, TRACE_MIN_BLOCKS) k_trace(const
             uint32_t any = __ballot_sync(0xffffffffu, pend_meta >> 31);
             if (any) {
 #pragma unroll
-                for (int c = 0; c < 2; ++c) {
-                    uint32_t m = __ballot_sync(0xffffffffu, (pend_meta >> 31) && ((pend_meta >> 30) & 1u) == (uint32_t) c);
+                for (int c = 0; c < N_QUEUES; ++c) {
+                    uint32_t m = __ballot_sync(0xffffffffu, (pend_meta >> 31) && ((pend_meta >> 29) & 3u) == (uint32_t) c);
                     if (m) {
                         uint32_t base = __shfl_sync(0xffffffffu, pend_base, __ffs(m) - 1);
                         if ((m >> lane) & 1u) io.hit_queue[c][base + __popc(m & lt_mask)] = pend_l;
@@ -330,6 +338,8 @@ __global__ void __launch_bounds__(TRACE_THREADS, TRACE_MIN_BLOCKS) k_trace(const
             if (io.steps) io.steps[l] = n_steps;
             if (ANY_HIT) {
                 io.occl[l] = L.occluded ? 1u : 0u;
+            } else if (DEFER && deferred) {
+                push = true; cls = 2;                // nothing decided yet: the follow-up launch redoes the query for this lane
             } else {
                 const bool hit = L.best.slot != BF_NONE;
                 io.hit[l] = make_float4(hit ? L.best.t : bf_inf(), L.best.u, L.best.v, __uint_as_float(L.best.slot));
@@ -348,11 +358,11 @@ __global__ void __launch_bounds__(TRACE_THREADS, TRACE_MIN_BLOCKS) k_trace(const
         }
         if (push_hits) {
 #pragma unroll
-            for (int c = 0; c < 2; ++c) {
+            for (int c = 0; c < N_QUEUES; ++c) {
                 uint32_t m = __ballot_sync(0xffffffffu, push && cls == (uint32_t) c);
                 if (m) {
                     if (lane == (uint32_t) (__ffs(m) - 1)) pend_base = atomic_add_async(io.hit_count[c], (uint32_t) __popc(m));   // consumed next round
-                    if ((m >> lane) & 1u) { pend_meta = 0x80000000u | ((uint32_t) c << 30); pend_l = l; }
+                    if ((m >> lane) & 1u) { pend_meta = 0x80000000u | ((uint32_t) c << 29); pend_l = l; }
                 }
             }
         }
@@ -381,7 +391,9 @@ __global__ void __launch_bounds__(TRACE_THREADS, TRACE_MIN_BLOCKS) k_trace(const
                     float4 ro = ld_stream(io.ray_o + l), rd = ld_stream(io.ray_d + l);
                     L.o = V3(ro.x, ro.y, ro.z); L.d = V3(rd.x, rd.y, rd.z); L.mint = ro.w; L.maxt = rd.w;
                     n_steps = 0;
-                    state = trace_begin<ANY_HIT>(sc, s_rect, L) ? BUSY : FINISHED;
+                    const bool traverse = trace_begin<ANY_HIT>(sc, s_rect, L);
+                    if (DEFER) { deferred = traverse; state = FINISHED; }
+                    else state = traverse ? BUSY : FINISHED;
                 } else {
                     state = EXHAUSTED;              // only reached once the cursor is past the end
                 }

@@ -60,7 +60,8 @@ int launch_raygen(const DevScene &sc, const Wave &w, uint64_t seed, uint64_t fir
 // queue == nullptr: lanes [0, n_direct); else lane ids from queue[0 .. *count)
 // depth = the shade iteration this trace feeds; lanes that hit are appended to w.queue_h / *hit_count
 int launch_trace_closest(const DevScene &sc, const Wave &w, const uint32_t *queue, const uint32_t *count, uint32_t n_direct,
-                         uint32_t depth, uint32_t *hit_count, uint32_t *work_cursor, const LaunchCfg &cfg, bool count_queries = true);
+                         uint32_t depth, uint32_t *hit_count, uint32_t *work_cursor, const LaunchCfg &cfg, bool count_queries = true,
+                         uint32_t *defer_queue = nullptr, uint32_t *defer_count = nullptr);
 int launch_trace_shadow(const DevScene &sc, const Wave &w, const uint32_t *queue, const uint32_t *count, uint32_t *work_cursor,
                         const LaunchCfg &cfg);
 // shades the lanes of w.queue_h[0 .. hit_counts[0]) and w.queue_h2[0 .. hit_counts[1]); n_bound >= their sum

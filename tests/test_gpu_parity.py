@@ -168,6 +168,7 @@ def test_deferred_primary_equals_fused(native, monkeypatch, width, frame):
     out = {}
     for mode in ("0", "1"):
         monkeypatch.setenv("BF_PRIMARY_DEFER", mode)
+        monkeypatch.setenv("BF_TRACE_DEFER", mode)           # the same split for the later closest-hit launches
         before = s.stats()
         rec = s.sample_records(n, seed=5)
         s.receive(1 << 18, seed=6)

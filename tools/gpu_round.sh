@@ -11,7 +11,7 @@ timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 800 --c
     python bench.py --steps 2 --warmup 1 --samples 16777216 --no-cpu-baseline > gpurun_out/ncu_launches_$tag.log 2>&1
 if [ "$2" = "full" ]; then
   BF_WAVE_LANES=8388608 BF_WAVE_STREAMS=1 timeout 900 ncu --set full --clock-control none --import-source on -f -o gpurun_out/prof_$tag \
-      --launch-skip 17 --launch-count 17 python tools/kernel_breakdown.py 8388608 > gpurun_out/ncu_full_$tag.log 2>&1
+      --launch-skip 20 --launch-count 20 python tools/kernel_breakdown.py 8388608 > gpurun_out/ncu_full_$tag.log 2>&1
 fi
 tail -3 gpurun_out/pytest_gpu_$tag.log
 cat gpurun_out/breakdown_8M_$tag.log
