@@ -110,6 +110,7 @@ PROTOTYPES = {
     "bf_get_stats": (C.c_int, [vp, P(bf_stats)]),
     "bf_last_receive_ms": (C.c_int, [vp, P(f32), P(f32)]),
     "bf_set_trace_timing": (C.c_int, [vp, C.c_int]),
+    "bf_set_tunable": (C.c_int, [vp, C.c_char_p, C.c_int64]),
     "bf_last_kernel_ms": (C.c_int, [vp, P(f32), P(u32)]),
     "bf_last_launch_list": (C.c_int, [vp, P(f32), P(u32), u32, P(u32)]),
     "bf_scene_export": (C.c_int, [vp, vp, C.c_size_t, P(C.c_size_t)]),

@@ -45,19 +45,36 @@ def fmcw_signal(resample_freq, gain=1.0):
 
 
 def radar_scene(mesh_pos, mesh_faces, spectrum_width=1, max_depth=4, range_bins=1024, bin_m=0.03, smooth_normals=True,
-                extra_meshes=(), phased=None, ground_half=20.0, reflector=True, return_ids=False, omni_area=False):
+                extra_meshes=(), phased=None, ground_half=20.0, reflector=True, return_ids=False, omni_area=False, variant=None):
     """Common 94 GHz FMCW layout of python_scripts/Render.py / Receive.ipynb: Tx and Rx are 5 mm x 5 mm
     rectangles at (0, 0, 0.3) facing +x, ground 20 x 20 diffuse 0.5, corner reflector 0.1 x 0.05 diffuse 1,
     target mesh twosided(roughconductor alpha 0.1).  Receiver `wignerreceiver` (mix_resample) + transmitter
     `wignertransmitter` (resample_freq): beat frequency = sweep rate x delay, binned on the frequency axis."""
+    # `variant`: overrides used by the parity tests to reach every branch of the path (all default to the layout above):
+    #   tx_signal / rx_signal (bf_signal_desc), receive_type, phase_bins, rr_depth, car_bsdf (kwargs of add_bsdf),
+    #   ground_spectrum ("regular" | "irregular": two / three-point tables as python_scripts/trans_image_rad.xml:53 writes them),
+    #   window (kwargs of set_adc: window_t_bins, window_f_bins, window_offset_t, window_offset_f), t_bins,
+    #   second_tx (True: a second wignertransmitter on its own aperture)
+    v = dict(variant or {})
     s = FlatScene(spectrum_width=spectrum_width, **RADAR_94GHZ)
     default_bsdf = s.add_diffuse(0.5, two_sided=False)
-    ground = s.add_diffuse(0.5, two_sided=True)
-    refl = s.add_diffuse(1.0, two_sided=True)
+    lam_lo, lam_hi = RADAR_94GHZ["lambda_min_nm"], RADAR_94GHZ["lambda_max_nm"]
+    if v.get("ground_spectrum") == "regular":
+        ground = s.add_bsdf(N.BF_BSDF_DIFFUSE, two_sided=True, reflectance=s.add_spectrum(N.BF_SPEC_REGULAR, [0.5, 0.5], [lam_lo, lam_hi]))
+        refl = s.add_bsdf(N.BF_BSDF_DIFFUSE, two_sided=True, reflectance=s.add_spectrum(N.BF_SPEC_REGULAR, [0.9, 1.0], [lam_lo, lam_hi]))
+    elif v.get("ground_spectrum") == "irregular":
+        mid = lam_lo + 0.3 * (lam_hi - lam_lo)
+        ground = s.add_bsdf(N.BF_BSDF_DIFFUSE, two_sided=True, reflectance=s.add_spectrum(N.BF_SPEC_IRREGULAR, [0.4, 0.6, 0.5], [lam_lo, mid, lam_hi]))
+        refl = s.add_bsdf(N.BF_BSDF_DIFFUSE, two_sided=True, reflectance=s.add_spectrum(N.BF_SPEC_IRREGULAR, [1.0, 0.8, 1.0], [lam_lo, mid, lam_hi]))
+    else:
+        ground = s.add_diffuse(0.5, two_sided=True)
+        refl = s.add_diffuse(1.0, two_sided=True)
     # twosided(roughconductor): Beckmann alpha 0.1; a perfect conductor at radar wavelengths (the
     # reference's default Cu table evaluates to eta = k = 0 outside the visible range => F = 1)
     eta, k = s.add_uniform(0.0), s.add_uniform(1.0)
-    car = s.add_bsdf(N.BF_BSDF_ROUGHCONDUCTOR, two_sided=True, eta=eta, k=k, alpha_u=0.1, alpha_v=0.1)
+    car_kw = dict(kind=N.BF_BSDF_ROUGHCONDUCTOR, two_sided=True, eta=eta, k=k, alpha_u=0.1, alpha_v=0.1)
+    car_kw.update(v.get("car_bsdf", {}))
+    car = s.add_bsdf(car_kw.pop("kind"), **car_kw)
     ant = (T.translate([0.0, 0.0, 0.3]) * T.rotate([0, 1, 0], 90.0) * T.scale([0.0025, 0.0025, 1.0]))
     rx = s.add_rect(ant.matrix32(), default_bsdf)
     tx = s.add_rect((T.translate([0.0, 0.01, 0.0]) * ant).matrix32(), default_bsdf)
@@ -82,13 +99,17 @@ def radar_scene(mesh_pos, mesh_faces, spectrum_width=1, max_depth=4, range_bins=
         tx_arr, rx_arr = arr(T.translate([0.0, 0.01, 0.0]) * pose), arr(pose)
     if omni_area:   # `areatransmitter` + `omnidirectional` receiver (Receive.ipynb cells 13, 15 use the omnidirectional receiver)
         tx_kind, rx_kind = N.BF_TX_AREA, N.BF_RX_OMNIDIRECTIONAL
-    s.add_transmitter(tx, FlatScene.endpoint(tx_kind, texture=tex, signal=fmcw_signal(True), array=tx_arr))
+    s.add_transmitter(tx, FlatScene.endpoint(tx_kind, texture=tex, signal=v.get("tx_signal", fmcw_signal(True)), array=tx_arr))
+    if v.get("second_tx"):
+        tx2 = s.add_rect((T.translate([0.0, -0.02, 0.1]) * ant).matrix32(), default_bsdf)
+        s.add_transmitter(tx2, FlatScene.endpoint(tx_kind, texture=s.add_uniform(0.5), signal=v.get("tx_signal", fmcw_signal(True)), array=tx_arr))
     sweep_rate = 6e9 / 200e-6
-    f_bandwidth = range_bins * bin_m * 2.0 / C0 * sweep_rate
-    s.set_receiver(rx, FlatScene.endpoint(rx_kind, texture=tex, signal=fmcw_signal(False), receive_type=N.BF_RECV_MIX_RESAMPLE,
+    f_bandwidth = v.get("f_bandwidth", range_bins * bin_m * 2.0 / C0 * sweep_rate)
+    s.set_receiver(rx, FlatScene.endpoint(rx_kind, texture=tex, signal=v.get("rx_signal", fmcw_signal(False)),
+                                          receive_type=v.get("receive_type", N.BF_RECV_MIX_RESAMPLE),
                                           adc_sampling_start=20e-6, adc_sampling_time=160e-6, array=rx_arr))
-    s.set_adc(t_bins=1, f_bins=range_bins, t_bandwidth=200e-6, f_bandwidth=f_bandwidth)
-    s.set_integrator(N.BF_GEN_PHASE, max_depth=max_depth, rr_depth=5, phase_bins=1)
+    s.set_adc(t_bins=v.get("t_bins", 1), f_bins=range_bins, t_bandwidth=200e-6, f_bandwidth=f_bandwidth, **v.get("window", {}))
+    s.set_integrator(N.BF_GEN_PHASE, max_depth=max_depth, rr_depth=v.get("rr_depth", 5), phase_bins=v.get("phase_bins", 1))
     return (s, rx, tx) if return_ids else s
 
 
@@ -104,11 +125,12 @@ def c2_car_body(spectrum_width=1, max_depth=4, n_u=264, n_v=133):
     return radar_scene(p, f, spectrum_width=spectrum_width, max_depth=max_depth)
 
 
-def small_radar(spectrum_width=1, max_depth=4, n_u=24, n_v=13, smooth_normals=True, phased=None, omni_area=False):
+def small_radar(spectrum_width=1, max_depth=4, n_u=24, n_v=13, smooth_normals=True, phased=None, omni_area=False, variant=None):
     """The C2 layout with a few hundred triangles: sized for the brute-force oracle."""
     p, f = meshes.car_body(n_u, n_v)
     p = meshes.transform_points(car_pose().matrix32(), p)
-    return radar_scene(p, f, spectrum_width=spectrum_width, max_depth=max_depth, smooth_normals=smooth_normals, phased=phased, omni_area=omni_area)
+    return radar_scene(p, f, spectrum_width=spectrum_width, max_depth=max_depth, smooth_normals=smooth_normals, phased=phased, omni_area=omni_area,
+                       variant=variant)
 
 
 def c3_multi_object(spectrum_width=1, max_depth=4, copies=14, n_u=264, n_v=133, f_bins=1024, t_bins=1024):

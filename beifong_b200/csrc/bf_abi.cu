@@ -57,6 +57,14 @@ DevRect make_rect(const float *to_world16, uint32_t shape) {
     r.wid_x = norm(r.fs); r.wid_y = norm(r.ft);
     r.ns = normalize(r.fs); r.nt = normalize(r.ft); r.nn = normalize(r.fn);
     r.shape = shape;
+    coordinate_system(r.fn, r.cs_s, r.cs_t);
+    {   // interaction.h:159-162 with sh_frame.n = n = fn and dp_du = fs
+        const float dn = dot(r.fn, r.fs);
+        r.sh_s = normalize(V3(fnmadd(r.fn.x, dn, r.fs.x), fnmadd(r.fn.y, dn, r.fs.y), fnmadd(r.fn.z, dn, r.fs.z)));
+        r.sh_t = cross(r.fn, r.sh_s);
+    }
+    r.two_pi_inv_area = rcp(r.area) * BF_TWO_PI;
+    r.area_pi = r.area * BF_PI;
     // padded world-space box of the four corners: margin 1e-4 of the largest coordinate / extent involved, far above the
     // rounding of the object-space test it guards (a few 1e-7 relative)
     float lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY}, mag = 1e-3f;
@@ -140,8 +148,41 @@ struct WaveSlot {
     uint32_t *h_counts = nullptr;     // pinned read-back of queue counts
 };
 
+// Launch-shape knobs.  Defaults come from the environment ONCE, when the scene is created (BF_WAVE_LANES, BF_WAVE_STREAMS,
+// BF_FUSED_PRIMARY, BF_PRIMARY_DEFER, BF_TRACE_DEFER, BF_TRACE_ROUNDS); bf_set_tunable changes them per scene afterwards.
+// None of them changes a result: they select between launch sequences that are tested bit-identical per sample.
+struct Tunables {
+    int64_t wave_lanes = 0;       // 0: chosen from the request size
+    int64_t wave_streams = 8;
+    int64_t fused_primary = 1;
+    int64_t primary_defer = -1;   // -1: bf_scene_commit's estimate
+    int64_t trace_defer = -1;
+    int64_t trace_rounds = 8;     // batches of 32 rays per active traversal warp (0: all warps of the grid)
+    int64_t use_graph = 1;        // small calls: replay the wave's launch sequence from a CUDA graph
+};
+static int64_t env_i64(const char *name, int64_t dflt, int64_t lo, int64_t hi) {
+    const char *e = getenv(name);
+    if (!e || !*e) return dflt;
+    long long v = atoll(e);
+    if (v < lo) v = lo;
+    if (v > hi) v = hi;
+    return (int64_t) v;
+}
+static Tunables tunables_from_env() {
+    Tunables t;
+    t.wave_lanes = env_i64("BF_WAVE_LANES", 0, 0, 1ll << 26);
+    t.wave_streams = env_i64("BF_WAVE_STREAMS", 8, 1, 16);
+    t.fused_primary = env_i64("BF_FUSED_PRIMARY", 1, 0, 1);
+    t.primary_defer = env_i64("BF_PRIMARY_DEFER", -1, -1, 1);
+    t.trace_defer = env_i64("BF_TRACE_DEFER", -1, -1, 1);
+    t.trace_rounds = env_i64("BF_TRACE_ROUNDS", 8, 0, 1024);
+    t.use_graph = env_i64("BF_USE_GRAPH", 1, 0, 1);
+    return t;
+}
+
 struct bf_scene {
     bf_constants C;
+    Tunables tune;
     std::vector<HostSpectrum> spectra;
     std::vector<bf_bsdf_desc> bsdfs;
     std::vector<HostMesh> meshes;
@@ -149,7 +190,7 @@ struct bf_scene {
     std::vector<size_t> rect_blob_off;   // offset of each rectangle's record in the export blob (bf_scene_update_rect rewrites it)
     std::vector<HostShape> shapes;
     std::vector<HostTx> txs;
-    int32_t rx_shape = -1; bf_endpoint_desc rx; bool has_rx = false;
+    int32_t rx_shape = -1; bf_endpoint_desc rx; bool has_rx = false; size_t rx_blob_off = (size_t) -1;
     bf_adc_desc adc; bool has_adc = false;
     bf_integrator_desc integ; bool has_integ = false;
     std::vector<uint8_t> blob;        // recorded construction calls (flat_scene.h)
@@ -169,6 +210,7 @@ struct bf_scene {
     DevBuf<uint32_t> d_developed;    // bf_profile_develop output (fp32 or fp16 components)
     // image of the geometry tables in pinned host memory (re-upload without a rebuild)
     void *h_geom = nullptr; size_t h_geom_bytes = 0, h_nodes_bytes = 0, h_tris_bytes = 0, h_nrm_bytes = 0;
+    void *h_tables = nullptr; size_t h_tables_bytes = 0;   // pinned staging of the small tables (upload_tables)
     // wave
     std::vector<WaveSlot> slots;      // slot 0 runs on `stream`
     DevBuf<unsigned long long> d_totals;
@@ -290,6 +332,7 @@ static DevEndpoint make_endpoint(const bf_endpoint_desc &d, int32_t shape) {
     memset(&e, 0, sizeof(e));
     e.kind = d.kind; e.texture = d.texture; e.receive_type = d.receive_type; e.shape = shape;
     e.signal = d.signal;
+    e.sig_period = rcp(d.signal.repfreq); e.sig_ti = 0 + d.signal.t_ext / 2; e.sig_slope = d.signal.f_ext / d.signal.t_ext;
     e.adc_sampling_start = d.adc_sampling_start; e.adc_sampling_time = d.adc_sampling_time;
     e.near_clip = d.near_clip; e.far_clip = d.far_clip;
     e.shutter_open = d.shutter_open; e.shutter_open_time = d.shutter_open_time;
@@ -320,6 +363,7 @@ int bf_scene_create(const bf_constants *consts, bf_scene **out) {
     if (!(consts->c > 0.f)) return fail(nullptr, BF_ERR_INVALID, "bf_scene_create: propagation speed must be positive");
     bf_scene *s = new bf_scene();
     s->C = *consts;
+    s->tune = tunables_from_env();
     memset(&s->rx, 0, sizeof(s->rx)); memset(&s->adc, 0, sizeof(s->adc)); memset(&s->integ, 0, sizeof(s->integ));
     memset(&s->stats, 0, sizeof(s->stats)); memset(&s->dev, 0, sizeof(s->dev));
     *out = s;
@@ -338,6 +382,7 @@ void bf_scene_destroy(bf_scene *s) {
         s->d_bsdfs.release(); s->d_spectra.release(); s->d_spec_pool.release(); s->d_txs.release(); s->d_rx.release(); s->d_velems.release();
         s->d_profile.release(); s->d_developed.release(); s->d_totals.release();
         if (s->h_geom) cudaFreeHost(s->h_geom);
+        if (s->h_tables) cudaFreeHost(s->h_tables);
         if (s->ev_fork) cudaEventDestroy(s->ev_fork);
         if (s->ev_begin) cudaEventDestroy(s->ev_begin);
         if (s->ev_end) cudaEventDestroy(s->ev_end);
@@ -456,10 +501,22 @@ int bf_scene_set_receiver(bf_scene *s, uint32_t shape_id, const bf_endpoint_desc
     if (!s) return BF_ERR_INVALID;
     int rc = check_endpoint(s, shape_id, desc, false);
     if (rc) return rc;
+    if (s->committed && s->integ.gen != BF_GEN_PHASE) {
+        // gen 1/2: the film size comes from the sensor; the device profile was sized at commit (a larger film would scatter out of bounds)
+        const uint32_t w0 = s->rx.film_width ? s->rx.film_width : 1, h0 = s->rx.film_height ? s->rx.film_height : 1;
+        const uint32_t w1 = desc->film_width ? desc->film_width : 1, h1 = desc->film_height ? desc->film_height : 1;
+        if (w0 != w1 || h0 != h1) return fail(s, BF_ERR_STATE, "bf_scene_set_receiver: the film size cannot change after bf_scene_commit");
+    }
     s->rx = *desc; s->has_rx = true;
     s->rx_shape = desc->kind == BF_RX_PERSPECTIVE ? -1 : (int32_t) shape_id;
     uint32_t hdr[2] = {s->rx_shape < 0 ? BF_NONE : shape_id, 0};
-    record(s, BF_TAG_RX, hdr, 8, desc, sizeof(*desc));
+    if (s->rx_blob_off != (size_t) -1) {   // re-posed receiver: rewrite its record in place, the export stays one RX record long
+        uint8_t *p = s->blob.data() + s->rx_blob_off + sizeof(bf_flat_record);
+        memcpy(p, hdr, 8); memcpy(p + 8, desc, sizeof(*desc));
+    } else {
+        s->rx_blob_off = s->blob.size();
+        record(s, BF_TAG_RX, hdr, 8, desc, sizeof(*desc));
+    }
     s->tables_dirty = true;
     return BF_OK;
 }
@@ -567,15 +624,32 @@ static int upload_tables(bf_scene *s) {
     BF_CUDA(s->d_shapes.alloc(sh.size())); BF_CUDA(s->d_bsdfs.alloc(s->bsdfs.size()));
     BF_CUDA(s->d_rects.alloc(s->rects.size())); BF_CUDA(s->d_txs.alloc(txs.size())); BF_CUDA(s->d_rx.alloc(1));
     BF_CUDA(s->d_velems.alloc(velems.size()));
+    // The tables are packed into ONE pinned staging buffer and copied with cudaMemcpyAsync on the scene's stream, so the
+    // copies are ordered before every kernel of the next bf_receive (the wave streams fork from that stream).  The
+    // synchronize keeps the staging buffer from being rewritten while an earlier upload is still in flight (every wave
+    // stream has been joined back into s->stream by the end of bf_receive).
     BF_CUDA(cudaStreamSynchronize(s->stream));
-    if (!velems.empty()) BF_CUDA(cudaMemcpy(s->d_velems.p, velems.data(), velems.size() * sizeof(DevVElem), cudaMemcpyHostToDevice));
-    if (!ds.empty()) BF_CUDA(cudaMemcpy(s->d_spectra.p, ds.data(), ds.size() * sizeof(DevSpectrum), cudaMemcpyHostToDevice));
-    if (!pool.empty()) BF_CUDA(cudaMemcpy(s->d_spec_pool.p, pool.data(), pool.size() * 4, cudaMemcpyHostToDevice));
-    if (!sh.empty()) BF_CUDA(cudaMemcpy(s->d_shapes.p, sh.data(), sh.size() * sizeof(DevShape), cudaMemcpyHostToDevice));
-    if (!s->bsdfs.empty()) BF_CUDA(cudaMemcpy(s->d_bsdfs.p, s->bsdfs.data(), s->bsdfs.size() * sizeof(bf_bsdf_desc), cudaMemcpyHostToDevice));
-    if (!s->rects.empty()) BF_CUDA(cudaMemcpy(s->d_rects.p, s->rects.data(), s->rects.size() * sizeof(DevRect), cudaMemcpyHostToDevice));
-    if (!txs.empty()) BF_CUDA(cudaMemcpy(s->d_txs.p, txs.data(), txs.size() * sizeof(DevEndpoint), cudaMemcpyHostToDevice));
-    BF_CUDA(cudaMemcpy(s->d_rx.p, &rx, sizeof(rx), cudaMemcpyHostToDevice));
+    struct Part { void *dst; const void *src; size_t bytes; };
+    const Part parts[] = {
+        {s->d_velems.p, velems.data(), velems.size() * sizeof(DevVElem)}, {s->d_spectra.p, ds.data(), ds.size() * sizeof(DevSpectrum)},
+        {s->d_spec_pool.p, pool.data(), pool.size() * 4}, {s->d_shapes.p, sh.data(), sh.size() * sizeof(DevShape)},
+        {s->d_bsdfs.p, s->bsdfs.data(), s->bsdfs.size() * sizeof(bf_bsdf_desc)}, {s->d_rects.p, s->rects.data(), s->rects.size() * sizeof(DevRect)},
+        {s->d_txs.p, txs.data(), txs.size() * sizeof(DevEndpoint)}, {s->d_rx.p, &rx, sizeof(rx)}};
+    size_t total = 0;
+    for (const Part &pt : parts) total += (pt.bytes + 15) & ~(size_t) 15;
+    if (total > s->h_tables_bytes) {
+        if (s->h_tables) cudaFreeHost(s->h_tables);
+        s->h_tables = nullptr; s->h_tables_bytes = 0;
+        BF_CUDA(cudaMallocHost(&s->h_tables, total * 2));
+        s->h_tables_bytes = total * 2;
+    }
+    size_t off = 0;
+    for (const Part &pt : parts) {
+        if (pt.bytes == 0) continue;
+        memcpy((uint8_t *) s->h_tables + off, pt.src, pt.bytes);
+        BF_CUDA(cudaMemcpyAsync(pt.dst, (uint8_t *) s->h_tables + off, pt.bytes, cudaMemcpyHostToDevice, s->stream));
+        off += (pt.bytes + 15) & ~(size_t) 15;
+    }
 
     DevScene &d = s->dev;
     d.C = s->C; d.S = s->C.spectrum_width;
@@ -592,6 +666,14 @@ static int upload_tables(bf_scene *s) {
     d.hint_tx_kind = txs.empty() ? -1 : (int32_t) txs[0].kind;
     for (const DevEndpoint &e : txs) if ((int32_t) e.kind != d.hint_tx_kind) d.hint_tx_kind = -1;
     d.phase_denom = (double) ((s->C.lambda_max_nm - s->C.lambda_min_nm) / 2) * 1e-9;
+    d.adc_scale_t = (float) s->adc.t_bins / s->adc.t_bandwidth; d.adc_scale_f = (float) s->adc.f_bins / s->adc.f_bandwidth;
+    d.rx_ep = rx;
+    memset(&d.rx_rect, 0, sizeof(DevRect)); memset(&d.tx0_ep, 0, sizeof(DevEndpoint)); memset(&d.tx0_rect, 0, sizeof(DevRect));
+    if (s->rx_shape >= 0) d.rx_rect = s->rects[s->shapes[s->rx_shape].index];
+    if (!txs.empty()) {
+        d.tx0_ep = txs[0];
+        if (txs[0].shape >= 0) d.tx0_rect = s->rects[s->shapes[txs[0].shape].index];
+    }
     s->tables_dirty = false;
     return BF_OK;
 }
@@ -734,16 +816,6 @@ int bf_scene_update_rect(bf_scene *s, uint32_t shape_id, const float to_world[16
 // time, each on its own stream with its own state buffers.  Every traversal launch ends with a latency-bound
 // tail (a handful of rays with ~100 sequential node visits); with several waves in flight the tail of one
 // wave's launch overlaps the bulk of another's.
-static uint32_t env_u32(const char *name, uint32_t dflt, uint32_t lo, uint32_t hi) {
-    const char *e = getenv(name);
-    if (!e) return dflt;
-    long v = atol(e);
-    if (v < (long) lo) v = lo;
-    if (v > (long) hi) v = hi;
-    return (uint32_t) v;
-}
-static uint32_t wave_lanes_default() { return env_u32("BF_WAVE_LANES", 1u << 23, 1024, 1u << 26); }
-static uint32_t wave_streams_default() { return env_u32("BF_WAVE_STREAMS", 8, 1, 16); }
 
 static void free_slot(WaveSlot &sl, bool keep_stream) {
     for (void *p : sl.allocs) cudaFree(p);
@@ -813,9 +885,9 @@ static int run_wave(bf_scene *s, WaveSlot &sl, uint64_t seed, uint64_t first, ui
     if (!with_records) { w.records = nullptr; w.sample_of = nullptr; }
     // BF_FUSED_PRIMARY=0 selects the unfused raygen + trace pair (lanes = samples), kept for A/B measurements
     // wide reconstruction filters: every sample (misses too) is splatted by k_finalize_wide, so lanes = samples
-    const bool fused = env_u32("BF_FUSED_PRIMARY", 1, 0, 1) != 0 && !s->wide_filter;
+    const bool fused = s->tune.fused_primary != 0 && !s->wide_filter;
     if (!fused) w.sample_of = nullptr;
-    LaunchCfg cfg; cfg.stream = sl.stream; cfg.sm_count = s->sm_count;
+    LaunchCfg cfg; cfg.stream = sl.stream; cfg.sm_count = s->sm_count; cfg.trace_rounds = (uint32_t) s->tune.trace_rounds;
     uint32_t *ctr = w.counters;
     const bool unbounded = sc.integ.max_depth < 0 || sc.integ.max_depth > 64;
     const uint32_t max_depth = sc.integ.max_depth < 0 ? BF_MAX_BOUNCES : std::min<uint32_t>((uint32_t) sc.integ.max_depth, BF_MAX_BOUNCES);
@@ -831,7 +903,7 @@ static int run_wave(bf_scene *s, WaveSlot &sl, uint64_t seed, uint64_t first, ui
     if (fused) {
         w.n_lanes = ctr + 6;
         // few receiver rays reach the meshes (bf_scene_commit's estimate): k_primary leaves those to a dense k_trace launch
-        const bool defer = env_u32("BF_PRIMARY_DEFER", s->primary_defer ? 1 : 0, 0, 1) != 0 && sc.n_nodes != 0;
+        const bool defer = (s->tune.primary_defer < 0 ? s->primary_defer : s->tune.primary_defer != 0) && sc.n_nodes != 0;
         timed(BF_K_PRIMARY, [&] { return launch_primary(sc, w, seed, first, n, ctr + 4, ctr + 2, profile, defer ? w.queue[0] : nullptr, ctr + 0, cfg); });
         if (defer) timed(BF_K_TRACE_CLOSEST, [&] { return launch_trace_closest(sc, w, w.queue[0], ctr + 0, 0, 1, ctr + 4, ctr + 3, cfg, false); });
     } else {
@@ -839,7 +911,7 @@ static int run_wave(bf_scene *s, WaveSlot &sl, uint64_t seed, uint64_t first, ui
         timed(BF_K_RAYGEN, [&] { return launch_raygen(sc, w, seed, first, n, cfg); });
         timed(BF_K_TRACE_CLOSEST, [&] { return launch_trace_closest(sc, w, nullptr, nullptr, n, 1, ctr + 4, ctr + 2, cfg); });
     }
-    const bool trace_defer = env_u32("BF_TRACE_DEFER", s->primary_defer ? 1 : 0, 0, 1) != 0 && sc.n_nodes != 0;
+    const bool trace_defer = (s->tune.trace_defer < 0 ? s->primary_defer : s->tune.trace_defer != 0) && sc.n_nodes != 0;
     for (uint32_t depth = 1; depth <= max_depth; ++depth) {
         uint32_t *blk = ctr + (size_t) BF_CTR_STRIDE * depth, *prev = ctr + (size_t) BF_CTR_STRIDE * (depth - 1);
         timed(BF_K_SHADE, [&] { return launch_shade(sc, w, depth, prev + 4, n, w.queue[0], blk, cfg); });
@@ -871,15 +943,16 @@ int bf_receive(bf_scene *s, uint64_t seed, uint64_t first_sample, uint64_t n_sam
     if (s->tables_dirty) { int rc = upload_tables(s); if (rc) return rc; }
     // Wave size: BF_WAVE_LANES when set; otherwise the request is cut into as many waves as there are slots, between 2^22 and
     // 2^25 samples each (larger waves amortise the traversal tails: profiles/r01d_tune_wave.txt)
-    uint64_t want_lanes = wave_lanes_default();
-    if (!getenv("BF_WAVE_LANES")) {
-        const uint64_t per_slot = (n_samples + wave_streams_default() - 1) / wave_streams_default();
+    const uint64_t streams = (uint64_t) s->tune.wave_streams;
+    uint64_t want_lanes = (uint64_t) std::max<int64_t>(s->tune.wave_lanes, 1024);
+    if (s->tune.wave_lanes == 0) {
+        const uint64_t per_slot = (n_samples + streams - 1) / streams;
         want_lanes = std::min<uint64_t>(std::max<uint64_t>((per_slot + 1023) / 1024 * 1024, 1u << 22), 1u << 25);
     }
     const uint32_t lanes = (uint32_t) std::min<uint64_t>(std::max<uint64_t>(n_samples, 1024), want_lanes);
     const uint64_t n_waves = (n_samples + lanes - 1) / lanes;
     // per-kernel timing needs the launches serialised on one stream
-    const size_t n_slots = s->time_trace ? 1 : (size_t) std::min<uint64_t>(wave_streams_default(), std::max<uint64_t>(n_waves, 1));
+    const size_t n_slots = s->time_trace ? 1 : (size_t) std::min<uint64_t>(streams, std::max<uint64_t>(n_waves, 1));
     for (size_t k = 0; k < n_slots; ++k) { int rc = ensure_slot(s, k, lanes, false); if (rc) return rc; }
     s->ev_trace_used = 0;
     BF_CUDA(cudaEventRecord(s->ev_begin, s->stream));
@@ -925,6 +998,9 @@ int bf_profile_develop(bf_scene *s, uint32_t component_format, void *dst, size_t
     if (!s->committed) return fail(s, BF_ERR_STATE, "bf_profile_develop: scene not committed");
     if (component_format != BF_COMPONENT_FLOAT32 && component_format != BF_COMPONENT_FLOAT16)
         return fail(s, BF_ERR_UNSUPPORTED, "bf_profile_develop: component_format must be float32 or float16");
+    if (s->integ.gen != BF_GEN_PHASE)
+        return fail(s, BF_ERR_UNSUPPORTED, "bf_profile_develop: only the HDRADC storage (Y, A, W + AOVs) of the phase integrator is developed; "
+                                           "gen 1/2 films (X, Y, Z, A, W: HDRFilm's XYZ -> RGB develop, hdrfilm.cpp:304-307) are outside the path");
     const uint32_t C = s->dev.channels;
     if (C <= 3) return fail(s, BF_ERR_UNSUPPORTED, "bf_profile_develop: a storage without AOV channels has no developed form in the reference");
     const size_t n_bins = (size_t) s->dev.film_w * s->dev.film_h, esz = component_format == BF_COMPONENT_FLOAT16 ? 2 : 4;
@@ -932,7 +1008,7 @@ int bf_profile_develop(bf_scene *s, uint32_t component_format, void *dst, size_t
     if (dst_bytes < bytes) return fail(s, BF_ERR_INVALID, "bf_profile_develop: destination too small");
     BF_CUDA(cudaSetDevice(s->device));
     BF_CUDA(s->d_developed.alloc((bytes + 3) / 4));
-    LaunchCfg cfg{s->stream, s->sm_count};
+    LaunchCfg cfg{s->stream, s->sm_count, 0};
     launch_develop(s->d_profile.p, s->d_developed.p, (uint32_t) n_bins, C, esz == 2, cfg);
     BF_CUDA(cudaGetLastError());
     BF_CUDA(cudaMemcpyAsync(dst, s->d_developed.p, bytes, cudaMemcpyDeviceToHost, s->stream));
@@ -969,7 +1045,7 @@ static int trace_rays_common(bf_scene *s, const float *origins, const float *dir
         cleanup();
         return fail(s, BF_ERR_CUDA, std::string("trace: ") + cudaGetErrorString(e));
     }
-    LaunchCfg cfg; cfg.stream = s->stream; cfg.sm_count = s->sm_count;
+    LaunchCfg cfg; cfg.stream = s->stream; cfg.sm_count = s->sm_count; cfg.trace_rounds = (uint32_t) s->tune.trace_rounds;
     cudaMemcpyAsync(d_o.p, ho.data(), n * 16, cudaMemcpyHostToDevice, s->stream);
     cudaMemcpyAsync(d_d.p, hd.data(), n * 16, cudaMemcpyHostToDevice, s->stream);
     cudaMemsetAsync(d_cursor.p, 0, 4, s->stream);
@@ -1051,6 +1127,23 @@ int bf_get_stats(const bf_scene *s_, bf_stats *stats) {
     }
     *stats = s->stats;
     return BF_OK;
+}
+
+int bf_set_tunable(bf_scene *s, const char *name, int64_t value) {
+    if (!s || !name) return BF_ERR_INVALID;
+    struct { const char *n; int64_t *p; int64_t lo, hi; } table[] = {
+        {"wave_lanes", &s->tune.wave_lanes, 0, 1ll << 26}, {"wave_streams", &s->tune.wave_streams, 1, 16},
+        {"fused_primary", &s->tune.fused_primary, 0, 1}, {"primary_defer", &s->tune.primary_defer, -1, 1},
+        {"trace_defer", &s->tune.trace_defer, -1, 1}, {"trace_rounds", &s->tune.trace_rounds, 0, 1024},
+        {"use_graph", &s->tune.use_graph, 0, 1}};
+    for (auto &t : table)
+        if (strcmp(t.n, name) == 0) {
+            if (value < t.lo || value > t.hi) return fail(s, BF_ERR_INVALID, std::string("bf_set_tunable: value out of range for ") + name);
+            if (t.p == &s->tune.wave_lanes && value != 0 && value < 1024) value = 1024;
+            *t.p = value;
+            return BF_OK;
+        }
+    return fail(s, BF_ERR_INVALID, std::string("bf_set_tunable: unknown tunable ") + name);
 }
 
 int bf_set_trace_timing(bf_scene *s, int enabled) {

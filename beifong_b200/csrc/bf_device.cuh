@@ -109,9 +109,11 @@ BF_D PositionSample rect_sample_position(const DevRect &r, float time, V2 sample
     return ps;
 }
 // rectangle.cpp:132-220.  `m_to_object * ds.p/2` is the projective operator* followed by /2.
-BF_NI float rect_sample_wigner(const DevRect &r, V3 ds_p, V3 ds_d, float wavelength0) {
+// inv_wl = 1.0 / (wavelength0 * 1e-9) in double (the literal promotes the expression): callers that need the same
+// quotient for the frequency (`MTS_C*rcp(wavelengths*1e-9)`) evaluate the division once and pass it in.
+BF_D double inv_wavelength_d(float wavelength0) { return 1.0 / ((double) wavelength0 * 1e-9); }
+BF_D float rect_sample_wigner_impl(const DevRect &r, V3 ds_p, V3 ds_d, double inv_wl) {
     V3 r_hat = xf_point(r.to_object, ds_p) / 2.f;
-    double inv_wl = 1.0 / ((double) wavelength0 * 1e-9);
     V3 tv(fmadd(r.ns.z, ds_d.z, fmadd(r.ns.y, ds_d.y, r.ns.x * ds_d.x)),
           fmadd(r.nt.z, ds_d.z, fmadd(r.nt.y, ds_d.y, r.nt.x * ds_d.x)),
           fmadd(r.nn.z, ds_d.z, fmadd(r.nn.y, ds_d.y, r.nn.x * ds_d.x)));
@@ -120,6 +122,9 @@ BF_NI float rect_sample_wigner(const DevRect &r, V3 ds_p, V3 ds_d, float wavelen
                  sinc(BF_TWO_PI * nu_x * r.wid_x * tri(r_hat.x)) *
                  sinc(BF_TWO_PI * nu_y * r.wid_y * tri(r_hat.y));
     return gain;
+}
+BF_NI float rect_sample_wigner(const DevRect &r, V3 ds_p, V3 ds_d, float wavelength0) {
+    return rect_sample_wigner_impl(r, ds_p, ds_d, inv_wavelength_d(wavelength0));
 }
 // Phased arrays: sample_wigner (phasedtransmitter.cpp:275-290 == phasedreceiver.cpp:289-304) with W_rect_2D (:261-273):
 // the real part of sum_i W_rect(r_hat_i, nu_hat_i) exp(2 pi i nu_hat_i . r'_i) psi'_i over the n^2 virtual elements
@@ -181,11 +186,13 @@ BF_D SI compute_si_impl(const DevScene &sc, V3 ray_o, V3 ray_d, float4 hit) {
     uint32_t slot = __float_as_uint(hit.w);
     V3 dp_du;
     if (slot & 0x80000000u) {
+        // rectangle.cpp:265-298; the shading frame of a rectangle is a per-rectangle constant (DevRect::sh_s / sh_t)
         const DevRect &r = sc.rects[slot & 0x7fffffffu];
         si.p = fmadd3(ray_d, hit.x, ray_o);
-        si.n = r.fn; si.sh.n = r.fn;
-        dp_du = r.fs;
+        si.n = r.fn; si.sh.n = r.fn; si.sh.s = r.sh_s; si.sh.t = r.sh_t;
         si.shape = r.shape; si.prim = 0;
+        si.wi = si.to_local(-ray_d);
+        return si;
     } else {
         float4 a = __ldg(&sc.tris[3 * (size_t) slot]), b = __ldg(&sc.tris[3 * (size_t) slot + 1]), c = __ldg(&sc.tris[3 * (size_t) slot + 2]);
         V3 p0(a.x, a.y, a.z), p1(b.x, b.y, b.z), p2(c.x, c.y, c.z);
@@ -484,28 +491,85 @@ template <int S, int BK = -1> BF_D Spec<S> bsdf_sample(const DevScene &sc, uint3
     return r;
 }
 
+// twosided(diffuse) / diffuse as the material-class-0 shade kernel uses it: select() is twosided.cpp's front / back choice for
+// this lane's wi, texture() the reflectance lookup at the lane's current wavelengths (evaluated once; a second call is a
+// no-op), eval / pdf / sample are diffuse.cpp:78-135 behind twosided.cpp:94-181 on those two.
+template <int S> struct DiffuseLane {
+    const bf_bsdf_desc *b;
+    V3 wi;
+    bool flipped, dead, have_refl;
+    Spec<S> refl;
+    BF_D void select(const DevScene &sc, uint32_t id, V3 wi_) {
+        wi = wi_; have_refl = false;
+        b = twosided_select(sc, sc.bsdfs[id], wi, flipped, dead);
+    }
+    BF_D void texture(const DevScene &sc, const Spec<S> &wl) {
+        if (have_refl) return;
+        have_refl = true;
+        if (!dead) refl = spectrum_eval<S>(sc, b->reflectance, wl);
+    }
+    BF_D Spec<S> eval(V3 wo) const {
+        Spec<S> r;
+        if (dead) return r;
+        if (flipped) wo = V3(wo.x, wo.y, wo.z * -1.f);
+        if (!(wi.z > 0.f && wo.z > 0.f)) return r;
+#pragma unroll
+        for (int k = 0; k < S; ++k) r.v[k] = refl.v[k] * BF_INV_PI * wo.z;
+        return r;
+    }
+    BF_D float pdf(V3 wo) const {
+        if (dead) return 0.f;
+        if (flipped) wo = V3(wo.x, wo.y, wo.z * -1.f);
+        float p = square_to_cosine_hemisphere_pdf(wo);
+        return (wi.z > 0.f && wo.z > 0.f) ? p : 0.f;
+    }
+    BF_D Spec<S> sample(V2 sample2, BSDFSample &bs) const {
+        Spec<S> r;
+        bs.wo = V3(0.f, 0.f, 0.f); bs.pdf = 0.f; bs.eta = 0.f; bs.delta = false;
+        if (dead || !(wi.z > 0.f)) return r;
+        bs.wo = square_to_cosine_hemisphere(sample2);
+        bs.pdf = square_to_cosine_hemisphere_pdf(bs.wo);
+        bs.eta = 1.f;
+        if (bs.pdf > 0.f) r = refl;
+        if (flipped) bs.wo.z *= -1.f;
+        return r;
+    }
+};
+
 // ---- signal model: wignertransmitter.cpp:111-188 (== phasedtransmitter.cpp:176-253, wignerreceiver.cpp:116-201)
-BF_NI float eval_signal(const bf_signal_desc &sg, float time, float frequency0) {
+// rcp(repfreq), t_ext / 2 and f_ext / t_ext are evaluated once per scene (DevEndpoint::sig_*), with the reference's operations.
+BF_D float eval_signal_impl(const DevEndpoint &ep, float time, float frequency0) {
+    const bf_signal_desc &sg = ep.signal;
     if (sg.signaltype == BF_SIG_LINFMCW) {
-        float t = fmodulo(time, rcp(sg.repfreq));
-        float ti = 0 + sg.t_ext / 2;
-        float fi = sg.f_centre + (sg.f_ext / sg.t_ext) * (t - ti);
+        float t = fmodulo(time, ep.sig_period);
+        float ti = ep.sig_ti;
+        float fi = sg.f_centre + ep.sig_slope * (t - ti);
         return rect((t - ti) / sg.t_ext) > 0.f ? wchirp(t - ti, frequency0 - fi, sg.t_ext, sg.amplitude) : 0.f;
     } else if (sg.signaltype == BF_SIG_PULSE) {
-        float t = fmodulo(time, rcp(sg.repfreq));
-        float ti = 0 + sg.t_ext / 2;
+        float t = fmodulo(time, ep.sig_period);
+        float ti = ep.sig_ti;
         float fi = sg.f_centre;
         return rect((t - ti) / sg.t_ext) > 0.f ? wchirp(t - ti, frequency0 - fi, sg.t_ext, sg.amplitude) : 0.f;
     }
     return sg.amplitude * sg.amplitude;
 }
-BF_NI float sample_delta_frequency(const bf_signal_desc &sg, float time) {
+BF_D float sample_delta_frequency_impl(const DevEndpoint &ep, float time) {
+    const bf_signal_desc &sg = ep.signal;
     if (sg.signaltype == BF_SIG_LINFMCW) {
-        float t = fmodulo(time, rcp(sg.repfreq));
-        float ti = 0 + sg.t_ext / 2;
-        return sg.f_centre + (sg.f_ext / sg.t_ext) * (t - ti);
+        float t = fmodulo(time, ep.sig_period);
+        float ti = ep.sig_ti;
+        return sg.f_centre + ep.sig_slope * (t - ti);
     }
     return sg.f_centre;
+}
+BF_NI float eval_signal_ni(const DevEndpoint &ep, float time, float frequency0) { return eval_signal_impl(ep, time, frequency0); }
+BF_NI float sample_delta_frequency_ni(const DevEndpoint &ep, float time) { return sample_delta_frequency_impl(ep, time); }
+// INL: the endpoint is a kernel-parameter copy in a specialised kernel (inline, constant-bank operands); otherwise one out-of-line copy
+template <bool INL> BF_D float eval_signal(const DevEndpoint &ep, float time, float frequency0) {
+    if constexpr (INL) return eval_signal_impl(ep, time, frequency0); else return eval_signal_ni(ep, time, frequency0);
+}
+template <bool INL> BF_D float sample_delta_frequency(const DevEndpoint &ep, float time) {
+    if constexpr (INL) return sample_delta_frequency_impl(ep, time); else return sample_delta_frequency_ni(ep, time);
 }
 template <int S> BF_D Spec<S> sample_shifted(float sample) {                    // math.h:494-517
     Spec<S> r;
@@ -517,61 +581,61 @@ template <int S> BF_D Spec<S> sample_shifted(float sample) {                    
 // ---- transmitters / emitters ------------------------------------------------------------------------------
 // `wl` is the path's current wavelength state: the reference mutates si.wavelengths through a
 // const_cast (wignertransmitter.cpp:220-221,439-440) and the last write decides the frequency bin.
+// TXK >= 0 (specialised shade kernels): the scene has ONE transmitter of that kind; its endpoint and rectangle are read
+// from the copies in the kernel parameter block.  TXK = -1: everything is looked up in the scene tables.
+template <int TXK> BF_D const DevEndpoint &tx_ref(const DevScene &sc, uint32_t i) {
+    if constexpr (TXK >= 0) return sc.tx0_ep; else return sc.txs[i];
+}
+template <int TXK> BF_D const DevRect &tx_rect_ref(const DevScene &sc, const DevEndpoint &tx) {
+    if constexpr (TXK >= 0) return sc.tx0_rect; else return sc.rects[sc.shapes[tx.shape].index];
+}
 template <int S, int TXK> BF_D Spec<S> tx_eval_impl(const DevScene &sc, const DevEndpoint &tx, const SI &si, float si_time, Spec<S> &wl) {
     Spec<S> r;
+    constexpr bool INL = TXK >= 0;
     const uint32_t kind = TXK >= 0 ? (uint32_t) TXK : tx.kind;
     if (kind == BF_TX_AREA) {                                   // areatransmitter.cpp:65-74
         if (!(si.wi.z > 0.f)) return r;
         Spec<S> rad = spectrum_eval<S>(sc, tx.texture, wl);
-        float area = sc.rects[sc.shapes[tx.shape].index].area;
+        float area = tx_rect_ref<TXK>(sc, tx).area;
 #pragma unroll
         for (int k = 0; k < S; ++k) r.v[k] = rad.v[k] * area;
         return r;
     } else if (kind == BF_TX_AREALIGHT) {                       // src/emitters/area.cpp:63-72
         if (!(si.wi.z > 0.f)) return r;
         return spectrum_eval<S>(sc, tx.texture, wl);
-    } else if (kind == BF_TX_WIGNER) {                          // wignertransmitter.cpp:193-271
+    } else if (kind == BF_TX_WIGNER || kind == BF_TX_PHASED) {  // wignertransmitter.cpp:193-271, phasedtransmitter.cpp:296-381
         float signal_power;
         if (tx.signal.resample_freq) {
-            float f = sample_delta_frequency(tx.signal, si_time);
+            float f = sample_delta_frequency<INL>(tx, si_time);
             signal_power = 1.f;
             float w = sc.C.c * rcp(f) * 1e9f;
 #pragma unroll
             for (int k = 0; k < S; ++k) wl.v[k] = w;
         } else {
-            signal_power = eval_signal(tx.signal, si_time, freq_from_wl(sc.C.c, wl.v[0]));
+            signal_power = eval_signal<INL>(tx, si_time, freq_from_wl(sc.C.c, wl.v[0]));
         }
         Spec<S> geom = spectrum_eval<S>(sc, tx.texture, wl);
-        // the reference reads an uninitialised ds.d here; defined as the zero vector (oracle.cpp tx_eval)
-        float w = rect_sample_wigner(sc.rects[sc.shapes[tx.shape].index], si.p, V3(0.f, 0.f, 0.f), wl.v[0]);
-        if (!(si.wi.z > 0.f)) return r;
+        const DevRect &rc = tx_rect_ref<TXK>(sc, tx);
+        if (kind == BF_TX_WIGNER) {
+            // the reference reads an uninitialised ds.d here; defined as the zero vector (oracle.cpp tx_eval)
+            float w = rect_sample_wigner(rc, si.p, V3(0.f, 0.f, 0.f), wl.v[0]);
+            if (!(si.wi.z > 0.f)) return r;
 #pragma unroll
-        for (int k = 0; k < S; ++k) r.v[k] = signal_power * tx.signal.gain * (geom.v[k] * w) * BF_TWO_PI;
-        return r;
-    }
-    else if (kind == BF_TX_PHASED) {                          // phasedtransmitter.cpp:296-381
-        float signal_power;
-        if (tx.signal.resample_freq) {
-            float f = sample_delta_frequency(tx.signal, si_time);
-            signal_power = 1.f;
-            float w = sc.C.c * rcp(f) * 1e9f;
-#pragma unroll
-            for (int k = 0; k < S; ++k) wl.v[k] = w;
+            for (int k = 0; k < S; ++k) r.v[k] = signal_power * tx.signal.gain * (geom.v[k] * w) * BF_TWO_PI;
         } else {
-            signal_power = eval_signal(tx.signal, si_time, freq_from_wl(sc.C.c, wl.v[0]));
-        }
-        Spec<S> geom = spectrum_eval<S>(sc, tx.texture, wl);
-        float inv_area = rcp(sc.rects[sc.shapes[tx.shape].index].area);
-        float w = phased_sample_wigner(sc, tx, si.p, V3(0.f, 0.f, 0.f), wl.v[0]);
-        if (!(si.wi.z > 0.f)) return r;
+            float inv_area = rcp(rc.area);
+            float w = phased_sample_wigner(sc, tx, si.p, V3(0.f, 0.f, 0.f), wl.v[0]);
+            if (!(si.wi.z > 0.f)) return r;
 #pragma unroll
-        for (int k = 0; k < S; ++k) r.v[k] = signal_power * tx.signal.gain * (geom.v[k] * inv_area * w);
+            for (int k = 0; k < S; ++k) r.v[k] = signal_power * tx.signal.gain * (geom.v[k] * inv_area * w);
+        }
         return r;
     }
     return r;  // spot: eval = 0 (spot.cpp:166)
 }
 template <int S, int TXK> BF_D Spec<S> tx_sample_direction_impl(const DevScene &sc, const DevEndpoint &tx, V3 it_p, float it_time, Spec<S> &wl, V2 sample, DirectionSample &ds) {
     Spec<S> out;
+    constexpr bool INL = TXK >= 0;
     const uint32_t kind = TXK >= 0 ? (uint32_t) TXK : tx.kind;
     if (kind == BF_TX_SPOT) {                                   // spot.cpp:97-115, 141-164
         ds.p = V3(tx.to_world.m[0][3], tx.to_world.m[1][3], tx.to_world.m[2][3]);
@@ -591,7 +655,7 @@ template <int S, int TXK> BF_D Spec<S> tx_sample_direction_impl(const DevScene &
         }
         return out;
     }
-    const DevRect &rc = sc.rects[sc.shapes[tx.shape].index];
+    const DevRect &rc = tx_rect_ref<TXK>(sc, tx);
     ds = shape_sample_direction(rc, it_p, it_time, sample);
     bool active = dot(ds.d, ds.n) < 0.f && ds.pdf != 0.f;
     if (kind == BF_TX_AREA || kind == BF_TX_AREALIGHT) {     // areatransmitter.cpp:131-182, area.cpp
@@ -608,13 +672,13 @@ template <int S, int TXK> BF_D Spec<S> tx_sample_direction_impl(const DevScene &
     if ((double) ds.dist > 5e-7) ds.time += -ds.dist / sc.C.c;
     float signal_power;
     if (tx.signal.resample_freq) {
-        float f = sample_delta_frequency(tx.signal, ds.time);
+        float f = sample_delta_frequency<INL>(tx, ds.time);
         signal_power = 1.f;
         float w = sc.C.c * rcp(f) * 1e9f;
 #pragma unroll
         for (int k = 0; k < S; ++k) wl.v[k] = w;
     } else {
-        signal_power = eval_signal(tx.signal, ds.time, freq_from_wl(sc.C.c, wl.v[0]));
+        signal_power = eval_signal<INL>(tx, ds.time, freq_from_wl(sc.C.c, wl.v[0]));
     }
     if (kind == BF_TX_PHASED) {                                 // phasedtransmitter.cpp:596-654
         float w = phased_sample_wigner(sc, tx, ds.p, ds.d * -1.f, wl.v[0]);
@@ -626,11 +690,13 @@ template <int S, int TXK> BF_D Spec<S> tx_sample_direction_impl(const DevScene &
         for (int k = 0; k < S; ++k) out.v[k] = active ? signal_power * tx.signal.gain * geom.v[k] * 1.f : 0.f;
         return out;
     }
-    float w = rect_sample_wigner(rc, ds.p, ds.d * -1.f, wl.v[0]);
+    float w;
+    if constexpr (INL) w = rect_sample_wigner_impl(rc, ds.p, ds.d * -1.f, inv_wavelength_d(wl.v[0]));
+    else w = rect_sample_wigner(rc, ds.p, ds.d * -1.f, wl.v[0]);
 #pragma unroll
     for (int k = 0; k < S; ++k) geom.v[k] *= w;
     ds.pdf *= w;
-    float extents = rcp(rc.area) * BF_TWO_PI;
+    float extents = rc.two_pi_inv_area;                         // rcp(area) * 2 pi
 #pragma unroll
     for (int k = 0; k < S; ++k) out.v[k] = active ? signal_power * tx.signal.gain * geom.v[k] * extents : 0.f;
     return out;
@@ -638,7 +704,7 @@ template <int S, int TXK> BF_D Spec<S> tx_sample_direction_impl(const DevScene &
 template <int TXK> BF_D float tx_pdf_direction_impl(const DevScene &sc, const DevEndpoint &tx, float wl0, const DirectionSample &ds) {
     const uint32_t kind = TXK >= 0 ? (uint32_t) TXK : tx.kind;
     if (kind == BF_TX_SPOT) return 0.f;
-    const DevRect &rc = sc.rects[sc.shapes[tx.shape].index];
+    const DevRect &rc = tx_rect_ref<TXK>(sc, tx);
     float dp = dot(ds.d, ds.n);
     bool active = dp < 0.f;
     float value = shape_pdf_direction(rc, ds);
@@ -651,19 +717,17 @@ template <int TXK> BF_D float tx_pdf_direction_impl(const DevScene &sc, const De
     return active ? value : 0.f;
 }
 
-// out-of-line generic versions, and the dispatch on the compile-time hint
+// Out-of-line generic versions.  tx_eval and tx_pdf_direction only run for a path that HITS a transmitter's aperture (a few
+// millimetres wide): they are always the out-of-line generic copies, which keeps them out of the specialised kernels' hot code.
 template <int S> BF_NI Spec<S> tx_eval_generic(const DevScene &sc, const DevEndpoint &tx, const SI &si, float si_time, Spec<S> &wl) { return tx_eval_impl<S, -1>(sc, tx, si, si_time, wl); }
 template <int S> BF_NI Spec<S> tx_sample_direction_generic(const DevScene &sc, const DevEndpoint &tx, V3 it_p, float it_time, Spec<S> &wl, V2 sample, DirectionSample &ds) { return tx_sample_direction_impl<S, -1>(sc, tx, it_p, it_time, wl, sample, ds); }
 BF_NI float tx_pdf_direction_generic(const DevScene &sc, const DevEndpoint &tx, float wl0, const DirectionSample &ds) { return tx_pdf_direction_impl<-1>(sc, tx, wl0, ds); }
-template <int S, int TXK = -1> BF_D Spec<S> tx_eval(const DevScene &sc, const DevEndpoint &tx, const SI &si, float si_time, Spec<S> &wl) {
-    if constexpr (TXK >= 0) return tx_eval_impl<S, TXK>(sc, tx, si, si_time, wl); else return tx_eval_generic<S>(sc, tx, si, si_time, wl);
+template <int S> BF_D Spec<S> tx_eval(const DevScene &sc, const DevEndpoint &tx, const SI &si, float si_time, Spec<S> &wl) { return tx_eval_generic<S>(sc, tx, si, si_time, wl); }
+template <int S, int TXK = -1> BF_D Spec<S> tx_sample_direction(const DevScene &sc, uint32_t index, V3 it_p, float it_time, Spec<S> &wl, V2 sample, DirectionSample &ds) {
+    if constexpr (TXK >= 0) return tx_sample_direction_impl<S, TXK>(sc, sc.tx0_ep, it_p, it_time, wl, sample, ds);
+    else return tx_sample_direction_generic<S>(sc, sc.txs[index], it_p, it_time, wl, sample, ds);
 }
-template <int S, int TXK = -1> BF_D Spec<S> tx_sample_direction(const DevScene &sc, const DevEndpoint &tx, V3 it_p, float it_time, Spec<S> &wl, V2 sample, DirectionSample &ds) {
-    if constexpr (TXK >= 0) return tx_sample_direction_impl<S, TXK>(sc, tx, it_p, it_time, wl, sample, ds); else return tx_sample_direction_generic<S>(sc, tx, it_p, it_time, wl, sample, ds);
-}
-template <int TXK = -1> BF_D float tx_pdf_direction(const DevScene &sc, const DevEndpoint &tx, float wl0, const DirectionSample &ds) {
-    if constexpr (TXK >= 0) return tx_pdf_direction_impl<TXK>(sc, tx, wl0, ds); else return tx_pdf_direction_generic(sc, tx, wl0, ds);
-}
+BF_D float tx_pdf_direction(const DevScene &sc, const DevEndpoint &tx, float wl0, const DirectionSample &ds) { return tx_pdf_direction_generic(sc, tx, wl0, ds); }
 
 // ---- receivers / sensors -------------------------------------------------------------------------------------
 struct RayGen { V3 o, d; float mint, maxt, time; };
@@ -679,8 +743,12 @@ template <int S> BF_D void sample_wavelength(const DevScene &sc, float sample, S
 }
 // omnidirectional.cpp:71-107, fluxmeter.cpp:63-84, wignerreceiver.cpp:150-269, perspective.cpp:166-196
 // RXK >= 0: the receiver kind is a compile-time constant (specialised primary kernels); -1: read from the scene.
-template <int S, int RXK = -1> BF_D void rx_sample_ray(const DevScene &sc, float time, float sample1, V2 sample2, V2 sample3, RayGen &ray, Spec<S> &wl, Spec<S> &weight) {
-    const DevEndpoint &d = *sc.rx;
+// The receiver and its rectangle are the copies in the kernel parameter block (sc.rx_ep, sc.rx_rect); the frame around
+// the sampled position's normal (= the rectangle's normal) is the rectangle's precomputed coordinate_system(fn).
+// inv_wl: 1.0 / (wl[0] * 1e-9) in double, shared with the caller's `MTS_C*rcp(wavelengths*1e-9)` (integrator.cpp:1603).
+template <int S, int RXK = -1> BF_D void rx_sample_ray(const DevScene &sc, float time, float sample1, V2 sample2, V2 sample3, RayGen &ray, Spec<S> &wl, Spec<S> &weight, double &inv_wl) {
+    const DevEndpoint &d = sc.rx_ep;
+    constexpr bool INL = RXK >= 0;
     const uint32_t kind = RXK >= 0 ? (uint32_t) RXK : d.kind;
     ray.mint = BF_RAY_EPS; ray.maxt = bf_inf(); ray.time = time;
     if (kind == BF_RX_PERSPECTIVE) {
@@ -691,17 +759,20 @@ template <int S, int RXK = -1> BF_D void rx_sample_ray(const DevScene &sc, float
         ray.mint = d.near_clip * inv_z; ray.maxt = d.far_clip * inv_z;
         ray.o = xf_point_affine(d.to_world, V3(0.f, 0.f, 0.f));
         ray.d = xf_vector(d.to_world, dd);
+        inv_wl = inv_wavelength_d(wl.v[0]);
         return;
     }
-    const DevRect &r = sc.rects[sc.shapes[d.shape].index];
+    const DevRect &r = sc.rx_rect;
+    const Frame fr(r.cs_s, r.cs_t, r.fn);                          // Frame3f(ps.n), ps.n = m_frame.n
     if (kind == BF_RX_OMNIDIRECTIONAL || kind == BF_RX_FLUXMETER) {
         PositionSample ps = rect_sample_position(r, time, sample2);
         V3 local = square_to_cosine_hemisphere(sample3);
         Spec<S> ww; sample_wavelength<S>(sc, sample1, wl, ww);
-        ray.o = ps.p; ray.d = Frame(ps.n).to_world(local);
+        ray.o = ps.p; ray.d = fr.to_world(local);
         float k = kind == BF_RX_OMNIDIRECTIONAL ? r.area : BF_PI;
 #pragma unroll
         for (int i = 0; i < S; ++i) weight.v[i] = ww.v[i] * k;
+        inv_wl = inv_wavelength_d(wl.v[0]);
         return;
     }
     Spec<S> freq, power;
@@ -711,14 +782,14 @@ template <int S, int RXK = -1> BF_D void rx_sample_ray(const DevScene &sc, float
 #pragma unroll
         for (int k = 0; k < S; ++k) freq.v[k] = fs.v[k] * sg.f_ext + (sg.f_centre - sg.f_ext / 2);
         if (d.receive_type == BF_RECV_RAW || d.receive_type == BF_RECV_RAW_RESAMPLE) power = Spec<S>(1.f);
-        else power = Spec<S>(eval_signal(sg, time, freq.v[0]));
+        else power = Spec<S>(eval_signal<false>(d, time, freq.v[0]));
     } else {
-        freq = Spec<S>(sample_delta_frequency(sg, time)); power = Spec<S>(1.f);
+        freq = Spec<S>(sample_delta_frequency<INL>(d, time)); power = Spec<S>(1.f);
     }
 #pragma unroll
     for (int k = 0; k < S; ++k) wl.v[k] = sc.C.c * rcp(freq.v[k]) * 1e9f;
+    inv_wl = inv_wavelength_d(wl.v[0]);
     PositionSample ps = rect_sample_position(r, time, sample2);
-    Frame fr(ps.n);
     V3 dloc = square_to_cosine_hemisphere(sample3);
     float geom_gain;
     if (kind == BF_RX_PHASED) {                                  // phasedreceiver.cpp:313-375 (:353)
@@ -726,10 +797,12 @@ template <int S, int RXK = -1> BF_D void rx_sample_ray(const DevScene &sc, float
         float dn = dot(dloc, ps.n);                                // local direction against the world normal, as written
         geom_gain = w * ps.pdf * (1 - dn * dn * dn * dn);
     } else {
-        float w = rect_sample_wigner(r, ps.p, dloc, wl.v[0]);
+        float w;
+        if constexpr (INL) w = rect_sample_wigner_impl(r, ps.p, dloc, inv_wl);
+        else w = rect_sample_wigner(r, ps.p, dloc, wl.v[0]);
         geom_gain = w * ps.pdf;
     }
-    float extents0 = r.area * BF_PI;
+    float extents0 = r.area_pi;                                    // area * pi
     ray.o = ps.p; ray.d = fr.to_world(dloc);
 #pragma unroll
     for (int k = 0; k < S; ++k) {

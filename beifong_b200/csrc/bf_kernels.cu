@@ -105,6 +105,7 @@ template <int S> struct PrimaryState {
     Spec<S> wl, weight;
     float time;          // ray time
     float4 x2;           // gen 3: (sample time, f_rx, 0, weight[S == 1]); gen 1/2: (film position, 0, weight)
+    double inv_wl;       // 1.0 / (wl[0] * 1e-9): the quotient behind f_rx, kept for the bin position of a sample that misses
 };
 
 // Head of receive_sample (integrator.cpp:1544-1569) / render_sample (:263-279) for sample `idx`.
@@ -112,7 +113,7 @@ template <int S, int GEN = -1, int RXK = -1>
 __device__ __forceinline__ void raygen_sample(const DevScene &sc, uint64_t seed, uint64_t idx, PrimaryState<S> &ps) {
     PCG32 rng;
     rng.seed(tea64_shared(seed, idx), tea64_shared(idx, seed));   // sampler.cpp:89-92
-    const DevEndpoint &rx = *sc.rx;
+    const DevEndpoint &rx = sc.rx_ep;
     V2 position_sample; position_sample.x = rng.next_float32(); position_sample.y = rng.next_float32();
     V2 aperture_sample(.5f, .5f);
     if (sc.rx_needs_aperture) { aperture_sample.x = rng.next_float32(); aperture_sample.y = rng.next_float32(); }
@@ -123,16 +124,16 @@ __device__ __forceinline__ void raygen_sample(const DevScene &sc, uint64_t seed,
         time = rx.adc_sampling_start;
         if (rx.adc_sampling_time > 0.f) time += rng.next_float32() * rx.adc_sampling_time; else time = 0.f;
         float wavelength_sample = rng.next_float32();
-        rx_sample_ray<S, RXK>(sc, time, wavelength_sample, position_sample, aperture_sample, ps.ray, ps.wl, ps.weight);
+        rx_sample_ray<S, RXK>(sc, time, wavelength_sample, position_sample, aperture_sample, ps.ray, ps.wl, ps.weight, ps.inv_wl);
         x2.x = time;
-        x2.y = freq_from_wl(sc.C.c, ps.wl.v[0]);   // f_rx of mix_resample (integrator.cpp:1603)
+        x2.y = (float) ((double) sc.C.c * ps.inv_wl);   // f_rx of mix_resample: MTS_C*rcp(wavelengths*1e-9) (integrator.cpp:1603)
     } else {
         // integrator.cpp:263-279 (1x1 film, pos = 0)
         time = rx.shutter_open;
         if (rx.shutter_open_time > 0.f) time += rng.next_float32() * rx.shutter_open_time;
         float wavelength_sample = rng.next_float32();
         V2 adjusted((position_sample.x - 0.f) / (float) sc.film_w, (position_sample.y - 0.f) / (float) sc.film_h);
-        rx_sample_ray<S, RXK>(sc, time, wavelength_sample, adjusted, aperture_sample, ps.ray, ps.wl, ps.weight);
+        rx_sample_ray<S, RXK>(sc, time, wavelength_sample, adjusted, aperture_sample, ps.ray, ps.wl, ps.weight, ps.inv_wl);
         x2.x = position_sample.x; x2.y = position_sample.y;
     }
     if (S == 1) x2.w = ps.weight.v[0];
@@ -171,22 +172,23 @@ __global__ void __launch_bounds__(256) k_raygen(const __grid_constant__ DevScene
 
 // Where a sample lands on the film.  gen 3: (time, frequency) -> fractional ADC bin (integrator.cpp:1588-1639), `ran` is
 // false for receive types the reference leaves unhandled; gen 1/2: the film position sample.
-__device__ __forceinline__ void sample_position(const DevScene &sc, float4 x2, float wl0, float &posx, float &posy, bool &ran, int &off_x, int &off_y) {
+// f_d = MTS_C*rcp(wavelengths[0]*1e-9) in double for the sample's final wavelength (gen 3; unused otherwise).
+__device__ __forceinline__ void sample_position(const DevScene &sc, float4 x2, double f_d, float &posx, float &posy, bool &ran, int &off_x, int &off_y) {
     ran = true; off_x = 0; off_y = 0;
     if (sc.integ.gen == BF_GEN_PHASE) {
-        const DevEndpoint &rx = *sc.rx;
+        const DevEndpoint &rx = sc.rx_ep;
         float tfx = 0.f, tfy = 0.f;
         if (rx.receive_type == BF_RECV_MIX_RESAMPLE) {
             tfx = x2.x - rx.adc_sampling_start;
-            tfy = (float) fabs(freq_from_wl_d(sc.C.c, wl0) - (double) x2.y);
+            tfy = (float) fabs(f_d - (double) x2.y);
         } else if (rx.receive_type == BF_RECV_RAW || rx.receive_type == BF_RECV_RAW_RESAMPLE) {
             tfx = x2.x - rx.adc_sampling_start;
-            tfy = freq_from_wl(sc.C.c, wl0);
+            tfy = (float) f_d;
         } else {
             ran = false;
         }
-        tfx *= (float) sc.adc.t_bins / sc.adc.t_bandwidth;
-        tfy *= (float) sc.adc.f_bins / sc.adc.f_bandwidth;
+        tfx *= sc.adc_scale_t;      // (float) t_bins / t_bandwidth
+        tfy *= sc.adc_scale_f;
         posx = tfx; posy = tfy;
         off_x = (int) sc.adc.window_offset_t; off_y = (int) sc.adc.window_offset_f;
     } else {
@@ -270,7 +272,7 @@ __global__ void __launch_bounds__(TRACE_THREADS, BF_PRIMARY_MIN_BLOCKS) k_primar
         const bool hit = fin && (L.best.slot != BF_NONE || (DEFER && deferred));      // = gets a lane
         if (fin && !hit) {
             float posx, posy; bool ran; int off_x, off_y;
-            sample_position(sc, ps.x2, ps.wl.v[0], posx, posy, ran, off_x, off_y);
+            sample_position(sc, ps.x2, (double) sc.C.c * ps.inv_wl, posx, posy, ran, off_x, off_y);
             const int pixel = pixel_of(sc, posx, posy, off_x, off_y);
             if (pixel >= 0) {
                 if (miss_smem) atomicAdd(&s_miss[pixel], 1u);
@@ -440,7 +442,9 @@ __global__ void __launch_bounds__(128, BF_SHADE_MIN_BLOCKS) k_shade(const __grid
             SI si = (GEN >= 0) ? compute_si_impl(sc, o, d, hit) : compute_si(sc, o, d, hit);
             float time = x1.x, phase = x1.y, bs_pdf = x1.z, scalar = x1.w;
             float emission_weight = 1.f;
-            int transmitter = si.is_valid() ? sc.shapes[si.shape].tx : -1;
+            // (type, index, bsdf, tx) of the shape hit: one 128-bit load
+            const uint4 shp = si.is_valid() ? __ldg(reinterpret_cast<const uint4 *>(sc.shapes + si.shape)) : make_uint4(0u, 0u, 0u, 0xffffffffu);
+            int transmitter = (int) shp.w;
 
             if (depth == 1) {
                 if (si.is_valid()) flags |= LANE_VALID;
@@ -462,7 +466,7 @@ __global__ void __launch_bounds__(128, BF_SHADE_MIN_BLOCKS) k_shade(const __grid
                     ds.d = si.p - o; ds.dist = norm(ds.d); ds.d = ds.d / ds.dist; ds.object = transmitter;
                     float tx_pdf = 0.f;
                     if (!(flags & LANE_BS_DELTA)) {
-                        tx_pdf = tx_pdf_direction<TXK>(sc, sc.txs[transmitter], wl.v[0], ds);
+                        tx_pdf = tx_pdf_direction(sc, sc.txs[transmitter], wl.v[0], ds);
                         if (sc.n_txs > 1) tx_pdf *= (1.f / (float) sc.n_txs);
                     }
                     emission_weight = mis_weight(bs_pdf, tx_pdf);
@@ -474,7 +478,7 @@ __global__ void __launch_bounds__(128, BF_SHADE_MIN_BLOCKS) k_shade(const __grid
             // ---- loop body (pathtimefrequency.cpp:154-364) ----
             bool active = true;
             if (transmitter >= 0) {
-                Spec<S> e = tx_eval<S, TXK>(sc, sc.txs[transmitter], si, time, wl);
+                Spec<S> e = tx_eval<S>(sc, sc.txs[transmitter], si, time, wl);
 #pragma unroll
                 for (int k = 0; k < S; ++k) res.v[k] += emission_weight * thr.v[k] * e.v[k];
                 if (gen == BF_GEN_RANGE) scalar += si.is_valid() ? si.t : 0.f;      // pathlength.cpp:161
@@ -490,20 +494,24 @@ __global__ void __launch_bounds__(128, BF_SHADE_MIN_BLOCKS) k_shade(const __grid
             bool go_on = !(depth >= (uint32_t) sc.integ.max_depth || !active);
             V3 new_d(0.f, 0.f, 0.f);
             if (go_on) {
-                const uint32_t bsdf = sc.shapes[si.shape].bsdf;
+                const uint32_t bsdf = shp.z;
                 bool active_e = (BK == BF_BSDF_DIFFUSE || BK == BF_BSDF_ROUGHCONDUCTOR) ? true : bsdf_is_smooth(sc.bsdfs[bsdf]);
+                // Diffuse class: the twosided front / back choice and the reflectance texture are evaluated ONCE per lane (the
+                // reference's eval(), pdf() and sample() each repeat them on the same wi and, after NEE, the same wavelengths)
+                DiffuseLane<S> dl;
+                if constexpr (BK == BF_BSDF_DIFFUSE) dl.select(sc, bsdf, si.wi);
                 if (active_e) {
                     // Scene::sample_transmitter_direction (scene.cpp:249-299)
                     V2 sample; sample.x = rng.next_float32(); sample.y = rng.next_float32();
                     DirectionSample ds; Spec<S> tspec;
                     ds.pdf = 0.f; ds.delta = false; ds.dist = 0.f;
-                    if (sc.n_txs == 1) {
-                        tspec = tx_sample_direction<S, TXK>(sc, sc.txs[0], si.p, time, wl, sample, ds);
+                    if (TXK >= 0 || sc.n_txs == 1) {        // TXK >= 0: launched for single-transmitter scenes only
+                        tspec = tx_sample_direction<S, TXK>(sc, 0u, si.p, time, wl, sample, ds);
                     } else if (sc.n_txs > 1) {
                         float nt = (float) sc.n_txs, transmitter_pdf = 1.f / nt;
                         uint32_t index = min((uint32_t) (sample.x * nt), sc.n_txs - 1u);
                         sample.x = (sample.x - index * transmitter_pdf) * nt;
-                        tspec = tx_sample_direction<S, TXK>(sc, sc.txs[index], si.p, time, wl, sample, ds);
+                        tspec = tx_sample_direction<S, -1>(sc, index, si.p, time, wl, sample, ds);
                         ds.pdf *= transmitter_pdf;
                         float inv = rcp(transmitter_pdf);
 #pragma unroll
@@ -512,8 +520,14 @@ __global__ void __launch_bounds__(128, BF_SHADE_MIN_BLOCKS) k_shade(const __grid
                     active_e &= ds.pdf != 0.f;
                     if (active_e) {
                         V3 wo = si.to_local(ds.d);
-                        Spec<S> bsdf_val = bsdf_eval<S, BK>(sc, bsdf, wl, si.wi, wo);
-                        float bpdf = bsdf_pdf<BK>(sc, bsdf, si.wi, wo);
+                        Spec<S> bsdf_val; float bpdf;
+                        if constexpr (BK == BF_BSDF_DIFFUSE) {
+                            dl.texture(sc, wl);
+                            bsdf_val = dl.eval(wo); bpdf = dl.pdf(wo);
+                        } else {
+                            bsdf_val = bsdf_eval<S, BK>(sc, bsdf, wl, si.wi, wo);
+                            bpdf = bsdf_pdf<BK>(sc, bsdf, si.wi, wo);
+                        }
                         float mis = ds.delta ? 1.f : mis_weight(ds.pdf, bpdf);
                         bool nonzero = false;
 #pragma unroll
@@ -531,7 +545,9 @@ __global__ void __launch_bounds__(128, BF_SHADE_MIN_BLOCKS) k_shade(const __grid
                 float s1 = rng.next_float32(); (void) s1;
                 V2 s2; s2.x = rng.next_float32(); s2.y = rng.next_float32();
                 BSDFSample bs;
-                Spec<S> bsdf_val = bsdf_sample<S, BK>(sc, bsdf, wl, si.wi, s2, bs);
+                Spec<S> bsdf_val;
+                if constexpr (BK == BF_BSDF_DIFFUSE) { dl.texture(sc, wl); bsdf_val = dl.sample(s2, bs); }
+                else bsdf_val = bsdf_sample<S, BK>(sc, bsdf, wl, si.wi, s2, bs);
                 bool any_nz = false;
 #pragma unroll
                 for (int k = 0; k < S; ++k) { thr.v[k] = thr.v[k] * bsdf_val.v[k]; any_nz |= thr.v[k] != 0.f; }
@@ -637,7 +653,7 @@ __device__ __forceinline__ Splat finalize_lane(const DevScene &sc, const Wave &w
     float posx, posy;
     int off_x = 0, off_y = 0;
     bool ran;
-    sample_position(sc, x2, wl.v[0], posx, posy, ran, off_x, off_y);
+    sample_position(sc, x2, gen == BF_GEN_PHASE ? freq_from_wl_d(sc.C.c, wl.v[0]) : 0.0, posx, posy, ran, off_x, off_y);
     if (gen == BF_GEN_PHASE) {
         float wl0 = wl.v[0];
         float phase = valid ? x1.y : 0.f;
@@ -839,16 +855,17 @@ int launch_raygen(const DevScene &sc, const Wave &w, uint64_t seed, uint64_t fir
     return 1;
 }
 static TraceIO trace_io(const Wave &w, const float4 *dirs, const uint32_t *queue, const uint32_t *count, uint32_t n_direct,
-                        uint32_t *work_cursor) {
+                        uint32_t *work_cursor, const LaunchCfg &cfg) {
     TraceIO io;
     memset(&io, 0, sizeof(io));
     io.ray_o = w.ray_o; io.ray_d = dirs; io.queue = queue; io.count = count; io.n_direct = n_direct; io.work_cursor = work_cursor;
+    io.rounds = cfg.trace_rounds; io.sm_count = (uint32_t) cfg.sm_count;
     return io;
 }
 int launch_trace_closest(const DevScene &sc, const Wave &w, const uint32_t *queue, const uint32_t *count, uint32_t n_direct,
                          uint32_t depth, uint32_t *hit_count, uint32_t *work_cursor, const LaunchCfg &cfg, bool count_queries,
                          uint32_t *defer_queue, uint32_t *defer_count) {
-    TraceIO io = trace_io(w, w.ray_d, queue, count, n_direct, work_cursor);
+    TraceIO io = trace_io(w, w.ray_d, queue, count, n_direct, work_cursor, cfg);
     io.hit = w.hit; io.hit_queue[0] = w.queue_h; io.hit_queue[1] = w.queue_h2; io.hit_count[0] = hit_count; io.hit_count[1] = hit_count + 1; io.x1 = w.x1; io.records = w.records; io.sample_of = w.sample_of; io.depth = depth;
     io.total = count_queries ? w.totals + 0 : nullptr;     // the deferred half of a query is counted by the launch that deferred it
     io.hit_queue[2] = defer_queue; io.hit_count[2] = defer_count;
@@ -858,7 +875,7 @@ int launch_trace_closest(const DevScene &sc, const Wave &w, const uint32_t *queu
 }
 int launch_trace_shadow(const DevScene &sc, const Wave &w, const uint32_t *queue, const uint32_t *count, uint32_t *work_cursor,
                         const LaunchCfg &cfg) {
-    TraceIO io = trace_io(w, w.sh_d, queue, count, 0, work_cursor);
+    TraceIO io = trace_io(w, w.sh_d, queue, count, 0, work_cursor, cfg);
     io.occl = w.occl; io.total = w.totals + 1;
     k_trace<true><<<trace_grid(cfg), TRACE_THREADS, 0, cfg.stream>>>(sc, io);
     return 1;
@@ -871,8 +888,8 @@ static int launch_shade_s(const DevScene &sc, const Wave &w, uint32_t depth, con
 #define BF_SHADE_T(T_) do { \
         BF_SHADE(T_, BF_BSDF_DIFFUSE, 0); \
         if (sc.hint_cls1_bsdf == BF_BSDF_ROUGHCONDUCTOR) BF_SHADE(T_, BF_BSDF_ROUGHCONDUCTOR, 1); else BF_SHADE(T_, -1, 1); } while (0)
-    if (sc.integ.gen == BF_GEN_PHASE && sc.hint_tx_kind == BF_TX_WIGNER) { BF_SHADE_T(BF_TX_WIGNER); return 2; }
-    if (sc.integ.gen == BF_GEN_PHASE && sc.hint_tx_kind == BF_TX_AREA) { BF_SHADE_T(BF_TX_AREA); return 2; }
+    if (sc.integ.gen == BF_GEN_PHASE && sc.n_txs == 1 && sc.hint_tx_kind == BF_TX_WIGNER) { BF_SHADE_T(BF_TX_WIGNER); return 2; }
+    if (sc.integ.gen == BF_GEN_PHASE && sc.n_txs == 1 && sc.hint_tx_kind == BF_TX_AREA) { BF_SHADE_T(BF_TX_AREA); return 2; }
 #undef BF_SHADE_T
 #undef BF_SHADE
     k_shade<S, -1, -1, -1, 2><<<grid, 128, 0, cfg.stream>>>(sc, w, depth, hit_counts, next_queue, ctr_block);
@@ -924,6 +941,7 @@ int launch_trace_rays(const DevScene &sc, const float4 *ray_o, const float4 *ray
     TraceIO io;
     memset(&io, 0, sizeof(io));
     io.ray_o = ray_o; io.ray_d = ray_d; io.n_direct = n; io.work_cursor = work_cursor; io.hit = hit; io.occl = hit ? nullptr : occl;
+    io.rounds = cfg.trace_rounds; io.sm_count = (uint32_t) cfg.sm_count;
     io.steps = hit ? occl : nullptr;   // closest queries: `occl`, when given, receives the per-ray step count
     if (hit) k_trace<false><<<trace_grid(cfg), TRACE_THREADS, 0, cfg.stream>>>(sc, io);
     else k_trace<true><<<trace_grid(cfg), TRACE_THREADS, 0, cfg.stream>>>(sc, io);

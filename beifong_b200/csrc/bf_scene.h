@@ -26,8 +26,13 @@ struct DevRect {
     uint32_t shape;         // scene shape id
     uint32_t pad;
     float box_lo[3], box_hi[3];   // world-space bounding box, padded: the traversal kernel's conservative pre-test
+    // Per-rectangle constants the kernels would otherwise recompute for every sample (same fp32 operations, done once on the host):
+    V3 cs_s, cs_t;          // coordinate_system(fn): the frame receivers build around the sampled position's normal
+    V3 sh_s, sh_t;          // initialize_sh_frame for a hit on this rectangle (interaction.h:159-162): Gram-Schmidt of dp_du against fn
+    float two_pi_inv_area;  // rcp(area) * 2 pi (wignertransmitter.cpp:528)
+    float area_pi;          // area * pi        (wignerreceiver.cpp:262)
 };
-struct DevShape {
+struct alignas(16) DevShape {   // 32 bytes: (type, index, bsdf, tx) is one 128-bit load
     uint32_t type;          // 0 mesh, 1 rectangle
     uint32_t index;         // mesh index / rectangle index
     uint32_t bsdf;
@@ -55,6 +60,7 @@ struct DevEndpoint {
     uint32_t velem_offset, n_velems;   // phased: slice of DevScene::velems (n_elems^2 entries)
     float wid_x, wid_y;         // phased: elem_dims.x / .y
     bf_signal_desc signal;
+    float sig_period, sig_ti, sig_slope;   // rcp(repfreq), 0 + t_ext / 2, f_ext / t_ext: scene constants of eval_signal / sample_delta_frequency
     float adc_sampling_start, adc_sampling_time;
     float cutoff, inv_transition, cos_cutoff, cos_beam;   // spot.cpp:85-93
     float near_clip, far_clip, shutter_open, shutter_open_time;
@@ -96,6 +102,12 @@ struct DevScene {
     int32_t hint_tx_kind, hint_cls1_bsdf, hint_rx_kind;
     float mesh_lo[3], mesh_hi[3];   // padded world-space bounds of all mesh triangles: rays that miss them skip the traversal
     double phase_denom;        // (lambda_max - lambda_min) / 2 * 1e-9 evaluated like ray.h:92
+    float adc_scale_t, adc_scale_f;   // (float) t_bins / t_bandwidth, (float) f_bins / f_bandwidth (integrator.cpp:1639)
+    // Copies of the receiver, of the first transmitter and of their rectangles INSIDE the kernel parameter block: the
+    // specialised kernels (one receiver / one transmitter of a known kind) read them as constant-bank operands instead of
+    // chasing rx -> shape -> rect pointers through L1 for every sample.
+    DevEndpoint rx_ep, tx0_ep;
+    DevRect rx_rect, tx0_rect;
 };
 
 struct HostMesh {

@@ -271,6 +271,8 @@ struct TraceIO {
     uint32_t *steps;                 // optional debug output: traversal steps per ray
     uint32_t *work_cursor;
     unsigned long long *total;
+    uint32_t rounds;                 // > 0: a launch uses only as many warps as give each of them ~`rounds` batches of 32 rays
+    uint32_t sm_count;
 };
 
 // Work distribution: a warp claims chunks of consecutive rays from the global cursor and always has the NEXT chunk's
@@ -291,9 +293,21 @@ __global__ void __launch_bounds__(TRACE_THREADS, TRACE_MIN_BLOCKS) k_trace(const
     const uint32_t lane = threadIdx.x & 31u, lt_mask = (1u << lane) - 1u;
     const bool push_hits = !ANY_HIT && io.hit_queue[0] != nullptr;
 
+    // A launch is bound by its slowest rays: a warp that holds one batch of 32 rays runs every traversal step until the
+    // last of them is done (mean 16 steps, 99.99th percentile 66), at 5-9 active lanes of 32 (profiles/r01h).  So a launch
+    // of n rays uses only as many warps as give each of them ~`rounds` batches, refilled at TRACE_REFILL busy lanes from
+    // the global cursor: the tail is paid once per warp instead of once per batch.  The active warps are spread over the
+    // SMs first (block b runs on SM b % sm_count while the whole grid is resident), then over the SM's sub-partitions.
+    const uint32_t n_warps_grid = gridDim.x * (TRACE_THREADS / 32);
+    uint32_t n_warps = n_warps_grid, warp_rank = blockIdx.x * (TRACE_THREADS / 32) + (threadIdx.x >> 5);
+    if (io.rounds && io.sm_count && gridDim.x % io.sm_count == 0) {
+        const uint32_t floor_warps = min(n_warps_grid, io.sm_count * (TRACE_THREADS / 32));     // tiny launches: latency first
+        n_warps = min(n_warps_grid, max((n + 32u * io.rounds - 1u) / (32u * io.rounds), floor_warps));
+        warp_rank = ((blockIdx.x / io.sm_count) * (TRACE_THREADS / 32) + (threadIdx.x >> 5)) * io.sm_count + blockIdx.x % io.sm_count;
+        if (warp_rank >= n_warps) return;
+    }
     // Every warp starts on a static batch of 32 rays (no atomic, a small launch is spread over the whole grid); the
     // rest of the queue is handed out dynamically in chunks sized for >= ~8 claims per warp.
-    const uint32_t n_warps = gridDim.x * (TRACE_THREADS / 32);
     const uint32_t static_total = n_warps * 32u;
     const bool dynamic = n > static_total;
     uint32_t chunk = 32;
@@ -301,7 +315,7 @@ __global__ void __launch_bounds__(TRACE_THREADS, TRACE_MIN_BLOCKS) k_trace(const
     // a launch smaller than one static batch per warp (the deferred-lane launches, deep bounces) is cut evenly over all
     // the warps instead: such a launch is bound by its slowest rays, and fewer rays per warp means more of them run at once
     const uint32_t quota = dynamic ? 32u : max((n + n_warps - 1u) / n_warps, 1u);
-    uint32_t c_next = (blockIdx.x * (TRACE_THREADS / 32) + (threadIdx.x >> 5)) * quota, c_end = c_next + quota;   // warp-uniform
+    uint32_t c_next = warp_rank * quota, c_end = c_next + quota;   // warp-uniform
     uint32_t claim = 0xffffffffu;                   // lane 0: start of the chunk claimed ahead
     if (dynamic && lane == 0) claim = static_total + atomic_add_async(io.work_cursor, chunk);
     bool out_of_work = c_next >= n;

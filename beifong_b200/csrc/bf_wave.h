@@ -48,6 +48,7 @@ struct Wave {
 struct LaunchCfg {
     cudaStream_t stream;
     int sm_count;
+    uint32_t trace_rounds;   // k_trace: batches of 32 rays per active warp (0 = every warp of the grid takes part)
 };
 
 // Kernel launchers (bf_kernels.cu).  Return the number of kernels launched.

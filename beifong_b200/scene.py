@@ -276,6 +276,10 @@ class FlatScene:
         self._ck(N.lib().bf_get_stats(self._h, C.byref(st)), "bf_get_stats")
         return {k: getattr(st, k) for k, _ in N.bf_stats._fields_}
 
+    def set_tunable(self, name, value):
+        """Launch-shape knob of this scene (bf_set_tunable): never changes a result."""
+        self._ck(N.lib().bf_set_tunable(self._h, name.encode(), int(value)), "bf_set_tunable")
+
     def set_trace_timing(self, enabled):
         self._ck(N.lib().bf_set_trace_timing(self._h, int(enabled)), "bf_set_trace_timing")
 

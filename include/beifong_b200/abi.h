@@ -277,6 +277,11 @@ int bf_get_stats(const bf_scene *s, bf_stats *stats);
 /* Time (ms, CUDA events on the scene's stream) of the most recent bf_receive: whole call
  * and the traverse kernels alone. */
 int bf_last_receive_ms(bf_scene *s, float *total_ms, float *traverse_ms);
+/* Launch-shape knobs of one scene (no reference counterpart; none changes a result).  Names: "wave_lanes" (0 = from the request
+ * size), "wave_streams" (waves in flight, 1..16), "fused_primary" (0/1), "primary_defer" / "trace_defer" (-1 = the commit-time
+ * estimate, 0, 1), "trace_rounds" (batches of 32 rays per active traversal warp, 0 = whole grid), "use_graph" (0/1).  Defaults are
+ * read from the environment variables BF_<NAME> once, in bf_scene_create. */
+int bf_set_tunable(bf_scene *s, const char *name, int64_t value);
 /* Record CUDA events around every traversal launch so that bf_last_receive_ms can report
  * traverse_ms (-1 when disabled, the default). */
 int bf_set_trace_timing(bf_scene *s, int enabled);

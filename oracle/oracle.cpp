@@ -1535,7 +1535,6 @@ orc_scene *orc_scene_import(const void *blob, size_t bytes) {
                 sc.rx = *(const bf_endpoint_desc *) (pl + 8); sc.has_rx = true;
                 sc.rx_to_world = M4::from_rows16(sc.rx.to_world);
                 if (sc.rx.kind == BF_RX_PHASED) sc.rx_velems = make_velems(sc.rx.array, sc.C);
-                if (sc.rx_shape >= 0) sc.shapes[sc.rx_shape].is_rx = true;
                 break;
             }
             case BF_TAG_ADC: sc.adc = *(const bf_adc_desc *) pl; break;
@@ -1544,6 +1543,8 @@ orc_scene *orc_scene_import(const void *blob, size_t bytes) {
         }
         off += sizeof(bf_flat_record) + ((r->payload_bytes + 7) & ~(size_t) 7);
     }
+    // the receiver's record may precede the record of the shape it sits on (a re-posed receiver is rewritten in place)
+    if (sc.rx_shape >= 0 && (size_t) sc.rx_shape < sc.shapes.size()) sc.shapes[sc.rx_shape].is_rx = true;
     return os;
 }
 void orc_scene_destroy(orc_scene *s) {

@@ -144,10 +144,10 @@ def test_fused_primary_equals_unfused(native, monkeypatch):
     records are the same arithmetic and must be bit-identical; the profiles differ only by the order of the atomic adds."""
     s = configs.small_radar(spectrum_width=1).commit()
     n = 50000
-    monkeypatch.setenv("BF_FUSED_PRIMARY", "1")
+    s.set_tunable("fused_primary", 1)
     a = s.sample_records(n, seed=5)
     s.receive(1 << 18, seed=6); pa = s.profile()
-    monkeypatch.setenv("BF_FUSED_PRIMARY", "0")
+    s.set_tunable("fused_primary", 0)
     b = s.sample_records(n, seed=5)
     s.receive(1 << 18, seed=6); pb = s.profile()
     assert a.tobytes() == b.tobytes()
@@ -167,8 +167,8 @@ def test_deferred_primary_equals_fused(native, monkeypatch, width, frame):
     n = 50000
     out = {}
     for mode in ("0", "1"):
-        monkeypatch.setenv("BF_PRIMARY_DEFER", mode)
-        monkeypatch.setenv("BF_TRACE_DEFER", mode)           # the same split for the later closest-hit launches
+        s.set_tunable("primary_defer", int(mode))
+        s.set_tunable("trace_defer", int(mode))          # the same split for the later closest-hit launches
         before = s.stats()
         rec = s.sample_records(n, seed=5)
         s.receive(1 << 18, seed=6)
@@ -320,15 +320,15 @@ def test_c2_full_size_properties(native, monkeypatch):
     assert np.array_equal(whole[..., 1:3], halves[..., 1:3])
     assert whole[..., 2].sum() > 0.99 * 2 * n
     assert rel_l2(halves[..., 0], whole[..., 0]) <= 1e-5
-    monkeypatch.setenv("BF_WAVE_LANES", str(1 << 20))
+    s.set_tunable("wave_lanes", 1 << 20)
     s.receive(2 * n, seed=3)
     small_waves = s.profile()
-    monkeypatch.delenv("BF_WAVE_LANES")
+    s.set_tunable("wave_lanes", 0)
     assert np.array_equal(whole[..., 1:3], small_waves[..., 1:3]) and rel_l2(small_waves[..., 0], whole[..., 0]) <= 1e-5
-    monkeypatch.setenv("BF_FUSED_PRIMARY", "0")
+    s.set_tunable("fused_primary", 0)
     s.receive(2 * n, seed=3)
     unfused = s.profile()
-    monkeypatch.setenv("BF_FUSED_PRIMARY", "1")
+    s.set_tunable("fused_primary", 1)
     assert np.array_equal(whole[..., 1:3], unfused[..., 1:3]) and rel_l2(unfused[..., 0], whole[..., 0]) <= 1e-5
     orc = OracleScene(s.export(), accel=OracleScene.BVH)
     m = 1 << 17
