@@ -159,6 +159,8 @@ struct Tunables {
     int64_t trace_defer = -1;
     int64_t trace_rounds = 8;     // batches of 32 rays per active traversal warp (0: all warps of the grid)
     int64_t use_graph = 1;        // small calls: replay the wave's launch sequence from a CUDA graph
+    int64_t path_fused = 1;       // scenes with a deferred primary: k_path integrates the rectangle-only paths in registers
+    int64_t path_blocks = 0;      // k_path CTAs per SM (0: the kernel's launch bound)
 };
 static int64_t env_i64(const char *name, int64_t dflt, int64_t lo, int64_t hi) {
     const char *e = getenv(name);
@@ -177,6 +179,8 @@ static Tunables tunables_from_env() {
     t.trace_defer = env_i64("BF_TRACE_DEFER", -1, -1, 1);
     t.trace_rounds = env_i64("BF_TRACE_ROUNDS", 8, 0, 1024);
     t.use_graph = env_i64("BF_USE_GRAPH", 1, 0, 1);
+    t.path_fused = env_i64("BF_PATH_FUSED", 1, 0, 1);
+    t.path_blocks = env_i64("BF_PATH_BLOCKS", 0, 0, 16);
     return t;
 }
 
@@ -861,7 +865,7 @@ static int ensure_slot(bf_scene *s, size_t index, uint32_t lanes, bool records) 
     int n_spec = s->C.spectrum_width == 1 ? 1 : 5;
     for (int k = 0; k < n_spec; ++k) BF_CUDA(A((void **) &w.spec[k], n * 16));
     BF_CUDA(A((void **) &w.flags, n * 4));
-    BF_CUDA(A((void **) &w.queue[0], n * 4)); BF_CUDA(A((void **) &w.queue_h, n * 4)); BF_CUDA(A((void **) &w.queue_h2, n * 4)); BF_CUDA(A((void **) &w.queue_s, n * 4));
+    BF_CUDA(A((void **) &w.queue[0], n * 4)); BF_CUDA(A((void **) &w.queue_h, n * 4)); BF_CUDA(A((void **) &w.queue_h2, n * 4)); BF_CUDA(A((void **) &w.queue_s, n * 4)); BF_CUDA(A((void **) &w.queue_d, n * 4));
     BF_CUDA(A((void **) &w.counters, (size_t) BF_CTR_STRIDE * (BF_MAX_BOUNCES + 2) * 4));
     if (records) { BF_CUDA(A((void **) &w.records, n * sizeof(bf_sample_record))); BF_CUDA(A((void **) &w.sample_of, n * 4)); }
     w.capacity = lanes;
@@ -888,6 +892,7 @@ static int run_wave(bf_scene *s, WaveSlot &sl, uint64_t seed, uint64_t first, ui
     const bool fused = s->tune.fused_primary != 0 && !s->wide_filter;
     if (!fused) w.sample_of = nullptr;
     LaunchCfg cfg; cfg.stream = sl.stream; cfg.sm_count = s->sm_count; cfg.trace_rounds = (uint32_t) s->tune.trace_rounds;
+    cfg.path_blocks = (int) s->tune.path_blocks;
     uint32_t *ctr = w.counters;
     const bool unbounded = sc.integ.max_depth < 0 || sc.integ.max_depth > 64;
     const uint32_t max_depth = sc.integ.max_depth < 0 ? BF_MAX_BOUNCES : std::min<uint32_t>((uint32_t) sc.integ.max_depth, BF_MAX_BOUNCES);
@@ -900,18 +905,27 @@ static int run_wave(bf_scene *s, WaveSlot &sl, uint64_t seed, uint64_t first, ui
         launches += fn();
         if (timing) { cudaEventRecord(next_trace_event(s, kind), sl.stream); }
     };
+    bool path = false;
     if (fused) {
         w.n_lanes = ctr + 6;
         // few receiver rays reach the meshes (bf_scene_commit's estimate): k_primary leaves those to a dense k_trace launch
         const bool defer = (s->tune.primary_defer < 0 ? s->primary_defer : s->tune.primary_defer != 0) && sc.n_nodes != 0;
-        timed(BF_K_PRIMARY, [&] { return launch_primary(sc, w, seed, first, n, ctr + 4, ctr + 2, profile, defer ? w.queue[0] : nullptr, ctr + 0, cfg); });
-        if (defer) timed(BF_K_TRACE_CLOSEST, [&] { return launch_trace_closest(sc, w, w.queue[0], ctr + 0, 0, 1, ctr + 4, ctr + 3, cfg, false); });
+        // ... and the paths that stay clear of the meshes altogether are integrated by k_path without touching the wave arrays
+        path = defer && s->tune.path_fused != 0 && path_kernel_available(sc);
+        if (path) {
+            timed(BF_K_PRIMARY, [&] { return launch_path(sc, w, seed, first, n, ctr, profile, w.queue_d, cfg); });
+            timed(BF_K_TRACE_CLOSEST, [&] { return launch_trace_closest(sc, w, w.queue_d, ctr + 0, 0, 1, ctr + 4, ctr + 3, cfg, false); });
+        } else {
+            timed(BF_K_PRIMARY, [&] { return launch_primary(sc, w, seed, first, n, ctr + 4, ctr + 2, profile, defer ? w.queue[0] : nullptr, ctr + 0, cfg); });
+            if (defer) timed(BF_K_TRACE_CLOSEST, [&] { return launch_trace_closest(sc, w, w.queue[0], ctr + 0, 0, 1, ctr + 4, ctr + 3, cfg, false); });
+        }
     } else {
         w.n_lanes = nullptr;
         timed(BF_K_RAYGEN, [&] { return launch_raygen(sc, w, seed, first, n, cfg); });
         timed(BF_K_TRACE_CLOSEST, [&] { return launch_trace_closest(sc, w, nullptr, nullptr, n, 1, ctr + 4, ctr + 2, cfg); });
     }
-    const bool trace_defer = (s->tune.trace_defer < 0 ? s->primary_defer : s->tune.trace_defer != 0) && sc.n_nodes != 0;
+    // k_path has already sorted the continuation rays of depth 1: what reaches queue[0] mostly needs the BVH
+    const bool trace_defer = !path && (s->tune.trace_defer < 0 ? s->primary_defer : s->tune.trace_defer != 0) && sc.n_nodes != 0;
     for (uint32_t depth = 1; depth <= max_depth; ++depth) {
         uint32_t *blk = ctr + (size_t) BF_CTR_STRIDE * depth, *prev = ctr + (size_t) BF_CTR_STRIDE * (depth - 1);
         timed(BF_K_SHADE, [&] { return launch_shade(sc, w, depth, prev + 4, n, w.queue[0], blk, cfg); });
@@ -1135,7 +1149,9 @@ int bf_set_tunable(bf_scene *s, const char *name, int64_t value) {
         {"wave_lanes", &s->tune.wave_lanes, 0, 1ll << 26}, {"wave_streams", &s->tune.wave_streams, 1, 16},
         {"fused_primary", &s->tune.fused_primary, 0, 1}, {"primary_defer", &s->tune.primary_defer, -1, 1},
         {"trace_defer", &s->tune.trace_defer, -1, 1}, {"trace_rounds", &s->tune.trace_rounds, 0, 1024},
-        {"use_graph", &s->tune.use_graph, 0, 1}};
+        {"use_graph", &s->tune.use_graph, 0, 1},
+        {"path_fused", &s->tune.path_fused, 0, 1},
+        {"path_blocks", &s->tune.path_blocks, 0, 16}};
     for (auto &t : table)
         if (strcmp(t.n, name) == 0) {
             if (value < t.lo || value > t.hi) return fail(s, BF_ERR_INVALID, std::string("bf_set_tunable: value out of range for ") + name);

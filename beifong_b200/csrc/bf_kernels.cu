@@ -365,6 +365,7 @@ __global__ void __launch_bounds__(TRACE_THREADS, BF_PRIMARY_MIN_BLOCKS) k_primar
     }
 }
 
+
 __global__ void k_resolve_hits(const __grid_constant__ DevScene sc, const float4 *__restrict__ hit, uint32_t n, uint32_t *shape, uint32_t *prim) {
     uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
@@ -385,20 +386,183 @@ __device__ __forceinline__ void update_state(const DevScene &sc, float &time, fl
     phase = (float) ((double) phase + (double) (BF_TWO_PI * t) / sc.phase_denom);
 }
 
-#ifndef BF_SHADE_MIN_BLOCKS
-#define BF_SHADE_MIN_BLOCKS 5
-#endif
+// Register-resident state of one lane between two shade steps (what the wave arrays hold in HBM).
+template <int S> struct LaneRegs {
+    uint32_t flags;
+    V3 o, d;                 // the ray whose closest hit is `hit`
+    float4 hit;              // t, u, v, slot
+    PCG32 rng;
+    float time, phase, bs_pdf, scalar;   // x1
+    Spec<S> thr, res, pend, wl;
+};
+// What one shade step hands to the ray queries that follow it.
+struct ShadeOut {
+    bool push_next, push_shadow;
+    V3 origin; float mint;   // Interaction::spawn_ray: shared by the continuation and the shadow ray
+    V3 new_d;                // continuation ray direction (maxt = inf)
+    V3 sh_d; float sh_maxt;  // shadow ray
+};
+
+// One iteration of the integrator loop for one lane: the tail of the previous iteration (time / phase update, emitter MIS)
+// and the body (emission, russian roulette, NEE, BSDF sampling) of PathTimeFrequencyIntegrator::sample
+// (pathtimefrequency.cpp:154-433) and its PathLength / PathTime twins.  Shared by k_shade (state in the wave arrays) and
+// k_path (state in registers).
 // GEN / TXK / BK >= 0: the integrator generation, the transmitter kind and the BSDF kind are compile-time constants (the
 // device functions are then inlined with their other branches folded away, which keeps the executed code inside the 32 KB
 // instruction cache and the intermediate structs in registers); -1: read from the scene (out-of-line generic functions).
-// QSEL: 0 / 1 = shade the lanes of one material-class queue, 2 = both.
+// TX_HIT = false: the caller guarantees that the surface hit carries no transmitter (k_path parks only such hits).
+template <int S, int GEN, int TXK, int BK, bool TX_HIT = true>
+__device__ __forceinline__ void shade_core(const DevScene &sc, uint32_t depth, LaneRegs<S> &R, bf_sample_record *rec, ShadeOut &out) {
+    const uint32_t gen = GEN >= 0 ? (uint32_t) GEN : sc.integ.gen;
+    bool push_next = false, push_shadow = false;
+    uint32_t flags = R.flags;
+    Spec<S> &thr = R.thr, &res = R.res, &pend = R.pend, &wl = R.wl;
+    PCG32 &rng = R.rng;
+    const V3 o = R.o, d = R.d;
+    SI si = (GEN >= 0) ? compute_si_impl(sc, o, d, R.hit) : compute_si(sc, o, d, R.hit);
+    float time = R.time, phase = R.phase, bs_pdf = R.bs_pdf, scalar = R.scalar;
+    float emission_weight = 1.f;
+    // (type, index, bsdf, tx) of the shape hit: one 128-bit load
+    const uint4 shp = si.is_valid() ? __ldg(reinterpret_cast<const uint4 *>(sc.shapes + si.shape)) : make_uint4(0u, 0u, 0u, 0xffffffffu);
+    const int transmitter = TX_HIT ? (int) shp.w : -1;
+
+    if (depth == 1) {
+        if (si.is_valid()) flags |= LANE_VALID;
+        if (gen == BF_GEN_PHASE) { if (si.is_valid()) update_state(sc, time, phase, -si.t); }
+        else if (gen == BF_GEN_RANGE) scalar += si.is_valid() ? si.t : 0.f;
+        else scalar = si.is_valid() ? si.t / 3.0e8f : 0.f;
+        if (rec) {
+            rec->first_shape = si.is_valid() ? si.shape : BF_NONE;
+            rec->first_prim = si.is_valid() ? si.prim : BF_NONE;
+            rec->first_t = si.t;
+        }
+    } else {
+        // tail of the previous loop iteration (pathtimefrequency.cpp:368-399)
+        if (gen == BF_GEN_PHASE) { phase = 0.f; update_state(sc, time, phase, -si.t); }
+        if (transmitter >= 0) {
+            DirectionSample ds;   // DirectionSample3f(si_bsdf, si), records.h:168-174
+            ds.p = si.p; ds.n = si.sh.n; ds.time = time; ds.delta = false; ds.pdf = 0.f;
+            ds.d = si.p - o; ds.dist = norm(ds.d); ds.d = ds.d / ds.dist; ds.object = transmitter;
+            float tx_pdf = 0.f;
+            if (!(flags & LANE_BS_DELTA)) {
+                tx_pdf = tx_pdf_direction(sc, sc.txs[transmitter], wl.v[0], ds);
+                if (sc.n_txs > 1) tx_pdf *= (1.f / (float) sc.n_txs);
+            }
+            emission_weight = mis_weight(bs_pdf, tx_pdf);
+        }
+        if (gen == BF_GEN_RANGE) scalar += si.is_valid() ? si.t : 0.f;
+        else if (gen == BF_GEN_TIME) scalar += si.is_valid() ? si.t / 3.0e8f : 0.f;
+    }
+
+    // ---- loop body (pathtimefrequency.cpp:154-364) ----
+    bool active = true;
+    if (transmitter >= 0) {
+        Spec<S> e = tx_eval<S>(sc, sc.txs[transmitter], si, time, wl);
+#pragma unroll
+        for (int k = 0; k < S; ++k) res.v[k] += emission_weight * thr.v[k] * e.v[k];
+        if (gen == BF_GEN_RANGE) scalar += si.is_valid() ? si.t : 0.f;      // pathlength.cpp:161
+    }
+    active &= si.is_valid();
+    if ((int) depth > sc.integ.rr_depth) {
+        float q = fminf(hmax_spec<S>(thr) * 1.f, .95f);
+        active &= rng.next_float32() < q;
+        float iq = rcp(q);
+#pragma unroll
+        for (int k = 0; k < S; ++k) thr.v[k] *= iq;
+    }
+    bool go_on = !(depth >= (uint32_t) sc.integ.max_depth || !active);
+    V3 new_d(0.f, 0.f, 0.f);
+    out.sh_d = V3(0.f, 0.f, 0.f); out.sh_maxt = 0.f;
+    if (go_on) {
+        const uint32_t bsdf = shp.z;
+        bool active_e = (BK == BF_BSDF_DIFFUSE || BK == BF_BSDF_ROUGHCONDUCTOR) ? true : bsdf_is_smooth(sc.bsdfs[bsdf]);
+        // Diffuse class: the twosided front / back choice and the reflectance texture are evaluated ONCE per lane (the
+        // reference's eval(), pdf() and sample() each repeat them on the same wi and, after NEE, the same wavelengths)
+        DiffuseLane<S> dl;
+        if constexpr (BK == BF_BSDF_DIFFUSE) dl.select(sc, bsdf, si.wi);
+        if (active_e) {
+            // Scene::sample_transmitter_direction (scene.cpp:249-299)
+            V2 sample; sample.x = rng.next_float32(); sample.y = rng.next_float32();
+            DirectionSample ds; Spec<S> tspec;
+            ds.pdf = 0.f; ds.delta = false; ds.dist = 0.f;
+            if (TXK >= 0 || sc.n_txs == 1) {        // TXK >= 0: launched for single-transmitter scenes only
+                tspec = tx_sample_direction<S, TXK>(sc, 0u, si.p, time, wl, sample, ds);
+            } else if (sc.n_txs > 1) {
+                float nt = (float) sc.n_txs, transmitter_pdf = 1.f / nt;
+                uint32_t index = min((uint32_t) (sample.x * nt), sc.n_txs - 1u);
+                sample.x = (sample.x - index * transmitter_pdf) * nt;
+                tspec = tx_sample_direction<S, -1>(sc, index, si.p, time, wl, sample, ds);
+                ds.pdf *= transmitter_pdf;
+                float inv = rcp(transmitter_pdf);
+#pragma unroll
+                for (int k = 0; k < S; ++k) tspec.v[k] *= inv;
+            }
+            active_e &= ds.pdf != 0.f;
+            if (active_e) {
+                V3 wo = si.to_local(ds.d);
+                Spec<S> bsdf_val; float bpdf;
+                if constexpr (BK == BF_BSDF_DIFFUSE) {
+                    dl.texture(sc, wl);
+                    bsdf_val = dl.eval(wo); bpdf = dl.pdf(wo);
+                } else {
+                    bsdf_val = bsdf_eval<S, BK>(sc, bsdf, wl, si.wi, wo);
+                    bpdf = bsdf_pdf<BK>(sc, bsdf, si.wi, wo);
+                }
+                float mis = ds.delta ? 1.f : mis_weight(ds.pdf, bpdf);
+                bool nonzero = false;
+#pragma unroll
+                for (int k = 0; k < S; ++k) { pend.v[k] = mis * thr.v[k] * bsdf_val.v[k] * tspec.v[k]; nonzero |= pend.v[k] != 0.f; }
+                if (rec) rec->n_shadow++;
+                if (nonzero) {   // a zero contribution needs no visibility test
+                    flags |= LANE_PENDING;
+                    push_shadow = true;
+                    out.sh_d = ds.d; out.sh_maxt = ds.dist * (1.f - BF_SHADOW_EPS);
+                }
+            }
+            if (gen == BF_GEN_RANGE) scalar += si.is_valid() ? si.t : 0.f;  // pathlength.cpp:209
+        }
+        // BSDF sampling (pathtimefrequency.cpp:346-364)
+        float s1 = rng.next_float32(); (void) s1;
+        V2 s2; s2.x = rng.next_float32(); s2.y = rng.next_float32();
+        BSDFSample bs;
+        Spec<S> bsdf_val;
+        if constexpr (BK == BF_BSDF_DIFFUSE) { dl.texture(sc, wl); bsdf_val = dl.sample(s2, bs); }
+        else bsdf_val = bsdf_sample<S, BK>(sc, bsdf, wl, si.wi, s2, bs);
+        bool any_nz = false;
+#pragma unroll
+        for (int k = 0; k < S; ++k) { thr.v[k] = thr.v[k] * bsdf_val.v[k]; any_nz |= thr.v[k] != 0.f; }
+        active &= any_nz;
+        if (active) {
+            new_d = si.to_world(bs.wo);
+            bs_pdf = bs.pdf;
+            flags = bs.delta ? (flags | LANE_BS_DELTA) : (flags & ~LANE_BS_DELTA);
+            push_next = true;
+        }
+        go_on = active;
+    }
+    // Interaction::spawn_ray (interaction.h:61-64); the shadow ray shares origin and mint
+    out.origin = si.p; out.mint = (1.f + hmax_abs(si.p)) * BF_RAY_EPS;
+    out.new_d = new_d;
+    out.push_next = push_next; out.push_shadow = push_shadow;
+    if (!go_on) flags &= ~LANE_ACTIVE;
+    R.flags = flags;
+    R.time = time; R.phase = phase; R.bs_pdf = bs_pdf; R.scalar = scalar;
+    if (rec) {
+        rec->depth = depth;
+        if (push_next) rec->n_closest++;
+    }
+}
+
+#ifndef BF_SHADE_MIN_BLOCKS
+#define BF_SHADE_MIN_BLOCKS 5
+#endif
+// QSEL: 0 / 1 = shade the lanes of one material-class queue, 2 = both.  GEN / TXK / BK: see shade_core.
 template <int S, int GEN, int TXK, int BK, int QSEL>
 __global__ void __launch_bounds__(128, BF_SHADE_MIN_BLOCKS) k_shade(const __grid_constant__ DevScene sc, const __grid_constant__ Wave w, uint32_t depth,
                                                const uint32_t *__restrict__ hit_counts, uint32_t *__restrict__ next_queue, uint32_t *ctr) {
     // two input queues, one per material class; the second starts on a warp boundary of the virtual index space
     const uint32_t n_a = QSEL == 1 ? 0u : hit_counts[0], n_b = QSEL == 0 ? 0u : hit_counts[1];
     const uint32_t n_a_round = (n_a + 31u) & ~31u;
-    const uint32_t gen = GEN >= 0 ? (uint32_t) GEN : sc.integ.gen;
     const uint32_t stride = gridDim.x * blockDim.x;
     const uint32_t n_round = n_a_round + ((n_b + 31u) & ~31u);   // keep warps converged for the ballot in queue_push
     // lane id of virtual index i, or BF_NONE in the padding between / after the two queues
@@ -424,158 +588,34 @@ __global__ void __launch_bounds__(128, BF_SHADE_MIN_BLOCKS) k_shade(const __grid
             for (int k = 0; k < (S == 1 ? 1 : 4); ++k) prefetch_l2(w.spec[k] + l_next);
         }
         if (l != BF_NONE) {
-            uint32_t flags = w.flags[l];
+            LaneRegs<S> R;
+            R.flags = w.flags[l];
             const float4 ro = w.ray_o[l], rd = w.ray_d[l];
-            const float4 hit = w.hit[l];
-            float4 x1 = w.x1[l];
-            PCG32 rng; { ulonglong2 r = w.rng[l]; rng.state = r.x; rng.inc = r.y; }
-            Spec<S> thr, res, pend, wl;
-            SpecIO<S>::load(w, l, thr, res, pend, wl);
-            if (flags & LANE_PENDING) {
+            R.hit = w.hit[l];
+            const float4 x1 = w.x1[l];
+            { ulonglong2 r = w.rng[l]; R.rng.state = r.x; R.rng.inc = r.y; }
+            SpecIO<S>::load(w, l, R.thr, R.res, R.pend, R.wl);
+            if (R.flags & LANE_PENDING) {
                 if (!w.occl[l]) {
 #pragma unroll
-                    for (int k = 0; k < S; ++k) res.v[k] += pend.v[k];
+                    for (int k = 0; k < S; ++k) R.res.v[k] += R.pend.v[k];
                 }
-                flags &= ~LANE_PENDING;
+                R.flags &= ~LANE_PENDING;
             }
-            const V3 o(ro.x, ro.y, ro.z), d(rd.x, rd.y, rd.z);
-            SI si = (GEN >= 0) ? compute_si_impl(sc, o, d, hit) : compute_si(sc, o, d, hit);
-            float time = x1.x, phase = x1.y, bs_pdf = x1.z, scalar = x1.w;
-            float emission_weight = 1.f;
-            // (type, index, bsdf, tx) of the shape hit: one 128-bit load
-            const uint4 shp = si.is_valid() ? __ldg(reinterpret_cast<const uint4 *>(sc.shapes + si.shape)) : make_uint4(0u, 0u, 0u, 0xffffffffu);
-            int transmitter = (int) shp.w;
-
-            if (depth == 1) {
-                if (si.is_valid()) flags |= LANE_VALID;
-                if (gen == BF_GEN_PHASE) { if (si.is_valid()) update_state(sc, time, phase, -si.t); }
-                else if (gen == BF_GEN_RANGE) scalar += si.is_valid() ? si.t : 0.f;
-                else scalar = si.is_valid() ? si.t / 3.0e8f : 0.f;
-                if (w.records) {
-                    bf_sample_record *r = rec_of(w, l);
-                    r->first_shape = si.is_valid() ? si.shape : BF_NONE;
-                    r->first_prim = si.is_valid() ? si.prim : BF_NONE;
-                    r->first_t = si.t;
-                }
-            } else {
-                // tail of the previous loop iteration (pathtimefrequency.cpp:368-399)
-                if (gen == BF_GEN_PHASE) { phase = 0.f; update_state(sc, time, phase, -si.t); }
-                if (transmitter >= 0) {
-                    DirectionSample ds;   // DirectionSample3f(si_bsdf, si), records.h:168-174
-                    ds.p = si.p; ds.n = si.sh.n; ds.time = time; ds.delta = false; ds.pdf = 0.f;
-                    ds.d = si.p - o; ds.dist = norm(ds.d); ds.d = ds.d / ds.dist; ds.object = transmitter;
-                    float tx_pdf = 0.f;
-                    if (!(flags & LANE_BS_DELTA)) {
-                        tx_pdf = tx_pdf_direction(sc, sc.txs[transmitter], wl.v[0], ds);
-                        if (sc.n_txs > 1) tx_pdf *= (1.f / (float) sc.n_txs);
-                    }
-                    emission_weight = mis_weight(bs_pdf, tx_pdf);
-                }
-                if (gen == BF_GEN_RANGE) scalar += si.is_valid() ? si.t : 0.f;
-                else if (gen == BF_GEN_TIME) scalar += si.is_valid() ? si.t / 3.0e8f : 0.f;
-            }
-
-            // ---- loop body (pathtimefrequency.cpp:154-364) ----
-            bool active = true;
-            if (transmitter >= 0) {
-                Spec<S> e = tx_eval<S>(sc, sc.txs[transmitter], si, time, wl);
-#pragma unroll
-                for (int k = 0; k < S; ++k) res.v[k] += emission_weight * thr.v[k] * e.v[k];
-                if (gen == BF_GEN_RANGE) scalar += si.is_valid() ? si.t : 0.f;      // pathlength.cpp:161
-            }
-            active &= si.is_valid();
-            if ((int) depth > sc.integ.rr_depth) {
-                float q = fminf(hmax_spec<S>(thr) * 1.f, .95f);
-                active &= rng.next_float32() < q;
-                float iq = rcp(q);
-#pragma unroll
-                for (int k = 0; k < S; ++k) thr.v[k] *= iq;
-            }
-            bool go_on = !(depth >= (uint32_t) sc.integ.max_depth || !active);
-            V3 new_d(0.f, 0.f, 0.f);
-            if (go_on) {
-                const uint32_t bsdf = shp.z;
-                bool active_e = (BK == BF_BSDF_DIFFUSE || BK == BF_BSDF_ROUGHCONDUCTOR) ? true : bsdf_is_smooth(sc.bsdfs[bsdf]);
-                // Diffuse class: the twosided front / back choice and the reflectance texture are evaluated ONCE per lane (the
-                // reference's eval(), pdf() and sample() each repeat them on the same wi and, after NEE, the same wavelengths)
-                DiffuseLane<S> dl;
-                if constexpr (BK == BF_BSDF_DIFFUSE) dl.select(sc, bsdf, si.wi);
-                if (active_e) {
-                    // Scene::sample_transmitter_direction (scene.cpp:249-299)
-                    V2 sample; sample.x = rng.next_float32(); sample.y = rng.next_float32();
-                    DirectionSample ds; Spec<S> tspec;
-                    ds.pdf = 0.f; ds.delta = false; ds.dist = 0.f;
-                    if (TXK >= 0 || sc.n_txs == 1) {        // TXK >= 0: launched for single-transmitter scenes only
-                        tspec = tx_sample_direction<S, TXK>(sc, 0u, si.p, time, wl, sample, ds);
-                    } else if (sc.n_txs > 1) {
-                        float nt = (float) sc.n_txs, transmitter_pdf = 1.f / nt;
-                        uint32_t index = min((uint32_t) (sample.x * nt), sc.n_txs - 1u);
-                        sample.x = (sample.x - index * transmitter_pdf) * nt;
-                        tspec = tx_sample_direction<S, -1>(sc, index, si.p, time, wl, sample, ds);
-                        ds.pdf *= transmitter_pdf;
-                        float inv = rcp(transmitter_pdf);
-#pragma unroll
-                        for (int k = 0; k < S; ++k) tspec.v[k] *= inv;
-                    }
-                    active_e &= ds.pdf != 0.f;
-                    if (active_e) {
-                        V3 wo = si.to_local(ds.d);
-                        Spec<S> bsdf_val; float bpdf;
-                        if constexpr (BK == BF_BSDF_DIFFUSE) {
-                            dl.texture(sc, wl);
-                            bsdf_val = dl.eval(wo); bpdf = dl.pdf(wo);
-                        } else {
-                            bsdf_val = bsdf_eval<S, BK>(sc, bsdf, wl, si.wi, wo);
-                            bpdf = bsdf_pdf<BK>(sc, bsdf, si.wi, wo);
-                        }
-                        float mis = ds.delta ? 1.f : mis_weight(ds.pdf, bpdf);
-                        bool nonzero = false;
-#pragma unroll
-                        for (int k = 0; k < S; ++k) { pend.v[k] = mis * thr.v[k] * bsdf_val.v[k] * tspec.v[k]; nonzero |= pend.v[k] != 0.f; }
-                        if (w.records) rec_of(w, l)->n_shadow++;
-                        if (nonzero) {   // a zero contribution needs no visibility test
-                            flags |= LANE_PENDING;
-                            push_shadow = true;
-                            w.sh_d[l] = make_float4(ds.d.x, ds.d.y, ds.d.z, ds.dist * (1.f - BF_SHADOW_EPS));
-                        }
-                    }
-                    if (gen == BF_GEN_RANGE) scalar += si.is_valid() ? si.t : 0.f;  // pathlength.cpp:209
-                }
-                // BSDF sampling (pathtimefrequency.cpp:346-364)
-                float s1 = rng.next_float32(); (void) s1;
-                V2 s2; s2.x = rng.next_float32(); s2.y = rng.next_float32();
-                BSDFSample bs;
-                Spec<S> bsdf_val;
-                if constexpr (BK == BF_BSDF_DIFFUSE) { dl.texture(sc, wl); bsdf_val = dl.sample(s2, bs); }
-                else bsdf_val = bsdf_sample<S, BK>(sc, bsdf, wl, si.wi, s2, bs);
-                bool any_nz = false;
-#pragma unroll
-                for (int k = 0; k < S; ++k) { thr.v[k] = thr.v[k] * bsdf_val.v[k]; any_nz |= thr.v[k] != 0.f; }
-                active &= any_nz;
-                if (active) {
-                    new_d = si.to_world(bs.wo);
-                    bs_pdf = bs.pdf;
-                    flags = bs.delta ? (flags | LANE_BS_DELTA) : (flags & ~LANE_BS_DELTA);
-                    push_next = true;
-                }
-                go_on = active;
-            }
+            R.o = V3(ro.x, ro.y, ro.z); R.d = V3(rd.x, rd.y, rd.z);
+            R.time = x1.x; R.phase = x1.y; R.bs_pdf = x1.z; R.scalar = x1.w;
+            ShadeOut so;
+            shade_core<S, GEN, TXK, BK>(sc, depth, R, w.records ? rec_of(w, l) : nullptr, so);
+            push_next = so.push_next; push_shadow = so.push_shadow;
             if (push_next || push_shadow) {
-                // Interaction::spawn_ray (interaction.h:61-64); the shadow ray shares origin and mint
-                float mint = (1.f + hmax_abs(si.p)) * BF_RAY_EPS;
-                w.ray_o[l] = make_float4(si.p.x, si.p.y, si.p.z, mint);
-                if (push_next) w.ray_d[l] = make_float4(new_d.x, new_d.y, new_d.z, bf_inf());
+                w.ray_o[l] = make_float4(so.origin.x, so.origin.y, so.origin.z, so.mint);
+                if (push_next) w.ray_d[l] = make_float4(so.new_d.x, so.new_d.y, so.new_d.z, bf_inf());
+                if (push_shadow) w.sh_d[l] = make_float4(so.sh_d.x, so.sh_d.y, so.sh_d.z, so.sh_maxt);
             }
-            if (!go_on) flags &= ~LANE_ACTIVE;
-            w.flags[l] = flags;
-            w.x1[l] = make_float4(time, phase, bs_pdf, scalar);
-            SpecIO<S>::store(w, l, thr, res, pend, wl);
-            w.rng[l] = make_ulonglong2(rng.state, rng.inc);
-            if (w.records) {
-                bf_sample_record *r = rec_of(w, l);
-                r->depth = depth;
-                if (push_next) r->n_closest++;
-            }
+            w.flags[l] = R.flags;
+            w.x1[l] = make_float4(R.time, R.phase, R.bs_pdf, R.scalar);
+            SpecIO<S>::store(w, l, R.thr, R.res, R.pend, R.wl);
+            w.rng[l] = make_ulonglong2(R.rng.state, R.rng.inc);
         }
         dpush.complete(w.queue_s, next_queue);       // the previous iteration's pushes
         dpush.reserve(push_shadow, ctr + 1, push_next, ctr + 0, l);
@@ -636,19 +676,12 @@ struct Splat {
     uint32_t var_rep;   // gen 1 writes the value to 3 consecutive channels
 };
 
+// res: the path's radiance with the pending NEE term already resolved; phase / scalar: x1.y / x1.w of the lane
 template <int S>
-__device__ __forceinline__ Splat finalize_lane(const DevScene &sc, const Wave &w, uint32_t l) {
+__device__ __forceinline__ Splat finalize_core(const DevScene &sc, uint32_t flags, float x1_phase, float x1_scalar, float4 x2, Spec<S> res,
+                                               const Spec<S> &wl, const Spec<S> &weight, bf_sample_record *rec) {
     Splat sp; sp.pixel = -1; sp.val_a = 0.f; sp.cnt_valid = false; sp.var_ch = -1; sp.var_val = 0.f; sp.var_rep = 1;
     const uint32_t gen = sc.integ.gen;
-    uint32_t flags = w.flags[l];
-    float4 x1 = w.x1[l], x2 = w.x2[l];
-    Spec<S> thr, res, pend, wl;
-    SpecIO<S>::load(w, l, thr, res, pend, wl);
-    if ((flags & LANE_PENDING) && !w.occl[l]) {
-#pragma unroll
-        for (int k = 0; k < S; ++k) res.v[k] += pend.v[k];
-    }
-    Spec<S> weight = SpecIO<S>::load_weight(w, l, x2);
     const bool valid = flags & LANE_VALID;
     float posx, posy;
     int off_x = 0, off_y = 0;
@@ -656,7 +689,7 @@ __device__ __forceinline__ Splat finalize_lane(const DevScene &sc, const Wave &w
     sample_position(sc, x2, gen == BF_GEN_PHASE ? freq_from_wl_d(sc.C.c, wl.v[0]) : 0.0, posx, posy, ran, off_x, off_y);
     if (gen == BF_GEN_PHASE) {
         float wl0 = wl.v[0];
-        float phase = valid ? x1.y : 0.f;
+        float phase = valid ? x1_phase : 0.f;
         if (!ran) {
 #pragma unroll
             for (int k = 0; k < S; ++k) res.v[k] = 0.f;
@@ -679,14 +712,13 @@ __device__ __forceinline__ Splat finalize_lane(const DevScene &sc, const Wave &w
         for (int k = 0; k < S; ++k) wres.v[k] = fabsf(weight.v[k]) * res.v[k];
         sp.val_a = (valid && ran) ? hsum_spec<S>(wres) : 0.f;
         sp.cnt_valid = valid && ran;
-        if (w.records) {
-            bf_sample_record *r = rec_of(w, l);
-            r->valid = (valid && ran) ? 1u : 0u; r->tf_t = posx; r->tf_f = posy; r->value = sp.val_a;
-            r->phase = phase; r->wavelength0 = wl0;
+        if (rec) {
+            rec->valid = (valid && ran) ? 1u : 0u; rec->tf_t = posx; rec->tf_f = posy; rec->value = sp.val_a;
+            rec->phase = phase; rec->wavelength0 = wl0;
         }
     } else {
         // range.cpp:141-161 / time.cpp:118-153: bins from the UNWEIGHTED spectrum, first channel
-        float scalar = x1.w, r0 = res.v[0];
+        float scalar = x1_scalar, r0 = res.v[0];
         if (gen == BF_GEN_RANGE) {
             for (uint32_t i = 0; i < sc.integ.range_bins; ++i) {
                 float lo = (float) i * sc.integ.dr, hi = (float) i * sc.integ.dr + sc.integ.dr;
@@ -705,14 +737,27 @@ __device__ __forceinline__ Splat finalize_lane(const DevScene &sc, const Wave &w
         // mono: xyz = value broadcast; spectral: the CIE matching functions vanish at radar wavelengths
         float x = S == 1 ? wres.v[0] : 0.f;
         sp.val_a = x; sp.cnt_valid = valid;
-        if (w.records) {
-            bf_sample_record *r = rec_of(w, l);
-            r->valid = valid ? 1u : 0u; r->tf_t = posx; r->tf_f = posy; r->value = r0; r->phase = scalar; r->wavelength0 = wl.v[0];
+        if (rec) {
+            rec->valid = valid ? 1u : 0u; rec->tf_t = posx; rec->tf_f = posy; rec->value = r0; rec->phase = scalar; rec->wavelength0 = wl.v[0];
         }
     }
     sp.pixel = pixel_of(sc, posx, posy, off_x, off_y);
     sp.posx = posx; sp.posy = posy; sp.off_x = off_x; sp.off_y = off_y;
     return sp;
+}
+
+template <int S>
+__device__ __forceinline__ Splat finalize_lane(const DevScene &sc, const Wave &w, uint32_t l) {
+    uint32_t flags = w.flags[l];
+    float4 x1 = w.x1[l], x2 = w.x2[l];
+    Spec<S> thr, res, pend, wl;
+    SpecIO<S>::load(w, l, thr, res, pend, wl);
+    if ((flags & LANE_PENDING) && !w.occl[l]) {
+#pragma unroll
+        for (int k = 0; k < S; ++k) res.v[k] += pend.v[k];
+    }
+    Spec<S> weight = SpecIO<S>::load_weight(w, l, x2);
+    return finalize_core<S>(sc, flags, x1.y, x1.w, x2, res, wl, weight, w.records ? rec_of(w, l) : nullptr);
 }
 
 // SMEM: the whole profile fits a per-CTA shared-memory histogram (range profiles): value channels are fp32 (CAS-loop
@@ -790,6 +835,304 @@ __global__ void __launch_bounds__(FIN_THREADS) k_finalize(const __grid_constant_
             const bool is_count = ch == n_fixed - 1 || ch == n_fixed - 2;
             const float v = is_count ? (float) __float_as_uint(s_hist[i]) : s_hist[i];
             if (v != 0.f) atomicAdd(profile + i, v);
+        }
+    }
+}
+
+// =========================================================================================================
+// path: raygen + the paths that never come near a mesh, start to end in registers
+// =========================================================================================================
+// Scenes whose receiver rays mostly miss the mesh bounds (bf_scene_commit's estimate; C2: 98 %) spend their samples on three
+// kinds of path: the receiver ray leaves the scene (half of them), it hits a diffuse rectangle (the ground) and both the
+// shadow ray and the continuation ray are decided by the rectangles alone, or -- a few percent -- some ray enters the mesh
+// bounds.  k_path integrates the first two kinds completely: receiver ray, rectangle tests, one shade step (shade_core,
+// the code k_shade runs), rectangle / mesh-bounds tests of the two spawned rays, binning (finalize_core, the code k_finalize
+// runs) into a per-CTA shared-memory profile.  Nothing of such a sample touches HBM.  Lanes of the third kind are SPILLED
+// into the wave arrays at the stage they have reached, exactly in the form the wavefront kernels expect there:
+//   receiver ray enters the mesh bounds          -> store_primary + defer queue       (k_trace<closest> -> k_shade(1) ...)
+//   rectangle hit that is not plain diffuse      -> store_primary + hit + class queue  (k_shade(1) ...)
+//   shadow / continuation ray still undecided    -> the state k_shade(1) would have stored + shadow / next queues
+// Hits are compacted inside the warp before they are shaded: a warp generates rounds of 32 samples, parks the plain
+// rectangle hits in a shared-memory stash, and runs the shade step whenever 32 of them are waiting, so shading warps are full.
+#define PATH_THREADS 128
+#define PATH_STASH 64
+#ifndef BF_PATH_MIN_BLOCKS
+#define BF_PATH_MIN_BLOCKS 4
+#endif
+template <int S> struct PathStash {
+    // words per parked hit: o(3) d(3) t slot | rng state(2) inc(2) | time f_rx sample | wl[S] weight[S]
+    static constexpr int WL = 15, WEIGHT = 15 + S, WORDS = 15 + 2 * S;
+};
+struct PathIO {
+    uint64_t seed, first_sample;
+    uint32_t n;
+    uint32_t *work_cursor;
+    uint32_t *n_lanes;                        // lanes handed out to spilled samples
+    unsigned long long *totals;               // [0] closest, [1] shadow queries decided here
+    float *profile;
+    uint32_t *defer_queue, *defer_count;      // receiver rays that enter the mesh bounds
+    uint32_t *hit_count;                      // [2]: class queues of shade(1) (w.queue_h / w.queue_h2)
+    uint32_t *next_queue, *next_count;        // continuation rays after shade(1) that are not decided here
+    uint32_t *shadow_count;                   // shadow rays after shade(1) that enter the mesh bounds (w.queue_s)
+    uint32_t hist_floats;                     // > 0: the profile fits a shared-memory copy of that many floats
+};
+
+// SignalBlock::put of one finished sample (box filter), as k_finalize does it per lane
+template <bool SMEM>
+__device__ __forceinline__ void scatter_splat(const Splat &sp, float *dst, uint32_t C, uint32_t n_fixed) {
+    if (sp.pixel < 0) return;
+    float *px = dst + (size_t) C * sp.pixel;
+    if (SMEM) {
+        atomicAdd(reinterpret_cast<uint32_t *>(px + n_fixed - 1), 1u);
+        if (sp.cnt_valid) atomicAdd(reinterpret_cast<uint32_t *>(px + n_fixed - 2), 1u);
+        if (sp.val_a != 0.f)
+            for (uint32_t r = 0; r < n_fixed - 2; ++r) atomicAdd(px + r, sp.val_a);
+        if (sp.var_ch >= 0 && sp.var_val != 0.f)
+            for (uint32_t r = 0; r < sp.var_rep; ++r) atomicAdd(px + sp.var_ch + r, sp.var_val);
+    } else if (C == 4 && n_fixed == 3) {
+        atomicAdd(reinterpret_cast<float4 *>(px), make_float4(sp.val_a, sp.cnt_valid ? 1.f : 0.f, 1.f, sp.var_ch >= 0 ? sp.var_val : 0.f));
+    } else {
+        atomicAdd(px + n_fixed - 1, 1.f);
+        if (sp.cnt_valid) atomicAdd(px + n_fixed - 2, 1.f);
+        if (sp.val_a != 0.f)
+            for (uint32_t r = 0; r < n_fixed - 2; ++r) atomicAdd(px + r, sp.val_a);
+        if (sp.var_ch >= 0 && sp.var_val != 0.f)
+            for (uint32_t r = 0; r < sp.var_rep; ++r) atomicAdd(px + sp.var_ch + r, sp.var_val);
+    }
+}
+
+template <int S, int RXK, int TXK>
+__global__ void __launch_bounds__(PATH_THREADS, BF_PATH_MIN_BLOCKS) k_path(const __grid_constant__ DevScene sc, const __grid_constant__ Wave w, const __grid_constant__ PathIO io) {
+    extern __shared__ __align__(16) uint32_t path_smem[];
+    float *s_rect = reinterpret_cast<float *>(path_smem);                        // RECT_SM_FLOATS * BF_MAX_RECTS
+    uint32_t *s_plain = path_smem + RECT_SM_FLOATS * BF_MAX_RECTS;               // per rectangle: 1 = diffuse class, no transmitter attached
+    uint32_t *s_stash = s_plain + BF_MAX_RECTS;                                  // per warp: WORDS x PATH_STASH, word-major
+    float *s_hist = reinterpret_cast<float *>(s_stash + (PATH_THREADS / 32) * PathStash<S>::WORDS * PATH_STASH);
+    constexpr uint32_t C_FIXED = 3u;                                             // gen 3: Y, A, W
+    const uint32_t C = sc.channels;
+    const bool hist = io.hist_floats != 0u;
+    if (hist) for (uint32_t i = threadIdx.x; i < io.hist_floats; i += blockDim.x) s_hist[i] = 0.f;
+    for (uint32_t r = threadIdx.x; r < sc.n_rects; r += blockDim.x) {
+        const DevShape sh = sc.shapes[sc.rects[r].shape];
+        s_plain[r] = (sh.mat_class == 0u && sh.tx < 0) ? 1u : 0u;
+    }
+    stage_rects(sc, s_rect);      // ends with __syncthreads()
+    const uint32_t n = io.n;
+    const uint32_t lane = threadIdx.x & 31u, lt_mask = (1u << lane) - 1u;
+    uint32_t *st = s_stash + (threadIdx.x >> 5) * PathStash<S>::WORDS * PATH_STASH;
+    float *dst = hist ? s_hist : io.profile;
+
+    // work distribution: a static first chunk per warp, then chunks claimed one ahead from the global cursor
+    const uint32_t n_warps = gridDim.x * (PATH_THREADS / 32);
+    uint32_t chunk = 32;
+    while (chunk < 512 && (uint64_t) chunk * 16u * n_warps <= n) chunk *= 2;
+    const uint32_t static_total = n_warps * chunk;
+    uint32_t c_next = (blockIdx.x * (PATH_THREADS / 32) + (threadIdx.x >> 5)) * chunk, c_end = c_next + chunk;   // warp-uniform
+    uint32_t claim = 0xffffffffu;
+    const bool dynamic = n > static_total;
+    if (dynamic && lane == 0) claim = static_total + atomic_add_async(io.work_cursor, chunk);
+    bool out_of_work = c_next >= n;
+
+    uint32_t cnt = 0;                       // parked hits of this warp (warp-uniform)
+    uint32_t q_closest = 0, q_shadow = 0;   // ray queries decided in this thread
+    while (true) {
+        // ---------------- generate rounds of 32 samples until 32 hits are parked ----------------
+        while (!out_of_work && cnt < 32u) {
+            const uint32_t i = c_next + lane;
+            c_next += 32u;
+            if (c_next >= c_end) {          // chunk used up: open the one claimed ahead
+                const uint32_t nxt = dynamic ? __shfl_sync(0xffffffffu, claim, 0) : 0xffffffffu;
+                if (nxt < n) {
+                    if (lane == 0) claim = static_total + atomic_add_async(io.work_cursor, chunk);
+                    c_next = nxt; c_end = nxt + chunk;
+                } else {
+                    out_of_work = true;
+                }
+            }
+            if (c_next >= n) out_of_work = true;
+            enum { K_NONE = 0, K_MISS = 1, K_PARK = 2, K_DEFER = 3, K_SHADE1 = 4 };
+            int kind = K_NONE;
+            PrimaryState<S> ps;
+            TraceLane L;
+            if (i < n) {
+                raygen_sample<S, BF_GEN_PHASE, RXK>(sc, io.seed, io.first_sample + i, ps);
+                L.o = ps.ray.o; L.d = ps.ray.d; L.mint = ps.ray.mint; L.maxt = ps.ray.maxt;
+                ++q_closest;
+                if (trace_begin<false, true>(sc, s_rect, L)) kind = K_DEFER;
+                else if (L.best.slot == BF_NONE) kind = K_MISS;
+                else kind = s_plain[L.best.slot & 0x7fffffffu] ? K_PARK : K_SHADE1;
+                if (w.records) {
+                    bf_sample_record *r = w.records + i;
+                    init_record(r, ps.wl.v[0]);
+                    if (kind == K_MISS) {
+                        float posx, posy; bool ran; int off_x, off_y;
+                        sample_position(sc, ps.x2, (double) sc.C.c * ps.inv_wl, posx, posy, ran, off_x, off_y);
+                        r->depth = 1; r->tf_t = posx; r->tf_f = posy;
+                    }
+                }
+            }
+            if (kind == K_MISS) {
+                // SignalBlock::put of a zero value: one count in the weight channel of the sample's bin
+                float posx, posy; bool ran; int off_x, off_y;
+                sample_position(sc, ps.x2, (double) sc.C.c * ps.inv_wl, posx, posy, ran, off_x, off_y);
+                const int pixel = pixel_of(sc, posx, posy, off_x, off_y);
+                if (pixel >= 0) {
+                    if (hist) atomicAdd(reinterpret_cast<uint32_t *>(s_hist + (size_t) C * pixel + C_FIXED - 1u), 1u);
+                    else atomicAdd(io.profile + (size_t) C * pixel + C_FIXED - 1u, 1.f);
+                }
+            }
+            // spills before the shade step: the lane gets the state k_primary would have given it
+            const uint32_t m_spill = __ballot_sync(0xffffffffu, kind >= K_DEFER);
+            if (m_spill) {
+                const uint32_t cls = kind == K_SHADE1 ? sc.shapes[L.best.shape].mat_class : 0u;
+                const uint32_t m0 = __ballot_sync(0xffffffffu, kind == K_SHADE1 && cls == 0u), m1 = __ballot_sync(0xffffffffu, kind == K_SHADE1 && cls != 0u);
+                const uint32_t md = m_spill & ~(m0 | m1);
+                uint32_t base = 0;
+                if (lane == 0) base = atomicAdd(io.n_lanes, (uint32_t) __popc(m_spill));
+                else if (lane == 1 && m0) base = atomicAdd(io.hit_count + 0, (uint32_t) __popc(m0));
+                else if (lane == 2 && m1) base = atomicAdd(io.hit_count + 1, (uint32_t) __popc(m1));
+                else if (lane == 3 && md) base = atomicAdd(io.defer_count, (uint32_t) __popc(md));
+                const uint32_t base_l = __shfl_sync(0xffffffffu, base, 0), base_0 = __shfl_sync(0xffffffffu, base, 1),
+                               base_1 = __shfl_sync(0xffffffffu, base, 2), base_d = __shfl_sync(0xffffffffu, base, 3);
+                if (kind >= K_DEFER) {
+                    const uint32_t dl = base_l + __popc(m_spill & lt_mask);
+                    store_primary<S>(w, dl, ps);
+                    if (w.sample_of) w.sample_of[dl] = i;
+                    if (kind == K_DEFER) {
+                        io.defer_queue[base_d + __popc(md & lt_mask)] = dl;     // (the query stays counted here, as in k_primary)
+                    } else {
+                        w.hit[dl] = make_float4(L.best.t, L.best.u, L.best.v, __uint_as_float(L.best.slot));
+                        if (cls == 0u) w.queue_h[base_0 + __popc(m0 & lt_mask)] = dl;
+                        else w.queue_h2[base_1 + __popc(m1 & lt_mask)] = dl;
+                    }
+                }
+            }
+            // park the plain rectangle hits
+            const uint32_t m_park = __ballot_sync(0xffffffffu, kind == K_PARK);
+            if (kind == K_PARK) {
+                uint32_t *e = st + cnt + __popc(m_park & lt_mask);
+                e[0 * PATH_STASH] = __float_as_uint(L.o.x); e[1 * PATH_STASH] = __float_as_uint(L.o.y); e[2 * PATH_STASH] = __float_as_uint(L.o.z);
+                e[3 * PATH_STASH] = __float_as_uint(L.d.x); e[4 * PATH_STASH] = __float_as_uint(L.d.y); e[5 * PATH_STASH] = __float_as_uint(L.d.z);
+                e[6 * PATH_STASH] = __float_as_uint(L.best.t); e[7 * PATH_STASH] = L.best.slot;
+                e[8 * PATH_STASH] = (uint32_t) ps.rng.state; e[9 * PATH_STASH] = (uint32_t) (ps.rng.state >> 32);
+                e[10 * PATH_STASH] = (uint32_t) ps.rng.inc; e[11 * PATH_STASH] = (uint32_t) (ps.rng.inc >> 32);
+                e[12 * PATH_STASH] = __float_as_uint(ps.time); e[13 * PATH_STASH] = __float_as_uint(ps.x2.y); e[14 * PATH_STASH] = i;
+#pragma unroll
+                for (int k = 0; k < S; ++k) {
+                    e[(PathStash<S>::WL + k) * PATH_STASH] = __float_as_uint(ps.wl.v[k]);
+                    e[(PathStash<S>::WEIGHT + k) * PATH_STASH] = __float_as_uint(ps.weight.v[k]);
+                }
+            }
+            cnt += __popc(m_park);
+            __syncwarp();
+        }
+        if (cnt == 0u) break;               // out of work and nothing parked
+        // ---------------- shade up to 32 parked hits ----------------
+        const uint32_t take = min(cnt, 32u);
+        const bool act = lane < take;
+        LaneRegs<S> R;
+        Spec<S> weight;
+        float f_rx = 0.f, t_sample = 0.f;
+        uint32_t smp = 0;
+        if (act) {
+            const uint32_t *e = st + (cnt - take) + lane;
+            R.o = V3(__uint_as_float(e[0 * PATH_STASH]), __uint_as_float(e[1 * PATH_STASH]), __uint_as_float(e[2 * PATH_STASH]));
+            R.d = V3(__uint_as_float(e[3 * PATH_STASH]), __uint_as_float(e[4 * PATH_STASH]), __uint_as_float(e[5 * PATH_STASH]));
+            R.hit = make_float4(__uint_as_float(e[6 * PATH_STASH]), 0.f, 0.f, __uint_as_float(e[7 * PATH_STASH]));
+            R.rng.state = (uint64_t) e[8 * PATH_STASH] | ((uint64_t) e[9 * PATH_STASH] << 32);
+            R.rng.inc = (uint64_t) e[10 * PATH_STASH] | ((uint64_t) e[11 * PATH_STASH] << 32);
+            t_sample = __uint_as_float(e[12 * PATH_STASH]); f_rx = __uint_as_float(e[13 * PATH_STASH]); smp = e[14 * PATH_STASH];
+#pragma unroll
+            for (int k = 0; k < S; ++k) {
+                R.wl.v[k] = __uint_as_float(e[(PathStash<S>::WL + k) * PATH_STASH]);
+                weight.v[k] = __uint_as_float(e[(PathStash<S>::WEIGHT + k) * PATH_STASH]);
+            }
+        }
+        cnt -= take;
+        __syncwarp();                        // entries are read before the next round overwrites them
+        bool sh_spill = false, nx_spill = false;
+        ShadeOut so; so.push_next = false; so.push_shadow = false;
+        float4 x2 = make_float4(t_sample, f_rx, 0.f, S == 1 ? weight.v[0] : 0.f);
+        if (act) {
+            R.flags = LANE_ACTIVE;
+            R.thr = Spec<S>(1.f); R.res = Spec<S>(0.f); R.pend = Spec<S>(0.f);
+            R.time = t_sample; R.phase = 0.f; R.bs_pdf = 0.f; R.scalar = 0.f;
+            bf_sample_record *rec = w.records ? w.records + smp : nullptr;
+            shade_core<S, BF_GEN_PHASE, TXK, BF_BSDF_DIFFUSE, false>(sc, 1u, R, rec, so);
+            if (so.push_shadow) {
+                TraceLane T; T.o = so.origin; T.d = so.sh_d; T.mint = so.mint; T.maxt = so.sh_maxt;
+                if (trace_begin<true>(sc, s_rect, T)) {
+                    sh_spill = true;
+                } else {
+                    ++q_shadow;
+                    if (!T.occluded) {
+#pragma unroll
+                        for (int k = 0; k < S; ++k) R.res.v[k] += R.pend.v[k];
+                    }
+                    R.flags &= ~LANE_PENDING;
+                }
+            }
+            if (so.push_next) {
+                TraceLane T; T.o = so.origin; T.d = so.new_d; T.mint = so.mint; T.maxt = bf_inf();
+                const bool need = trace_begin<false, true>(sc, s_rect, T);
+                if (need || T.best.slot != BF_NONE) {
+                    nx_spill = true;         // k_trace<closest> redoes the query for this lane
+                } else {
+                    // the continuation ray leaves the scene: the miss branch of k_trace (pathtimefrequency.cpp:368-371, t = inf)
+                    ++q_closest;
+                    R.time = -bf_inf(); R.phase = -bf_inf();
+                    if (rec) rec->depth = 2u;
+                }
+            }
+            if (!sh_spill && !nx_spill) {
+                const Splat sp = finalize_core<S>(sc, R.flags, R.phase, R.scalar, x2, R.res, R.wl, weight, rec);
+                if (hist) scatter_splat<true>(sp, dst, C, C_FIXED); else scatter_splat<false>(sp, dst, C, C_FIXED);
+            }
+        }
+        // spills after the shade step: what k_shade(1) would have left in the wave arrays
+        const uint32_t m_spill = __ballot_sync(0xffffffffu, sh_spill || nx_spill);
+        if (m_spill) {
+            const uint32_t ms = __ballot_sync(0xffffffffu, sh_spill), mn = __ballot_sync(0xffffffffu, nx_spill);
+            uint32_t base = 0;
+            if (lane == 0) base = atomicAdd(io.n_lanes, (uint32_t) __popc(m_spill));
+            else if (lane == 1 && ms) base = atomicAdd(io.shadow_count, (uint32_t) __popc(ms));
+            else if (lane == 2 && mn) base = atomicAdd(io.next_count, (uint32_t) __popc(mn));
+            const uint32_t base_l = __shfl_sync(0xffffffffu, base, 0), base_s = __shfl_sync(0xffffffffu, base, 1), base_n = __shfl_sync(0xffffffffu, base, 2);
+            if (sh_spill || nx_spill) {
+                const uint32_t dl = base_l + __popc(m_spill & lt_mask);
+                w.ray_o[dl] = make_float4(so.origin.x, so.origin.y, so.origin.z, so.mint);
+                if (nx_spill) w.ray_d[dl] = make_float4(so.new_d.x, so.new_d.y, so.new_d.z, bf_inf());
+                if (sh_spill) w.sh_d[dl] = make_float4(so.sh_d.x, so.sh_d.y, so.sh_d.z, so.sh_maxt);
+                w.flags[dl] = R.flags;
+                w.x1[dl] = make_float4(R.time, R.phase, R.bs_pdf, R.scalar);
+                float4 x2s = x2;
+                SpecIO<S>::store_weight(w, dl, weight, x2s);
+                w.x2[dl] = x2s;
+                SpecIO<S>::store(w, dl, R.thr, R.res, R.pend, R.wl);
+                w.rng[dl] = make_ulonglong2(R.rng.state, R.rng.inc);
+                if (w.sample_of) w.sample_of[dl] = smp;
+                if (sh_spill) w.queue_s[base_s + __popc(ms & lt_mask)] = dl;
+                if (nx_spill) io.next_queue[base_n + __popc(mn & lt_mask)] = dl;
+            }
+        }
+    }
+    // ray-query totals of this warp
+    {
+        uint32_t qc = q_closest, qs = q_shadow;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) { qc += __shfl_xor_sync(0xffffffffu, qc, o); qs += __shfl_xor_sync(0xffffffffu, qs, o); }
+        if (lane == 0 && io.totals) {
+            if (qc) atomicAdd(io.totals + 0, (unsigned long long) qc);
+            if (qs) atomicAdd(io.totals + 1, (unsigned long long) qs);
+        }
+    }
+    if (hist) {
+        __syncthreads();
+        for (uint32_t i = threadIdx.x; i < io.hist_floats; i += blockDim.x) {
+            const uint32_t ch = i % C;
+            const bool is_count = ch == C_FIXED - 1u || ch == C_FIXED - 2u;
+            const float v = is_count ? (float) __float_as_uint(s_hist[i]) : s_hist[i];
+            if (v != 0.f) atomicAdd(io.profile + i, v);
         }
     }
 }
@@ -935,6 +1278,43 @@ int launch_primary(const DevScene &sc, const Wave &w, uint64_t seed, uint64_t fi
 #undef BF_PRIMARY
     return 1;
 }
+// Dynamic shared memory of k_path: rectangles, per-rectangle flags, the warps' stashes, the profile copy
+static size_t path_smem_bytes(uint32_t S, uint32_t hist_floats) {
+    const size_t words = (S == 1 ? PathStash<1>::WORDS : PathStash<4>::WORDS);
+    return ((size_t) RECT_SM_FLOATS * BF_MAX_RECTS + BF_MAX_RECTS + (PATH_THREADS / 32) * words * PATH_STASH + hist_floats) * 4;
+}
+bool path_kernel_available(const DevScene &sc) {
+    return sc.integ.gen == BF_GEN_PHASE && sc.n_txs == 1 && (sc.hint_tx_kind == BF_TX_WIGNER || sc.hint_tx_kind == BF_TX_AREA) &&
+           (sc.hint_rx_kind == BF_RX_WIGNER || sc.hint_rx_kind == BF_RX_OMNIDIRECTIONAL) && sc.n_nodes != 0;
+}
+int launch_path(const DevScene &sc, const Wave &w, uint64_t seed, uint64_t first_sample, uint32_t n, uint32_t *ctr, float *profile,
+                uint32_t *defer_queue, const LaunchCfg &cfg) {
+    if (n == 0) return 0;
+    PathIO io;
+    io.seed = seed; io.first_sample = first_sample; io.n = n;
+    io.work_cursor = ctr + 2; io.n_lanes = w.n_lanes; io.totals = w.totals; io.profile = profile;
+    io.defer_queue = defer_queue; io.defer_count = ctr + 0; io.hit_count = ctr + 4;
+    uint32_t *blk1 = ctr + BF_CTR_STRIDE;
+    io.next_queue = w.queue[0]; io.next_count = blk1 + 0; io.shadow_count = blk1 + 1;
+    const uint32_t floats = sc.channels * sc.film_w * sc.film_h;
+    io.hist_floats = floats <= FIN_SMEM_FLOATS ? floats : 0u;
+    const size_t smem = path_smem_bytes(sc.S, io.hist_floats);
+    const int grid = cfg.sm_count * (cfg.path_blocks > 0 ? cfg.path_blocks : BF_PATH_MIN_BLOCKS);
+#define BF_PATH(S_, R_, T_) do { \
+        static bool attr_set = false; \
+        if (!attr_set) { cudaFuncSetAttribute(k_path<S_, R_, T_>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) path_smem_bytes(S_, FIN_SMEM_FLOATS)); attr_set = true; } \
+        k_path<S_, R_, T_><<<grid, PATH_THREADS, smem, cfg.stream>>>(sc, w, io); } while (0)
+#define BF_PATH_RT(S_) do { \
+        if (sc.hint_rx_kind == BF_RX_WIGNER && sc.hint_tx_kind == BF_TX_WIGNER) BF_PATH(S_, BF_RX_WIGNER, BF_TX_WIGNER); \
+        else if (sc.hint_rx_kind == BF_RX_WIGNER) BF_PATH(S_, BF_RX_WIGNER, BF_TX_AREA); \
+        else if (sc.hint_tx_kind == BF_TX_WIGNER) BF_PATH(S_, BF_RX_OMNIDIRECTIONAL, BF_TX_WIGNER); \
+        else BF_PATH(S_, BF_RX_OMNIDIRECTIONAL, BF_TX_AREA); } while (0)
+    if (sc.S == 1) BF_PATH_RT(1); else BF_PATH_RT(4);
+#undef BF_PATH_RT
+#undef BF_PATH
+    return 1;
+}
+
 int launch_trace_rays(const DevScene &sc, const float4 *ray_o, const float4 *ray_d, uint32_t n, float4 *hit, uint32_t *occl,
                       uint32_t *work_cursor, const LaunchCfg &cfg) {
     if (n == 0) return 0;

@@ -38,6 +38,7 @@ struct Wave {
     uint32_t *queue_h;   // lane-id queue of lanes whose continuation ray hit a diffuse surface (trace -> shade)
     uint32_t *queue_h2;  // ... any other material: a shading warp runs one BSDF class
     uint32_t *queue_s;   // lane-id queue for shadow rays
+    uint32_t *queue_d;   // k_path: lane-id queue of receiver rays that enter the mesh bounds
     uint32_t *counters;  // BF_CTR_STRIDE * (BF_MAX_BOUNCES + 2)
     unsigned long long *totals;  // [0] closest queries traced, [1] shadow queries traced
     bf_sample_record *records;   // optional debug records, indexed by sample (= lane unless sample_of is set)
@@ -49,6 +50,7 @@ struct LaunchCfg {
     cudaStream_t stream;
     int sm_count;
     uint32_t trace_rounds;   // k_trace: batches of 32 rays per active warp (0 = every warp of the grid takes part)
+    int path_blocks;         // k_path: CTAs per SM (0 = the kernel's launch bound)
 };
 
 // Kernel launchers (bf_kernels.cu).  Return the number of kernels launched.
@@ -57,6 +59,12 @@ struct LaunchCfg {
 // launch_trace_closest(depth 1) over defer_queue / defer_count
 int launch_primary(const DevScene &sc, const Wave &w, uint64_t seed, uint64_t first_sample, uint32_t n, uint32_t *hit_count,
                    uint32_t *work_cursor, float *profile, uint32_t *defer_queue, uint32_t *defer_count, const LaunchCfg &cfg);
+// k_path: raygen + the rectangle-only paths start to end in registers; everything else is spilled into the wave arrays
+// (counter layout: ctr + 0 defer_queue length, + 2 work cursor, + 4 / + 5 shade(1) class queues, ctr + BF_CTR_STRIDE + 0 / + 1
+// the continuation / shadow queues that shade(1) appends to).  path_kernel_available: the scene has an instantiation.
+bool path_kernel_available(const DevScene &sc);
+int launch_path(const DevScene &sc, const Wave &w, uint64_t seed, uint64_t first_sample, uint32_t n, uint32_t *ctr, float *profile,
+                uint32_t *defer_queue, const LaunchCfg &cfg);
 int launch_raygen(const DevScene &sc, const Wave &w, uint64_t seed, uint64_t first_sample, uint32_t n, const LaunchCfg &cfg);
 // queue == nullptr: lanes [0, n_direct); else lane ids from queue[0 .. *count)
 // depth = the shade iteration this trace feeds; lanes that hit are appended to w.queue_h / *hit_count

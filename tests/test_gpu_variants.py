@@ -12,6 +12,7 @@ from beifong_b200 import configs
 from beifong_b200 import _native as N
 from beifong_b200.scene import FlatScene
 from oracle_lib import OracleScene
+from record_binning import pixel_of, phase_channel, profile_from_records
 
 pytestmark = pytest.mark.gpu
 
@@ -69,7 +70,9 @@ def test_variant_against_oracle(native, name, width):
     if name == "russian_roulette":
         assert c["depth"].max() > 8            # the roulette branch ran well past rr_depth
     if chaotic:
-        exact = both & (g["first_t"].view(np.uint32) == c["first_t"].view(np.uint32)) & (c["depth"] == 1) & \
+        # single-scattering paths (one NEE evaluation at the first hit, continuation ray leaves the scene) whose first-hit
+        # distance and sample time are bit-identical on both sides
+        exact = both & (g["first_t"].view(np.uint32) == c["first_t"].view(np.uint32)) & (c["n_shadow"] == 1) & (c["depth"] <= 2) & \
             (g["tf_t"].view(np.uint32) == c["tf_t"].view(np.uint32))
         assert exact.sum() > 200
         rel = np.abs(g["value"][exact] - c["value"][exact]) / np.abs(c["value"][exact])
@@ -80,7 +83,12 @@ def test_variant_against_oracle(native, name, width):
     else:
         rel = np.abs(g["value"][both] - c["value"][both]) / np.abs(c["value"][both])
         assert np.percentile(rel, 99) <= 1e-4, np.percentile(rel, 99)
-        assert rel.max() <= 1e-2
+        # the few samples beyond 1e-3 sit on a zero crossing of a sinc (sinf of libdevice vs glibc, <= 2 ulp of an argument of
+        # ~10 rad): their ABSOLUTE error must be negligible against the typical sample value
+        far = rel > 1e-3
+        assert far.mean() <= 1e-3, far.mean()
+        scale = np.median(np.abs(c["value"][both]))
+        assert np.all(np.abs(g["value"][both][far] - c["value"][both][far]) <= 1e-4 * scale)
     # bin coordinates of the samples that agree
     assert np.allclose(g["tf_t"][both], c["tf_t"][both], rtol=1e-5, atol=1e-3)
     if not chaotic:
@@ -101,10 +109,34 @@ def test_variant_against_oracle(native, name, width):
     else:
         assert rel_l2(gp[..., 0], cp[..., 0]) <= 1e-3, rel_l2(gp[..., 0], cp[..., 0])
         aov_g, aov_c = gp[..., 3:], cp[..., 3:]
-        assert rel_l2(aov_g, aov_c) <= 1e-3, rel_l2(aov_g, aov_c)
-        if variant.get("phase_bins", 1) > 1:
+        bins = variant.get("phase_bins", 1)
+        if bins > 1:
             used = (np.abs(aov_c).reshape(-1, aov_c.shape[-1]).sum(axis=0) > 0).sum()
             assert used >= 6                    # the phase AOVs are spread over the bins, not piled into one
+            # The carrier phase is ~1e5 rad in fp32 (ulp 0.008 rad = 1 % of a bin): a sample whose path length differs by an ulp
+            # between libdevice and glibc sinf / cosf can cross a phase-bin edge and moves its whole value to the next channel.
+            # Count those samples on the per-sample records of the same run, show that every range bin without one meets
+            # 1e-3 channel by channel, and that the sum over the phase channels (which a flip conserves) meets it everywhere.
+            rg, rc = s.sample_records(m, seed=11), orc.sample_records(m, seed=11)
+            h, w_ = gp.shape[0], gp.shape[1]
+            pix_g, pix_c = pixel_of(rg, w_, h), pixel_of(rc, w_, h)
+            ch_g, ch_c = phase_channel(rg, bins), phase_channel(rc, bins)
+            contributes = (rc["valid"] != 0) & (rc["value"] != 0) & (pix_c >= 0)
+            flipped = contributes & ((pix_g != pix_c) | (ch_g != ch_c))
+            assert flipped.sum() <= 0.01 * contributes.sum(), (flipped.sum(), contributes.sum())
+            dirty = np.zeros(h * w_, bool)
+            dirty[pix_c[flipped]] = True
+            dirty[pix_g[flipped & (pix_g >= 0)]] = True
+            clean = ~dirty.reshape(h, w_)
+            assert clean.mean() >= 0.5
+            assert rel_l2(aov_g[clean], aov_c[clean]) <= 1e-3, rel_l2(aov_g[clean], aov_c[clean])
+            assert rel_l2(aov_g.sum(axis=-1), aov_c.sum(axis=-1)) <= 1e-3
+            # the device binning against a third implementation (numpy, from the reference text) on the GPU's own records
+            mine, _, _ = profile_from_records(rg, w_, h, bins)
+            assert np.array_equal(mine[..., 1:3], gp[..., 1:3].astype(np.float64))
+            assert rel_l2(gp[..., 0], mine[..., 0]) <= 1e-5
+        else:
+            assert rel_l2(aov_g, aov_c) <= 1e-3, rel_l2(aov_g, aov_c)
     s.close()
     orc.close()
 
