@@ -146,6 +146,7 @@ struct WaveSlot {
     Wave wave; uint32_t capacity = 0; std::vector<void *> allocs;
     cudaStream_t stream = nullptr; bool own_stream = false; cudaEvent_t done = nullptr;
     uint32_t *h_counts = nullptr;     // pinned read-back of queue counts
+    uint32_t *path_stash = nullptr;   // k_path's parking areas (path_stash_bytes), allocated on first use
 };
 
 // Launch-shape knobs.  Defaults come from the environment ONCE, when the scene is created (BF_WAVE_LANES, BF_WAVE_STREAMS,
@@ -160,7 +161,6 @@ struct Tunables {
     int64_t trace_rounds = 8;     // batches of 32 rays per active traversal warp (0: all warps of the grid)
     int64_t use_graph = 1;        // small calls: replay the wave's launch sequence from a CUDA graph
     int64_t path_fused = 1;       // scenes with a deferred primary: k_path integrates the rectangle-only paths in registers
-    int64_t path_blocks = 0;      // k_path CTAs per SM (0: the kernel's launch bound)
 };
 static int64_t env_i64(const char *name, int64_t dflt, int64_t lo, int64_t hi) {
     const char *e = getenv(name);
@@ -180,7 +180,6 @@ static Tunables tunables_from_env() {
     t.trace_rounds = env_i64("BF_TRACE_ROUNDS", 8, 0, 1024);
     t.use_graph = env_i64("BF_USE_GRAPH", 1, 0, 1);
     t.path_fused = env_i64("BF_PATH_FUSED", 1, 0, 1);
-    t.path_blocks = env_i64("BF_PATH_BLOCKS", 0, 0, 16);
     return t;
 }
 
@@ -825,7 +824,7 @@ static void free_slot(WaveSlot &sl, bool keep_stream) {
     for (void *p : sl.allocs) cudaFree(p);
     sl.allocs.clear();
     memset(&sl.wave, 0, sizeof(sl.wave));
-    sl.capacity = 0;
+    sl.capacity = 0; sl.path_stash = nullptr;
     if (!keep_stream) {
         if (sl.stream && sl.own_stream) cudaStreamDestroy(sl.stream);
         if (sl.done) cudaEventDestroy(sl.done);
@@ -892,7 +891,6 @@ static int run_wave(bf_scene *s, WaveSlot &sl, uint64_t seed, uint64_t first, ui
     const bool fused = s->tune.fused_primary != 0 && !s->wide_filter;
     if (!fused) w.sample_of = nullptr;
     LaunchCfg cfg; cfg.stream = sl.stream; cfg.sm_count = s->sm_count; cfg.trace_rounds = (uint32_t) s->tune.trace_rounds;
-    cfg.path_blocks = (int) s->tune.path_blocks;
     uint32_t *ctr = w.counters;
     const bool unbounded = sc.integ.max_depth < 0 || sc.integ.max_depth > 64;
     const uint32_t max_depth = sc.integ.max_depth < 0 ? BF_MAX_BOUNCES : std::min<uint32_t>((uint32_t) sc.integ.max_depth, BF_MAX_BOUNCES);
@@ -913,7 +911,11 @@ static int run_wave(bf_scene *s, WaveSlot &sl, uint64_t seed, uint64_t first, ui
         // ... and the paths that stay clear of the meshes altogether are integrated by k_path without touching the wave arrays
         path = defer && s->tune.path_fused != 0 && path_kernel_available(sc);
         if (path) {
-            timed(BF_K_PRIMARY, [&] { return launch_path(sc, w, seed, first, n, ctr, profile, w.queue_d, cfg); });
+            if (!sl.path_stash) {
+                BF_CUDA(cudaMalloc((void **) &sl.path_stash, path_stash_bytes(sc, s->sm_count)));
+                sl.allocs.push_back(sl.path_stash);
+            }
+            timed(BF_K_PRIMARY, [&] { return launch_path(sc, w, seed, first, n, ctr, profile, w.queue_d, sl.path_stash, cfg); });
             timed(BF_K_TRACE_CLOSEST, [&] { return launch_trace_closest(sc, w, w.queue_d, ctr + 0, 0, 1, ctr + 4, ctr + 3, cfg, false); });
         } else {
             timed(BF_K_PRIMARY, [&] { return launch_primary(sc, w, seed, first, n, ctr + 4, ctr + 2, profile, defer ? w.queue[0] : nullptr, ctr + 0, cfg); });
@@ -1150,8 +1152,7 @@ int bf_set_tunable(bf_scene *s, const char *name, int64_t value) {
         {"fused_primary", &s->tune.fused_primary, 0, 1}, {"primary_defer", &s->tune.primary_defer, -1, 1},
         {"trace_defer", &s->tune.trace_defer, -1, 1}, {"trace_rounds", &s->tune.trace_rounds, 0, 1024},
         {"use_graph", &s->tune.use_graph, 0, 1},
-        {"path_fused", &s->tune.path_fused, 0, 1},
-        {"path_blocks", &s->tune.path_blocks, 0, 16}};
+        {"path_fused", &s->tune.path_fused, 0, 1}};
     for (auto &t : table)
         if (strcmp(t.n, name) == 0) {
             if (value < t.lo || value > t.hi) return fail(s, BF_ERR_INVALID, std::string("bf_set_tunable: value out of range for ") + name);

@@ -852,12 +852,18 @@ __global__ void __launch_bounds__(FIN_THREADS) k_finalize(const __grid_constant_
 //   receiver ray enters the mesh bounds          -> store_primary + defer queue       (k_trace<closest> -> k_shade(1) ...)
 //   rectangle hit that is not plain diffuse      -> store_primary + hit + class queue  (k_shade(1) ...)
 //   shadow / continuation ray still undecided    -> the state k_shade(1) would have stored + shadow / next queues
-// Hits are compacted inside the warp before they are shaded: a warp generates rounds of 32 samples, parks the plain
-// rectangle hits in a shared-memory stash, and runs the shade step whenever 32 of them are waiting, so shading warps are full.
-#define PATH_THREADS 128
-#define PATH_STASH 64
-#ifndef BF_PATH_MIN_BLOCKS
-#define BF_PATH_MIN_BLOCKS 4
+// The two halves of the work -- generating receiver rays (raygen_sample + rectangle tests) and shading the rectangle hits
+// (shade_core + pre-tests + finalize_core) -- are ~16 KB and ~30 KB of executed code.  Run side by side on one SM they
+// thrash its 32 KB instruction cache (measured: 40 % of the stall samples "no instruction", profiles/r02c).  So the kernel
+// runs ONE CTA of 16 warps per SM and the whole CTA alternates between two long phases, separated by __syncthreads():
+//   G  every warp generates rounds of 32 samples; misses are binned, spills are stored, plain rectangle hits are PARKED
+//      in the CTA's stash (a word-major array in global memory, 0.5 MB per CTA: it lives in L2), until the stash is full;
+//   S  every warp takes batches of 32 parked hits -- full warps, whatever the hit rate -- and carries them to the end.
+// One phase lasts ~100 us, so the instruction cache is refilled a few thousand times per second instead of per round.
+#define PATH_THREADS 512
+#define PATH_WARPS (PATH_THREADS / 32)
+#ifndef BF_PATH_STASH_CAP
+#define BF_PATH_STASH_CAP 8192u
 #endif
 template <int S> struct PathStash {
     // words per parked hit: o(3) d(3) t slot | rng state(2) inc(2) | time f_rx sample | wl[S] weight[S]
@@ -875,6 +881,8 @@ struct PathIO {
     uint32_t *next_queue, *next_count;        // continuation rays after shade(1) that are not decided here
     uint32_t *shadow_count;                   // shadow rays after shade(1) that enter the mesh bounds (w.queue_s)
     uint32_t hist_floats;                     // > 0: the profile fits a shared-memory copy of that many floats
+    uint32_t *stash;                          // gridDim.x x WORDS x stash_cap words
+    uint32_t stash_cap;
 };
 
 // SignalBlock::put of one finished sample (box filter), as k_finalize does it per lane
@@ -902,12 +910,12 @@ __device__ __forceinline__ void scatter_splat(const Splat &sp, float *dst, uint3
 }
 
 template <int S, int RXK, int TXK>
-__global__ void __launch_bounds__(PATH_THREADS, BF_PATH_MIN_BLOCKS) k_path(const __grid_constant__ DevScene sc, const __grid_constant__ Wave w, const __grid_constant__ PathIO io) {
+__global__ void __launch_bounds__(PATH_THREADS, 1) k_path(const __grid_constant__ DevScene sc, const __grid_constant__ Wave w, const __grid_constant__ PathIO io) {
     extern __shared__ __align__(16) uint32_t path_smem[];
     float *s_rect = reinterpret_cast<float *>(path_smem);                        // RECT_SM_FLOATS * BF_MAX_RECTS
     uint32_t *s_plain = path_smem + RECT_SM_FLOATS * BF_MAX_RECTS;               // per rectangle: 1 = diffuse class, no transmitter attached
-    uint32_t *s_stash = s_plain + BF_MAX_RECTS;                                  // per warp: WORDS x PATH_STASH, word-major
-    float *s_hist = reinterpret_cast<float *>(s_stash + (PATH_THREADS / 32) * PathStash<S>::WORDS * PATH_STASH);
+    uint32_t *s_ctl = s_plain + BF_MAX_RECTS;                                    // [0] parked hits, [1] hits taken
+    float *s_hist = reinterpret_cast<float *>(s_ctl + 4);
     constexpr uint32_t C_FIXED = 3u;                                             // gen 3: Y, A, W
     const uint32_t C = sc.channels;
     const bool hist = io.hist_floats != 0u;
@@ -916,28 +924,31 @@ __global__ void __launch_bounds__(PATH_THREADS, BF_PATH_MIN_BLOCKS) k_path(const
         const DevShape sh = sc.shapes[sc.rects[r].shape];
         s_plain[r] = (sh.mat_class == 0u && sh.tx < 0) ? 1u : 0u;
     }
+    if (threadIdx.x < 4) s_ctl[threadIdx.x] = 0u;
     stage_rects(sc, s_rect);      // ends with __syncthreads()
     const uint32_t n = io.n;
     const uint32_t lane = threadIdx.x & 31u, lt_mask = (1u << lane) - 1u;
-    uint32_t *st = s_stash + (threadIdx.x >> 5) * PathStash<S>::WORDS * PATH_STASH;
+    const uint32_t cap = io.stash_cap;
+    uint32_t *st = io.stash + (size_t) blockIdx.x * PathStash<S>::WORDS * cap;    // word k of entry e: st[k * cap + e]
     float *dst = hist ? s_hist : io.profile;
+    volatile uint32_t *v_ctl = s_ctl;
 
     // work distribution: a static first chunk per warp, then chunks claimed one ahead from the global cursor
-    const uint32_t n_warps = gridDim.x * (PATH_THREADS / 32);
+    const uint32_t n_warps = gridDim.x * PATH_WARPS;
     uint32_t chunk = 32;
     while (chunk < 512 && (uint64_t) chunk * 16u * n_warps <= n) chunk *= 2;
     const uint32_t static_total = n_warps * chunk;
-    uint32_t c_next = (blockIdx.x * (PATH_THREADS / 32) + (threadIdx.x >> 5)) * chunk, c_end = c_next + chunk;   // warp-uniform
+    // warp ranks interleave the CTAs, so that a request smaller than the grid still spreads over all SMs
+    uint32_t c_next = ((threadIdx.x >> 5) * gridDim.x + blockIdx.x) * chunk, c_end = c_next + chunk;   // warp-uniform
     uint32_t claim = 0xffffffffu;
     const bool dynamic = n > static_total;
     if (dynamic && lane == 0) claim = static_total + atomic_add_async(io.work_cursor, chunk);
     bool out_of_work = c_next >= n;
 
-    uint32_t cnt = 0;                       // parked hits of this warp (warp-uniform)
     uint32_t q_closest = 0, q_shadow = 0;   // ray queries decided in this thread
     while (true) {
-        // ---------------- generate rounds of 32 samples until 32 hits are parked ----------------
-        while (!out_of_work && cnt < 32u) {
+        // ======================= phase G: generate until the stash is full =======================
+        while (!out_of_work && v_ctl[0] + PATH_THREADS <= cap) {
             const uint32_t i = c_next + lane;
             c_next += 32u;
             if (c_next >= c_end) {          // chunk used up: open the one claimed ahead
@@ -961,15 +972,7 @@ __global__ void __launch_bounds__(PATH_THREADS, BF_PATH_MIN_BLOCKS) k_path(const
                 if (trace_begin<false, true>(sc, s_rect, L)) kind = K_DEFER;
                 else if (L.best.slot == BF_NONE) kind = K_MISS;
                 else kind = s_plain[L.best.slot & 0x7fffffffu] ? K_PARK : K_SHADE1;
-                if (w.records) {
-                    bf_sample_record *r = w.records + i;
-                    init_record(r, ps.wl.v[0]);
-                    if (kind == K_MISS) {
-                        float posx, posy; bool ran; int off_x, off_y;
-                        sample_position(sc, ps.x2, (double) sc.C.c * ps.inv_wl, posx, posy, ran, off_x, off_y);
-                        r->depth = 1; r->tf_t = posx; r->tf_f = posy;
-                    }
-                }
+                if (w.records) init_record(w.records + i, ps.wl.v[0]);
             }
             if (kind == K_MISS) {
                 // SignalBlock::put of a zero value: one count in the weight channel of the sample's bin
@@ -980,6 +983,7 @@ __global__ void __launch_bounds__(PATH_THREADS, BF_PATH_MIN_BLOCKS) k_path(const
                     if (hist) atomicAdd(reinterpret_cast<uint32_t *>(s_hist + (size_t) C * pixel + C_FIXED - 1u), 1u);
                     else atomicAdd(io.profile + (size_t) C * pixel + C_FIXED - 1u, 1.f);
                 }
+                if (w.records) { bf_sample_record *r = w.records + i; r->depth = 1; r->tf_t = posx; r->tf_f = posy; }
             }
             // spills before the shade step: the lane gets the state k_primary would have given it
             const uint32_t m_spill = __ballot_sync(0xffffffffu, kind >= K_DEFER);
@@ -1007,114 +1011,125 @@ __global__ void __launch_bounds__(PATH_THREADS, BF_PATH_MIN_BLOCKS) k_path(const
                     }
                 }
             }
-            // park the plain rectangle hits
+            // park the plain rectangle hits: one shared-memory reservation per warp
             const uint32_t m_park = __ballot_sync(0xffffffffu, kind == K_PARK);
-            if (kind == K_PARK) {
-                uint32_t *e = st + cnt + __popc(m_park & lt_mask);
-                e[0 * PATH_STASH] = __float_as_uint(L.o.x); e[1 * PATH_STASH] = __float_as_uint(L.o.y); e[2 * PATH_STASH] = __float_as_uint(L.o.z);
-                e[3 * PATH_STASH] = __float_as_uint(L.d.x); e[4 * PATH_STASH] = __float_as_uint(L.d.y); e[5 * PATH_STASH] = __float_as_uint(L.d.z);
-                e[6 * PATH_STASH] = __float_as_uint(L.best.t); e[7 * PATH_STASH] = L.best.slot;
-                e[8 * PATH_STASH] = (uint32_t) ps.rng.state; e[9 * PATH_STASH] = (uint32_t) (ps.rng.state >> 32);
-                e[10 * PATH_STASH] = (uint32_t) ps.rng.inc; e[11 * PATH_STASH] = (uint32_t) (ps.rng.inc >> 32);
-                e[12 * PATH_STASH] = __float_as_uint(ps.time); e[13 * PATH_STASH] = __float_as_uint(ps.x2.y); e[14 * PATH_STASH] = i;
+            if (m_park) {
+                uint32_t pbase = 0;
+                if (lane == 0) pbase = atomicAdd(s_ctl, (uint32_t) __popc(m_park));
+                pbase = __shfl_sync(0xffffffffu, pbase, 0);
+                if (kind == K_PARK) {
+                    uint32_t *e = st + pbase + __popc(m_park & lt_mask);
+                    e[0 * cap] = __float_as_uint(L.o.x); e[1 * cap] = __float_as_uint(L.o.y); e[2 * cap] = __float_as_uint(L.o.z);
+                    e[3 * cap] = __float_as_uint(L.d.x); e[4 * cap] = __float_as_uint(L.d.y); e[5 * cap] = __float_as_uint(L.d.z);
+                    e[6 * cap] = __float_as_uint(L.best.t); e[7 * cap] = L.best.slot;
+                    e[8 * cap] = (uint32_t) ps.rng.state; e[9 * cap] = (uint32_t) (ps.rng.state >> 32);
+                    e[10 * cap] = (uint32_t) ps.rng.inc; e[11 * cap] = (uint32_t) (ps.rng.inc >> 32);
+                    e[12 * cap] = __float_as_uint(ps.time); e[13 * cap] = __float_as_uint(ps.x2.y); e[14 * cap] = i;
+#pragma unroll
+                    for (int k = 0; k < S; ++k) {
+                        e[(PathStash<S>::WL + k) * cap] = __float_as_uint(ps.wl.v[k]);
+                        e[(PathStash<S>::WEIGHT + k) * cap] = __float_as_uint(ps.weight.v[k]);
+                    }
+                }
+            }
+        }
+        const int all_out = __syncthreads_and(out_of_work ? 1 : 0);      // parked entries are visible to the whole CTA
+        const uint32_t total = v_ctl[0];
+        // ======================= phase S: shade the parked hits, 32 at a time =======================
+        while (true) {
+            uint32_t first = 0;
+            if (lane == 0) first = atomicAdd(s_ctl + 1, 32u);
+            first = __shfl_sync(0xffffffffu, first, 0);
+            if (first >= total) break;
+            const bool act = first + lane < total;
+            LaneRegs<S> R;
+            Spec<S> weight;
+            float f_rx = 0.f, t_sample = 0.f;
+            uint32_t smp = 0;
+            if (act) {
+                const uint32_t *e = st + first + lane;
+                R.o = V3(__uint_as_float(e[0 * cap]), __uint_as_float(e[1 * cap]), __uint_as_float(e[2 * cap]));
+                R.d = V3(__uint_as_float(e[3 * cap]), __uint_as_float(e[4 * cap]), __uint_as_float(e[5 * cap]));
+                R.hit = make_float4(__uint_as_float(e[6 * cap]), 0.f, 0.f, __uint_as_float(e[7 * cap]));
+                R.rng.state = (uint64_t) e[8 * cap] | ((uint64_t) e[9 * cap] << 32);
+                R.rng.inc = (uint64_t) e[10 * cap] | ((uint64_t) e[11 * cap] << 32);
+                t_sample = __uint_as_float(e[12 * cap]); f_rx = __uint_as_float(e[13 * cap]); smp = e[14 * cap];
 #pragma unroll
                 for (int k = 0; k < S; ++k) {
-                    e[(PathStash<S>::WL + k) * PATH_STASH] = __float_as_uint(ps.wl.v[k]);
-                    e[(PathStash<S>::WEIGHT + k) * PATH_STASH] = __float_as_uint(ps.weight.v[k]);
+                    R.wl.v[k] = __uint_as_float(e[(PathStash<S>::WL + k) * cap]);
+                    weight.v[k] = __uint_as_float(e[(PathStash<S>::WEIGHT + k) * cap]);
                 }
             }
-            cnt += __popc(m_park);
-            __syncwarp();
-        }
-        if (cnt == 0u) break;               // out of work and nothing parked
-        // ---------------- shade up to 32 parked hits ----------------
-        const uint32_t take = min(cnt, 32u);
-        const bool act = lane < take;
-        LaneRegs<S> R;
-        Spec<S> weight;
-        float f_rx = 0.f, t_sample = 0.f;
-        uint32_t smp = 0;
-        if (act) {
-            const uint32_t *e = st + (cnt - take) + lane;
-            R.o = V3(__uint_as_float(e[0 * PATH_STASH]), __uint_as_float(e[1 * PATH_STASH]), __uint_as_float(e[2 * PATH_STASH]));
-            R.d = V3(__uint_as_float(e[3 * PATH_STASH]), __uint_as_float(e[4 * PATH_STASH]), __uint_as_float(e[5 * PATH_STASH]));
-            R.hit = make_float4(__uint_as_float(e[6 * PATH_STASH]), 0.f, 0.f, __uint_as_float(e[7 * PATH_STASH]));
-            R.rng.state = (uint64_t) e[8 * PATH_STASH] | ((uint64_t) e[9 * PATH_STASH] << 32);
-            R.rng.inc = (uint64_t) e[10 * PATH_STASH] | ((uint64_t) e[11 * PATH_STASH] << 32);
-            t_sample = __uint_as_float(e[12 * PATH_STASH]); f_rx = __uint_as_float(e[13 * PATH_STASH]); smp = e[14 * PATH_STASH];
+            bool sh_spill = false, nx_spill = false;
+            ShadeOut so; so.push_next = false; so.push_shadow = false;
+            float4 x2 = make_float4(t_sample, f_rx, 0.f, S == 1 ? weight.v[0] : 0.f);
+            if (act) {
+                R.flags = LANE_ACTIVE;
+                R.thr = Spec<S>(1.f); R.res = Spec<S>(0.f); R.pend = Spec<S>(0.f);
+                R.time = t_sample; R.phase = 0.f; R.bs_pdf = 0.f; R.scalar = 0.f;
+                bf_sample_record *rec = w.records ? w.records + smp : nullptr;
+                shade_core<S, BF_GEN_PHASE, TXK, BF_BSDF_DIFFUSE, false>(sc, 1u, R, rec, so);
+                if (so.push_shadow) {
+                    TraceLane T; T.o = so.origin; T.d = so.sh_d; T.mint = so.mint; T.maxt = so.sh_maxt;
+                    if (trace_begin<true>(sc, s_rect, T)) {
+                        sh_spill = true;
+                    } else {
+                        ++q_shadow;
+                        if (!T.occluded) {
 #pragma unroll
-            for (int k = 0; k < S; ++k) {
-                R.wl.v[k] = __uint_as_float(e[(PathStash<S>::WL + k) * PATH_STASH]);
-                weight.v[k] = __uint_as_float(e[(PathStash<S>::WEIGHT + k) * PATH_STASH]);
-            }
-        }
-        cnt -= take;
-        __syncwarp();                        // entries are read before the next round overwrites them
-        bool sh_spill = false, nx_spill = false;
-        ShadeOut so; so.push_next = false; so.push_shadow = false;
-        float4 x2 = make_float4(t_sample, f_rx, 0.f, S == 1 ? weight.v[0] : 0.f);
-        if (act) {
-            R.flags = LANE_ACTIVE;
-            R.thr = Spec<S>(1.f); R.res = Spec<S>(0.f); R.pend = Spec<S>(0.f);
-            R.time = t_sample; R.phase = 0.f; R.bs_pdf = 0.f; R.scalar = 0.f;
-            bf_sample_record *rec = w.records ? w.records + smp : nullptr;
-            shade_core<S, BF_GEN_PHASE, TXK, BF_BSDF_DIFFUSE, false>(sc, 1u, R, rec, so);
-            if (so.push_shadow) {
-                TraceLane T; T.o = so.origin; T.d = so.sh_d; T.mint = so.mint; T.maxt = so.sh_maxt;
-                if (trace_begin<true>(sc, s_rect, T)) {
-                    sh_spill = true;
-                } else {
-                    ++q_shadow;
-                    if (!T.occluded) {
-#pragma unroll
-                        for (int k = 0; k < S; ++k) R.res.v[k] += R.pend.v[k];
+                            for (int k = 0; k < S; ++k) R.res.v[k] += R.pend.v[k];
+                        }
+                        R.flags &= ~LANE_PENDING;
                     }
-                    R.flags &= ~LANE_PENDING;
+                }
+                if (so.push_next) {
+                    TraceLane T; T.o = so.origin; T.d = so.new_d; T.mint = so.mint; T.maxt = bf_inf();
+                    const bool need = trace_begin<false, true>(sc, s_rect, T);
+                    if (need || T.best.slot != BF_NONE) {
+                        nx_spill = true;         // k_trace<closest> redoes the query for this lane
+                    } else {
+                        // the continuation ray leaves the scene: the miss branch of k_trace (pathtimefrequency.cpp:368-371, t = inf)
+                        ++q_closest;
+                        R.time = -bf_inf(); R.phase = -bf_inf();
+                        if (rec) rec->depth = 2u;
+                    }
+                }
+                if (!sh_spill && !nx_spill) {
+                    const Splat sp = finalize_core<S>(sc, R.flags, R.phase, R.scalar, x2, R.res, R.wl, weight, rec);
+                    if (hist) scatter_splat<true>(sp, dst, C, C_FIXED); else scatter_splat<false>(sp, dst, C, C_FIXED);
                 }
             }
-            if (so.push_next) {
-                TraceLane T; T.o = so.origin; T.d = so.new_d; T.mint = so.mint; T.maxt = bf_inf();
-                const bool need = trace_begin<false, true>(sc, s_rect, T);
-                if (need || T.best.slot != BF_NONE) {
-                    nx_spill = true;         // k_trace<closest> redoes the query for this lane
-                } else {
-                    // the continuation ray leaves the scene: the miss branch of k_trace (pathtimefrequency.cpp:368-371, t = inf)
-                    ++q_closest;
-                    R.time = -bf_inf(); R.phase = -bf_inf();
-                    if (rec) rec->depth = 2u;
+            // spills after the shade step: what k_shade(1) would have left in the wave arrays
+            const uint32_t m_spill = __ballot_sync(0xffffffffu, sh_spill || nx_spill);
+            if (m_spill) {
+                const uint32_t ms = __ballot_sync(0xffffffffu, sh_spill), mn = __ballot_sync(0xffffffffu, nx_spill);
+                uint32_t base = 0;
+                if (lane == 0) base = atomicAdd(io.n_lanes, (uint32_t) __popc(m_spill));
+                else if (lane == 1 && ms) base = atomicAdd(io.shadow_count, (uint32_t) __popc(ms));
+                else if (lane == 2 && mn) base = atomicAdd(io.next_count, (uint32_t) __popc(mn));
+                const uint32_t base_l = __shfl_sync(0xffffffffu, base, 0), base_s = __shfl_sync(0xffffffffu, base, 1), base_n = __shfl_sync(0xffffffffu, base, 2);
+                if (sh_spill || nx_spill) {
+                    const uint32_t dl = base_l + __popc(m_spill & lt_mask);
+                    w.ray_o[dl] = make_float4(so.origin.x, so.origin.y, so.origin.z, so.mint);
+                    if (nx_spill) w.ray_d[dl] = make_float4(so.new_d.x, so.new_d.y, so.new_d.z, bf_inf());
+                    if (sh_spill) w.sh_d[dl] = make_float4(so.sh_d.x, so.sh_d.y, so.sh_d.z, so.sh_maxt);
+                    w.flags[dl] = R.flags;
+                    w.x1[dl] = make_float4(R.time, R.phase, R.bs_pdf, R.scalar);
+                    float4 x2s = x2;
+                    SpecIO<S>::store_weight(w, dl, weight, x2s);
+                    w.x2[dl] = x2s;
+                    SpecIO<S>::store(w, dl, R.thr, R.res, R.pend, R.wl);
+                    w.rng[dl] = make_ulonglong2(R.rng.state, R.rng.inc);
+                    if (w.sample_of) w.sample_of[dl] = smp;
+                    if (sh_spill) w.queue_s[base_s + __popc(ms & lt_mask)] = dl;
+                    if (nx_spill) io.next_queue[base_n + __popc(mn & lt_mask)] = dl;
                 }
             }
-            if (!sh_spill && !nx_spill) {
-                const Splat sp = finalize_core<S>(sc, R.flags, R.phase, R.scalar, x2, R.res, R.wl, weight, rec);
-                if (hist) scatter_splat<true>(sp, dst, C, C_FIXED); else scatter_splat<false>(sp, dst, C, C_FIXED);
-            }
         }
-        // spills after the shade step: what k_shade(1) would have left in the wave arrays
-        const uint32_t m_spill = __ballot_sync(0xffffffffu, sh_spill || nx_spill);
-        if (m_spill) {
-            const uint32_t ms = __ballot_sync(0xffffffffu, sh_spill), mn = __ballot_sync(0xffffffffu, nx_spill);
-            uint32_t base = 0;
-            if (lane == 0) base = atomicAdd(io.n_lanes, (uint32_t) __popc(m_spill));
-            else if (lane == 1 && ms) base = atomicAdd(io.shadow_count, (uint32_t) __popc(ms));
-            else if (lane == 2 && mn) base = atomicAdd(io.next_count, (uint32_t) __popc(mn));
-            const uint32_t base_l = __shfl_sync(0xffffffffu, base, 0), base_s = __shfl_sync(0xffffffffu, base, 1), base_n = __shfl_sync(0xffffffffu, base, 2);
-            if (sh_spill || nx_spill) {
-                const uint32_t dl = base_l + __popc(m_spill & lt_mask);
-                w.ray_o[dl] = make_float4(so.origin.x, so.origin.y, so.origin.z, so.mint);
-                if (nx_spill) w.ray_d[dl] = make_float4(so.new_d.x, so.new_d.y, so.new_d.z, bf_inf());
-                if (sh_spill) w.sh_d[dl] = make_float4(so.sh_d.x, so.sh_d.y, so.sh_d.z, so.sh_maxt);
-                w.flags[dl] = R.flags;
-                w.x1[dl] = make_float4(R.time, R.phase, R.bs_pdf, R.scalar);
-                float4 x2s = x2;
-                SpecIO<S>::store_weight(w, dl, weight, x2s);
-                w.x2[dl] = x2s;
-                SpecIO<S>::store(w, dl, R.thr, R.res, R.pend, R.wl);
-                w.rng[dl] = make_ulonglong2(R.rng.state, R.rng.inc);
-                if (w.sample_of) w.sample_of[dl] = smp;
-                if (sh_spill) w.queue_s[base_s + __popc(ms & lt_mask)] = dl;
-                if (nx_spill) io.next_queue[base_n + __popc(mn & lt_mask)] = dl;
-            }
-        }
+        if (all_out) break;
+        __syncthreads();                     // every warp has left phase S
+        if (threadIdx.x == 0) { s_ctl[0] = 0u; s_ctl[1] = 0u; }
+        __syncthreads();
     }
     // ray-query totals of this warp
     {
@@ -1278,17 +1293,19 @@ int launch_primary(const DevScene &sc, const Wave &w, uint64_t seed, uint64_t fi
 #undef BF_PRIMARY
     return 1;
 }
-// Dynamic shared memory of k_path: rectangles, per-rectangle flags, the warps' stashes, the profile copy
-static size_t path_smem_bytes(uint32_t S, uint32_t hist_floats) {
-    const size_t words = (S == 1 ? PathStash<1>::WORDS : PathStash<4>::WORDS);
-    return ((size_t) RECT_SM_FLOATS * BF_MAX_RECTS + BF_MAX_RECTS + (PATH_THREADS / 32) * words * PATH_STASH + hist_floats) * 4;
+// Dynamic shared memory of k_path: rectangles, per-rectangle flags, phase counters, the profile copy
+static size_t path_smem_bytes(uint32_t hist_floats) {
+    return ((size_t) RECT_SM_FLOATS * BF_MAX_RECTS + BF_MAX_RECTS + 4 + hist_floats) * 4;
 }
 bool path_kernel_available(const DevScene &sc) {
     return sc.integ.gen == BF_GEN_PHASE && sc.n_txs == 1 && (sc.hint_tx_kind == BF_TX_WIGNER || sc.hint_tx_kind == BF_TX_AREA) &&
            (sc.hint_rx_kind == BF_RX_WIGNER || sc.hint_rx_kind == BF_RX_OMNIDIRECTIONAL) && sc.n_nodes != 0;
 }
+size_t path_stash_bytes(const DevScene &sc, int sm_count) {
+    return (size_t) sm_count * (sc.S == 1 ? PathStash<1>::WORDS : PathStash<4>::WORDS) * BF_PATH_STASH_CAP * 4;
+}
 int launch_path(const DevScene &sc, const Wave &w, uint64_t seed, uint64_t first_sample, uint32_t n, uint32_t *ctr, float *profile,
-                uint32_t *defer_queue, const LaunchCfg &cfg) {
+                uint32_t *defer_queue, uint32_t *stash, const LaunchCfg &cfg) {
     if (n == 0) return 0;
     PathIO io;
     io.seed = seed; io.first_sample = first_sample; io.n = n;
@@ -1298,12 +1315,10 @@ int launch_path(const DevScene &sc, const Wave &w, uint64_t seed, uint64_t first
     io.next_queue = w.queue[0]; io.next_count = blk1 + 0; io.shadow_count = blk1 + 1;
     const uint32_t floats = sc.channels * sc.film_w * sc.film_h;
     io.hist_floats = floats <= FIN_SMEM_FLOATS ? floats : 0u;
-    const size_t smem = path_smem_bytes(sc.S, io.hist_floats);
-    const int grid = cfg.sm_count * (cfg.path_blocks > 0 ? cfg.path_blocks : BF_PATH_MIN_BLOCKS);
-#define BF_PATH(S_, R_, T_) do { \
-        static bool attr_set = false; \
-        if (!attr_set) { cudaFuncSetAttribute(k_path<S_, R_, T_>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) path_smem_bytes(S_, FIN_SMEM_FLOATS)); attr_set = true; } \
-        k_path<S_, R_, T_><<<grid, PATH_THREADS, smem, cfg.stream>>>(sc, w, io); } while (0)
+    io.stash = stash; io.stash_cap = BF_PATH_STASH_CAP;
+    const size_t smem = path_smem_bytes(io.hist_floats);
+    const int grid = cfg.sm_count;       // one CTA per SM: the CTA-wide phases are what keeps the instruction cache warm
+#define BF_PATH(S_, R_, T_) k_path<S_, R_, T_><<<grid, PATH_THREADS, smem, cfg.stream>>>(sc, w, io)
 #define BF_PATH_RT(S_) do { \
         if (sc.hint_rx_kind == BF_RX_WIGNER && sc.hint_tx_kind == BF_TX_WIGNER) BF_PATH(S_, BF_RX_WIGNER, BF_TX_WIGNER); \
         else if (sc.hint_rx_kind == BF_RX_WIGNER) BF_PATH(S_, BF_RX_WIGNER, BF_TX_AREA); \

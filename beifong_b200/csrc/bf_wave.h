@@ -50,7 +50,6 @@ struct LaunchCfg {
     cudaStream_t stream;
     int sm_count;
     uint32_t trace_rounds;   // k_trace: batches of 32 rays per active warp (0 = every warp of the grid takes part)
-    int path_blocks;         // k_path: CTAs per SM (0 = the kernel's launch bound)
 };
 
 // Kernel launchers (bf_kernels.cu).  Return the number of kernels launched.
@@ -63,8 +62,9 @@ int launch_primary(const DevScene &sc, const Wave &w, uint64_t seed, uint64_t fi
 // (counter layout: ctr + 0 defer_queue length, + 2 work cursor, + 4 / + 5 shade(1) class queues, ctr + BF_CTR_STRIDE + 0 / + 1
 // the continuation / shadow queues that shade(1) appends to).  path_kernel_available: the scene has an instantiation.
 bool path_kernel_available(const DevScene &sc);
+size_t path_stash_bytes(const DevScene &sc, int sm_count);     // per wave slot: the CTAs' parking areas
 int launch_path(const DevScene &sc, const Wave &w, uint64_t seed, uint64_t first_sample, uint32_t n, uint32_t *ctr, float *profile,
-                uint32_t *defer_queue, const LaunchCfg &cfg);
+                uint32_t *defer_queue, uint32_t *stash, const LaunchCfg &cfg);
 int launch_raygen(const DevScene &sc, const Wave &w, uint64_t seed, uint64_t first_sample, uint32_t n, const LaunchCfg &cfg);
 // queue == nullptr: lanes [0, n_direct); else lane ids from queue[0 .. *count)
 // depth = the shade iteration this trace feeds; lanes that hit are appended to w.queue_h / *hit_count
