@@ -172,7 +172,7 @@ static int64_t env_i64(const char *name, int64_t dflt, int64_t lo, int64_t hi) {
 }
 static Tunables tunables_from_env() {
     Tunables t;
-    t.wave_lanes = env_i64("BF_WAVE_LANES", 0, 0, 1ll << 26);
+    t.wave_lanes = env_i64("BF_WAVE_LANES", 0, 0, 1ll << 28);
     t.wave_streams = env_i64("BF_WAVE_STREAMS", 8, 1, 16);
     t.fused_primary = env_i64("BF_FUSED_PRIMARY", 1, 0, 1);
     t.primary_defer = env_i64("BF_PRIMARY_DEFER", -1, -1, 1);
@@ -741,7 +741,7 @@ int bf_scene_commit(bf_scene *s, int device) {
     }
     WideBvh bvh;
     build_wide_bvh(tris, 4e-6f * std::max(scene_abs, 1e-3f), bvh);
-    if (bvh.stats.depth > BF_TRACE_STACK_DEPTH)
+    if (2 * bvh.stats.depth + 2 > BF_TRACE_STACK_DEPTH)   // node groups and parked triangle groups share the stack
         return fail(s, BF_ERR_UNSUPPORTED, "bf_scene_commit: BVH deeper than the traversal stack");
     bool any_normals = false;
     for (const HostMesh &m : s->meshes) any_normals |= !m.nrm.empty();
@@ -1148,7 +1148,7 @@ int bf_get_stats(const bf_scene *s_, bf_stats *stats) {
 int bf_set_tunable(bf_scene *s, const char *name, int64_t value) {
     if (!s || !name) return BF_ERR_INVALID;
     struct { const char *n; int64_t *p; int64_t lo, hi; } table[] = {
-        {"wave_lanes", &s->tune.wave_lanes, 0, 1ll << 26}, {"wave_streams", &s->tune.wave_streams, 1, 16},
+        {"wave_lanes", &s->tune.wave_lanes, 0, 1ll << 28}, {"wave_streams", &s->tune.wave_streams, 1, 16},
         {"fused_primary", &s->tune.fused_primary, 0, 1}, {"primary_defer", &s->tune.primary_defer, -1, 1},
         {"trace_defer", &s->tune.trace_defer, -1, 1}, {"trace_rounds", &s->tune.trace_rounds, 0, 1024},
         {"use_graph", &s->tune.use_graph, 0, 1},

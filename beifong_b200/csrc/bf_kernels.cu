@@ -855,12 +855,14 @@ __global__ void __launch_bounds__(FIN_THREADS) k_finalize(const __grid_constant_
 // The two halves of the work -- generating receiver rays (raygen_sample + rectangle tests) and shading the rectangle hits
 // (shade_core + pre-tests + finalize_core) -- are ~16 KB and ~30 KB of executed code.  Run side by side on one SM they
 // thrash its 32 KB instruction cache (measured: 40 % of the stall samples "no instruction", profiles/r02c).  So the kernel
-// runs ONE CTA of 16 warps per SM and the whole CTA alternates between two long phases, separated by __syncthreads():
+// runs ONE CTA of 32 warps per SM and the whole CTA alternates between two long phases, separated by __syncthreads():
 //   G  every warp generates rounds of 32 samples; misses are binned, spills are stored, plain rectangle hits are PARKED
 //      in the CTA's stash (a word-major array in global memory, 0.5 MB per CTA: it lives in L2), until the stash is full;
 //   S  every warp takes batches of 32 parked hits -- full warps, whatever the hit rate -- and carries them to the end.
 // One phase lasts ~100 us, so the instruction cache is refilled a few thousand times per second instead of per round.
-#define PATH_THREADS 512
+#ifndef PATH_THREADS
+#define PATH_THREADS 1024    // 32 warps at 64 registers: measured 10.3 Gsamples/s against 9.8 (768 x 80) and 8.7 (512 x 108), profiles/r02e
+#endif
 #define PATH_WARPS (PATH_THREADS / 32)
 #ifndef BF_PATH_STASH_CAP
 #define BF_PATH_STASH_CAP 8192u

@@ -23,6 +23,9 @@ namespace bf {
 #ifndef TRACE_MIN_BLOCKS
 #define TRACE_MIN_BLOCKS 8
 #endif
+#ifndef TRACE_TRI_MIN
+#define TRACE_TRI_MIN 0      // > 0: triangle tests are postponed when fewer lanes than this are testing.  Measured slower on C2 (8 / 16 / 24: trace_closest 1.93 / 1.88 / 1.92 ms per 64 M samples against 1.69 ms without, profiles/r02e), so off
+#endif
 
 __device__ __forceinline__ uint32_t sign_extend_s8x4(uint32_t x) {
     uint32_t r;
@@ -156,7 +159,11 @@ template <bool ANY_HIT>
 __device__ __forceinline__ bool trace_step(const DevScene &sc, uint2 *s_stack, uint2 *l_stack, TraceLane &L) {
     const uint32_t tid = threadIdx.x;
     uint2 tgroup = make_uint2(0u, 0u);
-    {
+    if (L.ngroup.y <= 0x00ffffffu) {
+        // the entry popped last was a parked triangle group (see below)
+        tgroup = L.ngroup;
+        L.ngroup = make_uint2(0u, 0u);
+    } else {
         const uint32_t hits_imask = L.ngroup.y;
         const uint32_t child_bit_index = 31u - __clz(hits_imask);
         const uint32_t child_node_base = L.ngroup.x;
@@ -218,7 +225,13 @@ __device__ __forceinline__ bool trace_step(const DevScene &sc, uint2 *s_stack, u
         tgroup.y = hitmask & 0x00ffffffu;
     }
 
+    // Triangle tests: the lanes of a warp have very different numbers of them after a node step.  Once fewer than
+    // TRACE_TRI_MIN lanes are still testing, a lane that has node work left parks its remaining triangles on the stack
+    // (an entry with only the low 24 bits set) and goes on with the nodes; the parked group is tested when it is popped,
+    // with whatever lanes are in their triangle phase then (Ylitie, Karras, Laine 2017, "postponing").  Results do not
+    // depend on the order: closest-hit ties are broken by (shape, prim).
     while (tgroup.y != 0) {
+        if (TRACE_TRI_MIN > 0 && L.ngroup.y > 0x00ffffffu && __popc(__activemask()) < TRACE_TRI_MIN) break;
         const uint32_t i = 31u - __clz(tgroup.y);
         tgroup.y &= ~(1u << i);
         const uint32_t slot = tgroup.x + i;
@@ -231,6 +244,11 @@ __device__ __forceinline__ bool trace_step(const DevScene &sc, uint2 *s_stack, u
         }
     }
 
+    if (tgroup.y != 0) {      // parked (only reached with node work left in L.ngroup)
+        if (L.sp < TRACE_SM_STACK) s_stack[L.sp * TRACE_THREADS + tid] = tgroup;
+        else l_stack[L.sp - TRACE_SM_STACK] = tgroup;
+        ++L.sp;
+    }
     if (L.ngroup.y <= 0x00ffffffu) {
         if (L.sp == 0) return false;
         --L.sp;
