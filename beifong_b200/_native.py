@@ -70,10 +70,16 @@ class bf_sample_record(C.Structure):
                 ("wavelength0", f32), ("depth", u32)]
 
 
+class bf_batch_item(C.Structure):
+    _fields_ = [("seed", u64), ("first_sample", u64), ("n_rect_updates", u32), ("receiver_shape", u32),
+                ("rect_shape_ids", C.POINTER(u32)), ("rect_to_world", C.POINTER(f32)), ("receiver", C.POINTER(bf_endpoint_desc))]
+
+
 class bf_stats(C.Structure):
     _fields_ = [("samples", u64), ("closest_queries", u64), ("shadow_queries", u64), ("kernel_launches", u64),
                 ("bvh_nodes", u32), ("bvh_tris", u32), ("bvh_depth", u32), ("n_rects", u32),
-                ("build_ms", C.c_double), ("upload_ms", C.c_double)]
+                ("build_ms", C.c_double), ("upload_ms", C.c_double),
+                ("path_closest_queries", u64), ("path_shadow_queries", u64)]
 
 
 # name -> (restype, argtypes); also the list of symbols include/beifong_b200/abi.h declares
@@ -99,10 +105,16 @@ PROTOTYPES = {
     "bf_profile_channels": (C.c_int, [vp, P(u32)]),
     "bf_profile_size": (C.c_int, [vp, P(u32), P(u32), P(u32)]),
     "bf_receive": (C.c_int, [vp, u64, u64, u64, C.c_int]),
+    "bf_receive_batch": (C.c_int, [vp, u32, P(bf_batch_item), u64, P(f32), C.c_size_t]),
+    "bf_batch_device_ptr": (C.c_int, [vp, P(vp), P(C.c_size_t), P(vp)]),
     "bf_profile_read": (C.c_int, [vp, P(f32), C.c_size_t]),
     "bf_profile_develop": (C.c_int, [vp, u32, vp, C.c_size_t]),
     "bf_profile_device_ptr": (C.c_int, [vp, P(vp), P(C.c_size_t), P(vp)]),
     "bf_synchronize": (C.c_int, [vp]),
+    "bf_multi_unique_id": (C.c_int, [vp, C.c_size_t]),
+    "bf_multi_init": (C.c_int, [vp, C.c_int, C.c_int, vp, C.c_size_t]),
+    "bf_multi_reduce": (C.c_int, [vp, C.c_int]),
+    "bf_multi_reduce_comm": (C.c_int, [vp, vp, C.c_int]),
     "bf_trace_first_hits": (C.c_int, [vp, P(f32), P(f32), P(f32), P(f32), u64, P(u32), P(u32), P(f32), P(f32), P(f32)]),
     "bf_trace_occluded": (C.c_int, [vp, P(f32), P(f32), P(f32), P(f32), u64, P(C.c_uint8)]),
     "bf_debug_trace_steps": (C.c_int, [vp, P(f32), P(f32), P(f32), P(f32), u64, P(u32), P(f32)]),

@@ -2,6 +2,7 @@
 // wavefront driver loop.  There is no CPU fallback behind this file: bf_scene_commit fails with
 // BF_ERR_CUDA when no device is usable and every compute entry point requires a committed scene.
 #include <cuda_runtime.h>
+#include <dlfcn.h>
 
 #include <algorithm>
 #include <chrono>
@@ -161,6 +162,7 @@ struct Tunables {
     int64_t trace_rounds = 8;     // batches of 32 rays per active traversal warp (0: all warps of the grid)
     int64_t use_graph = 1;        // small calls: replay the wave's launch sequence from a CUDA graph
     int64_t path_fused = 1;       // scenes with a deferred primary: k_path integrates the rectangle-only paths in registers
+    int64_t mega_max = 16384;     // requests up to this many samples, and every request on a scene without meshes (-1: never), run as ONE k_mega launch
 };
 static int64_t env_i64(const char *name, int64_t dflt, int64_t lo, int64_t hi) {
     const char *e = getenv(name);
@@ -180,6 +182,7 @@ static Tunables tunables_from_env() {
     t.trace_rounds = env_i64("BF_TRACE_ROUNDS", 8, 0, 1024);
     t.use_graph = env_i64("BF_USE_GRAPH", 1, 0, 1);
     t.path_fused = env_i64("BF_PATH_FUSED", 1, 0, 1);
+    t.mega_max = env_i64("BF_MEGA_MAX", 16384, -1, 1ll << 28);
     return t;
 }
 
@@ -201,6 +204,7 @@ struct bf_scene {
 
     // device side
     bool committed = false, tables_dirty = false;
+    bool tables_light = false;       // tables_dirty, but only rectangle poses and / or a non-phased receiver descriptor changed since the last upload
     int device = 0, sm_count = 148;
     cudaStream_t stream = nullptr;
     DevScene dev;
@@ -208,16 +212,22 @@ struct bf_scene {
     DevBuf<DevRect> d_rects; DevBuf<DevShape> d_shapes; DevBuf<bf_bsdf_desc> d_bsdfs;
     DevBuf<DevSpectrum> d_spectra; DevBuf<float> d_spec_pool; DevBuf<DevEndpoint> d_txs, d_rx; DevBuf<DevVElem> d_velems;
     DevBuf<float> d_profile; size_t profile_floats = 0;
+    DevBuf<float> d_batch; uint32_t batch_items = 0;   // bf_receive_batch: one profile per item
     bool primary_defer = false;      // fused primary: traverse the rays that enter the mesh bounds in a separate dense launch
     DevFilter filter; bool wide_filter = false;    // discretised reconstruction filter when wider than one bin
     DevBuf<uint32_t> d_developed;    // bf_profile_develop output (fp32 or fp16 components)
     // image of the geometry tables in pinned host memory (re-upload without a rebuild)
     void *h_geom = nullptr; size_t h_geom_bytes = 0, h_nodes_bytes = 0, h_tris_bytes = 0, h_nrm_bytes = 0;
     void *h_tables = nullptr; size_t h_tables_bytes = 0;   // pinned staging of the small tables (upload_tables)
+    // ring of pinned staging slots for the light uploads (rectangle poses + receiver descriptor): a slot is rewritten only
+    // after the event recorded behind its copy has completed, so per-frame re-posing never synchronises the stream
+    static const int RING = 32;
+    void *h_ring = nullptr; size_t ring_slot_bytes = 0; int ring_next = 0; cudaEvent_t ring_ev[RING] = {};
     // wave
     std::vector<WaveSlot> slots;      // slot 0 runs on `stream`
     DevBuf<unsigned long long> d_totals;
     cudaEvent_t ev_fork = nullptr;
+    void *nccl_comm = nullptr;        // bf_multi_init
     // stats / timing
     bf_stats stats;
     cudaEvent_t ev_begin = nullptr, ev_end = nullptr;
@@ -225,6 +235,7 @@ struct bf_scene {
     bool time_trace = false;
 };
 
+static void multi_destroy_comm(void *comm);
 static thread_local std::string g_create_error;
 
 static int fail(bf_scene *s, int code, const std::string &msg) {
@@ -380,12 +391,15 @@ void bf_scene_destroy(bf_scene *s) {
     if (s->committed) {
         cudaSetDevice(s->device);
         if (s->stream) cudaStreamSynchronize(s->stream);
+        if (s->nccl_comm) multi_destroy_comm(s->nccl_comm);
         free_wave(s);
         s->d_nodes.release(); s->d_tris.release(); s->d_tri_nrm.release(); s->d_rects.release(); s->d_shapes.release();
         s->d_bsdfs.release(); s->d_spectra.release(); s->d_spec_pool.release(); s->d_txs.release(); s->d_rx.release(); s->d_velems.release();
-        s->d_profile.release(); s->d_developed.release(); s->d_totals.release();
+        s->d_profile.release(); s->d_batch.release(); s->d_developed.release(); s->d_totals.release();
         if (s->h_geom) cudaFreeHost(s->h_geom);
         if (s->h_tables) cudaFreeHost(s->h_tables);
+        if (s->h_ring) cudaFreeHost(s->h_ring);
+        for (cudaEvent_t e : s->ring_ev) if (e) cudaEventDestroy(e);
         if (s->ev_fork) cudaEventDestroy(s->ev_fork);
         if (s->ev_begin) cudaEventDestroy(s->ev_begin);
         if (s->ev_end) cudaEventDestroy(s->ev_end);
@@ -412,7 +426,7 @@ int bf_scene_add_spectrum(bf_scene *s, uint32_t kind, uint32_t n, const float *l
     record(s, BF_TAG_SPECTRUM, hdr, 8, t.lambda.data(), 4 * (size_t) n, t.value.data(), 4 * (size_t) n);
     if (spectrum_id) *spectrum_id = (uint32_t) s->spectra.size();
     s->spectra.push_back(std::move(t));
-    s->tables_dirty = true;
+    s->tables_dirty = true; s->tables_light = false;
     return BF_OK;
 }
 
@@ -428,7 +442,7 @@ int bf_scene_add_bsdf(bf_scene *s, const bf_bsdf_desc *desc, uint32_t *bsdf_id) 
     record(s, BF_TAG_BSDF, desc, sizeof(*desc));
     if (bsdf_id) *bsdf_id = (uint32_t) s->bsdfs.size();
     s->bsdfs.push_back(*desc);
-    s->tables_dirty = true;
+    s->tables_dirty = true; s->tables_light = false;
     return BF_OK;
 }
 
@@ -496,7 +510,7 @@ int bf_scene_add_transmitter(bf_scene *s, uint32_t shape_id, const bf_endpoint_d
     if (t.shape >= 0) s->shapes[shape_id].tx = (int32_t) s->txs.size();
     if (transmitter_id) *transmitter_id = (uint32_t) s->txs.size();
     s->txs.push_back(t);
-    s->tables_dirty = true;
+    s->tables_dirty = true; s->tables_light = false;
     return BF_OK;
 }
 
@@ -510,6 +524,7 @@ int bf_scene_set_receiver(bf_scene *s, uint32_t shape_id, const bf_endpoint_desc
         const uint32_t w1 = desc->film_width ? desc->film_width : 1, h1 = desc->film_height ? desc->film_height : 1;
         if (w0 != w1 || h0 != h1) return fail(s, BF_ERR_STATE, "bf_scene_set_receiver: the film size cannot change after bf_scene_commit");
     }
+    const bool light = s->committed && s->has_rx && s->rx.kind == desc->kind && desc->kind != BF_RX_PHASED && s->rx.texture == desc->texture;
     s->rx = *desc; s->has_rx = true;
     s->rx_shape = desc->kind == BF_RX_PERSPECTIVE ? -1 : (int32_t) shape_id;
     uint32_t hdr[2] = {s->rx_shape < 0 ? BF_NONE : shape_id, 0};
@@ -520,6 +535,7 @@ int bf_scene_set_receiver(bf_scene *s, uint32_t shape_id, const bf_endpoint_desc
         s->rx_blob_off = s->blob.size();
         record(s, BF_TAG_RX, hdr, 8, desc, sizeof(*desc));
     }
+    if (light) { if (!s->tables_dirty) s->tables_light = true; } else s->tables_light = false;
     s->tables_dirty = true;
     return BF_OK;
 }
@@ -642,6 +658,8 @@ static int upload_tables(bf_scene *s) {
     for (const Part &pt : parts) total += (pt.bytes + 15) & ~(size_t) 15;
     if (total > s->h_tables_bytes) {
         if (s->h_tables) cudaFreeHost(s->h_tables);
+        if (s->h_ring) cudaFreeHost(s->h_ring);
+        for (cudaEvent_t e : s->ring_ev) if (e) cudaEventDestroy(e);
         s->h_tables = nullptr; s->h_tables_bytes = 0;
         BF_CUDA(cudaMallocHost(&s->h_tables, total * 2));
         s->h_tables_bytes = total * 2;
@@ -677,7 +695,43 @@ static int upload_tables(bf_scene *s) {
         d.tx0_ep = txs[0];
         if (txs[0].shape >= 0) d.tx0_rect = s->rects[s->shapes[txs[0].shape].index];
     }
-    s->tables_dirty = false;
+    s->tables_dirty = false; s->tables_light = false;
+    return BF_OK;
+}
+
+// Light upload: only rectangle poses and / or the (non-phased) receiver descriptor changed since the last upload (the
+// per-frame re-posing of C4 / C5, animated_trans_rad.py:305-355).  Re-stages the rectangle table and the receiver endpoint
+// through the pinned ring and refreshes the copies in the kernel parameter block; nothing else of the scene is touched.
+static int upload_tables_light(bf_scene *s) {
+    DevScene &d = s->dev;
+    const size_t rect_bytes = s->rects.size() * sizeof(DevRect);
+    const size_t need = ((rect_bytes + 15) & ~(size_t) 15) + sizeof(DevEndpoint);
+    if (!s->h_ring || need > s->ring_slot_bytes) {
+        BF_CUDA(cudaStreamSynchronize(s->stream));
+        if (s->h_ring) cudaFreeHost(s->h_ring);
+        s->h_ring = nullptr;
+        BF_CUDA(cudaMallocHost(&s->h_ring, need * 2 * bf_scene::RING));
+        s->ring_slot_bytes = need * 2;
+        for (int i = 0; i < bf_scene::RING; ++i) if (!s->ring_ev[i]) BF_CUDA(cudaEventCreateWithFlags(&s->ring_ev[i], cudaEventDisableTiming));
+    }
+    const int slot = s->ring_next; s->ring_next = (slot + 1) % bf_scene::RING;
+    BF_CUDA(cudaEventSynchronize(s->ring_ev[slot]));      // completed long ago unless RING uploads are in flight
+    uint8_t *h = (uint8_t *) s->h_ring + (size_t) slot * s->ring_slot_bytes;
+    DevEndpoint rx = make_endpoint(s->rx, s->rx_shape);
+    if (rect_bytes) {
+        memcpy(h, s->rects.data(), rect_bytes);
+        BF_CUDA(cudaMemcpyAsync(s->d_rects.p, h, rect_bytes, cudaMemcpyHostToDevice, s->stream));
+    }
+    memcpy(h + ((rect_bytes + 15) & ~(size_t) 15), &rx, sizeof(rx));
+    BF_CUDA(cudaMemcpyAsync(s->d_rx.p, h + ((rect_bytes + 15) & ~(size_t) 15), sizeof(rx), cudaMemcpyHostToDevice, s->stream));
+    BF_CUDA(cudaEventRecord(s->ring_ev[slot], s->stream));
+    if (d.n_nodes != 0) estimate_primary_defer(s);
+    d.rx_needs_aperture = s->rx.kind != BF_RX_PERSPECTIVE;
+    d.rx_ep = rx;
+    memset(&d.rx_rect, 0, sizeof(DevRect));
+    if (s->rx_shape >= 0) d.rx_rect = s->rects[s->shapes[s->rx_shape].index];
+    if (d.n_txs != 0 && d.tx0_ep.shape >= 0) d.tx0_rect = s->rects[s->shapes[d.tx0_ep.shape].index];
+    s->tables_dirty = false; s->tables_light = false;
     return BF_OK;
 }
 
@@ -782,8 +836,8 @@ int bf_scene_commit(bf_scene *s, int device) {
     s->profile_floats = (size_t) s->dev.film_w * s->dev.film_h * s->dev.channels;
     BF_CUDA(s->d_profile.alloc(s->profile_floats));
     BF_CUDA(cudaMemsetAsync(s->d_profile.p, 0, s->profile_floats * 4, s->stream));
-    BF_CUDA(s->d_totals.alloc(2));
-    BF_CUDA(cudaMemsetAsync(s->d_totals.p, 0, 16, s->stream));
+    BF_CUDA(s->d_totals.alloc(4));
+    BF_CUDA(cudaMemsetAsync(s->d_totals.p, 0, 32, s->stream));
     BF_CUDA(cudaEventCreateWithFlags(&s->ev_fork, cudaEventDisableTiming));
     BF_CUDA(cudaStreamSynchronize(s->stream));
     s->stats.upload_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t1).count();
@@ -810,6 +864,7 @@ int bf_scene_update_rect(bf_scene *s, uint32_t shape_id, const float to_world[16
     if (shape_id >= s->shapes.size() || s->shapes[shape_id].type != 1) return fail(s, BF_ERR_INVALID, "bf_scene_update_rect: not a rectangle");
     s->rects[s->shapes[shape_id].index] = make_rect(to_world, shape_id);
     memcpy(s->blob.data() + s->rect_blob_off[s->shapes[shape_id].index] + sizeof(bf_flat_record), to_world, 64);   // keep the export current
+    if (!s->tables_dirty) s->tables_light = true;
     s->tables_dirty = true;
     return BF_OK;
 }
@@ -904,6 +959,13 @@ static int run_wave(bf_scene *s, WaveSlot &sl, uint64_t seed, uint64_t first, ui
         if (timing) { cudaEventRecord(next_trace_event(s, kind), sl.stream); }
     };
     bool path = false;
+    if (fused && s->tune.mega_max >= 0 && (sc.n_nodes == 0 || (int64_t) n <= s->tune.mega_max)) {
+        // scenes without meshes, and small requests on any scene: the whole path of a sample in one thread, one launch
+        timed(BF_K_PRIMARY, [&] { return launch_mega(sc, w, seed, first, n, ctr + 2, profile, cfg); });
+        s->stats.kernel_launches += launches;
+        BF_CUDA(cudaGetLastError());
+        return BF_OK;
+    }
     if (fused) {
         w.n_lanes = ctr + 6;
         // few receiver rays reach the meshes (bf_scene_commit's estimate): k_primary leaves those to a dense k_trace launch
@@ -952,11 +1014,9 @@ static int run_wave(bf_scene *s, WaveSlot &sl, uint64_t seed, uint64_t first, ui
     return BF_OK;
 }
 
-int bf_receive(bf_scene *s, uint64_t seed, uint64_t first_sample, uint64_t n_samples, int accumulate) {
-    if (!s) return BF_ERR_INVALID;
-    if (!s->committed) return fail(s, BF_ERR_STATE, "bf_receive: scene not committed");
+static int receive_into(bf_scene *s, uint64_t seed, uint64_t first_sample, uint64_t n_samples, int accumulate, float *profile) {
     BF_CUDA(cudaSetDevice(s->device));
-    if (s->tables_dirty) { int rc = upload_tables(s); if (rc) return rc; }
+    if (s->tables_dirty) { int rc = (s->tables_light && s->committed) ? upload_tables_light(s) : upload_tables(s); if (rc) return rc; }
     // Wave size: BF_WAVE_LANES when set; otherwise the request is cut into as many waves as there are slots, between 2^22 and
     // 2^25 samples each (larger waves amortise the traversal tails: profiles/r01d_tune_wave.txt)
     const uint64_t streams = (uint64_t) s->tune.wave_streams;
@@ -972,7 +1032,7 @@ int bf_receive(bf_scene *s, uint64_t seed, uint64_t first_sample, uint64_t n_sam
     for (size_t k = 0; k < n_slots; ++k) { int rc = ensure_slot(s, k, lanes, false); if (rc) return rc; }
     s->ev_trace_used = 0;
     BF_CUDA(cudaEventRecord(s->ev_begin, s->stream));
-    if (!accumulate) BF_CUDA(cudaMemsetAsync(s->d_profile.p, 0, s->profile_floats * 4, s->stream));
+    if (!accumulate) BF_CUDA(cudaMemsetAsync(profile, 0, s->profile_floats * 4, s->stream));
     if (n_slots > 1) {
         BF_CUDA(cudaEventRecord(s->ev_fork, s->stream));
         for (size_t k = 1; k < n_slots; ++k) BF_CUDA(cudaStreamWaitEvent(s->slots[k].stream, s->ev_fork, 0));
@@ -980,7 +1040,7 @@ int bf_receive(bf_scene *s, uint64_t seed, uint64_t first_sample, uint64_t n_sam
     uint64_t wave_index = 0;
     for (uint64_t done = 0; done < n_samples; done += lanes, ++wave_index) {
         uint32_t n = (uint32_t) std::min<uint64_t>(lanes, n_samples - done);
-        int rc = run_wave(s, s->slots[wave_index % n_slots], seed, first_sample + done, n, s->d_profile.p, false);
+        int rc = run_wave(s, s->slots[wave_index % n_slots], seed, first_sample + done, n, profile, false);
         if (rc) return rc;
     }
     for (size_t k = 1; k < n_slots; ++k) {
@@ -990,6 +1050,124 @@ int bf_receive(bf_scene *s, uint64_t seed, uint64_t first_sample, uint64_t n_sam
     BF_CUDA(cudaEventRecord(s->ev_end, s->stream));
     s->stats.samples += n_samples;
     return BF_OK;
+}
+
+int bf_receive(bf_scene *s, uint64_t seed, uint64_t first_sample, uint64_t n_samples, int accumulate) {
+    if (!s) return BF_ERR_INVALID;
+    if (!s->committed) return fail(s, BF_ERR_STATE, "bf_receive: scene not committed");
+    return receive_into(s, seed, first_sample, n_samples, accumulate, s->d_profile.p);
+}
+
+// Many receive() calls as ONE submission (C4: the frames of a moving-target sequence; C5: the elements of a receive array --
+// the reference holds std::vector<ref<Receiver>>, scene.h:197, and calls receive() per receiver): item i re-poses the listed
+// rectangles and / or the receiver, then integrates n_samples into ITS OWN profile, slot i of a device-side batch buffer.
+// Nothing synchronises between items (light table uploads through the pinned ring); one copy brings all profiles back.
+int bf_receive_batch(bf_scene *s, uint32_t n_items, const bf_batch_item *items, uint64_t n_samples, float *profiles, size_t n_floats) {
+    if (!s || (n_items && !items)) return BF_ERR_INVALID;
+    if (!s->committed) return fail(s, BF_ERR_STATE, "bf_receive_batch: scene not committed");
+    if (profiles && n_floats < (size_t) n_items * s->profile_floats) return fail(s, BF_ERR_INVALID, "bf_receive_batch: destination too small");
+    BF_CUDA(cudaSetDevice(s->device));
+    BF_CUDA(s->d_batch.alloc((size_t) n_items * s->profile_floats));
+    for (uint32_t i = 0; i < n_items; ++i) {
+        const bf_batch_item &it = items[i];
+        for (uint32_t k = 0; k < it.n_rect_updates; ++k) {
+            int rc = bf_scene_update_rect(s, it.rect_shape_ids[k], it.rect_to_world + 16 * (size_t) k);
+            if (rc) return rc;
+        }
+        if (it.receiver) { int rc = bf_scene_set_receiver(s, it.receiver_shape, it.receiver); if (rc) return rc; }
+        int rc = receive_into(s, it.seed, it.first_sample, n_samples, 0, s->d_batch.p + (size_t) i * s->profile_floats);
+        if (rc) return rc;
+    }
+    s->batch_items = n_items;
+    if (profiles && n_items) {
+        BF_CUDA(cudaMemcpyAsync(profiles, s->d_batch.p, (size_t) n_items * s->profile_floats * 4, cudaMemcpyDeviceToHost, s->stream));
+        BF_CUDA(cudaStreamSynchronize(s->stream));
+    }
+    return BF_OK;
+}
+int bf_batch_device_ptr(bf_scene *s, void **dptr, size_t *n_floats, void **cuda_stream) {
+    if (!s || !s->committed) return BF_ERR_STATE;
+    if (dptr) *dptr = s->d_batch.p;
+    if (n_floats) *n_floats = (size_t) s->batch_items * s->profile_floats;
+    if (cuda_stream) *cuda_stream = (void *) s->stream;
+    return BF_OK;
+}
+
+// ---- multi-GPU: one ncclReduce of the per-rank profiles -----------------------------------------
+// NCCL is bound at run time so that the library has no link-time dependency on it.
+namespace {
+struct NcclId { char internal[128]; };
+struct NcclApi {
+    void *handle = nullptr;
+    int (*GetUniqueId)(NcclId *) = nullptr;
+    int (*CommInitRank)(void **, int, NcclId, int) = nullptr;
+    int (*Reduce)(const void *, void *, size_t, int, int, int, void *, cudaStream_t) = nullptr;
+    int (*CommDestroy)(void *) = nullptr;
+    const char *(*GetErrorString)(int) = nullptr;
+    std::string error;
+};
+NcclApi &nccl_api() {
+    static NcclApi api;
+    if (api.handle || !api.error.empty()) return api;
+    const char *names[] = {getenv("BF_NCCL_LIB"), "libnccl.so.2", "libnccl.so"};
+    for (const char *n : names) {
+        if (!n || !*n) continue;
+        api.handle = dlopen(n, RTLD_NOW | RTLD_GLOBAL);
+        if (api.handle) break;
+        api.error = dlerror();
+    }
+    if (!api.handle) { if (api.error.empty()) api.error = "libnccl.so.2 not found"; return api; }
+    api.GetUniqueId = (decltype(api.GetUniqueId)) dlsym(api.handle, "ncclGetUniqueId");
+    api.CommInitRank = (decltype(api.CommInitRank)) dlsym(api.handle, "ncclCommInitRank");
+    api.Reduce = (decltype(api.Reduce)) dlsym(api.handle, "ncclReduce");
+    api.CommDestroy = (decltype(api.CommDestroy)) dlsym(api.handle, "ncclCommDestroy");
+    api.GetErrorString = (decltype(api.GetErrorString)) dlsym(api.handle, "ncclGetErrorString");
+    if (!api.GetUniqueId || !api.CommInitRank || !api.Reduce || !api.CommDestroy) { api.error = "libnccl: missing symbols"; api.handle = nullptr; }
+    else api.error.clear();
+    return api;
+}
+std::string nccl_err(const NcclApi &api, int rc) { return api.GetErrorString ? api.GetErrorString(rc) : ("nccl error " + std::to_string(rc)); }
+}  // namespace
+
+}  // extern "C"
+static void multi_destroy_comm(void *comm) { if (nccl_api().handle) nccl_api().CommDestroy(comm); }
+extern "C" {
+int bf_multi_unique_id(void *id, size_t capacity) {
+    if (!id || capacity < BF_MULTI_ID_BYTES) return BF_ERR_INVALID;
+    NcclApi &api = nccl_api();
+    if (!api.handle) return fail(nullptr, BF_ERR_UNSUPPORTED, "bf_multi_unique_id: NCCL not available: " + api.error);
+    NcclId nid;
+    int rc = api.GetUniqueId(&nid);
+    if (rc != 0) return fail(nullptr, BF_ERR_CUDA, "ncclGetUniqueId: " + nccl_err(api, rc));
+    memcpy(id, &nid, sizeof(nid));
+    return BF_OK;
+}
+int bf_multi_init(bf_scene *s, int rank, int world, const void *id, size_t id_bytes) {
+    if (!s || !id || id_bytes < BF_MULTI_ID_BYTES || world < 1 || rank < 0 || rank >= world) return BF_ERR_INVALID;
+    if (!s->committed) return fail(s, BF_ERR_STATE, "bf_multi_init: scene not committed");
+    NcclApi &api = nccl_api();
+    if (!api.handle) return fail(s, BF_ERR_UNSUPPORTED, "bf_multi_init: NCCL not available: " + api.error);
+    BF_CUDA(cudaSetDevice(s->device));
+    if (s->nccl_comm) { api.CommDestroy(s->nccl_comm); s->nccl_comm = nullptr; }
+    NcclId nid; memcpy(&nid, id, sizeof(nid));
+    int rc = api.CommInitRank(&s->nccl_comm, world, nid, rank);
+    if (rc != 0) { s->nccl_comm = nullptr; return fail(s, BF_ERR_CUDA, "ncclCommInitRank: " + nccl_err(api, rc)); }
+    return BF_OK;
+}
+int bf_multi_reduce_comm(bf_scene *s, void *nccl_comm, int root) {
+    if (!s || !nccl_comm) return BF_ERR_INVALID;
+    if (!s->committed) return fail(s, BF_ERR_STATE, "bf_multi_reduce: scene not committed");
+    NcclApi &api = nccl_api();
+    if (!api.handle) return fail(s, BF_ERR_UNSUPPORTED, "bf_multi_reduce: NCCL not available: " + api.error);
+    BF_CUDA(cudaSetDevice(s->device));
+    int rc = api.Reduce(s->d_profile.p, s->d_profile.p, s->profile_floats, /* ncclFloat32 */ 7, /* ncclSum */ 0, root, nccl_comm, s->stream);
+    if (rc != 0) return fail(s, BF_ERR_CUDA, "ncclReduce: " + nccl_err(api, rc));
+    return BF_OK;
+}
+int bf_multi_reduce(bf_scene *s, int root) {
+    if (!s) return BF_ERR_INVALID;
+    if (!s->nccl_comm) return fail(s, BF_ERR_STATE, "bf_multi_reduce: bf_multi_init has not been called");
+    return bf_multi_reduce_comm(s, s->nccl_comm, root);
 }
 
 int bf_synchronize(bf_scene *s) {
@@ -1047,7 +1225,7 @@ static int trace_rays_common(bf_scene *s, const float *origins, const float *dir
     if (n_rays == 0) return BF_OK;
     if (n_rays > (1ull << 28)) return fail(s, BF_ERR_INVALID, "trace: too many rays in one call");
     BF_CUDA(cudaSetDevice(s->device));
-    if (s->tables_dirty) { int rc = upload_tables(s); if (rc) return rc; }
+    if (s->tables_dirty) { int rc = (s->tables_light && s->committed) ? upload_tables_light(s) : upload_tables(s); if (rc) return rc; }
     size_t n = (size_t) n_rays;
     std::vector<float4> ho(n), hd(n);
     for (size_t i = 0; i < n; ++i) {
@@ -1113,7 +1291,7 @@ int bf_debug_sample_records(bf_scene *s, uint64_t seed, uint64_t first_sample, u
     if (n_samples == 0) return BF_OK;
     if (n_samples > (1u << 24)) return fail(s, BF_ERR_INVALID, "bf_debug_sample_records: at most 2^24 samples per call");
     BF_CUDA(cudaSetDevice(s->device));
-    if (s->tables_dirty) { int rc = upload_tables(s); if (rc) return rc; }
+    if (s->tables_dirty) { int rc = (s->tables_light && s->committed) ? upload_tables_light(s) : upload_tables(s); if (rc) return rc; }
     int rc = ensure_slot(s, 0, (uint32_t) std::max<uint64_t>(n_samples, 1024), true);
     if (rc) return rc;
     DevBuf<float> scratch;
@@ -1136,10 +1314,11 @@ int bf_get_stats(const bf_scene *s_, bf_stats *stats) {
     if (!s || !stats) return BF_ERR_INVALID;
     if (s->committed) {
         BF_CUDA(cudaSetDevice(s->device));
-        unsigned long long t[2] = {0, 0};
+        unsigned long long t[4] = {0, 0, 0, 0};
         BF_CUDA(cudaStreamSynchronize(s->stream));
-        BF_CUDA(cudaMemcpy(t, s->d_totals.p, 16, cudaMemcpyDeviceToHost));
+        BF_CUDA(cudaMemcpy(t, s->d_totals.p, 32, cudaMemcpyDeviceToHost));
         s->stats.closest_queries = t[0]; s->stats.shadow_queries = t[1];
+        s->stats.path_closest_queries = t[2]; s->stats.path_shadow_queries = t[3];
     }
     *stats = s->stats;
     return BF_OK;
@@ -1152,7 +1331,7 @@ int bf_set_tunable(bf_scene *s, const char *name, int64_t value) {
         {"fused_primary", &s->tune.fused_primary, 0, 1}, {"primary_defer", &s->tune.primary_defer, -1, 1},
         {"trace_defer", &s->tune.trace_defer, -1, 1}, {"trace_rounds", &s->tune.trace_rounds, 0, 1024},
         {"use_graph", &s->tune.use_graph, 0, 1},
-        {"path_fused", &s->tune.path_fused, 0, 1}};
+        {"path_fused", &s->tune.path_fused, 0, 1}, {"mega_max", &s->tune.mega_max, -1, 1ll << 28}};
     for (auto &t : table)
         if (strcmp(t.n, name) == 0) {
             if (value < t.lo || value > t.hi) return fail(s, BF_ERR_INVALID, std::string("bf_set_tunable: value out of range for ") + name);

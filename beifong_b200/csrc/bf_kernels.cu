@@ -764,6 +764,63 @@ __device__ __forceinline__ Splat finalize_lane(const DevScene &sc, const Wave &w
 // shared atomics), the two count channels (alpha, weight) are accumulated as integers with native shared atomics and
 // converted at the flush, which is one global atomic per non-zero entry.  Otherwise samples go to HBM directly, as one
 // 128-bit reduction per sample when a pixel is four channels wide.
+// SignalBlock::put of the samples of one converged warp (box filter).  When all the lanes that land in the film land in ONE
+// bin (1 x 1 films: every warp) their counts and values are summed in registers first; otherwise one set of atomics per lane.
+// SMEM: dst is a shared-memory copy of the profile whose count channels hold integers.
+template <bool SMEM>
+__device__ __forceinline__ void scatter_warp(const Splat &sp, float *dst, uint32_t C, uint32_t n_fixed) {
+    const int pixel = sp.pixel;
+    const uint32_t in_film = __ballot_sync(0xffffffffu, pixel >= 0);
+    if (in_film == 0) return;
+    const int pixel0 = __shfl_sync(0xffffffffu, pixel, __ffs(in_film) - 1);
+    const bool one_pixel = __all_sync(0xffffffffu, pixel < 0 || pixel == pixel0) && (in_film & (in_film - 1));
+    if (one_pixel) {
+        const uint32_t nv = __popc(__ballot_sync(0xffffffffu, pixel >= 0 && sp.cnt_valid));
+        if (lane_id() == (uint32_t) (__ffs(in_film) - 1)) {
+            float *px = dst + (size_t) C * pixel;
+            if (SMEM) {
+                atomicAdd(reinterpret_cast<uint32_t *>(px + n_fixed - 1), (uint32_t) __popc(in_film));
+                if (nv) atomicAdd(reinterpret_cast<uint32_t *>(px + n_fixed - 2), nv);
+            } else {
+                atomicAdd(px + n_fixed - 1, (float) __popc(in_film));
+                if (nv) atomicAdd(px + n_fixed - 2, (float) nv);
+            }
+        }
+        agg_add(dst, pixel >= 0 ? pixel * (int) C : -1, sp.val_a, n_fixed - 2);   // gen 3: Y; gen 1/2: X = Y = Z
+        agg_add(dst, (pixel >= 0 && sp.var_ch >= 0) ? pixel * (int) C + sp.var_ch : -1, sp.var_val, sp.var_rep);
+        return;
+    }
+    if (pixel < 0) return;
+    float *px = dst + (size_t) C * pixel;
+    if (SMEM) {
+        atomicAdd(reinterpret_cast<uint32_t *>(px + n_fixed - 1), 1u);
+        if (sp.cnt_valid) atomicAdd(reinterpret_cast<uint32_t *>(px + n_fixed - 2), 1u);
+        if (sp.val_a != 0.f)
+            for (uint32_t r = 0; r < n_fixed - 2; ++r) atomicAdd(px + r, sp.val_a);
+        if (sp.var_ch >= 0 && sp.var_val != 0.f)
+            for (uint32_t r = 0; r < sp.var_rep; ++r) atomicAdd(px + sp.var_ch + r, sp.var_val);
+    } else if (C == 4 && n_fixed == 3) {
+        // gen 3, one phase bin: (Y, A, W, P0) is one aligned 16-byte record
+        atomicAdd(reinterpret_cast<float4 *>(px), make_float4(sp.val_a, sp.cnt_valid ? 1.f : 0.f, 1.f, sp.var_ch >= 0 ? sp.var_val : 0.f));
+    } else {
+        atomicAdd(px + n_fixed - 1, 1.f);
+        if (sp.cnt_valid) atomicAdd(px + n_fixed - 2, 1.f);
+        if (sp.val_a != 0.f)
+            for (uint32_t r = 0; r < n_fixed - 2; ++r) atomicAdd(px + r, sp.val_a);
+        if (sp.var_ch >= 0 && sp.var_val != 0.f)
+            for (uint32_t r = 0; r < sp.var_rep; ++r) atomicAdd(px + sp.var_ch + r, sp.var_val);
+    }
+}
+// flush of a shared-memory profile copy: one global atomic per non-zero entry
+__device__ __forceinline__ void flush_hist(const float *s_hist, uint32_t total_floats, uint32_t C, uint32_t n_fixed, float *profile) {
+    for (uint32_t i = threadIdx.x; i < total_floats; i += blockDim.x) {
+        const uint32_t ch = i % C;
+        const bool is_count = ch == n_fixed - 1 || ch == n_fixed - 2;
+        const float v = is_count ? (float) __float_as_uint(s_hist[i]) : s_hist[i];
+        if (v != 0.f) atomicAdd(profile + i, v);
+    }
+}
+
 template <int S, bool SMEM>
 __global__ void __launch_bounds__(FIN_THREADS) k_finalize(const __grid_constant__ DevScene sc, const __grid_constant__ Wave w, uint32_t n,
                                                          float *__restrict__ profile) {
@@ -781,61 +838,114 @@ __global__ void __launch_bounds__(FIN_THREADS) k_finalize(const __grid_constant_
     for (uint32_t l = blockIdx.x * blockDim.x + threadIdx.x; l < n_round; l += stride) {
         Splat sp; sp.pixel = -1; sp.val_a = 0.f; sp.cnt_valid = false; sp.var_ch = -1; sp.var_val = 0.f; sp.var_rep = 1;
         if (l < n) sp = finalize_lane<S>(sc, w, l);
-        const int pixel = sp.pixel;
-        // do all the lanes of the warp that land in the film land in one pixel?  (1x1 films: every warp)
-        const uint32_t in_film = __ballot_sync(0xffffffffu, pixel >= 0);
-        if (in_film == 0) continue;
-        const int pixel0 = __shfl_sync(0xffffffffu, pixel, __ffs(in_film) - 1);
-        const bool one_pixel = __all_sync(0xffffffffu, pixel < 0 || pixel == pixel0) && (in_film & (in_film - 1));
-        if (one_pixel) {
-            float *dst = SMEM ? s_hist : profile;
-            const uint32_t nv = __popc(__ballot_sync(0xffffffffu, pixel >= 0 && sp.cnt_valid));
-            if (lane_id() == (uint32_t) (__ffs(in_film) - 1)) {
-                float *px = dst + (size_t) C * pixel;
-                if (SMEM) {
-                    atomicAdd(reinterpret_cast<uint32_t *>(px + n_fixed - 1), (uint32_t) __popc(in_film));
-                    if (nv) atomicAdd(reinterpret_cast<uint32_t *>(px + n_fixed - 2), nv);
-                } else {
-                    atomicAdd(px + n_fixed - 1, (float) __popc(in_film));
-                    if (nv) atomicAdd(px + n_fixed - 2, (float) nv);
-                }
-            }
-            agg_add(dst, pixel >= 0 ? pixel * (int) C : -1, sp.val_a, n_fixed - 2);   // gen 3: Y; gen 1/2: X = Y = Z
-            agg_add(dst, (pixel >= 0 && sp.var_ch >= 0) ? pixel * (int) C + sp.var_ch : -1, sp.var_val, sp.var_rep);
-            continue;
-        }
-        if (pixel < 0) continue;
-        if (SMEM) {
-            float *px = s_hist + (size_t) C * pixel;
-            atomicAdd(reinterpret_cast<uint32_t *>(px + n_fixed - 1), 1u);
-            if (sp.cnt_valid) atomicAdd(reinterpret_cast<uint32_t *>(px + n_fixed - 2), 1u);
-            if (sp.val_a != 0.f)
-                for (uint32_t r = 0; r < n_fixed - 2; ++r) atomicAdd(px + r, sp.val_a);
-            if (sp.var_ch >= 0 && sp.var_val != 0.f)
-                for (uint32_t r = 0; r < sp.var_rep; ++r) atomicAdd(px + sp.var_ch + r, sp.var_val);
-        } else {
-            float *px = profile + (size_t) C * pixel;
-            if (C == 4 && n_fixed == 3) {
-                // gen 3, one phase bin: (Y, A, W, P0) is one aligned 16-byte record
-                atomicAdd(reinterpret_cast<float4 *>(px), make_float4(sp.val_a, sp.cnt_valid ? 1.f : 0.f, 1.f, sp.var_ch >= 0 ? sp.var_val : 0.f));
-            } else {
-                atomicAdd(px + n_fixed - 1, 1.f);
-                if (sp.cnt_valid) atomicAdd(px + n_fixed - 2, 1.f);
-                if (sp.val_a != 0.f)
-                    for (uint32_t r = 0; r < n_fixed - 2; ++r) atomicAdd(px + r, sp.val_a);
-                if (sp.var_ch >= 0 && sp.var_val != 0.f)
-                    for (uint32_t r = 0; r < sp.var_rep; ++r) atomicAdd(px + sp.var_ch + r, sp.var_val);
-            }
-        }
+        scatter_warp<SMEM>(sp, SMEM ? s_hist : profile, C, n_fixed);
     }
     if (SMEM) {
         __syncthreads();
-        for (uint32_t i = threadIdx.x; i < total_floats; i += blockDim.x) {
-            const uint32_t ch = i % C;
-            const bool is_count = ch == n_fixed - 1 || ch == n_fixed - 2;
-            const float v = is_count ? (float) __float_as_uint(s_hist[i]) : s_hist[i];
-            if (v != 0.f) atomicAdd(profile + i, v);
+        flush_hist(s_hist, total_floats, C, n_fixed, profile);
+    }
+}
+
+// =========================================================================================================
+// mega: one sample = one thread, start to end
+// =========================================================================================================
+// The whole path of a sample in one thread: receiver ray, then per depth a closest-hit query (rectangles + BVH), one shade step
+// (shade_core, the generic instantiation), the shadow query, until the path ends; then the binning (finalize_core).  Nothing
+// is written to HBM but the profile.  Two uses, both latency-bound, where one launch beats the ~17 of the wavefront:
+//   * scenes without meshes (C1 trans_rad.xml, C4 animated_trans_rad.py: three rectangles), at any size;
+//   * small receive() calls on any scene (the reference's drivers use 1 000 - 65 536 samples per call).
+// Same arithmetic as the wavefront sequence (records bit-identical: tests/test_gpu_parity.py::test_mega_kernel_equals_wavefront).
+#define MEGA_THREADS 128
+struct MegaIO {
+    uint64_t seed, first_sample;
+    uint32_t n;
+    uint32_t *work_cursor;
+    unsigned long long *totals;
+    float *profile;
+    uint32_t hist_floats;
+};
+template <int S>
+__global__ void __launch_bounds__(MEGA_THREADS) k_mega(const __grid_constant__ DevScene sc, const __grid_constant__ Wave w, const __grid_constant__ MegaIO io) {
+    extern __shared__ __align__(16) uint32_t mega_smem[];
+    float *s_rect = reinterpret_cast<float *>(mega_smem);
+    uint2 *s_stack = reinterpret_cast<uint2 *>(mega_smem + RECT_SM_FLOATS * BF_MAX_RECTS);
+    float *s_hist = reinterpret_cast<float *>(s_stack + TRACE_SM_STACK * MEGA_THREADS);
+    uint2 l_stack[TRACE_LOCAL_STACK];
+    static_assert(MEGA_THREADS == TRACE_THREADS, "trace_step indexes the shared-memory stack with TRACE_THREADS");
+    const uint32_t C = sc.channels, n_fixed = sc.integ.gen == BF_GEN_PHASE ? 3u : 5u;
+    const bool hist = io.hist_floats != 0u;
+    if (hist) for (uint32_t i = threadIdx.x; i < io.hist_floats; i += blockDim.x) s_hist[i] = 0.f;
+    stage_rects(sc, s_rect);
+    const uint32_t lane = threadIdx.x & 31u;
+    const uint32_t gen = sc.integ.gen;
+    uint32_t q_closest = 0, q_shadow = 0;
+    while (true) {
+        uint32_t base = 0;
+        if (lane == 0) base = atomicAdd(io.work_cursor, 32u);
+        base = __shfl_sync(0xffffffffu, base, 0);
+        if (base >= io.n) break;
+        const uint32_t i = base + lane;
+        const bool have = i < io.n;
+        PrimaryState<S> ps;
+        LaneRegs<S> R;
+        bf_sample_record *rec = (w.records && have) ? w.records + i : nullptr;
+        V3 ro(0.f, 0.f, 0.f), rd(0.f, 0.f, 1.f);
+        float mint = 0.f, maxt = 0.f;
+        bool alive = have;
+        if (have) {
+            raygen_sample<S>(sc, io.seed, io.first_sample + i, ps);
+            ro = ps.ray.o; rd = ps.ray.d; mint = ps.ray.mint; maxt = ps.ray.maxt;
+            R.flags = LANE_ACTIVE; R.rng = ps.rng;
+            R.thr = Spec<S>(1.f); R.res = Spec<S>(0.f); R.pend = Spec<S>(0.f); R.wl = ps.wl;
+            R.time = ps.time; R.phase = 0.f; R.bs_pdf = 0.f; R.scalar = 0.f;
+            if (rec) init_record(rec, ps.wl.v[0]);
         }
+        for (uint32_t depth = 1; alive; ++depth) {
+            TraceLane L; L.o = ro; L.d = rd; L.mint = mint; L.maxt = maxt;
+            if (trace_begin<false>(sc, s_rect, L)) { while (trace_step<false>(sc, s_stack, l_stack, L)) { } }
+            ++q_closest;
+            if (L.best.slot == BF_NONE) {
+                // the miss branch of the integrator loop (pathtimefrequency.cpp:368-371 with t = inf): see k_trace
+                if (depth > 1 && gen == BF_GEN_PHASE) { R.time = -bf_inf(); R.phase = -bf_inf(); }
+                if (rec) rec->depth = depth;
+                break;
+            }
+            R.o = ro; R.d = rd; R.hit = make_float4(L.best.t, L.best.u, L.best.v, __uint_as_float(L.best.slot));
+            ShadeOut so;
+            shade_core<S, -1, -1, -1>(sc, depth, R, rec, so);
+            if (so.push_shadow) {
+                TraceLane T; T.o = so.origin; T.d = so.sh_d; T.mint = so.mint; T.maxt = so.sh_maxt;
+                if (trace_begin<true>(sc, s_rect, T)) { while (trace_step<true>(sc, s_stack, l_stack, T)) { } }
+                ++q_shadow;
+                if (!T.occluded) {
+#pragma unroll
+                    for (int k = 0; k < S; ++k) R.res.v[k] += R.pend.v[k];
+                }
+                R.flags &= ~LANE_PENDING;
+            }
+            if (!so.push_next || depth >= BF_MAX_BOUNCES) break;
+            ro = so.origin; rd = so.new_d; mint = so.mint; maxt = bf_inf();
+        }
+        Splat sp; sp.pixel = -1; sp.val_a = 0.f; sp.cnt_valid = false; sp.var_ch = -1; sp.var_val = 0.f; sp.var_rep = 1;
+        if (have) {
+            float4 x2 = ps.x2;
+            sp = finalize_core<S>(sc, R.flags, R.phase, R.scalar, x2, R.res, R.wl, ps.weight, rec);
+        }
+        __syncwarp();
+        if (hist) scatter_warp<true>(sp, s_hist, C, n_fixed); else scatter_warp<false>(sp, io.profile, C, n_fixed);
+    }
+    {
+        uint32_t qc = q_closest, qs = q_shadow;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) { qc += __shfl_xor_sync(0xffffffffu, qc, o); qs += __shfl_xor_sync(0xffffffffu, qs, o); }
+        if (lane == 0 && io.totals) {
+            if (qc) atomicAdd(io.totals + 0, (unsigned long long) qc);
+            if (qs) atomicAdd(io.totals + 1, (unsigned long long) qs);
+        }
+    }
+    if (hist) {
+        __syncthreads();
+        flush_hist(s_hist, io.hist_floats, C, n_fixed, io.profile);
     }
 }
 
@@ -876,7 +986,7 @@ struct PathIO {
     uint32_t n;
     uint32_t *work_cursor;
     uint32_t *n_lanes;                        // lanes handed out to spilled samples
-    unsigned long long *totals;               // [0] closest, [1] shadow queries decided here
+    unsigned long long *totals;               // [0] closest, [1] shadow queries (all kernels); [2], [3] the ones decided here
     float *profile;
     uint32_t *defer_queue, *defer_count;      // receiver rays that enter the mesh bounds
     uint32_t *hit_count;                      // [2]: class queues of shade(1) (w.queue_h / w.queue_h2)
@@ -1139,18 +1249,13 @@ __global__ void __launch_bounds__(PATH_THREADS, 1) k_path(const __grid_constant_
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) { qc += __shfl_xor_sync(0xffffffffu, qc, o); qs += __shfl_xor_sync(0xffffffffu, qs, o); }
         if (lane == 0 && io.totals) {
-            if (qc) atomicAdd(io.totals + 0, (unsigned long long) qc);
-            if (qs) atomicAdd(io.totals + 1, (unsigned long long) qs);
+            if (qc) { atomicAdd(io.totals + 0, (unsigned long long) qc); atomicAdd(io.totals + 2, (unsigned long long) qc); }
+            if (qs) { atomicAdd(io.totals + 1, (unsigned long long) qs); atomicAdd(io.totals + 3, (unsigned long long) qs); }
         }
     }
     if (hist) {
         __syncthreads();
-        for (uint32_t i = threadIdx.x; i < io.hist_floats; i += blockDim.x) {
-            const uint32_t ch = i % C;
-            const bool is_count = ch == C_FIXED - 1u || ch == C_FIXED - 2u;
-            const float v = is_count ? (float) __float_as_uint(s_hist[i]) : s_hist[i];
-            if (v != 0.f) atomicAdd(io.profile + i, v);
-        }
+        flush_hist(s_hist, io.hist_floats, C, C_FIXED, io.profile);
     }
 }
 
@@ -1332,6 +1437,20 @@ int launch_path(const DevScene &sc, const Wave &w, uint64_t seed, uint64_t first
     return 1;
 }
 
+int launch_mega(const DevScene &sc, const Wave &w, uint64_t seed, uint64_t first_sample, uint32_t n, uint32_t *work_cursor, float *profile,
+                const LaunchCfg &cfg) {
+    if (n == 0) return 0;
+    MegaIO io;
+    io.seed = seed; io.first_sample = first_sample; io.n = n; io.work_cursor = work_cursor; io.totals = w.totals; io.profile = profile;
+    const uint32_t floats = sc.channels * sc.film_w * sc.film_h;
+    io.hist_floats = floats <= 4096u ? floats : 0u;
+    const size_t smem = ((size_t) RECT_SM_FLOATS * BF_MAX_RECTS + 2 * TRACE_SM_STACK * MEGA_THREADS + io.hist_floats) * 4;
+    // one warp per 32 samples up to a full machine; small requests get a small grid (and a small flush)
+    const int grid = (int) std::min<uint32_t>((uint32_t) cfg.sm_count * 4u, (n + MEGA_THREADS - 1) / MEGA_THREADS);
+    if (sc.S == 1) k_mega<1><<<grid, MEGA_THREADS, smem, cfg.stream>>>(sc, w, io);
+    else k_mega<4><<<grid, MEGA_THREADS, smem, cfg.stream>>>(sc, w, io);
+    return 1;
+}
 int launch_trace_rays(const DevScene &sc, const float4 *ray_o, const float4 *ray_d, uint32_t n, float4 *hit, uint32_t *occl,
                       uint32_t *work_cursor, const LaunchCfg &cfg) {
     if (n == 0) return 0;

@@ -65,6 +65,9 @@ bool path_kernel_available(const DevScene &sc);
 size_t path_stash_bytes(const DevScene &sc, int sm_count);     // per wave slot: the CTAs' parking areas
 int launch_path(const DevScene &sc, const Wave &w, uint64_t seed, uint64_t first_sample, uint32_t n, uint32_t *ctr, float *profile,
                 uint32_t *defer_queue, uint32_t *stash, const LaunchCfg &cfg);
+// k_mega: one thread carries one sample from the receiver ray to its bin (scenes without meshes; small requests)
+int launch_mega(const DevScene &sc, const Wave &w, uint64_t seed, uint64_t first_sample, uint32_t n, uint32_t *work_cursor, float *profile,
+                const LaunchCfg &cfg);
 int launch_raygen(const DevScene &sc, const Wave &w, uint64_t seed, uint64_t first_sample, uint32_t n, const LaunchCfg &cfg);
 // queue == nullptr: lanes [0, n_direct); else lane ids from queue[0 .. *count)
 // depth = the shade iteration this trace feeds; lanes that hit are appended to w.queue_h / *hit_count

@@ -54,16 +54,33 @@ class DeviceProfile:
         return torch.cuda.ExternalStream(self.stream_ptr, device=device)
 
 
-def receive_sharded(scene, n_total, seed, rank, world, accumulate=False, profile_tensor=None, stream=None, dst=0):
+def init_native_reduce(scene, rank, world):
+    """Create the library's own NCCL communicator for `scene` (bf_multi_init).  The 128-byte unique id travels through
+    the already initialised torch.distributed group (host-side plumbing only); the reduce itself is bf_multi_reduce."""
+    import torch.distributed as dist
+    box = [scene.multi_unique_id() if rank == 0 else None]
+    dist.broadcast_object_list(box, src=0)
+    scene.multi_init(rank, world, box[0])
+
+
+def receive_sharded(scene, n_total, seed, rank, world, accumulate=False, profile_tensor=None, stream=None, dst=0, native=False):
     """One sharded frame: this rank's slice of the sample range through bf_receive, then the single reduce, issued
-    on the scene's stream so that it follows the last wavefront without a host sync."""
+    on the scene's stream so that it follows the last wavefront without a host sync.
+    native=True: the reduce is bf_multi_reduce (after init_native_reduce); otherwise torch.distributed on profile_tensor.
+    accumulate=True: rank `dst` keeps the running total; the reduce is in place, so every other rank clears its partial sum
+    after it has been reduced (otherwise the next reduce would add it a second time)."""
     first, n = shard_samples(n_total, rank, world)
     if n > 0:
         scene.receive(n, seed=seed, first_sample=first, accumulate=accumulate)
     elif not accumulate:
         scene.receive(0, seed=seed, first_sample=first, accumulate=False)
-    if world > 1 and profile_tensor is not None:
-        import torch
-        with torch.cuda.stream(stream):
-            reduce_profile(profile_tensor, dst=dst)
+    if world > 1:
+        if native:
+            scene.multi_reduce(dst)
+        elif profile_tensor is not None:
+            import torch
+            with torch.cuda.stream(stream):
+                reduce_profile(profile_tensor, dst=dst)
+        if accumulate and rank != dst and (native or profile_tensor is not None):
+            scene.receive(0, seed=seed, first_sample=first, accumulate=False)      # clear: stream-ordered behind the reduce
     return first, n

@@ -207,8 +207,54 @@ class FlatScene:
     def receive(self, n_samples, seed=0, first_sample=0, accumulate=False):
         self._ck(N.lib().bf_receive(self._h, seed, first_sample, n_samples, int(accumulate)), "bf_receive")
 
+    def receive_batch(self, items, n_samples, read=True):
+        """bf_receive_batch: `items` is a list of dicts with keys seed, first_sample (default 0), rects = [(shape_id, to_world 4x4), ...]
+        (default none) and receiver = (shape_id_or_None, bf_endpoint_desc) (default: keep).  Returns the item profiles as an array
+        [item][f][t][channel] (read=True, synchronises) or None (read=False: asynchronous, the profiles stay on the device)."""
+        n = len(items)
+        arr = (N.bf_batch_item * max(n, 1))()
+        keep = []     # ctypes buffers must outlive the call
+        for i, it in enumerate(items):
+            arr[i].seed = int(it.get("seed", 0)); arr[i].first_sample = int(it.get("first_sample", 0))
+            rects = it.get("rects") or []
+            arr[i].n_rect_updates = len(rects)
+            if rects:
+                ids = (N.u32 * len(rects))(*[int(r[0]) for r in rects])
+                mats = np.ascontiguousarray(np.stack([_f32(r[1]).reshape(16) for r in rects]))
+                keep += [ids, mats]
+                arr[i].rect_shape_ids = ids
+                arr[i].rect_to_world = mats.ctypes.data_as(C.POINTER(N.f32))
+            rx = it.get("receiver")
+            if rx is not None:
+                arr[i].receiver_shape = N.BF_NONE if rx[0] is None else int(rx[0])
+                keep.append(rx[1])
+                arr[i].receiver = C.pointer(rx[1])
+        shape = self.profile_shape()
+        out = np.empty((n,) + tuple(shape), dtype=np.float32) if read else None
+        self._ck(N.lib().bf_receive_batch(self._h, n, arr, int(n_samples), _fp(out) if read else None, out.size if read else 0), "bf_receive_batch")
+        return out
+
     def synchronize(self):
         self._ck(N.lib().bf_synchronize(self._h), "bf_synchronize")
+
+    # ---- multi-GPU through the C ABI (NCCL bound inside the library, no torch on the data path) ----
+    @staticmethod
+    def multi_unique_id():
+        """Rank 0: a fresh NCCL unique id (bytes) to ship to the other ranks by any means."""
+        buf = C.create_string_buffer(128)
+        rc = N.lib().bf_multi_unique_id(buf, 128)
+        if rc != 0:
+            err = N.lib().bf_last_error(None)
+            raise RuntimeError(f"bf_multi_unique_id failed ({rc}): {err.decode() if err else ''}")
+        return buf.raw
+
+    def multi_init(self, rank, world, unique_id):
+        buf = C.create_string_buffer(bytes(unique_id), 128)
+        self._ck(N.lib().bf_multi_init(self._h, int(rank), int(world), buf, 128), "bf_multi_init")
+
+    def multi_reduce(self, root=0):
+        """One ncclReduce of the per-rank profiles onto `root`, in place, on the scene's stream."""
+        self._ck(N.lib().bf_multi_reduce(self._h, int(root)), "bf_multi_reduce")
 
     def profile(self, out=None):
         shape = self.profile_shape()

@@ -188,6 +188,8 @@ typedef struct bf_stats {
     uint64_t kernel_launches;  /* kernels launched by this library */
     uint32_t bvh_nodes, bvh_tris, bvh_depth, n_rects;
     double build_ms, upload_ms;
+    uint64_t path_closest_queries; /* of closest_queries / shadow_queries: decided inside k_path (rectangles + mesh bounds, */
+    uint64_t path_shadow_queries;  /* no traversal launch) */
 } bf_stats;
 
 uint32_t bf_abi_version(void);
@@ -243,6 +245,25 @@ int bf_profile_size(const bf_scene *s, uint32_t *width, uint32_t *height, uint32
  * Asynchronous on the scene's stream. */
 int bf_receive(bf_scene *s, uint64_t seed, uint64_t first_sample, uint64_t n_samples,
                int accumulate);
+/* Many receive() calls as one submission: the frames of a moving-target sequence (python_scripts/animated_trans_rad.py:289-311
+ * re-poses the antennas and calls the integrator once per frame) or the receivers of a scene (include/mitsuba/render/scene.h:197
+ * holds std::vector<ref<Receiver>>; Receive.ipynb loops over them).  Item i first re-poses the listed rectangles
+ * (bf_scene_update_rect) and / or replaces the receiver (bf_scene_set_receiver), then integrates sample indices
+ * [first_sample, first_sample + n_samples) with its seed into profile i of a device-side batch buffer.  No host
+ * synchronisation between items.  profiles != NULL: all item profiles are copied to it ([item][f][t][channel], n_floats >=
+ * n_items * profile floats) and the stream is synchronised; NULL: asynchronous, read them through bf_batch_device_ptr.
+ * The scene is left in the state of the last item. */
+typedef struct bf_batch_item {
+    uint64_t seed, first_sample;
+    uint32_t n_rect_updates;          /* rectangles re-posed before this item */
+    uint32_t receiver_shape;          /* shape the new receiver is attached to (BF_NONE: free standing); used if receiver != NULL */
+    const uint32_t *rect_shape_ids;   /* [n_rect_updates] */
+    const float *rect_to_world;       /* [n_rect_updates][16], row major */
+    const bf_endpoint_desc *receiver; /* NULL: keep the current receiver */
+} bf_batch_item;
+int bf_receive_batch(bf_scene *s, uint32_t n_items, const bf_batch_item *items, uint64_t n_samples,
+                     float *profiles, size_t n_floats);
+int bf_batch_device_ptr(bf_scene *s, void **dptr, size_t *n_floats, void **cuda_stream);
 /* HDRADC::bitmap(raw=true) (hdradc.cpp:219-233): [f][t][channel] fp32, un-normalised.
  * Synchronises the scene's stream. */
 int bf_profile_read(bf_scene *s, float *dst, size_t n_floats);
@@ -259,6 +280,21 @@ int bf_profile_develop(bf_scene *s, uint32_t component_format, void *dst, size_t
  * that reduces it with NCCL, §8e). */
 int bf_profile_device_ptr(bf_scene *s, void **dptr, size_t *n_floats, void **cuda_stream);
 int bf_synchronize(bf_scene *s);
+
+/* Multi-GPU (the reference has no equivalent): one process or thread per GPU, the scene replicated, sample
+ * indices sharded by the caller (disjoint [first_sample, first_sample + n) per rank), then ONE ncclReduce of the per-rank
+ * profiles onto `root`, in place, on the scene's stream behind the last wavefront (no host synchronisation).  NCCL is
+ * loaded at run time (dlopen "libnccl.so.2"; BF_ERR_UNSUPPORTED with the loader's message when it is absent).
+ *   bf_multi_unique_id   rank 0: ncclGetUniqueId into id (capacity >= BF_MULTI_ID_BYTES); the caller ships the bytes to the others
+ *   bf_multi_init        every rank, after bf_scene_commit: ncclCommInitRank on the scene's device (blocks until all ranks joined)
+ *   bf_multi_reduce      ncclReduce(profile, profile, n_floats, ncclFloat32, ncclSum, root) with the communicator of bf_multi_init
+ *   bf_multi_reduce_comm the same with a caller-owned ncclComm_t (a host that already has one, e.g. torch.distributed's)
+ * fp32 summation order differs from a single-GPU run: multi-GPU parity is <= 1e-3 relative L2, not bitwise. */
+#define BF_MULTI_ID_BYTES 128
+int bf_multi_unique_id(void *id, size_t capacity);
+int bf_multi_init(bf_scene *s, int rank, int world, const void *id, size_t id_bytes);
+int bf_multi_reduce(bf_scene *s, int root);
+int bf_multi_reduce_comm(bf_scene *s, void *nccl_comm, int root);
 
 /* Parity / measurement hooks */
 /* Scene::ray_intersect_preliminary (scene.cpp:150-156) for caller-provided rays. */

@@ -220,6 +220,52 @@ def test_path_kernel_equals_wavefront(native, width, kw):
         s.close()
 
 
+@pytest.mark.parametrize("case", ["radar1", "radar4", "radar_frame", "radar_unbounded", "phased", "c1", "c1_w4", "c4"])
+def test_mega_kernel_equals_wavefront(native, case):
+    """k_mega (one thread carries one sample from the receiver ray to its bin: scenes without meshes and small requests run as ONE
+    launch) against the wavefront sequence: per-sample records bit-identical, count channels identical, value channels equal up to
+    the order of the atomic adds, same ray-query totals -- on a mesh scene (BVH traversal inside the thread), a 2-D frame, unbounded
+    depth with russian roulette, phased endpoints, and the rectangle-only scenes of configs C1 (gen 1) and C4 (gen 2)."""
+    if case == "radar1":
+        s = configs.small_radar(spectrum_width=1)
+    elif case == "radar4":
+        s = configs.small_radar(spectrum_width=4)
+    elif case == "radar_frame":
+        s = configs.small_radar(spectrum_width=1)
+        s.set_adc(t_bins=64, f_bins=256, t_bandwidth=200e-6, f_bandwidth=256 * 0.12 * 2.0 / configs.C0 * (6e9 / 200e-6))
+    elif case == "radar_unbounded":
+        s = configs.small_radar(spectrum_width=1, max_depth=-1, variant=dict(rr_depth=2))
+    elif case == "phased":
+        s = configs.small_radar(spectrum_width=1, phased=dict(n_elems=2, steer=(0.0, 0.2, 0.0)))
+    elif case == "c1":
+        s = configs.c1_trans_rad(spectrum_width=1)
+    elif case == "c1_w4":
+        s = configs.c1_trans_rad(spectrum_width=4)
+    else:
+        s, _ = configs.c4_animated(frame=17)
+    s.commit()
+    out = {}
+    for mode in (-1, 1 << 28):
+        s.set_tunable("mega_max", mode)
+        before = s.stats()
+        rec = s.sample_records(30000, seed=5)
+        s.receive((1 << 16) + 33, seed=6)
+        prof = s.profile()
+        after = s.stats()
+        out[mode] = (rec, prof, after["closest_queries"] - before["closest_queries"], after["shadow_queries"] - before["shadow_queries"],
+                     after["kernel_launches"] - before["kernel_launches"])
+    a, b = out[-1], out[1 << 28]
+    assert b[4] == 2 and a[4] > 2                      # one launch per call
+    assert a[0].tobytes() == b[0].tobytes()
+    w_ch = 2 if a[1].shape[2] < 5 or case.startswith("radar") or case == "phased" else 4
+    assert np.array_equal(a[1][..., w_ch - 1:w_ch + 1], b[1][..., w_ch - 1:w_ch + 1])
+    fin = np.isfinite(a[1]) & np.isfinite(b[1])
+    assert np.array_equal(np.isfinite(a[1]), np.isfinite(b[1]))
+    assert np.abs(a[1][fin] - b[1][fin]).max() <= 1e-5 * max(np.abs(a[1][fin]).max(), 1e-30)
+    assert a[2] == b[2] and a[3] == b[3]
+    s.close()
+
+
 def test_range_time_frame_global_scatter(native):
     """A 64 x 256 (time x beat-frequency) frame does not fit the shared-memory histograms: samples are scattered to HBM
     directly (one 128-bit reduction per sample in k_finalize, weight-channel adds for the misses in k_primary)."""
@@ -285,6 +331,49 @@ def test_c4_sequence_moves_endpoints(native):
         assert np.array_equal(moved[0, 0, 3:5], fresh[0, 0, 3:5])
         assert fresh[0, 0, 5:].sum() > 0
         assert rel_l2(moved[0, 0, 5:], fresh[0, 0, 5:]) <= 1e-5
+    s.close()
+
+
+def test_receive_batch_equals_frame_loop(native):
+    """bf_receive_batch (the frames of the moving-target sequence as one submission, per-item profiles, no host synchronisation
+    between items) against one bf_receive + bf_profile_read per frame on a scene built from scratch for that frame."""
+    s, tx = configs.c4_animated(frame=0)
+    s.commit()
+    frames, n = [3, 64, 65, 200, 255], 4000
+    items = []
+    for f in frames:
+        pose = configs.c4_pose(f)
+        items.append(dict(seed=f, rects=[(tx, (pose * meshes.Transform.scale([0.5, 0.5, 1.0])).matrix32())], receiver=(None, configs.c4_receiver(pose))))
+    got = s.receive_batch(items, n)
+    assert got.shape[0] == len(frames)
+    for k, f in enumerate(frames):
+        fresh_scene, _ = configs.c4_animated(frame=f)
+        fresh_scene.commit()
+        fresh_scene.receive(n, seed=f)
+        fresh = fresh_scene.profile()
+        fresh_scene.close()
+        assert np.array_equal(got[k][0, 0, 3:5], fresh[0, 0, 3:5])
+        assert fresh[0, 0, 5:].sum() > 0
+        assert rel_l2(got[k][0, 0, 5:], fresh[0, 0, 5:]) <= 1e-5 and rel_l2(got[k][0, 0, :3], fresh[0, 0, :3]) <= 1e-5
+    # the same items again, asynchronously, then a plain receive: the batch leaves the scene in the last item's state
+    s.receive_batch(items, n, read=False)
+    s.receive(n, seed=frames[-1])
+    assert rel_l2(s.profile()[0, 0, 5:], got[-1][0, 0, 5:]) <= 1e-5
+    s.close()
+
+
+def test_receive_batch_receive_elements(native):
+    """C5 as a batch: the elements of the receive array are the items (the receiver rectangle re-posed per item, seed = element)."""
+    s, rx = configs.c5_urban(n_side=6, face_grid=3)
+    s.commit()
+    elems, n = [0, 1, 31, 63], 1 << 15
+    got = s.receive_batch([dict(seed=k, rects=[(rx, configs.c5_element_pose(k))]) for k in elems], n)
+    for i, k in enumerate(elems):
+        s.update_rect(rx, configs.c5_element_pose(k))
+        s.receive(n, seed=k)
+        one = s.profile()
+        assert np.array_equal(got[i][..., 1:3], one[..., 1:3])
+        assert rel_l2(got[i][..., 0], one[..., 0]) <= 1e-5
     s.close()
 
 
