@@ -148,6 +148,7 @@ struct WaveSlot {
     cudaStream_t stream = nullptr; bool own_stream = false; cudaEvent_t done = nullptr;
     uint32_t *h_counts = nullptr;     // pinned read-back of queue counts
     uint32_t *path_stash = nullptr;   // k_path's parking areas (path_stash_bytes), allocated on first use
+    DevRect *d_rects = nullptr; size_t n_rects = 0; DevEndpoint *d_rx = nullptr;   // bf_receive_batch: this slot's copy of the tables an item re-poses
 };
 
 // Launch-shape knobs.  Defaults come from the environment ONCE, when the scene is created (BF_WAVE_LANES, BF_WAVE_STREAMS,
@@ -162,7 +163,7 @@ struct Tunables {
     int64_t trace_rounds = 8;     // batches of 32 rays per active traversal warp (0: all warps of the grid)
     int64_t use_graph = 1;        // small calls: replay the wave's launch sequence from a CUDA graph
     int64_t path_fused = 1;       // scenes with a deferred primary: k_path integrates the rectangle-only paths in registers
-    int64_t mega_max = 16384;     // requests up to this many samples, and every request on a scene without meshes (-1: never), run as ONE k_mega launch
+    int64_t mega_max = 262144;    // requests up to this many samples, and every request on a scene without meshes (-1: never), run as ONE k_mega launch
 };
 static int64_t env_i64(const char *name, int64_t dflt, int64_t lo, int64_t hi) {
     const char *e = getenv(name);
@@ -182,7 +183,7 @@ static Tunables tunables_from_env() {
     t.trace_rounds = env_i64("BF_TRACE_ROUNDS", 8, 0, 1024);
     t.use_graph = env_i64("BF_USE_GRAPH", 1, 0, 1);
     t.path_fused = env_i64("BF_PATH_FUSED", 1, 0, 1);
-    t.mega_max = env_i64("BF_MEGA_MAX", 16384, -1, 1ll << 28);
+    t.mega_max = env_i64("BF_MEGA_MAX", 262144, -1, 1ll << 28);
     return t;
 }
 
@@ -702,17 +703,30 @@ static int upload_tables(bf_scene *s) {
 // Light upload: only rectangle poses and / or the (non-phased) receiver descriptor changed since the last upload (the
 // per-frame re-posing of C4 / C5, animated_trans_rad.py:305-355).  Re-stages the rectangle table and the receiver endpoint
 // through the pinned ring and refreshes the copies in the kernel parameter block; nothing else of the scene is touched.
-static int upload_tables_light(bf_scene *s) {
+static int upload_tables_light(bf_scene *s, WaveSlot *into = nullptr) {
     DevScene &d = s->dev;
     const size_t rect_bytes = s->rects.size() * sizeof(DevRect);
     const size_t need = ((rect_bytes + 15) & ~(size_t) 15) + sizeof(DevEndpoint);
     if (!s->h_ring || need > s->ring_slot_bytes) {
-        BF_CUDA(cudaStreamSynchronize(s->stream));
+        BF_CUDA(cudaDeviceSynchronize());
         if (s->h_ring) cudaFreeHost(s->h_ring);
         s->h_ring = nullptr;
         BF_CUDA(cudaMallocHost(&s->h_ring, need * 2 * bf_scene::RING));
         s->ring_slot_bytes = need * 2;
         for (int i = 0; i < bf_scene::RING; ++i) if (!s->ring_ev[i]) BF_CUDA(cudaEventCreateWithFlags(&s->ring_ev[i], cudaEventDisableTiming));
+    }
+    // destination: the scene's tables on the scene's stream, or (bf_receive_batch) a wave slot's private copies on its stream
+    DevRect *dst_rects = s->d_rects.p; DevEndpoint *dst_rx = s->d_rx.p; cudaStream_t stream = s->stream;
+    if (into) {
+        if (into->n_rects < s->rects.size() || !into->d_rx) {
+            BF_CUDA(cudaStreamSynchronize(into->stream));
+            if (into->d_rects) { cudaFree(into->d_rects); into->allocs.erase(std::remove(into->allocs.begin(), into->allocs.end(), (void *) into->d_rects), into->allocs.end()); }
+            if (into->d_rx) { cudaFree(into->d_rx); into->allocs.erase(std::remove(into->allocs.begin(), into->allocs.end(), (void *) into->d_rx), into->allocs.end()); }
+            BF_CUDA(cudaMalloc((void **) &into->d_rects, std::max<size_t>(rect_bytes, 16))); into->allocs.push_back(into->d_rects);
+            BF_CUDA(cudaMalloc((void **) &into->d_rx, sizeof(DevEndpoint))); into->allocs.push_back(into->d_rx);
+            into->n_rects = s->rects.size();
+        }
+        dst_rects = into->d_rects; dst_rx = into->d_rx; stream = into->stream;
     }
     const int slot = s->ring_next; s->ring_next = (slot + 1) % bf_scene::RING;
     BF_CUDA(cudaEventSynchronize(s->ring_ev[slot]));      // completed long ago unless RING uploads are in flight
@@ -720,18 +734,19 @@ static int upload_tables_light(bf_scene *s) {
     DevEndpoint rx = make_endpoint(s->rx, s->rx_shape);
     if (rect_bytes) {
         memcpy(h, s->rects.data(), rect_bytes);
-        BF_CUDA(cudaMemcpyAsync(s->d_rects.p, h, rect_bytes, cudaMemcpyHostToDevice, s->stream));
+        BF_CUDA(cudaMemcpyAsync(dst_rects, h, rect_bytes, cudaMemcpyHostToDevice, stream));
     }
     memcpy(h + ((rect_bytes + 15) & ~(size_t) 15), &rx, sizeof(rx));
-    BF_CUDA(cudaMemcpyAsync(s->d_rx.p, h + ((rect_bytes + 15) & ~(size_t) 15), sizeof(rx), cudaMemcpyHostToDevice, s->stream));
-    BF_CUDA(cudaEventRecord(s->ring_ev[slot], s->stream));
+    BF_CUDA(cudaMemcpyAsync(dst_rx, h + ((rect_bytes + 15) & ~(size_t) 15), sizeof(rx), cudaMemcpyHostToDevice, stream));
+    BF_CUDA(cudaEventRecord(s->ring_ev[slot], stream));
     if (d.n_nodes != 0) estimate_primary_defer(s);
     d.rx_needs_aperture = s->rx.kind != BF_RX_PERSPECTIVE;
     d.rx_ep = rx;
     memset(&d.rx_rect, 0, sizeof(DevRect));
     if (s->rx_shape >= 0) d.rx_rect = s->rects[s->shapes[s->rx_shape].index];
     if (d.n_txs != 0 && d.tx0_ep.shape >= 0) d.tx0_rect = s->rects[s->shapes[d.tx0_ep.shape].index];
-    s->tables_dirty = false; s->tables_light = false;
+    // a slot-private upload leaves the scene's own device tables stale: they are refreshed before the next plain bf_receive
+    s->tables_dirty = into != nullptr; s->tables_light = into != nullptr;
     return BF_OK;
 }
 
@@ -879,7 +894,7 @@ static void free_slot(WaveSlot &sl, bool keep_stream) {
     for (void *p : sl.allocs) cudaFree(p);
     sl.allocs.clear();
     memset(&sl.wave, 0, sizeof(sl.wave));
-    sl.capacity = 0; sl.path_stash = nullptr;
+    sl.capacity = 0; sl.path_stash = nullptr; sl.d_rects = nullptr; sl.n_rects = 0; sl.d_rx = nullptr;
     if (!keep_stream) {
         if (sl.stream && sl.own_stream) cudaStreamDestroy(sl.stream);
         if (sl.done) cudaEventDestroy(sl.done);
@@ -937,8 +952,9 @@ static cudaEvent_t next_trace_event(bf_scene *s, int kind) {
 }
 
 // One wave on one slot: lanes [0, n) <-> sample indices [first, first + n)
-static int run_wave(bf_scene *s, WaveSlot &sl, uint64_t seed, uint64_t first, uint32_t n, float *profile, bool with_records) {
-    const DevScene &sc = s->dev;
+static int run_wave(bf_scene *s, WaveSlot &sl, uint64_t seed, uint64_t first, uint32_t n, float *profile, bool with_records,
+                    const DevScene *scene_override = nullptr) {
+    const DevScene &sc = scene_override ? *scene_override : s->dev;
     Wave w = sl.wave;
     if (!with_records) { w.records = nullptr; w.sample_of = nullptr; }
     // BF_FUSED_PRIMARY=0 selects the unfused raygen + trace pair (lanes = samples), kept for A/B measurements
@@ -950,7 +966,8 @@ static int run_wave(bf_scene *s, WaveSlot &sl, uint64_t seed, uint64_t first, ui
     const bool unbounded = sc.integ.max_depth < 0 || sc.integ.max_depth > 64;
     const uint32_t max_depth = sc.integ.max_depth < 0 ? BF_MAX_BOUNCES : std::min<uint32_t>((uint32_t) sc.integ.max_depth, BF_MAX_BOUNCES);
     const uint32_t ctr_blocks = unbounded ? BF_MAX_BOUNCES + 2 : max_depth + 2;
-    BF_CUDA(cudaMemsetAsync(ctr, 0, (size_t) BF_CTR_STRIDE * ctr_blocks * 4, sl.stream));
+    const bool mega = fused && s->tune.mega_max >= 0 && (sc.n_nodes == 0 || (int64_t) n <= s->tune.mega_max);
+    BF_CUDA(cudaMemsetAsync(ctr, 0, (size_t) BF_CTR_STRIDE * (mega ? 1 : ctr_blocks) * 4, sl.stream));
     uint64_t launches = 0;
     const bool timing = s->time_trace;
     auto timed = [&](int kind, auto &&fn) {
@@ -959,7 +976,7 @@ static int run_wave(bf_scene *s, WaveSlot &sl, uint64_t seed, uint64_t first, ui
         if (timing) { cudaEventRecord(next_trace_event(s, kind), sl.stream); }
     };
     bool path = false;
-    if (fused && s->tune.mega_max >= 0 && (sc.n_nodes == 0 || (int64_t) n <= s->tune.mega_max)) {
+    if (mega) {
         // scenes without meshes, and small requests on any scene: the whole path of a sample in one thread, one launch
         timed(BF_K_PRIMARY, [&] { return launch_mega(sc, w, seed, first, n, ctr + 2, profile, cfg); });
         s->stats.kernel_launches += launches;
@@ -1067,16 +1084,57 @@ int bf_receive_batch(bf_scene *s, uint32_t n_items, const bf_batch_item *items, 
     if (!s->committed) return fail(s, BF_ERR_STATE, "bf_receive_batch: scene not committed");
     if (profiles && n_floats < (size_t) n_items * s->profile_floats) return fail(s, BF_ERR_INVALID, "bf_receive_batch: destination too small");
     BF_CUDA(cudaSetDevice(s->device));
+    if (s->d_batch.n < (size_t) n_items * s->profile_floats) BF_CUDA(cudaStreamSynchronize(s->stream));
     BF_CUDA(s->d_batch.alloc((size_t) n_items * s->profile_floats));
-    for (uint32_t i = 0; i < n_items; ++i) {
-        const bf_batch_item &it = items[i];
-        for (uint32_t k = 0; k < it.n_rect_updates; ++k) {
-            int rc = bf_scene_update_rect(s, it.rect_shape_ids[k], it.rect_to_world + 16 * (size_t) k);
+    // Items that fit one wave run concurrently: item i goes to wave slot i % slots, on that slot's stream, with the slot's OWN
+    // copy of the tables the item re-poses (rectangles, receiver), so neighbouring items never wait for each other.  Larger
+    // items (several waves each) already fill the machine and run one after the other on the scene's tables.
+    const bool concurrent = n_samples <= (1u << 22) && !s->time_trace && s->tune.wave_streams > 1;
+    if (!concurrent) {
+        for (uint32_t i = 0; i < n_items; ++i) {
+            const bf_batch_item &it = items[i];
+            for (uint32_t k = 0; k < it.n_rect_updates; ++k) {
+                int rc = bf_scene_update_rect(s, it.rect_shape_ids[k], it.rect_to_world + 16 * (size_t) k);
+                if (rc) return rc;
+            }
+            if (it.receiver) { int rc = bf_scene_set_receiver(s, it.receiver_shape, it.receiver); if (rc) return rc; }
+            int rc = receive_into(s, it.seed, it.first_sample, n_samples, 0, s->d_batch.p + (size_t) i * s->profile_floats);
             if (rc) return rc;
         }
-        if (it.receiver) { int rc = bf_scene_set_receiver(s, it.receiver_shape, it.receiver); if (rc) return rc; }
-        int rc = receive_into(s, it.seed, it.first_sample, n_samples, 0, s->d_batch.p + (size_t) i * s->profile_floats);
-        if (rc) return rc;
+    } else {
+        if (s->tables_dirty && !s->tables_light) { int rc = upload_tables(s); if (rc) return rc; }     // a heavy change pending from before the batch
+        const size_t n_slots = (size_t) std::min<int64_t>(s->tune.wave_streams, std::max<uint32_t>(n_items, 1u));
+        const uint32_t lanes = (uint32_t) std::max<uint64_t>(n_samples, 1024);
+        for (size_t k = 0; k < n_slots; ++k) { int rc = ensure_slot(s, k, lanes, false); if (rc) return rc; }
+        s->ev_trace_used = 0;
+        BF_CUDA(cudaEventRecord(s->ev_begin, s->stream));
+        BF_CUDA(cudaEventRecord(s->ev_fork, s->stream));
+        for (size_t k = 1; k < n_slots; ++k) BF_CUDA(cudaStreamWaitEvent(s->slots[k].stream, s->ev_fork, 0));
+        for (uint32_t i = 0; i < n_items; ++i) {
+            const bf_batch_item &it = items[i];
+            for (uint32_t k = 0; k < it.n_rect_updates; ++k) {
+                int rc = bf_scene_update_rect(s, it.rect_shape_ids[k], it.rect_to_world + 16 * (size_t) k);
+                if (rc) return rc;
+            }
+            if (it.receiver) { int rc = bf_scene_set_receiver(s, it.receiver_shape, it.receiver); if (rc) return rc; }
+            if (s->tables_dirty && !s->tables_light)
+                return fail(s, BF_ERR_UNSUPPORTED, "bf_receive_batch: an item may re-pose rectangles and replace the receiver by one of the same kind only");
+            WaveSlot &sl = s->slots[i % n_slots];
+            int rc = upload_tables_light(s, &sl);
+            if (rc) return rc;
+            DevScene sc = s->dev;
+            sc.rects = sl.d_rects; sc.rx = sl.d_rx;
+            float *profile = s->d_batch.p + (size_t) i * s->profile_floats;
+            BF_CUDA(cudaMemsetAsync(profile, 0, s->profile_floats * 4, sl.stream));
+            rc = run_wave(s, sl, it.seed, it.first_sample, (uint32_t) n_samples, profile, false, &sc);
+            if (rc) return rc;
+            s->stats.samples += n_samples;
+        }
+        for (size_t k = 1; k < n_slots; ++k) {
+            BF_CUDA(cudaEventRecord(s->slots[k].done, s->slots[k].stream));
+            BF_CUDA(cudaStreamWaitEvent(s->stream, s->slots[k].done, 0));
+        }
+        BF_CUDA(cudaEventRecord(s->ev_end, s->stream));
     }
     s->batch_items = n_items;
     if (profiles && n_items) {
