@@ -1,0 +1,110 @@
+"""Independent anchor for the radar rows the reference pins with no golden vector:
+tests/plate_path.py evaluates single path samples of a three-rectangle scene in numpy float64 straight from the reference's text;
+here the CPU oracle (not gpu) and the CUDA path (gpu) must reproduce it sample by sample -- first-hit distance, valid flag, both bin
+coordinates, the value hsum(|ray_weight| L) and the phase handed to the PhaseIntegrator -- and the binned profile must be the
+histogram of those values."""
+import math
+
+import numpy as np
+import pytest
+
+from beifong_b200 import _native as N
+from beifong_b200.meshes import Transform as T
+from beifong_b200.scene import FlatScene, RADAR_94GHZ
+from oracle_lib import OracleScene
+from plate_path import PlateScene, evaluate_sample
+from record_binning import profile_from_records
+
+
+def build(sc):
+    s = FlatScene(spectrum_width=1, **RADAR_94GHZ)
+    dflt = s.add_diffuse(0.5, two_sided=False)
+    plate_m = s.add_diffuse(sc.rho, two_sided=False)
+    rx = s.add_rect((T.scale([sc.a, sc.a, 1.0])).matrix32(), dflt)
+    tx = s.add_rect((T.translate([0.0, sc.tx_y, 0.0]) * T.scale([sc.a, sc.a, 1.0])).matrix32(), dflt)
+    s.add_rect((T.translate([0.0, 0.0, sc.R]) * T.rotate([1, 0, 0], 180.0) * T.scale([sc.plate_half, sc.plate_half, 1.0])).matrix32(), plate_m)
+    s.add_rect((T.translate([0.0, 0.0, sc.floor_z]) * T.scale([sc.floor_half, sc.floor_half, 1.0])).matrix32(), plate_m)
+    tex = s.add_uniform(1.0)
+    sig = dict(amplitude=1.0, repfreq=sc.repfreq, t_ext=sc.t_ext, f_centre=sc.f_c, f_ext=sc.f_ext, gain=1.0)
+    s.add_transmitter(tx, FlatScene.endpoint(N.BF_TX_WIGNER, texture=tex, signal=FlatScene.signal(N.BF_SIG_LINFMCW, sig_is_delta=True, resample_freq=True, **sig)))
+    s.set_receiver(rx, FlatScene.endpoint(N.BF_RX_WIGNER, texture=tex, signal=FlatScene.signal(N.BF_SIG_LINFMCW, sig_is_delta=True, resample_freq=False, **sig),
+                                          receive_type=N.BF_RECV_MIX_RESAMPLE, adc_sampling_start=sc.adc_start, adc_sampling_time=sc.adc_time))
+    s.set_adc(t_bins=sc.t_bins, f_bins=sc.f_bins, t_bandwidth=sc.t_bw, f_bandwidth=sc.f_bw)
+    s.set_integrator(N.BF_GEN_PHASE, max_depth=2, rr_depth=5, phase_bins=1)
+    return s
+
+
+def check_records(sc, rec, seed, idxs):
+    """Every modelled sample of `idxs` against the numpy evaluation."""
+    n_checked = n_valid = n_phase = 0
+    worst = 0.0
+    for i in idxs:
+        e = evaluate_sample(sc, seed, int(i))
+        if e is None:
+            continue
+        r = rec[i]
+        n_checked += 1
+        assert int(r["valid"]) == e["valid"], (i, r, e)
+        assert r["tf_t"] == pytest.approx(e["tf_t"], rel=2e-6, abs=1e-6), (i, r["tf_t"], e["tf_t"])
+        if not e["valid"]:
+            assert r["value"] == 0.0 and not math.isfinite(r["first_t"])
+            continue
+        n_valid += 1
+        assert r["first_t"] == pytest.approx(e["first_t"], rel=3e-6)
+        assert int(r["depth"]) == e["depth"]
+        # beat-frequency bin coordinate: a difference of two ~1e11 Hz values; the fp32 roundings of the two wavelengths are
+        # reproduced by the evaluator, so it agrees to a small fraction of a bin
+        assert r["tf_f"] == pytest.approx(e["tf_f"], abs=0.02 + 1e-5 * e["tf_f"]), (i, r["tf_f"], e["tf_f"])
+        scale = max(abs(e["value"]), 1e-12)
+        worst = max(worst, abs(r["value"] - e["value"]) / scale)
+        assert r["value"] == pytest.approx(e["value"], rel=2e-3, abs=1e-9), (i, r["value"], e["value"])
+        if math.isfinite(e["phase"]):
+            n_phase += 1
+            assert r["phase"] == pytest.approx(e["phase"], rel=1e-5)      # t2 of a grazing continuation ray carries the fp32 error of its direction
+        else:
+            assert r["phase"] == -math.inf
+    return n_checked, n_valid, n_phase, worst
+
+
+def test_oracle_reproduces_the_independent_path_evaluation():
+    sc = PlateScene()
+    s = build(sc)
+    orc = OracleScene(s.export(), accel=OracleScene.BRUTE)
+    seed, n = 9, 4000
+    rec = orc.sample_records(n, seed=seed)
+    checked, valid, with_phase, worst = check_records(sc, rec, seed, range(n))
+    assert checked >= 0.99 * n and valid > 0.15 * n and with_phase > 0.9 * valid
+    # median agreement is at fp32 rounding level, far inside the gate of the individual samples
+    vals = np.array([(rec[i]["value"], (evaluate_sample(sc, seed, i) or {"value": np.nan})["value"]) for i in range(400)])
+    ok = np.isfinite(vals[:, 1]) & (vals[:, 1] != 0)
+    assert np.median(np.abs(vals[ok, 0] - vals[ok, 1]) / np.abs(vals[ok, 1])) <= 2e-5
+    # SignalBlock::put: the oracle's binned profile is the histogram of its per-sample records (numpy restatement of the box splat)
+    prof = orc.receive(n, seed=seed, threads=1)
+    mine, _, _ = profile_from_records(rec, prof.shape[1], prof.shape[0], 1)
+    assert np.array_equal(mine[..., 1:3], prof[..., 1:3].astype(np.float64))
+    assert np.linalg.norm(mine[..., 0] - prof[..., 0]) <= 1e-5 * np.linalg.norm(mine[..., 0])
+    # the plate at R = 5 m and the sweep rate put the energy where the closed form says: f_beat = slope * (2 R / c) up to the
+    # offset of the transmitter, i.e. bin f_beat * f_bins / f_bw of the frequency axis
+    k = sc.f_ext / sc.t_ext * (2.0 * sc.R / sc.c) * sc.f_bins / sc.f_bw
+    energy = np.abs(prof[..., 0]).sum(axis=1)
+    assert abs(int(np.argmax(energy)) - int(k)) <= 1
+    assert energy[int(k) - 1:int(k) + 40].sum() >= 0.98 * energy.sum()       # oblique paths are longer: the tail lies above bin k
+    s.close(); orc.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("pipeline", ["wavefront", "mega"])
+def test_device_reproduces_the_independent_path_evaluation(native, pipeline):
+    sc = PlateScene()
+    s = build(sc).commit()
+    s.set_tunable("mega_max", (1 << 28) if pipeline == "mega" else -1)
+    seed, n = 9, 4000
+    rec = s.sample_records(n, seed=seed)
+    checked, valid, with_phase, worst = check_records(sc, rec, seed, range(n))
+    assert checked >= 0.99 * n and valid > 0.15 * n and with_phase > 0.9 * valid
+    s.receive(n, seed=seed)
+    prof = s.profile()
+    mine, _, _ = profile_from_records(rec, prof.shape[1], prof.shape[0], 1)
+    assert np.array_equal(mine[..., 1:3], prof[..., 1:3].astype(np.float64))
+    assert np.linalg.norm(mine[..., 0] - prof[..., 0]) <= 1e-5 * np.linalg.norm(mine[..., 0])
+    s.close()

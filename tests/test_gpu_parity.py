@@ -56,9 +56,11 @@ def test_occlusion_small_vs_bruteforce(small):
     assert 0 < g.sum() < len(g)
 
 
+@pytest.mark.parametrize("pipeline", ["wavefront", "mega"])
 @pytest.mark.parametrize("width", [1, 4])
-def test_sample_records_small(native, width):
+def test_sample_records_small(native, width, pipeline):
     s = configs.small_radar(spectrum_width=width).commit()
+    s.set_tunable("mega_max", (1 << 28) if pipeline == "mega" else -1)
     orc = OracleScene(s.export(), accel=OracleScene.BRUTE)
     n = 20000
     g = s.sample_records(n, seed=7)
@@ -82,9 +84,11 @@ def test_sample_records_small(native, width):
     s.close()
 
 
+@pytest.mark.parametrize("pipeline", ["wavefront", "mega"])
 @pytest.mark.parametrize("width", [1, 4])
-def test_profile_small(native, width):
+def test_profile_small(native, width, pipeline):
     s = configs.small_radar(spectrum_width=width).commit()
+    s.set_tunable("mega_max", (1 << 28) if pipeline == "mega" else -1)
     orc = OracleScene(s.export(), accel=OracleScene.BVH)
     n = 1 << 18
     s.receive(n, seed=11)
@@ -339,6 +343,7 @@ def test_receive_batch_equals_frame_loop(native):
     between items) against one bf_receive + bf_profile_read per frame on a scene built from scratch for that frame."""
     s, tx = configs.c4_animated(frame=0)
     s.commit()
+    s.set_tunable("mega_max", 1 << 18)       # the product default: a scene without meshes runs as one k_mega launch per item
     frames, n = [3, 64, 65, 200, 255], 4000
     items = []
     for f in frames:
