@@ -61,7 +61,7 @@ class bf_adc_desc(C.Structure):
 
 class bf_integrator_desc(C.Structure):
     _fields_ = [("gen", u32), ("max_depth", i32), ("rr_depth", i32), ("phase_bins", u32), ("range_bins", u32),
-                ("dr", f32), ("rng_mode", u32), ("reserved", u32)]
+                ("dr", f32), ("rng_mode", u32), ("doppler", u32)]
 
 
 class bf_sample_record(C.Structure):
@@ -94,12 +94,14 @@ PROTOTYPES = {
     "bf_scene_add_bsdf": (C.c_int, [vp, P(bf_bsdf_desc), P(u32)]),
     "bf_scene_add_mesh": (C.c_int, [vp, P(f32), u32, P(u32), u32, P(f32), u32, P(u32)]),
     "bf_scene_add_rect": (C.c_int, [vp, P(f32), u32, P(u32)]),
+    "bf_scene_set_shape_velocity": (C.c_int, [vp, u32, P(f32)]),
     "bf_scene_add_transmitter": (C.c_int, [vp, u32, P(bf_endpoint_desc), P(u32)]),
     "bf_scene_set_receiver": (C.c_int, [vp, u32, P(bf_endpoint_desc)]),
     "bf_scene_set_adc": (C.c_int, [vp, P(bf_adc_desc)]),
     "bf_scene_set_integrator": (C.c_int, [vp, P(bf_integrator_desc)]),
     "bf_scene_commit": (C.c_int, [vp, C.c_int]),
     "bf_scene_update_rect": (C.c_int, [vp, u32, P(f32)]),
+    "bf_scene_update_transform": (C.c_int, [vp, u32, P(f32)]),
     "bf_scene_reupload": (C.c_int, [vp]),
     "bf_scene_device_bytes": (C.c_int, [vp, P(C.c_size_t)]),
     "bf_profile_channels": (C.c_int, [vp, P(u32)]),

@@ -78,6 +78,7 @@ DevRect make_rect(const float *to_world16, uint32_t shape) {
     return r;
 }
 
+static M4 m4_identity() { M4 r; memset(&r, 0, sizeof(r)); for (int i = 0; i < 4; ++i) r.m[i][i] = 1.f; return r; }
 static M4 m4_mul(const M4 &a, const M4 &b) {
     M4 r;
     for (int i = 0; i < 4; ++i) for (int j = 0; j < 4; ++j) {
@@ -196,6 +197,7 @@ struct bf_scene {
     std::vector<DevRect> rects;
     std::vector<size_t> rect_blob_off;   // offset of each rectangle's record in the export blob (bf_scene_update_rect rewrites it)
     std::vector<HostShape> shapes;
+    std::vector<M4> velocities;      // per shape (identity unless bf_scene_set_shape_velocity)
     std::vector<HostTx> txs;
     int32_t rx_shape = -1; bf_endpoint_desc rx; bool has_rx = false; size_t rx_blob_off = (size_t) -1;
     bf_adc_desc adc; bool has_adc = false;
@@ -210,10 +212,13 @@ struct bf_scene {
     cudaStream_t stream = nullptr;
     DevScene dev;
     DevBuf<uint4> d_nodes; DevBuf<float4> d_tris, d_tri_nrm;
+    DevBuf<float4> d_tris_rest, d_nrm_rest; DevBuf<float> d_node_box; bool rest_saved = false;    // bf_scene_update_transform (refit)
+    std::vector<uint32_t> bvh_level_first; float bvh_pad_abs = 0.f;
     DevBuf<DevRect> d_rects; DevBuf<DevShape> d_shapes; DevBuf<bf_bsdf_desc> d_bsdfs;
-    DevBuf<DevSpectrum> d_spectra; DevBuf<float> d_spec_pool; DevBuf<DevEndpoint> d_txs, d_rx; DevBuf<DevVElem> d_velems;
+    DevBuf<DevSpectrum> d_spectra; DevBuf<float> d_spec_pool; DevBuf<DevEndpoint> d_txs, d_rx; DevBuf<DevVElem> d_velems; DevBuf<M4> d_velocities;
     DevBuf<float> d_profile; size_t profile_floats = 0;
     DevBuf<float> d_batch; uint32_t batch_items = 0;   // bf_receive_batch: one profile per item
+    bool geometry_moved = false;     // the device geometry differs from the pinned image (bf_scene_reupload would undo a refit)
     bool primary_defer = false;      // fused primary: traverse the rays that enter the mesh bounds in a separate dense launch
     DevFilter filter; bool wide_filter = false;    // discretised reconstruction filter when wider than one bin
     DevBuf<uint32_t> d_developed;    // bf_profile_develop output (fp32 or fp16 components)
@@ -394,8 +399,8 @@ void bf_scene_destroy(bf_scene *s) {
         if (s->stream) cudaStreamSynchronize(s->stream);
         if (s->nccl_comm) multi_destroy_comm(s->nccl_comm);
         free_wave(s);
-        s->d_nodes.release(); s->d_tris.release(); s->d_tri_nrm.release(); s->d_rects.release(); s->d_shapes.release();
-        s->d_bsdfs.release(); s->d_spectra.release(); s->d_spec_pool.release(); s->d_txs.release(); s->d_rx.release(); s->d_velems.release();
+        s->d_nodes.release(); s->d_tris.release(); s->d_tri_nrm.release(); s->d_tris_rest.release(); s->d_nrm_rest.release(); s->d_node_box.release(); s->d_rects.release(); s->d_shapes.release();
+        s->d_bsdfs.release(); s->d_spectra.release(); s->d_spec_pool.release(); s->d_txs.release(); s->d_rx.release(); s->d_velems.release(); s->d_velocities.release();
         s->d_profile.release(); s->d_batch.release(); s->d_developed.release(); s->d_totals.release();
         if (s->h_geom) cudaFreeHost(s->h_geom);
         if (s->h_tables) cudaFreeHost(s->h_tables);
@@ -458,6 +463,9 @@ int bf_scene_add_mesh(bf_scene *s, const float *positions, uint32_t n_vertices, 
     m.pos.assign(positions, positions + 3 * (size_t) n_vertices);
     m.idx.assign(faces, faces + 3 * (size_t) n_faces);
     if (normals) m.nrm.assign(normals, normals + 3 * (size_t) n_vertices);
+    for (int a = 0; a < 3; ++a) { m.rest_lo[a] = INFINITY; m.rest_hi[a] = -INFINITY; }
+    for (uint32_t v = 0; v < n_vertices; ++v)
+        for (int a = 0; a < 3; ++a) { m.rest_lo[a] = std::min(m.rest_lo[a], positions[3 * (size_t) v + a]); m.rest_hi[a] = std::max(m.rest_hi[a], positions[3 * (size_t) v + a]); }
     uint32_t hdr[4] = {n_vertices, n_faces, bsdf_id, normals ? 1u : 0u};
     record(s, BF_TAG_MESH, hdr, 16, m.pos.data(), 4 * m.pos.size(), m.idx.data(), 4 * m.idx.size(), normals ? m.nrm.data() : nullptr, normals ? 4 * m.nrm.size() : 0);
     HostShape sh; sh.type = 0; sh.index = (uint32_t) s->meshes.size(); sh.bsdf = bsdf_id; sh.tx = -1;
@@ -480,6 +488,17 @@ int bf_scene_add_rect(bf_scene *s, const float to_world[16], uint32_t bsdf_id, u
     s->rects.push_back(make_rect(to_world, id));
     s->shapes.push_back(sh);
     if (shape_id) *shape_id = id;
+    return BF_OK;
+}
+
+int bf_scene_set_shape_velocity(bf_scene *s, uint32_t shape_id, const float velocity[16]) {
+    if (!s || !velocity) return BF_ERR_INVALID;
+    if (shape_id >= s->shapes.size()) return fail(s, BF_ERR_INVALID, "bf_scene_set_shape_velocity: shape id out of range");
+    s->velocities.resize(s->shapes.size(), m4_identity());
+    memcpy(s->velocities[shape_id].m, velocity, 64);
+    uint32_t hdr[2] = {shape_id, 0};
+    record(s, BF_TAG_VELOCITY, hdr, 8, velocity, 64);
+    s->tables_dirty = true; s->tables_light = false;
     return BF_OK;
 }
 
@@ -644,6 +663,8 @@ static int upload_tables(bf_scene *s) {
     BF_CUDA(s->d_shapes.alloc(sh.size())); BF_CUDA(s->d_bsdfs.alloc(s->bsdfs.size()));
     BF_CUDA(s->d_rects.alloc(s->rects.size())); BF_CUDA(s->d_txs.alloc(txs.size())); BF_CUDA(s->d_rx.alloc(1));
     BF_CUDA(s->d_velems.alloc(velems.size()));
+    s->velocities.resize(s->shapes.size(), m4_identity());
+    BF_CUDA(s->d_velocities.alloc(s->velocities.size()));
     // The tables are packed into ONE pinned staging buffer and copied with cudaMemcpyAsync on the scene's stream, so the
     // copies are ordered before every kernel of the next bf_receive (the wave streams fork from that stream).  The
     // synchronize keeps the staging buffer from being rewritten while an earlier upload is still in flight (every wave
@@ -651,7 +672,7 @@ static int upload_tables(bf_scene *s) {
     BF_CUDA(cudaStreamSynchronize(s->stream));
     struct Part { void *dst; const void *src; size_t bytes; };
     const Part parts[] = {
-        {s->d_velems.p, velems.data(), velems.size() * sizeof(DevVElem)}, {s->d_spectra.p, ds.data(), ds.size() * sizeof(DevSpectrum)},
+        {s->d_velems.p, velems.data(), velems.size() * sizeof(DevVElem)}, {s->d_velocities.p, s->velocities.data(), s->velocities.size() * sizeof(M4)}, {s->d_spectra.p, ds.data(), ds.size() * sizeof(DevSpectrum)},
         {s->d_spec_pool.p, pool.data(), pool.size() * 4}, {s->d_shapes.p, sh.data(), sh.size() * sizeof(DevShape)},
         {s->d_bsdfs.p, s->bsdfs.data(), s->bsdfs.size() * sizeof(bf_bsdf_desc)}, {s->d_rects.p, s->rects.data(), s->rects.size() * sizeof(DevRect)},
         {s->d_txs.p, txs.data(), txs.size() * sizeof(DevEndpoint)}, {s->d_rx.p, &rx, sizeof(rx)}};
@@ -677,7 +698,7 @@ static int upload_tables(bf_scene *s) {
     d.C = s->C; d.S = s->C.spectrum_width;
     d.n_rects = (uint32_t) s->rects.size(); d.n_shapes = (uint32_t) sh.size(); d.n_txs = (uint32_t) txs.size();
     d.rects = s->d_rects.p; d.shapes = s->d_shapes.p; d.bsdfs = s->d_bsdfs.p; d.spectra = s->d_spectra.p;
-    d.spec_pool = s->d_spec_pool.p; d.txs = s->d_txs.p; d.rx = s->d_rx.p; d.velems = s->d_velems.p;
+    d.spec_pool = s->d_spec_pool.p; d.txs = s->d_txs.p; d.rx = s->d_rx.p; d.velems = s->d_velems.p; d.velocities = s->d_velocities.p;
     d.adc = s->adc; d.integ = s->integ;
     build_filter(s);
     estimate_primary_defer(s);
@@ -790,7 +811,10 @@ int bf_scene_commit(bf_scene *s, int device) {
             for (int k = 0; k < 3; ++k) {
                 uint32_t vi = m.idx[3 * (size_t) f + k];
                 float *dst = k == 0 ? t.p0 : (k == 1 ? t.p1 : t.p2);
-                for (int a = 0; a < 3; ++a) { dst[a] = m.pos[3 * (size_t) vi + a]; scene_abs = std::max(scene_abs, std::fabs(dst[a])); }
+                V3 p(m.pos[3 * (size_t) vi], m.pos[3 * (size_t) vi + 1], m.pos[3 * (size_t) vi + 2]);
+                if (m.moved) p = xf_point_affine(m.motion, p);          // bf_scene_update_transform before the commit
+                dst[0] = p.x; dst[1] = p.y; dst[2] = p.z;
+                for (int a = 0; a < 3; ++a) scene_abs = std::max(scene_abs, std::fabs(dst[a]));
             }
             tris.push_back(t);
         }
@@ -829,13 +853,19 @@ int bf_scene_commit(bf_scene *s, int device) {
             for (int k = 0; k < 3; ++k) {
                 float *dst = nr + 12 * slot + 4 * k;
                 if (m.nrm.empty()) { dst[0] = dst[1] = dst[2] = 0.f; }
-                else { uint32_t vi = m.idx[3 * (size_t) t.prim + k]; dst[0] = m.nrm[3 * (size_t) vi]; dst[1] = m.nrm[3 * (size_t) vi + 1]; dst[2] = m.nrm[3 * (size_t) vi + 2]; }
+                else {
+                    uint32_t vi = m.idx[3 * (size_t) t.prim + k];
+                    V3 n(m.nrm[3 * (size_t) vi], m.nrm[3 * (size_t) vi + 1], m.nrm[3 * (size_t) vi + 2]);
+                    if (m.moved) { n = xf_normal(m4_inverse(m.motion), n); if (n.x != 0.f || n.y != 0.f || n.z != 0.f) n = normalize(n); }
+                    dst[0] = n.x; dst[1] = n.y; dst[2] = n.z;
+                }
                 dst[3] = 0.f;
             }
         }
     }
     s->stats.build_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
     s->stats.bvh_nodes = bvh.stats.n_nodes; s->stats.bvh_tris = bvh.stats.n_tris; s->stats.bvh_depth = bvh.stats.depth;
+    s->bvh_level_first = bvh.level_first; s->bvh_pad_abs = bvh.pad_abs;
     s->stats.n_rects = (uint32_t) s->rects.size();
 
     auto t1 = std::chrono::steady_clock::now();
@@ -865,6 +895,16 @@ int bf_scene_reupload(bf_scene *s) {
     BF_CUDA(cudaSetDevice(s->device));
     int rc = upload_geometry(s);
     if (rc) return rc;
+    if (s->geometry_moved) {      // the pinned image is the committed pose: re-apply the motions set since
+        LaunchCfg cfg; memset(&cfg, 0, sizeof(cfg)); cfg.stream = s->stream; cfg.sm_count = s->sm_count;
+        for (size_t si = 0; si < s->shapes.size(); ++si) {
+            if (s->shapes[si].type != 0 || !s->meshes[s->shapes[si].index].moved) continue;
+            const HostMesh &m = s->meshes[s->shapes[si].index];
+            launch_refit_tris(s->d_tris_rest.p, s->dev.tri_nrm ? s->d_nrm_rest.p : nullptr, s->d_tris.p, s->d_tri_nrm.p, s->dev.n_tris, (uint32_t) si, m.motion,
+                              m4_inverse(m.motion), cfg);
+        }
+        launch_refit_nodes(s->d_nodes.p, s->d_tris.p, s->d_node_box.p, s->bvh_level_first.data(), (uint32_t) s->bvh_level_first.size() - 1, s->bvh_pad_abs, cfg);
+    }
     return upload_tables(s);
 }
 
@@ -881,6 +921,82 @@ int bf_scene_update_rect(bf_scene *s, uint32_t shape_id, const float to_world[16
     memcpy(s->blob.data() + s->rect_blob_off[s->shapes[shape_id].index] + sizeof(bf_flat_record), to_world, 64);   // keep the export current
     if (!s->tables_dirty) s->tables_light = true;
     s->tables_dirty = true;
+    return BF_OK;
+}
+
+// Padded world-space bounds of all meshes from the (moved) rest-pose boxes: conservative, host only
+static void refresh_mesh_bounds(bf_scene *s) {
+    float lo[3] = {INFINITY, INFINITY, INFINITY}, hi[3] = {-INFINITY, -INFINITY, -INFINITY}, mag = 1e-3f;
+    bool any = false;
+    for (const HostMesh &m : s->meshes) {
+        if (m.nf == 0) continue;
+        any = true;
+        for (int c = 0; c < 8; ++c) {
+            V3 p((c & 1) ? m.rest_hi[0] : m.rest_lo[0], (c & 2) ? m.rest_hi[1] : m.rest_lo[1], (c & 4) ? m.rest_hi[2] : m.rest_lo[2]);
+            if (m.moved) p = xf_point_affine(m.motion, p);
+            const float v[3] = {p.x, p.y, p.z};
+            for (int a = 0; a < 3; ++a) { lo[a] = std::min(lo[a], v[a]); hi[a] = std::max(hi[a], v[a]); }
+        }
+    }
+    for (int a = 0; a < 3; ++a) if (any) mag = std::max(mag, std::max(std::fabs(lo[a]), std::fabs(hi[a])));
+    for (int a = 0; a < 3; ++a) { s->dev.mesh_lo[a] = lo[a] - 2e-4f * mag; s->dev.mesh_hi[a] = hi[a] + 2e-4f * mag; }
+}
+
+int bf_scene_update_transform(bf_scene *s, uint32_t shape_id, const float motion[16]) {
+    if (!s || !motion) return BF_ERR_INVALID;
+    if (shape_id >= s->shapes.size()) return fail(s, BF_ERR_INVALID, "bf_scene_update_transform: shape id out of range");
+    if (s->shapes[shape_id].type == 1) return bf_scene_update_rect(s, shape_id, motion);
+    HostMesh &m = s->meshes[s->shapes[shape_id].index];
+    memcpy(m.motion.m, motion, 64);
+    m.moved = true;
+    uint32_t hdr[2] = {shape_id, 0};
+    record(s, BF_TAG_MESH_MOTION, hdr, 8, motion, 64);
+    if (!s->committed) return BF_OK;            // the moved vertices go into the build
+    BF_CUDA(cudaSetDevice(s->device));
+    const uint32_t n_tris = s->dev.n_tris;
+    if (n_tris == 0) return BF_OK;
+    if (!s->rest_saved) {
+        // first motion after the commit: the rest-pose triangle (and normal) records in leaf order, rebuilt from the vertices as
+        // given to bf_scene_add_mesh (the committed table may hold a pose set before the commit); (shape, prim) of every slot
+        // come from the pinned image of the committed geometry
+        const float *ht = (const float *) ((const uint8_t *) s->h_geom + s->h_nodes_bytes);
+        std::vector<float> rest(12 * (size_t) n_tris), rest_n(s->dev.tri_nrm ? 12 * (size_t) n_tris : 0);
+        for (size_t slot = 0; slot < n_tris; ++slot) {
+            uint32_t shape, prim; memcpy(&shape, ht + 12 * slot + 3, 4); memcpy(&prim, ht + 12 * slot + 7, 4);
+            const HostMesh &hm = s->meshes[s->shapes[shape].index];
+            for (int k = 0; k < 3; ++k) {
+                const uint32_t vi = hm.idx[3 * (size_t) prim + k];
+                float *dst = rest.data() + 12 * slot + 4 * k;
+                dst[0] = hm.pos[3 * (size_t) vi]; dst[1] = hm.pos[3 * (size_t) vi + 1]; dst[2] = hm.pos[3 * (size_t) vi + 2];
+                memcpy(dst + 3, ht + 12 * slot + 4 * k + 3, 4);
+                if (!rest_n.empty()) {
+                    float *dn = rest_n.data() + 12 * slot + 4 * k;
+                    if (hm.nrm.empty()) { dn[0] = dn[1] = dn[2] = 0.f; }
+                    else { dn[0] = hm.nrm[3 * (size_t) vi]; dn[1] = hm.nrm[3 * (size_t) vi + 1]; dn[2] = hm.nrm[3 * (size_t) vi + 2]; }
+                    dn[3] = 0.f;
+                }
+            }
+        }
+        BF_CUDA(s->d_tris_rest.alloc(3 * (size_t) n_tris));
+        BF_CUDA(cudaMemcpy(s->d_tris_rest.p, rest.data(), 48 * (size_t) n_tris, cudaMemcpyHostToDevice));
+        if (!rest_n.empty()) {
+            BF_CUDA(s->d_nrm_rest.alloc(3 * (size_t) n_tris));
+            BF_CUDA(cudaMemcpy(s->d_nrm_rest.p, rest_n.data(), 48 * (size_t) n_tris, cudaMemcpyHostToDevice));
+        }
+        BF_CUDA(s->d_node_box.alloc(6 * (size_t) s->dev.n_nodes));
+        s->rest_saved = true;
+    }
+    LaunchCfg cfg; memset(&cfg, 0, sizeof(cfg)); cfg.stream = s->stream; cfg.sm_count = s->sm_count;
+    uint64_t launches = 0;
+    launches += launch_refit_tris(s->d_tris_rest.p, s->dev.tri_nrm ? s->d_nrm_rest.p : nullptr, s->d_tris.p, s->d_tri_nrm.p, n_tris, shape_id, m.motion,
+                                  m4_inverse(m.motion), cfg);
+    launches += launch_refit_nodes(s->d_nodes.p, s->d_tris.p, s->d_node_box.p, s->bvh_level_first.data(), (uint32_t) s->bvh_level_first.size() - 1,
+                                   s->bvh_pad_abs, cfg);
+    s->stats.kernel_launches += launches;
+    BF_CUDA(cudaGetLastError());
+    refresh_mesh_bounds(s);
+    if (s->dev.n_nodes != 0 && s->has_rx) estimate_primary_defer(s);
+    s->geometry_moved = true;
     return BF_OK;
 }
 

@@ -168,6 +168,7 @@ void build_wide_bvh(const std::vector<BvhTriIn> &tris, float pad_abs, WideBvh &o
     out.nodes.clear();
     out.tris.clear();
     out.tri_src.clear();
+    out.level_first.clear();
     out.stats = BvhStats();
     const uint32_t N = (uint32_t) tris.size();
     if (N == 0) return;
@@ -206,6 +207,7 @@ void build_wide_bvh(const std::vector<BvhTriIn> &tris, float pad_abs, WideBvh &o
     while (!queue.empty()) {
         Item it = queue.front();
         queue.pop_front();
+        if (it.depth > max_depth) out.level_first.push_back(it.wide);      // breadth first: depths never decrease along the queue
         max_depth = std::max(max_depth, it.depth);
         const Node2 &root = B.nodes[it.n2];
         uint32_t child[8];
@@ -345,6 +347,8 @@ void build_wide_bvh(const std::vector<BvhTriIn> &tris, float pad_abs, WideBvh &o
         w[18] = pack4(qhi[2]); w[19] = pack4(qhi[2] + 4);
     }
 
+    out.level_first.push_back((uint32_t) (out.nodes.size() / 20));
+    out.pad_abs = pad_abs;
     out.stats.n_nodes = (uint32_t) (out.nodes.size() / 20);
     out.stats.n_tris = (uint32_t) (out.tris.size() / 12);
     out.stats.depth = max_depth;

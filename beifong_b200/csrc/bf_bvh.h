@@ -40,6 +40,8 @@ struct WideBvh {
     std::vector<uint32_t> nodes;     // 20 u32 per node
     std::vector<float> tris;         // 12 floats per triangle, leaf order
     std::vector<uint32_t> tri_src;   // leaf slot -> index into the input triangle array
+    std::vector<uint32_t> level_first;   // nodes are in breadth-first order: index of the first node of every depth, + the node count
+    float pad_abs = 0.f;
     BvhStats stats;
 };
 

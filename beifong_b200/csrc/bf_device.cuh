@@ -220,6 +220,18 @@ BF_D SI compute_si_impl(const DevScene &sc, V3 ray_o, V3 ray_d, float4 hit) {
 
 BF_NI SI compute_si(const DevScene &sc, V3 ray_o, V3 ray_d, float4 hit) { return compute_si_impl(sc, ray_o, ray_d, hit); }
 
+// Shape::doppler (src/librender/shape.cpp:375-389): 2 * dot(si.wi, m_velocity * Point3f(si.to_local(si.p))) / MTS_C * si.wavelengths.
+// Reproduced as written: the velocity transform is applied (projectively) to the hit position expressed in the shading frame.
+template <int S> BF_NI Spec<S> shape_doppler(const DevScene &sc, const SI &si, const Spec<S> &wl) {
+    const V3 pl = si.to_local(si.p);
+    const V3 vp = xf_point(sc.velocities[si.shape], pl);
+    const float f = 2 * dot(si.wi, vp) / sc.C.c;
+    Spec<S> r;
+#pragma unroll
+    for (int k = 0; k < S; ++k) r.v[k] = f * wl.v[k];
+    return r;
+}
+
 // ---- microfacet distribution: include/mitsuba/render/microfacet.h -------------------------------------
 struct Microfacet {
     int type; float au, av; bool sample_visible;

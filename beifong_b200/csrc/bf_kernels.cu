@@ -497,6 +497,12 @@ __device__ __forceinline__ void shade_core(const DevScene &sc, uint32_t depth, L
 #pragma unroll
                 for (int k = 0; k < S; ++k) tspec.v[k] *= inv;
             }
+            if (gen == BF_GEN_PHASE && sc.integ.doppler) {
+                // pathtimefrequency.cpp:252-256, commented out in the reference ("Took doppler out to test"), behind the flag
+                const Spec<S> shift = shape_doppler<S>(sc, si, wl);
+#pragma unroll
+                for (int k = 0; k < S; ++k) wl.v[k] += shift.v[k];
+            }
             active_e &= ds.pdf != 0.f;
             if (active_e) {
                 V3 wo = si.to_local(ds.d);
@@ -1467,6 +1473,129 @@ int launch_resolve_hits(const DevScene &sc, const float4 *hit, uint32_t n, uint3
     if (n == 0) return 0;
     k_resolve_hits<<<(n + 255) / 256, 256, 0, cfg.stream>>>(sc, hit, n, shape, prim);
     return 1;
+}
+
+// =========================================================================================================
+// refit: moving meshes without a rebuild (bf_scene_update_transform)
+// =========================================================================================================
+// A mesh that moves rigidly between frames (the reference rebuilds its scene per frame,
+// animated_trans_rad.py:289-311) keeps the TOPOLOGY of the 8-wide BVH and gets new boxes:
+//   k_refit_tris    the rest-pose triangle records of the moved shape are transformed with the same fp32 fmadd chain as
+//                   Transform::transform_affine (transform.h:91-99), so the device triangles equal those of a scene built on
+//                   the moved vertices bit for bit (and with them t, u, v of every hit);
+//   k_refit_level   one thread per node, one launch per tree level, deepest first: child boxes from the triangles (leaf children)
+//                   or from the boxes the level below has just written (inner children), then the node's own quantisation
+//                   frame and its 8-bit child corners, rounded outwards exactly as bf_bvh.cpp does.
+__global__ void __launch_bounds__(256) k_refit_tris(const float4 *__restrict__ rest, const float4 *__restrict__ rest_nrm, float4 *__restrict__ tris,
+                                                    float4 *__restrict__ nrm, uint32_t n_tris, uint32_t shape, M4 M, M4 Minv) {
+    const uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x;
+    if (slot >= n_tris) return;
+    const float4 a = rest[3 * (size_t) slot];
+    if (__float_as_uint(a.w) != shape) return;
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        const float4 v = k == 0 ? a : rest[3 * (size_t) slot + k];
+        const V3 p = xf_point_affine(M, V3(v.x, v.y, v.z));
+        tris[3 * (size_t) slot + k] = make_float4(p.x, p.y, p.z, v.w);
+        if (rest_nrm) {
+            const float4 nv = rest_nrm[3 * (size_t) slot + k];
+            V3 n = xf_normal(Minv, V3(nv.x, nv.y, nv.z));
+            if (n.x != 0.f || n.y != 0.f || n.z != 0.f) n = normalize(n);
+            nrm[3 * (size_t) slot + k] = make_float4(n.x, n.y, n.z, 0.f);
+        }
+    }
+}
+
+__global__ void __launch_bounds__(128) k_refit_level(uint4 *__restrict__ nodes, const float4 *__restrict__ tris, float *__restrict__ node_box,
+                                                     uint32_t first, uint32_t count, float pad_abs) {
+    const uint32_t i = first + blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= first + count) return;
+    uint4 *np = nodes + 5 * (size_t) i;
+    const uint4 n0 = np[0], n1 = np[1];
+    const uint32_t imask = n0.w >> 24, child_base = n1.x, tri_base = n1.y;
+    float clo[8][3], chi[8][3];
+    bool used[8];
+    float lo[3] = {bf_inf(), bf_inf(), bf_inf()}, hi[3] = {-bf_inf(), -bf_inf(), -bf_inf()};
+#pragma unroll
+    for (int s = 0; s < 8; ++s) {
+        const uint32_t m = ((s < 4 ? n1.z : n1.w) >> (8 * (s & 3))) & 0xffu;
+        used[s] = m != 0u;
+        if (!used[s]) continue;
+        const uint32_t low5 = m & 31u;
+        if (low5 >= 24u) {         // inner child: the box the level below has written
+            const uint32_t c = child_base + __popc(imask & ((1u << s) - 1u));
+#pragma unroll
+            for (int a = 0; a < 3; ++a) { clo[s][a] = node_box[6 * (size_t) c + a]; chi[s][a] = node_box[6 * (size_t) c + 3 + a]; }
+        } else {                   // leaf child: 1 - 3 triangles, boxes padded as in build_wide_bvh
+            const uint32_t cnt = __popc(m >> 5);
+#pragma unroll
+            for (int a = 0; a < 3; ++a) { clo[s][a] = bf_inf(); chi[s][a] = -bf_inf(); }
+            for (uint32_t t = 0; t < cnt; ++t) {
+                const size_t slot = (size_t) tri_base + low5 + t;
+                const float4 p0 = tris[3 * slot], p1 = tris[3 * slot + 1], p2 = tris[3 * slot + 2];
+                const float v[3][3] = {{p0.x, p0.y, p0.z}, {p1.x, p1.y, p1.z}, {p2.x, p2.y, p2.z}};
+#pragma unroll
+                for (int a = 0; a < 3; ++a) {
+                    const float l = fminf(v[0][a], fminf(v[1][a], v[2][a])), h = fmaxf(v[0][a], fmaxf(v[1][a], v[2][a]));
+                    const float pad = pad_abs + 4e-7f * fmaxf(fabsf(l), fabsf(h));
+                    clo[s][a] = fminf(clo[s][a], l - pad); chi[s][a] = fmaxf(chi[s][a], h + pad);
+                }
+            }
+        }
+#pragma unroll
+        for (int a = 0; a < 3; ++a) { lo[a] = fminf(lo[a], clo[s][a]); hi[a] = fmaxf(hi[a], chi[s][a]); }
+    }
+#pragma unroll
+    for (int a = 0; a < 3; ++a) { node_box[6 * (size_t) i + a] = lo[a]; node_box[6 * (size_t) i + 3 + a] = hi[a]; }
+    // quantisation frame: origin = lo, per-axis power-of-two step with 255 steps covering the extent (bf_bvh.cpp)
+    uint32_t ebyte[3]; float scale[3];
+#pragma unroll
+    for (int a = 0; a < 3; ++a) {
+        const double ext = (double) hi[a] - (double) lo[a];
+        int e = ext > 0.0 ? (int) ceil(log2(ext / 255.0)) : -100;
+        e = max(-120, min(120, e));
+        while (ldexp(255.0, e) < ext * (1.0 + 1e-6)) ++e;
+        ebyte[a] = (uint32_t) (e + 127);
+        scale[a] = ldexpf(1.0f, e);
+    }
+    uint32_t q[6][2] = {{0u, 0u}, {0u, 0u}, {0u, 0u}, {0u, 0u}, {0u, 0u}, {0u, 0u}};      // qlo.x, qlo.y, qlo.z, qhi.x, qhi.y, qhi.z
+#pragma unroll
+    for (int s = 0; s < 8; ++s) {
+#pragma unroll
+        for (int a = 0; a < 3; ++a) {
+            int ql = 255, qh = 0;          // empty slot: inverted box
+            if (used[s]) {
+                const double lo_q = floor(((double) clo[s][a] - (double) lo[a]) / (double) scale[a]);
+                const double hi_q = ceil(((double) chi[s][a] - (double) lo[a]) / (double) scale[a]);
+                ql = (int) fmax(0.0, fmin(255.0, lo_q)); qh = (int) fmax(0.0, fmin(255.0, hi_q));
+                while (ql > 0 && lo[a] + (float) ql * scale[a] > clo[s][a]) --ql;
+                while (qh < 255 && lo[a] + (float) qh * scale[a] < chi[s][a]) ++qh;
+            }
+            q[a][s >> 2] |= (uint32_t) ql << (8 * (s & 3));
+            q[3 + a][s >> 2] |= (uint32_t) qh << (8 * (s & 3));
+        }
+    }
+    np[0] = make_uint4(__float_as_uint(lo[0]), __float_as_uint(lo[1]), __float_as_uint(lo[2]), ebyte[0] | (ebyte[1] << 8) | (ebyte[2] << 16) | (imask << 24));
+    np[2] = make_uint4(q[0][0], q[0][1], q[1][0], q[1][1]);
+    np[3] = make_uint4(q[2][0], q[2][1], q[3][0], q[3][1]);
+    np[4] = make_uint4(q[4][0], q[4][1], q[5][0], q[5][1]);
+}
+
+int launch_refit_tris(const float4 *rest, const float4 *rest_nrm, float4 *tris, float4 *nrm, uint32_t n_tris, uint32_t shape, const M4 &M, const M4 &Minv,
+                      const LaunchCfg &cfg) {
+    if (n_tris == 0) return 0;
+    k_refit_tris<<<(n_tris + 255) / 256, 256, 0, cfg.stream>>>(rest, rest_nrm, tris, nrm, n_tris, shape, M, Minv);
+    return 1;
+}
+int launch_refit_nodes(uint4 *nodes, const float4 *tris, float *node_box, const uint32_t *level_first, uint32_t n_levels, float pad_abs, const LaunchCfg &cfg) {
+    int launches = 0;
+    for (uint32_t l = n_levels; l-- > 0;) {
+        const uint32_t first = level_first[l], count = level_first[l + 1] - first;
+        if (count == 0) continue;
+        k_refit_level<<<(count + 127) / 128, 128, 0, cfg.stream>>>(nodes, tris, node_box, first, count, pad_abs);
+        ++launches;
+    }
+    return launches;
 }
 
 // =========================================================================================================

@@ -93,6 +93,7 @@ struct DevScene {
     const DevEndpoint *txs;
     const DevEndpoint *rx;
     const DevVElem *velems;
+    const M4 *velocities;      // per shape: the `velocity` transform (shape.cpp:39-42); read only when integ.doppler is set
     bf_adc_desc adc;
     bf_integrator_desc integ;
     uint32_t film_w, film_h, channels;
@@ -111,10 +112,12 @@ struct DevScene {
 };
 
 struct HostMesh {
-    std::vector<float> pos;
+    std::vector<float> pos;          // as given to bf_scene_add_mesh: the rest pose bf_scene_update_transform moves
     std::vector<uint32_t> idx;
     std::vector<float> nrm;
     uint32_t nv = 0, nf = 0;
+    bool moved = false; M4 motion;   // bf_scene_update_transform: world position = motion * rest position
+    float rest_lo[3], rest_hi[3];    // bounds of the rest pose
 };
 struct HostSpectrum {
     uint32_t kind = 0;

@@ -169,9 +169,21 @@ class FlatScene:
                           t_bandwidth, f_bandwidth, filter_radius, filter_kind)
         self._ck(N.lib().bf_scene_set_adc(self._h, C.byref(d)), "bf_scene_set_adc")
 
-    def set_integrator(self, gen, max_depth=-1, rr_depth=5, phase_bins=1, range_bins=0, dr=0.0):
-        d = N.bf_integrator_desc(gen, max_depth, rr_depth, phase_bins, range_bins, dr, 0, 0)
+    def set_integrator(self, gen, max_depth=-1, rr_depth=5, phase_bins=1, range_bins=0, dr=0.0, doppler=False):
+        """doppler=True restores the Doppler statement the reference has commented out (pathtimefrequency.cpp:252-256)."""
+        d = N.bf_integrator_desc(gen, max_depth, rr_depth, phase_bins, range_bins, dr, 0, 1 if doppler else 0)
         self._ck(N.lib().bf_scene_set_integrator(self._h, C.byref(d)), "bf_scene_set_integrator")
+
+    def update_transform(self, shape, motion):
+        """bf_scene_update_transform: re-pose a rectangle (to_world) or move a mesh (motion applied to the vertices as added);
+        after commit() a mesh is refitted on the device, without a rebuild."""
+        m = _f32(motion).reshape(16)
+        self._ck(N.lib().bf_scene_update_transform(self._h, shape, _fp(m)), "bf_scene_update_transform")
+
+    def set_shape_velocity(self, shape, velocity):
+        """The shape's `velocity` transform (shape.cpp:39-42), a 4 x 4 matrix; read by Shape::doppler only."""
+        m = _f32(velocity).reshape(16)
+        self._ck(N.lib().bf_scene_set_shape_velocity(self._h, shape, _fp(m)), "bf_scene_set_shape_velocity")
 
     def update_rect(self, shape, to_world):
         m = _f32(to_world).reshape(16)

@@ -164,7 +164,10 @@ typedef struct bf_integrator_desc {
     uint32_t range_bins;   /* gen 2: range.cpp "bins"; gen 1 fixed 50 */
     float dr;              /* gen 2: range.cpp "dr" */
     uint32_t rng_mode;     /* 0 = per-sample streams (sampler.cpp:89-92), the only GPU mode */
-    uint32_t reserved;
+    uint32_t doppler;      /* gen 3.  0 (default) = what the reference executes today: its Doppler statements are commented out
+                            * ("Took doppler out to test", pathtimefrequency.cpp:124-126, 141-144, 252-256).  1 = the statement of
+                            * :254-256 restored: after the transmitter connection of every bounce the path's wavelengths are shifted
+                            * by Shape::doppler of the shape hit (shape.cpp:375-389), from its `velocity` transform. */
 } bf_integrator_desc;
 
 /* Per-sample record written by bf_debug_sample_records (parity hook, no reference
@@ -215,6 +218,10 @@ int bf_scene_add_mesh(bf_scene *s, const float *positions, uint32_t n_vertices,
 int bf_scene_add_rect(bf_scene *s, const float to_world[16], uint32_t bsdf_id,
                       uint32_t *shape_id);
 
+/* The shape's `velocity` transform (Shape::Shape, src/librender/shape.cpp:39-42; default identity).  Only read by
+ * Shape::doppler (shape.cpp:375-389), i.e. when the integrator's doppler flag is set.  Before or after bf_scene_commit. */
+int bf_scene_set_shape_velocity(bf_scene *s, uint32_t shape_id, const float velocity[16]);
+
 /* Endpoint attached to a shape (Shape::Shape, src/librender/shape.cpp:38-99) or free
  * standing (shape_id = BF_NONE: spot, perspective). */
 int bf_scene_add_transmitter(bf_scene *s, uint32_t shape_id, const bf_endpoint_desc *desc,
@@ -227,6 +234,14 @@ int bf_scene_set_integrator(bf_scene *s, const bf_integrator_desc *desc);
  * compressed 8-wide nodes, upload.  Re-commit after bf_scene_update_* is allowed. */
 int bf_scene_commit(bf_scene *s, int device);
 int bf_scene_update_rect(bf_scene *s, uint32_t shape_id, const float to_world[16]);
+/* Moving geometry between frames (the reference rebuilds its whole scene per frame, python_scripts/animated_trans_rad.py:289-311).
+ * Rectangle: the same as bf_scene_update_rect.  Mesh: `motion` is applied to the vertices AS GIVEN to bf_scene_add_mesh (the rest
+ * pose; motions do not accumulate), with Transform::transform_affine's fp32 operations (transform.h:91-99); vertex normals get the
+ * inverse transpose and are re-normalised (mesh.cpp:117-124).  Before bf_scene_commit the moved vertices go into the build; after
+ * it the device triangles are re-posed and the 8-wide BVH is REFITTED (same topology, new boxes, one small kernel per tree level)
+ * on the scene's stream, without a rebuild or a host synchronisation.  Hits on a refitted scene equal those of a scene built on the
+ * moved vertices bit for bit (same triangles); only the traversal cost can degrade when the motion is large. */
+int bf_scene_update_transform(bf_scene *s, uint32_t shape_id, const float motion[16]);
 /* Copy the flattened geometry (BVH nodes, triangles, normals) again from the library's pinned host
  * image to the device without rebuilding: the host->device leg of Scene::accel_init_gpu
  * (scene_optix.inl:236-300) on its own, used to time the path end to end from host buffers. */

@@ -15,6 +15,8 @@
  *   BF_TAG_RX       : u32 shape, u32 pad, bf_endpoint_desc
  *   BF_TAG_ADC      : bf_adc_desc
  *   BF_TAG_INTEGRATOR : bf_integrator_desc
+ *   BF_TAG_VELOCITY : u32 shape, u32 pad, float velocity[16]
+ *   BF_TAG_MESH_MOTION : u32 shape, u32 pad, float motion[16]   (bf_scene_update_transform on a mesh; the last record per shape wins)
  */
 #ifndef BEIFONG_B200_FLAT_SCENE_H
 #define BEIFONG_B200_FLAT_SCENE_H
@@ -36,7 +38,7 @@ typedef struct bf_flat_header {
 
 enum {
     BF_TAG_SPECTRUM = 1, BF_TAG_BSDF = 2, BF_TAG_MESH = 3, BF_TAG_RECT = 4,
-    BF_TAG_TX = 5, BF_TAG_RX = 6, BF_TAG_ADC = 7, BF_TAG_INTEGRATOR = 8
+    BF_TAG_TX = 5, BF_TAG_RX = 6, BF_TAG_ADC = 7, BF_TAG_INTEGRATOR = 8, BF_TAG_VELOCITY = 9, BF_TAG_MESH_MOTION = 10
 };
 
 typedef struct bf_flat_record {

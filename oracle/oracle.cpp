@@ -69,7 +69,8 @@ struct SI {
 struct PI { float t = Infinity; V2 uv; uint32_t prim = 0; int shape = -1; };
 
 struct SpectrumTex { uint32_t kind = 0; std::vector<float> lambda, value; float inv_interval = 0; };
-struct MeshData { std::vector<float> pos; std::vector<uint32_t> idx; std::vector<float> nrm; uint32_t nv = 0, nf = 0; };
+struct MeshData { std::vector<float> pos; std::vector<uint32_t> idx; std::vector<float> nrm; uint32_t nv = 0, nf = 0;
+                  std::vector<float> pos_rest, nrm_rest; /* as imported: BF_TAG_MESH_MOTION moves the mesh from this pose */ };
 struct RectData { M4 to_world, to_object; Frame frame; float inv_area = 0, area = 0; };
 struct ShapeRec { int type = 0; /*0 mesh 1 rect*/ int index = 0; uint32_t bsdf = 0; int tx = -1; bool is_rx = false; };
 // Virtual element (i, j) of a phased array: phasedtransmitter.cpp:119-167 == phasedreceiver.cpp:115-173
@@ -113,6 +114,7 @@ struct Scene {
     std::vector<MeshData> meshes;
     std::vector<RectData> rects;
     std::vector<ShapeRec> shapes;
+    std::vector<M4> velocities;      // per shape, identity by default (shape.cpp:39-42)
     std::vector<TxRec> txs;
     int rx_shape = -1; bf_endpoint_desc rx; bool has_rx = false;
     M4 rx_to_world;
@@ -1168,6 +1170,15 @@ static PathOut path_time_frequency(const Scene &sc, Sampler &sampler, Ray &ray_,
         bool active_e = active && bsdf_is_smooth(sc, bsdf);
         if (active_e) {
             TxDirResult tr = scene_sample_transmitter_direction(sc, si, sampler.next_2d(), cnt);
+            if (sc.integ.doppler) {
+                // pathtimefrequency.cpp:252-256 (commented out in the reference; restored behind bf_integrator_desc::doppler):
+                // wavelengths += si.shape->doppler(si), Shape::doppler = 2*dot(si.wi, m_velocity*Point3f(si.to_local(si.p)))/MTS_C*si.wavelengths (shape.cpp:375-389)
+                M4 vel; memset(&vel, 0, sizeof(vel)); for (int i = 0; i < 4; ++i) vel.m[i][i] = 1.f;
+                if (si.shape < sc.velocities.size()) vel = sc.velocities[si.shape];
+                const V3 vp = xf_point(vel, si.to_local(si.p));
+                const float f = 2 * dot(si.wi, vp) / sc.C.c;
+                for (int k = 0; k < sc.S; ++k) si.wl.v[k] += f * si.wl.v[k];
+            }
             active_e &= tr.ds.pdf != 0.f;
             V3 wo = si.to_local(tr.ds.d);
             Spec bsdf_val = active_e ? bsdf_eval(sc, bsdf, si, wo) : Spec(0.f);
@@ -1539,6 +1550,31 @@ orc_scene *orc_scene_import(const void *blob, size_t bytes) {
             }
             case BF_TAG_ADC: sc.adc = *(const bf_adc_desc *) pl; break;
             case BF_TAG_INTEGRATOR: sc.integ = *(const bf_integrator_desc *) pl; break;
+            case BF_TAG_MESH_MOTION: {
+                // bf_scene_update_transform on a mesh: world = motion * rest (Transform::transform_affine, transform.h:91-99);
+                // normals by the inverse transpose, re-normalised (mesh.cpp:117-124)
+                uint32_t shape = *(const uint32_t *) pl;
+                if (shape >= sc.shapes.size() || sc.shapes[shape].type != 0) break;
+                MeshData &m = sc.meshes[sc.shapes[shape].index];
+                if (m.pos_rest.empty()) { m.pos_rest = m.pos; m.nrm_rest = m.nrm; }
+                M4 M = M4::from_rows16((const float *) (pl + 8)), Minv = inverse(M);
+                for (uint32_t v = 0; v < m.nv; ++v) {
+                    V3 p = xf_point_affine(M, V3(m.pos_rest[3 * v], m.pos_rest[3 * v + 1], m.pos_rest[3 * v + 2]));
+                    m.pos[3 * v] = p.x; m.pos[3 * v + 1] = p.y; m.pos[3 * v + 2] = p.z;
+                    if (!m.nrm_rest.empty()) {
+                        V3 n = xf_normal(Minv, V3(m.nrm_rest[3 * v], m.nrm_rest[3 * v + 1], m.nrm_rest[3 * v + 2]));
+                        if (n.x != 0.f || n.y != 0.f || n.z != 0.f) n = normalize(n);
+                        m.nrm[3 * v] = n.x; m.nrm[3 * v + 1] = n.y; m.nrm[3 * v + 2] = n.z;
+                    }
+                }
+                break;
+            }
+            case BF_TAG_VELOCITY: {
+                uint32_t shape = *(const uint32_t *) pl;
+                if (sc.velocities.size() < sc.shapes.size()) { M4 id; memset(&id, 0, sizeof(id)); for (int i = 0; i < 4; ++i) id.m[i][i] = 1.f; sc.velocities.resize(sc.shapes.size(), id); }
+                if (shape < sc.velocities.size()) memcpy(sc.velocities[shape].m, pl + 8, 64);
+                break;
+            }
             default: break;
         }
         off += sizeof(bf_flat_record) + ((r->payload_bytes + 7) & ~(size_t) 7);

@@ -110,8 +110,9 @@ class PlateScene:
         return 4.0 * tri(rx) * tri(ry) * sinc(2.0 * math.pi * nux * wid * tri(rx)) * sinc(2.0 * math.pi * nuy * wid * tri(ry))
 
 
-def evaluate_sample(sc, seed, idx):
-    """-> dict(first_t, valid, tf_t, tf_f, value, phase, depth) of sample `idx`; None when the path leaves the modelled cases."""
+def evaluate_sample(sc, seed, idx, plate_velocity=None):
+    """-> dict(first_t, valid, tf_t, tf_f, value, phase, depth, wavelength0) of sample `idx`; None when the path leaves the modelled cases.
+    plate_velocity = (vx, vy, vz): the integrator's doppler flag is set and the plate's `velocity` transform is that translation."""
     rng = PCG32(tea64(seed, idx), tea64(idx, seed))
     # ---- receive_sample head: src/librender/integrator.cpp:1544-1569 ----
     pos = (rng.next_float(), rng.next_float())
@@ -185,6 +186,15 @@ def evaluate_sample(sc, seed, idx):
         p2 = p1 + t2 * d2
         if abs(p2[0]) <= sc.floor_half and abs(p2[1]) <= sc.floor_half:
             phase = 2.0 * math.pi * (-t2) / denom                 # spawn_ray starts a fresh ray (phase 0); ray_.phase += ray.phase
+    if plate_velocity is not None:
+        # Shape::doppler (src/librender/shape.cpp:375-389) at the statement of pathtimefrequency.cpp:254-256 (commented out in the
+        # reference, behind a flag here): 2 * dot(si.wi, velocity * Point3f(si.to_local(si.p))) / MTS_C * si.wavelengths, with the hit
+        # position expressed in the plate's shading frame (s, t, n) = ((1, 0, 0), (0, -1, 0), (0, 0, -1)), as the reference writes it
+        p_loc = np.array([p1[0], -p1[1], -p1[2]]) + np.asarray(plate_velocity, float)
+        wi = np.array([-d[0], d[1], d[2]])
+        fshift = F(2.0 * float(wi @ p_loc) / sc.c32)
+        lam2 = F(lam2 + fshift * lam2)
+    out["wavelength0"] = float(lam2)
     # ---- receive_sample tail: integrator.cpp:1588-1665 ----
     f_end = sc.c32 * (1.0 / (float(lam2) * 1e-9))
     out["tf_f"] = abs(f_end - float(F(f_rx))) * sc.f_bins / sc.f_bw      # f_rx is stored in a fp32 Wavelength (:1592)

@@ -16,13 +16,15 @@ from plate_path import PlateScene, evaluate_sample
 from record_binning import profile_from_records
 
 
-def build(sc):
+def build(sc, plate_velocity=None):
     s = FlatScene(spectrum_width=1, **RADAR_94GHZ)
     dflt = s.add_diffuse(0.5, two_sided=False)
     plate_m = s.add_diffuse(sc.rho, two_sided=False)
     rx = s.add_rect((T.scale([sc.a, sc.a, 1.0])).matrix32(), dflt)
     tx = s.add_rect((T.translate([0.0, sc.tx_y, 0.0]) * T.scale([sc.a, sc.a, 1.0])).matrix32(), dflt)
-    s.add_rect((T.translate([0.0, 0.0, sc.R]) * T.rotate([1, 0, 0], 180.0) * T.scale([sc.plate_half, sc.plate_half, 1.0])).matrix32(), plate_m)
+    plate = s.add_rect((T.translate([0.0, 0.0, sc.R]) * T.rotate([1, 0, 0], 180.0) * T.scale([sc.plate_half, sc.plate_half, 1.0])).matrix32(), plate_m)
+    if plate_velocity is not None:
+        s.set_shape_velocity(plate, T.translate(list(plate_velocity)).matrix32())
     s.add_rect((T.translate([0.0, 0.0, sc.floor_z]) * T.scale([sc.floor_half, sc.floor_half, 1.0])).matrix32(), plate_m)
     tex = s.add_uniform(1.0)
     sig = dict(amplitude=1.0, repfreq=sc.repfreq, t_ext=sc.t_ext, f_centre=sc.f_c, f_ext=sc.f_ext, gain=1.0)
@@ -30,16 +32,16 @@ def build(sc):
     s.set_receiver(rx, FlatScene.endpoint(N.BF_RX_WIGNER, texture=tex, signal=FlatScene.signal(N.BF_SIG_LINFMCW, sig_is_delta=True, resample_freq=False, **sig),
                                           receive_type=N.BF_RECV_MIX_RESAMPLE, adc_sampling_start=sc.adc_start, adc_sampling_time=sc.adc_time))
     s.set_adc(t_bins=sc.t_bins, f_bins=sc.f_bins, t_bandwidth=sc.t_bw, f_bandwidth=sc.f_bw)
-    s.set_integrator(N.BF_GEN_PHASE, max_depth=2, rr_depth=5, phase_bins=1)
+    s.set_integrator(N.BF_GEN_PHASE, max_depth=2, rr_depth=5, phase_bins=1, doppler=plate_velocity is not None)
     return s
 
 
-def check_records(sc, rec, seed, idxs):
+def check_records(sc, rec, seed, idxs, plate_velocity=None):
     """Every modelled sample of `idxs` against the numpy evaluation."""
     n_checked = n_valid = n_phase = 0
     worst = 0.0
     for i in idxs:
-        e = evaluate_sample(sc, seed, int(i))
+        e = evaluate_sample(sc, seed, int(i), plate_velocity)
         if e is None:
             continue
         r = rec[i]
@@ -52,9 +54,11 @@ def check_records(sc, rec, seed, idxs):
         n_valid += 1
         assert r["first_t"] == pytest.approx(e["first_t"], rel=3e-6)
         assert int(r["depth"]) == e["depth"]
+        if plate_velocity is not None:      # the Doppler-shifted wavelength itself, to fp32 rounding
+            assert r["wavelength0"] == pytest.approx(e["wavelength0"], rel=3e-7), (i, r["wavelength0"], e["wavelength0"])
         # beat-frequency bin coordinate: a difference of two ~1e11 Hz values; the fp32 roundings of the two wavelengths are
         # reproduced by the evaluator, so it agrees to a small fraction of a bin
-        assert r["tf_f"] == pytest.approx(e["tf_f"], abs=0.02 + 1e-5 * e["tf_f"]), (i, r["tf_f"], e["tf_f"])
+        assert r["tf_f"] == pytest.approx(e["tf_f"], abs=(0.02 if plate_velocity is None else 1.5) + 1e-5 * e["tf_f"]), (i, r["tf_f"], e["tf_f"])
         scale = max(abs(e["value"]), 1e-12)
         worst = max(worst, abs(r["value"] - e["value"]) / scale)
         assert r["value"] == pytest.approx(e["value"], rel=2e-3, abs=1e-9), (i, r["value"], e["value"])
@@ -89,6 +93,45 @@ def test_oracle_reproduces_the_independent_path_evaluation():
     energy = np.abs(prof[..., 0]).sum(axis=1)
     assert abs(int(np.argmax(energy)) - int(k)) <= 1
     assert energy[int(k) - 1:int(k) + 40].sum() >= 0.98 * energy.sum()       # oblique paths are longer: the tail lies above bin k
+    s.close(); orc.close()
+
+
+VELOCITY = (0.0, 0.0, 30.0)      # 30 m/s along the plate normal: a shift of ~2e-7 relative, ~19 kHz at 94 GHz, ~1.6 frequency bins
+
+
+def test_oracle_doppler_flag_against_the_independent_evaluation():
+    """Shape::doppler (shape.cpp:375-389) behind the integrator's doppler flag: the shifted wavelength and beat-frequency coordinate of
+    every sample against the numpy evaluation; with the flag off (the default, what the reference executes) the velocity is inert."""
+    sc = PlateScene()
+    s = build(sc, VELOCITY)
+    orc = OracleScene(s.export(), accel=OracleScene.BRUTE)
+    seed, n = 9, 1500
+    rec = orc.sample_records(n, seed=seed)
+    checked, valid, _, _ = check_records(sc, rec, seed, range(n), VELOCITY)
+    assert checked >= 0.99 * n and valid > 0.15 * n
+    off = build(sc)
+    off.set_shape_velocity(2, T.translate(list(VELOCITY)).matrix32())       # velocity present, flag off
+    rec_off = OracleScene(off.export(), accel=OracleScene.BRUTE).sample_records(n, seed=seed)
+    base = OracleScene(build(sc).export(), accel=OracleScene.BRUTE).sample_records(n, seed=seed)
+    assert rec_off.tobytes() == base.tobytes()
+    hit = rec["valid"] == 1
+    assert np.median(rec["tf_f"][hit] - base["tf_f"][hit]) > 0.5             # the approaching plate raises the beat frequency
+    s.close(); off.close(); orc.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("pipeline", ["wavefront", "mega"])
+def test_device_doppler_flag(native, pipeline):
+    sc = PlateScene()
+    s = build(sc, VELOCITY).commit()
+    s.set_tunable("mega_max", (1 << 28) if pipeline == "mega" else -1)
+    seed, n = 9, 1500
+    rec = s.sample_records(n, seed=seed)
+    checked, valid, _, _ = check_records(sc, rec, seed, range(n), VELOCITY)
+    assert checked >= 0.99 * n and valid > 0.15 * n
+    orc = OracleScene(s.export(), accel=OracleScene.BRUTE)
+    c = orc.sample_records(n, seed=seed)
+    assert np.array_equal(rec["wavelength0"].view(np.uint32)[rec["valid"] == 1], c["wavelength0"].view(np.uint32)[c["valid"] == 1])
     s.close(); orc.close()
 
 
