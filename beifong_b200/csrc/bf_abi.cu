@@ -506,7 +506,7 @@ static int check_endpoint(bf_scene *s, uint32_t shape_id, const bf_endpoint_desc
     if (!d) return fail(s, BF_ERR_INVALID, "endpoint: null descriptor");
     bool free_standing = is_tx ? d->kind == BF_TX_SPOT : d->kind == BF_RX_PERSPECTIVE;
     if ((is_tx && d->kind == BF_TX_PHASED) || (!is_tx && d->kind == BF_RX_PHASED)) {
-        if (d->array.n_elems < 1 || d->array.n_elems > BF_MAX_ARRAY_ELEMS) return fail(s, BF_ERR_INVALID, "phased endpoint: n_elems must be in [1, 16]");
+        if (d->array.n_elems < 1 || d->array.n_elems > BF_MAX_ARRAY_ELEMS) return fail(s, BF_ERR_INVALID, "phased endpoint: n_elems must be in [1, 64]");
         if (d->array.elem_dims[0] == 0.f || d->array.elem_dims[1] == 0.f || d->array.elem_dims[2] == 0.f)
             return fail(s, BF_ERR_INVALID, "phased endpoint: elem_dims has a zero component (scale() of the virtual element is singular)");
     }

@@ -96,7 +96,7 @@ enum { BF_RX_OMNIDIRECTIONAL = 0, BF_RX_WIGNER = 1, BF_RX_PHASED = 2, BF_RX_FLUX
 enum { BF_SIG_CW = 0, BF_SIG_LINFMCW = 1, BF_SIG_PULSE = 2, BF_SIG_OTHER = 3, BF_SIG_UNSET = 4 };
 enum { BF_RECV_RAW = 0, BF_RECV_RAW_RESAMPLE = 1, BF_RECV_MIX_RESAMPLE = 2, BF_RECV_MIXER = 3 };
 
-#define BF_MAX_ARRAY_ELEMS 16u
+#define BF_MAX_ARRAY_ELEMS 64u    /* config C5's 64-element array as ONE phased endpoint: 64^2 virtual elements */
 
 typedef struct bf_signal_desc {     /* wignertransmitter.cpp:59-102, phasedreceiver.cpp:67-113 */
     uint32_t signaltype;            /* BF_SIG_* */

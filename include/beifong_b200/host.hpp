@@ -131,16 +131,36 @@ struct Signal {
     }
 };
 
+// Phased array block of `phasedtransmitter` / `phasedreceiver` (phasedtransmitter.cpp:104-117): same property names.
+struct Array {
+    uint32_t n_elems = 1;
+    float steering_vector[3] = {0.f, 0.f, 0.f};
+    Matrix4f array_loc = {1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1};
+    float elem_dims[3] = {1.f, 1.f, 1.f}, elem_spacing[3] = {0.f, 0.f, 0.f}, elem_axis[3] = {0.f, 1.f, 0.f};
+    bf_array_desc desc() const {
+        bf_array_desc d;
+        std::memset(&d, 0, sizeof(d));
+        d.n_elems = n_elems;
+        std::memcpy(d.steering_vector, steering_vector, 12); std::memcpy(d.array_loc, array_loc, 64);
+        std::memcpy(d.elem_dims, elem_dims, 12); std::memcpy(d.elem_spacing, elem_spacing, 12); std::memcpy(d.elem_axis, elem_axis, 12);
+        return d;
+    }
+};
+
 // Receiver (src/librender/receiver.cpp:16-62 + src/receivers/*.cpp): owns its ADC like the reference's does.
 class Receiver {
 public:
-    // type: "omnidirectional" | "wignerreceiver" (the plugin names of src/receivers); receive_type as receiver.cpp:44-52
+    // type: "omnidirectional" | "wignerreceiver" | "phasedreceiver" (the plugin names of src/receivers); receive_type as receiver.cpp:44-52
     Receiver(const std::string &type, uint32_t shape_id, const ADC &adc, const Signal &signal = Signal(), const std::string &receive_type = "raw",
-             float adc_sampling_start = 0.f, float adc_sampling_end = 0.f, uint32_t antenna_texture = 0)
+             float adc_sampling_start = 0.f, float adc_sampling_end = 0.f, uint32_t antenna_texture = 0, const Array *array = nullptr)
         : m_shape(shape_id), m_adc(adc), m_receive_type(receive_type) {
         std::memset(&m_desc, 0, sizeof(m_desc));
         if (type == "omnidirectional") m_desc.kind = BF_RX_OMNIDIRECTIONAL;
         else if (type == "wignerreceiver") m_desc.kind = BF_RX_WIGNER;
+        else if (type == "phasedreceiver") {
+            if (!array) throw Error("phasedreceiver: the array parameters (n_elems, steering_vector, array_loc, elem_dims, elem_spacing, elem_axis) are required");
+            m_desc.kind = BF_RX_PHASED; m_desc.array = array->desc();
+        }
         else throw NotImplementedError("receiver plugin \"" + type + "\"");
         if (receive_type == "raw") m_desc.receive_type = BF_RECV_RAW;
         else if (receive_type == "raw_resample") m_desc.receive_type = BF_RECV_RAW_RESAMPLE;
@@ -202,12 +222,16 @@ public:
                                 normals.empty() ? nullptr : normals.data(), bsdf, &id), "bf_scene_add_mesh");
         return id;
     }
-    // <transmitter type="wignertransmitter|areatransmitter"> attached to a rectangle
-    uint32_t add_transmitter(const std::string &type, uint32_t shape_id, const Signal &signal, uint32_t antenna_texture) {
+    // <transmitter type="wignertransmitter|phasedtransmitter|areatransmitter"> attached to a rectangle
+    uint32_t add_transmitter(const std::string &type, uint32_t shape_id, const Signal &signal, uint32_t antenna_texture, const Array *array = nullptr) {
         bf_endpoint_desc d;
         std::memset(&d, 0, sizeof(d));
         if (type == "wignertransmitter") d.kind = BF_TX_WIGNER;
         else if (type == "areatransmitter") d.kind = BF_TX_AREA;
+        else if (type == "phasedtransmitter") {
+            if (!array) throw Error("phasedtransmitter: the array parameters are required");
+            d.kind = BF_TX_PHASED; d.array = array->desc();
+        }
         else throw NotImplementedError("transmitter plugin \"" + type + "\"");
         d.signal = signal.desc(); d.texture = antenna_texture;
         uint32_t id; check(bf_scene_add_transmitter(m_h, shape_id, &d, &id), "bf_scene_add_transmitter"); return id;
@@ -217,6 +241,10 @@ public:
     }
     // Moving geometry between frames (animated_trans_rad.py rebuilds the scene; here the rectangle is re-posed in place)
     void update_rectangle(uint32_t shape_id, const Matrix4f to_world) { check(bf_scene_update_rect(m_h, shape_id, to_world), "bf_scene_update_rect"); }
+    // <transform name="velocity"> of a shape (shape.cpp:39-42); read by Shape::doppler when the integrator's doppler flag is set
+    void set_shape_velocity(uint32_t shape_id, const Matrix4f velocity) { check(bf_scene_set_shape_velocity(m_h, shape_id, velocity), "bf_scene_set_shape_velocity"); }
+    // A mesh moved rigidly from the pose it was added in: goes into the build before commit(), a device refit (no rebuild) after it
+    void update_transform(uint32_t shape_id, const Matrix4f motion) { check(bf_scene_update_transform(m_h, shape_id, motion), "bf_scene_update_transform"); }
     // SAH build + upload; throws when there is no CUDA device (no CPU fallback)
     void commit(int device = 0) { check(bf_scene_commit(m_h, device), "bf_scene_commit"); m_committed = true; }
     bool committed() const { return m_committed; }
@@ -260,6 +288,8 @@ public:
         return names;
     }
     const bf_integrator_desc &desc() const { return m_desc; }
+    // Restores the Doppler statement the reference has commented out (pathtimefrequency.cpp:252-256); off by default.  Before prepare().
+    void set_doppler(bool on) { m_desc.doppler = on ? 1u : 0u; }
 
     // Configure the scene for this integrator and receiver (the part of Scene construction that depends on them) and
     // commit it.  Call once; receive() may then be called any number of times.
@@ -295,6 +325,17 @@ public:
         scene.check(bf_profile_read(scene.handle(), adc->m_storage.data(), adc->m_storage.size()), "bf_profile_read");   // adc->put(block)
         m_samples_done = done;
         return !m_stop;
+    }
+    // Many receive() calls as one submission (the frames of a sequence, the receivers of a scene: scene.h:197 holds a vector of them):
+    // item i re-poses rectangles and / or the receiver (bf_batch_item), then integrates `sample_count` samples into profile i.
+    // Returns [item][f][t][channel]; the receiver's ADC is not touched.
+    std::vector<float> receive_batch(Scene &scene, const std::vector<bf_batch_item> &items, uint64_t sample_count) {
+        if (!scene.committed()) throw Error("Integrator::receive_batch: call prepare() first");
+        uint32_t w = 0, h = 0, c = 0;
+        scene.check(bf_profile_size(scene.handle(), &w, &h, &c), "bf_profile_size");
+        std::vector<float> out((size_t) items.size() * w * h * c);
+        scene.check(bf_receive_batch(scene.handle(), (uint32_t) items.size(), items.data(), sample_count, out.data(), out.size()), "bf_receive_batch");
+        return out;
     }
     void cancel() { m_stop = true; }                 // integrator.cpp:48-51: only sets m_stop
     bool should_stop() const { return m_stop; }
