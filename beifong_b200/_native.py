@@ -111,6 +111,7 @@ PROTOTYPES = {
     "bf_batch_device_ptr": (C.c_int, [vp, P(vp), P(C.c_size_t), P(vp)]),
     "bf_profile_read": (C.c_int, [vp, P(f32), C.c_size_t]),
     "bf_profile_develop": (C.c_int, [vp, u32, vp, C.c_size_t]),
+    "bf_profile_power_db": (C.c_int, [vp, u32, C.c_double, C.c_int, P(f32), C.c_size_t]),
     "bf_profile_device_ptr": (C.c_int, [vp, P(vp), P(C.c_size_t), P(vp)]),
     "bf_synchronize": (C.c_int, [vp]),
     "bf_multi_unique_id": (C.c_int, [vp, C.c_size_t]),

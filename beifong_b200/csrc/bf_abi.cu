@@ -1384,6 +1384,21 @@ int bf_profile_develop(bf_scene *s, uint32_t component_format, void *dst, size_t
     return BF_OK;
 }
 
+int bf_profile_power_db(bf_scene *s, uint32_t channel, double sample_count, int mode, float *dst, size_t n_floats) {
+    if (!s || !dst) return BF_ERR_INVALID;
+    if (!s->committed) return fail(s, BF_ERR_STATE, "bf_profile_power_db: scene not committed");
+    const uint32_t C = s->dev.channels, bins = (uint32_t) (s->profile_floats / C);
+    if (channel >= C || !(sample_count > 0.0) || (mode != 0 && mode != 1)) return fail(s, BF_ERR_INVALID, "bf_profile_power_db: channel / sample_count / mode");
+    if (n_floats < bins) return fail(s, BF_ERR_INVALID, "bf_profile_power_db: destination too small");
+    BF_CUDA(cudaSetDevice(s->device));
+    BF_CUDA(s->d_developed.alloc(bins));
+    LaunchCfg cfg; memset(&cfg, 0, sizeof(cfg)); cfg.stream = s->stream; cfg.sm_count = s->sm_count;
+    s->stats.kernel_launches += launch_power_db(s->d_profile.p, (float *) s->d_developed.p, bins, C, channel, sample_count, mode, cfg);
+    BF_CUDA(cudaMemcpyAsync(dst, s->d_developed.p, (size_t) bins * 4, cudaMemcpyDeviceToHost, s->stream));
+    BF_CUDA(cudaStreamSynchronize(s->stream));
+    return BF_OK;
+}
+
 int bf_profile_device_ptr(bf_scene *s, void **dptr, size_t *n_floats, void **cuda_stream) {
     if (!s || !s->committed) return BF_ERR_STATE;
     if (dptr) *dptr = s->d_profile.p;

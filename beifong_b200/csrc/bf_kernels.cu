@@ -1620,6 +1620,26 @@ __global__ void __launch_bounds__(256) k_develop(const float *__restrict__ raw, 
     }
 }
 
+// Receive.ipynb cells 26-27 and 31: what the reference's scripts do with bitmap(raw=True) on the host, one value per bin --
+//   mode 0:  10 * log10(v * (v > 0) / sample_count + eps)       (cells 26-27; numpy promotes to float64, eps = 2^-52)
+//   mode 1:  10 * log10(|v| / sample_count + eps)               (cell 31, with sample_count = 1 there)
+// evaluated in double like numpy does, one thread per bin, reading channel `ch` of the raw profile.
+__global__ void __launch_bounds__(256) k_power_db(const float *__restrict__ raw, float *__restrict__ out, uint32_t n_bins, uint32_t C, uint32_t ch,
+                                                  double inv_count, int mode) {
+    const uint32_t stride = gridDim.x * blockDim.x;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n_bins; i += stride) {
+        const double v = (double) raw[(size_t) i * C + ch];
+        const double lin = (mode == 0 ? (v > 0.0 ? v : 0.0) : fabs(v)) * inv_count + 2.220446049250313e-16;
+        out[i] = (float) (10.0 * log10(lin));
+    }
+}
+int launch_power_db(const float *raw, float *out, uint32_t n_bins, uint32_t channels, uint32_t ch, double sample_count, int mode, const LaunchCfg &cfg) {
+    if (n_bins == 0) return 0;
+    const int grid = (int) std::min<uint32_t>((n_bins + 255) / 256, (uint32_t) cfg.sm_count * 8);
+    k_power_db<<<grid, 256, 0, cfg.stream>>>(raw, out, n_bins, channels, ch, 1.0 / sample_count, mode);
+    return 1;
+}
+
 int launch_develop(const float *raw, void *out, uint32_t n_bins, uint32_t channels, bool half_out, const LaunchCfg &cfg) {
     if (n_bins == 0 || channels < 2) return 0;
     const uint64_t total = (uint64_t) n_bins * (channels - 1u);

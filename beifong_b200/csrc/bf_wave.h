@@ -85,6 +85,7 @@ int launch_finalize(const DevScene &sc, const Wave &w, uint32_t n, float *profil
 int launch_refit_tris(const float4 *rest, const float4 *rest_nrm, float4 *tris, float4 *nrm, uint32_t n_tris, uint32_t shape, const M4 &M, const M4 &Minv,
                       const LaunchCfg &cfg);
 int launch_refit_nodes(uint4 *nodes, const float4 *tris, float *node_box, const uint32_t *level_first, uint32_t n_levels, float pad_abs, const LaunchCfg &cfg);
+int launch_power_db(const float *raw, float *out, uint32_t n_bins, uint32_t channels, uint32_t ch, double sample_count, int mode, const LaunchCfg &cfg);
 int launch_develop(const float *raw, void *out, uint32_t n_bins, uint32_t channels, bool half_out, const LaunchCfg &cfg);
 // Stand-alone ray queries (Scene::ray_intersect_preliminary / ray_test for caller-provided rays)
 int launch_trace_rays(const DevScene &sc, const float4 *ray_o, const float4 *ray_d, uint32_t n, float4 *hit, uint32_t *occl,

@@ -6,6 +6,7 @@ reference raises for the same condition: `RuntimeError` for `Throw(...)`, `NotIm
 unsupported plugins (include/mitsuba/core/logger.h:134-138).
 """
 import ctypes as C
+import os
 
 import numpy as np
 
@@ -288,6 +289,37 @@ class FlatScene:
         out = np.empty((h, w, max(c - 1, 0)), dtype=fmt[1])
         self._ck(N.lib().bf_profile_develop(self._h, fmt[0], out.ctypes.data_as(C.c_void_p), out.nbytes), "bf_profile_develop")
         return out
+
+    def channel_names(self, raw=True):
+        """Channel names of bitmap(raw): gen 3 ["Y", "A", "W"] + "phase.bin<k>" (integrator.cpp:359-370, phase.cpp:140-145); the developed
+        bitmap drops the weight channel (hdradc.cpp:246-266)."""
+        h, w, c = self.profile_shape()
+        names = ["Y", "A", "W"] + [f"phase.bin{k}" for k in range(c - 3)]
+        return names if raw else [n for n in names if n != "W"]
+
+    def develop(self, filename, component_format="float16"):
+        """HDRADC::develop() (hdradc.cpp:277-295): the developed bitmap written as a multichannel OpenEXR file; the extension is
+        forced to ".exr" as the reference does.  Returns the path written."""
+        from . import exr
+        if not filename:
+            raise BeifongError("Destination file not specified, cannot develop.")
+        root, ext = os.path.splitext(filename)
+        path = filename if ext.lower() == ".exr" else root + ".exr"
+        exr.write_exr(path, self.bitmap(raw=False, component_format=component_format), self.channel_names(raw=False))
+        return path
+
+    def power_db(self, sample_count, channel=0, mode="mask"):
+        """The scripts' own post-processing on the device (Receive.ipynb cells 26-27: mode "mask"; cell 31: mode "abs"):
+        10 log10(v (v > 0) / sample_count + eps) resp. 10 log10(|v| / sample_count + eps), one value per bin -> [f][t] float32."""
+        h, w, c = self.profile_shape()
+        out = np.empty((h, w), dtype=np.float32)
+        self._ck(N.lib().bf_profile_power_db(self._h, int(channel), float(sample_count), {"mask": 0, "abs": 1}[mode], _fp(out), out.size), "bf_profile_power_db")
+        return out
+
+    @staticmethod
+    def range_axis(tr_min, tr_max, bins):
+        """Receive.ipynb cells 26-27, 31: xvals = linspace(tr_min, tr_max, tr_bins) / 2 (two-way path length -> range)."""
+        return np.linspace(tr_min, tr_max, bins) / 2
 
     def profile_device(self):
         """(device pointer, n_floats, cuda stream handle) of the accumulated profile."""

@@ -291,6 +291,11 @@ int bf_profile_read(bf_scene *s, float *dst, size_t n_floats);
  * "Y" field the unnamed source does not have) return BF_ERR_UNSUPPORTED. */
 enum { BF_COMPONENT_FLOAT32 = 0, BF_COMPONENT_FLOAT16 = 1 };
 int bf_profile_develop(bf_scene *s, uint32_t component_format, void *dst, size_t dst_bytes);
+/* The scripts' own post-processing of bitmap(raw=True) (python_scripts/Receive.ipynb cells 26-27, 31), one value per bin of one
+ * channel, evaluated on the device in double as numpy does:  mode 0: 10 log10(v (v > 0) / sample_count + eps);
+ * mode 1: 10 log10(|v| / sample_count + eps), eps = 2^-52.  dst: [f][t] fp32, n_floats >= bins.  Synchronises the scene's stream.
+ * The range axis of those plots is linspace(tr_min, tr_max, bins) / 2 (host arithmetic, not offered here). */
+int bf_profile_power_db(bf_scene *s, uint32_t channel, double sample_count, int mode, float *dst, size_t n_floats);
 /* Device pointer of the accumulated profile + the stream it is produced on (for a caller
  * that reduces it with NCCL, §8e). */
 int bf_profile_device_ptr(bf_scene *s, void **dptr, size_t *n_floats, void **cuda_stream);
