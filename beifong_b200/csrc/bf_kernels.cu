@@ -411,7 +411,8 @@ struct ShadeOut {
 // device functions are then inlined with their other branches folded away, which keeps the executed code inside the 32 KB
 // instruction cache and the intermediate structs in registers); -1: read from the scene (out-of-line generic functions).
 // TX_HIT = false: the caller guarantees that the surface hit carries no transmitter (k_path parks only such hits).
-template <int S, int GEN, int TXK, int BK, bool TX_HIT = true>
+// DOPPLER = false: the kernel is never launched for a scene with the integrator's doppler flag set (the specialised instantiations).
+template <int S, int GEN, int TXK, int BK, bool TX_HIT = true, bool DOPPLER = true>
 __device__ __forceinline__ void shade_core(const DevScene &sc, uint32_t depth, LaneRegs<S> &R, bf_sample_record *rec, ShadeOut &out) {
     const uint32_t gen = GEN >= 0 ? (uint32_t) GEN : sc.integ.gen;
     bool push_next = false, push_shadow = false;
@@ -497,7 +498,7 @@ __device__ __forceinline__ void shade_core(const DevScene &sc, uint32_t depth, L
 #pragma unroll
                 for (int k = 0; k < S; ++k) tspec.v[k] *= inv;
             }
-            if (gen == BF_GEN_PHASE && sc.integ.doppler) {
+            if (DOPPLER && gen == BF_GEN_PHASE && sc.integ.doppler) {
                 // pathtimefrequency.cpp:252-256, commented out in the reference ("Took doppler out to test"), behind the flag
                 const Spec<S> shift = shape_doppler<S>(sc, si, wl);
 #pragma unroll
@@ -611,7 +612,7 @@ __global__ void __launch_bounds__(128, BF_SHADE_MIN_BLOCKS) k_shade(const __grid
             R.o = V3(ro.x, ro.y, ro.z); R.d = V3(rd.x, rd.y, rd.z);
             R.time = x1.x; R.phase = x1.y; R.bs_pdf = x1.z; R.scalar = x1.w;
             ShadeOut so;
-            shade_core<S, GEN, TXK, BK>(sc, depth, R, w.records ? rec_of(w, l) : nullptr, so);
+            shade_core<S, GEN, TXK, BK, true, (GEN < 0)>(sc, depth, R, w.records ? rec_of(w, l) : nullptr, so);      // doppler scenes run the generic kernel
             push_next = so.push_next; push_shadow = so.push_shadow;
             if (push_next || push_shadow) {
                 w.ray_o[l] = make_float4(so.origin.x, so.origin.y, so.origin.z, so.mint);
@@ -1027,8 +1028,11 @@ __device__ __forceinline__ void scatter_splat(const Splat &sp, float *dst, uint3
     }
 }
 
+#ifndef PATH_BOUND_THREADS
+#define PATH_BOUND_THREADS PATH_THREADS      // register budget = 65536 / this
+#endif
 template <int S, int RXK, int TXK>
-__global__ void __launch_bounds__(PATH_THREADS, 1) k_path(const __grid_constant__ DevScene sc, const __grid_constant__ Wave w, const __grid_constant__ PathIO io) {
+__global__ void __launch_bounds__(PATH_BOUND_THREADS, 1) k_path(const __grid_constant__ DevScene sc, const __grid_constant__ Wave w, const __grid_constant__ PathIO io) {
     extern __shared__ __align__(16) uint32_t path_smem[];
     float *s_rect = reinterpret_cast<float *>(path_smem);                        // RECT_SM_FLOATS * BF_MAX_RECTS
     uint32_t *s_plain = path_smem + RECT_SM_FLOATS * BF_MAX_RECTS;               // per rectangle: 1 = diffuse class, no transmitter attached
@@ -1186,7 +1190,7 @@ __global__ void __launch_bounds__(PATH_THREADS, 1) k_path(const __grid_constant_
                 R.thr = Spec<S>(1.f); R.res = Spec<S>(0.f); R.pend = Spec<S>(0.f);
                 R.time = t_sample; R.phase = 0.f; R.bs_pdf = 0.f; R.scalar = 0.f;
                 bf_sample_record *rec = w.records ? w.records + smp : nullptr;
-                shade_core<S, BF_GEN_PHASE, TXK, BF_BSDF_DIFFUSE, false>(sc, 1u, R, rec, so);
+                shade_core<S, BF_GEN_PHASE, TXK, BF_BSDF_DIFFUSE, false, false>(sc, 1u, R, rec, so);
                 if (so.push_shadow) {
                     TraceLane T; T.o = so.origin; T.d = so.sh_d; T.mint = so.mint; T.maxt = so.sh_maxt;
                     if (trace_begin<true>(sc, s_rect, T)) {
@@ -1359,8 +1363,8 @@ static int launch_shade_s(const DevScene &sc, const Wave &w, uint32_t depth, con
 #define BF_SHADE_T(T_) do { \
         BF_SHADE(T_, BF_BSDF_DIFFUSE, 0); \
         if (sc.hint_cls1_bsdf == BF_BSDF_ROUGHCONDUCTOR) BF_SHADE(T_, BF_BSDF_ROUGHCONDUCTOR, 1); else BF_SHADE(T_, -1, 1); } while (0)
-    if (sc.integ.gen == BF_GEN_PHASE && sc.n_txs == 1 && sc.hint_tx_kind == BF_TX_WIGNER) { BF_SHADE_T(BF_TX_WIGNER); return 2; }
-    if (sc.integ.gen == BF_GEN_PHASE && sc.n_txs == 1 && sc.hint_tx_kind == BF_TX_AREA) { BF_SHADE_T(BF_TX_AREA); return 2; }
+    if (sc.integ.gen == BF_GEN_PHASE && sc.n_txs == 1 && !sc.integ.doppler && sc.hint_tx_kind == BF_TX_WIGNER) { BF_SHADE_T(BF_TX_WIGNER); return 2; }
+    if (sc.integ.gen == BF_GEN_PHASE && sc.n_txs == 1 && !sc.integ.doppler && sc.hint_tx_kind == BF_TX_AREA) { BF_SHADE_T(BF_TX_AREA); return 2; }
 #undef BF_SHADE_T
 #undef BF_SHADE
     k_shade<S, -1, -1, -1, 2><<<grid, 128, 0, cfg.stream>>>(sc, w, depth, hit_counts, next_queue, ctr_block);
@@ -1411,7 +1415,7 @@ static size_t path_smem_bytes(uint32_t hist_floats) {
     return ((size_t) RECT_SM_FLOATS * BF_MAX_RECTS + BF_MAX_RECTS + 4 + hist_floats) * 4;
 }
 bool path_kernel_available(const DevScene &sc) {
-    return sc.integ.gen == BF_GEN_PHASE && sc.n_txs == 1 && (sc.hint_tx_kind == BF_TX_WIGNER || sc.hint_tx_kind == BF_TX_AREA) &&
+    return sc.integ.gen == BF_GEN_PHASE && !sc.integ.doppler && sc.n_txs == 1 && (sc.hint_tx_kind == BF_TX_WIGNER || sc.hint_tx_kind == BF_TX_AREA) &&
            (sc.hint_rx_kind == BF_RX_WIGNER || sc.hint_rx_kind == BF_RX_OMNIDIRECTIONAL) && sc.n_nodes != 0;
 }
 size_t path_stash_bytes(const DevScene &sc, int sm_count) {

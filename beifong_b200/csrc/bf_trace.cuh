@@ -23,6 +23,12 @@ namespace bf {
 #ifndef TRACE_MIN_BLOCKS
 #define TRACE_MIN_BLOCKS 8
 #endif
+#ifndef TRACE_TRI_QUEUE
+#define TRACE_TRI_QUEUE 8    // k_trace: triangle slots a lane can queue for the warp's triangle phase (0: test them right behind the node step)
+#endif
+#ifndef TRACE_TRI_LANES
+#define TRACE_TRI_LANES 12   // the triangle phase starts when this many lanes hold queued triangles (and runs down to half of it)
+#endif
 #ifndef TRACE_TRI_MIN
 #define TRACE_TRI_MIN 0      // > 0: triangle tests are postponed when fewer lanes than this are testing.  Measured slower on C2 (8 / 16 / 24: trace_closest 1.93 / 1.88 / 1.92 ms per 64 M samples against 1.69 ms without, profiles/r02e), so off
 #endif
@@ -155,15 +161,11 @@ __device__ __forceinline__ bool trace_begin(const DevScene &sc, const float *s_r
 // the triangles of the leaves hit.  Returns false when the traversal is finished.
 // Closest hit: lowest t, ties broken by the lowest (shape, prim) — the order a brute-force loop over the
 // scene's shapes visits them in (ray_intersect_naive, scene_native.inl:43-61).
-template <bool ANY_HIT>
-__device__ __forceinline__ bool trace_step(const DevScene &sc, uint2 *s_stack, uint2 *l_stack, TraceLane &L) {
+// The node half of a traversal step: pops one child of the current node group, tests its 8 quantised child boxes.  On return
+// L.ngroup holds the inner children hit and `tgroup` the leaf triangles hit (base slot, bit mask).  Precondition: L.ngroup has a node.
+__device__ __forceinline__ void node_step(const DevScene &sc, uint2 *s_stack, uint2 *l_stack, TraceLane &L, uint2 &tgroup) {
     const uint32_t tid = threadIdx.x;
-    uint2 tgroup = make_uint2(0u, 0u);
-    if (L.ngroup.y <= 0x00ffffffu) {
-        // the entry popped last was a parked triangle group (see below)
-        tgroup = L.ngroup;
-        L.ngroup = make_uint2(0u, 0u);
-    } else {
+    {
         const uint32_t hits_imask = L.ngroup.y;
         const uint32_t child_bit_index = 31u - __clz(hits_imask);
         const uint32_t child_node_base = L.ngroup.x;
@@ -223,6 +225,20 @@ __device__ __forceinline__ bool trace_step(const DevScene &sc, uint2 *s_stack, u
         }
         L.ngroup.y = (hitmask & 0xff000000u) | imask;
         tgroup.y = hitmask & 0x00ffffffu;
+    }
+
+}
+
+template <bool ANY_HIT>
+__device__ __forceinline__ bool trace_step(const DevScene &sc, uint2 *s_stack, uint2 *l_stack, TraceLane &L) {
+    const uint32_t tid = threadIdx.x;
+    uint2 tgroup = make_uint2(0u, 0u);
+    if (L.ngroup.y <= 0x00ffffffu) {
+        // the entry popped last was a parked triangle group (see below)
+        tgroup = L.ngroup;
+        L.ngroup = make_uint2(0u, 0u);
+    } else {
+        node_step(sc, s_stack, l_stack, L, tgroup);
     }
 
     // Triangle tests: the lanes of a warp have very different numbers of them after a node step.  Once fewer than
@@ -304,6 +320,10 @@ template <bool ANY_HIT, bool DEFER = false>
 __global__ void __launch_bounds__(TRACE_THREADS, TRACE_MIN_BLOCKS) k_trace(const __grid_constant__ DevScene sc, const __grid_constant__ TraceIO io) {
     __shared__ float s_rect[RECT_SM_FLOATS * BF_MAX_RECTS];
     __shared__ uint2 s_stack[TRACE_SM_STACK * TRACE_THREADS];
+    // closest-hit queries queue their triangle tests (measured on C3: 1 537 us against 1 675 us, 16.7 against 13.9 threads per
+    // instruction, profiles/r02n); any-hit queries test on the spot (an early hit ends the ray: queueing made them slower)
+    constexpr int TQ = ANY_HIT ? 0 : TRACE_TRI_QUEUE;
+    __shared__ uint32_t s_tq[TQ > 0 ? TQ * TRACE_THREADS : 1];      // per-lane queue of triangle slots awaiting their test
     uint2 l_stack[TRACE_LOCAL_STACK];
     stage_rects(sc, s_rect);
     const uint32_t n = io.queue ? *io.count : io.n_direct;
@@ -346,6 +366,8 @@ __global__ void __launch_bounds__(TRACE_THREADS, TRACE_MIN_BLOCKS) k_trace(const
     enum { EMPTY = 0, BUSY = 1, FINISHED = 2, EXHAUSTED = 3 };
     int state = EMPTY;
     uint32_t l = 0, n_steps = 0, pend_l = 0;
+    uint32_t qcnt = 0;                      // triangles queued in s_tq for this lane
+    uint2 tpend = make_uint2(0u, 0u);       // triangle group of the last node step not yet expanded into the queue
     TraceLane L;
     while (true) {
         // ---- complete the push reserved at the previous commit point ----
@@ -422,7 +444,7 @@ __global__ void __launch_bounds__(TRACE_THREADS, TRACE_MIN_BLOCKS) k_trace(const
                     l = io.queue ? ld_stream(io.queue + i) : i;
                     float4 ro = ld_stream(io.ray_o + l), rd = ld_stream(io.ray_d + l);
                     L.o = V3(ro.x, ro.y, ro.z); L.d = V3(rd.x, rd.y, rd.z); L.mint = ro.w; L.maxt = rd.w;
-                    n_steps = 0;
+                    n_steps = 0; qcnt = 0u; tpend = make_uint2(0u, 0u);
                     const bool traverse = trace_begin<ANY_HIT>(sc, s_rect, L);
                     if (DEFER) { deferred = traverse; state = FINISHED; }
                     else state = traverse ? BUSY : FINISHED;
@@ -444,11 +466,57 @@ __global__ void __launch_bounds__(TRACE_THREADS, TRACE_MIN_BLOCKS) k_trace(const
         // lanes actually traverse, so that a node step is never run for a handful of lanes
         if (!drained && fin != 0 && __popc(busy) < min_busy) continue;
         // ---- traverse until too few lanes are left ----
+        if (TQ == 0) {
+            do {
+                if (state == BUSY) {
+                    ++n_steps;
+                    if (!trace_step<ANY_HIT>(sc, s_stack, l_stack, L)) state = FINISHED;
+                }
+            } while (__popc(__ballot_sync(0xffffffffu, state == BUSY)) >= min_busy);
+            continue;
+        }
+        // Two phases per iteration.  NODE: every busy lane does one node step; the leaf triangles it finds are not tested on the
+        // spot (after a node step ~2 of 32 lanes have one: profiles/r02e) but QUEUED, slot by slot, in the lane's shared-memory
+        // queue.  TRIANGLE: when enough lanes hold queued triangles (or nothing else is left to do) those lanes test one triangle
+        // each per pass, for as long as enough of them have some; what is left stays queued.  Results do not depend on the order
+        // of the tests: closest-hit ties are broken by (shape, prim).
         do {
             if (state == BUSY) {
-                ++n_steps;
-                if (!trace_step<ANY_HIT>(sc, s_stack, l_stack, L)) state = FINISHED;
+                if (tpend.y == 0u) {
+                    if (L.ngroup.y <= 0x00ffffffu && L.sp > 0) {
+                        --L.sp;
+                        L.ngroup = L.sp < TRACE_SM_STACK ? s_stack[L.sp * TRACE_THREADS + threadIdx.x] : l_stack[L.sp - TRACE_SM_STACK];
+                    }
+                    if (L.ngroup.y > 0x00ffffffu) { ++n_steps; node_step(sc, s_stack, l_stack, L, tpend); }
+                }
+                while (tpend.y != 0u && qcnt < (uint32_t) TQ) {
+                    const uint32_t i = 31u - __clz(tpend.y);
+                    tpend.y &= ~(1u << i);
+                    s_tq[qcnt * TRACE_THREADS + threadIdx.x] = tpend.x + i;
+                    ++qcnt;
+                }
             }
+            const uint32_t have_tri = __ballot_sync(0xffffffffu, state == BUSY && qcnt > 0u);
+            const uint32_t can_node = __ballot_sync(0xffffffffu, state == BUSY && tpend.y == 0u && (L.ngroup.y > 0x00ffffffu || L.sp > 0));
+            if (have_tri != 0u && (__popc(have_tri) >= TRACE_TRI_LANES || can_node == 0u)) {
+                uint32_t m = have_tri;
+                do {
+                    if (state == BUSY && qcnt > 0u) {
+                        --qcnt;
+                        const uint32_t slot = s_tq[qcnt * TRACE_THREADS + threadIdx.x];
+                        float t, u, v; uint32_t shape, prim;
+                        if (tri_test(sc.tris, slot, L.o, L.d, L.mint, L.maxt, t, u, v, shape, prim)) {
+                            if (ANY_HIT) { L.occluded = true; state = FINISHED; qcnt = 0u; tpend.y = 0u; }
+                            else if (t < L.best.t || (t == L.best.t && (shape < L.best.shape || (shape == L.best.shape && prim < L.best.prim)))) {
+                                L.best.t = t; L.best.u = u; L.best.v = v; L.best.slot = slot; L.best.shape = shape; L.best.prim = prim;
+                            }
+                        }
+                    }
+                    m = __ballot_sync(0xffffffffu, state == BUSY && qcnt > 0u);
+                } while (m != 0u && (__popc(m) >= (TRACE_TRI_LANES + 1) / 2 || can_node == 0u));
+            }
+            // nothing left anywhere for this lane: the traversal is finished
+            if (state == BUSY && qcnt == 0u && tpend.y == 0u && L.ngroup.y <= 0x00ffffffu && L.sp == 0) state = FINISHED;
         } while (__popc(__ballot_sync(0xffffffffu, state == BUSY)) >= min_busy);
     }
 }
