@@ -3,6 +3,7 @@
 // BF_ERR_CUDA when no device is usable and every compute entry point requires a committed scene.
 #include <cuda_runtime.h>
 #include <dlfcn.h>
+#include <nvtx3/nvToolsExt.h>      // header-only; ranges are no-ops unless a profiler injects itself
 
 #include <algorithm>
 #include <chrono>
@@ -242,6 +243,7 @@ struct bf_scene {
 };
 
 static void multi_destroy_comm(void *comm);
+namespace { struct NvtxRange { explicit NvtxRange(const char *name) { nvtxRangePushA(name); } ~NvtxRange() { nvtxRangePop(); } }; }
 static thread_local std::string g_create_error;
 
 static int fail(bf_scene *s, int code, const std::string &msg) {
@@ -782,6 +784,7 @@ static int upload_geometry(bf_scene *s) {
 
 int bf_scene_commit(bf_scene *s, int device) {
     if (!s) return BF_ERR_INVALID;
+    NvtxRange range("bf_scene_commit (SAH build + upload)");
     if (!s->has_rx) return fail(s, BF_ERR_STATE, "bf_scene_commit: no receiver / sensor set");
     if (!s->has_integ) return fail(s, BF_ERR_STATE, "bf_scene_commit: no integrator set");
     if (s->integ.gen == BF_GEN_PHASE && !s->has_adc) return fail(s, BF_ERR_STATE, "bf_scene_commit: phase integrator needs an ADC");
@@ -943,6 +946,7 @@ static void refresh_mesh_bounds(bf_scene *s) {
 }
 
 int bf_scene_update_transform(bf_scene *s, uint32_t shape_id, const float motion[16]) {
+    NvtxRange range("bf_scene_update_transform (refit)");
     if (!s || !motion) return BF_ERR_INVALID;
     if (shape_id >= s->shapes.size()) return fail(s, BF_ERR_INVALID, "bf_scene_update_transform: shape id out of range");
     if (s->shapes[shape_id].type == 1) return bf_scene_update_rect(s, shape_id, motion);
@@ -1071,6 +1075,7 @@ static cudaEvent_t next_trace_event(bf_scene *s, int kind) {
 static int run_wave(bf_scene *s, WaveSlot &sl, uint64_t seed, uint64_t first, uint32_t n, float *profile, bool with_records,
                     const DevScene *scene_override = nullptr) {
     const DevScene &sc = scene_override ? *scene_override : s->dev;
+    NvtxRange range("bf wave");
     Wave w = sl.wave;
     if (!with_records) { w.records = nullptr; w.sample_of = nullptr; }
     // BF_FUSED_PRIMARY=0 selects the unfused raygen + trace pair (lanes = samples), kept for A/B measurements
@@ -1148,6 +1153,7 @@ static int run_wave(bf_scene *s, WaveSlot &sl, uint64_t seed, uint64_t first, ui
 }
 
 static int receive_into(bf_scene *s, uint64_t seed, uint64_t first_sample, uint64_t n_samples, int accumulate, float *profile) {
+    NvtxRange range("bf_receive");
     BF_CUDA(cudaSetDevice(s->device));
     if (s->tables_dirty) { int rc = (s->tables_light && s->committed) ? upload_tables_light(s) : upload_tables(s); if (rc) return rc; }
     // Wave size: BF_WAVE_LANES when set; otherwise the request is cut into as many waves as there are slots, between 2^22 and
@@ -1196,6 +1202,7 @@ int bf_receive(bf_scene *s, uint64_t seed, uint64_t first_sample, uint64_t n_sam
 // rectangles and / or the receiver, then integrates n_samples into ITS OWN profile, slot i of a device-side batch buffer.
 // Nothing synchronises between items (light table uploads through the pinned ring); one copy brings all profiles back.
 int bf_receive_batch(bf_scene *s, uint32_t n_items, const bf_batch_item *items, uint64_t n_samples, float *profiles, size_t n_floats) {
+    NvtxRange range("bf_receive_batch");
     if (!s || (n_items && !items)) return BF_ERR_INVALID;
     if (!s->committed) return fail(s, BF_ERR_STATE, "bf_receive_batch: scene not committed");
     if (profiles && n_floats < (size_t) n_items * s->profile_floats) return fail(s, BF_ERR_INVALID, "bf_receive_batch: destination too small");

@@ -143,8 +143,8 @@ def test_phased_endpoints_from_xml():
         xmlscene.load_string(text.replace('<transmitter type="phasedtransmitter">',
                                           '<transmitter type="phasedtransmitter"><transform name="to_world"><translate x="1"/></transform>'),
                              consts=RADAR_94GHZ)
-    with pytest.raises(BeifongError):     # n_elems outside [1, 16]
-        xmlscene.load_string(text.replace('<integer name="n_elems" value="4"/>', '<integer name="n_elems" value="40"/>'), consts=RADAR_94GHZ)
+    with pytest.raises(BeifongError):     # n_elems outside [1, 64]
+        xmlscene.load_string(text.replace('<integer name="n_elems" value="4"/>', '<integer name="n_elems" value="80"/>'), consts=RADAR_94GHZ)
 
 
 def test_adc_reconstruction_filters_from_xml():
