@@ -213,7 +213,7 @@ def reference_arm(args, workload, threads):
     steps, warmup = args.steps, max(args.warmup, 0)
     n = args.cpu_samples
     if n <= 0:
-        rate, _, _, _, _ = cpu_run(blob, 1 << 15, 1, 0, threads)
+        rate, _, _, _, _ = cpu_run(blob, 1 << 19, 1, 0, threads)
         n = int(max(1 << 15, min(1 << 31, rate * 20.0 / max(steps + min(warmup, 1) / 8.0, 1))))
     value, dt, kind, what, qps = cpu_run(blob, n, steps, min(warmup, 1), threads)
     note = ""
@@ -367,7 +367,7 @@ def main():
                "config": workload,
                "run": {"samples_per_step": int(n_global), "samples_per_step_this_gpu": int(n_local),
                        "parallelism": (f"{N_ITEMS[name]} items dealt round-robin to {world} GPU(s), no reduce" if itemised else
-                                       f"sample-index sharding x{world}, scene replicated, 1 ncclReduce of {int(nfloats * 4)} B per step (bf_multi_reduce)"),
+                                       f"sample-index sharding x{world}, scene replicated" + (f", 1 ncclReduce of {int(nfloats * 4)} B per step (bf_multi_reduce)" if world > 1 else "")),
                        "e2e_excludes": "bf_scene_add_mesh + SAH build (reported as build_ms); the CPU arm excludes its BVH build too",
                        "build_ms": st1["build_ms"], "upload_ms": st1["upload_ms"]},
                "clocks": clk, "gpu_launches": int(launches),
@@ -381,8 +381,8 @@ def main():
         cpu = None
         if world == 1 and not args.no_cpu_baseline:
             blob, src = scene_blob(name, args.mesh, scene)
-            rate, _, _, _, _ = cpu_run(blob, 1 << 15, 1, 0, threads)
-            cn = args.cpu_samples or int(max(1 << 15, min(1 << 31, rate * 12.0)))
+            rate, _, _, _, _ = cpu_run(blob, 1 << 19, 1, 0, threads)
+            cn = args.cpu_samples or int(max(1 << 15, min(1 << 31, rate * 15.0)))
             v, dt, kind, what, _ = cpu_run(blob, cn, 1, 0, threads)
             cpu = {"value": v, "unit": UNIT, "cores": threads, "kind": kind, "sample": f"1 x {cn} samples of the same workload ({dt:.1f} s); {what}"}
             if not args.no_extras and name == "c2":
