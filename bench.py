@@ -356,6 +356,9 @@ def main():
             whole = scene.profile().astype(np.float64)
             fin = np.isfinite(whole[..., 0]) & np.isfinite(reduced[..., 0])
             reduce_check = {"rel_l2_Y": float(np.linalg.norm(reduced[..., 0][fin] - whole[..., 0][fin]) / max(np.linalg.norm(whole[..., 0][fin]), 1e-300)),
+                            # alpha / weight channels are fp32 counts: exact below 2^24 per bin, rounded above (C2 puts half of all samples
+                            # -- the receiver rays that hit nothing -- into one bin), in the reference's fp32 ADC storage just the same
+                            "counts_rel_max": float(np.max(np.abs(reduced[..., 1:3] - whole[..., 1:3]) / np.maximum(whole[..., 1:3], 1.0))),
                             "counts_equal": bool(np.array_equal(reduced[..., 1:3], whole[..., 1:3])), "samples": int(m * world),
                             "what": "rank 0's reduced profile of the sharded run vs one GPU running the whole index range", "bytes_reduced": int(nfloats * 4)}
         sync_all()
