@@ -79,7 +79,7 @@ class bf_stats(C.Structure):
     _fields_ = [("samples", u64), ("closest_queries", u64), ("shadow_queries", u64), ("kernel_launches", u64),
                 ("bvh_nodes", u32), ("bvh_tris", u32), ("bvh_depth", u32), ("n_rects", u32),
                 ("build_ms", C.c_double), ("upload_ms", C.c_double),
-                ("path_closest_queries", u64), ("path_shadow_queries", u64)]
+                ("path_closest_queries", u64), ("path_shadow_queries", u64), ("mesh_bounds_fraction", C.c_double)]
 
 
 # name -> (restype, argtypes); also the list of symbols include/beifong_b200/abi.h declares

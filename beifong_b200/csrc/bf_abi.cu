@@ -221,6 +221,7 @@ struct bf_scene {
     DevBuf<float> d_batch; uint32_t batch_items = 0;   // bf_receive_batch: one profile per item
     bool geometry_moved = false;     // the device geometry differs from the pinned image (bf_scene_reupload would undo a refit)
     bool primary_defer = false;      // fused primary: traverse the rays that enter the mesh bounds in a separate dense launch
+    bool path_defer = false;         // same, at the (higher) share of rays below which k_path + dense traversal wins over k_primary
     DevFilter filter; bool wide_filter = false;    // discretised reconstruction filter when wider than one bin
     DevBuf<uint32_t> d_developed;    // bf_profile_develop output (fp32 or fp16 components)
     // image of the geometry tables in pinned host memory (re-upload without a rebuild)
@@ -311,9 +312,10 @@ static void build_filter(bf_scene *s) {
 
 // Which primary kernel: the share of receiver rays (cosine-weighted about the receiver rectangle's normal, from its centre)
 // that enter the padded bounds of the meshes, on a 64 x 64 stratified grid.  Below a quarter, traversal is left to a
-// separate dense launch (k_primary<DEFER>); results are the same either way.
+// separate dense launch (k_primary<DEFER>); results are the same either way.  Scenes k_path can run switch at one half:
+// measured on a B200 (tools/bounds_fraction.py), C3 at 0.32 gains 15 % from k_path + dense k_trace, C5 at 1.0 loses 4 %.
 static void estimate_primary_defer(bf_scene *s) {
-    s->primary_defer = false;
+    s->primary_defer = false; s->path_defer = false;
     if (!s->has_rx || s->rx_shape < 0 || (size_t) s->rx_shape >= s->shapes.size() || s->shapes[s->rx_shape].type != 1) return;
     const DevRect &r = s->rects[s->shapes[s->rx_shape].index];
     const float *lo = s->dev.mesh_lo, *hi = s->dev.mesh_hi;
@@ -336,7 +338,9 @@ static void estimate_primary_defer(bf_scene *s) {
             }
             inside += t0 <= t1;
         }
+    s->stats.mesh_bounds_fraction = (double) inside / (double) (N * N);
     s->primary_defer = inside * 4 < N * N;
+    s->path_defer = inside * 2 < N * N;
 }
 
 static uint32_t n_channels(const bf_scene *s) {
@@ -1107,9 +1111,10 @@ static int run_wave(bf_scene *s, WaveSlot &sl, uint64_t seed, uint64_t first, ui
     if (fused) {
         w.n_lanes = ctr + 6;
         // few receiver rays reach the meshes (bf_scene_commit's estimate): k_primary leaves those to a dense k_trace launch
-        const bool defer = (s->tune.primary_defer < 0 ? s->primary_defer : s->tune.primary_defer != 0) && sc.n_nodes != 0;
+        const bool path_ok = s->tune.path_fused != 0 && path_kernel_available(sc);
+        const bool defer = (s->tune.primary_defer < 0 ? s->primary_defer || (s->path_defer && path_ok) : s->tune.primary_defer != 0) && sc.n_nodes != 0;
         // ... and the paths that stay clear of the meshes altogether are integrated by k_path without touching the wave arrays
-        path = defer && s->tune.path_fused != 0 && path_kernel_available(sc);
+        path = defer && path_ok;
         if (path) {
             if (!sl.path_stash) {
                 BF_CUDA(cudaMalloc((void **) &sl.path_stash, path_stash_bytes(sc, s->sm_count)));

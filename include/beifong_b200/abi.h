@@ -193,6 +193,7 @@ typedef struct bf_stats {
     double build_ms, upload_ms;
     uint64_t path_closest_queries; /* of closest_queries / shadow_queries: decided inside k_path (rectangles + mesh bounds, */
     uint64_t path_shadow_queries;  /* no traversal launch) */
+    double mesh_bounds_fraction;   /* bf_scene_commit's estimate: share of cosine-weighted receiver rays that enter the padded mesh bounds */
 } bf_stats;
 
 uint32_t bf_abi_version(void);
