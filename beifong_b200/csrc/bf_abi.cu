@@ -162,7 +162,7 @@ struct Tunables {
     int64_t fused_primary = 1;
     int64_t primary_defer = -1;   // -1: bf_scene_commit's estimate
     int64_t trace_defer = -1;
-    int64_t trace_rounds = 8;     // batches of 32 rays per active traversal warp (0: all warps of the grid)
+    int64_t trace_rounds = -1;    // batches of 32 rays per active traversal warp (0: all warps of the grid, -1: by the request, see receive_into)
     int64_t use_graph = 1;        // small calls: replay the wave's launch sequence from a CUDA graph
     int64_t path_fused = 1;       // scenes with a deferred primary: k_path integrates the rectangle-only paths in registers
     int64_t mega_max = 262144;    // requests up to this many samples, and every request on a scene without meshes (-1: never), run as ONE k_mega launch
@@ -182,7 +182,7 @@ static Tunables tunables_from_env() {
     t.fused_primary = env_i64("BF_FUSED_PRIMARY", 1, 0, 1);
     t.primary_defer = env_i64("BF_PRIMARY_DEFER", -1, -1, 1);
     t.trace_defer = env_i64("BF_TRACE_DEFER", -1, -1, 1);
-    t.trace_rounds = env_i64("BF_TRACE_ROUNDS", 8, 0, 1024);
+    t.trace_rounds = env_i64("BF_TRACE_ROUNDS", -1, -1, 1024);
     t.use_graph = env_i64("BF_USE_GRAPH", 1, 0, 1);
     t.path_fused = env_i64("BF_PATH_FUSED", 1, 0, 1);
     t.mega_max = env_i64("BF_MEGA_MAX", 262144, -1, 1ll << 28);
@@ -221,6 +221,7 @@ struct bf_scene {
     DevBuf<float> d_batch; uint32_t batch_items = 0;   // bf_receive_batch: one profile per item
     bool geometry_moved = false;     // the device geometry differs from the pinned image (bf_scene_reupload would undo a refit)
     bool primary_defer = false;      // fused primary: traverse the rays that enter the mesh bounds in a separate dense launch
+    uint32_t auto_rounds = 8;        // k_trace batches per warp for the request being issued (tune.trace_rounds < 0)
     bool path_defer = false;         // same, at the (higher) share of rays below which k_path + dense traversal wins over k_primary
     DevFilter filter; bool wide_filter = false;    // discretised reconstruction filter when wider than one bin
     DevBuf<uint32_t> d_developed;    // bf_profile_develop output (fp32 or fp16 components)
@@ -1086,7 +1087,7 @@ static int run_wave(bf_scene *s, WaveSlot &sl, uint64_t seed, uint64_t first, ui
     // wide reconstruction filters: every sample (misses too) is splatted by k_finalize_wide, so lanes = samples
     const bool fused = s->tune.fused_primary != 0 && !s->wide_filter;
     if (!fused) w.sample_of = nullptr;
-    LaunchCfg cfg; cfg.stream = sl.stream; cfg.sm_count = s->sm_count; cfg.trace_rounds = (uint32_t) s->tune.trace_rounds;
+    LaunchCfg cfg; cfg.stream = sl.stream; cfg.sm_count = s->sm_count; cfg.trace_rounds = s->tune.trace_rounds >= 0 ? (uint32_t) s->tune.trace_rounds : s->auto_rounds;
     uint32_t *ctr = w.counters;
     const bool unbounded = sc.integ.max_depth < 0 || sc.integ.max_depth > 64;
     const uint32_t max_depth = sc.integ.max_depth < 0 ? BF_MAX_BOUNCES : std::min<uint32_t>((uint32_t) sc.integ.max_depth, BF_MAX_BOUNCES);
@@ -1174,6 +1175,11 @@ static int receive_into(bf_scene *s, uint64_t seed, uint64_t first_sample, uint6
     // per-kernel timing needs the launches serialised on one stream
     const size_t n_slots = s->time_trace ? 1 : (size_t) std::min<uint64_t>(streams, std::max<uint64_t>(n_waves, 1));
     for (size_t k = 0; k < n_slots; ++k) { int rc = ensure_slot(s, k, lanes, false); if (rc) return rc; }
+    // A traversal launch trades its tail against its latency: few warps with many batches each pay the per-warp tail (the
+    // last rays of a warp run at a few lanes of 32) once per many rays but leave the SMs to the launch's slowest warp.  A
+    // request of several waves in flight fills those gaps with the other waves' launches, so it takes 48 batches per warp
+    // (C2 +1.5 %, C3 +7.6 % over 8: tools/ab_env4.sh, profiles/r02u); a request that is one wave keeps 8 for its latency.
+    s->auto_rounds = n_waves >= 4 ? 48u : 8u;
     s->ev_trace_used = 0;
     BF_CUDA(cudaEventRecord(s->ev_begin, s->stream));
     if (!accumulate) BF_CUDA(cudaMemsetAsync(profile, 0, s->profile_floats * 4, s->stream));
@@ -1234,6 +1240,7 @@ int bf_receive_batch(bf_scene *s, uint32_t n_items, const bf_batch_item *items, 
         const size_t n_slots = (size_t) std::min<int64_t>(s->tune.wave_streams, std::max<uint32_t>(n_items, 1u));
         const uint32_t lanes = (uint32_t) std::max<uint64_t>(n_samples, 1024);
         for (size_t k = 0; k < n_slots; ++k) { int rc = ensure_slot(s, k, lanes, false); if (rc) return rc; }
+        s->auto_rounds = 8u;        // items of <= 2^22 samples: measured no better at 16, worse at 32 (C5, tools/ab_env4.sh)
         s->ev_trace_used = 0;
         BF_CUDA(cudaEventRecord(s->ev_begin, s->stream));
         BF_CUDA(cudaEventRecord(s->ev_fork, s->stream));
@@ -1440,7 +1447,7 @@ static int trace_rays_common(bf_scene *s, const float *origins, const float *dir
         cleanup();
         return fail(s, BF_ERR_CUDA, std::string("trace: ") + cudaGetErrorString(e));
     }
-    LaunchCfg cfg; cfg.stream = s->stream; cfg.sm_count = s->sm_count; cfg.trace_rounds = (uint32_t) s->tune.trace_rounds;
+    LaunchCfg cfg; cfg.stream = s->stream; cfg.sm_count = s->sm_count; cfg.trace_rounds = s->tune.trace_rounds >= 0 ? (uint32_t) s->tune.trace_rounds : s->auto_rounds;
     cudaMemcpyAsync(d_o.p, ho.data(), n * 16, cudaMemcpyHostToDevice, s->stream);
     cudaMemcpyAsync(d_d.p, hd.data(), n * 16, cudaMemcpyHostToDevice, s->stream);
     cudaMemsetAsync(d_cursor.p, 0, 4, s->stream);
@@ -1530,7 +1537,7 @@ int bf_set_tunable(bf_scene *s, const char *name, int64_t value) {
     struct { const char *n; int64_t *p; int64_t lo, hi; } table[] = {
         {"wave_lanes", &s->tune.wave_lanes, 0, 1ll << 28}, {"wave_streams", &s->tune.wave_streams, 1, 16},
         {"fused_primary", &s->tune.fused_primary, 0, 1}, {"primary_defer", &s->tune.primary_defer, -1, 1},
-        {"trace_defer", &s->tune.trace_defer, -1, 1}, {"trace_rounds", &s->tune.trace_rounds, 0, 1024},
+        {"trace_defer", &s->tune.trace_defer, -1, 1}, {"trace_rounds", &s->tune.trace_rounds, -1, 1024},
         {"use_graph", &s->tune.use_graph, 0, 1},
         {"path_fused", &s->tune.path_fused, 0, 1}, {"mega_max", &s->tune.mega_max, -1, 1ll << 28}};
     for (auto &t : table)
