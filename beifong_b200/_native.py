@@ -11,6 +11,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("BF_NATIVE_LIB") or os.path.join(_HERE, "libbeifong_b200.so")   # BF_NATIVE_LIB: an alternative build of the same library (tuning experiments)
 
 BF_NONE = 0xFFFFFFFF
+BF_STATIC_TRACE_MAX_RAYS = 65536      # abi.h
 BF_OK, BF_ERR_INVALID, BF_ERR_UNSUPPORTED, BF_ERR_CUDA, BF_ERR_STATE, BF_ERR_IO = 0, -1, -2, -3, -4, -5
 BF_SPEC_UNIFORM, BF_SPEC_REGULAR, BF_SPEC_IRREGULAR, BF_SPEC_ZERO_OUTSIDE_VISIBLE = 0, 1, 2, 3
 BF_BSDF_DIFFUSE, BF_BSDF_ROUGHCONDUCTOR, BF_BSDF_CONDUCTOR, BF_BSDF_NULL_BLACK = 0, 1, 2, 3
@@ -119,6 +120,7 @@ PROTOTYPES = {
     "bf_multi_reduce": (C.c_int, [vp, C.c_int]),
     "bf_multi_reduce_comm": (C.c_int, [vp, vp, C.c_int]),
     "bf_trace_first_hits": (C.c_int, [vp, P(f32), P(f32), P(f32), P(f32), u64, P(u32), P(u32), P(f32), P(f32), P(f32)]),
+    "bf_trace_first_hits_static": (C.c_int, [vp, P(f32), P(f32), P(f32), P(f32), u64, P(u32), P(u32), P(f32), P(f32), P(f32)]),
     "bf_trace_occluded": (C.c_int, [vp, P(f32), P(f32), P(f32), P(f32), u64, P(C.c_uint8)]),
     "bf_debug_trace_steps": (C.c_int, [vp, P(f32), P(f32), P(f32), P(f32), u64, P(u32), P(f32)]),
     "bf_debug_sample_records": (C.c_int, [vp, u64, u64, u64, P(bf_sample_record)]),

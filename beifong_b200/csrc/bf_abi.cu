@@ -1482,6 +1482,29 @@ int bf_trace_first_hits(bf_scene *s, const float *origins, const float *directio
                         uint64_t n_rays, uint32_t *shape, uint32_t *prim, float *t, float *u, float *v) {
     return trace_rays_common(s, origins, directions, mint, maxt, n_rays, shape, prim, t, u, v, nullptr);
 }
+// No allocation on this path: no DevBuf, no std::vector, no table upload (see abi.h).  The scratch array, its
+// cudaGetSymbolAddress look-up and the kernels that use it are in bf_kernels.cu (static_trace_first_hits).
+int bf_trace_first_hits_static(bf_scene *s, const float *origins, const float *directions, const float *mint, const float *maxt,
+                               uint64_t n_rays, uint32_t *shape, uint32_t *prim, float *t, float *u, float *v) {
+    if (!s || !origins || !directions) return BF_ERR_INVALID;
+    if (!s->committed) return fail(s, BF_ERR_STATE, "bf_trace_first_hits_static: scene not committed");
+    if (n_rays > BF_STATIC_TRACE_MAX_RAYS)
+        return fail(s, BF_ERR_INVALID, "bf_trace_first_hits_static: at most 65536 rays per call (BF_STATIC_TRACE_MAX_RAYS, the size of the static scratch array)");
+    if (s->device >= BF_STATIC_TRACE_MAX_DEVICES)
+        return fail(s, BF_ERR_UNSUPPORTED, "bf_trace_first_hits_static: device ordinal beyond BF_STATIC_TRACE_MAX_DEVICES");
+    if (s->tables_dirty)
+        return fail(s, BF_ERR_STATE, "bf_trace_first_hits_static: scene edits pending; apply them with bf_receive or bf_trace_first_hits first (that may allocate)");
+    if (n_rays == 0) return BF_OK;
+    BF_CUDA(cudaSetDevice(s->device));
+    LaunchCfg cfg; memset(&cfg, 0, sizeof(cfg)); cfg.stream = s->stream; cfg.sm_count = s->sm_count; cfg.trace_rounds = 8;
+    int launches = 0;
+    cudaError_t e = static_trace_first_hits(s->dev, s->device, origins, directions, mint, maxt, (uint32_t) n_rays, shape, prim, t, u, v, cfg, &launches);
+    s->stats.kernel_launches += (uint64_t) launches;
+    const cudaError_t e2 = cudaStreamSynchronize(s->stream);
+    if (e == cudaSuccess) e = e2;
+    if (e != cudaSuccess) return fail(s, BF_ERR_CUDA, std::string("bf_trace_first_hits_static: ") + cudaGetErrorString(e));
+    return BF_OK;
+}
 int bf_debug_trace_steps(bf_scene *s, const float *origins, const float *directions, const float *mint, const float *maxt,
                          uint64_t n_rays, uint32_t *steps, float *t) {
     if (!steps) return BF_ERR_INVALID;

@@ -11,6 +11,7 @@
 //                signalblock.cpp:162-169)
 // Compiled with -fmad=false: see bf_math.h for the arithmetic contract.
 #include <cuda_fp16.h>
+#include <mutex>
 #include "bf_wave.h"
 #include "bf_device.cuh"
 #include "bf_trace.cuh"
@@ -1651,6 +1652,104 @@ int launch_develop(const float *raw, void *out, uint32_t n_bins, uint32_t channe
     if (half_out) k_develop<__half><<<grid, 256, 0, cfg.stream>>>(raw, (__half *) out, n_bins, channels);
     else k_develop<float><<<grid, 256, 0, cfg.stream>>>(raw, (float *) out, n_bins, channels);
     return 1;
+}
+
+// =========================================================================================================
+// bf_trace_first_hits_static: closest-hit queries for callers that may not allocate device memory
+// =========================================================================================================
+// The stand-alone ray query (launch_trace_rays + launch_resolve_hits above) with every device-side temporary -- the staged
+// caller arrays, the packed rays, k_trace's work cursor and hit records, the resolved ids -- in ONE file-scope array instead
+// of cudaMalloc'ed buffers.  Every GPU that loads the library holds the array (6.25 MiB + 256 B) until the process exits; every
+// call on a device shares it and finds the previous call's contents in it, so the one word that must start at zero (the work
+// cursor) is cleared per call, and two calls that overlap on a GPU (two scenes on two streams) race.
+// On the host `g_static_trace` is a stand-in symbol, not a device address: host code gets the address from
+// cudaGetSymbolAddress, once per device with that device current (static_trace_base); device code names the array directly.
+#define ST_N BF_STATIC_TRACE_MAX_RAYS
+enum : uint32_t {              // word offsets into g_static_trace; each block is sized for ST_N rays
+    ST_CURSOR = 0, ST_HDR = 64,
+    ST_IN_O = ST_HDR, ST_IN_D = ST_IN_O + 3u * ST_N, ST_IN_MINT = ST_IN_D + 3u * ST_N, ST_IN_MAXT = ST_IN_MINT + ST_N,
+    ST_RO = ST_IN_MAXT + ST_N, ST_RD = ST_RO + 4u * ST_N, ST_HIT = ST_RD + 4u * ST_N,
+    ST_SHAPE = ST_HIT + 4u * ST_N, ST_PRIM = ST_SHAPE + ST_N, ST_T = ST_PRIM + ST_N, ST_U = ST_T + ST_N, ST_V = ST_U + ST_N,
+    ST_WORDS = ST_V + ST_N
+};
+static_assert(ST_N % 64 == 0 && ST_RO % 4 == 0, "float4 blocks of the static scratch must stay 16-byte aligned");
+static __device__ __align__(256) uint32_t g_static_trace[ST_WORDS];
+
+// (origin xyz, mint) / (direction xyz, maxt) records from the staged caller arrays; the defaults are trace_rays_common's
+__global__ void __launch_bounds__(256) k_static_pack(uint32_t n, int has_mint, int has_maxt) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float *o = reinterpret_cast<const float *>(g_static_trace + ST_IN_O), *d = reinterpret_cast<const float *>(g_static_trace + ST_IN_D);
+    const float mint = has_mint ? __uint_as_float(g_static_trace[ST_IN_MINT + i]) : BF_RAY_EPS;
+    const float maxt = has_maxt ? __uint_as_float(g_static_trace[ST_IN_MAXT + i]) : bf_inf();
+    reinterpret_cast<float4 *>(g_static_trace + ST_RO)[i] = make_float4(o[3 * i], o[3 * i + 1], o[3 * i + 2], mint);
+    reinterpret_cast<float4 *>(g_static_trace + ST_RD)[i] = make_float4(d[3 * i], d[3 * i + 1], d[3 * i + 2], maxt);
+}
+// k_resolve_hits on the static hit records, plus the planar t / u / v the caller asked for
+__global__ void __launch_bounds__(256) k_static_resolve(const __grid_constant__ DevScene sc, uint32_t n) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float4 h = reinterpret_cast<const float4 *>(g_static_trace + ST_HIT)[i];
+    const uint32_t slot = __float_as_uint(h.w);
+    uint32_t shape = BF_NONE, prim = BF_NONE;
+    if (!(h.x == bf_inf() || slot == BF_NONE)) {
+        if (slot & 0x80000000u) { shape = sc.rects[slot & 0x7fffffffu].shape; prim = 0; }
+        else { shape = __float_as_uint(__ldg(&sc.tris[3 * (size_t) slot]).w); prim = __float_as_uint(__ldg(&sc.tris[3 * (size_t) slot + 1]).w); }
+    }
+    g_static_trace[ST_SHAPE + i] = shape; g_static_trace[ST_PRIM + i] = prim;
+    g_static_trace[ST_T + i] = __float_as_uint(h.x); g_static_trace[ST_U + i] = __float_as_uint(h.y); g_static_trace[ST_V + i] = __float_as_uint(h.z);
+}
+
+// Device address of g_static_trace on the CURRENT device (`device` is its ordinal): looked up once per device.
+static cudaError_t static_trace_base(int device, uint32_t **base) {
+    static std::mutex lock;
+    static uint32_t *known[BF_STATIC_TRACE_MAX_DEVICES] = {};
+    if (device < 0 || device >= BF_STATIC_TRACE_MAX_DEVICES) return cudaErrorInvalidDevice;
+    std::lock_guard<std::mutex> guard(lock);
+    if (!known[device]) {
+        void *p = nullptr;
+        cudaError_t e = cudaGetSymbolAddress(&p, g_static_trace);
+        if (e != cudaSuccess) return e;
+        if (!p) return cudaErrorInvalidSymbol;
+        known[device] = static_cast<uint32_t *>(p);
+    }
+    *base = known[device];
+    return cudaSuccess;
+}
+
+// Allocates nothing (host or device).  The caller arrays may be host or device memory (cudaMemcpyDefault); the copies back
+// are queued on cfg.stream and the caller synchronises it.
+cudaError_t static_trace_first_hits(const DevScene &sc, int device, const float *origins, const float *directions, const float *mint,
+                                    const float *maxt, uint32_t n, uint32_t *shape, uint32_t *prim, float *t, float *u, float *v,
+                                    const LaunchCfg &cfg, int *launches) {
+    *launches = 0;
+    if (n == 0) return cudaSuccess;
+    if (n > ST_N) return cudaErrorInvalidValue;
+    uint32_t *base = nullptr;
+    cudaError_t e = static_trace_base(device, &base);
+    if (e != cudaSuccess) return e;
+    cudaStream_t st = cfg.stream;
+    if ((e = cudaMemsetAsync(base + ST_CURSOR, 0, ST_HDR * 4, st)) != cudaSuccess) return e;
+    if ((e = cudaMemcpyAsync(base + ST_IN_O, origins, (size_t) n * 12, cudaMemcpyDefault, st)) != cudaSuccess) return e;
+    if ((e = cudaMemcpyAsync(base + ST_IN_D, directions, (size_t) n * 12, cudaMemcpyDefault, st)) != cudaSuccess) return e;
+    if (mint && (e = cudaMemcpyAsync(base + ST_IN_MINT, mint, (size_t) n * 4, cudaMemcpyDefault, st)) != cudaSuccess) return e;
+    if (maxt && (e = cudaMemcpyAsync(base + ST_IN_MAXT, maxt, (size_t) n * 4, cudaMemcpyDefault, st)) != cudaSuccess) return e;
+    k_static_pack<<<(n + 255) / 256, 256, 0, st>>>(n, mint != nullptr, maxt != nullptr);
+    TraceIO io;
+    memset(&io, 0, sizeof(io));
+    io.ray_o = reinterpret_cast<const float4 *>(base + ST_RO); io.ray_d = reinterpret_cast<const float4 *>(base + ST_RD);
+    io.n_direct = n; io.work_cursor = base + ST_CURSOR; io.hit = reinterpret_cast<float4 *>(base + ST_HIT);
+    io.rounds = cfg.trace_rounds; io.sm_count = (uint32_t) cfg.sm_count;
+    k_trace<false><<<trace_grid(cfg), TRACE_THREADS, 0, st>>>(sc, io);
+    k_static_resolve<<<(n + 255) / 256, 256, 0, st>>>(sc, n);
+    *launches = 3;
+    if ((e = cudaGetLastError()) != cudaSuccess) return e;
+    if (shape && (e = cudaMemcpyAsync(shape, base + ST_SHAPE, (size_t) n * 4, cudaMemcpyDefault, st)) != cudaSuccess) return e;
+    if (prim && (e = cudaMemcpyAsync(prim, base + ST_PRIM, (size_t) n * 4, cudaMemcpyDefault, st)) != cudaSuccess) return e;
+    if (t && (e = cudaMemcpyAsync(t, base + ST_T, (size_t) n * 4, cudaMemcpyDefault, st)) != cudaSuccess) return e;
+    if (u && (e = cudaMemcpyAsync(u, base + ST_U, (size_t) n * 4, cudaMemcpyDefault, st)) != cudaSuccess) return e;
+    if (v && (e = cudaMemcpyAsync(v, base + ST_V, (size_t) n * 4, cudaMemcpyDefault, st)) != cudaSuccess) return e;
+    return cudaSuccess;
 }
 
 }  // namespace bf

@@ -92,5 +92,9 @@ int launch_trace_rays(const DevScene &sc, const float4 *ray_o, const float4 *ray
                       uint32_t *work_cursor, const LaunchCfg &cfg);
 // resolve (slot -> shape, prim) for hits produced by launch_trace_rays
 int launch_resolve_hits(const DevScene &sc, const float4 *hit, uint32_t n, uint32_t *shape, uint32_t *prim, const LaunchCfg &cfg);
+// the same query with all temporaries in bf_kernels.cu's static device array (bf_trace_first_hits_static): no allocation
+cudaError_t static_trace_first_hits(const DevScene &sc, int device, const float *origins, const float *directions, const float *mint,
+                                    const float *maxt, uint32_t n, uint32_t *shape, uint32_t *prim, float *t, float *u, float *v,
+                                    const LaunchCfg &cfg, int *launches);
 
 }  // namespace bf

@@ -339,6 +339,20 @@ class FlatScene:
                  "bf_trace_first_hits")
         return shape, prim, t, u, v
 
+    def trace_first_hits_static(self, origins, directions, mint=None, maxt=None):
+        """bf_trace_first_hits_static: the same query without any allocation inside the library (abi.h); at most
+        N.BF_STATIC_TRACE_MAX_RAYS rays per call."""
+        o, d = _f32(origins).reshape(-1, 3), _f32(directions).reshape(-1, 3)
+        n = len(o)
+        mi = _f32(mint) if mint is not None else None
+        ma = _f32(maxt) if maxt is not None else None
+        shape, prim = np.empty(n, np.uint32), np.empty(n, np.uint32)
+        t, u, v = np.empty(n, np.float32), np.empty(n, np.float32), np.empty(n, np.float32)
+        self._ck(N.lib().bf_trace_first_hits_static(self._h, _fp(o), _fp(d), _fp(mi) if mi is not None else None,
+                                                    _fp(ma) if ma is not None else None, n, _up(shape), _up(prim), _fp(t), _fp(u), _fp(v)),
+                 "bf_trace_first_hits_static")
+        return shape, prim, t, u, v
+
     def trace_occluded(self, origins, directions, mint=None, maxt=None):
         o, d = _f32(origins).reshape(-1, 3), _f32(directions).reshape(-1, 3)
         n = len(o)

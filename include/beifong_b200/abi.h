@@ -325,6 +325,24 @@ int bf_trace_first_hits(bf_scene *s, const float *origins, const float *directio
 /* Scene::ray_test (scene.cpp:170-178) */
 int bf_trace_occluded(bf_scene *s, const float *origins, const float *directions,
                       const float *mint, const float *maxt, uint64_t n_rays, uint8_t *hit);
+/* bf_trace_first_hits for callers that cannot allocate device memory (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid cudaMalloc).  No counterpart in the reference.
+ * Same arguments, results and defaults as bf_trace_first_hits; every device-side temporary lives in one static device array of
+ * the library (6.25 MiB, held by every GPU that loads the library until the process exits), so the call makes no cudaMalloc /
+ * cudaFree / allocating library call (nor a host allocation).  Limits and rules:
+ *   - n_rays <= BF_STATIC_TRACE_MAX_RAYS, else BF_ERR_INVALID with a message naming the limit;
+ *   - device ordinal < BF_STATIC_TRACE_MAX_DEVICES;
+ *   - scene edits made after bf_scene_commit must have been applied by an earlier bf_receive / bf_trace_* call (applying them may
+ *     allocate): BF_ERR_STATE otherwise;
+ *   - the array is shared by every call on that GPU and keeps the last call's contents (the call clears what it needs): calls
+ *     that overlap on one GPU -- two scenes on two host threads -- race.  Calls on one scene are ordered on its stream.
+ * origins / directions / mint / maxt and the outputs may be host or device pointers (copied with cudaMemcpyDefault on the
+ * scene's stream, which is synchronised before returning).  Null outputs are skipped; null mint / maxt = the defaults. */
+#define BF_STATIC_TRACE_MAX_RAYS 65536u
+#define BF_STATIC_TRACE_MAX_DEVICES 64
+int bf_trace_first_hits_static(bf_scene *s, const float *origins, const float *directions,
+                               const float *mint, const float *maxt, uint64_t n_rays,
+                               uint32_t *shape, uint32_t *prim, float *t, float *u, float *v);
 /* Tuning hook: BVH traversal steps (wide nodes visited) per closest-hit query. */
 int bf_debug_trace_steps(bf_scene *s, const float *origins, const float *directions, const float *mint, const float *maxt,
                          uint64_t n_rays, uint32_t *steps, float *t);
