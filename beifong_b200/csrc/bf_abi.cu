@@ -164,6 +164,7 @@ struct Tunables {
     int64_t trace_defer = -1;
     int64_t trace_rounds = -1;    // batches of 32 rays per active traversal warp (0: all warps of the grid, -1: by the request, see receive_into)
     int64_t use_graph = 1;        // small calls: replay the wave's launch sequence from a CUDA graph
+    int64_t mega_batch = 1;       // bf_receive_batch: items that k_mega can run go out as one launch
     int64_t path_fused = 1;       // scenes with a deferred primary: k_path integrates the rectangle-only paths in registers
     int64_t mega_max = 262144;    // requests up to this many samples, and every request on a scene without meshes (-1: never), run as ONE k_mega launch
 };
@@ -184,6 +185,7 @@ static Tunables tunables_from_env() {
     t.trace_defer = env_i64("BF_TRACE_DEFER", -1, -1, 1);
     t.trace_rounds = env_i64("BF_TRACE_ROUNDS", -1, -1, 1024);
     t.use_graph = env_i64("BF_USE_GRAPH", 1, 0, 1);
+    t.mega_batch = env_i64("BF_MEGA_BATCH", 1, 0, 1);
     t.path_fused = env_i64("BF_PATH_FUSED", 1, 0, 1);
     t.mega_max = env_i64("BF_MEGA_MAX", 262144, -1, 1ll << 28);
     return t;
@@ -219,6 +221,8 @@ struct bf_scene {
     DevBuf<DevSpectrum> d_spectra; DevBuf<float> d_spec_pool; DevBuf<DevEndpoint> d_txs, d_rx; DevBuf<DevVElem> d_velems; DevBuf<M4> d_velocities;
     DevBuf<float> d_profile; size_t profile_floats = 0;
     DevBuf<float> d_batch; uint32_t batch_items = 0;   // bf_receive_batch: one profile per item
+    // ... small items in one k_mega_batch launch: per-item tables [MegaItem | DevEndpoint | DevRect x n_rects] x items + one cursor each
+    DevBuf<uint8_t> d_items; uint8_t *h_items = nullptr; size_t h_items_bytes = 0; cudaEvent_t items_ev = nullptr;
     bool geometry_moved = false;     // the device geometry differs from the pinned image (bf_scene_reupload would undo a refit)
     bool primary_defer = false;      // fused primary: traverse the rays that enter the mesh bounds in a separate dense launch
     uint32_t auto_rounds = 8;        // k_trace batches per warp for the request being issued (tune.trace_rounds < 0)
@@ -408,7 +412,9 @@ void bf_scene_destroy(bf_scene *s) {
         free_wave(s);
         s->d_nodes.release(); s->d_tris.release(); s->d_tri_nrm.release(); s->d_tris_rest.release(); s->d_nrm_rest.release(); s->d_node_box.release(); s->d_rects.release(); s->d_shapes.release();
         s->d_bsdfs.release(); s->d_spectra.release(); s->d_spec_pool.release(); s->d_txs.release(); s->d_rx.release(); s->d_velems.release(); s->d_velocities.release();
-        s->d_profile.release(); s->d_batch.release(); s->d_developed.release(); s->d_totals.release();
+        s->d_profile.release(); s->d_batch.release(); s->d_items.release();
+        if (s->h_items) { cudaFreeHost(s->h_items); s->h_items = nullptr; s->h_items_bytes = 0; }
+        if (s->items_ev) { cudaEventDestroy(s->items_ev); s->items_ev = nullptr; } s->d_developed.release(); s->d_totals.release();
         if (s->h_geom) cudaFreeHost(s->h_geom);
         if (s->h_tables) cudaFreeHost(s->h_tables);
         if (s->h_ring) cudaFreeHost(s->h_ring);
@@ -1212,6 +1218,65 @@ int bf_receive(bf_scene *s, uint64_t seed, uint64_t first_sample, uint64_t n_sam
 // the reference holds std::vector<ref<Receiver>>, scene.h:197, and calls receive() per receiver): item i re-poses the listed
 // rectangles and / or the receiver, then integrates n_samples into ITS OWN profile, slot i of a device-side batch buffer.
 // Nothing synchronises between items (light table uploads through the pinned ring); one copy brings all profiles back.
+// Every item's tables into one pinned block, one upload, one memset of the profiles and cursors, one k_mega_batch launch.
+static int receive_batch_one_launch(bf_scene *s, uint32_t n_items, const bf_batch_item *items, uint32_t n_samples) {
+    if (s->tables_dirty && !s->tables_light) { int rc = upload_tables(s); if (rc) return rc; }     // a heavy change pending from before the batch
+    const size_t n_rects = s->rects.size();
+    const size_t rect_bytes = (n_rects * sizeof(DevRect) + 15) & ~(size_t) 15;
+    const size_t ep_bytes = (sizeof(DevEndpoint) + 15) & ~(size_t) 15, item_bytes = (sizeof(MegaItem) + 15) & ~(size_t) 15;
+    const size_t off_ep = item_bytes * n_items, off_rects = off_ep + ep_bytes * n_items;
+    const size_t off_cursors = off_rects + rect_bytes * n_items, total = off_cursors + 4 * (size_t) n_items;
+    if (s->h_items_bytes < total || s->d_items.n < total) {
+        BF_CUDA(cudaStreamSynchronize(s->stream));
+        if (s->h_items) cudaFreeHost(s->h_items);
+        s->h_items = nullptr; s->h_items_bytes = 0;
+        BF_CUDA(cudaMallocHost((void **) &s->h_items, total));
+        s->h_items_bytes = total;
+        BF_CUDA(s->d_items.alloc(total));
+    }
+    if (!s->items_ev) BF_CUDA(cudaEventCreateWithFlags(&s->items_ev, cudaEventDisableTiming));
+    BF_CUDA(cudaEventSynchronize(s->items_ev));          // the previous batch's upload has left the pinned block
+    uint8_t *h = s->h_items, *d = s->d_items.p;
+    for (uint32_t i = 0; i < n_items; ++i) {
+        const bf_batch_item &it = items[i];
+        for (uint32_t k = 0; k < it.n_rect_updates; ++k) {
+            int rc = bf_scene_update_rect(s, it.rect_shape_ids[k], it.rect_to_world + 16 * (size_t) k);
+            if (rc) return rc;
+        }
+        if (it.receiver) { int rc = bf_scene_set_receiver(s, it.receiver_shape, it.receiver); if (rc) return rc; }
+        if (s->tables_dirty && !s->tables_light)
+            return fail(s, BF_ERR_UNSUPPORTED, "bf_receive_batch: an item may re-pose rectangles and replace the receiver by one of the same kind only");
+        if ((s->rx.kind != BF_RX_PERSPECTIVE) != (s->dev.rx_needs_aperture != 0))
+            return fail(s, BF_ERR_UNSUPPORTED, "bf_receive_batch: an item may re-pose rectangles and replace the receiver by one of the same kind only");
+        MegaItem m;
+        memset((void *) &m, 0, sizeof(m));
+        m.seed = it.seed; m.first_sample = it.first_sample;
+        m.profile = s->d_batch.p + (size_t) i * s->profile_floats;
+        m.rects = (const DevRect *) (d + off_rects + rect_bytes * i);
+        m.rx = (const DevEndpoint *) (d + off_ep + ep_bytes * i);
+        m.rx_ep = make_endpoint(s->rx, s->rx_shape);
+        if (s->rx_shape >= 0) m.rx_rect = s->rects[s->shapes[s->rx_shape].index];
+        if (s->dev.n_txs != 0 && s->dev.tx0_ep.shape >= 0) m.tx0_rect = s->rects[s->shapes[s->dev.tx0_ep.shape].index];
+        memcpy(h + item_bytes * i, &m, sizeof(m));
+        memcpy(h + off_ep + ep_bytes * i, &m.rx_ep, sizeof(DevEndpoint));
+        if (n_rects) memcpy(h + off_rects + rect_bytes * i, s->rects.data(), n_rects * sizeof(DevRect));
+    }
+    s->ev_trace_used = 0;
+    BF_CUDA(cudaEventRecord(s->ev_begin, s->stream));
+    BF_CUDA(cudaMemcpyAsync(d, h, off_cursors, cudaMemcpyHostToDevice, s->stream));
+    BF_CUDA(cudaEventRecord(s->items_ev, s->stream));
+    BF_CUDA(cudaMemsetAsync(d + off_cursors, 0, 4 * (size_t) n_items, s->stream));
+    BF_CUDA(cudaMemsetAsync(s->d_batch.p, 0, (size_t) n_items * s->profile_floats * 4, s->stream));
+    LaunchCfg cfg; memset(&cfg, 0, sizeof(cfg)); cfg.stream = s->stream; cfg.sm_count = s->sm_count;
+    s->stats.kernel_launches += launch_mega_batch(s->dev, (const MegaItem *) d, n_items, n_samples, (uint32_t *) (d + off_cursors), s->d_totals.p, cfg);
+    BF_CUDA(cudaGetLastError());
+    BF_CUDA(cudaEventRecord(s->ev_end, s->stream));
+    s->stats.samples += (uint64_t) n_items * n_samples;
+    // the scene's own device tables hold none of the items' poses: refreshed (light) before the next plain bf_receive
+    s->tables_dirty = true; s->tables_light = true;
+    return BF_OK;
+}
+
 int bf_receive_batch(bf_scene *s, uint32_t n_items, const bf_batch_item *items, uint64_t n_samples, float *profiles, size_t n_floats) {
     NvtxRange range("bf_receive_batch");
     if (!s || (n_items && !items)) return BF_ERR_INVALID;
@@ -1224,7 +1289,14 @@ int bf_receive_batch(bf_scene *s, uint32_t n_items, const bf_batch_item *items, 
     // copy of the tables the item re-poses (rectangles, receiver), so neighbouring items never wait for each other.  Larger
     // items (several waves each) already fill the machine and run one after the other on the scene's tables.
     const bool concurrent = n_samples <= (1u << 22) && !s->time_trace && s->tune.wave_streams > 1;
-    if (!concurrent) {
+    // Items small enough for k_mega (no meshes, or <= mega_max samples) go out as ONE launch over (samples, items)
+    const bool one_launch = n_items > 1 && s->tune.mega_batch != 0 && s->tune.fused_primary != 0 && !s->wide_filter && !s->time_trace &&
+        s->tune.mega_max >= 0 && n_samples > 0 && n_samples <= (1u << 22) && (s->dev.n_nodes == 0 || (int64_t) n_samples <= s->tune.mega_max) &&
+        (uint64_t) n_items <= 65535u;
+    if (one_launch) {
+        int rc = receive_batch_one_launch(s, n_items, items, (uint32_t) n_samples);
+        if (rc) return rc;
+    } else if (!concurrent) {
         for (uint32_t i = 0; i < n_items; ++i) {
             const bf_batch_item &it = items[i];
             for (uint32_t k = 0; k < it.n_rect_updates; ++k) {
@@ -1561,7 +1633,7 @@ int bf_set_tunable(bf_scene *s, const char *name, int64_t value) {
         {"wave_lanes", &s->tune.wave_lanes, 0, 1ll << 28}, {"wave_streams", &s->tune.wave_streams, 1, 16},
         {"fused_primary", &s->tune.fused_primary, 0, 1}, {"primary_defer", &s->tune.primary_defer, -1, 1},
         {"trace_defer", &s->tune.trace_defer, -1, 1}, {"trace_rounds", &s->tune.trace_rounds, -1, 1024},
-        {"use_graph", &s->tune.use_graph, 0, 1},
+        {"use_graph", &s->tune.use_graph, 0, 1}, {"mega_batch", &s->tune.mega_batch, 0, 1},
         {"path_fused", &s->tune.path_fused, 0, 1}, {"mega_max", &s->tune.mega_max, -1, 1ll << 28}};
     for (auto &t : table)
         if (strcmp(t.n, name) == 0) {

@@ -873,8 +873,7 @@ struct MegaIO {
     uint32_t hist_floats;
 };
 template <int S>
-__global__ void __launch_bounds__(MEGA_THREADS) k_mega(const __grid_constant__ DevScene sc, const __grid_constant__ Wave w, const __grid_constant__ MegaIO io) {
-    extern __shared__ __align__(16) uint32_t mega_smem[];
+__device__ __forceinline__ void mega_body(const DevScene &sc, bf_sample_record *records, const MegaIO &io, uint32_t *mega_smem) {
     float *s_rect = reinterpret_cast<float *>(mega_smem);
     uint2 *s_stack = reinterpret_cast<uint2 *>(mega_smem + RECT_SM_FLOATS * BF_MAX_RECTS);
     float *s_hist = reinterpret_cast<float *>(s_stack + TRACE_SM_STACK * MEGA_THREADS);
@@ -896,7 +895,7 @@ __global__ void __launch_bounds__(MEGA_THREADS) k_mega(const __grid_constant__ D
         const bool have = i < io.n;
         PrimaryState<S> ps;
         LaneRegs<S> R;
-        bf_sample_record *rec = (w.records && have) ? w.records + i : nullptr;
+        bf_sample_record *rec = (records && have) ? records + i : nullptr;
         V3 ro(0.f, 0.f, 0.f), rd(0.f, 0.f, 1.f);
         float mint = 0.f, maxt = 0.f;
         bool alive = have;
@@ -955,6 +954,43 @@ __global__ void __launch_bounds__(MEGA_THREADS) k_mega(const __grid_constant__ D
         __syncthreads();
         flush_hist(s_hist, io.hist_floats, C, n_fixed, io.profile);
     }
+}
+template <int S>
+__global__ void __launch_bounds__(MEGA_THREADS) k_mega(const __grid_constant__ DevScene sc, const __grid_constant__ Wave w, const __grid_constant__ MegaIO io) {
+    extern __shared__ __align__(16) uint32_t mega_smem[];
+    mega_body<S>(sc, w.records, io, mega_smem);
+}
+
+// bf_receive_batch of small items (C4: 256 frames of 1 000 samples; the phased sweep on a small scene) in ONE launch:
+// blockIdx.y is the item.  An item differs from the committed scene in its rectangle table, its receiver and the copies of
+// both inside DevScene (MegaItem); the CTA builds the item's DevScene in shared memory -- the parameter block with those
+// members replaced -- and runs the k_mega body on it.  Reading the scene from shared memory instead of the constant bank
+// costs instructions; launching, uploading and zeroing per item cost 20 us each, ten times the work of such an item.
+template <int S>
+__global__ void __launch_bounds__(MEGA_THREADS) k_mega_batch(const __grid_constant__ DevScene sc0, const MegaItem *__restrict__ items, uint32_t n,
+                                                             uint32_t *cursors, unsigned long long *totals, uint32_t hist_floats) {
+    extern __shared__ __align__(16) uint32_t mega_smem[];
+    __shared__ __align__(16) uint32_t s_scene[(sizeof(DevScene) + 3) / 4];
+    DevScene &sc = *reinterpret_cast<DevScene *>(s_scene);
+    const MegaItem &it = items[blockIdx.y];
+    {
+        const uint32_t *src = reinterpret_cast<const uint32_t *>(&sc0);
+        for (uint32_t i = threadIdx.x; i < sizeof(DevScene) / 4; i += blockDim.x) s_scene[i] = src[i];
+        __syncthreads();
+        auto patch = [&](void *dst, const void *from, uint32_t bytes) {
+            uint32_t *d = static_cast<uint32_t *>(dst); const uint32_t *f = static_cast<const uint32_t *>(from);
+            for (uint32_t i = threadIdx.x; i < bytes / 4; i += blockDim.x) d[i] = f[i];
+        };
+        patch(&sc.rx_ep, &it.rx_ep, sizeof(DevEndpoint));
+        patch(&sc.rx_rect, &it.rx_rect, sizeof(DevRect));
+        patch(&sc.tx0_rect, &it.tx0_rect, sizeof(DevRect));
+        if (threadIdx.x == 0) { sc.rects = it.rects; sc.rx = it.rx; }
+        __syncthreads();
+    }
+    MegaIO io;
+    io.seed = it.seed; io.first_sample = it.first_sample; io.n = n; io.work_cursor = cursors + blockIdx.y; io.totals = totals;
+    io.profile = it.profile; io.hist_floats = hist_floats;
+    mega_body<S>(sc, nullptr, io, mega_smem);
 }
 
 // =========================================================================================================
@@ -1460,6 +1496,19 @@ int launch_mega(const DevScene &sc, const Wave &w, uint64_t seed, uint64_t first
     const int grid = (int) std::min<uint32_t>((uint32_t) cfg.sm_count * 4u, (n + MEGA_THREADS - 1) / MEGA_THREADS);
     if (sc.S == 1) k_mega<1><<<grid, MEGA_THREADS, smem, cfg.stream>>>(sc, w, io);
     else k_mega<4><<<grid, MEGA_THREADS, smem, cfg.stream>>>(sc, w, io);
+    return 1;
+}
+int launch_mega_batch(const DevScene &sc, const MegaItem *items, uint32_t n_items, uint32_t n, uint32_t *cursors, unsigned long long *totals,
+                      const LaunchCfg &cfg) {
+    if (n == 0 || n_items == 0) return 0;
+    const uint32_t floats = sc.channels * sc.film_w * sc.film_h;
+    const uint32_t hist_floats = floats <= 4096u ? floats : 0u;
+    const size_t smem = ((size_t) RECT_SM_FLOATS * BF_MAX_RECTS + 2 * TRACE_SM_STACK * MEGA_THREADS + hist_floats) * 4;
+    // per item: one warp per 32 samples, capped so that the whole batch is a few CTAs per SM
+    const uint32_t per_item_cap = std::max<uint32_t>(((uint32_t) cfg.sm_count * 8u + n_items - 1) / n_items, 1u);
+    const dim3 grid(std::min<uint32_t>(per_item_cap, (n + MEGA_THREADS - 1) / MEGA_THREADS), n_items);
+    if (sc.S == 1) k_mega_batch<1><<<grid, MEGA_THREADS, smem, cfg.stream>>>(sc, items, n, cursors, totals, hist_floats);
+    else k_mega_batch<4><<<grid, MEGA_THREADS, smem, cfg.stream>>>(sc, items, n, cursors, totals, hist_floats);
     return 1;
 }
 int launch_trace_rays(const DevScene &sc, const float4 *ray_o, const float4 *ray_d, uint32_t n, float4 *hit, uint32_t *occl,

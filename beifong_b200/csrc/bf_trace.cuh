@@ -24,7 +24,7 @@ namespace bf {
 #define TRACE_MIN_BLOCKS 8
 #endif
 #ifndef TRACE_TRI_QUEUE
-#define TRACE_TRI_QUEUE 8    // k_trace: triangle slots a lane can queue for the warp's triangle phase (0: test them right behind the node step)
+#define TRACE_TRI_QUEUE 1    // k_trace: leaf triangle groups a lane can queue (besides the one it is testing) for the warp's triangle phase (0: test them right behind the node step)
 #endif
 #ifndef TRACE_TRI_LANES
 #define TRACE_TRI_LANES 12   // the triangle phase starts when this many lanes hold queued triangles (and runs down to half of it)
@@ -323,7 +323,7 @@ __global__ void __launch_bounds__(TRACE_THREADS, TRACE_MIN_BLOCKS) k_trace(const
     // closest-hit queries queue their triangle tests (measured on C3: 1 537 us against 1 675 us, 16.7 against 13.9 threads per
     // instruction, profiles/r02n); any-hit queries test on the spot (an early hit ends the ray: queueing made them slower)
     constexpr int TQ = ANY_HIT ? 0 : TRACE_TRI_QUEUE;
-    __shared__ uint32_t s_tq[TQ > 0 ? TQ * TRACE_THREADS : 1];      // per-lane queue of triangle slots awaiting their test
+    __shared__ uint2 s_tq[TQ > 0 ? TQ * TRACE_THREADS : 1];         // per-lane queue of leaf triangle groups awaiting their tests
     uint2 l_stack[TRACE_LOCAL_STACK];
     stage_rects(sc, s_rect);
     const uint32_t n = io.queue ? *io.count : io.n_direct;
@@ -366,8 +366,8 @@ __global__ void __launch_bounds__(TRACE_THREADS, TRACE_MIN_BLOCKS) k_trace(const
     enum { EMPTY = 0, BUSY = 1, FINISHED = 2, EXHAUSTED = 3 };
     int state = EMPTY;
     uint32_t l = 0, n_steps = 0, pend_l = 0;
-    uint32_t qcnt = 0;                      // triangles queued in s_tq for this lane
-    uint2 tpend = make_uint2(0u, 0u);       // triangle group of the last node step not yet expanded into the queue
+    uint32_t qcnt = 0;                      // triangle groups queued in s_tq for this lane
+    uint2 tpend = make_uint2(0u, 0u);       // the triangle group this lane is testing (base slot, mask of the triangles left)
     TraceLane L;
     while (true) {
         // ---- complete the push reserved at the previous commit point ----
@@ -476,34 +476,35 @@ __global__ void __launch_bounds__(TRACE_THREADS, TRACE_MIN_BLOCKS) k_trace(const
             continue;
         }
         // Two phases per iteration.  NODE: every busy lane does one node step; the leaf triangles it finds are not tested on the
-        // spot (after a node step ~2 of 32 lanes have one: profiles/r02e) but QUEUED, slot by slot, in the lane's shared-memory
-        // queue.  TRIANGLE: when enough lanes hold queued triangles (or nothing else is left to do) those lanes test one triangle
-        // each per pass, for as long as enough of them have some; what is left stays queued.  Results do not depend on the order
-        // of the tests: closest-hit ties are broken by (shape, prim).
+        // spot (after a node step ~2 of 32 lanes have one: profiles/r02e) but kept as a (base slot, bit mask) group: the lane's
+        // current group in registers, up to TQ more in its shared-memory queue.  TRIANGLE: when enough lanes hold a group (or
+        // nothing else is left to do) those lanes test one triangle each per pass, for as long as enough of them have some; what
+        // is left stays queued.  Results do not depend on the order of the tests: closest-hit ties are broken by (shape, prim).
         do {
-            if (state == BUSY) {
-                if (tpend.y == 0u) {
-                    if (L.ngroup.y <= 0x00ffffffu && L.sp > 0) {
-                        --L.sp;
-                        L.ngroup = L.sp < TRACE_SM_STACK ? s_stack[L.sp * TRACE_THREADS + threadIdx.x] : l_stack[L.sp - TRACE_SM_STACK];
-                    }
-                    if (L.ngroup.y > 0x00ffffffu) { ++n_steps; node_step(sc, s_stack, l_stack, L, tpend); }
+            if (state == BUSY && qcnt < (uint32_t) TQ) {
+                if (L.ngroup.y <= 0x00ffffffu && L.sp > 0) {
+                    --L.sp;
+                    L.ngroup = L.sp < TRACE_SM_STACK ? s_stack[L.sp * TRACE_THREADS + threadIdx.x] : l_stack[L.sp - TRACE_SM_STACK];
                 }
-                while (tpend.y != 0u && qcnt < (uint32_t) TQ) {
-                    const uint32_t i = 31u - __clz(tpend.y);
-                    tpend.y &= ~(1u << i);
-                    s_tq[qcnt * TRACE_THREADS + threadIdx.x] = tpend.x + i;
-                    ++qcnt;
+                if (L.ngroup.y > 0x00ffffffu) {
+                    uint2 tg;
+                    ++n_steps; node_step(sc, s_stack, l_stack, L, tg);
+                    if (tg.y != 0u) {
+                        if (tpend.y == 0u) tpend = tg;
+                        else { s_tq[qcnt * TRACE_THREADS + threadIdx.x] = tg; ++qcnt; }
+                    }
                 }
             }
-            const uint32_t have_tri = __ballot_sync(0xffffffffu, state == BUSY && qcnt > 0u);
-            const uint32_t can_node = __ballot_sync(0xffffffffu, state == BUSY && tpend.y == 0u && (L.ngroup.y > 0x00ffffffu || L.sp > 0));
+            const uint32_t have_tri = __ballot_sync(0xffffffffu, state == BUSY && tpend.y != 0u);
+            const uint32_t can_node = __ballot_sync(0xffffffffu, state == BUSY && qcnt < (uint32_t) TQ && (L.ngroup.y > 0x00ffffffu || L.sp > 0));
             if (have_tri != 0u && (__popc(have_tri) >= TRACE_TRI_LANES || can_node == 0u)) {
                 uint32_t m = have_tri;
                 do {
-                    if (state == BUSY && qcnt > 0u) {
-                        --qcnt;
-                        const uint32_t slot = s_tq[qcnt * TRACE_THREADS + threadIdx.x];
+                    if (state == BUSY && tpend.y != 0u) {
+                        const uint32_t i = 31u - __clz(tpend.y);
+                        tpend.y &= ~(1u << i);
+                        const uint32_t slot = tpend.x + i;
+                        if (tpend.y == 0u && qcnt > 0u) { --qcnt; tpend = s_tq[qcnt * TRACE_THREADS + threadIdx.x]; }
                         float t, u, v; uint32_t shape, prim;
                         if (tri_test(sc.tris, slot, L.o, L.d, L.mint, L.maxt, t, u, v, shape, prim)) {
                             if (ANY_HIT) { L.occluded = true; state = FINISHED; qcnt = 0u; tpend.y = 0u; }
@@ -512,11 +513,11 @@ __global__ void __launch_bounds__(TRACE_THREADS, TRACE_MIN_BLOCKS) k_trace(const
                             }
                         }
                     }
-                    m = __ballot_sync(0xffffffffu, state == BUSY && qcnt > 0u);
+                    m = __ballot_sync(0xffffffffu, state == BUSY && tpend.y != 0u);
                 } while (m != 0u && (__popc(m) >= (TRACE_TRI_LANES + 1) / 2 || can_node == 0u));
             }
             // nothing left anywhere for this lane: the traversal is finished
-            if (state == BUSY && qcnt == 0u && tpend.y == 0u && L.ngroup.y <= 0x00ffffffu && L.sp == 0) state = FINISHED;
+            if (state == BUSY && tpend.y == 0u && L.ngroup.y <= 0x00ffffffu && L.sp == 0) state = FINISHED;
         } while (__popc(__ballot_sync(0xffffffffu, state == BUSY)) >= min_busy);
     }
 }

@@ -87,6 +87,18 @@ int launch_refit_tris(const float4 *rest, const float4 *rest_nrm, float4 *tris, 
 int launch_refit_nodes(uint4 *nodes, const float4 *tris, float *node_box, const uint32_t *level_first, uint32_t n_levels, float pad_abs, const LaunchCfg &cfg);
 int launch_power_db(const float *raw, float *out, uint32_t n_bins, uint32_t channels, uint32_t ch, double sample_count, int mode, const LaunchCfg &cfg);
 int launch_develop(const float *raw, void *out, uint32_t n_bins, uint32_t channels, bool half_out, const LaunchCfg &cfg);
+// One item of a batched k_mega launch (bf_receive_batch): what differs from the committed scene
+struct MegaItem {
+    uint64_t seed, first_sample;
+    float *profile;
+    const DevRect *rects;      // this item's rectangle table and receiver (device)
+    const DevEndpoint *rx;
+    DevEndpoint rx_ep;         // ... and the copies DevScene carries by value
+    DevRect rx_rect, tx0_rect;
+};
+// all items in one launch (grid.y = item); cursors: one zeroed word per item
+int launch_mega_batch(const DevScene &sc, const MegaItem *items, uint32_t n_items, uint32_t n, uint32_t *cursors, unsigned long long *totals,
+                      const LaunchCfg &cfg);
 // Stand-alone ray queries (Scene::ray_intersect_preliminary / ray_test for caller-provided rays)
 int launch_trace_rays(const DevScene &sc, const float4 *ray_o, const float4 *ray_d, uint32_t n, float4 *hit, uint32_t *occl,
                       uint32_t *work_cursor, const LaunchCfg &cfg);

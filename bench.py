@@ -279,6 +279,7 @@ def main():
     if itemised:
         mine = multi.shard_items(N_ITEMS[name], rank, world)
         items = batch_items(name, ids, mine)
+        packed = scene.pack_batch(items)      # the bf_batch_item array the C ABI takes (host buffers), marshalled once
         n_local, n_global = S * len(mine), S * N_ITEMS[name]
         first = 0
     elif args.scaling == "strong":
@@ -289,7 +290,7 @@ def main():
 
     def step(i, e2e=False):
         if itemised:
-            return scene.receive_batch(items, S, read=e2e)          # e2e: per-item poses in, item profiles out
+            return scene.receive_batch(packed, S, read=e2e)         # e2e: per-item poses in, item profiles out
         if e2e:
             scene.reupload()                                        # host -> device: flattened scene from pinned memory
         scene.receive(n_local, seed=i, first_sample=first, accumulate=False)

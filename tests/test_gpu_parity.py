@@ -339,12 +339,16 @@ def test_c4_sequence_moves_endpoints(native):
     s.close()
 
 
-def test_receive_batch_equals_frame_loop(native):
+@pytest.mark.parametrize("one_launch", [1, 0])
+def test_receive_batch_equals_frame_loop(native, one_launch):
     """bf_receive_batch (the frames of the moving-target sequence as one submission, per-item profiles, no host synchronisation
-    between items) against one bf_receive + bf_profile_read per frame on a scene built from scratch for that frame."""
+    between items) against one bf_receive + bf_profile_read per frame on a scene built from scratch for that frame.
+    one_launch = 1: the product default for small items, every item in ONE k_mega_batch launch; 0: one k_mega launch per item."""
     s, tx = configs.c4_animated(frame=0)
     s.commit()
-    s.set_tunable("mega_max", 1 << 18)       # the product default: a scene without meshes runs as one k_mega launch per item
+    s.set_tunable("mega_max", 1 << 18)       # the product default: a scene without meshes runs as k_mega
+    s.set_tunable("mega_batch", one_launch)
+    launches_before = s.stats()["kernel_launches"]
     frames, n = [3, 64, 65, 200, 255], 4000
     items = []
     for f in frames:
@@ -352,6 +356,7 @@ def test_receive_batch_equals_frame_loop(native):
         items.append(dict(seed=f, rects=[(tx, (pose * meshes.Transform.scale([0.5, 0.5, 1.0])).matrix32())], receiver=(None, configs.c4_receiver(pose))))
     got = s.receive_batch(items, n)
     assert got.shape[0] == len(frames)
+    assert s.stats()["kernel_launches"] - launches_before == (1 if one_launch else len(frames))
     for k, f in enumerate(frames):
         fresh_scene, _ = configs.c4_animated(frame=f)
         fresh_scene.commit()
@@ -368,10 +373,14 @@ def test_receive_batch_equals_frame_loop(native):
     s.close()
 
 
-def test_receive_batch_receive_elements(native):
-    """C5 as a batch: the elements of the receive array are the items (the receiver rectangle re-posed per item, seed = element)."""
+@pytest.mark.parametrize("pipeline", ["wavefront", "one_launch"])
+def test_receive_batch_receive_elements(native, pipeline):
+    """C5 as a batch: the elements of the receive array are the items (the receiver rectangle re-posed per item, seed = element).
+    one_launch: items of <= mega_max samples on a scene WITH meshes, all in one k_mega_batch launch."""
     s, rx = configs.c5_urban(n_side=6, face_grid=3)
     s.commit()
+    if pipeline == "one_launch":
+        s.set_tunable("mega_max", 1 << 18)
     elems, n = [0, 1, 31, 63], 1 << 15
     got = s.receive_batch([dict(seed=k, rects=[(rx, configs.c5_element_pose(k))]) for k in elems], n)
     for i, k in enumerate(elems):
