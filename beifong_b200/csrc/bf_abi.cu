@@ -1268,7 +1268,9 @@ static int receive_batch_one_launch(bf_scene *s, uint32_t n_items, const bf_batc
     BF_CUDA(cudaMemsetAsync(d + off_cursors, 0, 4 * (size_t) n_items, s->stream));
     BF_CUDA(cudaMemsetAsync(s->d_batch.p, 0, (size_t) n_items * s->profile_floats * 4, s->stream));
     LaunchCfg cfg; memset(&cfg, 0, sizeof(cfg)); cfg.stream = s->stream; cfg.sm_count = s->sm_count;
+    if (s->time_trace) cudaEventRecord(next_trace_event(s, BF_K_PRIMARY), s->stream);
     s->stats.kernel_launches += launch_mega_batch(s->dev, (const MegaItem *) d, n_items, n_samples, (uint32_t *) (d + off_cursors), s->d_totals.p, cfg);
+    if (s->time_trace) cudaEventRecord(next_trace_event(s, BF_K_PRIMARY), s->stream);
     BF_CUDA(cudaGetLastError());
     BF_CUDA(cudaEventRecord(s->ev_end, s->stream));
     s->stats.samples += (uint64_t) n_items * n_samples;
@@ -1290,7 +1292,7 @@ int bf_receive_batch(bf_scene *s, uint32_t n_items, const bf_batch_item *items, 
     // items (several waves each) already fill the machine and run one after the other on the scene's tables.
     const bool concurrent = n_samples <= (1u << 22) && !s->time_trace && s->tune.wave_streams > 1;
     // Items small enough for k_mega (no meshes, or <= mega_max samples) go out as ONE launch over (samples, items)
-    const bool one_launch = n_items > 1 && s->tune.mega_batch != 0 && s->tune.fused_primary != 0 && !s->wide_filter && !s->time_trace &&
+    const bool one_launch = n_items > 1 && s->tune.mega_batch != 0 && s->tune.fused_primary != 0 && !s->wide_filter &&
         s->tune.mega_max >= 0 && n_samples > 0 && n_samples <= (1u << 22) && (s->dev.n_nodes == 0 || (int64_t) n_samples <= s->tune.mega_max) &&
         (uint64_t) n_items <= 65535u;
     if (one_launch) {

@@ -1498,6 +1498,9 @@ int launch_mega(const DevScene &sc, const Wave &w, uint64_t seed, uint64_t first
     else k_mega<4><<<grid, MEGA_THREADS, smem, cfg.stream>>>(sc, w, io);
     return 1;
 }
+#ifndef MEGA_BATCH_CTAS_PER_SM
+#define MEGA_BATCH_CTAS_PER_SM 8u
+#endif
 int launch_mega_batch(const DevScene &sc, const MegaItem *items, uint32_t n_items, uint32_t n, uint32_t *cursors, unsigned long long *totals,
                       const LaunchCfg &cfg) {
     if (n == 0 || n_items == 0) return 0;
@@ -1505,7 +1508,7 @@ int launch_mega_batch(const DevScene &sc, const MegaItem *items, uint32_t n_item
     const uint32_t hist_floats = floats <= 4096u ? floats : 0u;
     const size_t smem = ((size_t) RECT_SM_FLOATS * BF_MAX_RECTS + 2 * TRACE_SM_STACK * MEGA_THREADS + hist_floats) * 4;
     // per item: one warp per 32 samples, capped so that the whole batch is a few CTAs per SM
-    const uint32_t per_item_cap = std::max<uint32_t>(((uint32_t) cfg.sm_count * 8u + n_items - 1) / n_items, 1u);
+    const uint32_t per_item_cap = std::max<uint32_t>(((uint32_t) cfg.sm_count * MEGA_BATCH_CTAS_PER_SM + n_items - 1) / n_items, 1u);
     const dim3 grid(std::min<uint32_t>(per_item_cap, (n + MEGA_THREADS - 1) / MEGA_THREADS), n_items);
     if (sc.S == 1) k_mega_batch<1><<<grid, MEGA_THREADS, smem, cfg.stream>>>(sc, items, n, cursors, totals, hist_floats);
     else k_mega_batch<4><<<grid, MEGA_THREADS, smem, cfg.stream>>>(sc, items, n, cursors, totals, hist_floats);

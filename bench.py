@@ -413,7 +413,8 @@ def roofline_block(scene, workload, n, first, per_gpu_value, itemised, items):
     for i in range(reps):
         a = scene.stats()
         if itemised:
-            scene.receive_batch(items[:1], n, read=False)
+            # items k_mega can run (no meshes) are ONE launch for the whole batch: time that launch; otherwise one item's waves
+            scene.receive_batch(items if workload["triangles"] == 0 else items[:1], n, read=False)
         else:
             scene.receive(n, seed=3000 + i, first_sample=first)
         scene.synchronize()
@@ -440,6 +441,11 @@ def roofline_block(scene, workload, n, first, per_gpu_value, itemised, items):
                   "scatter for every path that stays clear of the meshes; spills the rest into the wavefront")
         alg_per_launch = (tot["path_closest_queries"] * b_closest + tot["path_shadow_queries"] * b_shadow + samples * b_bins) / max(dom_launch, 1)
         unit_note = "queries decided inside k_path x (B_path [+ 48]) + 8 C per sample"
+    elif dom == "primary" and workload["triangles"] == 0:
+        kernel = ("k_mega (k_mega_batch when the step is a bf_receive_batch): one thread per sample, receiver ray to range bin in one launch; "
+                  "the scene has no meshes, so SURVEY 8(d)'s bytes per query are an upper bound that no kernel here moves")
+        alg_per_launch = samples * b_closest / max(dom_launch, 1)
+        unit_note = "one closest-hit query per sample x (B_path + 48)"
     elif dom == "primary":
         kernel = "k_primary: receiver ray generation + first closest-hit query + compaction"
         alg_per_launch = samples * b_closest / max(dom_launch, 1)
