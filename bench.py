@@ -468,7 +468,8 @@ def roofline_block(scene, workload, n, first, per_gpu_value, itemised, items):
             ceiling = 148 * 4 * sm_clock / tr["step_warp_inst_per_sample"]
             issue = {"warp_inst_per_sample": tr["step_warp_inst_per_sample"], "k_path_warp_inst_per_sample": tr.get("k_path_warp_inst_per_sample"),
                      "ceiling_samples_per_s": ceiling, "frac": per_gpu_value / ceiling, "dram_bytes_per_sample_step": tr.get("step_dram_bytes_per_sample"),
-                     "dram_frac_step": tr.get("step_dram_bytes_per_sample", 0) * per_gpu_value / 1e9 / peak, "source": tr.get("source")}
+                     "dram_frac_step": tr.get("step_dram_bytes_per_sample", 0) * per_gpu_value / 1e9 / peak,
+                     "traversal_thread_inst_per_inst": tr.get("traversal_thread_inst_per_inst"), "source": tr.get("source")}
     except Exception:   # noqa: BLE001
         pass
     return {"bound": "hbm", "limiter": "issue slots (ncu: the scene is L2-resident, DRAM moves a few % of peak; see `issue`)" if workload["triangles"] < 5_000_000 else "hbm / L2 (the scene exceeds L2)",
