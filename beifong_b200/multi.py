@@ -67,8 +67,8 @@ def receive_sharded(scene, n_total, seed, rank, world, accumulate=False, profile
     """One sharded frame: this rank's slice of the sample range through bf_receive, then the single reduce, issued
     on the scene's stream so that it follows the last wavefront without a host sync.
     native=True: the reduce is bf_multi_reduce (after init_native_reduce); otherwise torch.distributed on profile_tensor.
-    accumulate=True: rank `dst` keeps the running total; the reduce is in place, so every other rank clears its partial sum
-    after it has been reduced (otherwise the next reduce would add it a second time)."""
+    accumulate=True: rank `dst` keeps the running total.  The reduce is in place, so every other rank clears its partial sum
+    after it has been reduced, on every frame (otherwise a later accumulated frame would add it a second time)."""
     first, n = shard_samples(n_total, rank, world)
     if n > 0:
         scene.receive(n, seed=seed, first_sample=first, accumulate=accumulate)
@@ -81,6 +81,8 @@ def receive_sharded(scene, n_total, seed, rank, world, accumulate=False, profile
             import torch
             with torch.cuda.stream(stream):
                 reduce_profile(profile_tensor, dst=dst)
-        if accumulate and rank != dst and (native or profile_tensor is not None):
-            scene.receive(0, seed=seed, first_sample=first, accumulate=False)      # clear: stream-ordered behind the reduce
+        if rank != dst and (native or profile_tensor is not None):
+            # clear, stream-ordered behind the reduce -- after EVERY frame, also one received with accumulate=False: the next
+            # frame may accumulate, and this rank's partial sum is already part of dst's total
+            scene.receive(0, seed=seed, first_sample=first, accumulate=False)
     return first, n
