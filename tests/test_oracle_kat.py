@@ -567,3 +567,39 @@ def test_cubic_and_lanczos_filter_tables():
     x = 2.0 * int(1.5 * 31 / 2.0) / 31
     want = (1 / 6) * (-3 * x ** 3 + 15 * x ** 2 - 24 * x + 12)
     assert want < 0 and np.isclose(o[0, 9], want, rtol=1e-4) and np.isclose(o[0, 6], want, rtol=1e-4)
+
+
+def test_rfilter_reference_spot_checks():
+    """The reference's own reconstruction-filter spot checks (src/rfilters/tests/test_rfilter.py:16-51: gaussian eval(0.2) = 0.9227,
+    lanczos eval(1.4) = -0.14668, mitchell eval(0) = 0.8888, catmullrom eval(0) = 0.9765, tent eval(0.1) = 0.903, zero beyond the
+    radius; same tolerances) read off the oracle's wide splat: a sample at distance x from a bin centre on a one-row film deposits
+    f(x) f(0), and f(0)^2 when it sits on the centre."""
+    def f_of(kind, radius, x):
+        centre = _splat(32, 1, kind, radius, 16.5, 0.5)[0, 16]
+        return _splat(32, 1, kind, radius, 16.5 + x, 0.5)[0, 16] / math.sqrt(centre), math.sqrt(centre)
+    g, g0 = f_of(1, 2.0, 0.2)
+    assert abs(g - 0.9227) <= 8e-3 and f_of(1, 2.0, 2.1)[0] == 0
+    lz, _ = f_of(5, 3.0, 1.4)
+    assert abs(lz - (-0.14668)) <= 1e-2 and f_of(5, 3.0, 3.1)[0] == 0
+    _, m0 = f_of(3, 2.0, 0.0)
+    assert abs(m0 - 0.8888) <= 1e-3 and f_of(3, 2.0, 2.1)[0] == 0
+    _, c0 = f_of(4, 2.0, 0.0)
+    assert abs(c0 - 0.9765) <= 5e-2 and f_of(4, 2.0, 2.1)[0] == 0
+    t, _ = f_of(2, 1.0, 0.1)
+    assert abs(t - 0.903) <= 5e-2 and f_of(2, 1.0, 1.1)[0] == 0
+
+
+def test_develop_reference_property_unit_weights():
+    """The reference's own film test (src/adcs/tests/test_hdrfilm.py:73-140, test03_develop): a 41 x 37 image put with unit
+    weights and developed with float32 components comes back unchanged (atol 1e-5), the weight channel dropped.  Same seed and
+    size; here the storage layout is the radar ADC's (Y, A, W, aovs) with the weight at index 2 (hdradc.cpp:256-259)."""
+    from oracle.develop import develop
+    np.random.seed(12345 + ord("e"))
+    contents = np.random.uniform(size=(37, 41, 5)).astype(np.float32)
+    contents[:, :, 2] = 1.0
+    img = develop(contents, "float32")
+    assert img.shape == (37, 41, 4)
+    assert np.allclose(img, contents[:, :, [0, 1, 3, 4]], atol=1e-5)
+    # and a constant non-unit weight rescales every channel by it
+    contents[:, :, 2] = 4.0
+    assert np.allclose(develop(contents, "float32") * 4.0, contents[:, :, [0, 1, 3, 4]], atol=1e-5)
