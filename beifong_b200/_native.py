@@ -115,6 +115,7 @@ PROTOTYPES = {
     "bf_profile_power_db": (C.c_int, [vp, u32, C.c_double, C.c_int, P(f32), C.c_size_t]),
     "bf_profile_device_ptr": (C.c_int, [vp, P(vp), P(C.c_size_t), P(vp)]),
     "bf_synchronize": (C.c_int, [vp]),
+    "bf_scene_set_stream": (C.c_int, [vp, vp]),
     "bf_multi_unique_id": (C.c_int, [vp, C.c_size_t]),
     "bf_multi_init": (C.c_int, [vp, C.c_int, C.c_int, vp, C.c_size_t]),
     "bf_multi_reduce": (C.c_int, [vp, C.c_int]),

@@ -166,6 +166,7 @@ struct Tunables {
     int64_t use_graph = 1;        // small calls: replay the wave's launch sequence from a CUDA graph
     int64_t mega_batch = 1;       // bf_receive_batch: items that k_mega can run go out as one launch
     int64_t path_fused = 1;       // scenes with a deferred primary: k_path integrates the rectangle-only paths in registers
+    int64_t l2_persist_mb = 0;    // > 0: an L2 access-policy window (persisting) over the first MB of the breadth-first BVH node array, i.e. its top levels
     int64_t mega_max = 262144;    // requests up to this many samples, and every request on a scene without meshes (-1: never), run as ONE k_mega launch
 };
 static int64_t env_i64(const char *name, int64_t dflt, int64_t lo, int64_t hi) {
@@ -188,6 +189,7 @@ static Tunables tunables_from_env() {
     t.mega_batch = env_i64("BF_MEGA_BATCH", 1, 0, 1);
     t.path_fused = env_i64("BF_PATH_FUSED", 1, 0, 1);
     t.mega_max = env_i64("BF_MEGA_MAX", 262144, -1, 1ll << 28);
+    t.l2_persist_mb = env_i64("BF_L2_PERSIST_MB", 0, 0, 4096);
     return t;
 }
 
@@ -212,7 +214,9 @@ struct bf_scene {
     bool committed = false, tables_dirty = false;
     bool tables_light = false;       // tables_dirty, but only rectangle poses and / or a non-phased receiver descriptor changed since the last upload
     int device = 0, sm_count = 148;
-    cudaStream_t stream = nullptr;
+    cudaStream_t stream = nullptr;        // the stream every entry point enqueues on: own_stream, or the caller's (bf_scene_set_stream)
+    cudaStream_t own_stream = nullptr;
+    size_t l2_window_max = 0; bool l2_window_touched = false;     // tune.l2_persist_mb
     DevScene dev;
     DevBuf<uint4> d_nodes; DevBuf<float4> d_tris, d_tri_nrm;
     DevBuf<float4> d_tris_rest, d_nrm_rest; DevBuf<float> d_node_box; bool rest_saved = false;    // bf_scene_update_transform (refit)
@@ -402,6 +406,7 @@ int bf_scene_create(const bf_constants *consts, bf_scene **out) {
 }
 
 static void free_wave(bf_scene *s);
+static void apply_l2_persistence(bf_scene *s);
 
 void bf_scene_destroy(bf_scene *s) {
     if (!s) return;
@@ -423,7 +428,7 @@ void bf_scene_destroy(bf_scene *s) {
         if (s->ev_begin) cudaEventDestroy(s->ev_begin);
         if (s->ev_end) cudaEventDestroy(s->ev_end);
         for (cudaEvent_t e : s->ev_trace) cudaEventDestroy(e);
-        if (s->stream) cudaStreamDestroy(s->stream);
+        if (s->own_stream) cudaStreamDestroy(s->own_stream);
     }
     delete s;
 }
@@ -810,7 +815,8 @@ int bf_scene_commit(bf_scene *s, int device) {
     cudaDeviceProp prop;
     BF_CUDA(cudaGetDeviceProperties(&prop, device));
     s->sm_count = prop.multiProcessorCount;
-    BF_CUDA(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
+    BF_CUDA(cudaStreamCreateWithFlags(&s->own_stream, cudaStreamNonBlocking));
+    s->stream = s->own_stream;
     BF_CUDA(cudaEventCreate(&s->ev_begin)); BF_CUDA(cudaEventCreate(&s->ev_end));
 
     // ---- BVH over all mesh triangles, shape order ----
@@ -901,6 +907,7 @@ int bf_scene_commit(bf_scene *s, int device) {
     BF_CUDA(cudaStreamSynchronize(s->stream));
     s->stats.upload_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t1).count();
     s->committed = true;
+    apply_l2_persistence(s);      // BF_L2_PERSIST_MB / bf_set_tunable("l2_persist_mb"): off unless asked for
     return BF_OK;
 }
 
@@ -1038,12 +1045,40 @@ static void free_wave(bf_scene *s) {
     s->slots.clear();
 }
 
+// L2 persistence for the top of the BVH: the node array is in breadth-first order, so a window over its
+// first bytes covers the levels every ray visits.  Kernels launched on `st` afterwards inherit the window.
+static void apply_l2_window(bf_scene *s, cudaStream_t st) {
+    if (!s->l2_window_touched && s->tune.l2_persist_mb <= 0) return;
+    cudaStreamAttrValue a;
+    memset(&a, 0, sizeof(a));
+    size_t bytes = std::min<size_t>((size_t) s->tune.l2_persist_mb << 20, s->dev.n_nodes * (size_t) 80);
+    bytes = std::min<size_t>(bytes, s->l2_window_max);
+    a.accessPolicyWindow.base_ptr = bytes ? (void *) s->d_nodes.p : nullptr;
+    a.accessPolicyWindow.num_bytes = bytes;
+    a.accessPolicyWindow.hitRatio = bytes ? 1.f : 0.f;
+    a.accessPolicyWindow.hitProp = bytes ? cudaAccessPropertyPersisting : cudaAccessPropertyNormal;
+    a.accessPolicyWindow.missProp = cudaAccessPropertyNormal;
+    if (cudaStreamSetAttribute(st, cudaStreamAttributeAccessPolicyWindow, &a) != cudaSuccess) cudaGetLastError();
+    s->l2_window_touched = true;
+}
+static void apply_l2_persistence(bf_scene *s) {
+    if (!s->committed || (!s->l2_window_touched && s->tune.l2_persist_mb <= 0)) return;
+    cudaDeviceProp prop;
+    if (cudaGetDeviceProperties(&prop, s->device) != cudaSuccess) { cudaGetLastError(); return; }
+    s->l2_window_max = (size_t) std::max(prop.accessPolicyMaxWindowSize, 0);
+    const size_t want = std::min<size_t>((size_t) s->tune.l2_persist_mb << 20, (size_t) std::max(prop.persistingL2CacheMaxSize, 0));
+    if (cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, want) != cudaSuccess) cudaGetLastError();
+    if (want == 0) cudaCtxResetPersistingL2Cache();
+    apply_l2_window(s, s->stream);
+    for (WaveSlot &sl : s->slots) if (sl.own_stream) apply_l2_window(s, sl.stream);
+}
+
 static int ensure_slot(bf_scene *s, size_t index, uint32_t lanes, bool records) {
     while (s->slots.size() <= index) {
         WaveSlot sl;
         memset(&sl.wave, 0, sizeof(sl.wave));
         if (s->slots.empty()) { sl.stream = s->stream; sl.own_stream = false; }
-        else { BF_CUDA(cudaStreamCreateWithFlags(&sl.stream, cudaStreamNonBlocking)); sl.own_stream = true; }
+        else { BF_CUDA(cudaStreamCreateWithFlags(&sl.stream, cudaStreamNonBlocking)); sl.own_stream = true; apply_l2_window(s, sl.stream); }
         BF_CUDA(cudaEventCreateWithFlags(&sl.done, cudaEventDisableTiming));
         BF_CUDA(cudaMallocHost((void **) &sl.h_counts, 64));
         s->slots.push_back(sl);
@@ -1437,6 +1472,23 @@ int bf_multi_reduce(bf_scene *s, int root) {
     return bf_multi_reduce_comm(s, s->nccl_comm, root);
 }
 
+int bf_scene_set_stream(bf_scene *s, void *cuda_stream) {
+    if (!s) return BF_ERR_INVALID;
+    if (!s->committed) return fail(s, BF_ERR_STATE, "bf_scene_set_stream: the scene is not committed");
+    BF_CUDA(cudaSetDevice(s->device));
+    BF_CUDA(cudaStreamSynchronize(s->stream));     // nothing of this scene is left on the stream being given up
+    cudaStream_t next = cuda_stream ? (cudaStream_t) cuda_stream : s->own_stream;
+    if (cuda_stream) {
+        // a handle that is not a stream of this device's context fails here, not inside a later launch
+        const cudaError_t e = cudaStreamQuery(next);
+        if (e != cudaSuccess && e != cudaErrorNotReady) { cudaGetLastError(); return fail(s, BF_ERR_INVALID, std::string("bf_scene_set_stream: not a usable stream (") + cudaGetErrorString(e) + ")"); }
+    }
+    s->stream = next;
+    apply_l2_window(s, next);
+    if (!s->slots.empty() && !s->slots[0].own_stream) s->slots[0].stream = next;      // wave slot 0 runs on the scene's stream
+    return BF_OK;
+}
+
 int bf_synchronize(bf_scene *s) {
     if (!s || !s->committed) return BF_ERR_STATE;
     BF_CUDA(cudaSetDevice(s->device));
@@ -1636,12 +1688,14 @@ int bf_set_tunable(bf_scene *s, const char *name, int64_t value) {
         {"fused_primary", &s->tune.fused_primary, 0, 1}, {"primary_defer", &s->tune.primary_defer, -1, 1},
         {"trace_defer", &s->tune.trace_defer, -1, 1}, {"trace_rounds", &s->tune.trace_rounds, -1, 1024},
         {"use_graph", &s->tune.use_graph, 0, 1}, {"mega_batch", &s->tune.mega_batch, 0, 1},
-        {"path_fused", &s->tune.path_fused, 0, 1}, {"mega_max", &s->tune.mega_max, -1, 1ll << 28}};
+        {"path_fused", &s->tune.path_fused, 0, 1}, {"mega_max", &s->tune.mega_max, -1, 1ll << 28},
+        {"l2_persist_mb", &s->tune.l2_persist_mb, 0, 4096}};
     for (auto &t : table)
         if (strcmp(t.n, name) == 0) {
             if (value < t.lo || value > t.hi) return fail(s, BF_ERR_INVALID, std::string("bf_set_tunable: value out of range for ") + name);
             if (t.p == &s->tune.wave_lanes && value != 0 && value < 1024) value = 1024;
             *t.p = value;
+            if (t.p == &s->tune.l2_persist_mb) apply_l2_persistence(s);
             return BF_OK;
         }
     return fail(s, BF_ERR_INVALID, std::string("bf_set_tunable: unknown tunable ") + name);

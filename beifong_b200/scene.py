@@ -268,6 +268,10 @@ class FlatScene:
     def synchronize(self):
         self._ck(N.lib().bf_synchronize(self._h), "bf_synchronize")
 
+    def set_stream(self, cuda_stream):
+        """bf_scene_set_stream: every entry point enqueues on `cuda_stream` (a cudaStream_t as an integer; None / 0: the library's own)."""
+        self._ck(N.lib().bf_scene_set_stream(self._h, C.c_void_p(int(cuda_stream) if cuda_stream else None)), "bf_scene_set_stream")
+
     # ---- multi-GPU through the C ABI (NCCL bound inside the library, no torch on the data path) ----
     @staticmethod
     def multi_unique_id():

@@ -301,6 +301,14 @@ int bf_profile_power_db(bf_scene *s, uint32_t channel, double sample_count, int 
  * that reduces it with NCCL, §8e). */
 int bf_profile_device_ptr(bf_scene *s, void **dptr, size_t *n_floats, void **cuda_stream);
 int bf_synchronize(bf_scene *s);
+/* Caller-supplied stream (the plugin runs inside a host application that owns its streams; the reference's
+ * GPU variant launches on the default stream, src/librender/scene_optix.inl:284,336,348, i.e. ordered with the application's own work).  After bf_scene_commit every entry point
+ * of the scene enqueues on ONE stream -- the library's own by default; this call synchronises that stream and adopts
+ * `cuda_stream` (a cudaStream_t of the scene's device) instead, NULL goes back to the library's own.  bf_receive still fans
+ * its waves out over internal streams, but forks from and joins back into this stream, so the call is ordered after the
+ * caller's earlier work on it and the caller's later work sees the finished profile.  The caller keeps ownership: the
+ * stream must stay alive until the scene is destroyed or given another one.  BF_ERR_STATE before commit. */
+int bf_scene_set_stream(bf_scene *s, void *cuda_stream);
 
 /* Multi-GPU (the reference has no equivalent): one process or thread per GPU, the scene replicated, sample
  * indices sharded by the caller (disjoint [first_sample, first_sample + n) per rank), then ONE ncclReduce of the per-rank

@@ -248,6 +248,8 @@ public:
     // SAH build + upload; throws when there is no CUDA device (no CPU fallback)
     void commit(int device = 0) { check(bf_scene_commit(m_h, device), "bf_scene_commit"); m_committed = true; }
     bool committed() const { return m_committed; }
+    // every later call of this scene is enqueued on the application's stream (a cudaStream_t; nullptr: the library's own)
+    void set_stream(void *cuda_stream) { check(bf_scene_set_stream(m_h, cuda_stream), "bf_scene_set_stream"); }
     bf_scene *handle() { return m_h; }
 
     void check(int rc, const char *what) const {

@@ -63,6 +63,8 @@ def test_commit_fails_loudly_without_gpu(native):
         s.commit(0)
     with pytest.raises(BeifongError, match="not committed"):
         s.receive(16)
+    with pytest.raises(BeifongError, match="not committed"):
+        s.set_stream(None)                                   # streams exist from bf_scene_commit on
 
 
 def test_error_behaviour_mirrors_reference():
