@@ -6,6 +6,7 @@
 #include <atomic>
 #include <chrono>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <deque>
 #include <limits>
@@ -18,6 +19,13 @@ constexpr int kBins = 16;
 constexpr float kCostNode = 1.0f;   // relative cost of one wide-node visit
 constexpr float kCostTri = 0.3f;    // relative cost of one triangle test
 constexpr uint32_t kLeafMax = 3;    // triangles per leaf child (unary count in 3 bits)
+
+// Share of a wide-node visit charged to one more binary level when a group of <= 3 triangles decides between staying one leaf
+// child and being split further (build-time experiment knob BF_BVH_SPLIT_SHARE; results never depend on the tree shape).
+inline float split_node_share() {
+    static const float v = [] { const char *e = std::getenv("BF_BVH_SPLIT_SHARE"); float x = e ? (float) std::atof(e) : 0.25f; return x > 0.f ? x : 0.25f; }();
+    return v;
+}
 
 struct Ref {
     float lo[3], hi[3];
@@ -120,7 +128,7 @@ struct Builder {
         float area = half_area(lo, hi);
         if (count <= kLeafMax) {
             float leaf_cost = kCostTri * area * (float) count;
-            float split_cost = kCostNode * area * 0.25f + kCostTri * best_cost;  // a binary level is ~1/3 of a wide level
+            float split_cost = kCostNode * area * split_node_share() + kCostTri * best_cost;  // a binary level is a fraction of a wide level
             if (best_axis < 0 || leaf_cost <= split_cost) return;  // stay a leaf
         }
 
