@@ -29,7 +29,7 @@ class RenderScene:
 
 
 def evaluate_render_sample(sc, seed, idx):
-    """-> dict(pos, first_t, valid, value, scalar, depth); None when the BSDF-sampled ray lands on the emitter (not modelled)."""
+    """-> dict(pos, first_t, valid, value, scalar, depth[, on_emitter])."""
     rng = PCG32(tea64(seed, idx), tea64(idx, seed))
     # ---- render_sample head (integrator.cpp:259-274): pixel (0, 0) of a 1 x 1 film, no aperture sample, shutter closed ----
     pos = (rng.next_float(), rng.next_float())
@@ -78,7 +78,14 @@ def evaluate_render_sample(sc, seed, idx):
         t0 = -p1[2] / d2[2]
         q = p1 + t0 * d2
         if abs(q[0] - sc.em_x) <= a and abs(q[1]) <= a:
-            return None                                           # lands on the emitter: the emission + MIS branch is not modelled
+            # The BSDF-sampled ray lands on the emitter (pathlength.cpp:207-226, then the top of the loop at depth 2, :104-109):
+            # emission weighted against emitter sampling, throughput = rho (cosine-sampled diffuse lobe), and the segment
+            # length added twice -- once for the new intersection, once more where the emission is evaluated.
+            bs_pdf = wo[2] / math.pi
+            em_pdf = (1.0 / area) * (t0 * t0) / abs(d2[2])        # Shape::pdf_direction for the point hit
+            w_em = (bs_pdf * bs_pdf) / (bs_pdf * bs_pdf + em_pdf * em_pdf)
+            out["value"], out["scalar"], out["on_emitter"] = res + w_em * sc.rho * sc.radiance, scalar + 2.0 * t0, True
+            return out
         t2 = (sc.floor_z - p1[2]) / d2[2]
         p2 = p1 + t2 * d2
         if abs(p2[0]) <= sc.floor_half and abs(p2[1]) <= sc.floor_half:
