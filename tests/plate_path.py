@@ -110,7 +110,7 @@ class PlateScene:
         return 4.0 * tri(rx) * tri(ry) * sinc(2.0 * math.pi * nux * wid * tri(rx)) * sinc(2.0 * math.pi * nuy * wid * tri(ry))
 
 
-def evaluate_sample(sc, seed, idx, plate_velocity=None):
+def evaluate_sample(sc, seed, idx, plate_velocity=None, max_depth=2):
     """-> dict(first_t, valid, tf_t, tf_f, value, phase, depth, wavelength0) of sample `idx`; None when the path leaves the modelled cases.
     plate_velocity = (vx, vy, vz): the integrator's doppler flag is set and the plate's `velocity` transform is that translation."""
     rng = PCG32(tea64(seed, idx), tea64(idx, seed))
@@ -186,6 +186,34 @@ def evaluate_sample(sc, seed, idx, plate_velocity=None):
         p2 = p1 + t2 * d2
         if abs(p2[0]) <= sc.floor_half and abs(p2[1]) <= sc.floor_half:
             phase = 2.0 * math.pi * (-t2) / denom                 # spawn_ray starts a fresh ray (phase 0); ray_.phase += ray.phase
+            if max_depth >= 3:
+                # ---- second loop iteration, at the floor (pathtimefrequency.cpp:153-345 once more) ----
+                # spawn_ray carries the interaction's time and (resampled) wavelengths; update_state(-t2) advances the time
+                ray_time2 = F(ray_time + F(-t2) / F(sc.c))
+                # NEE: the transmitter faces +z and is seen from below, so `dot(ds.d, ds.n) < 0` fails and the contribution is
+                # masked out -- but sample_direction has already overwritten the interaction's wavelengths with the delta
+                # frequency at ds.time (wignertransmitter.cpp:436-441, unconditional in a scalar variant)
+                s4 = (rng.next_float(), rng.next_float())
+                tl = (2.0 * s4[0] - 1.0, 2.0 * s4[1] - 1.0)
+                p_tx2 = np.array([a * tl[0], sc.tx_y + a * tl[1], 0.0])
+                dist_b = math.sqrt(float((p_tx2 - p2) @ (p_tx2 - p2)))
+                ds_time2 = F(ray_time2 + F(-dist_b) / F(sc.c))
+                lam2 = sc.wavelength_nm(sc.delta_frequency(ds_time2))
+                # BSDF sampling on the floor (frame = world axes), third segment
+                rng.next_float()
+                s5 = (rng.next_float(), rng.next_float())
+                d3 = cosine_hemisphere(*s5)
+                out["depth"] = 3
+                phase = -math.inf
+                if d3[2] > 0.0:
+                    tz = (0.0 - p2[2]) / d3[2]
+                    qz = p2 + tz * d3
+                    if (abs(qz[0]) <= a and abs(qz[1]) <= a) or (abs(qz[0]) <= a and abs(qz[1] - sc.tx_y) <= a):
+                        return None                               # reaches an aperture from behind: not modelled
+                    t3 = (sc.R - p2[2]) / d3[2]
+                    p3 = p2 + t3 * d3
+                    if abs(p3[0]) <= sc.plate_half and abs(p3[1]) <= sc.plate_half:
+                        phase = 2.0 * math.pi * (-t3) / denom
     if plate_velocity is not None:
         # Shape::doppler (src/librender/shape.cpp:375-389) at the statement of pathtimefrequency.cpp:254-256 (commented out in the
         # reference, behind a flag here): 2 * dot(si.wi, velocity * Point3f(si.to_local(si.p))) / MTS_C * si.wavelengths, with the hit

@@ -16,7 +16,7 @@ from plate_path import PlateScene, evaluate_sample
 from record_binning import profile_from_records
 
 
-def build(sc, plate_velocity=None):
+def build(sc, plate_velocity=None, max_depth=2):
     s = FlatScene(spectrum_width=1, **RADAR_94GHZ)
     dflt = s.add_diffuse(0.5, two_sided=False)
     plate_m = s.add_diffuse(sc.rho, two_sided=False)
@@ -32,16 +32,16 @@ def build(sc, plate_velocity=None):
     s.set_receiver(rx, FlatScene.endpoint(N.BF_RX_WIGNER, texture=tex, signal=FlatScene.signal(N.BF_SIG_LINFMCW, sig_is_delta=True, resample_freq=False, **sig),
                                           receive_type=N.BF_RECV_MIX_RESAMPLE, adc_sampling_start=sc.adc_start, adc_sampling_time=sc.adc_time))
     s.set_adc(t_bins=sc.t_bins, f_bins=sc.f_bins, t_bandwidth=sc.t_bw, f_bandwidth=sc.f_bw)
-    s.set_integrator(N.BF_GEN_PHASE, max_depth=2, rr_depth=5, phase_bins=1, doppler=plate_velocity is not None)
+    s.set_integrator(N.BF_GEN_PHASE, max_depth=max_depth, rr_depth=5, phase_bins=1, doppler=plate_velocity is not None)
     return s
 
 
-def check_records(sc, rec, seed, idxs, plate_velocity=None):
+def check_records(sc, rec, seed, idxs, plate_velocity=None, max_depth=2):
     """Every modelled sample of `idxs` against the numpy evaluation."""
     n_checked = n_valid = n_phase = 0
     worst = 0.0
     for i in idxs:
-        e = evaluate_sample(sc, seed, int(i), plate_velocity)
+        e = evaluate_sample(sc, seed, int(i), plate_velocity, max_depth)
         if e is None:
             continue
         r = rec[i]
@@ -150,4 +150,36 @@ def test_device_reproduces_the_independent_path_evaluation(native, pipeline):
     mine, _, _ = profile_from_records(rec, prof.shape[1], prof.shape[0], 1)
     assert np.array_equal(mine[..., 1:3], prof[..., 1:3].astype(np.float64))
     assert np.linalg.norm(mine[..., 0] - prof[..., 0]) <= 1e-5 * np.linalg.norm(mine[..., 0])
+    s.close()
+
+
+def test_oracle_three_segment_path_against_the_independent_evaluation():
+    """max_depth 3: a second loop iteration at the floor.  Its emitter sampling contributes nothing (the transmitter is seen from
+    behind) but resamples the interaction's wavelengths at the later time, so the sample's beat-frequency coordinate moves on by the
+    sweep rate times the extra delay; the time is carried over three segments and the phase comes from the third."""
+    sc = PlateScene()
+    s = build(sc, max_depth=3)
+    orc = OracleScene(s.export(), accel=OracleScene.BRUTE)
+    seed, n = 13, 3000
+    rec = orc.sample_records(n, seed=seed)
+    checked, valid, with_phase, _ = check_records(sc, rec, seed, range(n), max_depth=3)
+    assert checked >= 0.99 * n and valid > 0.15 * n and with_phase > 0.05 * valid       # the third segment meets the plate for ~1 in 10
+    two = OracleScene(build(sc).export(), accel=OracleScene.BRUTE).sample_records(n, seed=seed)
+    deeper = (rec["valid"] == 1) & (rec["depth"] == 3)
+    assert deeper.sum() > 0.1 * n
+    assert np.array_equal(rec["value"][deeper], two["value"][deeper])                    # same radiance ...
+    assert np.median(rec["tf_f"][deeper] - two["tf_f"][deeper]) > 1.0                    # ... binned at a later beat frequency
+    s.close(); orc.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("pipeline", ["wavefront", "mega"])
+def test_device_three_segment_path(native, pipeline):
+    sc = PlateScene()
+    s = build(sc, max_depth=3).commit()
+    s.set_tunable("mega_max", (1 << 28) if pipeline == "mega" else -1)
+    seed, n = 13, 3000
+    rec = s.sample_records(n, seed=seed)
+    checked, valid, with_phase, _ = check_records(sc, rec, seed, range(n), max_depth=3)
+    assert checked >= 0.99 * n and valid > 0.15 * n and with_phase > 0.05 * valid
     s.close()
