@@ -16,13 +16,29 @@ from plate_path import PlateScene, evaluate_sample
 from record_binning import profile_from_records
 
 
-def build(sc, plate_velocity=None, max_depth=2):
+def build(sc, plate_velocity=None, max_depth=2, mesh_plate=None):
     s = FlatScene(spectrum_width=1, **RADAR_94GHZ)
     dflt = s.add_diffuse(0.5, two_sided=False)
     plate_m = s.add_diffuse(sc.rho, two_sided=False)
     rx = s.add_rect((T.scale([sc.a, sc.a, 1.0])).matrix32(), dflt)
     tx = s.add_rect((T.translate([0.0, sc.tx_y, 0.0]) * T.scale([sc.a, sc.a, 1.0])).matrix32(), dflt)
-    plate = s.add_rect((T.translate([0.0, 0.0, sc.R]) * T.rotate([1, 0, 0], 180.0) * T.scale([sc.plate_half, sc.plate_half, 1.0])).matrix32(), plate_m)
+    if mesh_plate:
+        # the same plate as a triangle mesh facing -z (an n x n grid of quads; "smooth": with vertex normals, all (0, 0, -1)): the
+        # first hit then goes through the BVH, Moeller-Trumbore and Mesh::compute_surface_interaction (mesh.cpp:452-548) instead of
+        # the analytic rectangle; without UVs the tangent comes from coordinate_system(n), which for n = (0, 0, -1) gives the
+        # rectangle's own shading frame ((1, 0, 0), (0, -1, 0)), so the independent evaluation applies unchanged
+        g = 6
+        xs = np.linspace(-sc.plate_half, sc.plate_half, g + 1)
+        pos = np.array([[x, y, sc.R] for y in xs for x in xs], np.float32)
+        faces = []
+        for j in range(g):
+            for i in range(g):
+                v = j * (g + 1) + i
+                faces += [[v, v + g + 1, v + 1], [v + 1, v + g + 1, v + g + 2]]       # wound so that the normal is -z
+        nrm = np.tile(np.array([[0.0, 0.0, -1.0]], np.float32), (len(pos), 1)) if mesh_plate == "smooth" else None
+        plate = s.add_mesh(pos, np.array(faces, np.uint32), plate_m, normals=nrm)
+    else:
+        plate = s.add_rect((T.translate([0.0, 0.0, sc.R]) * T.rotate([1, 0, 0], 180.0) * T.scale([sc.plate_half, sc.plate_half, 1.0])).matrix32(), plate_m)
     if plate_velocity is not None:
         s.set_shape_velocity(plate, T.translate(list(plate_velocity)).matrix32())
     s.add_rect((T.translate([0.0, 0.0, sc.floor_z]) * T.scale([sc.floor_half, sc.floor_half, 1.0])).matrix32(), plate_m)
@@ -182,4 +198,32 @@ def test_device_three_segment_path(native, pipeline):
     rec = s.sample_records(n, seed=seed)
     checked, valid, with_phase, _ = check_records(sc, rec, seed, range(n), max_depth=3)
     assert checked >= 0.99 * n and valid > 0.15 * n and with_phase > 0.05 * valid
+    s.close()
+
+
+@pytest.mark.parametrize("mesh_plate", ["flat", "smooth"])
+def test_oracle_mesh_plate_against_the_independent_evaluation(mesh_plate):
+    """The plate as a triangle mesh: BVH / Moeller-Trumbore / Mesh::compute_surface_interaction in place of the analytic rectangle."""
+    sc = PlateScene()
+    s = build(sc, max_depth=3, mesh_plate=mesh_plate)
+    for accel in (OracleScene.BRUTE, OracleScene.BVH):
+        orc = OracleScene(s.export(), accel=accel)
+        rec = orc.sample_records(2000, seed=17)
+        checked, valid, with_phase, _ = check_records(sc, rec, 17, range(2000), max_depth=3)
+        assert checked >= 0.99 * 2000 and valid > 0.15 * 2000 and with_phase > 0.05 * valid
+        assert (rec["first_prim"][rec["valid"] == 1] < 72).all() and len(np.unique(rec["first_prim"][rec["valid"] == 1])) > 20
+        orc.close()
+    s.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("pipeline", ["wavefront", "mega"])
+@pytest.mark.parametrize("mesh_plate", ["flat", "smooth"])
+def test_device_mesh_plate(native, mesh_plate, pipeline):
+    sc = PlateScene()
+    s = build(sc, max_depth=3, mesh_plate=mesh_plate).commit()
+    s.set_tunable("mega_max", (1 << 28) if pipeline == "mega" else -1)
+    rec = s.sample_records(2000, seed=17)
+    checked, valid, with_phase, _ = check_records(sc, rec, 17, range(2000), max_depth=3)
+    assert checked >= 0.99 * 2000 and valid > 0.15 * 2000 and with_phase > 0.05 * valid
     s.close()
