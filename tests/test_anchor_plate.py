@@ -16,8 +16,8 @@ from plate_path import PlateScene, evaluate_sample
 from record_binning import profile_from_records
 
 
-def build(sc, plate_velocity=None, max_depth=2, mesh_plate=None):
-    s = FlatScene(spectrum_width=1, **RADAR_94GHZ)
+def build(sc, plate_velocity=None, max_depth=2, mesh_plate=None, spectrum_width=1):
+    s = FlatScene(spectrum_width=spectrum_width, **RADAR_94GHZ)
     dflt = s.add_diffuse(0.5, two_sided=False)
     plate_m = s.add_diffuse(sc.rho, two_sided=False)
     rx = s.add_rect((T.scale([sc.a, sc.a, 1.0])).matrix32(), dflt)
@@ -52,7 +52,7 @@ def build(sc, plate_velocity=None, max_depth=2, mesh_plate=None):
     return s
 
 
-def check_records(sc, rec, seed, idxs, plate_velocity=None, max_depth=2):
+def check_records(sc, rec, seed, idxs, plate_velocity=None, max_depth=2, value_scale=1.0):
     """Every modelled sample of `idxs` against the numpy evaluation."""
     n_checked = n_valid = n_phase = 0
     worst = 0.0
@@ -60,6 +60,7 @@ def check_records(sc, rec, seed, idxs, plate_velocity=None, max_depth=2):
         e = evaluate_sample(sc, seed, int(i), plate_velocity, max_depth)
         if e is None:
             continue
+        e["value"] *= value_scale
         r = rec[i]
         n_checked += 1
         assert int(r["valid"]) == e["valid"], (i, r, e)
@@ -226,4 +227,28 @@ def test_device_mesh_plate(native, mesh_plate, pipeline):
     rec = s.sample_records(2000, seed=17)
     checked, valid, with_phase, _ = check_records(sc, rec, 17, range(2000), max_depth=3)
     assert checked >= 0.99 * 2000 and valid > 0.15 * 2000 and with_phase > 0.05 * valid
+    s.close()
+
+
+def test_oracle_spectral_variant_against_the_independent_evaluation():
+    """`*_spectral` variants carry four wavelengths; a delta signal gives all four the same frequency (wignerreceiver.cpp:163-175
+    assigns a Float to a Wavelength), so every per-wavelength quantity is the scalar one and aovs[0] = hsum(...) is four times it."""
+    sc = PlateScene()
+    s = build(sc, max_depth=3, spectrum_width=4)
+    orc = OracleScene(s.export(), accel=OracleScene.BRUTE)
+    rec = orc.sample_records(2000, seed=19)
+    checked, valid, _, _ = check_records(sc, rec, 19, range(2000), max_depth=3, value_scale=4.0)
+    assert checked >= 0.99 * 2000 and valid > 0.15 * 2000
+    s.close(); orc.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("pipeline", ["wavefront", "mega"])
+def test_device_spectral_variant(native, pipeline):
+    sc = PlateScene()
+    s = build(sc, max_depth=3, spectrum_width=4).commit()
+    s.set_tunable("mega_max", (1 << 28) if pipeline == "mega" else -1)
+    rec = s.sample_records(2000, seed=19)
+    checked, valid, _, _ = check_records(sc, rec, 19, range(2000), max_depth=3, value_scale=4.0)
+    assert checked >= 0.99 * 2000 and valid > 0.15 * 2000
     s.close()
