@@ -36,8 +36,8 @@ def abi_signal(sg):
                             t_ext=float(sg.T), f_centre=float(sg.f_c), f_ext=float(sg.f_ext), gain=float(sg.gain))
 
 
-def build(sc, var):
-    s = FlatScene(spectrum_width=1, **RADAR_94GHZ)
+def build(sc, var, spectrum_width=1):
+    s = FlatScene(spectrum_width=spectrum_width, **RADAR_94GHZ)
     dflt = s.add_diffuse(0.5, two_sided=False)
     plate_m = s.add_diffuse(sc.rho, two_sided=False)
     rx = s.add_rect((T.scale([sc.a, sc.a, 1.0])).matrix32(), dflt)
@@ -59,9 +59,12 @@ def build(sc, var):
     return s
 
 
-def check_records(sc, var, rec, seed, n):
+def check_records(sc, var, rec, seed, n, value_scale=1.0):
     """Every modelled sample against the numpy evaluation; -> (checked, valid, nonzero, share of values within 2e-3)."""
     ev = [evaluate_sample(sc, var, seed, i) for i in range(n)]
+    for e in ev:
+        if e is not None:
+            e["value"] *= value_scale
     scale = np.median([abs(e["value"]) for e in ev if e is not None and e["value"] != 0.0])
     checked = valid = nonzero = close = 0
     for i, e in enumerate(ev):
@@ -113,4 +116,28 @@ def test_device_reproduces_the_independent_endpoint_evaluation(native, name, pip
     rec = s.sample_records(n, seed=seed)
     checked, valid, nonzero, _ = check_records(sc, var, rec, seed, n)
     assert checked >= 0.99 * n and valid > 0.15 * n and nonzero > 0.8 * valid
+    s.close()
+
+
+def test_oracle_phased_endpoints_spectral_variant():
+    """Four wavelengths: sample_wigner reads wavelength[0] and a delta signal gives all four the same frequency, so hsum(...) is four
+    times the scalar evaluation (phasedreceiver.cpp:264-345 returns a Spectrum broadcast from real(W))."""
+    sc, var = make_variant("phased2")
+    s = build(sc, var, spectrum_width=4)
+    orc = OracleScene(s.export(), accel=OracleScene.BRUTE)
+    rec = orc.sample_records(2000, seed=23)
+    checked, valid, nonzero, _ = check_records(sc, var, rec, 23, 2000, value_scale=4.0)
+    assert checked >= 0.99 * 2000 and valid > 0.15 * 2000 and nonzero > 0.8 * valid
+    s.close(); orc.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("pipeline", ["wavefront", "mega"])
+def test_device_phased_endpoints_spectral_variant(native, pipeline):
+    sc, var = make_variant("phased2")
+    s = build(sc, var, spectrum_width=4).commit()
+    s.set_tunable("mega_max", (1 << 28) if pipeline == "mega" else -1)
+    rec = s.sample_records(2000, seed=23)
+    checked, valid, nonzero, _ = check_records(sc, var, rec, 23, 2000, value_scale=4.0)
+    assert checked >= 0.99 * 2000 and valid > 0.15 * 2000 and nonzero > 0.8 * valid
     s.close()

@@ -106,10 +106,12 @@ def test_profile_small(native, width, pipeline):
     s.close()
 
 
+@pytest.mark.parametrize("width", [1, 4])
 @pytest.mark.parametrize("n_elems,steer", [(1, (0.0, 0.0, 0.0)), (4, (0.0, 0.05, 0.0))])
-def test_phased_endpoints(native, n_elems, steer):
-    """phasedtransmitter + phasedreceiver (a15 / a16): per-sample records and the range profile against the oracle."""
-    s = configs.small_radar(spectrum_width=1, phased=dict(n_elems=n_elems, steer=steer)).commit()
+def test_phased_endpoints(native, n_elems, steer, width):
+    """phasedtransmitter + phasedreceiver (a15 / a16): per-sample records and the range profile against the oracle; width 4 runs the
+    generic (not endpoint-specialised) instantiations of k_primary / k_shade with four wavelengths."""
+    s = configs.small_radar(spectrum_width=width, phased=dict(n_elems=n_elems, steer=steer)).commit()
     orc = OracleScene(s.export(), accel=OracleScene.BVH)
     n = 20000
     g, c = s.sample_records(n, seed=9), orc.sample_records(n, seed=9)
