@@ -1482,6 +1482,14 @@ int bf_scene_set_stream(bf_scene *s, void *cuda_stream) {
         // a handle that is not a stream of this device's context fails here, not inside a later launch
         const cudaError_t e = cudaStreamQuery(next);
         if (e != cudaSuccess && e != cudaErrorNotReady) { cudaGetLastError(); return fail(s, BF_ERR_INVALID, std::string("bf_scene_set_stream: not a usable stream (") + cudaGetErrorString(e) + ")"); }
+        int dev = s->device;
+        if (cudaStreamGetDevice(next, &dev) != cudaSuccess) cudaGetLastError();
+        else if (dev != s->device) return fail(s, BF_ERR_INVALID, "bf_scene_set_stream: the stream belongs to another device than the scene");
+    }
+    if (s->l2_window_touched && s->stream != s->own_stream) {      // leave no access-policy window behind on a stream that is not ours
+        cudaStreamAttrValue a;
+        memset(&a, 0, sizeof(a));
+        if (cudaStreamSetAttribute(s->stream, cudaStreamAttributeAccessPolicyWindow, &a) != cudaSuccess) cudaGetLastError();
     }
     s->stream = next;
     apply_l2_window(s, next);

@@ -362,8 +362,11 @@ int bf_get_stats(const bf_scene *s, bf_stats *stats);
 int bf_last_receive_ms(bf_scene *s, float *total_ms, float *traverse_ms);
 /* Launch-shape knobs of one scene (no reference counterpart; none changes a result).  Names: "wave_lanes" (0 = from the request
  * size), "wave_streams" (waves in flight, 1..16), "fused_primary" (0/1), "primary_defer" / "trace_defer" (-1 = the commit-time
- * estimate, 0, 1), "trace_rounds" (batches of 32 rays per active traversal warp, 0 = whole grid), "use_graph" (0/1).  Defaults are
- * read from the environment variables BF_<NAME> once, in bf_scene_create. */
+ * estimate, 0, 1), "trace_rounds" (batches of 32 rays per active traversal warp, 0 = whole grid), "use_graph" (0/1), "mega_max"
+ * (largest request run as one k_mega launch, -1 = never), "mega_batch" / "path_fused" (0/1), "l2_persist_mb" (MB of the top of the BVH
+ * node array put under a persisting L2 access-policy window; 0 = off, the default: measured no gain on C3 / C5.  The carve-out
+ * `cudaLimitPersistingL2CacheSize` it sets is per DEVICE, shared by every scene on it).  Defaults are read from the environment
+ * variables BF_<NAME> once, in bf_scene_create. */
 int bf_set_tunable(bf_scene *s, const char *name, int64_t value);
 /* Record CUDA events around every traversal launch so that bf_last_receive_ms can report
  * traverse_ms (-1 when disabled, the default). */
