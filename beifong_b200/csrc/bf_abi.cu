@@ -149,7 +149,7 @@ struct WaveSlot {
     Wave wave; uint32_t capacity = 0; std::vector<void *> allocs;
     cudaStream_t stream = nullptr; bool own_stream = false; cudaEvent_t done = nullptr;
     uint32_t *h_counts = nullptr;     // pinned read-back of queue counts
-    uint32_t *path_stash = nullptr;   // k_path's parking areas (path_stash_bytes), allocated on first use
+    uint32_t *path_stash = nullptr; uint32_t stash_cap = 0;   // k_path's parking areas (path_stash_bytes), allocated on first use
     DevRect *d_rects = nullptr; size_t n_rects = 0; DevEndpoint *d_rx = nullptr;   // bf_receive_batch: this slot's copy of the tables an item re-poses
 };
 
@@ -166,6 +166,7 @@ struct Tunables {
     int64_t use_graph = 1;        // small calls: replay the wave's launch sequence from a CUDA graph
     int64_t mega_batch = 1;       // bf_receive_batch: items that k_mega can run go out as one launch
     int64_t path_fused = 1;       // scenes with a deferred primary: k_path integrates the rectangle-only paths in registers
+    int64_t path_stash_max = 65536;   // k_path: most entries of one CTA's parking area (path_stash_cap); 17 (S = 1) / 23 (S = 4) words x 148 CTAs each per wave slot
     int64_t l2_persist_mb = 0;    // > 0: an L2 access-policy window (persisting) over the first MB of the breadth-first BVH node array, i.e. its top levels
     int64_t mega_max = 262144;    // requests up to this many samples, and every request on a scene without meshes (-1: never), run as ONE k_mega launch
 };
@@ -190,6 +191,7 @@ static Tunables tunables_from_env() {
     t.path_fused = env_i64("BF_PATH_FUSED", 1, 0, 1);
     t.mega_max = env_i64("BF_MEGA_MAX", 262144, -1, 1ll << 28);
     t.l2_persist_mb = env_i64("BF_L2_PERSIST_MB", 0, 0, 4096);
+    t.path_stash_max = env_i64("BF_PATH_STASH_MAX", 65536, 1024, 1 << 20);
     return t;
 }
 
@@ -1159,10 +1161,11 @@ static int run_wave(bf_scene *s, WaveSlot &sl, uint64_t seed, uint64_t first, ui
         path = defer && path_ok;
         if (path) {
             if (!sl.path_stash) {
-                BF_CUDA(cudaMalloc((void **) &sl.path_stash, path_stash_bytes(sc, s->sm_count)));
+                sl.stash_cap = path_stash_cap(sl.capacity, s->sm_count, (uint32_t) s->tune.path_stash_max);
+                BF_CUDA(cudaMalloc((void **) &sl.path_stash, path_stash_bytes(sc, s->sm_count, sl.stash_cap)));
                 sl.allocs.push_back(sl.path_stash);
             }
-            timed(BF_K_PRIMARY, [&] { return launch_path(sc, w, seed, first, n, ctr, profile, w.queue_d, sl.path_stash, cfg); });
+            timed(BF_K_PRIMARY, [&] { return launch_path(sc, w, seed, first, n, ctr, profile, w.queue_d, sl.path_stash, sl.stash_cap, cfg); });
             timed(BF_K_TRACE_CLOSEST, [&] { return launch_trace_closest(sc, w, w.queue_d, ctr + 0, 0, 1, ctr + 4, ctr + 3, cfg, false); });
         } else {
             timed(BF_K_PRIMARY, [&] { return launch_primary(sc, w, seed, first, n, ctr + 4, ctr + 2, profile, defer ? w.queue[0] : nullptr, ctr + 0, cfg); });
@@ -1697,7 +1700,7 @@ int bf_set_tunable(bf_scene *s, const char *name, int64_t value) {
         {"trace_defer", &s->tune.trace_defer, -1, 1}, {"trace_rounds", &s->tune.trace_rounds, -1, 1024},
         {"use_graph", &s->tune.use_graph, 0, 1}, {"mega_batch", &s->tune.mega_batch, 0, 1},
         {"path_fused", &s->tune.path_fused, 0, 1}, {"mega_max", &s->tune.mega_max, -1, 1ll << 28},
-        {"l2_persist_mb", &s->tune.l2_persist_mb, 0, 4096}};
+        {"l2_persist_mb", &s->tune.l2_persist_mb, 0, 4096}, {"path_stash_max", &s->tune.path_stash_max, 1024, 1 << 20}};
     for (auto &t : table)
         if (strcmp(t.n, name) == 0) {
             if (value < t.lo || value > t.hi) return fail(s, BF_ERR_INVALID, std::string("bf_set_tunable: value out of range for ") + name);

@@ -1455,11 +1455,21 @@ bool path_kernel_available(const DevScene &sc) {
     return sc.integ.gen == BF_GEN_PHASE && !sc.integ.doppler && sc.n_txs == 1 && (sc.hint_tx_kind == BF_TX_WIGNER || sc.hint_tx_kind == BF_TX_AREA) &&
            (sc.hint_rx_kind == BF_RX_WIGNER || sc.hint_rx_kind == BF_RX_OMNIDIRECTIONAL) && sc.n_nodes != 0;
 }
-size_t path_stash_bytes(const DevScene &sc, int sm_count) {
-    return (size_t) sm_count * (sc.S == 1 ? PathStash<1>::WORDS : PathStash<4>::WORDS) * BF_PATH_STASH_CAP * 4;
+// Entries of one CTA's parking area.  A CTA alternates a generate and a shade phase each time the area fills up, and every switch
+// costs an instruction-cache refill, two CTA-wide barriers and the ragged ends of both phases: measured on C2 (2^25-sample waves,
+// 226 000 samples per CTA of which ~45 % are parked) 8 192 entries 1.055e10 samples/s, 16 384 1.069e10, 32 768 1.085e10, 65 536
+// 1.092e10 (profiles/r02z).  So the area holds what one CTA can park in a wave -- no more than the samples it generates -- between
+// BF_PATH_STASH_CAP and `cap_max` (bf_set_tunable "path_stash_max") entries; a full area only ends the phase early, it never overflows.
+uint32_t path_stash_cap(uint32_t lanes, int sm_count, uint32_t cap_max) {
+    const uint64_t per_cta = ((uint64_t) lanes + (uint64_t) sm_count - 1u) / (uint64_t) std::max(sm_count, 1);
+    const uint64_t cap = (per_cta + PATH_THREADS + 1023u) / 1024u * 1024u;
+    return (uint32_t) std::min<uint64_t>(std::max<uint64_t>(cap, BF_PATH_STASH_CAP), std::max<uint64_t>(cap_max, BF_PATH_STASH_CAP));
+}
+size_t path_stash_bytes(const DevScene &sc, int sm_count, uint32_t cap) {
+    return (size_t) sm_count * (sc.S == 1 ? PathStash<1>::WORDS : PathStash<4>::WORDS) * cap * 4;
 }
 int launch_path(const DevScene &sc, const Wave &w, uint64_t seed, uint64_t first_sample, uint32_t n, uint32_t *ctr, float *profile,
-                uint32_t *defer_queue, uint32_t *stash, const LaunchCfg &cfg) {
+                uint32_t *defer_queue, uint32_t *stash, uint32_t stash_cap, const LaunchCfg &cfg) {
     if (n == 0) return 0;
     PathIO io;
     io.seed = seed; io.first_sample = first_sample; io.n = n;
@@ -1469,7 +1479,7 @@ int launch_path(const DevScene &sc, const Wave &w, uint64_t seed, uint64_t first
     io.next_queue = w.queue[0]; io.next_count = blk1 + 0; io.shadow_count = blk1 + 1;
     const uint32_t floats = sc.channels * sc.film_w * sc.film_h;
     io.hist_floats = floats <= FIN_SMEM_FLOATS ? floats : 0u;
-    io.stash = stash; io.stash_cap = BF_PATH_STASH_CAP;
+    io.stash = stash; io.stash_cap = stash_cap;
     const size_t smem = path_smem_bytes(io.hist_floats);
     const int grid = cfg.sm_count;       // one CTA per SM: the CTA-wide phases are what keeps the instruction cache warm
 #define BF_PATH(S_, R_, T_) k_path<S_, R_, T_><<<grid, PATH_THREADS, smem, cfg.stream>>>(sc, w, io)

@@ -62,9 +62,10 @@ int launch_primary(const DevScene &sc, const Wave &w, uint64_t seed, uint64_t fi
 // (counter layout: ctr + 0 defer_queue length, + 2 work cursor, + 4 / + 5 shade(1) class queues, ctr + BF_CTR_STRIDE + 0 / + 1
 // the continuation / shadow queues that shade(1) appends to).  path_kernel_available: the scene has an instantiation.
 bool path_kernel_available(const DevScene &sc);
-size_t path_stash_bytes(const DevScene &sc, int sm_count);     // per wave slot: the CTAs' parking areas
+uint32_t path_stash_cap(uint32_t lanes, int sm_count, uint32_t cap_max);     // entries per CTA for a wave slot of `lanes` samples
+size_t path_stash_bytes(const DevScene &sc, int sm_count, uint32_t cap);     // per wave slot: the CTAs' parking areas
 int launch_path(const DevScene &sc, const Wave &w, uint64_t seed, uint64_t first_sample, uint32_t n, uint32_t *ctr, float *profile,
-                uint32_t *defer_queue, uint32_t *stash, const LaunchCfg &cfg);
+                uint32_t *defer_queue, uint32_t *stash, uint32_t stash_cap, const LaunchCfg &cfg);
 // k_mega: one thread carries one sample from the receiver ray to its bin (scenes without meshes; small requests)
 int launch_mega(const DevScene &sc, const Wave &w, uint64_t seed, uint64_t first_sample, uint32_t n, uint32_t *work_cursor, float *profile,
                 const LaunchCfg &cfg);
