@@ -603,3 +603,18 @@ def test_develop_reference_property_unit_weights():
     # and a constant non-unit weight rescales every channel by it
     contents[:, :, 2] = 4.0
     assert np.allclose(develop(contents, "float32") * 4.0, contents[:, :, [0, 1, 3, 4]], atol=1e-5)
+
+
+def test_spectra_reference_values():
+    """The reference's own spectrum tests (src/spectra/tests/test_regular.py:22-31: `regular` 500..600 nm with values 1, 2 evaluates
+    to 0, 1, 1.5, 2, 0 at 450, 500, 550, 600, 650 nm; test_irregular.py:22-31: `irregular` (500, 600, 650) -> (1, 2, 0.5) evaluates
+    to 0, 1, 1.5, 2, 0.5, 0 at 450 .. 700 nm), read off the oracle's spectrum evaluation of a scene that holds them."""
+    s = configs.small_radar(spectrum_width=4)
+    reg = s.add_spectrum(N.BF_SPEC_REGULAR, [1.0, 2.0], [500.0, 600.0])
+    irr = s.add_spectrum(N.BF_SPEC_IRREGULAR, [1.0, 2.0, 0.5], [500.0, 600.0, 650.0])
+    orc = OracleScene(s.export(), accel=OracleScene.BRUTE)
+    got = [lib().orc_spectrum_eval(orc._h, reg, 450.0 + 50.0 * i) for i in range(5)]
+    assert np.allclose(got, [0, 1, 1.5, 2, 0])
+    got = [lib().orc_spectrum_eval(orc._h, irr, 450.0 + 50.0 * i) for i in range(6)]
+    assert np.allclose(got, [0, 1, 1.5, 2, 0.5, 0])
+    s.close(); orc.close()
