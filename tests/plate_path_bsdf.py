@@ -14,20 +14,28 @@ import numpy as np
 from plate_path import F, PCG32, cosine_hemisphere, tea64
 
 
-def beckmann_d(m, alpha):
+def microfacet_d(m, alpha, ggx=False):
+    """MicrofacetDistribution::eval (microfacet.h:184-202), isotropic."""
     c = m[2]
     c2 = c * c
-    r = math.exp(-((m[0] / alpha) ** 2 + (m[1] / alpha) ** 2) / c2) / (math.pi * alpha * alpha * c2 * c2)
+    if ggx:
+        r = 1.0 / (math.pi * alpha * alpha * ((m[0] / alpha) ** 2 + (m[1] / alpha) ** 2 + m[2] ** 2) ** 2)
+    else:
+        r = math.exp(-((m[0] / alpha) ** 2 + (m[1] / alpha) ** 2) / c2) / (math.pi * alpha * alpha * c2 * c2)
     return r if r * c > 1e-20 else 0.0
 
 
-def smith_g1(v, m, alpha):
+def smith_g1(v, m, alpha, ggx=False):
+    """microfacet.h:331-355: the rational Beckmann fit, or the closed GGX form."""
     xy = (alpha * v[0]) ** 2 + (alpha * v[1]) ** 2
     if float(v @ m) * v[2] <= 0.0:
         return 0.0
     if xy == 0.0:
         return 1.0
-    a = 1.0 / math.sqrt(xy / (v[2] * v[2]))
+    t2 = xy / (v[2] * v[2])
+    if ggx:
+        return 2.0 / (1.0 + math.sqrt(1.0 + t2))
+    a = 1.0 / math.sqrt(t2)
     return 1.0 if a >= 1.6 else (3.535 * a + 2.181 * a * a) / (1.0 + 2.276 * a + 2.577 * a * a)
 
 
@@ -45,7 +53,7 @@ def fresnel_conductor(cos_i, eta, k):
     return 0.5 * (rs + rp)
 
 
-def evaluate_sample(sc, seed, idx, alpha, eta, k):
+def evaluate_sample(sc, seed, idx, alpha, eta, k, ggx=False):
     """-> dict(first_t, valid, tf_t, tf_f, value) of sample `idx` on a plate of roughconductor(alpha, eta + ik)."""
     rng = PCG32(tea64(seed, idx), tea64(idx, seed))
     pos = (rng.next_float(), rng.next_float())
@@ -89,11 +97,11 @@ def evaluate_sample(sc, seed, idx, alpha, eta, k):
     res = 0.0
     if active and pdf != 0.0 and wi[2] > 0.0 and wo[2] > 0.0:
         H = (wo + wi) / np.linalg.norm(wo + wi)
-        D = beckmann_d(H, alpha)
+        D = microfacet_d(H, alpha, ggx)
         if D != 0.0:
-            G = smith_g1(wi, H, alpha) * smith_g1(wo, H, alpha)
+            G = smith_g1(wi, H, alpha, ggx) * smith_g1(wo, H, alpha, ggx)
             bsdf_val = fresnel_conductor(float(wi @ H), eta, k) * (D * G / (4.0 * wi[2]))
-            bsdf_pdf = D * smith_g1(wi, H, alpha) / (4.0 * wi[2]) if (float(wi @ H) > 0.0 and float(wo @ H) > 0.0) else 0.0
+            bsdf_pdf = D * smith_g1(wi, H, alpha, ggx) / (4.0 * wi[2]) if (float(wi @ H) > 0.0 and float(wo @ H) > 0.0) else 0.0
             mis = (pdf * pdf) / (pdf * pdf + bsdf_pdf * bsdf_pdf)
             res = mis * bsdf_val * tx_val
     out["tf_f"] = abs(sc.c32 * (1.0 / (float(lam2) * 1e-9)) - float(F(f_rx))) * sc.f_bins / sc.f_bw

@@ -16,10 +16,11 @@ from plate_path_bsdf import evaluate_sample
 ALPHA, ETA, K = 0.3, 0.2, 3.0
 
 
-def build(sc, two_sided=False):
+def build(sc, two_sided=False, ggx=False):
     s = FlatScene(spectrum_width=1, **RADAR_94GHZ)
     dflt = s.add_diffuse(0.5, two_sided=False)
-    rough = s.add_bsdf(N.BF_BSDF_ROUGHCONDUCTOR, two_sided=two_sided, eta=s.add_uniform(ETA), k=s.add_uniform(K), alpha_u=ALPHA, alpha_v=ALPHA)
+    rough = s.add_bsdf(N.BF_BSDF_ROUGHCONDUCTOR, two_sided=two_sided, eta=s.add_uniform(ETA), k=s.add_uniform(K), alpha_u=ALPHA, alpha_v=ALPHA,
+                       distribution=N.BF_MICROFACET_GGX if ggx else N.BF_MICROFACET_BECKMANN)
     floor_m = s.add_diffuse(sc.rho, two_sided=False)
     rx = s.add_rect((T.scale([sc.a, sc.a, 1.0])).matrix32(), dflt)
     tx = s.add_rect((T.translate([0.0, sc.tx_y, 0.0]) * T.scale([sc.a, sc.a, 1.0])).matrix32(), dflt)
@@ -35,8 +36,8 @@ def build(sc, two_sided=False):
     return s
 
 
-def check_records(sc, rec, seed, n):
-    ev = [evaluate_sample(sc, seed, i, ALPHA, ETA, K) for i in range(n)]
+def check_records(sc, rec, seed, n, ggx=False):
+    ev = [evaluate_sample(sc, seed, i, ALPHA, ETA, K, ggx) for i in range(n)]
     scale = np.median([abs(e["value"]) for e in ev if e["value"] != 0.0])
     valid = nonzero = 0
     for i, e in enumerate(ev):
@@ -55,24 +56,26 @@ def check_records(sc, rec, seed, n):
     return valid, nonzero
 
 
+@pytest.mark.parametrize("ggx", [False, True])
 @pytest.mark.parametrize("two_sided", [False, True])
-def test_oracle_reproduces_the_independent_roughconductor_evaluation(two_sided):
+def test_oracle_reproduces_the_independent_roughconductor_evaluation(two_sided, ggx):
     sc = PlateScene()
-    s = build(sc, two_sided)
+    s = build(sc, two_sided, ggx)
     orc = OracleScene(s.export(), accel=OracleScene.BRUTE)
     rec = orc.sample_records(3000, seed=29)
-    valid, nonzero = check_records(sc, rec, 29, 3000)
+    valid, nonzero = check_records(sc, rec, 29, 3000, ggx)
     assert valid > 0.15 * 3000 and nonzero > 0.5 * valid
     s.close(); orc.close()
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("ggx", [False, True])
 @pytest.mark.parametrize("pipeline", ["wavefront", "mega"])
-def test_device_reproduces_the_independent_roughconductor_evaluation(native, pipeline):
+def test_device_reproduces_the_independent_roughconductor_evaluation(native, pipeline, ggx):
     sc = PlateScene()
-    s = build(sc, True).commit()
+    s = build(sc, True, ggx).commit()
     s.set_tunable("mega_max", (1 << 28) if pipeline == "mega" else -1)
     rec = s.sample_records(3000, seed=29)
-    valid, nonzero = check_records(sc, rec, 29, 3000)
+    valid, nonzero = check_records(sc, rec, 29, 3000, ggx)
     assert valid > 0.15 * 3000 and nonzero > 0.5 * valid
     s.close()
