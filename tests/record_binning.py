@@ -50,3 +50,66 @@ def profile_from_records(rec, film_w, film_h, phase_bins, mask=None, off_t=0, of
     np.add.at(out[:, 1], pix[sel], (rec["valid"][sel] != 0).astype(np.float64))
     np.add.at(out[:, 2], pix[sel], 1.0)
     return out.reshape(film_h, film_w, C), pix, ch
+
+
+# ---- SignalBlock::put, filters wider than one bin -------------------------------------------------------------------------------
+RAY_EPS = 1500.0 * 2.0 ** -24
+FILTER_RESOLUTION = 31           # MTS_FILTER_RESOLUTION (include/mitsuba/core/rfilter.h)
+
+
+def rfilter_eval(kind, x, radius):
+    """The reference's reconstruction filters, from src/rfilters/{gaussian,tent,mitchell,catmullrom,lanczos}.cpp."""
+    import math
+    x = abs(x)
+    if kind == 1:                                   # gaussian, stddev = radius / 4
+        stddev = radius / 4.0
+        alpha = -1.0 / (2.0 * stddev * stddev)
+        return max(0.0, math.exp(alpha * x * x) - math.exp(alpha * radius * radius))
+    if kind == 2:                                   # tent
+        return max(0.0, 1.0 - x / radius)
+    if kind in (3, 4):                              # mitchell (B = C = 1/3), catmullrom (B = 0, C = 1/2)
+        B, C = (1.0 / 3.0, 1.0 / 3.0) if kind == 3 else (0.0, 0.5)
+        x2, x3 = x * x, x * x * x
+        if x < 1.0:
+            r = (12 - 9 * B - 6 * C) * x3 + (-18 + 12 * B + 6 * C) * x2 + (6 - 2 * B)
+        else:
+            r = (-B - 6 * C) * x3 + (6 * B + 30 * C) * x2 + (-12 * B - 48 * C) * x + (8 * B + 24 * C)
+        return r / 6.0 if x < 2.0 else 0.0
+    if kind == 5:                                   # lanczos, lobes = radius
+        if x < 2.0 ** -24:
+            return 1.0
+        if x > radius:
+            return 0.0
+        x1 = math.pi * x
+        x2 = x1 / radius
+        return (math.sin(x1) * math.sin(x2)) / (x1 * x2)
+    raise ValueError(kind)
+
+
+def wide_splat(size_x, size_y, kind, radius, px, py, off=(0, 0)):
+    """One unit-valued sample splatted by SignalBlock::put's wide branch (src/librender/signalblock.cpp:107-160) over the discretised
+    filter (rfilter.cpp:9-20, rfilter.h:62-65) into a block with its border, then cropped to the storage as ADC::put(block) does
+    (signalblock.cpp:49-77).  Written from the reference text; compared with the oracle's splat in tests/test_oracle_kat.py."""
+    import math
+    table = [rfilter_eval(kind, radius * i / FILTER_RESOLUTION, radius) for i in range(FILTER_RESOLUTION)] + [0.0]
+    scale = FILTER_RESOLUTION / radius
+    border = int(math.ceil(radius - 0.5 - 2.0 * RAY_EPS))
+    sx, sy = size_x + 2 * border, size_y + 2 * border
+    pos = (px - (off[0] - border + 0.5), py - (off[1] - border + 0.5))
+    lo = (max(math.ceil(pos[0] - radius), 0), max(math.ceil(pos[1] - radius), 0))
+    hi = (min(math.floor(pos[0] + radius), sx - 1), min(math.floor(pos[1] + radius), sy - 1))
+    n = int(math.ceil((radius - 2.0 * RAY_EPS) * 2.0))
+    w = lambda x: table[min(int(abs(x * scale)), FILTER_RESOLUTION)]
+    wx = [w(lo[0] - pos[0] + i) for i in range(n)]
+    wy = [w(lo[1] - pos[1] + i) for i in range(n)]
+    data = np.zeros((sy, sx))
+    for yr in range(n):
+        y = lo[1] + yr
+        if y > hi[1]:
+            continue
+        for xr in range(n):
+            x = lo[0] + xr
+            if x > hi[0]:
+                break
+            data[y, x] += wy[yr] * wx[xr]
+    return data[border:border + size_y, border:border + size_x]

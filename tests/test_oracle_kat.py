@@ -618,3 +618,21 @@ def test_spectra_reference_values():
     got = [lib().orc_spectrum_eval(orc._h, irr, 450.0 + 50.0 * i) for i in range(6)]
     assert np.allclose(got, [0, 1, 1.5, 2, 0.5, 0])
     s.close(); orc.close()
+
+
+def test_wide_splat_against_independent_restatement():
+    """SignalBlock::put's wide branch restated in numpy from the reference text (tests/record_binning.py: footprint lo / hi, the n
+    weights per axis from the discretised filter, the border and its crop) against the oracle's splat, for all five rfilter plugins at
+    random sample positions including ones outside the window."""
+    from record_binning import wide_splat
+    rng = np.random.default_rng(3)
+    for kind, radius in ((1, 2.0), (2, 1.0), (3, 2.0), (4, 2.0), (5, 3.0)):
+        worst = 0.0
+        for _ in range(150):
+            px, py = rng.uniform(-3.5, 15.5, size=2)
+            off = (int(rng.integers(0, 3)), int(rng.integers(0, 3)))
+            a = _splat(12, 9, kind, radius, float(px) + off[0], float(py) + off[1], off=off).astype(np.float64)
+            b = wide_splat(12, 9, kind, radius, float(np.float32(px + off[0])), float(np.float32(py + off[1])), off=off)
+            worst = max(worst, float(np.abs(a - b).max()))
+            assert np.array_equal(a != 0, np.abs(b) > 1e-9) or np.abs(a - b).max() <= 2e-6, (kind, px, py)
+        assert worst <= 2e-6, (kind, worst)
