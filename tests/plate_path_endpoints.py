@@ -125,8 +125,9 @@ def rect_wigner(local_xy, dvec, lam_nm, wid):
 class Variant:
     """What differs from plate_path.evaluate_sample: the endpoint plugins and their signal blocks."""
 
-    def __init__(self, sc, endpoints="wigner", rx_signal=None, tx_signal=None, n_elems=2, steer=(0.0, 0.2, 0.0)):
+    def __init__(self, sc, endpoints="wigner", rx_signal=None, tx_signal=None, n_elems=2, steer=(0.0, 0.2, 0.0), second_tx=None):
         self.endpoints = endpoints
+        self.second_tx = second_tx      # dict(y=..., gain=...): a second wignertransmitter on its own aperture (Scene::sample_transmitter_direction picks one)
         base = dict(repfreq=sc.repfreq, t_ext=sc.t_ext, f_c=sc.f_c, f_ext=sc.f_ext)
         self.rx_signal = rx_signal or Signal("linfmcw", True, False, **base)
         self.tx_signal = tx_signal or Signal("linfmcw", True, True, **base)
@@ -184,8 +185,16 @@ def evaluate_sample(sc, var, seed, idx):
     ray_time = F(time + F(-t1) / F(sc.c))                         # Ray::update_state, ray.h:89-93
     # ---- NEE: Scene::sample_transmitter_direction -> Transmitter::sample_direction ----
     s2 = (rng.next_float(), rng.next_float())
+    tx_y, tx_gain, pick = sc.tx_y, 1.0, 1.0
+    if var.second_tx is not None:
+        # scene.cpp:262-274: index = min(uint(sample.x * n), n - 1); the sample is re-stretched, pdf *= 1 / n, value *= n
+        index = min(int(float(F(F(s2[0]) * F(2.0)))), 1)
+        s2 = (float(F(F(F(s2[0]) - F(index) * F(0.5)) * F(2.0))), s2[1])
+        pick = 0.5
+        if index == 1:
+            tx_y, tx_gain = var.second_tx["y"], var.second_tx["gain"]
     tloc = (2.0 * s2[0] - 1.0, 2.0 * s2[1] - 1.0)
-    p_tx = np.array([a * tloc[0], sc.tx_y + a * tloc[1], 0.0])
+    p_tx = np.array([a * tloc[0], tx_y + a * tloc[1], 0.0])
     dv = p_tx - p1
     dist2 = float(dv @ dv); dist = math.sqrt(dist2); dv = dv / dist
     dp = abs(dv[2])
@@ -206,8 +215,10 @@ def evaluate_sample(sc, var, seed, idx):
         pdf = abs(pdf * wgain)
     else:
         wgain = rect_wigner(tloc, -dv, lam2, 2.0 * a)             # wignertransmitter.cpp:443-452
-        tx_val = power_tx * float(ts.gain) * geom * wgain * ((1.0 / area) * 2.0 * math.pi)
+        tx_val = power_tx * float(ts.gain) * tx_gain * geom * wgain * ((1.0 / area) * 2.0 * math.pi)
         pdf = pdf * wgain
+    pdf *= pick                                                   # ds.pdf *= transmitter_pdf; spec *= rcp(transmitter_pdf)
+    tx_val *= 1.0 / pick
     if not active:
         tx_val = 0.0
     # diffuse plate facing -z (src/bsdfs/diffuse.cpp:78-135) and the MIS weight of pathtimefrequency.cpp:276-300, 472-477
@@ -226,7 +237,8 @@ def evaluate_sample(sc, var, seed, idx):
     if d2[2] < 0.0:
         t0 = (0.0 - p1[2]) / d2[2]
         q = p1 + t0 * d2
-        if (abs(q[0]) <= a and abs(q[1]) <= a) or (abs(q[0]) <= a and abs(q[1] - sc.tx_y) <= a):
+        ys = [0.0, sc.tx_y] + ([var.second_tx["y"]] if var.second_tx is not None else [])
+        if any(abs(q[0]) <= a and abs(q[1] - y0) <= a for y0 in ys):
             return None                                            # lands on an aperture: not modelled
     # ---- receive_sample tail: integrator.cpp:1588-1665 ----
     out["tf_f"] = abs(frequency_of(sc.c32, lam2) - float(f_rx)) * sc.f_bins / sc.f_bw

@@ -25,6 +25,9 @@ def make_variant(name):
         sc = PlateScene()
         n = int(name[len("phased"):])
         return sc, Variant(sc, endpoints="phased", n_elems=n, steer=(0.0, 0.2, 0.0) if n == 2 else (0.1, -0.15, 0.0))
+    if name == "two_tx":
+        sc = PlateScene()
+        return sc, Variant(sc, second_tx=dict(y=-0.02, gain=0.25))
     sc = PlateScene(f_ext=2e6, t_ext=150e-6, adc_start=5e-6, adc_time=140e-6, f_bw=3.0e6)
     kind = {"pulse": "pulse", "cw": "cw", "fmcw_nodelta": "linfmcw"}[name]
     base = dict(repfreq=sc.repfreq, t_ext=sc.t_ext, f_c=sc.f_c, f_ext=sc.f_ext, amplitude=1.5, gain=0.5)
@@ -52,6 +55,12 @@ def build(sc, var, spectrum_width=1):
         tx_kind, rx_kind = N.BF_TX_PHASED, N.BF_RX_PHASED
         tx_arr, rx_arr = arr(T.translate([0.0, sc.tx_y, 0.0])), arr(T.translate([0.0, 0.0, 0.0]))
     s.add_transmitter(tx, FlatScene.endpoint(tx_kind, texture=tex, signal=abi_signal(var.tx_signal), array=tx_arr))
+    if var.second_tx is not None:
+        import copy
+        sg2 = copy.copy(var.tx_signal)
+        sg2.gain = np.float32(float(var.tx_signal.gain) * var.second_tx["gain"])
+        tx2 = s.add_rect((T.translate([0.0, var.second_tx["y"], 0.0]) * T.scale([sc.a, sc.a, 1.0])).matrix32(), dflt)
+        s.add_transmitter(tx2, FlatScene.endpoint(tx_kind, texture=tex, signal=abi_signal(sg2)))
     s.set_receiver(rx, FlatScene.endpoint(rx_kind, texture=tex, signal=abi_signal(var.rx_signal), receive_type=N.BF_RECV_MIX_RESAMPLE,
                                           adc_sampling_start=sc.adc_start, adc_sampling_time=sc.adc_time, array=rx_arr))
     s.set_adc(t_bins=sc.t_bins, f_bins=sc.f_bins, t_bandwidth=sc.t_bw, f_bandwidth=sc.f_bw)
@@ -90,7 +99,7 @@ def check_records(sc, var, rec, seed, n, value_scale=1.0):
     return checked, valid, nonzero, close / max(valid, 1)
 
 
-VARIANTS = ["phased2", "phased3", "pulse", "cw", "fmcw_nodelta"]
+VARIANTS = ["phased2", "phased3", "pulse", "cw", "fmcw_nodelta", "two_tx"]
 
 
 @pytest.mark.parametrize("name", VARIANTS)
