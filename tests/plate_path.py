@@ -227,5 +227,6 @@ def evaluate_sample(sc, seed, idx, plate_velocity=None, max_depth=2):
     f_end = sc.c32 * (1.0 / (float(lam2) * 1e-9))
     out["tf_f"] = abs(f_end - float(F(f_rx))) * sc.f_bins / sc.f_bw      # f_rx is stored in a fp32 Wavelength (:1592)
     out["value"] = abs(weight) * res
+    out["radiance"] = res                                         # what the PhaseIntegrator writes to its AOV: hsum(L) before the ray weight (phase.cpp:117-124)
     out["phase"] = phase
     return out

@@ -252,3 +252,40 @@ def test_device_spectral_variant(native, pipeline):
     checked, valid, _, _ = check_records(sc, rec, 19, range(2000), max_depth=3, value_scale=4.0)
     assert checked >= 0.99 * 2000 and valid > 0.15 * 2000
     s.close()
+
+
+def test_oracle_phase_bins_and_window_offsets_against_numpy_binning():
+    """PhaseIntegrator with 8 phase bins (phase.cpp:117-124) and a cropped ADC window with offsets (adc.cpp:29-47): the oracle's
+    binned profile against the numpy restatement of the binning (tests/record_binning.py) applied to its own per-sample records."""
+    from record_binning import phase_channel
+    sc = PlateScene()
+    s = build(sc, max_depth=3)
+    s.set_integrator(N.BF_GEN_PHASE, max_depth=3, rr_depth=5, phase_bins=8)
+    s.set_adc(t_bins=sc.t_bins, f_bins=sc.f_bins, t_bandwidth=sc.t_bw, f_bandwidth=sc.f_bw, window_f_bins=96, window_offset_f=40, window_t_bins=3, window_offset_t=1)
+    orc = OracleScene(s.export(), accel=OracleScene.BRUTE)
+    n = 20000
+    rec = orc.sample_records(n, seed=31)
+    prof = orc.receive(n, seed=31, threads=1)
+    assert prof.shape == (96, 3, 3 + 8)
+    mine, pix, ch = profile_from_records(rec, 3, 96, 8, off_t=1, off_f=40)
+    assert np.array_equal(mine[..., 1:3], prof[..., 1:3].astype(np.float64))           # valid and weight counts, bin by bin
+    assert np.linalg.norm(mine[..., 0] - prof[..., 0]) <= 1e-5 * np.linalg.norm(mine[..., 0])
+    # the phase AOVs hold the integrator's UNWEIGHTED hsum(L) (phase.cpp:117-124 runs inside sample(), before receive_sample applies
+    # |ray_weight|), in the channel of the sample's phase bin: L comes from the independent evaluation, bin and channel from the records
+    aov = np.zeros((96 * 3, 8))
+    unmodelled = np.zeros(96 * 3, bool)
+    for i in range(n):
+        if pix[i] < 0 or not rec["valid"][i]:
+            continue
+        e = evaluate_sample(sc, 31, i, None, 3)
+        if e is None:
+            unmodelled[pix[i]] = True
+        elif ch[i] >= 0:
+            aov[pix[i], ch[i]] += e["radiance"]
+    got = prof[..., 3:].reshape(-1, 8).astype(np.float64)
+    assert (np.abs(got).sum(axis=0) > 0).sum() >= 6                                    # spread over the bins, not piled into one
+    clean = ~unmodelled
+    assert clean.mean() > 0.5 and np.abs(aov[clean]).sum() > 0
+    assert np.linalg.norm(got[clean] - aov[clean]) <= 2e-3 * np.linalg.norm(aov[clean])
+    assert 0 < (pix >= 0).sum() < n                                                    # the window really crops
+    s.close(); orc.close()
