@@ -165,3 +165,17 @@ def test_serialized_reference_fixtures(features):
         assert nrm is None
         assert np.allclose(meshes.vertex_normals(pos, faces)[[0, 2, 3]], [0.0, 1.0, 0.0], atol=1e-6) or \
             np.allclose(meshes.vertex_normals(pos, faces)[[0, 2, 3]], [0.0, -1.0, 0.0], atol=1e-6)
+
+
+def test_tunables_by_name():
+    """bf_set_tunable: every documented knob is accepted before the commit (none changes a result), ranges and names are checked."""
+    s = configs.small_radar()
+    for name, value in (("wave_lanes", 1 << 22), ("wave_streams", 4), ("fused_primary", 1), ("primary_defer", -1), ("trace_defer", 0),
+                        ("trace_rounds", 16), ("use_graph", 1), ("mega_batch", 0), ("path_fused", 1), ("mega_max", -1),
+                        ("l2_persist_mb", 0), ("path_stash_max", 32768)):
+        s.set_tunable(name, value)
+    with pytest.raises(BeifongError, match="out of range"):
+        s.set_tunable("wave_streams", 99)
+    with pytest.raises(BeifongError, match="unknown tunable"):
+        s.set_tunable("no_such_knob", 1)
+    s.close()
